@@ -1,0 +1,482 @@
+#pragma once
+#include <stdint.h>
+
+/* Inferred minimum I/O channel counts (from splN usage / pin declarations) */
+#define DSPJSFX_INPUT_CHANNELS 2
+#define DSPJSFX_OUTPUT_CHANNELS 2
+#define DSPJSFX_PROCESS_CHANNELS 2
+#define DSPJSFX_USES_MIDI 0
+#define DSPJSFX_USES_GMEM 0
+#define DSPJSFX_USES_MSG 0
+#define DSPJSFX_USES_MSG_BUFFERS 0
+#define DSPJSFX_USES_SAMPLE_POOL 0
+#define DSPJSFX_USES_RAW_SAMPLE_READ 0
+#define DSPJSFX_USES_SAMPLE_EXPORT_MEM 0
+#define DSPJSFX_USES_LEGACY_FILE_IO 0
+#define DSPJSFX_COMM_API_VERSION 1
+#define DSPJSFX_SAMPLE_POOL_API_VERSION 1
+#define DSPJSFX_ACCEPTS_MIDI_INPUT 0
+#define DSPJSFX_PRODUCES_MIDI_OUTPUT 0
+#define DSPJSFX_HAS_SAMPLE_SECTION 1
+#define DSPJSFX_PLUGIN_KIND "audio_effect"
+
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct DSPJSFX_MidiEvent {
+    int32_t sampleOffset;
+    int32_t msg1;
+    int32_t msg2;
+    int32_t msg3;
+} DSPJSFX_MidiEvent;
+
+typedef struct DSPJSFX_State {
+    double spl[64];
+    double sliders[64];
+    double vars[144];
+    double* mem;
+    int64_t memN;
+    double srate;
+    double samplesblock;
+    DSPJSFX_MidiEvent* midiIn;
+    int32_t midiInCount;
+    int32_t midiInReadIndex;
+    int32_t midiInCapacity;
+    DSPJSFX_MidiEvent* midiOut;
+    int32_t midiOutCount;
+    int32_t midiOutCapacity;
+    int32_t currentBlockSize;
+    double currentSampleRate;
+    int32_t pendingNoteCleanup;
+    int32_t midiInDropped;
+    int32_t midiOutDropped;
+    int32_t midiInCountLastBlock;
+    int32_t midiOutCountLastBlock;
+    int32_t midiInPeak;
+    int32_t midiOutPeak;
+    int64_t pendingSliderChangeMask;
+    int64_t pendingSliderAutomateMask;
+    int64_t pendingSliderAutomateEndMask;
+    uint32_t randMT[624];
+    uint32_t randIndex;
+    int64_t sliderVisibleMask;
+    int32_t sliderVisibilityInit;
+    void* runtimeOpaque;
+    double midi_bus;
+    double ext_midi_bus;
+} DSPJSFX_State;
+
+/* User vars (name -> vars[] index) */
+typedef struct DSPJSFX_VarDesc { const char* name; int32_t index; } DSPJSFX_VarDesc;
+#define DSPJSFX_VARS_COUNT 144
+static const DSPJSFX_VarDesc DSPJSFX_VARS[144] = {
+    {"BUF_LEN", 0},
+    {"BUF_MASK", 1},
+    {"EPS", 2},
+    {"MAX_TAPS", 3},
+    {"__fnlocal__slider__alpha_lp__a", 4},
+    {"__fnlocal__slider__rebuild_taps__acc", 5},
+    {"__fnlocal__slider__rebuild_taps__air", 6},
+    {"__fnlocal__slider__rebuild_taps__b0", 7},
+    {"__fnlocal__slider__rebuild_taps__b1", 8},
+    {"__fnlocal__slider__rebuild_taps__bal", 9},
+    {"__fnlocal__slider__rebuild_taps__binI", 10},
+    {"__fnlocal__slider__rebuild_taps__binN", 11},
+    {"__fnlocal__slider__rebuild_taps__binSum", 12},
+    {"__fnlocal__slider__rebuild_taps__dMs", 13},
+    {"__fnlocal__slider__rebuild_taps__dS", 14},
+    {"__fnlocal__slider__rebuild_taps__decayMs", 15},
+    {"__fnlocal__slider__rebuild_taps__diffW", 16},
+    {"__fnlocal__slider__rebuild_taps__directW", 17},
+    {"__fnlocal__slider__rebuild_taps__dist", 18},
+    {"__fnlocal__slider__rebuild_taps__fcD", 19},
+    {"__fnlocal__slider__rebuild_taps__fcE", 20},
+    {"__fnlocal__slider__rebuild_taps__fcL", 21},
+    {"__fnlocal__slider__rebuild_taps__gL", 22},
+    {"__fnlocal__slider__rebuild_taps__gMaxTap", 23},
+    {"__fnlocal__slider__rebuild_taps__gR", 24},
+    {"__fnlocal__slider__rebuild_taps__gTap", 25},
+    {"__fnlocal__slider__rebuild_taps__hiBin", 26},
+    {"__fnlocal__slider__rebuild_taps__i", 27},
+    {"__fnlocal__slider__rebuild_taps__itdAbsMax", 28},
+    {"__fnlocal__slider__rebuild_taps__itdMaxS", 29},
+    {"__fnlocal__slider__rebuild_taps__level", 30},
+    {"__fnlocal__slider__rebuild_taps__level_db", 31},
+    {"__fnlocal__slider__rebuild_taps__loBin", 32},
+    {"__fnlocal__slider__rebuild_taps__maxMs", 33},
+    {"__fnlocal__slider__rebuild_taps__maxMsQ", 34},
+    {"__fnlocal__slider__rebuild_taps__maxT", 35},
+    {"__fnlocal__slider__rebuild_taps__minMs", 36},
+    {"__fnlocal__slider__rebuild_taps__offMs", 37},
+    {"__fnlocal__slider__rebuild_taps__powExp", 38},
+    {"__fnlocal__slider__rebuild_taps__q", 39},
+    {"__fnlocal__slider__rebuild_taps__room", 40},
+    {"__fnlocal__slider__rebuild_taps__roomScaleT", 41},
+    {"__fnlocal__slider__rebuild_taps__roomScaleW", 42},
+    {"__fnlocal__slider__rebuild_taps__sc", 43},
+    {"__fnlocal__slider__rebuild_taps__seed", 44},
+    {"__fnlocal__slider__rebuild_taps__sp", 45},
+    {"__fnlocal__slider__rebuild_taps__splitMs", 46},
+    {"__fnlocal__slider__rebuild_taps__sumW", 47},
+    {"__fnlocal__slider__rebuild_taps__tNorm", 48},
+    {"__fnlocal__slider__rebuild_taps__u", 49},
+    {"__fnlocal__slider__rebuild_taps__v", 50},
+    {"__fnlocal__slider__rebuild_taps__w", 51},
+    {"__fnlocal__slider__rebuild_taps__wet", 52},
+    {"__fnlocal__slider__rebuild_taps__wid", 53},
+    {"aM", 54},
+    {"a_dir", 55},
+    {"a_early", 56},
+    {"a_late", 57},
+    {"bD0", 58},
+    {"bDL", 59},
+    {"bDR", 60},
+    {"bGL", 61},
+    {"bGR", 62},
+    {"bL", 63},
+    {"bR", 64},
+    {"bSCR", 65},
+    {"bW", 66},
+    {"baseD", 67},
+    {"c", 68},
+    {"col", 69},
+    {"dInL", 70},
+    {"dInR", 71},
+    {"dL", 72},
+    {"dR", 73},
+    {"diffGainTotal", 74},
+    {"dirZL", 75},
+    {"dirZR", 76},
+    {"directGain", 77},
+    {"distN", 78},
+    {"dryp", 79},
+    {"eZL", 80},
+    {"eZR", 81},
+    {"found", 82},
+    {"g", 83},
+    {"gL", 84},
+    {"gR", 85},
+    {"g_dist_m", 86},
+    {"g_fcD", 87},
+    {"g_fcE", 88},
+    {"g_fcL", 89},
+    {"g_gMaxTap", 90},
+    {"g_itdMaxS", 91},
+    {"g_itdPlotMax", 92},
+    {"g_maxMs", 93},
+    {"g_minMs", 94},
+    {"g_roomScaleT", 95},
+    {"g_roomScaleW", 96},
+    {"g_splitMs", 97},
+    {"g_zoomMaxMs", 98},
+    {"g_zoomMinMs", 99},
+    {"gfx_ext_retina", 100},
+    {"gfx_h", 101},
+    {"gfx_w", 102},
+    {"i", 103},
+    {"idxL", 104},
+    {"idxR", 105},
+    {"itd", 106},
+    {"j", 107},
+    {"lZL", 108},
+    {"lZR", 109},
+    {"m", 110},
+    {"m_diffCorr", 111},
+    {"m_diffL", 112},
+    {"m_diffR", 113},
+    {"m_dirE", 114},
+    {"m_earlyE", 115},
+    {"m_lateE", 116},
+    {"m_totalE", 117},
+    {"mon", 118},
+    {"mono", 119},
+    {"oL", 120},
+    {"oR", 121},
+    {"out_gain", 122},
+    {"padT", 123},
+    {"r", 124},
+    {"s_abs", 125},
+    {"s_dir", 126},
+    {"s_ear", 127},
+    {"s_lat", 128},
+    {"s_tot", 129},
+    {"splitSamp", 130},
+    {"srcL", 131},
+    {"srcR", 132},
+    {"sumEL", 133},
+    {"sumER", 134},
+    {"sumLL", 135},
+    {"sumLR", 136},
+    {"tapN", 137},
+    {"wetp", 138},
+    {"wofs", 139},
+    {"xL", 140},
+    {"xR", 141},
+    {"yL", 142},
+    {"yR", 143},
+};
+
+/* @gfx user-var sync flags (vars[] index).
+   bit0: sync audio-owned updates into the @gfx VM (audio -> gfx)
+   bit1: feed @gfx-authored writes back into the DSP state (gfx -> audio)
+   Mode: legacy */
+#define DSPJSFX_GFX_VAR_FLAG_TO_GFX 1u
+#define DSPJSFX_GFX_VAR_FLAG_FROM_GFX 2u
+#define DSPJSFX_GFX_VAR_FLAGS_COUNT 144
+static const uint8_t DSPJSFX_GFX_VAR_FLAGS[144] = {
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+    3,
+};
+
+/* String literals (opaque runtime handles used by MIDI/string helpers) */
+typedef struct DSPJSFX_StringLiteralDesc { int64_t handle; int32_t length; const uint8_t* data; } DSPJSFX_StringLiteralDesc;
+#define DSPJSFX_STRING_LITERALS_COUNT 0
+static const uint8_t DSPJSFX_STRING_LITERAL_BYTES_0[1] = { 0 };
+static const DSPJSFX_StringLiteralDesc DSPJSFX_STRING_LITERALS[1] = {
+    { 0LL, 0, DSPJSFX_STRING_LITERAL_BYTES_0 },
+};
+
+/* Sections */
+void jsfx_init(DSPJSFX_State* st);
+void jsfx_slider(DSPJSFX_State* st);
+void jsfx_block(DSPJSFX_State* st);
+void jsfx_sample(DSPJSFX_State* st);
+
+/* Entry point intended to be called from JUCE processBlock().
+   inputs/outputs are arrays of channel pointers (non-interleaved). */
+void jsfx_process_block(DSPJSFX_State* st,
+                        const float* const* inputs,
+                        float* const* outputs,
+                        int32_t numChannels,
+                        int32_t numSamples);
+
+/* Runtime hook required by mem[] growth checks. You must provide this when linking.
+   Even if you never exceed memN, the symbol must exist. */
+void jsfx_ensure_mem(DSPJSFX_State* st, int64_t needed);
+int jsfx_midirecv(DSPJSFX_State* st, double* offset, double* msg1, double* msg2, double* msg3);
+int jsfx_midirecv_msg23(DSPJSFX_State* st, double* offset, double* msg1, double* msg23);
+int jsfx_midirecv_buf(DSPJSFX_State* st, double* offset, double buf, double maxlen);
+int jsfx_midirecv_str(DSPJSFX_State* st, double* offset, double* strSlot);
+int jsfx_midisend(DSPJSFX_State* st, double offset, double msg1, double msg2, double msg3);
+int jsfx_midisend_msg23(DSPJSFX_State* st, double offset, double msg1, double msg23);
+int jsfx_midisend_buf(DSPJSFX_State* st, double offset, double buf, double len);
+int jsfx_midisend_str(DSPJSFX_State* st, double offset, double strHandle);
+int jsfx_midisyx(DSPJSFX_State* st, double offset, double msgptr, double len);
+int jsfx_strlen(DSPJSFX_State* st, double strHandle);
+int jsfx_str_getchar(DSPJSFX_State* st, double strHandle, double index);
+int jsfx_sliderchange(DSPJSFX_State* st, double sliderMask);
+int jsfx_slider_automate(DSPJSFX_State* st, double sliderMask, double endTouch);
+double jsfx_slider_next_chg(DSPJSFX_State* st, double sliderIndex, double* outValue);
+double jsfx_instance_id(DSPJSFX_State* st);
+int jsfx_instance_uid(DSPJSFX_State* st, double* outStr);
+int jsfx_instance_set_name(DSPJSFX_State* st, double strHandle);
+int jsfx_instance_get_name(DSPJSFX_State* st, double* outStr);
+int jsfx_track_name(DSPJSFX_State* st, double* outStr);
+double jsfx_track_name_available(DSPJSFX_State* st);
+double jsfx_track_name_seq(DSPJSFX_State* st);
+int jsfx_comm_join(DSPJSFX_State* st, double domainHandle);
+int jsfx_gmem_attach(DSPJSFX_State* st, double nameHandle);
+int jsfx_gmem_attach_size(DSPJSFX_State* st, double nameHandle, double cells);
+double jsfx_gmem_size(DSPJSFX_State* st);
+double jsfx_gmem_load(DSPJSFX_State* st, double idx);
+double jsfx_gmem_store(DSPJSFX_State* st, double idx, double value);
+int jsfx_gmem_get(DSPJSFX_State* st, double dstBase, double srcIdx, double count);
+int jsfx_gmem_put(DSPJSFX_State* st, double dstIdx, double srcBase, double count);
+int jsfx_gmem_fill(DSPJSFX_State* st, double dstIdx, double value, double count);
+int jsfx_gmem_zero(DSPJSFX_State* st, double dstIdx, double count);
+int jsfx_gmem_copy(DSPJSFX_State* st, double dstIdx, double srcIdx, double count);
+double jsfx_gmem_seq(DSPJSFX_State* st, double page);
+double jsfx_gmem_page(DSPJSFX_State* st, double idx);
+int jsfx_msg_subscribe(DSPJSFX_State* st, double chanHandle);
+int jsfx_msg_unsubscribe(DSPJSFX_State* st, double chanHandle);
+int jsfx_msg_advertise(DSPJSFX_State* st, double chanHandle, double caps);
+int jsfx_msg_send(DSPJSFX_State* st, double chanHandle, double tag, double a, double b, double c, double d);
+int jsfx_msg_sendto(DSPJSFX_State* st, double targetId, double chanHandle, double tag, double a, double b, double c, double d);
+double jsfx_msg_avail(DSPJSFX_State* st, double chanHandle);
+double jsfx_msg_kind(DSPJSFX_State* st, double chanHandle);
+int jsfx_msg_recv(DSPJSFX_State* st, double chanHandle, double* src, double* tag, double* a, double* b, double* c, double* d);
+int jsfx_msg_send_buf(DSPJSFX_State* st, double chanHandle, double tag, double srcBase, double len);
+int jsfx_msg_sendto_buf(DSPJSFX_State* st, double targetId, double chanHandle, double tag, double srcBase, double len);
+int jsfx_msg_recv_buf(DSPJSFX_State* st, double chanHandle, double* src, double* tag, double dstBase, double maxLen);
+double jsfx_msg_length(DSPJSFX_State* st);
+double jsfx_msg_dropped(DSPJSFX_State* st, double chanHandle);
+int jsfx_msg_clear(DSPJSFX_State* st, double chanHandle);
+double jsfx_msg_peer_count(DSPJSFX_State* st, double chanHandle, double role);
+double jsfx_msg_peer_id(DSPJSFX_State* st, double chanHandle, double role, double index);
+int jsfx_msg_peer_name(DSPJSFX_State* st, double peerId, double* outStr);
+int jsfx_msg_peer_uid(DSPJSFX_State* st, double peerId, double* outStr);
+double jsfx_msg_peer_caps(DSPJSFX_State* st, double peerId);
+double jsfx_msg_peer_alive(DSPJSFX_State* st, double peerId);
+double jsfx_sample_pool_from_slot(DSPJSFX_State* st, double slot, double nameHandle);
+double jsfx_sample_pool_set_mode(DSPJSFX_State* st, double pool, double mode);
+double jsfx_sample_pool_set_budget_mb(DSPJSFX_State* st, double pool, double mb);
+double jsfx_sample_pool_commit(DSPJSFX_State* st, double pool);
+double jsfx_sample_pool_state(DSPJSFX_State* st, double pool);
+double jsfx_sample_pool_selected(DSPJSFX_State* st, double pool);
+double jsfx_sample_pool_loaded(DSPJSFX_State* st, double pool);
+double jsfx_sample_pool_failed(DSPJSFX_State* st, double pool);
+double jsfx_sample_pool_ram_mb(DSPJSFX_State* st, double pool);
+double jsfx_sample_pool_generation(DSPJSFX_State* st, double pool);
+double jsfx_sample_get(DSPJSFX_State* st, double pool, double index);
+double jsfx_sample_len(DSPJSFX_State* st, double pool, double sampleId);
+double jsfx_sample_channels(DSPJSFX_State* st, double pool, double sampleId);
+double jsfx_sample_srate(DSPJSFX_State* st, double pool, double sampleId);
+double jsfx_sample_peak(DSPJSFX_State* st, double pool, double sampleId);
+double jsfx_sample_rms(DSPJSFX_State* st, double pool, double sampleId);
+double jsfx_sample_name(DSPJSFX_State* st, double pool, double sampleId, double* outStr);
+double jsfx_sample_read(DSPJSFX_State* st, double pool, double sampleId, double channel, double frame);
+double jsfx_sample_read_interp(DSPJSFX_State* st, double pool, double sampleId, double channel, double phase);
+double jsfx_sample_read2(DSPJSFX_State* st, double pool, double sampleId, double phase, double* outL, double* outR);
+double jsfx_sample_read2_interp(DSPJSFX_State* st, double pool, double sampleId, double phase, double* outL, double* outR);
+double jsfx_sample_preview_bins(DSPJSFX_State* st, double pool, double sampleId);
+double jsfx_sample_preview_read(DSPJSFX_State* st, double pool, double sampleId, double bin, double* minValue, double* maxValue, double* rmsValue);
+double jsfx_sample_export_mem(DSPJSFX_State* st, double pool, double sampleId, double dstBase, double srcFrame, double frameCount);
+double jsfx_sample_export_mem2(DSPJSFX_State* st, double pool, double sampleId, double dstBase, double srcFrame, double frameCount);
+
+#ifdef __cplusplus
+}
+#endif

@@ -1,0 +1,90 @@
+#!/usr/bin/env python3
+"""oracle/build_ref.py -- TEST INFRASTRUCTURE: build the real reference into oracle/_ref/.
+
+For every plugin in PLUGINS this runs the reference's OWN compiler, read-only, from where it lies
+(`/root/reference/dsp_jsfx_aot.py --opt 2`, the same invocation as scripts/build.py:385-393) on the
+plugin's .jsfx source, and links the emitted object with oracle/ref_shim.c (and, for FFT users,
+oracle/ref_fft_hooks.c over /root/reference/src/WDL/fft.c compiled in place) into
+
+    oracle/_ref/libref_<key>.so   + <key>.json (the compiler's own --meta: var table, channel counts)
+
+Nothing from /root/reference is copied into the repo: sources are compiled where they lie and only
+build outputs land in oracle/_ref/ (git-ignored, but shipped to the GPU box by gpurun).
+On a machine without /root/reference (the GPU box) this script is a no-op and the prebuilt files
+are used.
+"""
+from __future__ import annotations
+
+import os
+import subprocess
+import sys
+from pathlib import Path
+
+HERE = Path(__file__).resolve().parent
+REPO = HERE.parent
+REF = Path(os.environ.get("ZA_REFERENCE_ROOT", "/root/reference"))
+OUT = HERE / "_ref"
+PKG = REPO / "zorakaudio-experimental-plugins_b200"
+
+# key -> (jsfx source, needs FFT hooks)
+PLUGINS = {
+    "cascade8": (PKG / "plugins/Workloads/cascade8/src/cascade8.jsfx", False),
+    "stft_mask2048": (PKG / "plugins/Workloads/stft_mask2048/src/stft_mask2048.jsfx", True),
+    "EasyExpander": (REF / "plugins/Dynamics/EasyExpander/src/EasyExpander.jsfx", False),
+    "RTT": (REF / "plugins/Dynamics/RTT/src/Reverb Tail Tamer.jsfx", False),
+    "SOMA": (REF / "plugins/Dynamics/SOMA/src/SOMA.jsfx", False),
+    "ATTACK": (REF / "plugins/Dynamics/ATTACK/src/ATTACK.jsfx", False),
+    "ERBTilt": (REF / "plugins/Spectral/ERBTilt/src/ERB Tilt.jsfx", False),
+    "SpectralStabilizer": (REF / "plugins/Spectral/SpectralStabilizer/src/Spectral Stabilizer.jsfx", False),
+    "DDT": (REF / "plugins/Spatialization/DDT/src/DDT.jsfx", False),
+}
+
+
+def _newer(dst: Path, *srcs: Path) -> bool:
+    if not dst.exists():
+        return False
+    t = dst.stat().st_mtime
+    return all(s.exists() and s.stat().st_mtime <= t for s in srcs)
+
+
+def build_one(key: str, force: bool = False) -> Path | None:
+    src, needs_fft = PLUGINS[key]
+    so = OUT / f"libref_{key}.so"
+    if not REF.exists() or not src.exists():
+        return so if so.exists() else None
+    shim = HERE / "ref_shim.c"
+    hooks = HERE / "ref_fft_hooks.c"
+    deps = [src, shim] + ([hooks] if needs_fft else [])
+    if not force and _newer(so, *deps):
+        return so
+    OUT.mkdir(exist_ok=True)
+    obj, hdr, meta = OUT / f"{key}.o", OUT / f"{key}.h", OUT / f"{key}.json"
+    subprocess.run(
+        [sys.executable, str(REF / "dsp_jsfx_aot.py"), str(src), "--out-obj", str(obj), "--out-h", str(hdr),
+         "--meta", str(meta), "--out-ll", os.devnull, "--opt", "2"],
+        check=True, stdout=subprocess.DEVNULL)
+    cmd = ["gcc", "-O2", "-fPIC", "-shared", "-fvisibility=hidden", "-ffp-contract=off",
+           f'-DZREF_HEADER="{hdr}"', str(shim), str(obj)]
+    if needs_fft:
+        # WDL_FFT_REALSIZE=8: cmake/plugin/CMakeLists.txt:224
+        cmd += ["-DWDL_FFT_REALSIZE=8", f"-I{REF / 'src'}", f'-DZREF_WDL_FFT_C="{REF / "src/WDL/fft.c"}"', str(hooks)]
+    cmd += ["-o", str(so), "-lm", "-lpthread"]
+    subprocess.run(cmd, check=True)
+    return so
+
+
+def build_all(keys=None, force: bool = False) -> dict:
+    res = {}
+    for k in (keys or PLUGINS):
+        try:
+            res[k] = build_one(k, force)
+        except subprocess.CalledProcessError as e:  # keep going: one broken leaf must not hide the others
+            print(f"[build_ref] {k}: FAILED ({e})", file=sys.stderr)
+            res[k] = None
+    return res
+
+
+if __name__ == "__main__":
+    keys = [a for a in sys.argv[1:] if not a.startswith("-")] or None
+    for k, v in build_all(keys, force="--force" in sys.argv).items():
+        print(f"{k:22s} {v}")

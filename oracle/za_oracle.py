@@ -1,0 +1,255 @@
+"""oracle/za_oracle.py -- TEST INFRASTRUCTURE ONLY.
+
+Python harness around (a) oracle/_ref/libref_<key>.so = the reference's own compiled DSP-JSFX
+object behind oracle/ref_shim.c, and (b) oracle/libza_oracle_port.so = the plain-C restatement
+(oracle/za_oracle_port.c).  Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+--impl reference legs may import this module; the product (libza_gpu.so) never does.
+
+Also holds the seeded synthetic signal / parameter generators of SURVEY.md section 8(d) so the
+tests, the golden-fixture generator and bench.py all render exactly the same inputs.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import json
+import os
+import re
+from pathlib import Path
+
+import numpy as np
+
+HERE = Path(__file__).resolve().parent
+REPO = HERE.parent
+PKG = REPO / "zorakaudio-experimental-plugins_b200"
+REF_DIR = HERE / "_ref"
+
+
+# ------------------------------------------------------------------------------------------------
+# slider layout (restates parseJsfxSliderDecls, src/JSFXJuceProcessor.cpp:710-939, numeric part)
+# ------------------------------------------------------------------------------------------------
+class SliderLayout(C.Structure):
+    _fields_ = [("n", C.c_int32), ("index0", C.c_int32 * 64), ("alias", C.c_int32 * 64),
+                ("vmin", C.c_float * 64), ("vmax", C.c_float * 64), ("vstep", C.c_float * 64),
+                ("is_choice", C.c_int32 * 64)]
+
+
+_RE_SLIDER = re.compile(r"^\s*slider\s*([0-9]{1,2})\s*:\s*([^<\r\n;]+)\s*(?:<\s*([^>]+)\s*>)?\s*(.*)$")
+
+
+def _parse_float(tok: str):
+    m = re.match(r"\s*[-+]?(?:\d+\.?\d*(?:[eE][-+]?\d+)?|\.\d+(?:[eE][-+]?\d+)?)", tok)
+    if not m:
+        return None
+    return np.float32(float(m.group(0)))
+
+
+def _split_top_commas(s: str):
+    parts, cur, depth = [], "", 0
+    for ch in s:
+        if ch == "{":
+            depth += 1
+        elif ch == "}" and depth > 0:
+            depth -= 1
+        if ch == "," and depth == 0:
+            parts.append(cur.strip()); cur = ""
+        else:
+            cur += ch
+    parts.append(cur.strip())
+    return parts
+
+
+def parse_sliders(jsfx_text: str):
+    """-> list of dict(index0, var, default, min, max, step, is_choice), sorted by index."""
+    out = {}
+    for line in re.split(r"[\r\n]+", jsfx_text):
+        m = _RE_SLIDER.match(line)
+        if not m:
+            continue
+        n = int(m.group(1))
+        if n < 1 or n > 64:
+            continue
+        tok = m.group(2).strip()
+        var, deftok = "", tok
+        if "=" in tok:
+            eq = tok.rfind("=")
+            var, deftok = tok[:eq].strip(), tok[eq + 1:].strip()
+        d = _parse_float(deftok)
+        d = np.float32(0.0) if d is None else d
+        rng = m.group(3)
+        if rng is not None and rng.strip().lower() in ("string", "str", "text"):
+            continue
+        if var.startswith("#"):
+            continue
+        vmin, vmax, vstep, is_choice = np.float32(0), np.float32(1), np.float32(0.001), False
+        if rng is not None:
+            parts = _split_top_commas(rng)
+            if len(parts) >= 2:
+                a, b = _parse_float(parts[0]), _parse_float(parts[1])
+                vmin = np.float32(0) if a is None else a
+                vmax = np.float32(1) if b is None else b
+            if len(parts) >= 3:
+                st = parts[2]
+                if "{" in st:
+                    bp = st.find("{"); cp = st.find("}", bp + 1)
+                    if cp >= 0 and [x for x in st[bp + 1:cp].split(",") if x.strip()]:
+                        is_choice = True
+                    st = st[:bp].strip()
+                if ":" in st:
+                    st = st[:st.find(":")].strip()
+                if st == "":
+                    vstep = np.float32(1)
+                else:
+                    v = _parse_float(st)
+                    vstep = np.float32(1) if v is None else v
+            if vmax < vmin:
+                vmin, vmax = vmax, vmin
+            if not (vstep > 0):
+                vstep = np.float32(0.001)
+            d = min(max(d, vmin), vmax)
+        if (n - 1) not in out:
+            out[n - 1] = dict(index0=n - 1, var=var, default=float(d), min=float(vmin), max=float(vmax),
+                              step=float(vstep), is_choice=is_choice)
+    return [out[k] for k in sorted(out)]
+
+
+def make_layout(sliders, var_index) -> SliderLayout:
+    L = SliderLayout()
+    L.n = len(sliders)
+    for j, s in enumerate(sliders):
+        L.index0[j] = s["index0"]
+        L.alias[j] = var_index(s["var"]) if s["var"] else -1
+        L.vmin[j], L.vmax[j], L.vstep[j] = s["min"], s["max"], s["step"]
+        L.is_choice[j] = 1 if s["is_choice"] else 0
+    return L
+
+
+def quantise(sliders, values: np.ndarray) -> np.ndarray:
+    """numpy restatement of hostParameterToJsfxSliderValue (src/JSFXJuceProcessor.cpp:5556-5597);
+    values[..., n_sliders] float32 -> float64."""
+    v = np.asarray(values, dtype=np.float32).astype(np.float64)
+    out = np.empty_like(v)
+    for j, s in enumerate(sliders):
+        mn, mx, st = float(np.float32(s["min"])), float(np.float32(s["max"])), float(np.float32(s["step"]))
+        x = v[..., j]
+        if s["is_choice"]:
+            x = mn + _llround(x) * st
+        x = np.clip(x, mn, mx)
+        if not s["is_choice"] and st > 0:
+            x = np.clip(mn + _llround((x - mn) / st) * st, mn, mx)
+        out[..., j] = x
+    return out
+
+
+def _llround(x):
+    return np.where(x >= 0, np.floor(x + 0.5), -np.floor(-x + 0.5))
+
+
+# ------------------------------------------------------------------------------------------------
+# plugin sources (the catalog stays where it is; authored workloads live in the package)
+# ------------------------------------------------------------------------------------------------
+def plugin_source_text(key: str) -> str:
+    """Slider layout text.  Authored workloads: read the .jsfx.  Catalog leaves: the layout is
+    committed in the package's plugin table (the reference tree does not exist on the GPU box)."""
+    for p in (PKG / "plugins").rglob("*.jsfx"):
+        if p.parent.parent.name == key:
+            return p.read_text()
+    raise KeyError(key)
+
+
+class RefPlugin:
+    """The reference's compiled DSP for one plugin (oracle/_ref/libref_<key>.so)."""
+
+    def __init__(self, key: str, sliders=None):
+        so = REF_DIR / f"libref_{key}.so"
+        if not so.exists():
+            raise FileNotFoundError(f"{so} (run oracle/build_ref.py where /root/reference exists)")
+        self.key = key
+        self.lib = C.CDLL(str(so))
+        L = self.lib
+        L.zref_var_index.argtypes = [C.c_char_p]
+        L.zref_new.restype = C.c_void_p
+        L.zref_new.argtypes = [C.POINTER(SliderLayout)]
+        L.zref_free.argtypes = [C.c_void_p]
+        L.zref_prepare.argtypes = [C.c_void_p, C.c_double, C.c_void_p]
+        L.zref_vars.restype = C.POINTER(C.c_double)
+        L.zref_vars.argtypes = [C.c_void_p]
+        L.zref_mem.restype = C.POINTER(C.c_double)
+        L.zref_mem.argtypes = [C.c_void_p, C.POINTER(C.c_int64)]
+        L.zref_render.argtypes = [C.POINTER(SliderLayout), C.c_double, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
+                                  C.c_void_p, C.c_int, C.c_int64, C.c_int64, C.c_int, C.c_int]
+        self.n_in, self.n_out = L.zref_in_channels(), L.zref_out_channels()
+        self.sliders = sliders if sliders is not None else parse_sliders(plugin_source_text(key))
+        self.layout = make_layout(self.sliders, lambda name: L.zref_var_index(name.encode()))
+        self.meta = json.loads((REF_DIR / f"{key}.json").read_text()) if (REF_DIR / f"{key}.json").exists() else {}
+
+    def render(self, params, x, srate=48000.0, block=512, want_f64=False, threads=0):
+        """params [n_streams,n_sliders] or [n_blocks,n_streams,n_sliders] f32; x [n_streams,n_in,n_frames] f32
+        -> (y f32 [n_streams,n_out,n_frames], y64 or None)."""
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        ns, nin, nf = x.shape
+        assert nin == self.n_in, (nin, self.n_in)
+        p = np.ascontiguousarray(params, dtype=np.float32)
+        npb = 1 if p.ndim == 2 else p.shape[0]
+        assert p.shape[-2] == ns and p.shape[-1] == len(self.sliders)
+        y = np.zeros((ns, self.n_out, nf), np.float32)
+        yd = np.zeros((ns, self.n_out, nf), np.float64) if want_f64 else None
+        th = threads or (os.cpu_count() or 1)
+        rc = self.lib.zref_render(C.byref(self.layout), srate, p.ctypes.data, npb, x.ctypes.data, y.ctypes.data,
+                                  yd.ctypes.data if want_f64 else None, ns, nf, nf, block, th)
+        assert rc == 0
+        return y, yd
+
+
+def have_ref(key: str) -> bool:
+    return (REF_DIR / f"libref_{key}.so").exists()
+
+
+# ------------------------------------------------------------------------------------------------
+# the plain-C restatement (oracle/za_oracle_port.c)
+# ------------------------------------------------------------------------------------------------
+PORT_SO = HERE / "libza_oracle_port.so"
+
+
+def build_port(force: bool = False) -> Path:
+    import subprocess
+    src = HERE / "za_oracle_port.c"
+    if force or not PORT_SO.exists() or PORT_SO.stat().st_mtime < src.stat().st_mtime:
+        subprocess.run(["gcc", "-O2", "-fPIC", "-shared", "-fvisibility=hidden", "-ffp-contract=off",
+                        str(src), "-o", str(PORT_SO), "-lm", "-lpthread"], check=True)
+    return PORT_SO
+
+
+class PortPlugin:
+    """Plain-C restatement of one plugin; same render() contract as RefPlugin."""
+
+    CHANNELS = {"cascade8": (1, 1), "EasyExpander": (2, 2), "stft_mask2048": (2, 2)}
+
+    def __init__(self, key: str, sliders=None, var_index=None):
+        self.key = key
+        self.lib = C.CDLL(str(build_port()))
+        self.fn = getattr(self.lib, f"zo_{key.lower()}_render")
+        self.fn.argtypes = [C.POINTER(SliderLayout), C.c_double, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
+                            C.c_void_p, C.c_int, C.c_int64, C.c_int64, C.c_int, C.c_int]
+        self.n_in, self.n_out = self.CHANNELS[key]
+        self.sliders = sliders if sliders is not None else parse_sliders(plugin_source_text(key))
+        self.layout = make_layout(self.sliders, var_index or (lambda name: -1))
+
+    def render(self, params, x, srate=48000.0, block=512, want_f64=False, threads=0):
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        ns, nin, nf = x.shape
+        assert nin == self.n_in
+        p = np.ascontiguousarray(params, dtype=np.float32)
+        npb = 1 if p.ndim == 2 else p.shape[0]
+        assert p.shape[-2] == ns and p.shape[-1] == len(self.sliders)
+        y = np.zeros((ns, self.n_out, nf), np.float32)
+        yd = np.zeros((ns, self.n_out, nf), np.float64) if want_f64 else None
+        th = threads or (os.cpu_count() or 1)
+        rc = self.fn(C.byref(self.layout), srate, p.ctypes.data, npb, x.ctypes.data, y.ctypes.data,
+                     yd.ctypes.data if want_f64 else None, ns, nf, nf, block, th)
+        assert rc == 0
+        return y, yd
+
+
+def best_oracle(key: str):
+    """The real reference when its build is present, else the pinned restatement."""
+    return RefPlugin(key) if have_ref(key) else PortPlugin(key)

@@ -1,0 +1,80 @@
+"""Seeded synthetic workloads of BASELINE.json configs.
+
+numpy generators for parity-sized cases (tests, golden fixtures, CPU baseline samples) and the
+matching description of the full-size cases bench.py generates on the device.  No reference or
+oracle code is used here: these are inputs only.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+SRATE = 48000.0
+
+
+def cascade8_params(n_streams: int, first_stream: int = 0) -> np.ndarray:
+    """cfg2: per-stream fc log-uniform 40 Hz-16 kHz, Q uniform 0.5-4, seed 1000+stream.
+    Column order = slider order of cascade8.jsfx (fc1,q1,...,fc6,q6,fc7,fc8,mix)."""
+    p = np.empty((n_streams, 15), np.float32)
+    lo = np.array([40.0, 4000.0, 40.0, 40.0, 4000.0, 40.0, 8000.0, 8000.0])      # HP LP BP BP LP HP 1p 1p
+    hi = np.array([400.0, 16000.0, 16000.0, 16000.0, 16000.0, 400.0, 16000.0, 16000.0])
+    for i in range(n_streams):
+        r = np.random.default_rng(1000 + first_stream + i)
+        fc = np.exp(r.uniform(np.log(lo), np.log(hi)))   # log-uniform inside 40 Hz-16 kHz, EQ-shaped:
+        q = r.uniform(0.5, 4.0, 6)                       # high-passes low, low-passes high, bands anywhere
+        p[i, 0:12:2] = fc[:6]
+        p[i, 1:12:2] = q
+        p[i, 12], p[i, 13] = fc[6], fc[7]
+        p[i, 14] = r.uniform(0.0, 1.0)
+    return p
+
+
+def noise_two_sines(n_streams: int, n_frames: int, first_stream: int = 0, n_ch: int = 1) -> np.ndarray:
+    """cfg2 input: seeded uniform noise x0.25 + two sines (-18 dBFS each); [stream][ch][frame] f32."""
+    x = np.empty((n_streams, n_ch, n_frames), np.float32)
+    t = np.arange(n_frames, dtype=np.float64) / SRATE
+    for i in range(n_streams):
+        r = np.random.default_rng(5000 + first_stream + i)
+        f1, f2 = r.uniform(60.0, 400.0), r.uniform(1000.0, 6000.0)
+        for c in range(n_ch):
+            nz = r.uniform(-0.25, 0.25, n_frames)
+            x[i, c] = (nz + 0.125 * np.sin(2 * np.pi * f1 * t + c) + 0.125 * np.sin(2 * np.pi * f2 * t)).astype(np.float32)
+    return x
+
+
+def programme_bursts(n_streams: int, n_frames: int, first_stream: int = 0, n_ch: int = 2) -> np.ndarray:
+    """cfg3 input: noise x slow random envelope sweeping -60..-6 dBFS so gain computers traverse
+    knee / hysteresis regions; [stream][ch][frame] f32."""
+    x = np.empty((n_streams, n_ch, n_frames), np.float32)
+    seg = 2400  # 50 ms envelope knots
+    nk = n_frames // seg + 2
+    for i in range(n_streams):
+        r = np.random.default_rng(9000 + first_stream + i)
+        knots_db = r.uniform(-60.0, -6.0, nk)
+        env_db = np.interp(np.arange(n_frames) / seg, np.arange(nk), knots_db)
+        env = 10.0 ** (env_db / 20.0)
+        mono = r.uniform(-1.0, 1.0, n_frames)
+        for c in range(n_ch):
+            side = r.uniform(-1.0, 1.0, n_frames) * 0.3
+            x[i, c] = (env * (mono + side) * 0.7).astype(np.float32)
+    return x
+
+
+def automation(sliders, n_blocks: int, n_streams: int, which, first_stream: int = 0, base=None) -> np.ndarray:
+    """cfg3 per-block automation: sliders listed in `which` (column indices) follow a seeded
+    piecewise-linear + sine-LFO trajectory sampled at block starts; others stay at `base`
+    (default: declared defaults).  -> float32 [n_blocks][n_streams][n_sliders] of HOST values."""
+    ns = len(sliders)
+    p = np.empty((n_blocks, n_streams, ns), np.float32)
+    dflt = np.array([s["default"] for s in sliders], np.float32) if base is None else np.asarray(base, np.float32)
+    p[:] = dflt
+    b = np.arange(n_blocks, dtype=np.float64)
+    for i in range(n_streams):
+        r = np.random.default_rng(7000 + first_stream + i)
+        for j in which:
+            lo, hi = sliders[j]["min"], sliders[j]["max"]
+            nk = max(2, n_blocks // 40 + 2)
+            knots = r.uniform(lo + 0.1 * (hi - lo), hi - 0.1 * (hi - lo), nk)
+            traj = np.interp(b / 40.0, np.arange(nk), knots)
+            traj += 0.05 * (hi - lo) * np.sin(2 * np.pi * b / r.uniform(13.0, 90.0))
+            p[:, i, j] = np.clip(traj, lo, hi).astype(np.float32)
+    return p
