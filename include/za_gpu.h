@@ -1,0 +1,141 @@
+/*
+ * za_gpu.h -- C ABI of the B200 batch renderer (libza_gpu.so).
+ *
+ * Drop-in boundary for ONE path of ZorakAudio-Experimental-Plugins: the per-sample / per-block
+ * DSP of a plugin instance (reference: generated `jsfx_init/slider/block/sample/process_block`,
+ * dsp_jsfx_aot.py:5713-5905, driven by JSFXJuceProcessor::prepareToPlay / processBlock,
+ * src/JSFXJuceProcessor.cpp:3239-3342, 3435-3772; Faust: FaustJuceProcessor.cpp:430-482),
+ * rendered for thousands of independent instances ("streams") at once.
+ *
+ * Plain pointers and sizes only; no C++/torch types; never throws.  Every function returns
+ * ZA_OK (0) or a negative za_status; za_gpu_last_error() gives the text for the calling thread.
+ * There is NO CPU fallback: without a CUDA device every compute entry point returns ZA_ERR_CUDA.
+ *
+ * Buffer layout (both directions):  planar float32, [stream][channel][frame]; element
+ * (s, c, i) lives at base[(s * n_ch + c) * frame_stride + i].  This is the reference's
+ * `const float* const* in / float* const* out` (one pointer per channel, dsp_jsfx_aot.py:5716-5719)
+ * made dense over streams.  in == out (in-place) is legal when n_in == n_out, as JUCE bus buffers
+ * alias in the reference (src/JSFXJuceProcessor.cpp:3456-3528).
+ *
+ * Parameter block: float32 HOST values as the reference's parameter atomics hold them
+ * (src/JSFXJuceProcessor.cpp:5564-5566): the plain slider value, or the choice index for
+ * `step{A,B,C}` sliders.  Column j = j-th declared slider in slider-index order.  The library
+ * clamps and step-quantises exactly as hostParameterToJsfxSliderValue (:5556-5597) once per
+ * host block, runs @slider only when a quantised value changed (:3545-3547), and mirrors alias
+ * variables (:9347-9352).
+ */
+#ifndef ZA_GPU_H
+#define ZA_GPU_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define ZA_API __attribute__((visibility("default")))
+#else
+#define ZA_API
+#endif
+
+typedef struct za_gpu_instance* za_gpu_handle;
+
+typedef enum za_status {
+    ZA_OK = 0,
+    ZA_ERR_ARG = -1,        /* bad argument (null, negative size, misaligned for the requested mode) */
+    ZA_ERR_PLUGIN = -2,     /* unknown plugin_key */
+    ZA_ERR_CUDA = -3,       /* CUDA runtime/driver error or no device (no CPU fallback exists) */
+    ZA_ERR_STATE = -4,      /* call order violated (process before prepare) */
+    ZA_ERR_UNSUPPORTED = -5 /* valid request this build does not implement */
+} za_status;
+
+typedef enum za_precision { ZA_F32 = 0, ZA_F64 = 1 } za_precision;   /* arithmetic type; I/O is always float32 */
+typedef enum za_memory { ZA_MEM_HOST = 0, ZA_MEM_DEVICE = 1 } za_memory;
+
+typedef struct za_plugin_info {
+    int32_t n_in;          /* DSPJSFX_INPUT_CHANNELS  (generated header, dsp_jsfx_aot.py:5924-6190) */
+    int32_t n_out;         /* DSPJSFX_OUTPUT_CHANNELS */
+    int32_t n_sliders;     /* declared numeric sliders = columns of a parameter block */
+    int32_t kind;          /* 0 = DSP-JSFX leaf, 1 = Faust leaf, 2 = authored DSP-JSFX workload */
+    int32_t latency;       /* frames of algorithmic latency the plugin reports (0 if none) */
+} za_plugin_info;
+
+typedef struct za_slider_info {    /* JsfxSliderDecl, src/JSFXJuceProcessor.cpp:520-545, numeric part */
+    int32_t index0;        /* slider number - 1 */
+    int32_t is_choice;
+    float def, min, max, step;    /* stored as float like the reference (:531-534) */
+    char alias[64];        /* `sliderN:alias=...` variable name, "" if none */
+} za_slider_info;
+
+/* ---- catalogue ---------------------------------------------------------------------------- */
+ZA_API int za_gpu_plugin_count(void);
+ZA_API const char* za_gpu_plugin_key(int i);                       /* plugin.json "slug" */
+ZA_API int za_gpu_plugin_info(const char* plugin_key, za_plugin_info* out);
+ZA_API int za_gpu_slider_info(const char* plugin_key, int column, za_slider_info* out);
+/* parseJsfxSliderDecls (src/JSFXJuceProcessor.cpp:710-939) on arbitrary .jsfx text: fills up to
+ * `cap` entries sorted by slider index, returns the count (>= 0) or a negative za_status. */
+ZA_API int za_gpu_parse_sliders(const char* jsfx_text, za_slider_info* out, int cap);
+/* hostParameterToJsfxSliderValue (src/JSFXJuceProcessor.cpp:5556-5597) for one value. */
+ZA_API int za_gpu_quantise(const za_slider_info* slider, float host_value, double* out);
+
+/* ---- instance life cycle ------------------------------------------------------------------ */
+/* One handle = n_streams independent instances of one plugin on one device, all state in
+ * structure-of-arrays HBM buffers owned by the library.  block_len = host block size the
+ * reference would be driven with (samplesblock; parameters are sampled once per block). */
+ZA_API int za_gpu_create(const char* plugin_key, int n_streams, double sample_rate, int block_len,
+                         int precision, int device, za_gpu_handle* out);
+ZA_API int za_gpu_destroy(za_gpu_handle h);
+/* Run on an existing CUDA stream (e.g. the caller's torch stream); NULL = the handle's own. */
+ZA_API int za_gpu_set_stream(za_gpu_handle h, void* cuda_stream);
+
+/* prepareToPlay order (src/JSFXJuceProcessor.cpp:3250-3318): reset state (keeping memory),
+ * push param_block0 [n_streams][n_sliders] to the sliders, @init, alias re-apply, @slider. */
+ZA_API int za_gpu_prepare(za_gpu_handle h, const float* param_block0);
+
+/* processBlock for every stream over n_frames frames, split into host blocks of block_len
+ * (last one short).  For block b the parameter row is param_block[min(b, n_param_blocks-1)]
+ * ([n_param_blocks][n_streams][n_sliders], host memory); n_param_blocks == 0 keeps the current
+ * sliders.  Per block: quantise+push sliders, @slider if changed, @block, then per frame @sample
+ * (dsp_jsfx_aot.py:5766-5892).  State carries over between calls (time-chunked rendering).
+ * mem = ZA_MEM_DEVICE: in/out are device pointers on the handle's device, work is enqueued on the
+ * handle's stream and the call returns without synchronising.  mem = ZA_MEM_HOST: in/out are host
+ * buffers (pinned or pageable); copies are pipelined with the kernels and the call returns when
+ * `out` is complete. */
+ZA_API int za_gpu_process(za_gpu_handle h, const float* param_block, int n_param_blocks,
+                          const float* in, float* out, int64_t n_frames, int64_t frame_stride, int mem);
+
+/* Same, additionally writing st.spl[] as double BEFORE the (float) store of
+ * dsp_jsfx_aot.py:5866-5892 to tap64 [stream][out_ch][frame] (same stride, same memory kind).
+ * Parity instrument for "fp64 mode within 1e-12"; requires precision == ZA_F64. */
+ZA_API int za_gpu_process_tap64(za_gpu_handle h, const float* param_block, int n_param_blocks,
+                                const float* in, float* out, double* tap64, int64_t n_frames,
+                                int64_t frame_stride, int mem);
+
+/* Read one named per-stream state variable (DSPJSFX_VARS name -> vars[] slot in the reference) as
+ * double into out[n_streams] (host).  Integer state (counters, ring positions) is exact. */
+ZA_API int za_gpu_read_state(za_gpu_handle h, const char* var_name, double* out);
+ZA_API int za_gpu_sync(za_gpu_handle h);
+
+/* ---- introspection for benches ------------------------------------------------------------- */
+ZA_API int za_gpu_launch_count(za_gpu_handle h, int64_t* kernels_launched);   /* our kernels, cumulative */
+/* Device time (ms, CUDA events on the handle's stream) of the dominant kernel launches of the
+ * most recent za_gpu_process call, and how many launches that covers. */
+ZA_API int za_gpu_last_kernel_ms(za_gpu_handle h, double* ms, int* launches);
+/* Tuning knob for experiments: name = "force_generic_io" | "warps_per_stream" | "host_chunk_streams". */
+ZA_API int za_gpu_set_option(za_gpu_handle h, const char* name, int value);
+
+/* ---- one-shot form sketched in BASELINE.json north_star ------------------------------------ */
+/* za_gpu_process(plugin_key, param_block, in, out, n_streams, n_frames): create + prepare +
+ * process (host buffers, static parameters, 48 kHz, block 512, fp64) + destroy. */
+ZA_API int za_gpu_render(const char* plugin_key, const float* param_block, const float* in, float* out,
+                         int n_streams, int64_t n_frames);
+
+ZA_API const char* za_gpu_last_error(void);
+ZA_API int za_gpu_device_count(void);
+ZA_API const char* za_gpu_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ZA_GPU_H */

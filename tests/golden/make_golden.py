@@ -1,0 +1,44 @@
+#!/usr/bin/env python3
+"""Generate tests/golden/*.npz by running the REFERENCE's own compiled DSP (oracle/_ref, built from
+/root/reference by oracle/build_ref.py) on seeded inputs.  Run in the build container only."""
+import hashlib
+import sys
+from pathlib import Path
+
+import numpy as np
+
+HERE = Path(__file__).resolve().parent
+REPO = HERE.parent.parent
+sys.path.insert(0, str(REPO / "oracle"))
+sys.path.insert(0, str(REPO / "zorakaudio-experimental-plugins_b200"))
+import za_oracle as zo  # noqa: E402
+from za_gpu import workloads as wl  # noqa: E402
+
+EXCERPT = 2048
+
+
+def golden(key, params, x, block=512, tag=""):
+    ref = zo.RefPlugin(key)
+    y, yd = ref.render(params, x, block=block, want_f64=True, threads=1)
+    out = HERE / f"{key}{tag}.npz"
+    np.savez_compressed(
+        out, params=np.asarray(params, np.float32), block=block,
+        n_streams=x.shape[0], n_frames=x.shape[2],
+        y64_head=yd[:, :, :EXCERPT], y64_tail=yd[:, :, -EXCERPT:],
+        y32_sha256=np.frombuffer(hashlib.sha256(y.tobytes()).digest(), np.uint8),
+        y64_sha256=np.frombuffer(hashlib.sha256(yd.tobytes()).digest(), np.uint8),
+        x_sha256=np.frombuffer(hashlib.sha256(x.tobytes()).digest(), np.uint8),
+        y64_abs_sum=np.abs(yd).sum(axis=2))
+    print(out, out.stat().st_size)
+
+
+if __name__ == "__main__":
+    ns, nf = 8, 48000
+    golden("cascade8", wl.cascade8_params(ns), wl.noise_two_sines(ns, nf))
+    # automation: parameters move every 512-frame block
+    base = wl.cascade8_params(4)
+    nb = 20
+    auto = np.repeat(base[None], nb, axis=0).copy()
+    auto[:, :, 4] *= np.linspace(1.0, 2.0, nb)[:, None]      # sweep the S3 band frequency
+    auto[5:, :, 14] = 0.25                                   # and step the mix at block 5
+    golden("cascade8", auto, wl.noise_two_sines(4, nb * 512 - 100), tag="_auto")

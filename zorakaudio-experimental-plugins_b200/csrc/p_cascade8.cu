@@ -1,0 +1,146 @@
+// p_cascade8.cu -- plugin "cascade8": host half (@init / @slider) + device launch plan.
+//
+// @slider runs on the host with glibc's sin/cos/exp so the coefficients are bit-identical to what
+// the reference's compiled @slider produces (it calls the same libm, dsp_jsfx_aot.py:3746-3754);
+// a 1-ulp difference in a1/a2 of a 40 Hz biquad moves its response by ~1e-11, which would already
+// break the 1e-12 fp64 criterion.  Everything per-sample runs in k_cascade8.cu.
+#include <cmath>
+#include <cstring>
+
+#include "za_host.h"
+
+namespace za {
+
+namespace {
+
+const char* kSliderText =
+    "slider1:fc1=80<20,20000,0.01>S1 HP fc (Hz)\n"
+    "slider2:q1=0.707<0.1,8,0.001>S1 HP Q\n"
+    "slider3:fc2=12000<20,20000,0.01>S2 LP fc (Hz)\n"
+    "slider4:q2=0.707<0.1,8,0.001>S2 LP Q\n"
+    "slider5:fc3=1000<20,20000,0.01>S3 BP(peak) fc (Hz)\n"
+    "slider6:q3=1<0.1,8,0.001>S3 BP(peak) Q\n"
+    "slider7:fc4=3000<20,20000,0.01>S4 BP(skirt) fc (Hz)\n"
+    "slider8:q4=1<0.1,8,0.001>S4 BP(skirt) Q\n"
+    "slider9:fc5=8000<20,20000,0.01>S5 LP fc (Hz)\n"
+    "slider10:q5=0.707<0.1,8,0.001>S5 LP Q\n"
+    "slider11:fc6=40<20,20000,0.01>S6 HP fc (Hz)\n"
+    "slider12:q6=0.707<0.1,8,0.001>S6 HP Q\n"
+    "slider13:fc7=16000<20,20000,0.01>S7 one-pole LP fc (Hz)\n"
+    "slider14:fc8=18000<20,20000,0.01>S8 one-pole LP fc (Hz)\n"
+    "slider15:mix=1<0,1,0.001>S3/S4 band mix\n";
+
+inline double jmin(double a, double b) { return a < b ? a : b; }   // olt/ogt selects, dsp_jsfx_aot.py:5223-5232
+inline double jmax(double a, double b) { return a > b ? a : b; }
+
+// cascade8.jsfx @slider, expression order kept
+void c8_slider(const double* sl, double srate, double* c /* kC8Coefs */)
+{
+    const double two_pi = 6.283185307179586;
+    static const int kind[6] = {0, 1, 2, 3, 1, 0};    // HP LP BPpeak BPskirt LP HP
+    for (int k = 0; k < 6; ++k) {
+        const double f = jmin(jmax(sl[2 * k], 10), srate * 0.45), q = jmax(sl[2 * k + 1], 0.1);
+        const double w0 = two_pi * f / srate, cw = std::cos(w0), sw = std::sin(w0), alpha = sw / (2.0 * q);
+        const double aa0 = 1.0 + alpha;
+        double* b = c + 5 * k;
+        switch (kind[k]) {
+        case 0: b[0] = ((1.0 + cw) / 2.0) / aa0; b[1] = (-(1.0 + cw)) / aa0; b[2] = ((1.0 + cw) / 2.0) / aa0; break;
+        case 1: b[0] = ((1.0 - cw) / 2.0) / aa0; b[1] = (1.0 - cw) / aa0;    b[2] = ((1.0 - cw) / 2.0) / aa0; break;
+        case 2: b[0] = alpha / aa0;      b[1] = 0.0; b[2] = (-alpha) / aa0;    break;
+        default: b[0] = (sw / 2.0) / aa0; b[1] = 0.0; b[2] = (-sw / 2.0) / aa0; break;
+        }
+        b[3] = (-2.0 * cw) / aa0; b[4] = (1.0 - alpha) / aa0;
+    }
+    const double a7 = std::exp(-two_pi * jmin(sl[12], srate * 0.45) / srate);
+    c[30] = a7; c[31] = 1 - a7;
+    c[32] = 1.0 - std::exp(-two_pi * jmin(sl[13], srate * 0.45) / srate);
+    c[33] = sl[14]; c[34] = 0; c[35] = 0;
+}
+
+class Cascade8 : public PluginImpl {
+    std::vector<double> h_coef;
+    double* d_coef = nullptr;
+    void* d_tables = nullptr;
+    double* d_state = nullptr;
+
+public:
+    ~Cascade8() override { cudaFree(d_coef); cudaFree(d_tables); cudaFree(d_state); }
+
+    bool create(Instance& I) override
+    {
+        h_coef.assign((size_t)I.n_streams * kC8Coefs, 0.0);
+        return cuda_ok(cudaMalloc(&d_coef, h_coef.size() * sizeof(double)), "cascade8 coef") &&
+               cuda_ok(cudaMalloc(&d_tables, (size_t)I.n_streams * cascade8_tables_bytes(I.precision)), "cascade8 tables") &&
+               cuda_ok(cudaMalloc(&d_state, (size_t)I.n_streams * kC8State * sizeof(double)), "cascade8 state");
+    }
+
+    bool reset(Instance& I) override   // @init: all filter state zero
+    {
+        return cuda_ok(cudaMemsetAsync(d_state, 0, (size_t)I.n_streams * kC8State * sizeof(double), I.stream), "cascade8 reset");
+    }
+
+    bool sliders_changed(Instance& I, int s0, int ns, const std::vector<int>& streams) override
+    {
+        const int nd = (int)I.decls.size();
+        for (int s : streams) c8_slider(&I.sliders[(size_t)s * nd], I.srate, &h_coef[(size_t)s * kC8Coefs]);
+        // The copy source must stay valid until the copy ran: h_coef is pageable, so the async copy
+        // is staged by the runtime before returning.
+        if (!cuda_ok(cudaMemcpyAsync(d_coef + (size_t)s0 * kC8Coefs, &h_coef[(size_t)s0 * kC8Coefs],
+                                     (size_t)ns * kC8Coefs * sizeof(double), cudaMemcpyHostToDevice, I.stream), "cascade8 coef upload"))
+            return false;
+        ++I.launches;
+        return cascade8_build_tables(d_coef + (size_t)s0 * kC8Coefs,
+                                     (char*)d_tables + (size_t)s0 * cascade8_tables_bytes(I.precision), ns, I.precision, I.stream);
+    }
+
+    bool run(Instance& I, int s0, int ns, const float* in, float* out, double* tap, int64_t n, int64_t stride) override
+    {
+        // cascade8 has no @block section and its @sample does not read samplesblock, so a run of
+        // host blocks with unchanged sliders is one contiguous span.
+        C8Launch L;
+        L.row_stride = stride; L.n_streams = ns; L.precision = I.precision; L.stream = I.stream;
+        L.tables = (char*)d_tables + (size_t)s0 * cascade8_tables_bytes(I.precision);
+        L.state = d_state + (size_t)s0 * kC8State;
+        L.warps = I.opt_warps ? I.opt_warps : cascade8_pick_warps(ns, I.precision, I.device);
+        const bool aligned = ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) & 15) == 0 && (stride % 4) == 0;
+        const int64_t n_main = (aligned && !I.opt_force_generic) ? n - (n % kL_host()) : 0;
+        if (n_main > 0) {
+            L.in = in; L.out = out; L.tap = tap; L.n_frames = n_main; L.use_tma = true;
+            const bool timed = I.time_begin();
+            if (!cascade8_launch(L)) return false;
+            if (timed) I.time_end();
+            ++I.launches;
+        }
+        if (n > n_main) {
+            L.in = in + n_main; L.out = out + n_main; L.tap = tap ? tap + n_main : nullptr;
+            L.n_frames = n - n_main; L.use_tma = false;
+            const bool timed = (n_main == 0) && I.time_begin();
+            if (!cascade8_launch(L)) return false;
+            if (timed) I.time_end();
+            ++I.launches;
+        }
+        return true;
+    }
+
+    bool read_state(Instance& I, const char* name, double* out) override
+    {
+        static const char* names[14] = {"z11", "z12", "z21", "z22", "z31", "z32", "z41", "z42", "z51", "z52", "z61", "z62", "lp7", "lp8"};
+        int idx = -1;
+        for (int i = 0; i < 14; ++i) if (std::strcmp(name, names[i]) == 0) idx = i;
+        if (idx < 0) { set_error(std::string("cascade8: unknown state variable ") + name); return false; }
+        std::vector<double> h((size_t)I.n_streams * kC8State);
+        if (!cuda_ok(cudaStreamSynchronize(I.stream), "sync")) return false;
+        if (!cuda_ok(cudaMemcpy(h.data(), d_state, h.size() * sizeof(double), cudaMemcpyDeviceToHost), "state read")) return false;
+        for (int s = 0; s < I.n_streams; ++s) out[s] = h[(size_t)s * kC8State + idx];
+        return true;
+    }
+
+    static int kL_host() { return 32; }
+};
+
+}  // namespace
+
+PluginImpl* make_cascade8() { return new Cascade8(); }
+const char* cascade8_slider_text() { return kSliderText; }
+
+}  // namespace za

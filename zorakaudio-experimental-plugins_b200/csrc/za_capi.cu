@@ -1,0 +1,445 @@
+// za_capi.cu -- the C ABI of include/za_gpu.h: catalogue, instance life cycle, and the batch
+// entry points that mirror prepareToPlay / processBlock (src/JSFXJuceProcessor.cpp:3239-3342,
+// 3435-3772) over n_streams instances.  No CPU fallback: every compute call needs a CUDA device.
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+
+#include "za_host.h"
+
+namespace za {
+
+// ---- errors -------------------------------------------------------------------------------------
+static thread_local std::string g_err;
+void set_error(const std::string& msg) { g_err = msg; }
+bool cuda_ok(cudaError_t e, const char* what)
+{
+    if (e == cudaSuccess) return true;
+    set_error(std::string(what) + ": " + cudaGetErrorString(e));
+    return false;
+}
+
+// ---- tensor maps (driver entry point resolved at run time; libcuda is not linked) ---------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_tiled()
+{
+    static EncodeTiledFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = (EncodeTiledFn)p;
+    });
+    return fn;
+}
+
+bool make_chunk_tensor_map(CUtensorMap* map, const float* base, int64_t n_chunks, int64_t n_rows,
+                           int64_t row_stride_frames, int box_rows)
+{
+    EncodeTiledFn fn = encode_tiled();
+    if (!fn) { set_error("cuTensorMapEncodeTiled is not available from this driver"); return false; }
+    const cuuint64_t dims[3] = {32, (cuuint64_t)n_chunks, (cuuint64_t)n_rows};
+    const cuuint64_t strides[2] = {128, (cuuint64_t)row_stride_frames * 4};   // bytes, dims 1 and 2
+    const cuuint32_t box[3] = {32, (cuuint32_t)box_rows, 1};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    const CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void*)base, dims, strides, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        char buf[160];
+        std::snprintf(buf, sizeof buf, "cuTensorMapEncodeTiled failed (%d): chunks=%lld rows=%lld stride=%lld", (int)r,
+                      (long long)n_chunks, (long long)n_rows, (long long)row_stride_frames);
+        set_error(buf);
+        return false;
+    }
+    return true;
+}
+
+// ---- catalogue ----------------------------------------------------------------------------------
+const char* cascade8_slider_text();
+
+const std::vector<PluginDesc>& plugin_table()
+{
+    static const std::vector<PluginDesc> t = {
+        {"cascade8", 1, 1, 2, 0, cascade8_slider_text(), &make_cascade8},
+    };
+    return t;
+}
+const PluginDesc* find_plugin(const char* key)
+{
+    if (!key) return nullptr;
+    for (const auto& p : plugin_table())
+        if (std::strcmp(p.key, key) == 0) return &p;
+    return nullptr;
+}
+
+// ---- kernel timing ------------------------------------------------------------------------------
+bool Instance::time_begin()
+{
+    if (ev_used + 2 > 2048) return false;
+    while ((int)ev.size() < ev_used + 2) {
+        cudaEvent_t e;
+        if (cudaEventCreate(&e) != cudaSuccess) return false;
+        ev.push_back(e);
+    }
+    cudaEventRecord(ev[ev_used], stream);
+    return true;
+}
+void Instance::time_end()
+{
+    cudaEventRecord(ev[ev_used + 1], stream);
+    ev_used += 2;
+}
+
+// ---- processBlock over a stream range with device buffers ----------------------------------------
+// params: [n_param_blocks][n_streams][n_decl] host floats (may be null with n_param_blocks == 0).
+// in/out/tap point at stream s0's first row.
+static bool process_range(Instance& I, const float* params, int n_param_blocks, int s0, int ns, const float* in,
+                          float* out, double* tap, int64_t n_frames, int64_t stride)
+{
+    const int nd = (int)I.decls.size();
+    const int64_t bl = I.block_len;
+    const int64_t n_blocks = (n_frames + bl - 1) / bl;
+    std::vector<int> changed;
+    int64_t run_start = 0;     // first frame of the pending run
+    for (int64_t b = 0; b < n_blocks; ++b) {
+        changed.clear();
+        // pushParamsToStateSliders (:9286-9357): only rows that can differ need a look
+        if (params && n_param_blocks > 0 && (b < n_param_blocks)) {
+            const float* row = params + ((size_t)b * I.n_streams + s0) * nd;
+            for (int s = 0; s < ns; ++s) {
+                double* cur = &I.sliders[(size_t)(s0 + s) * nd];
+                bool ch = false;
+                for (int j = 0; j < nd; ++j) {
+                    const double v = quantise_slider(I.decls[j], row[(size_t)s * nd + j]);
+                    if (!I.sliders_valid[s0 + s] || v != cur[j]) { ch = true; cur[j] = v; }
+                }
+                I.sliders_valid[s0 + s] = 1;
+                if (ch) changed.push_back(s0 + s);
+            }
+        }
+        if (!changed.empty()) {
+            const int64_t f = b * bl;
+            if (f > run_start) {   // flush the run rendered with the old parameters
+                if (!I.impl->run(I, s0, ns, in + run_start, out + run_start, tap ? tap + run_start : nullptr, f - run_start, stride))
+                    return false;
+                run_start = f;
+            }
+            if (!I.impl->sliders_changed(I, s0, ns, changed)) return false;   // @slider (:3545-3547)
+        }
+        if (!(params && n_param_blocks > 0 && b + 1 < n_param_blocks)) break;  // nothing can change any more
+    }
+    if (n_frames > run_start)
+        if (!I.impl->run(I, s0, ns, in + run_start, out + run_start, tap ? tap + run_start : nullptr, n_frames - run_start, stride))
+            return false;
+    return true;
+}
+
+static void free_staging(Instance& I)
+{
+    for (int i = 0; i < 3; ++i) {
+        cudaFree(I.stage_in[i]); cudaFree(I.stage_out[i]); cudaFree(I.stage_tap[i]);
+        I.stage_in[i] = I.stage_out[i] = nullptr; I.stage_tap[i] = nullptr;
+    }
+    I.stage_in_bytes = I.stage_out_bytes = I.stage_tap_bytes = 0;
+}
+
+// Host buffers: stream chunks flow H2D -> kernels -> D2H through three staging slots on three CUDA
+// streams, so PCIe traffic in both directions overlaps the kernels.
+static bool process_host(Instance& I, const float* params, int npb, const float* in, float* out, double* tap,
+                         int64_t n_frames, int64_t stride)
+{
+    const int n_in = I.desc->n_in, n_out = I.desc->n_out;
+    const int64_t dstride = (n_frames + 31) / 32 * 32;                 // device rows stay TMA-aligned
+    int cs = I.opt_host_chunk;
+    if (cs <= 0) {
+        const int64_t per_stream = dstride * 4 * (n_in + n_out) + (tap ? dstride * 8 * n_out : 0);
+        cs = (int)std::max<int64_t>(1, std::min<int64_t>(I.n_streams, (256ll << 20) / std::max<int64_t>(per_stream, 1)));
+        if (cs >= 8) cs &= ~7;
+    }
+    cs = std::min(cs, I.n_streams);
+    const size_t need_in = (size_t)cs * n_in * dstride * 4, need_out = (size_t)cs * n_out * dstride * 4;
+    const size_t need_tap = tap ? (size_t)cs * n_out * dstride * 8 : 0;
+    if (need_in > I.stage_in_bytes || need_out > I.stage_out_bytes || need_tap > I.stage_tap_bytes) {
+        free_staging(I);
+        for (int i = 0; i < 3; ++i) {
+            if (!cuda_ok(cudaMalloc(&I.stage_in[i], need_in), "staging in")) return false;
+            if (!cuda_ok(cudaMalloc(&I.stage_out[i], need_out), "staging out")) return false;
+            if (need_tap && !cuda_ok(cudaMalloc(&I.stage_tap[i], need_tap), "staging tap")) return false;
+        }
+        I.stage_in_bytes = need_in; I.stage_out_bytes = need_out; I.stage_tap_bytes = need_tap;
+    }
+    if (!I.h2d) {
+        if (!cuda_ok(cudaStreamCreateWithFlags(&I.h2d, cudaStreamNonBlocking), "h2d stream")) return false;
+        if (!cuda_ok(cudaStreamCreateWithFlags(&I.d2h, cudaStreamNonBlocking), "d2h stream")) return false;
+        for (int i = 0; i < 3; ++i) {
+            cudaEventCreateWithFlags(&I.ev_h2d[i], cudaEventDisableTiming);
+            cudaEventCreateWithFlags(&I.ev_comp[i], cudaEventDisableTiming);
+            cudaEventCreateWithFlags(&I.ev_d2h[i], cudaEventDisableTiming);
+        }
+    }
+    int c = 0;
+    for (int s0 = 0; s0 < I.n_streams; s0 += cs, ++c) {
+        const int ns = std::min(cs, I.n_streams - s0), slot = c % 3;
+        if (c >= 3) cudaStreamWaitEvent(I.h2d, I.ev_d2h[slot], 0);     // slot drained
+        if (!cuda_ok(cudaMemcpy2DAsync(I.stage_in[slot], dstride * 4, in + (size_t)s0 * n_in * stride, stride * 4,
+                                       n_frames * 4, (size_t)ns * n_in, cudaMemcpyHostToDevice, I.h2d), "H2D"))
+            return false;
+        cudaEventRecord(I.ev_h2d[slot], I.h2d);
+        cudaStreamWaitEvent(I.stream, I.ev_h2d[slot], 0);
+        if (!process_range(I, params, npb, s0, ns, I.stage_in[slot], I.stage_out[slot], tap ? I.stage_tap[slot] : nullptr,
+                           n_frames, dstride))
+            return false;
+        cudaEventRecord(I.ev_comp[slot], I.stream);
+        cudaStreamWaitEvent(I.d2h, I.ev_comp[slot], 0);
+        if (!cuda_ok(cudaMemcpy2DAsync(out + (size_t)s0 * n_out * stride, stride * 4, I.stage_out[slot], dstride * 4,
+                                       n_frames * 4, (size_t)ns * n_out, cudaMemcpyDeviceToHost, I.d2h), "D2H"))
+            return false;
+        if (tap && !cuda_ok(cudaMemcpy2DAsync(tap + (size_t)s0 * n_out * stride, stride * 8, I.stage_tap[slot], dstride * 8,
+                                              n_frames * 8, (size_t)ns * n_out, cudaMemcpyDeviceToHost, I.d2h), "D2H tap"))
+            return false;
+        cudaEventRecord(I.ev_d2h[slot], I.d2h);
+    }
+    return cuda_ok(cudaStreamSynchronize(I.d2h), "D2H sync") && cuda_ok(cudaStreamSynchronize(I.stream), "compute sync");
+}
+
+static int do_process(Instance* I, const float* params, int npb, const float* in, float* out, double* tap,
+                      int64_t n_frames, int64_t stride, int mem)
+{
+    if (!I || !in || !out || n_frames < 0 || stride < n_frames || npb < 0 || (npb > 0 && !params)) {
+        set_error("za_gpu_process: bad argument");
+        return ZA_ERR_ARG;
+    }
+    if (!I->prepared) { set_error("za_gpu_process before za_gpu_prepare"); return ZA_ERR_STATE; }
+    if (tap && I->precision != ZA_F64) { set_error("za_gpu_process_tap64 needs precision ZA_F64"); return ZA_ERR_ARG; }
+    if (!cuda_ok(cudaSetDevice(I->device), "cudaSetDevice")) return ZA_ERR_CUDA;
+    I->ev_used = 0;
+    if (n_frames == 0) return ZA_OK;
+    bool ok;
+    if (mem == ZA_MEM_DEVICE) ok = process_range(*I, params, npb, 0, I->n_streams, in, out, tap, n_frames, stride);
+    else if (mem == ZA_MEM_HOST) ok = process_host(*I, params, npb, in, out, tap, n_frames, stride);
+    else { set_error("za_gpu_process: unknown memory kind"); return ZA_ERR_ARG; }
+    return ok ? ZA_OK : ZA_ERR_CUDA;
+}
+
+}  // namespace za
+
+using namespace za;
+
+struct za_gpu_instance { Instance I; };
+
+extern "C" {
+
+ZA_API const char* za_gpu_last_error(void) { return g_err.c_str(); }
+ZA_API const char* za_gpu_version(void) { return "za_gpu 0.1 (sm_100a)"; }
+ZA_API int za_gpu_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+ZA_API int za_gpu_plugin_count(void) { return (int)plugin_table().size(); }
+ZA_API const char* za_gpu_plugin_key(int i)
+{
+    return (i >= 0 && i < (int)plugin_table().size()) ? plugin_table()[i].key : nullptr;
+}
+ZA_API int za_gpu_plugin_info(const char* key, za_plugin_info* out)
+{
+    const PluginDesc* d = find_plugin(key);
+    if (!d) { set_error("unknown plugin_key"); return ZA_ERR_PLUGIN; }
+    if (!out) return ZA_ERR_ARG;
+    out->n_in = d->n_in; out->n_out = d->n_out; out->kind = d->kind; out->latency = d->latency;
+    out->n_sliders = (int)parse_slider_decls(d->slider_text).size();
+    return ZA_OK;
+}
+static void fill_slider(const SliderDecl& s, za_slider_info* o)
+{
+    std::memset(o, 0, sizeof *o);
+    o->index0 = s.index0; o->is_choice = s.is_choice ? 1 : 0;
+    o->def = s.def; o->min = s.min; o->max = s.max; o->step = s.step;
+    std::strncpy(o->alias, s.alias.c_str(), sizeof(o->alias) - 1);
+}
+ZA_API int za_gpu_slider_info(const char* key, int column, za_slider_info* out)
+{
+    const PluginDesc* d = find_plugin(key);
+    if (!d) { set_error("unknown plugin_key"); return ZA_ERR_PLUGIN; }
+    const auto decls = parse_slider_decls(d->slider_text);
+    if (!out || column < 0 || column >= (int)decls.size()) return ZA_ERR_ARG;
+    fill_slider(decls[column], out);
+    return ZA_OK;
+}
+ZA_API int za_gpu_parse_sliders(const char* text, za_slider_info* out, int cap)
+{
+    if (!text || cap < 0 || (cap > 0 && !out)) return ZA_ERR_ARG;
+    const auto decls = parse_slider_decls(text);
+    for (int i = 0; i < (int)decls.size() && i < cap; ++i) fill_slider(decls[i], &out[i]);
+    return (int)decls.size();
+}
+ZA_API int za_gpu_quantise(const za_slider_info* s, float host_value, double* out)
+{
+    if (!s || !out) return ZA_ERR_ARG;
+    SliderDecl d;
+    d.index0 = s->index0; d.is_choice = s->is_choice != 0; d.def = s->def; d.min = s->min; d.max = s->max; d.step = s->step;
+    *out = quantise_slider(d, host_value);
+    return ZA_OK;
+}
+
+ZA_API int za_gpu_create(const char* key, int n_streams, double srate, int block_len, int precision, int device,
+                         za_gpu_handle* out)
+{
+    if (!out) return ZA_ERR_ARG;
+    *out = nullptr;
+    const PluginDesc* d = find_plugin(key);
+    if (!d) { set_error(std::string("unknown plugin_key: ") + (key ? key : "(null)")); return ZA_ERR_PLUGIN; }
+    if (n_streams <= 0 || block_len <= 0 || !(srate > 0) || (precision != ZA_F32 && precision != ZA_F64)) {
+        set_error("za_gpu_create: bad argument");
+        return ZA_ERR_ARG;
+    }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) {
+        cudaGetLastError();
+        set_error("no CUDA device: this library has no CPU fallback");
+        return ZA_ERR_CUDA;
+    }
+    if (device < 0 || device >= ndev) { set_error("za_gpu_create: bad device index"); return ZA_ERR_ARG; }
+    if (!cuda_ok(cudaSetDevice(device), "cudaSetDevice")) return ZA_ERR_CUDA;
+    auto* h = new za_gpu_instance();
+    Instance& I = h->I;
+    I.desc = d; I.decls = parse_slider_decls(d->slider_text);
+    I.n_streams = n_streams; I.block_len = block_len; I.precision = precision; I.device = device; I.srate = srate;
+    I.sliders.assign((size_t)n_streams * I.decls.size(), 0.0);
+    for (int s = 0; s < n_streams; ++s)
+        for (size_t j = 0; j < I.decls.size(); ++j) I.sliders[(size_t)s * I.decls.size() + j] = (double)I.decls[j].def;
+    I.sliders_valid.assign(n_streams, 0);
+    if (!cuda_ok(cudaStreamCreateWithFlags(&I.own_stream, cudaStreamNonBlocking), "stream create")) { delete h; return ZA_ERR_CUDA; }
+    I.stream = I.own_stream;
+    I.impl.reset(d->make());
+    if (!I.impl->create(I)) { za_gpu_destroy(h); return ZA_ERR_CUDA; }
+    *out = h;
+    return ZA_OK;
+}
+
+ZA_API int za_gpu_destroy(za_gpu_handle h)
+{
+    if (!h) return ZA_OK;
+    Instance& I = h->I;
+    cudaSetDevice(I.device);
+    cudaDeviceSynchronize();
+    I.impl.reset();
+    free_staging(I);
+    for (auto e : I.ev) cudaEventDestroy(e);
+    for (int i = 0; i < 3; ++i) {
+        if (I.ev_h2d[i]) cudaEventDestroy(I.ev_h2d[i]);
+        if (I.ev_comp[i]) cudaEventDestroy(I.ev_comp[i]);
+        if (I.ev_d2h[i]) cudaEventDestroy(I.ev_d2h[i]);
+    }
+    if (I.h2d) cudaStreamDestroy(I.h2d);
+    if (I.d2h) cudaStreamDestroy(I.d2h);
+    if (I.own_stream) cudaStreamDestroy(I.own_stream);
+    delete h;
+    return ZA_OK;
+}
+
+ZA_API int za_gpu_set_stream(za_gpu_handle h, void* s)
+{
+    if (!h) return ZA_ERR_ARG;
+    h->I.stream = s ? (cudaStream_t)s : h->I.own_stream;
+    return ZA_OK;
+}
+
+ZA_API int za_gpu_prepare(za_gpu_handle h, const float* p0)
+{
+    if (!h) return ZA_ERR_ARG;
+    Instance& I = h->I;
+    if (!cuda_ok(cudaSetDevice(I.device), "cudaSetDevice")) return ZA_ERR_CUDA;
+    const int nd = (int)I.decls.size();
+    // resetStateStructOnly + lastSlidersValid=false (:3250, 3298), push sliders BEFORE @init (:3297-3303)
+    std::vector<int> all(I.n_streams);
+    for (int s = 0; s < I.n_streams; ++s) {
+        all[s] = s;
+        for (int j = 0; j < nd; ++j) {
+            const float hv = p0 ? p0[(size_t)s * nd + j] : I.decls[j].def;
+            I.sliders[(size_t)s * nd + j] = quantise_slider(I.decls[j], hv);
+        }
+        I.sliders_valid[s] = 1;
+    }
+    if (!I.impl->reset(I)) return ZA_ERR_CUDA;                       // @init
+    if (!I.impl->sliders_changed(I, 0, I.n_streams, all)) return ZA_ERR_CUDA;   // alias re-apply + @slider (:3308-3318)
+    I.prepared = true;
+    return ZA_OK;
+}
+
+ZA_API int za_gpu_process(za_gpu_handle h, const float* params, int npb, const float* in, float* out, int64_t n_frames,
+                          int64_t stride, int mem)
+{
+    return do_process(h ? &h->I : nullptr, params, npb, in, out, nullptr, n_frames, stride, mem);
+}
+ZA_API int za_gpu_process_tap64(za_gpu_handle h, const float* params, int npb, const float* in, float* out, double* tap,
+                                int64_t n_frames, int64_t stride, int mem)
+{
+    if (!tap) { set_error("za_gpu_process_tap64: tap64 is null"); return ZA_ERR_ARG; }
+    return do_process(h ? &h->I : nullptr, params, npb, in, out, tap, n_frames, stride, mem);
+}
+
+ZA_API int za_gpu_read_state(za_gpu_handle h, const char* name, double* out)
+{
+    if (!h || !name || !out) return ZA_ERR_ARG;
+    if (!cuda_ok(cudaSetDevice(h->I.device), "cudaSetDevice")) return ZA_ERR_CUDA;
+    return h->I.impl->read_state(h->I, name, out) ? ZA_OK : ZA_ERR_ARG;
+}
+ZA_API int za_gpu_sync(za_gpu_handle h)
+{
+    if (!h) return ZA_ERR_ARG;
+    cudaSetDevice(h->I.device);
+    return cuda_ok(cudaStreamSynchronize(h->I.stream), "sync") ? ZA_OK : ZA_ERR_CUDA;
+}
+ZA_API int za_gpu_launch_count(za_gpu_handle h, int64_t* n)
+{
+    if (!h || !n) return ZA_ERR_ARG;
+    *n = h->I.launches;
+    return ZA_OK;
+}
+ZA_API int za_gpu_last_kernel_ms(za_gpu_handle h, double* ms, int* launches)
+{
+    if (!h || !ms) return ZA_ERR_ARG;
+    Instance& I = h->I;
+    cudaSetDevice(I.device);
+    if (!cuda_ok(cudaStreamSynchronize(I.stream), "sync")) return ZA_ERR_CUDA;
+    double tot = 0;
+    for (int i = 0; i + 1 < I.ev_used; i += 2) {
+        float t = 0;
+        if (cudaEventElapsedTime(&t, I.ev[i], I.ev[i + 1]) == cudaSuccess) tot += t;
+    }
+    *ms = tot;
+    if (launches) *launches = I.ev_used / 2;
+    return ZA_OK;
+}
+ZA_API int za_gpu_set_option(za_gpu_handle h, const char* name, int value)
+{
+    if (!h || !name) return ZA_ERR_ARG;
+    Instance& I = h->I;
+    if (!std::strcmp(name, "force_generic_io")) I.opt_force_generic = value;
+    else if (!std::strcmp(name, "warps_per_stream")) I.opt_warps = value;
+    else if (!std::strcmp(name, "host_chunk_streams")) I.opt_host_chunk = value;
+    else { set_error(std::string("unknown option ") + name); return ZA_ERR_ARG; }
+    return ZA_OK;
+}
+
+ZA_API int za_gpu_render(const char* key, const float* params, const float* in, float* out, int n_streams, int64_t n_frames)
+{
+    za_gpu_handle h = nullptr;
+    int rc = za_gpu_create(key, n_streams, 48000.0, 512, ZA_F64, 0, &h);
+    if (rc != ZA_OK) return rc;
+    rc = za_gpu_prepare(h, params);
+    if (rc == ZA_OK) rc = za_gpu_process(h, nullptr, 0, in, out, n_frames, n_frames, ZA_MEM_HOST);
+    za_gpu_destroy(h);
+    return rc;
+}
+
+}  // extern "C"

@@ -1,0 +1,79 @@
+// za_host.h -- host-side runtime behind the C ABI: plugin registry, slider layout, instances.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "../../include/za_gpu.h"
+#include "za_internal.h"
+
+namespace za {
+
+struct SliderDecl {          // JsfxSliderDecl, src/JSFXJuceProcessor.cpp:520-545 (numeric part)
+    int index0 = 0;
+    bool is_choice = false;
+    float def = 0, min = 0, max = 1, step = 0.001f;
+    std::string alias;
+};
+
+std::vector<SliderDecl> parse_slider_decls(const char* jsfx_text);
+double quantise_slider(const SliderDecl& d, float host_value);
+
+struct Instance;
+
+// Per-plugin device back end.  All state lives in SoA device buffers owned by the implementation.
+// Streams [s0, s0+ns) may be driven independently of other ranges (host-memory pipelining).
+class PluginImpl {
+public:
+    virtual ~PluginImpl() {}
+    virtual bool create(Instance& inst) = 0;
+    virtual bool reset(Instance& inst) = 0;                                            // memset + @init
+    virtual bool sliders_changed(Instance& inst, int s0, int ns, const std::vector<int>& streams) = 0;  // @slider
+    // frames [0, n) of rows starting at in/out (device pointers to stream s0, first frame of the run),
+    // parameters constant over the run, split into host blocks of inst.block_len (@block per block).
+    virtual bool run(Instance& inst, int s0, int ns, const float* in, float* out, double* tap,
+                     int64_t n, int64_t stride) = 0;
+    virtual bool read_state(Instance& inst, const char* name, double* out) = 0;
+};
+
+struct PluginDesc {
+    const char* key;
+    int n_in, n_out, kind, latency;
+    const char* slider_text;                 // the plugin's slider declaration lines (its parameter API)
+    PluginImpl* (*make)();
+};
+
+const std::vector<PluginDesc>& plugin_table();
+const PluginDesc* find_plugin(const char* key);
+
+struct Instance {
+    const PluginDesc* desc = nullptr;
+    std::vector<SliderDecl> decls;
+    int n_streams = 0, block_len = 512, precision = 1, device = 0;
+    double srate = 48000.0;
+    cudaStream_t stream = nullptr, own_stream = nullptr, h2d = nullptr, d2h = nullptr;
+    bool prepared = false;
+    std::vector<double> sliders;             // [n_streams][n_decl] current quantised values (st.sliders)
+    std::vector<uint8_t> sliders_valid;      // lastSlidersValid per stream
+    std::unique_ptr<PluginImpl> impl;
+    int64_t launches = 0;
+    // options
+    int opt_force_generic = 0, opt_warps = 0, opt_host_chunk = 0;
+    // timing of the dominant kernel
+    std::vector<cudaEvent_t> ev;             // pairs
+    int ev_used = 0;
+    bool time_begin();                       // records a start event on `stream` (false if pool exhausted)
+    void time_end();
+    // host-memory staging
+    float* stage_in[3] = {nullptr, nullptr, nullptr};
+    float* stage_out[3] = {nullptr, nullptr, nullptr};
+    double* stage_tap[3] = {nullptr, nullptr, nullptr};
+    size_t stage_in_bytes = 0, stage_out_bytes = 0, stage_tap_bytes = 0;
+    cudaEvent_t ev_h2d[3] = {}, ev_comp[3] = {}, ev_d2h[3] = {};
+};
+
+PluginImpl* make_cascade8();
+
+}  // namespace za

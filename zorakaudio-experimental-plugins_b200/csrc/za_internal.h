@@ -1,0 +1,43 @@
+// za_internal.h -- host-side declarations shared between the C-ABI layer and the kernel files.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+
+namespace za {
+
+void set_error(const std::string& msg);          // thread-local text behind za_gpu_last_error()
+bool cuda_ok(cudaError_t e, const char* what);   // false + set_error on failure
+
+// Encodes a 3-D SWIZZLE_128B tensor map over planar float rows:
+//   dim0 = 32 frames (one chunk), dim1 = n_chunks, dim2 = n_rows; box = {32, box_rows, 1}.
+// base must be 16-byte aligned and row_stride_frames a multiple of 4.
+bool make_chunk_tensor_map(CUtensorMap* map, const float* base, int64_t n_chunks, int64_t n_rows,
+                           int64_t row_stride_frames, int box_rows);
+
+// ---- cascade8 (LTI cascade: 6 TDF-II biquads + 2 one-poles) -----------------------------------
+constexpr int kC8Coefs = 36;     // per stream: 6 x (b0,b1,b2,a1,a2), a7, 1-a7, c8, mix, pad
+constexpr int kC8State = 16;     // per stream: z[6][2], lp7, lp8, pad (double, persists across calls)
+
+struct C8Launch {
+    const float* in;         // row 0, first frame of this launch
+    float* out;
+    double* tap;             // optional double tap (same indexing), fp64 only
+    int64_t row_stride;      // frames between consecutive streams
+    int64_t n_frames;        // frames in this launch
+    int n_streams;
+    const void* tables;      // C8Tables<R>[n_streams] (device)
+    double* state;           // [n_streams][kC8State] (device)
+    int precision;           // 0 = f32, 1 = f64
+    int warps;               // warps per stream (1, 2 or 4)
+    bool use_tma;            // needs n_frames % 32 == 0, 16-byte aligned rows
+    cudaStream_t stream;
+};
+
+size_t cascade8_tables_bytes(int precision);
+bool cascade8_build_tables(const double* d_coef, void* d_tables, int n_streams, int precision, cudaStream_t s);
+bool cascade8_launch(const C8Launch& a);
+int cascade8_pick_warps(int n_streams, int precision, int device);
+
+}  // namespace za

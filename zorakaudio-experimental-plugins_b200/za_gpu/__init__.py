@@ -1,0 +1,216 @@
+"""za_gpu -- thin ctypes binding over libza_gpu.so (the C ABI of include/za_gpu.h).
+
+This is plumbing for tests and bench.py: the product is the shared library.  `BatchProcessor`
+mirrors the reference host processor's call shape (prepareToPlay / processBlock,
+src/JSFXJuceProcessor.cpp:3239, 3435) over n_streams instances.  There is no CPU fallback:
+if the library is missing or no CUDA device exists, construction raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+
+import numpy as np
+
+PKG = Path(__file__).resolve().parent.parent
+LIB_PATH = PKG / "libza_gpu.so"
+
+ZA_F32, ZA_F64 = 0, 1
+ZA_MEM_HOST, ZA_MEM_DEVICE = 0, 1
+
+
+class ZaError(RuntimeError):
+    pass
+
+
+class PluginInfo(C.Structure):
+    _fields_ = [("n_in", C.c_int32), ("n_out", C.c_int32), ("n_sliders", C.c_int32), ("kind", C.c_int32),
+                ("latency", C.c_int32)]
+
+
+class SliderInfo(C.Structure):
+    _fields_ = [("index0", C.c_int32), ("is_choice", C.c_int32), ("def_", C.c_float), ("min", C.c_float),
+                ("max", C.c_float), ("step", C.c_float), ("alias", C.c_char * 64)]
+
+
+# every symbol include/za_gpu.h declares (tests check the library exports all of them)
+SYMBOLS = [
+    "za_gpu_plugin_count", "za_gpu_plugin_key", "za_gpu_plugin_info", "za_gpu_slider_info", "za_gpu_parse_sliders",
+    "za_gpu_quantise", "za_gpu_create", "za_gpu_destroy", "za_gpu_set_stream", "za_gpu_prepare", "za_gpu_process",
+    "za_gpu_process_tap64", "za_gpu_read_state", "za_gpu_sync", "za_gpu_launch_count", "za_gpu_last_kernel_ms",
+    "za_gpu_set_option", "za_gpu_render", "za_gpu_last_error", "za_gpu_device_count", "za_gpu_version",
+]
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    global _lib
+    if _lib is None:
+        if not LIB_PATH.exists():
+            raise ZaError(f"{LIB_PATH} is missing: build it with `python __graft_entry__.py build` "
+                          "(there is no CPU fallback)")
+        L = C.CDLL(str(LIB_PATH))
+        L.za_gpu_plugin_key.restype = C.c_char_p
+        L.za_gpu_plugin_key.argtypes = [C.c_int]
+        L.za_gpu_last_error.restype = C.c_char_p
+        L.za_gpu_version.restype = C.c_char_p
+        L.za_gpu_plugin_info.argtypes = [C.c_char_p, C.POINTER(PluginInfo)]
+        L.za_gpu_slider_info.argtypes = [C.c_char_p, C.c_int, C.POINTER(SliderInfo)]
+        L.za_gpu_parse_sliders.argtypes = [C.c_char_p, C.POINTER(SliderInfo), C.c_int]
+        L.za_gpu_quantise.argtypes = [C.POINTER(SliderInfo), C.c_float, C.POINTER(C.c_double)]
+        L.za_gpu_create.argtypes = [C.c_char_p, C.c_int, C.c_double, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
+        L.za_gpu_destroy.argtypes = [C.c_void_p]
+        L.za_gpu_set_stream.argtypes = [C.c_void_p, C.c_void_p]
+        L.za_gpu_prepare.argtypes = [C.c_void_p, C.c_void_p]
+        L.za_gpu_process.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int]
+        L.za_gpu_process_tap64.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
+                                           C.c_int64, C.c_int]
+        L.za_gpu_read_state.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p]
+        L.za_gpu_sync.argtypes = [C.c_void_p]
+        L.za_gpu_launch_count.argtypes = [C.c_void_p, C.POINTER(C.c_int64)]
+        L.za_gpu_last_kernel_ms.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int)]
+        L.za_gpu_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
+        L.za_gpu_render.argtypes = [C.c_char_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int64]
+        _lib = L
+    return _lib
+
+
+def _check(rc: int, what: str):
+    if rc != 0:
+        raise ZaError(f"{what} failed ({rc}): {lib().za_gpu_last_error().decode()}")
+
+
+def plugin_keys():
+    L = lib()
+    return [L.za_gpu_plugin_key(i).decode() for i in range(L.za_gpu_plugin_count())]
+
+
+def plugin_info(key: str) -> PluginInfo:
+    info = PluginInfo()
+    _check(lib().za_gpu_plugin_info(key.encode(), C.byref(info)), "za_gpu_plugin_info")
+    return info
+
+
+def slider_layout(key: str):
+    n = plugin_info(key).n_sliders
+    out = []
+    for j in range(n):
+        s = SliderInfo()
+        _check(lib().za_gpu_slider_info(key.encode(), j, C.byref(s)), "za_gpu_slider_info")
+        out.append(s)
+    return out
+
+
+def parse_sliders(text: str):
+    arr = (SliderInfo * 64)()
+    n = lib().za_gpu_parse_sliders(text.encode(), arr, 64)
+    if n < 0:
+        raise ZaError("za_gpu_parse_sliders")
+    return [arr[i] for i in range(n)]
+
+
+def quantise(slider: SliderInfo, value: float) -> float:
+    out = C.c_double()
+    _check(lib().za_gpu_quantise(C.byref(slider), C.c_float(value), C.byref(out)), "za_gpu_quantise")
+    return out.value
+
+
+def _ptr(a):
+    """numpy array, torch tensor or None -> (address, keepalive)."""
+    if a is None:
+        return None
+    if isinstance(a, np.ndarray):
+        return a.ctypes.data
+    return a.data_ptr()      # torch tensor (device or pinned host)
+
+
+class BatchProcessor:
+    """n_streams instances of one plugin on one B200 (one za_gpu handle)."""
+
+    def __init__(self, plugin_key: str, n_streams: int, sample_rate: float = 48000.0, block_len: int = 512,
+                 precision: str = "f64", device: int = 0):
+        self.key = plugin_key
+        self.info = plugin_info(plugin_key)
+        self.n_streams = n_streams
+        self.block_len = block_len
+        self.precision = ZA_F64 if precision in ("f64", ZA_F64) else ZA_F32
+        self._h = C.c_void_p()
+        _check(lib().za_gpu_create(plugin_key.encode(), n_streams, sample_rate, block_len, self.precision, device,
+                                   C.byref(self._h)), "za_gpu_create")
+
+    # prepareToPlay
+    def prepare(self, param_block0=None):
+        p = None if param_block0 is None else np.ascontiguousarray(param_block0, np.float32)
+        if p is not None:
+            assert p.shape == (self.n_streams, self.info.n_sliders), p.shape
+        _check(lib().za_gpu_prepare(self._h, _ptr(p)), "za_gpu_prepare")
+        return self
+
+    # processBlock over many host blocks
+    def process(self, x, out=None, params=None, tap64=None, n_frames=None, frame_stride=None):
+        """x/out: numpy (host) or torch CUDA tensors [n_streams, n_ch, frames] float32.
+        params: None | [n_streams, n_sliders] | [n_blocks, n_streams, n_sliders] float32 (host)."""
+        is_np = isinstance(x, np.ndarray)
+        dev = (not is_np) and x.is_cuda
+        if n_frames is None:
+            n_frames = x.shape[-1]
+        if frame_stride is None:
+            frame_stride = x.shape[-1]
+        if out is None:
+            if is_np:
+                out = np.empty((self.n_streams, self.info.n_out, x.shape[-1]), np.float32)
+            else:
+                import torch
+                out = torch.empty((self.n_streams, self.info.n_out, x.shape[-1]), dtype=torch.float32, device=x.device,
+                                  pin_memory=(not dev and x.is_pinned()))
+        p, npb = None, 0
+        if params is not None:
+            p = np.ascontiguousarray(params, np.float32)
+            if p.ndim == 2:
+                p = p[None]
+            assert p.shape[1:] == (self.n_streams, self.info.n_sliders), p.shape
+            npb = p.shape[0]
+        mem = ZA_MEM_DEVICE if dev else ZA_MEM_HOST
+        if tap64 is None:
+            _check(lib().za_gpu_process(self._h, _ptr(p), npb, _ptr(x), _ptr(out), n_frames, frame_stride, mem),
+                   "za_gpu_process")
+        else:
+            _check(lib().za_gpu_process_tap64(self._h, _ptr(p), npb, _ptr(x), _ptr(out), _ptr(tap64), n_frames,
+                                              frame_stride, mem), "za_gpu_process_tap64")
+        return out
+
+    def read_state(self, name: str) -> np.ndarray:
+        out = np.empty(self.n_streams, np.float64)
+        _check(lib().za_gpu_read_state(self._h, name.encode(), out.ctypes.data), "za_gpu_read_state")
+        return out
+
+    def set_stream(self, cuda_stream_ptr):
+        _check(lib().za_gpu_set_stream(self._h, cuda_stream_ptr), "za_gpu_set_stream")
+
+    def set_option(self, name: str, value: int):
+        _check(lib().za_gpu_set_option(self._h, name.encode(), value), "za_gpu_set_option")
+
+    def sync(self):
+        _check(lib().za_gpu_sync(self._h), "za_gpu_sync")
+
+    def launch_count(self) -> int:
+        n = C.c_int64()
+        _check(lib().za_gpu_launch_count(self._h, C.byref(n)), "za_gpu_launch_count")
+        return n.value
+
+    def last_kernel_ms(self):
+        ms, k = C.c_double(), C.c_int()
+        _check(lib().za_gpu_last_kernel_ms(self._h, C.byref(ms), C.byref(k)), "za_gpu_last_kernel_ms")
+        return ms.value, k.value
+
+    def close(self):
+        if self._h:
+            lib().za_gpu_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
