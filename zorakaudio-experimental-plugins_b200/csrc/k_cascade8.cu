@@ -23,8 +23,9 @@
 namespace za {
 
 template <typename R> struct C8Tables {
-    R H2[6][kL][2];    // biquads: H2[s][k] = A^(31-k) B   (zero-state end-state response to x_k)
-    R P2[6][33][4];    // biquads: (A^32)^j, j = 0..32, row-major 2x2
+    R H2[6][kL][2];    // biquads: H2[s][k] = T A^(31-k) B  (zero-state end-state response to x_k, scan coords)
+    R P2[6][33][4];    // biquads: (N^32)^j, j = 0..32, row-major 2x2
+    R T2[6][8];        // biquads: T (4) and T^-1 (4): scan coordinates w = T s with T A T^-1 = N normal
     R H1[2][kL];       // one-poles
     R P1[2][36];       // one-poles: (alpha^32)^j, j = 0..32 (padded)
     R coef[kC8Coefs];
@@ -45,25 +46,41 @@ __global__ void cascade8_tables_kernel(const double* __restrict__ coef, C8Tables
     C8Tables<R>& t = tabs[s];
     if (sec < 6) {
         const double b0 = c[5 * sec], b1 = c[5 * sec + 1], b2 = c[5 * sec + 2], a1 = c[5 * sec + 3], a2 = c[5 * sec + 4];
-        // state update of the TDF-II recurrence: s' = A s + B x, A = [[-a1, 1], [-a2, 0]]
-        double v1 = b1 - a1 * b0, v2 = b2 - a2 * b0;
+        // state update of the TDF-II recurrence: s' = A s + B x, A = [[-a1, 1], [-a2, 0]].
+        // For poles near z = 1 the powers of A are large (|A^n| ~ 1/theta) and a scan in these
+        // coordinates loses ~cond^2 * eps.  The scan therefore runs in the real normal form of A:
+        // w = T s, T A T^-1 = N = [[sg, om], [-om, sg]] (a scaled rotation, |N^n| = r^n <= 1).
+        const double sg = -0.5 * a1, w2 = a2 - sg * sg;
+        double t00 = 1, t01 = 0, t10 = 0, t11 = 1, i00 = 1, i01 = 0, i10 = 0, i11 = 1;   // T, T^-1
+        double n00 = -a1, n01 = 1, n10 = -a2, n11 = 0;                                   // N
+        if (w2 > 1e-14 && a2 > 1e-14) {              // complex pole pair
+            const double om = sqrt(w2);
+            t00 = 0; t01 = -1.0 / a2; t10 = 1.0 / om; t11 = sg / (om * a2);
+            i00 = sg; i01 = om; i10 = -a2; i11 = 0;
+            n00 = sg; n01 = om; n10 = -om; n11 = sg;
+        }
+        const double bb1 = b1 - a1 * b0, bb2 = b2 - a2 * b0;
+        double v1 = t00 * bb1 + t01 * bb2, v2 = t10 * bb1 + t11 * bb2;
         for (int k = kL - 1; k >= 0; --k) {
             t.H2[sec][k][0] = (R)v1; t.H2[sec][k][1] = (R)v2;
-            const double n1 = -a1 * v1 + v2, n2 = -a2 * v1;
-            v1 = n1; v2 = n2;
+            const double x1 = n00 * v1 + n01 * v2, x2 = n10 * v1 + n11 * v2;
+            v1 = x1; v2 = x2;
         }
-        double m00 = 1, m01 = 0, m10 = 0, m11 = 1;       // A^32 by 32 left-multiplications
+        double m00 = 1, m01 = 0, m10 = 0, m11 = 1;       // N^32 by 32 left-multiplications
         for (int k = 0; k < kL; ++k) {
-            const double n00 = -a1 * m00 + m10, n01 = -a1 * m01 + m11, n10 = -a2 * m00, n11 = -a2 * m01;
-            m00 = n00; m01 = n01; m10 = n10; m11 = n11;
+            const double x00 = n00 * m00 + n01 * m10, x01 = n00 * m01 + n01 * m11;
+            const double x10 = n10 * m00 + n11 * m10, x11 = n10 * m01 + n11 * m11;
+            m00 = x00; m01 = x01; m10 = x10; m11 = x11;
         }
         double p00 = 1, p01 = 0, p10 = 0, p11 = 1;
         for (int j = 0; j <= 32; ++j) {
             t.P2[sec][j][0] = (R)p00; t.P2[sec][j][1] = (R)p01; t.P2[sec][j][2] = (R)p10; t.P2[sec][j][3] = (R)p11;
-            const double n00 = m00 * p00 + m01 * p10, n01 = m00 * p01 + m01 * p11;
-            const double n10 = m10 * p00 + m11 * p10, n11 = m10 * p01 + m11 * p11;
-            p00 = n00; p01 = n01; p10 = n10; p11 = n11;
+            const double x00 = m00 * p00 + m01 * p10, x01 = m00 * p01 + m01 * p11;
+            const double x10 = m10 * p00 + m11 * p10, x11 = m10 * p01 + m11 * p11;
+            p00 = x00; p01 = x01; p10 = x10; p11 = x11;
         }
+        t.T2[sec][0] = (R)t00; t.T2[sec][1] = (R)t01; t.T2[sec][2] = (R)t10; t.T2[sec][3] = (R)t11;
+        t.T2[sec][4] = (R)i00; t.T2[sec][5] = (R)i01; t.T2[sec][6] = (R)i10; t.T2[sec][7] = (R)i11;
     } else {
         const int o = sec - 6;
         // S7: lp = (1-a7) x + a7 lp ; S8: lp += c8 (x - lp)  ->  s' = alpha s + beta x
@@ -77,8 +94,11 @@ __global__ void cascade8_tables_kernel(const double* __restrict__ coef, C8Tables
         for (int j = 0; j <= 32; ++j) { t.P1[o][j] = (R)p; p *= m; }
         for (int j = 33; j < 36; ++j) t.P1[o][j] = (R)0;
     }
-    if (sec == 0)
+    if (sec == 0) {
         for (int i = 0; i < kC8Coefs; ++i) t.coef[i] = (R)c[i];
+        if (sizeof(R) == 4)     // fp32 mode: delta-coded feedback, a1 = -2 + d1, a2 = 1 - d2 (see biquad pass B)
+            for (int k = 0; k < 6; ++k) { t.coef[5 * k + 3] = (R)(c[5 * k + 3] + 2.0); t.coef[5 * k + 4] = (R)(1.0 - c[5 * k + 4]); }
+    }
 }
 
 bool cascade8_build_tables(const double* d_coef, void* d_tables, int n_streams, int precision, cudaStream_t s)
@@ -134,14 +154,18 @@ __device__ __forceinline__ void biquad_section(Ctx<R, W>& cx, R (&x)[kL], const 
             z2 = fma_(m.z, n1, fma_(m.w, n2, z2));
         }
     }
-    // state entering my warp
+    // state entering my warp: exact sequential state (z1, z2) -> scan coordinates w = T s
+    const Quad<R> tf = ld4(&tb.T2[sec][0]);
+    const Quad<R> ti = ld4(&tb.T2[sec][4]);
     R s1, s2;
     if (W == 1) {
-        s1 = cx.c[2 * sec]; s2 = cx.c[2 * sec + 1];
+        const R c1 = cx.c[2 * sec], c2 = cx.c[2 * sec + 1];
+        s1 = fma_(tf.x, c1, tf.y * c2); s2 = fma_(tf.z, c1, tf.w * c2);
     } else {
         if (cx.lane == 31) { cx.sm->wtot[sec][cx.warp][0] = z1; cx.sm->wtot[sec][cx.warp][1] = z2; }
         __syncthreads();
-        s1 = cx.sm->carry[cx.par][2 * sec]; s2 = cx.sm->carry[cx.par][2 * sec + 1];
+        const R c1 = cx.sm->carry[cx.par][2 * sec], c2 = cx.sm->carry[cx.par][2 * sec + 1];
+        s1 = fma_(tf.x, c1, tf.y * c2); s2 = fma_(tf.z, c1, tf.w * c2);
         const Quad<R> m = ld4(&tb.P2[sec][32][0]);
         for (int w = 0; w < cx.warp; ++w) {
             const R t1 = fma_(m.x, s1, fma_(m.y, s2, cx.sm->wtot[sec][w][0]));
@@ -149,12 +173,14 @@ __device__ __forceinline__ void biquad_section(Ctx<R, W>& cx, R (&x)[kL], const 
             s1 = t1; s2 = t2;
         }
     }
-    // my start state: exclusive prefix + M^lane * warp-incoming state
+    // my start state: exclusive prefix + N^(32 lane) * warp-incoming state, back to (z1, z2) = T^-1 w
     R e1 = shfl_up(z1, 1), e2 = shfl_up(z2, 1);
     if (cx.lane == 0) { e1 = 0; e2 = 0; }
     const Quad<R> pl = ld4(&tb.P2[sec][cx.lane][0]);
-    R st1 = fma_(pl.x, s1, fma_(pl.y, s2, e1));
-    R st2 = fma_(pl.z, s1, fma_(pl.w, s2, e2));
+    const R w1 = fma_(pl.x, s1, fma_(pl.y, s2, e1));
+    const R w2 = fma_(pl.z, s1, fma_(pl.w, s2, e2));
+    R st1 = fma_(ti.x, w1, ti.y * w2);
+    R st2 = fma_(ti.z, w1, ti.w * w2);
     // pass B: the reference recurrence, reference operation order (Spectral Stabilizer.jsfx:98-111)
     const R b0 = tb.coef[5 * sec], b1 = tb.coef[5 * sec + 1], b2 = tb.coef[5 * sec + 2];
     const R a1 = tb.coef[5 * sec + 3], a2 = tb.coef[5 * sec + 4];
@@ -163,9 +189,19 @@ __device__ __forceinline__ void biquad_section(Ctx<R, W>& cx, R (&x)[kL], const 
 #pragma unroll
     for (int k = 0; k < kL; ++k) {
         const R xx = x[k];
-        const R y = add(mul(b0, xx), st1);
-        const R n1 = add(sub(mul(b1, xx), mul(a1, y)), st2);
-        const R n2 = sub(mul(b2, xx), mul(a2, y));
+        R y, n1, n2;
+        if (sizeof(R) == 8) {
+            y = add(mul(b0, xx), st1);
+            n1 = add(sub(mul(b1, xx), mul(a1, y)), st2);
+            n2 = sub(mul(b2, xx), mul(a2, y));
+        } else {
+            // fp32 mode: a1, a2 hold d1 = a1 + 2 and d2 = 1 - a2.  Poles near z = 1 have a1 ~ -2,
+            // a2 ~ 1; rounding those to float moves a 40 Hz pole by ~1e-3 of its frequency, while
+            // d1, d2 keep full relative precision.  Same recurrence, one extra FMA.
+            y = fma_(b0, xx, st1);
+            n1 = fma_((R)2, y, fma_(-a1, y, fma_(b1, xx, st2)));
+            n2 = fma_(a2, y, fma_(b2, xx, -y));
+        }
         st1 = n1; st2 = n2;
         x[k] = MIX ? add(xx, mul(mix, y)) : y;
         if (PARTIAL && k + 1 == cx.v_last) { sn1 = st1; sn2 = st2; }
