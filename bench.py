@@ -37,6 +37,8 @@ SRATE = 48000.0
 N_STREAMS = 1024
 SECONDS = 60
 BYTES_PER_FRAME = 8           # mono float32 in + out
+CPU_SAMPLE_STREAMS = 1024     # bounded CPU sample: all 1024 streams x 20 s (a third of the workload)
+CPU_SAMPLE_SECONDS = 20.0
 
 
 def peaks():
@@ -105,7 +107,7 @@ def run_reference_arm(args):
     if rank != 0:
         return
     threads = os.cpu_count() or 1
-    ns, secs = max(threads * 4, 64), 10.0
+    ns, secs = CPU_SAMPLE_STREAMS, CPU_SAMPLE_SECONDS
     vals = []
     for i in range(args.warmup + args.steps):
         v, kind, dt = cpu_reference_run(ns, secs, threads)
@@ -153,6 +155,9 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the renderer has no CPU fallback")
     torch.cuda.set_device(local)
+    # a real (non-NULL) stream: the library enqueues on it and torch's events time it
+    run_stream = torch.cuda.Stream()
+    torch.cuda.set_stream(run_stream)
     dist = None
     if world > 1:
         import torch.distributed as dist
@@ -299,10 +304,10 @@ def main():
     cpu = None
     if not args.no_cpu:
         threads = os.cpu_count() or 1
-        cns = max(threads * 4, 64)
-        v, kind, dt = cpu_reference_run(cns, 10.0, threads)
+        cns = CPU_SAMPLE_STREAMS
+        v, kind, dt = cpu_reference_run(cns, CPU_SAMPLE_SECONDS, threads)
         cpu = {"value": v, "unit": "frames/s", "cores": threads, "kind": kind,
-               "sample": f"{cns} streams x 10 s of the same workload ({dt:.1f} s of wall time), block 512",
+               "sample": f"{cns} streams x {CPU_SAMPLE_SECONDS:g} s of the same workload ({dt:.1f} s of wall time), block 512",
                "x_realtime": v / SRATE}
 
     line = {

@@ -78,3 +78,13 @@ def automation(sliders, n_blocks: int, n_streams: int, which, first_stream: int 
             traj += 0.05 * (hi - lo) * np.sin(2 * np.pi * b / r.uniform(13.0, 90.0))
             p[:, i, j] = np.clip(traj, lo, hi).astype(np.float32)
     return p
+
+
+def default_params(plugin_key: str, n_streams: int, first_stream: int = 0) -> np.ndarray:
+    """Static per-stream parameter block of a plugin's bench workload: cascade8 -> the seeded cfg2
+    parameters; catalog leaves -> declared slider defaults for every stream."""
+    if plugin_key == "cascade8":
+        return cascade8_params(n_streams, first_stream)
+    import za_gpu
+    d = np.array([s.def_ for s in za_gpu.slider_layout(plugin_key)], np.float32)
+    return np.tile(d, (n_streams, 1))
