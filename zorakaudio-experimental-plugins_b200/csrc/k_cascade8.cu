@@ -300,7 +300,7 @@ cascade8_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constan
 {
     constexpr int T = 32 * W;
     extern __shared__ uint8_t smem_raw[];
-    C8Smem<R, W>* sm = reinterpret_cast<C8Smem<R, W>*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    C8Smem<R, W>* sm = reinterpret_cast<C8Smem<R, W>*>(smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u));
     const int stream = blockIdx.x;
     Ctx<R, W> cx;
     cx.sm = sm; cx.tid = threadIdx.x; cx.lane = threadIdx.x & 31; cx.warp = threadIdx.x >> 5; cx.par = 0;

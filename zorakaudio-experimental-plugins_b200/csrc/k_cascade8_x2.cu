@@ -1,0 +1,464 @@
+// k_cascade8_x2.cu -- linear IIR class, fp32 arithmetic, packed-FP32 (FFMA2) edition for sm_100a.
+//
+// Same job as k_cascade8.cu (plugin "cascade8": the generated per-sample loop of
+// dsp_jsfx_aot.py:5713-5905 for n_streams instances), restructured around what ncu showed for v1
+// (profiles/r01_cascade8_v1_ncu.md): DRAM traffic == algorithmic bytes, the kernel is bound by
+// instruction count.  Blackwell's packed `fma.rn.f32x2` (SASS FFMA2) retires two FMAs per issue
+// slot with the same latency as FFMA, so:
+//
+//   * every thread owns TWO adjacent 32-frame chunks (A = 2t, B = 2t+1) and keeps them as 32
+//     register PAIRS (xA[k], xB[k]); pass A (zero-state FIR) and pass B (the recurrence) run on
+//     both chunks in lockstep, one FFMA2 per formerly two FFMAs, coefficients as (c, c) pairs;
+//   * the warp-shuffle scan runs once per 64 frames (the thread first folds A into B);
+//   * one CTA = one stream; a tile (64 * T frames) arrives by ONE TMA tensor load into a single
+//     smem buffer, is computed in registers, written back to the SAME rows (each thread only
+//     touches its own two rows) and leaves by one TMA tensor store.  The next tile is pulled
+//     into L2 by a TMA prefetch while this one computes, so the exposed load is an L2 hit;
+//     other resident CTAs cover it.  smem per CTA = 16 KB (W = 2) + 7 KB tables, which lets 7-8
+//     CTAs share an SM where a 3-stage ring allowed fewer warps.
+//
+// Arithmetic notes (fp32 mode only has to null below -100 dBFS against the fp64 oracle):
+//   * feedback coefficients are delta-coded, a1 = -2 + d1, a2 = 1 - d2, as in v1;
+//   * both one-poles run as s += c (x - s) (exact DC gain in float);
+//   * the scan runs in the real normal form of each biquad (|N^n| <= 1), tables built in double.
+#include "za_device.cuh"
+#include "za_internal.h"
+
+namespace za {
+
+struct alignas(16) C8TablesX2 {
+    float HA[6][kL][4];     // biquads: (h1k, h1k, h2k, h2k), h_k = T A^(31-k) B (zero-state end state, scan coords)
+    float P2[6][34][4];     // (N^64)^j for j = 0..32 (row-major 2x2); [33] = N^32
+    float T2[6][8];         // T (4), T^-1 (4)
+    float H1[2][kL][2];     // one-poles: (h_k, h_k)
+    float P1[2][36];        // (alpha^64)^j, j = 0..32; [33] = alpha^32
+    float coef[40];         // per biquad k: b0 b1 b2 -d1 d2 at [5k..5k+4]; [30] = c7, [31] = c8, [32] = mix
+};
+
+size_t cascade8_x2_tables_bytes() { return sizeof(C8TablesX2); }
+
+// one thread per (stream, section); double arithmetic, stored as float
+__global__ void cascade8_x2_tables_kernel(const double* __restrict__ coef, C8TablesX2* __restrict__ tabs, int n_streams)
+{
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    const int s = g >> 3, sec = g & 7;
+    if (s >= n_streams) return;
+    const double* c = coef + (size_t)s * kC8Coefs;
+    C8TablesX2& t = tabs[s];
+    if (sec < 6) {
+        const double b0 = c[5 * sec], b1 = c[5 * sec + 1], b2 = c[5 * sec + 2], a1 = c[5 * sec + 3], a2 = c[5 * sec + 4];
+        // s' = A s + B x with A = [[-a1, 1], [-a2, 0]]; scan coordinates w = T s, T A T^-1 = N (scaled rotation)
+        const double sg = -0.5 * a1, w2 = a2 - sg * sg;
+        double t00 = 1, t01 = 0, t10 = 0, t11 = 1, i00 = 1, i01 = 0, i10 = 0, i11 = 1;
+        double n00 = -a1, n01 = 1, n10 = -a2, n11 = 0;
+        if (w2 > 1e-14 && a2 > 1e-14) {
+            const double om = sqrt(w2);
+            t00 = 0; t01 = -1.0 / a2; t10 = 1.0 / om; t11 = sg / (om * a2);
+            i00 = sg; i01 = om; i10 = -a2; i11 = 0;
+            n00 = sg; n01 = om; n10 = -om; n11 = sg;
+        }
+        const double bb1 = b1 - a1 * b0, bb2 = b2 - a2 * b0;
+        double v1 = t00 * bb1 + t01 * bb2, v2 = t10 * bb1 + t11 * bb2;
+        for (int k = kL - 1; k >= 0; --k) {
+            t.HA[sec][k][0] = (float)v1; t.HA[sec][k][1] = (float)v1;
+            t.HA[sec][k][2] = (float)v2; t.HA[sec][k][3] = (float)v2;
+            const double x1 = n00 * v1 + n01 * v2, x2 = n10 * v1 + n11 * v2;
+            v1 = x1; v2 = x2;
+        }
+        double m00 = 1, m01 = 0, m10 = 0, m11 = 1;       // N^32, then N^64
+        for (int k = 0; k < kL; ++k) {
+            const double x00 = n00 * m00 + n01 * m10, x01 = n00 * m01 + n01 * m11;
+            const double x10 = n10 * m00 + n11 * m10, x11 = n10 * m01 + n11 * m11;
+            m00 = x00; m01 = x01; m10 = x10; m11 = x11;
+        }
+        t.P2[sec][33][0] = (float)m00; t.P2[sec][33][1] = (float)m01; t.P2[sec][33][2] = (float)m10; t.P2[sec][33][3] = (float)m11;
+        {
+            const double x00 = m00 * m00 + m01 * m10, x01 = m00 * m01 + m01 * m11;
+            const double x10 = m10 * m00 + m11 * m10, x11 = m10 * m01 + m11 * m11;
+            m00 = x00; m01 = x01; m10 = x10; m11 = x11;
+        }
+        double p00 = 1, p01 = 0, p10 = 0, p11 = 1;
+        for (int j = 0; j <= 32; ++j) {
+            t.P2[sec][j][0] = (float)p00; t.P2[sec][j][1] = (float)p01; t.P2[sec][j][2] = (float)p10; t.P2[sec][j][3] = (float)p11;
+            const double x00 = m00 * p00 + m01 * p10, x01 = m00 * p01 + m01 * p11;
+            const double x10 = m10 * p00 + m11 * p10, x11 = m10 * p01 + m11 * p11;
+            p00 = x00; p01 = x01; p10 = x10; p11 = x11;
+        }
+        t.T2[sec][0] = (float)t00; t.T2[sec][1] = (float)t01; t.T2[sec][2] = (float)t10; t.T2[sec][3] = (float)t11;
+        t.T2[sec][4] = (float)i00; t.T2[sec][5] = (float)i01; t.T2[sec][6] = (float)i10; t.T2[sec][7] = (float)i11;
+        t.coef[5 * sec + 0] = (float)b0; t.coef[5 * sec + 1] = (float)b1; t.coef[5 * sec + 2] = (float)b2;
+        t.coef[5 * sec + 3] = (float)(-(a1 + 2.0));      // -d1
+        t.coef[5 * sec + 4] = (float)(1.0 - a2);         //  d2
+    } else {
+        const int o = sec - 6;
+        // S7: lp = (1-a7) x + a7 lp ; S8: lp += c8 (x - lp); both are s' = (1-c) s + c x
+        const double cc = o == 0 ? c[31] : c[32];
+        const double alpha = o == 0 ? c[30] : 1.0 - c[32];
+        double v = cc;
+        for (int k = kL - 1; k >= 0; --k) { t.H1[o][k][0] = (float)v; t.H1[o][k][1] = (float)v; v *= alpha; }
+        double m = 1;
+        for (int k = 0; k < kL; ++k) m *= alpha;
+        t.P1[o][33] = (float)m;
+        m *= m;
+        double p = 1;
+        for (int j = 0; j <= 32; ++j) { t.P1[o][j] = (float)p; p *= m; }
+        t.P1[o][34] = 0; t.P1[o][35] = 0;
+        t.coef[30 + o] = (float)cc;
+        if (o == 0) { t.coef[32] = (float)c[33]; for (int i = 33; i < 40; ++i) t.coef[i] = 0; }
+    }
+}
+
+bool cascade8_x2_build_tables(const double* d_coef, void* d_tables, int n_streams, cudaStream_t s)
+{
+    const int threads = 128, blocks = (n_streams * 8 + threads - 1) / threads;
+    cascade8_x2_tables_kernel<<<blocks, threads, 0, s>>>(d_coef, (C8TablesX2*)d_tables, n_streams);
+    return cuda_ok(cudaGetLastError(), "cascade8_x2_tables_kernel");
+}
+
+// ---------------------------------------------------------------------------------------------
+// device side
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ float2 f2(float a, float b) { return make_float2(a, b); }
+__device__ __forceinline__ float2 dup(float a) { return make_float2(a, a); }
+__device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c) { return __ffma2_rn(a, b, c); }
+__device__ __forceinline__ float2 mul2(float2 a, float2 b) { return __fmul2_rn(a, b); }
+__device__ __forceinline__ float2 add2(float2 a, float2 b) { return __fadd2_rn(a, b); }
+__device__ __forceinline__ float2 neg2(float2 a) { return make_float2(-a.x, -a.y); }
+
+template <int W, int NBUF> struct X2Smem {
+    alignas(1024) float tile[NBUF][64 * W * kL]; // 2T rows x 32 frames per buffer, SWIZZLE_128B
+    alignas(16) C8TablesX2 tab;
+    alignas(16) float carry[2][kC8State];        // tile-parity double buffer (W > 1 only)
+    alignas(16) float wtot[8][W][2];             // per-section warp totals (W > 1 only)
+    alignas(8) uint64_t full[NBUF];
+};
+
+template <int W, int NBUF> struct X2Ctx {
+    X2Smem<W, NBUF>* sm;
+    int tid, lane, warp;
+    int t_last, half_last;  // owner thread of the tile's last valid chunk and which of its two chunks that is
+    int par;
+    float c[kC8State];      // W == 1: carry lives in registers
+};
+
+// ---- one biquad section over both chunks of the thread ------------------------------------------
+// x[k] = (frame k of chunk A, frame k of chunk B).  B1ZERO: band-pass sections (b1 == 0 exactly).
+template <int W, int NBUF, bool B1ZERO, bool MIX>
+__device__ __forceinline__ void biquad_x2(X2Ctx<W, NBUF>& cx, float2 (&x)[kL], const int sec)
+{
+    const C8TablesX2& tb = cx.sm->tab;
+    // pass A: zero-state end state of both chunks; 4 independent FFMA2 chains
+    float2 z1 = f2(0, 0), z2 = f2(0, 0), y1 = f2(0, 0), y2 = f2(0, 0);
+#pragma unroll
+    for (int k = 0; k < kL; k += 2) {
+        const float4 h = *reinterpret_cast<const float4*>(&tb.HA[sec][k][0]);
+        const float4 g = *reinterpret_cast<const float4*>(&tb.HA[sec][k + 1][0]);
+        z1 = fma2(f2(h.x, h.y), x[k], z1); z2 = fma2(f2(h.z, h.w), x[k], z2);
+        y1 = fma2(f2(g.x, g.y), x[k + 1], y1); y2 = fma2(f2(g.z, g.w), x[k + 1], y2);
+    }
+    z1 = add2(z1, y1); z2 = add2(z2, y2);             // z1 = (z1A, z1B), z2 = (z2A, z2B)
+    // fold A into B: c = N^32 zA + zB  (zero-state end state of the thread's 64 frames)
+    const float4 n32 = *reinterpret_cast<const float4*>(&tb.P2[sec][33][0]);
+    float c1 = fmaf(n32.x, z1.x, fmaf(n32.y, z2.x, z1.y));
+    float c2 = fmaf(n32.z, z1.x, fmaf(n32.w, z2.x, z2.y));
+    // inclusive Kogge-Stone scan of w -> M w + c over the warp's 32 threads, M = N^64
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const float u1 = shfl_up(c1, d), u2 = shfl_up(c2, d);
+        const float4 m = *reinterpret_cast<const float4*>(&tb.P2[sec][d][0]);
+        if (cx.lane >= d) {
+            c1 = fmaf(m.x, u1, fmaf(m.y, u2, c1));
+            c2 = fmaf(m.z, u1, fmaf(m.w, u2, c2));
+        }
+    }
+    // state entering my warp: exact sequential state (z1, z2) -> scan coordinates
+    const float4 tf = *reinterpret_cast<const float4*>(&tb.T2[sec][0]);
+    const float4 ti = *reinterpret_cast<const float4*>(&tb.T2[sec][4]);
+    float s1, s2;
+    if (W == 1) {
+        const float a = cx.c[2 * sec], b = cx.c[2 * sec + 1];
+        s1 = fmaf(tf.x, a, tf.y * b); s2 = fmaf(tf.z, a, tf.w * b);
+    } else {
+        if (cx.lane == 31) { cx.sm->wtot[sec][cx.warp][0] = c1; cx.sm->wtot[sec][cx.warp][1] = c2; }
+        __syncthreads();
+        const float a = cx.sm->carry[cx.par][2 * sec], b = cx.sm->carry[cx.par][2 * sec + 1];
+        s1 = fmaf(tf.x, a, tf.y * b); s2 = fmaf(tf.z, a, tf.w * b);
+        const float4 m = *reinterpret_cast<const float4*>(&tb.P2[sec][32][0]);
+        for (int w = 0; w < cx.warp; ++w) {
+            const float t1 = fmaf(m.x, s1, fmaf(m.y, s2, cx.sm->wtot[sec][w][0]));
+            const float t2 = fmaf(m.z, s1, fmaf(m.w, s2, cx.sm->wtot[sec][w][1]));
+            s1 = t1; s2 = t2;
+        }
+    }
+    // start of chunk A: exclusive prefix + M^lane * warp-incoming state; start of chunk B: N^32 wA + zA
+    float e1 = shfl_up(c1, 1), e2 = shfl_up(c2, 1);
+    if (cx.lane == 0) { e1 = 0; e2 = 0; }
+    const float4 pl = *reinterpret_cast<const float4*>(&tb.P2[sec][cx.lane][0]);
+    const float wa1 = fmaf(pl.x, s1, fmaf(pl.y, s2, e1));
+    const float wa2 = fmaf(pl.z, s1, fmaf(pl.w, s2, e2));
+    const float wb1 = fmaf(n32.x, wa1, fmaf(n32.y, wa2, z1.x));
+    const float wb2 = fmaf(n32.z, wa1, fmaf(n32.w, wa2, z2.x));
+    // back to the recurrence's own coordinates (z1, z2) = T^-1 w, as pairs
+    float2 st1 = fma2(dup(ti.x), f2(wa1, wb1), mul2(dup(ti.y), f2(wa2, wb2)));
+    float2 st2 = fma2(dup(ti.z), f2(wa1, wb1), mul2(dup(ti.w), f2(wa2, wb2)));
+    // pass B: the TDF-II recurrence (Spectral Stabilizer.jsfx:98-111) on both chunks in lockstep
+    const float2 b0 = dup(tb.coef[5 * sec]), b1 = dup(tb.coef[5 * sec + 1]), b2 = dup(tb.coef[5 * sec + 2]);
+    const float2 nd1 = dup(tb.coef[5 * sec + 3]), d2 = dup(tb.coef[5 * sec + 4]);
+    const float2 two = dup(2.0f), mix = dup(tb.coef[32]);
+#pragma unroll
+    for (int k = 0; k < kL; ++k) {
+        const float2 xx = x[k];
+        const float2 y = fma2(b0, xx, st1);
+        // z1' = b1 x - a1 y + z2 = (b1 x + z2) + 2 y - d1 y ;  z2' = b2 x - a2 y = (b2 x - y) + d2 y
+        const float2 t = B1ZERO ? st2 : fma2(b1, xx, st2);
+        st1 = fma2(two, y, fma2(nd1, y, t));
+        st2 = fma2(d2, y, fma2(b2, xx, neg2(y)));
+        x[k] = MIX ? fma2(mix, y, xx) : y;
+    }
+    // publish the exact sequential state after the tile's last valid chunk
+    const float sn1 = cx.half_last ? st1.y : st1.x, sn2 = cx.half_last ? st2.y : st2.x;
+    if (W == 1) {
+        cx.c[2 * sec] = shfl_idx(sn1, cx.t_last); cx.c[2 * sec + 1] = shfl_idx(sn2, cx.t_last);
+    } else if (cx.tid == cx.t_last) {
+        cx.sm->carry[cx.par ^ 1][2 * sec] = sn1; cx.sm->carry[cx.par ^ 1][2 * sec + 1] = sn2;
+    }
+}
+
+// ---- one one-pole section: s += c (x - s)  (ERB Tilt.jsfx:397 and EasyExpander.jsfx:186 forms) ------
+template <int W, int NBUF, int O>
+__device__ __forceinline__ void onepole_x2(X2Ctx<W, NBUF>& cx, float2 (&x)[kL])
+{
+    const C8TablesX2& tb = cx.sm->tab;
+    constexpr int sec = 6 + O, ci = 12 + O;
+    float2 z = f2(0, 0), za = f2(0, 0), zb = f2(0, 0), zc = f2(0, 0);
+#pragma unroll
+    for (int k = 0; k < kL; k += 4) {
+        const float4 h = *reinterpret_cast<const float4*>(&tb.H1[O][k][0]);
+        const float4 g = *reinterpret_cast<const float4*>(&tb.H1[O][k + 2][0]);
+        z = fma2(f2(h.x, h.y), x[k], z); za = fma2(f2(h.z, h.w), x[k + 1], za);
+        zb = fma2(f2(g.x, g.y), x[k + 2], zb); zc = fma2(f2(g.z, g.w), x[k + 3], zc);
+    }
+    z = add2(add2(z, za), add2(zb, zc));              // (zA, zB)
+    const float a32 = tb.P1[O][33];
+    float c = fmaf(a32, z.x, z.y);
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const float u = shfl_up(c, d);
+        const float m = tb.P1[O][d];
+        if (cx.lane >= d) c = fmaf(m, u, c);
+    }
+    float s;
+    if (W == 1) {
+        s = cx.c[ci];
+    } else {
+        if (cx.lane == 31) cx.sm->wtot[sec][cx.warp][0] = c;
+        __syncthreads();
+        s = cx.sm->carry[cx.par][ci];
+        const float m = tb.P1[O][32];
+        for (int w = 0; w < cx.warp; ++w) s = fmaf(m, s, cx.sm->wtot[sec][w][0]);
+    }
+    float e = shfl_up(c, 1);
+    if (cx.lane == 0) e = 0;
+    const float sa = fmaf(tb.P1[O][cx.lane], s, e);
+    const float sb = fmaf(a32, sa, z.x);
+    float2 st = f2(sa, sb);
+    const float2 cc = dup(tb.coef[30 + O]);
+#pragma unroll
+    for (int k = 0; k < kL; ++k) {
+        st = fma2(cc, add2(x[k], neg2(st)), st);
+        x[k] = st;
+    }
+    const float sn = cx.half_last ? st.y : st.x;
+    if (W == 1) cx.c[ci] = shfl_idx(sn, cx.t_last);
+    else if (cx.tid == cx.t_last) cx.sm->carry[cx.par ^ 1][ci] = sn;
+}
+
+// ---- the whole cascade over one tile (cascade8.jsfx @sample) ----------------------------------
+template <int W, int NBUF>
+__device__ __forceinline__ void cascade8_x2_tile(X2Ctx<W, NBUF>& cx, float2 (&x)[kL])
+{
+    biquad_x2<W, NBUF, false, false>(cx, x, 0);   // S1 HP
+    biquad_x2<W, NBUF, false, false>(cx, x, 1);   // S2 LP
+    biquad_x2<W, NBUF, true, true>(cx, x, 2);     // S3 BP (peak), u3 = y2 + mix*y3
+    biquad_x2<W, NBUF, true, true>(cx, x, 3);     // S4 BP (skirt), u4 = u3 + mix*y4
+    biquad_x2<W, NBUF, false, false>(cx, x, 4);   // S5 LP
+    biquad_x2<W, NBUF, false, false>(cx, x, 5);   // S6 HP
+    onepole_x2<W, NBUF, 0>(cx, x);                // S7
+    onepole_x2<W, NBUF, 1>(cx, x);                // S8
+}
+
+__device__ __forceinline__ void tma_prefetch_3d(const CUtensorMap* map, int c0, int c1, int c2)
+{
+    asm volatile("cp.async.bulk.prefetch.tensor.3d.L2.global.tile [%0, {%1, %2, %3}];"
+                 ::"l"(map), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
+
+struct X2Args {
+    int64_t n_chunks;          // 32-frame chunks per stream in this launch
+    const void* tables; double* state;
+};
+
+// One CTA per stream, persistent over time.  n_frames % 32 == 0, rows 16-byte aligned (TMA).
+template <int W, int NBUF>
+__global__ void __launch_bounds__(32 * W)
+cascade8_x2_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constant__ CUtensorMap out_map, const X2Args a)
+{
+    constexpr int T = 32 * W;
+    constexpr int kTileBytes = 64 * W * kL * 4;
+    extern __shared__ uint8_t smem_raw[];
+    using Smem = X2Smem<W, NBUF>;
+    // pointer arithmetic on the __shared__ array itself keeps the address space known to ptxas (LDS/STS, not generic LD/ST)
+    Smem* sm = reinterpret_cast<Smem*>(smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u));
+    const int stream = blockIdx.x;
+    X2Ctx<W, NBUF> cx;
+    cx.sm = sm;
+    cx.tid = threadIdx.x; cx.lane = threadIdx.x & 31; cx.warp = threadIdx.x >> 5; cx.par = 0;
+
+    const int64_t n_chunks = a.n_chunks;
+    const int n_tiles = (int)((n_chunks + 2 * T - 1) / (2 * T));
+
+    if (cx.tid == 0) {
+        prefetch_tensormap(&in_map); prefetch_tensormap(&out_map);
+        for (int s = 0; s < NBUF; ++s) mbar_init(&sm->full[s], 1);
+        fence_barrier_init();
+    }
+    {   // per-stream tables -> shared memory (once per launch)
+        const uint4* src = reinterpret_cast<const uint4*>(reinterpret_cast<const C8TablesX2*>(a.tables) + stream);
+        uint4* dst = reinterpret_cast<uint4*>(&sm->tab);
+        for (int i = cx.tid; i < (int)(sizeof(C8TablesX2) / 16); i += T) dst[i] = src[i];
+    }
+    const double* gstate = a.state + (size_t)stream * kC8State;
+    if (W == 1) {
+#pragma unroll
+        for (int i = 0; i < kC8State; ++i) cx.c[i] = (float)gstate[i];
+    } else if (cx.tid < kC8State) {
+        sm->carry[0][cx.tid] = (float)gstate[cx.tid];
+    }
+    __syncthreads();
+    if (cx.tid == 0) {
+        for (int s = 0; s < NBUF && s < n_tiles; ++s) {
+            mbar_expect_tx(&sm->full[s], kTileBytes);
+            tma_load_3d(sm->tile[s], &in_map, &sm->full[s], 0, s * 2 * T, stream);
+        }
+        if (NBUF == 1 && n_tiles > 1) tma_prefetch_3d(&in_map, 0, 2 * T, stream);
+    }
+
+    float2 x[kL];
+    for (int i = 0; i < n_tiles; ++i) {
+        const int b = NBUF == 1 ? 0 : (i & 1);
+        float* tile = sm->tile[b];
+        const int64_t c0 = (int64_t)i * 2 * T;
+        const int nvc = (int)((n_chunks - c0) < 2 * T ? (n_chunks - c0) : 2 * T);    // valid chunks in this tile
+        cx.t_last = (nvc - 1) >> 1;
+        cx.half_last = (nvc - 1) & 1;
+        mbar_wait(&sm->full[b], (uint32_t)((NBUF == 1 ? i : (i >> 1)) & 1));
+        // rows 2t (chunk A) and 2t+1 (chunk B) -> register pairs
+#pragma unroll
+        for (int j = 0; j < kL / 4; ++j) {
+            const float4 va = *reinterpret_cast<const float4*>(tile + swz_piece(2 * cx.tid, j));
+            const float4 vb = *reinterpret_cast<const float4*>(tile + swz_piece(2 * cx.tid + 1, j));
+            x[4 * j + 0] = f2(va.x, vb.x); x[4 * j + 1] = f2(va.y, vb.y);
+            x[4 * j + 2] = f2(va.z, vb.z); x[4 * j + 3] = f2(va.w, vb.w);
+        }
+
+        cascade8_x2_tile<W, NBUF>(cx, x);
+
+#pragma unroll
+        for (int j = 0; j < kL / 4; ++j) {
+            *reinterpret_cast<float4*>(tile + swz_piece(2 * cx.tid, j)) =
+                make_float4(x[4 * j].x, x[4 * j + 1].x, x[4 * j + 2].x, x[4 * j + 3].x);
+            *reinterpret_cast<float4*>(tile + swz_piece(2 * cx.tid + 1, j)) =
+                make_float4(x[4 * j].y, x[4 * j + 1].y, x[4 * j + 2].y, x[4 * j + 3].y);
+        }
+        fence_proxy_async();
+        if (W == 1) __syncwarp(); else __syncthreads();
+        if (cx.tid == 0) {
+            tma_store_3d(&out_map, tile, 0, (int)c0, stream);
+            tma_commit();
+            if (NBUF == 1) {
+                if (i + 1 < n_tiles) {
+                    tma_wait_read<0>();                       // the store has read the buffer: refill it
+                    mbar_expect_tx(&sm->full[0], kTileBytes);
+                    tma_load_3d(sm->tile[0], &in_map, &sm->full[0], 0, (int)c0 + 2 * T, stream);
+                    if (i + 2 < n_tiles) tma_prefetch_3d(&in_map, 0, (int)c0 + 4 * T, stream);
+                }
+            } else {
+                // buffer b is free once this store has read it; tile i+2 goes there, tile i+1 is already in flight
+                if (i + 2 < n_tiles) {
+                    tma_wait_read<0>();
+                    mbar_expect_tx(&sm->full[b], kTileBytes);
+                    tma_load_3d(sm->tile[b], &in_map, &sm->full[b], 0, (int)c0 + 4 * T, stream);
+                }
+            }
+        }
+        cx.par ^= 1;
+    }
+
+    // state after the last frame -> HBM (double), carried into the next call
+    double* gs = a.state + (size_t)stream * kC8State;
+    if (W == 1) {
+        if (cx.tid == 0) {
+#pragma unroll
+            for (int i = 0; i < 14; ++i) gs[i] = (double)cx.c[i];
+        }
+    } else {
+        __syncthreads();
+        if (cx.tid < 14) gs[cx.tid] = (double)sm->carry[cx.par][cx.tid];
+    }
+    if (cx.tid == 0) tma_wait_all<0>();
+}
+
+// ---------------------------------------------------------------------------------------------
+// host launchers
+// ---------------------------------------------------------------------------------------------
+template <int W, int NBUF>
+static bool launch_x2(const C8Launch& L)
+{
+    X2Args a{L.n_frames / kL, L.tables_x2, L.state};
+    CUtensorMap in_map, out_map;
+    if (!make_chunk_tensor_map(&in_map, L.in, a.n_chunks, L.n_streams, L.row_stride, 64 * W)) return false;
+    if (!make_chunk_tensor_map(&out_map, L.out, a.n_chunks, L.n_streams, L.row_stride, 64 * W)) return false;
+    auto kern = cascade8_x2_kernel<W, NBUF>;
+    const size_t smem = sizeof(X2Smem<W, NBUF>) + 1024;
+    static bool attr_done = false;    // per template instantiation
+    if (!attr_done) {
+        if (!cuda_ok(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "smem attr")) return false;
+        attr_done = true;
+    }
+    kern<<<L.n_streams, 32 * W, smem, L.stream>>>(in_map, out_map, a);
+    return cuda_ok(cudaGetLastError(), "cascade8_x2_kernel launch");
+}
+
+bool cascade8_x2_launch(const C8Launch& L)
+{
+    if (L.n_frames <= 0 || L.n_streams <= 0) return true;
+    if ((L.n_frames % kL) != 0) { set_error("cascade8_x2: needs n_frames % 32 == 0"); return false; }
+    const int key = L.warps * 10 + L.nbuf;
+    switch (key) {
+    case 11: return launch_x2<1, 1>(L);
+    case 12: return launch_x2<1, 2>(L);
+    case 21: return launch_x2<2, 1>(L);
+    case 22: return launch_x2<2, 2>(L);
+    case 41: return launch_x2<4, 1>(L);
+    case 42: return launch_x2<4, 2>(L);
+    default: set_error("cascade8_x2: warps_per_stream must be 1, 2 or 4 and tile_buffers 1 or 2"); return false;
+    }
+}
+
+// Warps per stream and tile buffers: all streams resident in one wave when they fit (one CTA = one
+// stream runs the whole time axis), as many warps per SM as the register file allows (128 regs/thread
+// -> 16 warps), double-buffered tiles only if shared memory still fits that many CTAs.
+void cascade8_x2_pick(int n_streams, int device, int* warps, int* nbuf)
+{
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    const int per_sm = (n_streams + sms - 1) / sms;      // CTAs each SM must host for one wave
+    int w = 4;
+    while (w > 1 && per_sm * w > 16) w >>= 1;
+    const int ctas = per_sm < 16 / w ? per_sm : 16 / w;  // resident CTAs per SM we plan for
+    const size_t smem2 = (w == 1 ? sizeof(X2Smem<1, 2>) : w == 2 ? sizeof(X2Smem<2, 2>) : sizeof(X2Smem<4, 2>)) + 2048;
+    *warps = w;
+    *nbuf = (smem2 * (size_t)ctas <= 227u * 1024u) ? 2 : 1;
+}
+
+}  // namespace za

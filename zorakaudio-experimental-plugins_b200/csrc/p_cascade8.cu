@@ -61,14 +61,18 @@ class Cascade8 : public PluginImpl {
     std::vector<double> h_coef;
     double* d_coef = nullptr;
     void* d_tables = nullptr;
+    void* d_tables_x2 = nullptr;     // fp32 mode: tables of the packed-FP32 kernel
     double* d_state = nullptr;
 
 public:
-    ~Cascade8() override { cudaFree(d_coef); cudaFree(d_tables); cudaFree(d_state); }
+    ~Cascade8() override { cudaFree(d_coef); cudaFree(d_tables); cudaFree(d_tables_x2); cudaFree(d_state); }
 
     bool create(Instance& I) override
     {
         h_coef.assign((size_t)I.n_streams * kC8Coefs, 0.0);
+        if (!I.precision &&
+            !cuda_ok(cudaMalloc(&d_tables_x2, (size_t)I.n_streams * cascade8_x2_tables_bytes()), "cascade8 x2 tables"))
+            return false;
         return cuda_ok(cudaMalloc(&d_coef, h_coef.size() * sizeof(double)), "cascade8 coef") &&
                cuda_ok(cudaMalloc(&d_tables, (size_t)I.n_streams * cascade8_tables_bytes(I.precision)), "cascade8 tables") &&
                cuda_ok(cudaMalloc(&d_state, (size_t)I.n_streams * kC8State * sizeof(double)), "cascade8 state");
@@ -89,6 +93,12 @@ public:
                                      (size_t)ns * kC8Coefs * sizeof(double), cudaMemcpyHostToDevice, I.stream), "cascade8 coef upload"))
             return false;
         ++I.launches;
+        if (d_tables_x2) {
+            ++I.launches;
+            if (!cascade8_x2_build_tables(d_coef + (size_t)s0 * kC8Coefs,
+                                          (char*)d_tables_x2 + (size_t)s0 * cascade8_x2_tables_bytes(), ns, I.stream))
+                return false;
+        }
         return cascade8_build_tables(d_coef + (size_t)s0 * kC8Coefs,
                                      (char*)d_tables + (size_t)s0 * cascade8_tables_bytes(I.precision), ns, I.precision, I.stream);
     }
@@ -106,14 +116,22 @@ public:
         const int64_t n_main = (aligned && !I.opt_force_generic) ? n - (n % kL_host()) : 0;
         if (n_main > 0) {
             L.in = in; L.out = out; L.tap = tap; L.n_frames = n_main; L.use_tma = true;
+            const bool packed = !I.precision && !I.opt_scalar_f32;
+            if (packed) {
+                L.tables_x2 = (char*)d_tables_x2 + (size_t)s0 * cascade8_x2_tables_bytes();
+                cascade8_x2_pick(ns, I.device, &L.warps, &L.nbuf);
+                if (I.opt_warps) L.warps = I.opt_warps;
+                if (I.opt_nbuf) L.nbuf = I.opt_nbuf;
+            }
             const bool timed = I.time_begin();
-            if (!cascade8_launch(L)) return false;
+            if (!(packed ? cascade8_x2_launch(L) : cascade8_launch(L))) return false;
             if (timed) I.time_end();
             ++I.launches;
         }
         if (n > n_main) {
             L.in = in + n_main; L.out = out + n_main; L.tap = tap ? tap + n_main : nullptr;
             L.n_frames = n - n_main; L.use_tma = false;
+            L.warps = I.opt_warps ? I.opt_warps : cascade8_pick_warps(ns, I.precision, I.device);
             const bool timed = (n_main == 0) && I.time_begin();
             if (!cascade8_launch(L)) return false;
             if (timed) I.time_end();

@@ -427,6 +427,8 @@ ZA_API int za_gpu_set_option(za_gpu_handle h, const char* name, int value)
     if (!std::strcmp(name, "force_generic_io")) I.opt_force_generic = value;
     else if (!std::strcmp(name, "warps_per_stream")) I.opt_warps = value;
     else if (!std::strcmp(name, "host_chunk_streams")) I.opt_host_chunk = value;
+    else if (!std::strcmp(name, "tile_buffers")) I.opt_nbuf = value;
+    else if (!std::strcmp(name, "scalar_f32")) I.opt_scalar_f32 = value;
     else { set_error(std::string("unknown option ") + name); return ZA_ERR_ARG; }
     return ZA_OK;
 }

@@ -60,7 +60,7 @@ struct Instance {
     std::unique_ptr<PluginImpl> impl;
     int64_t launches = 0;
     // options
-    int opt_force_generic = 0, opt_warps = 0, opt_host_chunk = 0;
+    int opt_force_generic = 0, opt_warps = 0, opt_host_chunk = 0, opt_nbuf = 0, opt_scalar_f32 = 0;
     // timing of the dominant kernel
     std::vector<cudaEvent_t> ev;             // pairs
     int ev_used = 0;

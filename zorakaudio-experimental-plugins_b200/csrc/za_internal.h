@@ -32,6 +32,8 @@ struct C8Launch {
     int precision;           // 0 = f32, 1 = f64
     int warps;               // warps per stream (1, 2 or 4)
     bool use_tma;            // needs n_frames % 32 == 0, 16-byte aligned rows
+    const void* tables_x2 = nullptr;   // C8TablesX2[n_streams] (fp32 packed kernel, k_cascade8_x2.cu)
+    int nbuf = 1;            // tile buffers per CTA of the packed kernel (1 or 2)
     cudaStream_t stream;
 };
 
@@ -39,5 +41,11 @@ size_t cascade8_tables_bytes(int precision);
 bool cascade8_build_tables(const double* d_coef, void* d_tables, int n_streams, int precision, cudaStream_t s);
 bool cascade8_launch(const C8Launch& a);
 int cascade8_pick_warps(int n_streams, int precision, int device);
+
+// fp32 packed-FP32 (FFMA2) kernel, two chunks per thread (k_cascade8_x2.cu); TMA-aligned spans only
+size_t cascade8_x2_tables_bytes();
+bool cascade8_x2_build_tables(const double* d_coef, void* d_tables, int n_streams, cudaStream_t s);
+bool cascade8_x2_launch(const C8Launch& a);
+void cascade8_x2_pick(int n_streams, int device, int* warps, int* nbuf);
 
 }  // namespace za
