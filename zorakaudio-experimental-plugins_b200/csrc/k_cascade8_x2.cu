@@ -8,14 +8,21 @@
 //
 //   * every thread owns TWO adjacent 32-frame chunks (A = 2t, B = 2t+1) and keeps them as 32
 //     register PAIRS (xA[k], xB[k]); pass A (zero-state FIR) and pass B (the recurrence) run on
-//     both chunks in lockstep, one FFMA2 per formerly two FFMAs, coefficients as (c, c) pairs;
+//     both chunks in lockstep, one FFMA2 per formerly two FFMAs.  The pairs are carried as 64-bit
+//     values (inline-PTX fma.rn.f32x2 on .b64 registers) so ptxas keeps them in aligned register
+//     pairs across the run-time stage loops; CTA-uniform coefficients use FFMA2's scalar-broadcast
+//     operand form (`R.F32`), negated addends fold into its operand modifier;
 //   * the warp-shuffle scan runs once per 64 frames (the thread first folds A into B);
-//   * one CTA = one stream; a tile (64 * T frames) arrives by ONE TMA tensor load into a single
-//     smem buffer, is computed in registers, written back to the SAME rows (each thread only
-//     touches its own two rows) and leaves by one TMA tensor store.  The next tile is pulled
-//     into L2 by a TMA prefetch while this one computes, so the exposed load is an L2 hit;
-//     other resident CTAs cover it.  smem per CTA = 16 KB (W = 2) + 7 KB tables, which lets 7-8
-//     CTAs share an SM where a 3-stage ring allowed fewer warps.
+//   * pass A of stage s+1 is fused into the pass-B loop of stage s (independent FFMA2s that fill
+//     the recurrence's dependent-chain bubbles), and the six biquads run as runtime loops over
+//     two loop bodies (plain / band-pass+mix) so the hot code stays inside the instruction cache
+//     (v2a, fully unrolled, lost 12 % of its issue slots to `no_instruction` stalls);
+//   * one CTA = one stream; each WARP moves its own 64-row half of the tile: ONE TMA tensor load
+//     into the warp's smem rows, compute in registers, results written back to the SAME rows
+//     (a thread only touches its own two rows), one TMA tensor store.  The next tile is pulled
+//     into L2 by a TMA prefetch while this one computes, so the exposed load is an L2 hit that
+//     the other resident warps cover.  smem per CTA = 16 KB (W = 2) + 8 KB tables, so 8 CTAs
+//     (16 warps at 128 registers) share an SM.
 //
 // Arithmetic notes (fp32 mode only has to null below -100 dBFS against the fp64 oracle):
 //   * feedback coefficients are delta-coded, a1 = -2 + d1, a2 = 1 - d2, as in v1;
@@ -27,10 +34,11 @@
 namespace za {
 
 struct alignas(16) C8TablesX2 {
-    float HA[6][kL][4];     // biquads: (h1k, h1k, h2k, h2k), h_k = T A^(31-k) B (zero-state end state, scan coords)
+    float HA[7][kL][2];     // stages 0-5, biquads: (h1k, h2k), h_k = T A^(31-k) B (zero-state end state, scan
+                            // coords); stage 6 = one-pole S7 in the same row format: (h_k, 0)
+    float HB[kL];           // one-pole S8: h_k
     float P2[6][34][4];     // (N^64)^j for j = 0..32 (row-major 2x2); [33] = N^32
     float T2[6][8];         // T (4), T^-1 (4)
-    float H1[2][kL][2];     // one-poles: (h_k, h_k)
     float P1[2][36];        // (alpha^64)^j, j = 0..32; [33] = alpha^32
     float coef[40];         // per biquad k: b0 b1 b2 -d1 d2 at [5k..5k+4]; [30] = c7, [31] = c8, [32] = mix
 };
@@ -60,8 +68,7 @@ __global__ void cascade8_x2_tables_kernel(const double* __restrict__ coef, C8Tab
         const double bb1 = b1 - a1 * b0, bb2 = b2 - a2 * b0;
         double v1 = t00 * bb1 + t01 * bb2, v2 = t10 * bb1 + t11 * bb2;
         for (int k = kL - 1; k >= 0; --k) {
-            t.HA[sec][k][0] = (float)v1; t.HA[sec][k][1] = (float)v1;
-            t.HA[sec][k][2] = (float)v2; t.HA[sec][k][3] = (float)v2;
+            t.HA[sec][k][0] = (float)v1; t.HA[sec][k][1] = (float)v2;
             const double x1 = n00 * v1 + n01 * v2, x2 = n10 * v1 + n11 * v2;
             v1 = x1; v2 = x2;
         }
@@ -95,7 +102,11 @@ __global__ void cascade8_x2_tables_kernel(const double* __restrict__ coef, C8Tab
         const double cc = o == 0 ? c[31] : c[32];
         const double alpha = o == 0 ? c[30] : 1.0 - c[32];
         double v = cc;
-        for (int k = kL - 1; k >= 0; --k) { t.H1[o][k][0] = (float)v; t.H1[o][k][1] = (float)v; v *= alpha; }
+        for (int k = kL - 1; k >= 0; --k) {
+            if (o == 0) { t.HA[6][k][0] = (float)v; t.HA[6][k][1] = 0; }
+            else        { t.HB[k] = (float)v; }
+            v *= alpha;
+        }
         double m = 1;
         for (int k = 0; k < kL; ++k) m *= alpha;
         t.P1[o][33] = (float)m;
@@ -115,22 +126,42 @@ bool cascade8_x2_build_tables(const double* d_coef, void* d_tables, int n_stream
     return cuda_ok(cudaGetLastError(), "cascade8_x2_tables_kernel");
 }
 
+
 // ---------------------------------------------------------------------------------------------
 // device side
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ float2 f2(float a, float b) { return make_float2(a, b); }
-__device__ __forceinline__ float2 dup(float a) { return make_float2(a, a); }
-__device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c) { return __ffma2_rn(a, b, c); }
-__device__ __forceinline__ float2 mul2(float2 a, float2 b) { return __fmul2_rn(a, b); }
-__device__ __forceinline__ float2 add2(float2 a, float2 b) { return __fadd2_rn(a, b); }
-__device__ __forceinline__ float2 neg2(float2 a) { return make_float2(-a.x, -a.y); }
+// A pair of floats in one 64-bit register (lo = chunk A, hi = chunk B).
+typedef unsigned long long p2;
+__device__ __forceinline__ p2 pk(float lo, float hi) { p2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ float lo(p2 a) { float l, h; asm("mov.b64 {%0, %1}, %2;" : "=f"(l), "=f"(h) : "l"(a)); (void)h; return l; }
+__device__ __forceinline__ float hi(p2 a) { float l, h; asm("mov.b64 {%0, %1}, %2;" : "=f"(l), "=f"(h) : "l"(a)); (void)l; return h; }
+// a*b + c on both halves
+__device__ __forceinline__ p2 fma2(p2 a, p2 b, p2 c) { p2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
+// s*b + c, scalar s broadcast to both halves (SASS: FFMA2 Rd, Rs.F32, Rb.F32x2, Rc.F32x2)
+__device__ __forceinline__ p2 fma2s(float s, p2 b, p2 c)
+{
+    p2 r;
+    asm("{.reg .b64 t; mov.b64 t, {%1, %1}; fma.rn.f32x2 %0, t, %2, %3;}" : "=l"(r) : "f"(s), "l"(b), "l"(c));
+    return r;
+}
+// s*b - c (the negation folds into FFMA2's operand modifier)
+__device__ __forceinline__ p2 fma2s_sub(float s, p2 b, p2 c)
+{
+    p2 r;
+    asm("{.reg .b64 t, u; .reg .f32 l, h; mov.b64 t, {%1, %1}; mov.b64 {l, h}, %3; neg.f32 l, l; neg.f32 h, h;"
+        " mov.b64 u, {l, h}; fma.rn.f32x2 %0, t, %2, u;}" : "=l"(r) : "f"(s), "l"(b), "l"(c));
+    return r;
+}
+__device__ __forceinline__ p2 add2(p2 a, p2 b) { p2 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ p2 sub2(p2 a, p2 b) { p2 r; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ float4 lds4(const float* p) { return *reinterpret_cast<const float4*>(p); }
 
 template <int W, int NBUF> struct X2Smem {
-    alignas(1024) float tile[NBUF][64 * W * kL]; // 2T rows x 32 frames per buffer, SWIZZLE_128B
+    alignas(1024) float tile[NBUF][64 * W * kL]; // 2T rows x 32 frames per buffer, SWIZZLE_128B; warp w owns rows [64w, 64w+64)
     alignas(16) C8TablesX2 tab;
     alignas(16) float carry[2][kC8State];        // tile-parity double buffer (W > 1 only)
-    alignas(16) float wtot[8][W][2];             // per-section warp totals (W > 1 only)
-    alignas(8) uint64_t full[NBUF];
+    alignas(16) float wtot[8][W][2];             // per-stage warp totals (W > 1 only)
+    alignas(8) uint64_t full[NBUF][W];           // one mbarrier per warp and buffer
 };
 
 template <int W, int NBUF> struct X2Ctx {
@@ -141,49 +172,58 @@ template <int W, int NBUF> struct X2Ctx {
     float c[kC8State];      // W == 1: carry lives in registers
 };
 
-// ---- one biquad section over both chunks of the thread ------------------------------------------
-// x[k] = (frame k of chunk A, frame k of chunk B).  B1ZERO: band-pass sections (b1 == 0 exactly).
-template <int W, int NBUF, bool B1ZERO, bool MIX>
-__device__ __forceinline__ void biquad_x2(X2Ctx<W, NBUF>& cx, float2 (&x)[kL], const int sec)
+// pass A of stage 0 (no previous stage to fuse it into): zero-state end states of both chunks
+__device__ __forceinline__ void pass_a0(const C8TablesX2& tb, const p2 (&x)[kL], p2& z1, p2& z2)
 {
-    const C8TablesX2& tb = cx.sm->tab;
-    // pass A: zero-state end state of both chunks; 4 independent FFMA2 chains
-    float2 z1 = f2(0, 0), z2 = f2(0, 0), y1 = f2(0, 0), y2 = f2(0, 0);
+    p2 a1 = pk(0.f, 0.f), a2 = a1, b1 = a1, b2 = a1;
 #pragma unroll
     for (int k = 0; k < kL; k += 2) {
-        const float4 h = *reinterpret_cast<const float4*>(&tb.HA[sec][k][0]);
-        const float4 g = *reinterpret_cast<const float4*>(&tb.HA[sec][k + 1][0]);
-        z1 = fma2(f2(h.x, h.y), x[k], z1); z2 = fma2(f2(h.z, h.w), x[k], z2);
-        y1 = fma2(f2(g.x, g.y), x[k + 1], y1); y2 = fma2(f2(g.z, g.w), x[k + 1], y2);
+        const float4 h = lds4(&tb.HA[0][k][0]);        // (h1[k], h2[k], h1[k+1], h2[k+1])
+        a1 = fma2s(h.x, x[k], a1); a2 = fma2s(h.y, x[k], a2);
+        b1 = fma2s(h.z, x[k + 1], b1); b2 = fma2s(h.w, x[k + 1], b2);
     }
-    z1 = add2(z1, y1); z2 = add2(z2, y2);             // z1 = (z1A, z1B), z2 = (z2A, z2B)
+    z1 = add2(a1, b1); z2 = add2(a2, b2);
+}
+
+// ---- one biquad stage over both chunks of the thread ---------------------------------------------
+// x[k] = (frame k of chunk A, frame k of chunk B).  In: (z1, z2) = zero-state end states of THIS stage
+// (z1 = (z1A, z1B), z2 = (z2A, z2B)); out: the same for stage sec+1, accumulated while pass B runs.
+// BP: band-pass stages S3/S4 (b1 == 0 exactly, output mixed onto the through signal).
+template <int W, int NBUF, bool BP>
+__device__ __forceinline__ void biquad_stage(X2Ctx<W, NBUF>& cx, p2 (&x)[kL], const int sec, p2& z1, p2& z2)
+{
+    const C8TablesX2& tb = cx.sm->tab;
+    const float z1a = lo(z1), z1b = hi(z1), z2a = lo(z2), z2b = hi(z2);
     // fold A into B: c = N^32 zA + zB  (zero-state end state of the thread's 64 frames)
-    const float4 n32 = *reinterpret_cast<const float4*>(&tb.P2[sec][33][0]);
-    float c1 = fmaf(n32.x, z1.x, fmaf(n32.y, z2.x, z1.y));
-    float c2 = fmaf(n32.z, z1.x, fmaf(n32.w, z2.x, z2.y));
+    const float4 n32 = lds4(&tb.P2[sec][33][0]);
+    float c1 = fmaf(n32.x, z1a, fmaf(n32.y, z2a, z1b));
+    float c2 = fmaf(n32.z, z1a, fmaf(n32.w, z2a, z2b));
     // inclusive Kogge-Stone scan of w -> M w + c over the warp's 32 threads, M = N^64
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
         const float u1 = shfl_up(c1, d), u2 = shfl_up(c2, d);
-        const float4 m = *reinterpret_cast<const float4*>(&tb.P2[sec][d][0]);
+        const float4 m = lds4(&tb.P2[sec][d][0]);
         if (cx.lane >= d) {
             c1 = fmaf(m.x, u1, fmaf(m.y, u2, c1));
             c2 = fmaf(m.z, u1, fmaf(m.w, u2, c2));
         }
     }
     // state entering my warp: exact sequential state (z1, z2) -> scan coordinates
-    const float4 tf = *reinterpret_cast<const float4*>(&tb.T2[sec][0]);
-    const float4 ti = *reinterpret_cast<const float4*>(&tb.T2[sec][4]);
+    const float4 tf = lds4(&tb.T2[sec][0]);
+    const float4 ti = lds4(&tb.T2[sec][4]);
     float s1, s2;
     if (W == 1) {
-        const float a = cx.c[2 * sec], b = cx.c[2 * sec + 1];
+        float a = 0, b = 0;
+#pragma unroll
+        for (int q = 0; q < 6; ++q)                   // sec is a run-time value: select from the register file
+            if (q == sec) { a = cx.c[2 * q]; b = cx.c[2 * q + 1]; }
         s1 = fmaf(tf.x, a, tf.y * b); s2 = fmaf(tf.z, a, tf.w * b);
     } else {
         if (cx.lane == 31) { cx.sm->wtot[sec][cx.warp][0] = c1; cx.sm->wtot[sec][cx.warp][1] = c2; }
         __syncthreads();
         const float a = cx.sm->carry[cx.par][2 * sec], b = cx.sm->carry[cx.par][2 * sec + 1];
         s1 = fmaf(tf.x, a, tf.y * b); s2 = fmaf(tf.z, a, tf.w * b);
-        const float4 m = *reinterpret_cast<const float4*>(&tb.P2[sec][32][0]);
+        const float4 m = lds4(&tb.P2[sec][32][0]);
         for (int w = 0; w < cx.warp; ++w) {
             const float t1 = fmaf(m.x, s1, fmaf(m.y, s2, cx.sm->wtot[sec][w][0]));
             const float t2 = fmaf(m.z, s1, fmaf(m.w, s2, cx.sm->wtot[sec][w][1]));
@@ -193,54 +233,61 @@ __device__ __forceinline__ void biquad_x2(X2Ctx<W, NBUF>& cx, float2 (&x)[kL], c
     // start of chunk A: exclusive prefix + M^lane * warp-incoming state; start of chunk B: N^32 wA + zA
     float e1 = shfl_up(c1, 1), e2 = shfl_up(c2, 1);
     if (cx.lane == 0) { e1 = 0; e2 = 0; }
-    const float4 pl = *reinterpret_cast<const float4*>(&tb.P2[sec][cx.lane][0]);
+    const float4 pl = lds4(&tb.P2[sec][cx.lane][0]);
     const float wa1 = fmaf(pl.x, s1, fmaf(pl.y, s2, e1));
     const float wa2 = fmaf(pl.z, s1, fmaf(pl.w, s2, e2));
-    const float wb1 = fmaf(n32.x, wa1, fmaf(n32.y, wa2, z1.x));
-    const float wb2 = fmaf(n32.z, wa1, fmaf(n32.w, wa2, z2.x));
+    const float wb1 = fmaf(n32.x, wa1, fmaf(n32.y, wa2, z1a));
+    const float wb2 = fmaf(n32.z, wa1, fmaf(n32.w, wa2, z2a));
     // back to the recurrence's own coordinates (z1, z2) = T^-1 w, as pairs
-    float2 st1 = fma2(dup(ti.x), f2(wa1, wb1), mul2(dup(ti.y), f2(wa2, wb2)));
-    float2 st2 = fma2(dup(ti.z), f2(wa1, wb1), mul2(dup(ti.w), f2(wa2, wb2)));
-    // pass B: the TDF-II recurrence (Spectral Stabilizer.jsfx:98-111) on both chunks in lockstep
-    const float2 b0 = dup(tb.coef[5 * sec]), b1 = dup(tb.coef[5 * sec + 1]), b2 = dup(tb.coef[5 * sec + 2]);
-    const float2 nd1 = dup(tb.coef[5 * sec + 3]), d2 = dup(tb.coef[5 * sec + 4]);
-    const float2 two = dup(2.0f), mix = dup(tb.coef[32]);
+    const p2 w1 = pk(wa1, wb1), w2 = pk(wa2, wb2), zero = pk(0.f, 0.f);
+    p2 st1 = fma2s(ti.x, w1, fma2s(ti.y, w2, zero));
+    p2 st2 = fma2s(ti.z, w1, fma2s(ti.w, w2, zero));
+    // pass B: the TDF-II recurrence (Spectral Stabilizer.jsfx:98-111) on both chunks in lockstep,
+    // with pass A of the next stage riding along on the fresh outputs
+    const float* cf = &tb.coef[5 * sec];
+    const float b0 = cf[0], b1 = cf[1], b2 = cf[2], nd1 = cf[3], d2 = cf[4], mix = tb.coef[32];
+    const float* hn = &tb.HA[sec + 1][0][0];
+    p2 p1 = zero, pp2 = zero, q1 = zero, q2 = zero;
 #pragma unroll
-    for (int k = 0; k < kL; ++k) {
-        const float2 xx = x[k];
-        const float2 y = fma2(b0, xx, st1);
-        // z1' = b1 x - a1 y + z2 = (b1 x + z2) + 2 y - d1 y ;  z2' = b2 x - a2 y = (b2 x - y) + d2 y
-        const float2 t = B1ZERO ? st2 : fma2(b1, xx, st2);
-        st1 = fma2(two, y, fma2(nd1, y, t));
-        st2 = fma2(d2, y, fma2(b2, xx, neg2(y)));
-        x[k] = MIX ? fma2(mix, y, xx) : y;
+    for (int k = 0; k < kL; k += 2) {
+        const float4 h = lds4(hn + 2 * k);             // next stage's (h1[k], h2[k], h1[k+1], h2[k+1])
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const p2 xx = x[k + j];
+            const p2 y = fma2s(b0, xx, st1);
+            // z1' = b1 x - a1 y + z2 = (b1 x + z2) + 2 y - d1 y ;  z2' = b2 x - a2 y = (b2 x - y) + d2 y
+            const p2 t = BP ? st2 : fma2s(b1, xx, st2);
+            st1 = fma2s(2.0f, y, fma2s(nd1, y, t));
+            st2 = fma2s(d2, y, fma2s_sub(b2, xx, y));
+            const p2 xo = BP ? fma2s(mix, y, xx) : y;
+            x[k + j] = xo;
+            if (j) { q1 = fma2s(h.z, xo, q1); q2 = fma2s(h.w, xo, q2); }
+            else   { p1 = fma2s(h.x, xo, p1); pp2 = fma2s(h.y, xo, pp2); }
+        }
     }
+    z1 = add2(p1, q1); z2 = add2(pp2, q2);
     // publish the exact sequential state after the tile's last valid chunk
-    const float sn1 = cx.half_last ? st1.y : st1.x, sn2 = cx.half_last ? st2.y : st2.x;
+    const float sn1 = cx.half_last ? hi(st1) : lo(st1), sn2 = cx.half_last ? hi(st2) : lo(st2);
     if (W == 1) {
-        cx.c[2 * sec] = shfl_idx(sn1, cx.t_last); cx.c[2 * sec + 1] = shfl_idx(sn2, cx.t_last);
+        const float g1 = shfl_idx(sn1, cx.t_last), g2 = shfl_idx(sn2, cx.t_last);
+#pragma unroll
+        for (int q = 0; q < 6; ++q)
+            if (q == sec) { cx.c[2 * q] = g1; cx.c[2 * q + 1] = g2; }
     } else if (cx.tid == cx.t_last) {
         cx.sm->carry[cx.par ^ 1][2 * sec] = sn1; cx.sm->carry[cx.par ^ 1][2 * sec + 1] = sn2;
     }
 }
 
-// ---- one one-pole section: s += c (x - s)  (ERB Tilt.jsfx:397 and EasyExpander.jsfx:186 forms) ------
+// ---- one one-pole stage: s += c (x - s)  (ERB Tilt.jsfx:397 and EasyExpander.jsfx:186 forms) --------
+// In: z = (zA, zB) zero-state end states of this stage; O == 0 also accumulates pass A of S8 into it.
 template <int W, int NBUF, int O>
-__device__ __forceinline__ void onepole_x2(X2Ctx<W, NBUF>& cx, float2 (&x)[kL])
+__device__ __forceinline__ void onepole_stage(X2Ctx<W, NBUF>& cx, p2 (&x)[kL], p2& z)
 {
     const C8TablesX2& tb = cx.sm->tab;
     constexpr int sec = 6 + O, ci = 12 + O;
-    float2 z = f2(0, 0), za = f2(0, 0), zb = f2(0, 0), zc = f2(0, 0);
-#pragma unroll
-    for (int k = 0; k < kL; k += 4) {
-        const float4 h = *reinterpret_cast<const float4*>(&tb.H1[O][k][0]);
-        const float4 g = *reinterpret_cast<const float4*>(&tb.H1[O][k + 2][0]);
-        z = fma2(f2(h.x, h.y), x[k], z); za = fma2(f2(h.z, h.w), x[k + 1], za);
-        zb = fma2(f2(g.x, g.y), x[k + 2], zb); zc = fma2(f2(g.z, g.w), x[k + 3], zc);
-    }
-    z = add2(add2(z, za), add2(zb, zc));              // (zA, zB)
+    const float za = lo(z), zb = hi(z);
     const float a32 = tb.P1[O][33];
-    float c = fmaf(a32, z.x, z.y);
+    float c = fmaf(a32, za, zb);
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
         const float u = shfl_up(c, d);
@@ -260,31 +307,50 @@ __device__ __forceinline__ void onepole_x2(X2Ctx<W, NBUF>& cx, float2 (&x)[kL])
     float e = shfl_up(c, 1);
     if (cx.lane == 0) e = 0;
     const float sa = fmaf(tb.P1[O][cx.lane], s, e);
-    const float sb = fmaf(a32, sa, z.x);
-    float2 st = f2(sa, sb);
-    const float2 cc = dup(tb.coef[30 + O]);
+    const float sb = fmaf(a32, sa, za);
+    p2 st = pk(sa, sb);
+    const float cc = tb.coef[30 + O];
+    const p2 zero = pk(0.f, 0.f);
+    p2 p = zero, q = zero, r = zero, t = zero;
 #pragma unroll
-    for (int k = 0; k < kL; ++k) {
-        st = fma2(cc, add2(x[k], neg2(st)), st);
-        x[k] = st;
+    for (int k = 0; k < kL; k += 4) {
+        float4 h = make_float4(0, 0, 0, 0);
+        if (O == 0) h = lds4(&tb.HB[k]);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            st = fma2s(cc, sub2(x[k + j], st), st);
+            x[k + j] = st;
+        }
+        if (O == 0) {
+            p = fma2s(h.x, x[k], p); q = fma2s(h.y, x[k + 1], q);
+            r = fma2s(h.z, x[k + 2], r); t = fma2s(h.w, x[k + 3], t);
+        }
     }
-    const float sn = cx.half_last ? st.y : st.x;
+    if (O == 0) z = add2(add2(p, q), add2(r, t));
+    const float sn = cx.half_last ? hi(st) : lo(st);
     if (W == 1) cx.c[ci] = shfl_idx(sn, cx.t_last);
     else if (cx.tid == cx.t_last) cx.sm->carry[cx.par ^ 1][ci] = sn;
 }
 
 // ---- the whole cascade over one tile (cascade8.jsfx @sample) ----------------------------------
 template <int W, int NBUF>
-__device__ __forceinline__ void cascade8_x2_tile(X2Ctx<W, NBUF>& cx, float2 (&x)[kL])
+__device__ __forceinline__ void cascade8_x2_tile(X2Ctx<W, NBUF>& cx, p2 (&x)[kL])
 {
-    biquad_x2<W, NBUF, false, false>(cx, x, 0);   // S1 HP
-    biquad_x2<W, NBUF, false, false>(cx, x, 1);   // S2 LP
-    biquad_x2<W, NBUF, true, true>(cx, x, 2);     // S3 BP (peak), u3 = y2 + mix*y3
-    biquad_x2<W, NBUF, true, true>(cx, x, 3);     // S4 BP (skirt), u4 = u3 + mix*y4
-    biquad_x2<W, NBUF, false, false>(cx, x, 4);   // S5 LP
-    biquad_x2<W, NBUF, false, false>(cx, x, 5);   // S6 HP
-    onepole_x2<W, NBUF, 0>(cx, x);                // S7
-    onepole_x2<W, NBUF, 1>(cx, x);                // S8
+    p2 z1, z2;
+    pass_a0(cx.sm->tab, x, z1, z2);
+    // S1 HP, S2 LP | S3 BP(peak) + mix, S4 BP(skirt) + mix | S5 LP, S6 HP: two loop bodies, run-time stage index
+#pragma unroll 1
+    for (int g = 0; g < 3; ++g) {
+        if (g == 1) {
+#pragma unroll 1
+            for (int j = 0; j < 2; ++j) biquad_stage<W, NBUF, true>(cx, x, 2 + j, z1, z2);
+        } else {
+#pragma unroll 1
+            for (int j = 0; j < 2; ++j) biquad_stage<W, NBUF, false>(cx, x, 2 * g + j, z1, z2);
+        }
+    }
+    onepole_stage<W, NBUF, 0>(cx, x, z1);   // S7 (its pass A came out of S6's loop as z1)
+    onepole_stage<W, NBUF, 1>(cx, x, z1);   // S8
 }
 
 __device__ __forceinline__ void tma_prefetch_3d(const CUtensorMap* map, int c0, int c1, int c2)
@@ -299,12 +365,13 @@ struct X2Args {
 };
 
 // One CTA per stream, persistent over time.  n_frames % 32 == 0, rows 16-byte aligned (TMA).
+// The tensor maps have box {32 frames, 64 chunks, 1 stream}: one box = one warp's share of a tile.
 template <int W, int NBUF>
-__global__ void __launch_bounds__(32 * W)
+__global__ void __launch_bounds__(32 * W, 16 / W)     // <= 128 registers: 4 warps per SM sub-partition (16 K registers each)
 cascade8_x2_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constant__ CUtensorMap out_map, const X2Args a)
 {
     constexpr int T = 32 * W;
-    constexpr int kTileBytes = 64 * W * kL * 4;
+    constexpr int kWarpBytes = 64 * kL * 4;            // 8 KB: 64 rows of 128 B
     extern __shared__ uint8_t smem_raw[];
     using Smem = X2Smem<W, NBUF>;
     // pointer arithmetic on the __shared__ array itself keeps the address space known to ptxas (LDS/STS, not generic LD/ST)
@@ -316,10 +383,12 @@ cascade8_x2_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_cons
 
     const int64_t n_chunks = a.n_chunks;
     const int n_tiles = (int)((n_chunks + 2 * T - 1) / (2 * T));
+    const int wrow = 64 * cx.warp;                     // first row (chunk) of this warp inside a tile
 
     if (cx.tid == 0) {
         prefetch_tensormap(&in_map); prefetch_tensormap(&out_map);
-        for (int s = 0; s < NBUF; ++s) mbar_init(&sm->full[s], 1);
+        for (int s = 0; s < NBUF; ++s)
+            for (int w = 0; w < W; ++w) mbar_init(&sm->full[s][w], 1);
         fence_barrier_init();
     }
     {   // per-stream tables -> shared memory (once per launch)
@@ -335,15 +404,18 @@ cascade8_x2_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_cons
         sm->carry[0][cx.tid] = (float)gstate[cx.tid];
     }
     __syncthreads();
-    if (cx.tid == 0) {
-        for (int s = 0; s < NBUF && s < n_tiles; ++s) {
-            mbar_expect_tx(&sm->full[s], kTileBytes);
-            tma_load_3d(sm->tile[s], &in_map, &sm->full[s], 0, s * 2 * T, stream);
-        }
-        if (NBUF == 1 && n_tiles > 1) tma_prefetch_3d(&in_map, 0, 2 * T, stream);
+    // a warp whose 64 chunks lie entirely past the end takes no part in the copies of that tile
+    auto warp_live = [&](int tile_idx) { return (int64_t)tile_idx * 2 * T + wrow < n_chunks; };
+    if (cx.lane == 0) {
+        for (int s = 0; s < NBUF && s < n_tiles; ++s)
+            if (warp_live(s)) {
+                mbar_expect_tx(&sm->full[s][cx.warp], kWarpBytes);
+                tma_load_3d(sm->tile[s] + wrow * kL, &in_map, &sm->full[s][cx.warp], 0, s * 2 * T + wrow, stream);
+            }
+        if (NBUF == 1 && n_tiles > 1 && warp_live(1)) tma_prefetch_3d(&in_map, 0, 2 * T + wrow, stream);
     }
 
-    float2 x[kL];
+    p2 x[kL];
     for (int i = 0; i < n_tiles; ++i) {
         const int b = NBUF == 1 ? 0 : (i & 1);
         float* tile = sm->tile[b];
@@ -351,43 +423,44 @@ cascade8_x2_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_cons
         const int nvc = (int)((n_chunks - c0) < 2 * T ? (n_chunks - c0) : 2 * T);    // valid chunks in this tile
         cx.t_last = (nvc - 1) >> 1;
         cx.half_last = (nvc - 1) & 1;
-        mbar_wait(&sm->full[b], (uint32_t)((NBUF == 1 ? i : (i >> 1)) & 1));
-        // rows 2t (chunk A) and 2t+1 (chunk B) -> register pairs
+        const bool live = warp_live(i);
+        if (live) {
+            mbar_wait(&sm->full[b][cx.warp], (uint32_t)((NBUF == 1 ? i : (i >> 1)) & 1));
+            // rows 2t (chunk A) and 2t+1 (chunk B) -> register pairs
 #pragma unroll
-        for (int j = 0; j < kL / 4; ++j) {
-            const float4 va = *reinterpret_cast<const float4*>(tile + swz_piece(2 * cx.tid, j));
-            const float4 vb = *reinterpret_cast<const float4*>(tile + swz_piece(2 * cx.tid + 1, j));
-            x[4 * j + 0] = f2(va.x, vb.x); x[4 * j + 1] = f2(va.y, vb.y);
-            x[4 * j + 2] = f2(va.z, vb.z); x[4 * j + 3] = f2(va.w, vb.w);
+            for (int j = 0; j < kL / 4; ++j) {
+                const float4 va = lds4(tile + swz_piece(2 * cx.tid, j));
+                const float4 vb = lds4(tile + swz_piece(2 * cx.tid + 1, j));
+                x[4 * j + 0] = pk(va.x, vb.x); x[4 * j + 1] = pk(va.y, vb.y);
+                x[4 * j + 2] = pk(va.z, vb.z); x[4 * j + 3] = pk(va.w, vb.w);
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < kL; ++k) x[k] = pk(0.f, 0.f);
         }
 
         cascade8_x2_tile<W, NBUF>(cx, x);
 
+        if (live) {
 #pragma unroll
-        for (int j = 0; j < kL / 4; ++j) {
-            *reinterpret_cast<float4*>(tile + swz_piece(2 * cx.tid, j)) =
-                make_float4(x[4 * j].x, x[4 * j + 1].x, x[4 * j + 2].x, x[4 * j + 3].x);
-            *reinterpret_cast<float4*>(tile + swz_piece(2 * cx.tid + 1, j)) =
-                make_float4(x[4 * j].y, x[4 * j + 1].y, x[4 * j + 2].y, x[4 * j + 3].y);
-        }
-        fence_proxy_async();
-        if (W == 1) __syncwarp(); else __syncthreads();
-        if (cx.tid == 0) {
-            tma_store_3d(&out_map, tile, 0, (int)c0, stream);
-            tma_commit();
-            if (NBUF == 1) {
-                if (i + 1 < n_tiles) {
-                    tma_wait_read<0>();                       // the store has read the buffer: refill it
-                    mbar_expect_tx(&sm->full[0], kTileBytes);
-                    tma_load_3d(sm->tile[0], &in_map, &sm->full[0], 0, (int)c0 + 2 * T, stream);
-                    if (i + 2 < n_tiles) tma_prefetch_3d(&in_map, 0, (int)c0 + 4 * T, stream);
-                }
-            } else {
-                // buffer b is free once this store has read it; tile i+2 goes there, tile i+1 is already in flight
-                if (i + 2 < n_tiles) {
-                    tma_wait_read<0>();
-                    mbar_expect_tx(&sm->full[b], kTileBytes);
-                    tma_load_3d(sm->tile[b], &in_map, &sm->full[b], 0, (int)c0 + 4 * T, stream);
+            for (int j = 0; j < kL / 4; ++j) {
+                *reinterpret_cast<float4*>(tile + swz_piece(2 * cx.tid, j)) =
+                    make_float4(lo(x[4 * j]), lo(x[4 * j + 1]), lo(x[4 * j + 2]), lo(x[4 * j + 3]));
+                *reinterpret_cast<float4*>(tile + swz_piece(2 * cx.tid + 1, j)) =
+                    make_float4(hi(x[4 * j]), hi(x[4 * j + 1]), hi(x[4 * j + 2]), hi(x[4 * j + 3]));
+            }
+            fence_proxy_async();
+            __syncwarp();
+            if (cx.lane == 0) {
+                tma_store_3d(&out_map, tile + wrow * kL, 0, (int)c0 + wrow, stream);
+                tma_commit();
+                const int nx = i + NBUF;                      // the tile that reuses this buffer
+                if (nx < n_tiles && warp_live(nx)) {
+                    tma_wait_read<0>();                       // the store has read the rows: refill them
+                    mbar_expect_tx(&sm->full[b][cx.warp], kWarpBytes);
+                    tma_load_3d(tile + wrow * kL, &in_map, &sm->full[b][cx.warp], 0, nx * 2 * T + wrow, stream);
+                    if (NBUF == 1 && nx + 1 < n_tiles && warp_live(nx + 1))
+                        tma_prefetch_3d(&in_map, 0, (nx + 1) * 2 * T + wrow, stream);
                 }
             }
         }
@@ -405,7 +478,7 @@ cascade8_x2_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_cons
         __syncthreads();
         if (cx.tid < 14) gs[cx.tid] = (double)sm->carry[cx.par][cx.tid];
     }
-    if (cx.tid == 0) tma_wait_all<0>();
+    if (cx.lane == 0) tma_wait_all<0>();
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -416,13 +489,15 @@ static bool launch_x2(const C8Launch& L)
 {
     X2Args a{L.n_frames / kL, L.tables_x2, L.state};
     CUtensorMap in_map, out_map;
-    if (!make_chunk_tensor_map(&in_map, L.in, a.n_chunks, L.n_streams, L.row_stride, 64 * W)) return false;
-    if (!make_chunk_tensor_map(&out_map, L.out, a.n_chunks, L.n_streams, L.row_stride, 64 * W)) return false;
+    if (!make_chunk_tensor_map(&in_map, L.in, a.n_chunks, L.n_streams, L.row_stride, 64)) return false;
+    if (!make_chunk_tensor_map(&out_map, L.out, a.n_chunks, L.n_streams, L.row_stride, 64)) return false;
     auto kern = cascade8_x2_kernel<W, NBUF>;
     const size_t smem = sizeof(X2Smem<W, NBUF>) + 1024;
     static bool attr_done = false;    // per template instantiation
     if (!attr_done) {
         if (!cuda_ok(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "smem attr")) return false;
+        // all of L1 as shared memory: the kernel's only L1 traffic is TMA, and 8 CTAs x 26 KB must fit
+        if (!cuda_ok(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared), "carveout")) return false;
         attr_done = true;
     }
     kern<<<L.n_streams, 32 * W, smem, L.stream>>>(in_map, out_map, a);
@@ -446,8 +521,8 @@ bool cascade8_x2_launch(const C8Launch& L)
 }
 
 // Warps per stream and tile buffers: all streams resident in one wave when they fit (one CTA = one
-// stream runs the whole time axis), as many warps per SM as the register file allows (128 regs/thread
-// -> 16 warps), double-buffered tiles only if shared memory still fits that many CTAs.
+// stream runs the whole time axis), up to 16 warps per SM (128 registers per thread), double-buffered
+// tiles only if shared memory still fits that many CTAs.
 void cascade8_x2_pick(int n_streams, int device, int* warps, int* nbuf)
 {
     int sms = 148;
