@@ -6,23 +6,30 @@
 // instruction count.  Blackwell's packed `fma.rn.f32x2` (SASS FFMA2) retires two FMAs per issue
 // slot with the same latency as FFMA, so:
 //
-//   * every thread owns TWO adjacent 32-frame chunks (A = 2t, B = 2t+1) and keeps them as 32
-//     register PAIRS (xA[k], xB[k]); pass A (zero-state FIR) and pass B (the recurrence) run on
-//     both chunks in lockstep, one FFMA2 per formerly two FFMAs.  The pairs are carried as 64-bit
-//     values (inline-PTX fma.rn.f32x2 on .b64 registers) so ptxas keeps them in aligned register
-//     pairs across the run-time stage loops; CTA-uniform coefficients use FFMA2's scalar-broadcast
-//     operand form (`R.F32`), negated addends fold into its operand modifier;
-//   * the warp-shuffle scan runs once per 64 frames (the thread first folds A into B);
-//   * pass A of stage s+1 is fused into the pass-B loop of stage s (independent FFMA2s that fill
-//     the recurrence's dependent-chain bubbles), and the six biquads run as runtime loops over
-//     two loop bodies (plain / band-pass+mix) so the hot code stays inside the instruction cache
-//     (v2a, fully unrolled, lost 12 % of its issue slots to `no_instruction` stalls);
-//   * one CTA = one stream; each WARP moves its own 64-row half of the tile: ONE TMA tensor load
+//   * every thread owns 64 consecutive frames = rows 2t and 2t+1 of the tile = FOUR 16-frame chunks
+//     (A, B | C, D) and keeps them as 32 register PAIRS (A[k], B[k]), (C[k], D[k]); pass A (zero-
+//     state FIR) and pass B (the recurrence) run on the pairs, one FFMA2 per formerly two FFMAs,
+//     as two independent chains (AB, CD) so a single warp can keep the FMA pipe fed.  The pairs
+//     are carried as 64-bit values (inline-PTX fma.rn.f32x2 on .b64 registers) so ptxas keeps them
+//     in aligned register pairs across the run-time stage loops; CTA-uniform coefficients use
+//     FFMA2's scalar-broadcast operand form (`R.F32`), negated addends fold into its operand
+//     modifier, and pass B is arranged so that every read of x[k] precedes y (z2' = (b2-b0) x - z1
+//     + d2 y), which lets y overwrite x[k] in place: the stage loops hold no register copies;
+//   * the warp-shuffle scan runs once per 64 frames (the thread first folds its four chunks);
+//   * pass A of stage s+1 is fused into the pass-B loop of stage s, and the six biquads run as
+//     run-time loops over two loop bodies (plain / band-pass+mix) so the hot code stays inside the
+//     instruction cache (v2a, fully unrolled, lost 12 % of its issue slots to `no_instruction`);
+//   * one CTA = one stream; each WARP moves its own 64-row share of the tile: ONE TMA tensor load
 //     into the warp's smem rows, compute in registers, results written back to the SAME rows
 //     (a thread only touches its own two rows), one TMA tensor store.  The next tile is pulled
 //     into L2 by a TMA prefetch while this one computes, so the exposed load is an L2 hit that
-//     the other resident warps cover.  smem per CTA = 16 KB (W = 2) + 8 KB tables, so 8 CTAs
+//     the other resident warps cover.  smem per CTA = 16 KB (W = 2) + 6 KB tables, so 8 CTAs
 //     (16 warps at 128 registers) share an SM.
+//
+// What bounds it (profiles/r01_cascade8_x2_ncu.md): 56 FMAs per frame are irreducible for this
+// scan formulation (2 pass A + 6 pass B per biquad frame); an FFMA2 holds the sub-partition's
+// dispatch port for 2 cycles, as does every 16-lane ALU-pipe instruction (tools/ubench_issue.cu),
+// so the kernel is dispatch-bound, not HBM-bound: DRAM traffic equals the algorithmic bytes.
 //
 // Arithmetic notes (fp32 mode only has to null below -100 dBFS against the fp64 oracle):
 //   * feedback coefficients are delta-coded, a1 = -2 + d1, a2 = 1 - d2, as in v1;
@@ -33,14 +40,16 @@
 
 namespace za {
 
+constexpr int kH = 16;   // frames per thread-chunk of the packed kernel: 4 chunks (A, B | C, D) = 2 rows of a tile
+
 struct alignas(16) C8TablesX2 {
-    float HA[7][kL][2];     // stages 0-5, biquads: (h1k, h2k), h_k = T A^(31-k) B (zero-state end state, scan
-                            // coords); stage 6 = one-pole S7 in the same row format: (h_k, 0)
-    float HB[kL];           // one-pole S8: h_k
-    float P2[6][34][4];     // (N^64)^j for j = 0..32 (row-major 2x2); [33] = N^32
+    float HA[7][kH][2];     // stages 0-5, biquads: (h1k, h2k), h_k = T A^(15-k) B (zero-state end state of a
+                            // 16-frame chunk, scan coords); stage 6 = one-pole S7 in the same row format: (h_k, 0)
+    float HB[kH];           // one-pole S8: h_k
+    float P2[6][36][4];     // (N^64)^j for j = 0..32 (row-major 2x2); [33] = N^16, [34] = N^32
     float T2[6][8];         // T (4), T^-1 (4)
-    float P1[2][36];        // (alpha^64)^j, j = 0..32; [33] = alpha^32
-    float coef[40];         // per biquad k: b0 b1 b2 -d1 d2 at [5k..5k+4]; [30] = c7, [31] = c8, [32] = mix
+    float P1[2][36];        // (alpha^64)^j, j = 0..32; [33] = alpha^16, [34] = alpha^32
+    float coef[40];         // per biquad k: b0 b1 (b2-b0) -d1 d2 at [5k..5k+4]; [30] = c7, [31] = c8, [32] = mix
 };
 
 size_t cascade8_x2_tables_bytes() { return sizeof(C8TablesX2); }
@@ -67,19 +76,20 @@ __global__ void cascade8_x2_tables_kernel(const double* __restrict__ coef, C8Tab
         }
         const double bb1 = b1 - a1 * b0, bb2 = b2 - a2 * b0;
         double v1 = t00 * bb1 + t01 * bb2, v2 = t10 * bb1 + t11 * bb2;
-        for (int k = kL - 1; k >= 0; --k) {
+        for (int k = kH - 1; k >= 0; --k) {
             t.HA[sec][k][0] = (float)v1; t.HA[sec][k][1] = (float)v2;
             const double x1 = n00 * v1 + n01 * v2, x2 = n10 * v1 + n11 * v2;
             v1 = x1; v2 = x2;
         }
-        double m00 = 1, m01 = 0, m10 = 0, m11 = 1;       // N^32, then N^64
-        for (int k = 0; k < kL; ++k) {
+        double m00 = 1, m01 = 0, m10 = 0, m11 = 1;       // N^16, then squared to N^32 and N^64
+        for (int k = 0; k < kH; ++k) {
             const double x00 = n00 * m00 + n01 * m10, x01 = n00 * m01 + n01 * m11;
             const double x10 = n10 * m00 + n11 * m10, x11 = n10 * m01 + n11 * m11;
             m00 = x00; m01 = x01; m10 = x10; m11 = x11;
         }
-        t.P2[sec][33][0] = (float)m00; t.P2[sec][33][1] = (float)m01; t.P2[sec][33][2] = (float)m10; t.P2[sec][33][3] = (float)m11;
-        {
+        for (int q = 33; q <= 35; ++q) {
+            if (q < 35) { t.P2[sec][q][0] = (float)m00; t.P2[sec][q][1] = (float)m01; t.P2[sec][q][2] = (float)m10; t.P2[sec][q][3] = (float)m11; }
+            else        { t.P2[sec][q][0] = 0; t.P2[sec][q][1] = 0; t.P2[sec][q][2] = 0; t.P2[sec][q][3] = 0; break; }
             const double x00 = m00 * m00 + m01 * m10, x01 = m00 * m01 + m01 * m11;
             const double x10 = m10 * m00 + m11 * m10, x11 = m10 * m01 + m11 * m11;
             m00 = x00; m01 = x01; m10 = x10; m11 = x11;
@@ -93,7 +103,7 @@ __global__ void cascade8_x2_tables_kernel(const double* __restrict__ coef, C8Tab
         }
         t.T2[sec][0] = (float)t00; t.T2[sec][1] = (float)t01; t.T2[sec][2] = (float)t10; t.T2[sec][3] = (float)t11;
         t.T2[sec][4] = (float)i00; t.T2[sec][5] = (float)i01; t.T2[sec][6] = (float)i10; t.T2[sec][7] = (float)i11;
-        t.coef[5 * sec + 0] = (float)b0; t.coef[5 * sec + 1] = (float)b1; t.coef[5 * sec + 2] = (float)b2;
+        t.coef[5 * sec + 0] = (float)b0; t.coef[5 * sec + 1] = (float)b1; t.coef[5 * sec + 2] = (float)(b2 - b0);
         t.coef[5 * sec + 3] = (float)(-(a1 + 2.0));      // -d1
         t.coef[5 * sec + 4] = (float)(1.0 - a2);         //  d2
     } else {
@@ -102,18 +112,20 @@ __global__ void cascade8_x2_tables_kernel(const double* __restrict__ coef, C8Tab
         const double cc = o == 0 ? c[31] : c[32];
         const double alpha = o == 0 ? c[30] : 1.0 - c[32];
         double v = cc;
-        for (int k = kL - 1; k >= 0; --k) {
+        for (int k = kH - 1; k >= 0; --k) {
             if (o == 0) { t.HA[6][k][0] = (float)v; t.HA[6][k][1] = 0; }
             else        { t.HB[k] = (float)v; }
             v *= alpha;
         }
         double m = 1;
-        for (int k = 0; k < kL; ++k) m *= alpha;
+        for (int k = 0; k < kH; ++k) m *= alpha;
         t.P1[o][33] = (float)m;
+        m *= m;
+        t.P1[o][34] = (float)m;
         m *= m;
         double p = 1;
         for (int j = 0; j <= 32; ++j) { t.P1[o][j] = (float)p; p *= m; }
-        t.P1[o][34] = 0; t.P1[o][35] = 0;
+        t.P1[o][35] = 0;
         t.coef[30 + o] = (float)cc;
         if (o == 0) { t.coef[32] = (float)c[33]; for (int i = 33; i < 40; ++i) t.coef[i] = 0; }
     }
@@ -172,32 +184,45 @@ template <int W, int NBUF> struct X2Ctx {
     float c[kC8State];      // W == 1: carry lives in registers
 };
 
-// pass A of stage 0 (no previous stage to fuse it into): zero-state end states of both chunks
-__device__ __forceinline__ void pass_a0(const C8TablesX2& tb, const p2 (&x)[kL], p2& z1, p2& z2)
+// Register layout of a thread's 64 frames (rows 2t and 2t+1 of the tile, 4 chunks of 16 in time order
+// A, B | C, D):  x[k] = (A[k], B[k]),  x[16 + k] = (C[k], D[k]),  k = 0..15.  Every pass runs two
+// independent FFMA2 chains (AB and CD) so one warp alone can keep the FMA pipe busy.
+struct ZS { p2 ab1, ab2, cd1, cd2; };     // zero-state end states: ab1 = (z1 of A, z1 of B), ...
+
+// pass A of stage 0 (no previous stage to fuse it into)
+__device__ __forceinline__ void pass_a0(const C8TablesX2& tb, const p2 (&x)[kL], ZS& z)
 {
-    p2 a1 = pk(0.f, 0.f), a2 = a1, b1 = a1, b2 = a1;
+    const p2 zero = pk(0.f, 0.f);
+    z.ab1 = zero; z.ab2 = zero; z.cd1 = zero; z.cd2 = zero;
 #pragma unroll
-    for (int k = 0; k < kL; k += 2) {
+    for (int k = 0; k < kH; k += 2) {
         const float4 h = lds4(&tb.HA[0][k][0]);        // (h1[k], h2[k], h1[k+1], h2[k+1])
-        a1 = fma2s(h.x, x[k], a1); a2 = fma2s(h.y, x[k], a2);
-        b1 = fma2s(h.z, x[k + 1], b1); b2 = fma2s(h.w, x[k + 1], b2);
+        z.ab1 = fma2s(h.x, x[k], z.ab1); z.ab2 = fma2s(h.y, x[k], z.ab2);
+        z.cd1 = fma2s(h.x, x[kH + k], z.cd1); z.cd2 = fma2s(h.y, x[kH + k], z.cd2);
+        z.ab1 = fma2s(h.z, x[k + 1], z.ab1); z.ab2 = fma2s(h.w, x[k + 1], z.ab2);
+        z.cd1 = fma2s(h.z, x[kH + k + 1], z.cd1); z.cd2 = fma2s(h.w, x[kH + k + 1], z.cd2);
     }
-    z1 = add2(a1, b1); z2 = add2(a2, b2);
 }
 
-// ---- one biquad stage over both chunks of the thread ---------------------------------------------
-// x[k] = (frame k of chunk A, frame k of chunk B).  In: (z1, z2) = zero-state end states of THIS stage
-// (z1 = (z1A, z1B), z2 = (z2A, z2B)); out: the same for stage sec+1, accumulated while pass B runs.
+// ---- one biquad stage over the four chunks of the thread -------------------------------------------
+// In: z = zero-state end states of THIS stage; out: the same for stage sec+1, accumulated while pass B runs.
 // BP: band-pass stages S3/S4 (b1 == 0 exactly, output mixed onto the through signal).
 template <int W, int NBUF, bool BP>
-__device__ __forceinline__ void biquad_stage(X2Ctx<W, NBUF>& cx, p2 (&x)[kL], const int sec, p2& z1, p2& z2)
+__device__ __forceinline__ void biquad_stage(X2Ctx<W, NBUF>& cx, p2 (&x)[kL], const int sec, ZS& z)
 {
     const C8TablesX2& tb = cx.sm->tab;
-    const float z1a = lo(z1), z1b = hi(z1), z2a = lo(z2), z2b = hi(z2);
-    // fold A into B: c = N^32 zA + zB  (zero-state end state of the thread's 64 frames)
-    const float4 n32 = lds4(&tb.P2[sec][33][0]);
-    float c1 = fmaf(n32.x, z1a, fmaf(n32.y, z2a, z1b));
-    float c2 = fmaf(n32.z, z1a, fmaf(n32.w, z2a, z2b));
+    const float zA1 = lo(z.ab1), zB1 = hi(z.ab1), zA2 = lo(z.ab2), zB2 = hi(z.ab2);
+    const float zC1 = lo(z.cd1), zD1 = hi(z.cd1), zC2 = lo(z.cd2), zD2 = hi(z.cd2);
+    const float4 n16 = lds4(&tb.P2[sec][33][0]);
+    const float4 n32 = lds4(&tb.P2[sec][34][0]);
+    const p2 zero = pk(0.f, 0.f);
+    // fold the chunks: (cAB, cCD) = N^16 (zA, zC) + (zB, zD), then c = N^32 cAB + cCD (64-frame zero-state end state)
+    const p2 zAC1 = pk(zA1, zC1), zAC2 = pk(zA2, zC2);
+    const p2 f1 = fma2s(n16.x, zAC1, fma2s(n16.y, zAC2, pk(zB1, zD1)));
+    const p2 f2 = fma2s(n16.z, zAC1, fma2s(n16.w, zAC2, pk(zB2, zD2)));
+    const float cAB1 = lo(f1), cCD1 = hi(f1), cAB2 = lo(f2), cCD2 = hi(f2);
+    float c1 = fmaf(n32.x, cAB1, fmaf(n32.y, cAB2, cCD1));
+    float c2 = fmaf(n32.z, cAB1, fmaf(n32.w, cAB2, cCD2));
     // inclusive Kogge-Stone scan of w -> M w + c over the warp's 32 threads, M = N^64
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
@@ -230,44 +255,51 @@ __device__ __forceinline__ void biquad_stage(X2Ctx<W, NBUF>& cx, p2 (&x)[kL], co
             s1 = t1; s2 = t2;
         }
     }
-    // start of chunk A: exclusive prefix + M^lane * warp-incoming state; start of chunk B: N^32 wA + zA
+    // chunk start states in scan coordinates: wA = exclusive prefix + M^lane * warp-incoming state,
+    // wC = N^32 wA + cAB, (wB, wD) = N^16 (wA, wC) + (zA, zC)
     float e1 = shfl_up(c1, 1), e2 = shfl_up(c2, 1);
     if (cx.lane == 0) { e1 = 0; e2 = 0; }
     const float4 pl = lds4(&tb.P2[sec][cx.lane][0]);
-    const float wa1 = fmaf(pl.x, s1, fmaf(pl.y, s2, e1));
-    const float wa2 = fmaf(pl.z, s1, fmaf(pl.w, s2, e2));
-    const float wb1 = fmaf(n32.x, wa1, fmaf(n32.y, wa2, z1a));
-    const float wb2 = fmaf(n32.z, wa1, fmaf(n32.w, wa2, z2a));
-    // back to the recurrence's own coordinates (z1, z2) = T^-1 w, as pairs
-    const p2 w1 = pk(wa1, wb1), w2 = pk(wa2, wb2), zero = pk(0.f, 0.f);
-    p2 st1 = fma2s(ti.x, w1, fma2s(ti.y, w2, zero));
-    p2 st2 = fma2s(ti.z, w1, fma2s(ti.w, w2, zero));
-    // pass B: the TDF-II recurrence (Spectral Stabilizer.jsfx:98-111) on both chunks in lockstep,
+    const float wA1 = fmaf(pl.x, s1, fmaf(pl.y, s2, e1));
+    const float wA2 = fmaf(pl.z, s1, fmaf(pl.w, s2, e2));
+    const float wC1 = fmaf(n32.x, wA1, fmaf(n32.y, wA2, cAB1));
+    const float wC2 = fmaf(n32.z, wA1, fmaf(n32.w, wA2, cAB2));
+    const p2 wAC1 = pk(wA1, wC1), wAC2 = pk(wA2, wC2);
+    const p2 wBD1 = fma2s(n16.x, wAC1, fma2s(n16.y, wAC2, zAC1));
+    const p2 wBD2 = fma2s(n16.z, wAC1, fma2s(n16.w, wAC2, zAC2));
+    // back to the recurrence's own coordinates (z1, z2) = T^-1 w, as (A, B) and (C, D) pairs
+    const p2 wab1 = pk(wA1, lo(wBD1)), wab2 = pk(wA2, lo(wBD2)), wcd1 = pk(wC1, hi(wBD1)), wcd2 = pk(wC2, hi(wBD2));
+    p2 sa1 = fma2s(ti.x, wab1, fma2s(ti.y, wab2, zero)), sa2 = fma2s(ti.z, wab1, fma2s(ti.w, wab2, zero));
+    p2 sc1 = fma2s(ti.x, wcd1, fma2s(ti.y, wcd2, zero)), sc2 = fma2s(ti.z, wcd1, fma2s(ti.w, wcd2, zero));
+    // pass B: the TDF-II recurrence (Spectral Stabilizer.jsfx:98-111), chains AB and CD in lockstep,
     // with pass A of the next stage riding along on the fresh outputs
     const float* cf = &tb.coef[5 * sec];
-    const float b0 = cf[0], b1 = cf[1], b2 = cf[2], nd1 = cf[3], d2 = cf[4], mix = tb.coef[32];
+    const float b0 = cf[0], b1 = cf[1], b20 = cf[2], nd1 = cf[3], d2 = cf[4], mix = tb.coef[32];
     const float* hn = &tb.HA[sec + 1][0][0];
-    p2 p1 = zero, pp2 = zero, q1 = zero, q2 = zero;
+    z.ab1 = zero; z.ab2 = zero; z.cd1 = zero; z.cd2 = zero;
 #pragma unroll
-    for (int k = 0; k < kL; k += 2) {
+    for (int k = 0; k < kH; k += 2) {
         const float4 h = lds4(hn + 2 * k);             // next stage's (h1[k], h2[k], h1[k+1], h2[k+1])
 #pragma unroll
         for (int j = 0; j < 2; ++j) {
-            const p2 xx = x[k + j];
-            const p2 y = fma2s(b0, xx, st1);
-            // z1' = b1 x - a1 y + z2 = (b1 x + z2) + 2 y - d1 y ;  z2' = b2 x - a2 y = (b2 x - y) + d2 y
-            const p2 t = BP ? st2 : fma2s(b1, xx, st2);
-            st1 = fma2s(2.0f, y, fma2s(nd1, y, t));
-            st2 = fma2s(d2, y, fma2s_sub(b2, xx, y));
-            const p2 xo = BP ? fma2s(mix, y, xx) : y;
-            x[k + j] = xo;
-            if (j) { q1 = fma2s(h.z, xo, q1); q2 = fma2s(h.w, xo, q2); }
-            else   { p1 = fma2s(h.x, xo, p1); pp2 = fma2s(h.y, xo, pp2); }
+            const float h1 = j ? h.z : h.x, h2 = j ? h.w : h.y;
+            // z1' = b1 x - a1 y + z2 = (b1 x + z2) + 2 y - d1 y
+            // z2' = b2 x - a2 y = (b2 x - y) + d2 y = ((b2 - b0) x - z1) + d2 y     [y = b0 x + z1]
+            // -> every read of x[k] precedes y, so y is written in place (no register copies in the loop)
+            const p2 xa = x[k + j], xc = x[kH + k + j];
+            const p2 ta = BP ? sa2 : fma2s(b1, xa, sa2), tc = BP ? sc2 : fma2s(b1, xc, sc2);
+            const p2 ua = fma2s_sub(b20, xa, sa1), uc = fma2s_sub(b20, xc, sc1);
+            const p2 ya = fma2s(b0, xa, sa1), yc = fma2s(b0, xc, sc1);
+            sa1 = fma2s(2.0f, ya, fma2s(nd1, ya, ta)); sc1 = fma2s(2.0f, yc, fma2s(nd1, yc, tc));
+            sa2 = fma2s(d2, ya, ua); sc2 = fma2s(d2, yc, uc);
+            const p2 oa = BP ? fma2s(mix, ya, xa) : ya, oc = BP ? fma2s(mix, yc, xc) : yc;
+            x[k + j] = oa; x[kH + k + j] = oc;
+            z.ab1 = fma2s(h1, oa, z.ab1); z.ab2 = fma2s(h2, oa, z.ab2);
+            z.cd1 = fma2s(h1, oc, z.cd1); z.cd2 = fma2s(h2, oc, z.cd2);
         }
     }
-    z1 = add2(p1, q1); z2 = add2(pp2, q2);
-    // publish the exact sequential state after the tile's last valid chunk
-    const float sn1 = cx.half_last ? hi(st1) : lo(st1), sn2 = cx.half_last ? hi(st2) : lo(st2);
+    // publish the exact sequential state after the tile's last valid 32-frame chunk (B or D of thread t_last)
+    const float sn1 = cx.half_last ? hi(sc1) : hi(sa1), sn2 = cx.half_last ? hi(sc2) : hi(sa2);
     if (W == 1) {
         const float g1 = shfl_idx(sn1, cx.t_last), g2 = shfl_idx(sn2, cx.t_last);
 #pragma unroll
@@ -279,15 +311,16 @@ __device__ __forceinline__ void biquad_stage(X2Ctx<W, NBUF>& cx, p2 (&x)[kL], co
 }
 
 // ---- one one-pole stage: s += c (x - s)  (ERB Tilt.jsfx:397 and EasyExpander.jsfx:186 forms) --------
-// In: z = (zA, zB) zero-state end states of this stage; O == 0 also accumulates pass A of S8 into it.
+// In: (z.ab1, z.cd1) = zero-state end states of this stage; O == 0 also accumulates pass A of S8 into them.
 template <int W, int NBUF, int O>
-__device__ __forceinline__ void onepole_stage(X2Ctx<W, NBUF>& cx, p2 (&x)[kL], p2& z)
+__device__ __forceinline__ void onepole_stage(X2Ctx<W, NBUF>& cx, p2 (&x)[kL], ZS& z)
 {
     const C8TablesX2& tb = cx.sm->tab;
     constexpr int sec = 6 + O, ci = 12 + O;
-    const float za = lo(z), zb = hi(z);
-    const float a32 = tb.P1[O][33];
-    float c = fmaf(a32, za, zb);
+    const float zA = lo(z.ab1), zB = hi(z.ab1), zC = lo(z.cd1), zD = hi(z.cd1);
+    const float a16 = tb.P1[O][33], a32 = tb.P1[O][34];
+    const float cAB = fmaf(a16, zA, zB), cCD = fmaf(a16, zC, zD);
+    float c = fmaf(a32, cAB, cCD);
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
         const float u = shfl_up(c, d);
@@ -306,28 +339,31 @@ __device__ __forceinline__ void onepole_stage(X2Ctx<W, NBUF>& cx, p2 (&x)[kL], p
     }
     float e = shfl_up(c, 1);
     if (cx.lane == 0) e = 0;
-    const float sa = fmaf(tb.P1[O][cx.lane], s, e);
-    const float sb = fmaf(a32, sa, za);
-    p2 st = pk(sa, sb);
+    const float sA = fmaf(tb.P1[O][cx.lane], s, e);
+    const float sB = fmaf(a16, sA, zA);
+    const float sC = fmaf(a32, sA, cAB);
+    const float sD = fmaf(a16, sC, zC);
+    p2 sa = pk(sA, sB), sc = pk(sC, sD);
     const float cc = tb.coef[30 + O];
     const p2 zero = pk(0.f, 0.f);
-    p2 p = zero, q = zero, r = zero, t = zero;
+    p2 pa = zero, pc = zero, qa = zero, qc = zero;
 #pragma unroll
-    for (int k = 0; k < kL; k += 4) {
+    for (int k = 0; k < kH; k += 4) {
         float4 h = make_float4(0, 0, 0, 0);
         if (O == 0) h = lds4(&tb.HB[k]);
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            st = fma2s(cc, sub2(x[k + j], st), st);
-            x[k + j] = st;
-        }
-        if (O == 0) {
-            p = fma2s(h.x, x[k], p); q = fma2s(h.y, x[k + 1], q);
-            r = fma2s(h.z, x[k + 2], r); t = fma2s(h.w, x[k + 3], t);
+            sa = fma2s(cc, sub2(x[k + j], sa), sa); sc = fma2s(cc, sub2(x[kH + k + j], sc), sc);
+            x[k + j] = sa; x[kH + k + j] = sc;
+            if (O == 0) {
+                const float hh = j == 0 ? h.x : j == 1 ? h.y : j == 2 ? h.z : h.w;
+                if (j & 1) { qa = fma2s(hh, sa, qa); qc = fma2s(hh, sc, qc); }
+                else       { pa = fma2s(hh, sa, pa); pc = fma2s(hh, sc, pc); }
+            }
         }
     }
-    if (O == 0) z = add2(add2(p, q), add2(r, t));
-    const float sn = cx.half_last ? hi(st) : lo(st);
+    if (O == 0) { z.ab1 = add2(pa, qa); z.cd1 = add2(pc, qc); }
+    const float sn = cx.half_last ? hi(sc) : hi(sa);
     if (W == 1) cx.c[ci] = shfl_idx(sn, cx.t_last);
     else if (cx.tid == cx.t_last) cx.sm->carry[cx.par ^ 1][ci] = sn;
 }
@@ -336,21 +372,21 @@ __device__ __forceinline__ void onepole_stage(X2Ctx<W, NBUF>& cx, p2 (&x)[kL], p
 template <int W, int NBUF>
 __device__ __forceinline__ void cascade8_x2_tile(X2Ctx<W, NBUF>& cx, p2 (&x)[kL])
 {
-    p2 z1, z2;
-    pass_a0(cx.sm->tab, x, z1, z2);
+    ZS z;
+    pass_a0(cx.sm->tab, x, z);
     // S1 HP, S2 LP | S3 BP(peak) + mix, S4 BP(skirt) + mix | S5 LP, S6 HP: two loop bodies, run-time stage index
 #pragma unroll 1
     for (int g = 0; g < 3; ++g) {
         if (g == 1) {
 #pragma unroll 1
-            for (int j = 0; j < 2; ++j) biquad_stage<W, NBUF, true>(cx, x, 2 + j, z1, z2);
+            for (int j = 0; j < 2; ++j) biquad_stage<W, NBUF, true>(cx, x, 2 + j, z);
         } else {
 #pragma unroll 1
-            for (int j = 0; j < 2; ++j) biquad_stage<W, NBUF, false>(cx, x, 2 * g + j, z1, z2);
+            for (int j = 0; j < 2; ++j) biquad_stage<W, NBUF, false>(cx, x, 2 * g + j, z);
         }
     }
-    onepole_stage<W, NBUF, 0>(cx, x, z1);   // S7 (its pass A came out of S6's loop as z1)
-    onepole_stage<W, NBUF, 1>(cx, x, z1);   // S8
+    onepole_stage<W, NBUF, 0>(cx, x, z);    // S7 (its pass A came out of S6's loop)
+    onepole_stage<W, NBUF, 1>(cx, x, z);    // S8
 }
 
 __device__ __forceinline__ void tma_prefetch_3d(const CUtensorMap* map, int c0, int c1, int c2)
@@ -426,13 +462,15 @@ cascade8_x2_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_cons
         const bool live = warp_live(i);
         if (live) {
             mbar_wait(&sm->full[b][cx.warp], (uint32_t)((NBUF == 1 ? i : (i >> 1)) & 1));
-            // rows 2t (chunk A) and 2t+1 (chunk B) -> register pairs
+            // row 2t = chunks A | B, row 2t+1 = chunks C | D  ->  register pairs (A[k], B[k]), (C[k], D[k])
 #pragma unroll
-            for (int j = 0; j < kL / 4; ++j) {
-                const float4 va = lds4(tile + swz_piece(2 * cx.tid, j));
-                const float4 vb = lds4(tile + swz_piece(2 * cx.tid + 1, j));
+            for (int j = 0; j < 4; ++j) {
+                const float4 va = lds4(tile + swz_piece(2 * cx.tid, j)), vb = lds4(tile + swz_piece(2 * cx.tid, j + 4));
+                const float4 vc = lds4(tile + swz_piece(2 * cx.tid + 1, j)), vd = lds4(tile + swz_piece(2 * cx.tid + 1, j + 4));
                 x[4 * j + 0] = pk(va.x, vb.x); x[4 * j + 1] = pk(va.y, vb.y);
                 x[4 * j + 2] = pk(va.z, vb.z); x[4 * j + 3] = pk(va.w, vb.w);
+                x[kH + 4 * j + 0] = pk(vc.x, vd.x); x[kH + 4 * j + 1] = pk(vc.y, vd.y);
+                x[kH + 4 * j + 2] = pk(vc.z, vd.z); x[kH + 4 * j + 3] = pk(vc.w, vd.w);
             }
         } else {
 #pragma unroll
@@ -443,11 +481,15 @@ cascade8_x2_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_cons
 
         if (live) {
 #pragma unroll
-            for (int j = 0; j < kL / 4; ++j) {
+            for (int j = 0; j < 4; ++j) {
                 *reinterpret_cast<float4*>(tile + swz_piece(2 * cx.tid, j)) =
                     make_float4(lo(x[4 * j]), lo(x[4 * j + 1]), lo(x[4 * j + 2]), lo(x[4 * j + 3]));
-                *reinterpret_cast<float4*>(tile + swz_piece(2 * cx.tid + 1, j)) =
+                *reinterpret_cast<float4*>(tile + swz_piece(2 * cx.tid, j + 4)) =
                     make_float4(hi(x[4 * j]), hi(x[4 * j + 1]), hi(x[4 * j + 2]), hi(x[4 * j + 3]));
+                *reinterpret_cast<float4*>(tile + swz_piece(2 * cx.tid + 1, j)) =
+                    make_float4(lo(x[kH + 4 * j]), lo(x[kH + 4 * j + 1]), lo(x[kH + 4 * j + 2]), lo(x[kH + 4 * j + 3]));
+                *reinterpret_cast<float4*>(tile + swz_piece(2 * cx.tid + 1, j + 4)) =
+                    make_float4(hi(x[kH + 4 * j]), hi(x[kH + 4 * j + 1]), hi(x[kH + 4 * j + 2]), hi(x[kH + 4 * j + 3]));
             }
             fence_proxy_async();
             __syncwarp();
