@@ -122,7 +122,7 @@ ZA_API int za_gpu_launch_count(za_gpu_handle h, int64_t* kernels_launched);   /*
 /* Device time (ms, CUDA events on the handle's stream) of the dominant kernel launches of the
  * most recent za_gpu_process call, and how many launches that covers. */
 ZA_API int za_gpu_last_kernel_ms(za_gpu_handle h, double* ms, int* launches);
-/* Tuning knobs for experiments: name = "force_generic_io" | "warps_per_stream" | "host_chunk_streams" |
+/* Tuning knobs for experiments: name = "force_generic_io" | "warps_per_stream" | "host_chunk_frames" |
  * "tile_buffers" (1|2, packed fp32 kernel) | "scalar_f32" (1 = fp32 on the scalar-FFMA kernel). */
 ZA_API int za_gpu_set_option(za_gpu_handle h, const char* name, int value);
 

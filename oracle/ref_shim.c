@@ -208,6 +208,7 @@ typedef struct Job {
     const float* in; float* out; double* out_d;
     int n_streams, n_in, n_out, block; int64_t n_frames, frame_stride;
     int s0, s1;
+    double* vars_out;      /* optional [n_streams][DSPJSFX_VARS_COUNT]: st.vars after the last frame */
 } Job;
 
 static void* worker(void* arg)
@@ -254,15 +255,28 @@ static void* worker(void* arg)
             }
             pos += n; ++b;
         }
+        if (j->vars_out) memcpy(j->vars_out + (size_t)s * DSPJSFX_VARS_COUNT, z->st.vars, sizeof(double) * DSPJSFX_VARS_COUNT);
         zref_free(z);
     }
     free(zero); free(scratch);
     return NULL;
 }
 
+ZREF_API int zref_render_vars(const ZrefSliders* sl, double srate, const float* params, int n_param_blocks,
+                              const float* in, float* out, double* out_d, int n_streams, int64_t n_frames,
+                              int64_t frame_stride, int block, int n_threads, double* vars_out);
+
 ZREF_API int zref_render(const ZrefSliders* sl, double srate, const float* params, int n_param_blocks,
                          const float* in, float* out, double* out_d, int n_streams, int64_t n_frames,
                          int64_t frame_stride, int block, int n_threads)
+{
+    return zref_render_vars(sl, srate, params, n_param_blocks, in, out, out_d, n_streams, n_frames, frame_stride, block,
+                            n_threads, NULL);
+}
+
+ZREF_API int zref_render_vars(const ZrefSliders* sl, double srate, const float* params, int n_param_blocks,
+                              const float* in, float* out, double* out_d, int n_streams, int64_t n_frames,
+                              int64_t frame_stride, int block, int n_threads, double* vars_out)
 {
     if (n_threads < 1) n_threads = 1;
     if (n_threads > n_streams) n_threads = n_streams > 0 ? n_streams : 1;
@@ -273,7 +287,7 @@ ZREF_API int zref_render(const ZrefSliders* sl, double srate, const float* param
         j->sl = sl; j->srate = srate; j->params = params; j->n_param_blocks = n_param_blocks;
         j->in = in; j->out = out; j->out_d = out_d; j->n_streams = n_streams;
         j->n_in = DSPJSFX_INPUT_CHANNELS; j->n_out = DSPJSFX_OUTPUT_CHANNELS;
-        j->block = block; j->n_frames = n_frames; j->frame_stride = frame_stride;
+        j->block = block; j->n_frames = n_frames; j->frame_stride = frame_stride; j->vars_out = vars_out;
         j->s0 = (int)((int64_t)n_streams * t / n_threads);
         j->s1 = (int)((int64_t)n_streams * (t + 1) / n_threads);
         if (n_threads == 1) { worker(j); return 0; }

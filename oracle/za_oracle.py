@@ -153,7 +153,21 @@ def plugin_source_text(key: str) -> str:
     for p in (PKG / "plugins").rglob("*.jsfx"):
         if p.parent.parent.name == key:
             return p.read_text()
+    if key in CATALOG_SLIDERS:
+        return CATALOG_SLIDERS[key]
     raise KeyError(key)
+
+
+# slider declaration lines of the catalog leaves under test (their parameter API, restated from the
+# plugin sources: EasyExpander.jsfx:13-21)
+CATALOG_SLIDERS = {
+    "EasyExpander": (
+        "slider1:thresh_db=-40<-80,0,0.1>Threshold (dB)\n"
+        "slider2:depth_db=24<0,60,1>Depth (dB)\n"
+        "slider3:contour=50<0,100,1>Contour (0=gentle, 100=hard)\n"
+        "slider4:det_hpf_hz=0<0,20000,1:log=1000>Detector HPF (Hz, 0=Off)\n"
+        "slider5:det_lpf_hz=20000<20,20000,1:log=1000>Detector LPF (Hz, 20k=Off)\n"),
+}
 
 
 class RefPlugin:
@@ -177,17 +191,30 @@ class RefPlugin:
         L.zref_mem.argtypes = [C.c_void_p, C.POINTER(C.c_int64)]
         L.zref_render.argtypes = [C.POINTER(SliderLayout), C.c_double, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
                                   C.c_void_p, C.c_int, C.c_int64, C.c_int64, C.c_int, C.c_int]
+        L.zref_render_vars.argtypes = L.zref_render.argtypes + [C.c_void_p]
         self.n_in, self.n_out = L.zref_in_channels(), L.zref_out_channels()
+        self.var_cap = L.zref_var_cap()
         self.sliders = sliders if sliders is not None else parse_sliders(plugin_source_text(key))
         self.layout = make_layout(self.sliders, lambda name: L.zref_var_index(name.encode()))
         self.meta = json.loads((REF_DIR / f"{key}.json").read_text()) if (REF_DIR / f"{key}.json").exists() else {}
 
-    def render(self, params, x, srate=48000.0, block=512, want_f64=False, threads=0):
+    def render(self, params, x, srate=48000.0, block=512, want_f64=False, threads=0, want_vars=False):
         """params [n_streams,n_sliders] or [n_blocks,n_streams,n_sliders] f32; x [n_streams,n_in,n_frames] f32
-        -> (y f32 [n_streams,n_out,n_frames], y64 or None)."""
+        -> (y f32 [n_streams,n_out,n_frames], y64 or None[, {var name: final value per stream}])."""
         x = np.ascontiguousarray(x, dtype=np.float32)
         ns, nin, nf = x.shape
         assert nin == self.n_in, (nin, self.n_in)
+        if want_vars:
+            p = np.ascontiguousarray(params, dtype=np.float32)
+            npb = 1 if p.ndim == 2 else p.shape[0]
+            y = np.zeros((ns, self.n_out, nf), np.float32)
+            yd = np.zeros((ns, self.n_out, nf), np.float64) if want_f64 else None
+            vars_out = np.zeros((ns, self.var_cap), np.float64)
+            rc = self.lib.zref_render_vars(C.byref(self.layout), srate, p.ctypes.data, npb, x.ctypes.data, y.ctypes.data,
+                                           yd.ctypes.data if want_f64 else None, ns, nf, nf, block,
+                                           threads or (os.cpu_count() or 1), vars_out.ctypes.data)
+            assert rc == 0
+            return y, yd, {k: vars_out[:, i] for k, i in self.meta.get("vars", {}).items()}
         p = np.ascontiguousarray(params, dtype=np.float32)
         npb = 1 if p.ndim == 2 else p.shape[0]
         assert p.shape[-2] == ns and p.shape[-1] == len(self.sliders)

@@ -42,3 +42,7 @@ if __name__ == "__main__":
     auto[:, :, 4] *= np.linspace(1.0, 2.0, nb)[:, None]      # sweep the S3 band frequency
     auto[5:, :, 14] = 0.25                                   # and step the mix at block 5
     golden("cascade8", auto, wl.noise_two_sines(4, nb * 512 - 100), tag="_auto")
+    # EasyExpander (cfg3 shape): threshold / depth automated every block, programme-like bursts
+    ee = zo.RefPlugin("EasyExpander")
+    nf = 48000
+    golden("EasyExpander", wl.automation(ee.sliders, (nf + 511) // 512, 6, which=[0, 1]), wl.programme_bursts(6, nf), tag="_auto")

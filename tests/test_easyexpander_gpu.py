@@ -1,0 +1,145 @@
+"""GPU parity tests for the nonlinear dynamics class (plugin EasyExpander, BASELINE config 3): the CUDA
+path through the C ABI against the reference's own compiled DSP on the same seeded inputs.
+
+Criteria (BASELINE.json north_star / SURVEY.md section 8c):
+  fp64 mode: |gpu - ref| <= 1e-12 * max(|ref|, block peak) on the doubles before the float store;
+  fp32 mode: residual vs the reference render below -100 dBFS RMS (re full scale 1.0);
+  integer state (the hysteresis flag `expanding`) and the host-block positions of parameter changes: exact."""
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+import za_oracle as zo
+from za_gpu import workloads as wl
+
+pytestmark = pytest.mark.gpu
+GOLD = Path(__file__).parent / "golden"
+TOL64 = 1e-12
+
+
+def block_peak(ref, block=512):
+    ns, nc, nf = ref.shape
+    nb = (nf + block - 1) // block
+    pad = np.zeros((ns, nc, nb * block))
+    pad[:, :, :nf] = np.abs(ref)
+    pk = pad.reshape(ns, nc, nb, block).max(axis=3)
+    return np.repeat(pk, block, axis=2)[:, :, :nf]
+
+
+def rel_err(got, ref):
+    return np.abs(got - ref) / np.maximum(np.maximum(np.abs(ref), block_peak(ref)), 1e-300)
+
+
+def dbfs_rms(r):
+    return 20 * np.log10(np.sqrt(np.mean(r ** 2)) + 1e-300)
+
+
+@pytest.fixture(scope="module")
+def gpu(built_lib):
+    import za_gpu
+    if za_gpu.lib().za_gpu_device_count() < 1:
+        pytest.fail("GPU test run without a CUDA device")
+    return za_gpu
+
+
+@pytest.fixture(scope="module")
+def ref():
+    return zo.RefPlugin("EasyExpander")
+
+
+def make_case(ref, ns, nf, automate, detector_filters=False, block=512):
+    x = wl.programme_bursts(ns, nf)
+    nb = (nf + block - 1) // block
+    base = np.array([s["default"] for s in ref.sliders], np.float32)
+    if detector_filters:
+        base[3], base[4] = 120.0, 6000.0
+    if automate:
+        p = wl.automation(ref.sliders, nb, ns, which=[0, 1], base=base)     # threshold and depth move every block
+    else:
+        p = np.tile(base, (ns, 1))
+    return p, x
+
+
+@pytest.mark.parametrize("automate,filters,ns,nf", [(False, False, 21, 48000 + 13), (True, False, 16, 48000 * 2 + 5),
+                                                    (True, True, 7, 30000)])
+def test_fp64_parity_and_state(gpu, ref, automate, filters, ns, nf):
+    p, x = make_case(ref, ns, nf, automate, filters)
+    y, yd, v = ref.render(p, x, want_f64=True, want_vars=True)
+    bp = gpu.BatchProcessor("EasyExpander", ns, precision="f64").prepare(p if p.ndim == 2 else p[0])
+    tap = np.zeros_like(yd)
+    out = bp.process(x, tap64=tap, params=p if p.ndim == 3 else None)
+    e = rel_err(tap, yd).max()
+    assert e <= TOL64, e
+    assert np.mean(out == y) > 0.9999
+    assert np.array_equal(bp.read_state("expanding"), v["expanding"])        # integer state: exact
+    for name in ("gain_db_s", "det_slow", "det_db_m", "gr_db_m", "hpf_lp", "lpf_y"):
+        got, want = bp.read_state(name), v[name]
+        assert np.abs(got - want).max() <= 1e-11 * max(1.0, np.abs(want).max()), name
+    bp.close()
+
+
+def test_split_calls_match_one_shot(gpu, ref):
+    """State carries across calls; a call boundary on a host-block boundary keeps the block grid."""
+    ns, nf = 9, 512 * 40 + 77
+    p, x = make_case(ref, ns, nf, True)
+    y, yd = ref.render(p, x, want_f64=True)
+    bp = gpu.BatchProcessor("EasyExpander", ns, precision="f64").prepare(p[0])
+    tap = np.zeros_like(yd)
+    for a, b in ((0, 512 * 3), (512 * 3, 512 * 17), (512 * 17, nf)):
+        t = np.zeros((ns, 2, b - a))
+        bp.process(np.ascontiguousarray(x[:, :, a:b]), tap64=t, params=p[a // 512:])
+        tap[:, :, a:b] = t
+    assert rel_err(tap, yd).max() <= TOL64
+    bp.close()
+
+
+def test_fp32_mode_residual(gpu, ref):
+    ns, nf = 16, 48000 * 2
+    p, x = make_case(ref, ns, nf, True)
+    y, yd = ref.render(p, x, want_f64=True)
+    bp = gpu.BatchProcessor("EasyExpander", ns, precision="f32").prepare(p[0])
+    out = bp.process(x, params=p)
+    r = out.astype(np.float64) - yd
+    per_stream = np.array([dbfs_rms(r[s]) for s in range(ns)])
+    print("fp32 residual dBFS rms per stream: min %.1f median %.1f max %.1f" % (per_stream.min(), np.median(per_stream), per_stream.max()))
+    assert per_stream.max() < -100.0, per_stream.max()
+    bp.close()
+
+
+def test_matches_golden_from_reference(gpu):
+    g = np.load(GOLD / "EasyExpander_auto.npz")
+    ns, nf, block = int(g["n_streams"]), int(g["n_frames"]), int(g["block"])
+    x = wl.programme_bursts(ns, nf)
+    p = g["params"]
+    bp = gpu.BatchProcessor("EasyExpander", ns, block_len=block, precision="f64").prepare(p[0])
+    tap = np.zeros((ns, 2, nf))
+    bp.process(x, tap64=tap, params=p)
+    n = g["y64_head"].shape[-1]
+    for got, want in ((tap[:, :, :n], g["y64_head"]), (tap[:, :, -n:], g["y64_tail"])):
+        assert (np.abs(got - want) <= TOL64 * np.maximum(np.abs(want), np.abs(want).max(axis=2, keepdims=True))).all()
+    assert np.allclose(np.abs(tap).sum(axis=2), g["y64_abs_sum"], rtol=1e-11, atol=0)
+    bp.close()
+
+
+def test_device_buffers_large_batch(gpu, ref):
+    """4096 stereo streams x 1 s from device buffers (cfg3 shape), 10 streams re-rendered by the reference."""
+    torch = pytest.importorskip("torch")
+    ns, nf = 4096, 48000
+    gsel = np.random.default_rng(3).choice(ns, 10, replace=False)
+    xs = wl.programme_bursts(10, nf, first_stream=500)
+    x = torch.zeros((ns, 2, nf), dtype=torch.float32, device="cuda")
+    x[:] = torch.from_numpy(xs[0]).cuda()
+    for i, s in enumerate(gsel):
+        x[int(s)] = torch.from_numpy(xs[i]).cuda()
+    nb = (nf + 511) // 512
+    p = wl.automation(ref.sliders, nb, ns, which=[0, 1])
+    bp = gpu.BatchProcessor("EasyExpander", ns, precision="f64").prepare(p[0])
+    torch.cuda.synchronize()
+    y = bp.process(x, params=p)
+    bp.sync()
+    yr, _ = ref.render(np.ascontiguousarray(p[:, gsel]), xs)
+    got = y[torch.from_numpy(gsel).cuda()].cpu().numpy()
+    assert np.mean(got == yr) > 0.9999
+    assert np.abs(got.astype(np.float64) - yr).max() <= 2.0 ** -22 * np.abs(yr).max()
+    bp.close()

@@ -69,3 +69,18 @@ def test_quantiser_numpy_vs_c():
     # the grid is float-min + k*float-step widened to double (src/JSFXJuceProcessor.cpp:5583-5594)
     s = port.sliders[0]
     assert s["step"] == float(np.float32(0.01)) and s["step"] != 0.01
+
+
+@pytest.mark.skipif(not zo.have_ref("EasyExpander"), reason="oracle/_ref not built (needs /root/reference)")
+def test_easyexpander_reference_build_matches_golden():
+    """The reference's compiled EasyExpander behind oracle/ref_shim.c reproduces the committed fixture
+    (guards the shim: slider quantisation, block grid, prepare order)."""
+    g = np.load(GOLD / "EasyExpander_auto.npz")
+    ns, nf = int(g["n_streams"]), int(g["n_frames"])
+    x = wl.programme_bursts(ns, nf)
+    assert np.array_equal(sha(x), g["x_sha256"]), "seeded input generator drifted"
+    y, yd, v = zo.RefPlugin("EasyExpander").render(g["params"], x, block=int(g["block"]), want_f64=True, threads=2,
+                                                    want_vars=True)
+    assert np.array_equal(sha(yd), g["y64_sha256"])
+    assert np.array_equal(sha(y), g["y32_sha256"])
+    assert set(np.unique(v["expanding"])) <= {0.0, 1.0}

@@ -62,11 +62,13 @@ bool make_chunk_tensor_map(CUtensorMap* map, const float* base, int64_t n_chunks
 
 // ---- catalogue ----------------------------------------------------------------------------------
 const char* cascade8_slider_text();
+const char* easyexpander_slider_text();
 
 const std::vector<PluginDesc>& plugin_table()
 {
     static const std::vector<PluginDesc> t = {
         {"cascade8", 1, 1, 2, 0, cascade8_slider_text(), &make_cascade8},
+        {"EasyExpander", 2, 2, 0, 0, easyexpander_slider_text(), &make_easyexpander},
     };
     return t;
 }
@@ -105,6 +107,22 @@ static bool process_range(Instance& I, const float* params, int n_param_blocks, 
     const int nd = (int)I.decls.size();
     const int64_t bl = I.block_len;
     const int64_t n_blocks = (n_frames + bl - 1) / bl;
+    if (I.impl->takes_block_params()) {
+        // quantise the whole automation trajectory once (pushParamsToStateSliders per host block, :9286-9357)
+        const int nbq = (params && n_param_blocks > 0) ? (int)std::min<int64_t>(n_param_blocks, n_blocks) : 1;
+        std::vector<double> q((size_t)nbq * ns * nd);
+        for (int b = 0; b < nbq; ++b)
+            for (int s = 0; s < ns; ++s)
+                for (int j = 0; j < nd; ++j)
+                    q[((size_t)b * ns + s) * nd + j] = (params && n_param_blocks > 0)
+                        ? quantise_slider(I.decls[j], params[((size_t)b * I.n_streams + s0 + s) * nd + j])
+                        : I.sliders[(size_t)(s0 + s) * nd + j];
+        for (int s = 0; s < ns; ++s) {
+            for (int j = 0; j < nd; ++j) I.sliders[(size_t)(s0 + s) * nd + j] = q[((size_t)(nbq - 1) * ns + s) * nd + j];
+            I.sliders_valid[s0 + s] = 1;
+        }
+        return I.impl->run_blocks(I, s0, ns, q.data(), nbq, in, out, tap, n_frames, stride);
+    }
     std::vector<int> changed;
     int64_t run_start = 0;     // first frame of the pending run
     for (int64_t b = 0; b < n_blocks; ++b) {
@@ -146,33 +164,38 @@ static void free_staging(Instance& I)
         cudaFree(I.stage_in[i]); cudaFree(I.stage_out[i]); cudaFree(I.stage_tap[i]);
         I.stage_in[i] = I.stage_out[i] = nullptr; I.stage_tap[i] = nullptr;
     }
-    I.stage_in_bytes = I.stage_out_bytes = I.stage_tap_bytes = 0;
+    I.stage_in_bytes = I.stage_out_bytes = I.stage_tap_bytes = 0; I.stage_stride = 0;
 }
 
-// Host buffers: stream chunks flow H2D -> kernels -> D2H through three staging slots on three CUDA
-// streams, so PCIe traffic in both directions overlaps the kernels.
+// Host buffers: TIME chunks of all streams flow H2D -> kernels -> D2H through three staging slots on
+// three CUDA streams, so PCIe traffic in both directions overlaps the kernels.  Chunks are whole host
+// blocks (the block grid of the call is kept) and every chunk launches over all streams, so the
+// kernels see the same grid shapes as a device-resident render; state carries from chunk to chunk.
 static bool process_host(Instance& I, const float* params, int npb, const float* in, float* out, double* tap,
                          int64_t n_frames, int64_t stride)
 {
-    const int n_in = I.desc->n_in, n_out = I.desc->n_out;
-    const int64_t dstride = (n_frames + 31) / 32 * 32;                 // device rows stay TMA-aligned
-    int cs = I.opt_host_chunk;
-    if (cs <= 0) {
-        const int64_t per_stream = dstride * 4 * (n_in + n_out) + (tap ? dstride * 8 * n_out : 0);
-        cs = (int)std::max<int64_t>(1, std::min<int64_t>(I.n_streams, (256ll << 20) / std::max<int64_t>(per_stream, 1)));
-        if (cs >= 8) cs &= ~7;
+    const int n_in = I.desc->n_in, n_out = I.desc->n_out, nd = (int)I.decls.size();
+    const int64_t bl = I.block_len;
+    int64_t cf;                                                        // frames per chunk
+    if (I.opt_host_chunk > 0) {
+        cf = (int64_t)I.opt_host_chunk;
+    } else {
+        const int64_t per_frame = (int64_t)I.n_streams * (4 * (n_in + n_out) + (tap ? 8 * n_out : 0));
+        cf = (384ll << 20) / std::max<int64_t>(per_frame, 1);
     }
-    cs = std::min(cs, I.n_streams);
-    const size_t need_in = (size_t)cs * n_in * dstride * 4, need_out = (size_t)cs * n_out * dstride * 4;
-    const size_t need_tap = tap ? (size_t)cs * n_out * dstride * 8 : 0;
-    if (need_in > I.stage_in_bytes || need_out > I.stage_out_bytes || need_tap > I.stage_tap_bytes) {
+    cf = std::max<int64_t>(bl, cf / bl * bl);
+    cf = std::min<int64_t>(cf, (n_frames + bl - 1) / bl * bl);
+    const int64_t dstride = (cf + 31) / 32 * 32;                       // device rows stay TMA-aligned
+    const size_t need_in = (size_t)I.n_streams * n_in * dstride * 4, need_out = (size_t)I.n_streams * n_out * dstride * 4;
+    const size_t need_tap = tap ? (size_t)I.n_streams * n_out * dstride * 8 : 0;
+    if (need_in > I.stage_in_bytes || need_out > I.stage_out_bytes || need_tap > I.stage_tap_bytes || dstride != I.stage_stride) {
         free_staging(I);
         for (int i = 0; i < 3; ++i) {
             if (!cuda_ok(cudaMalloc(&I.stage_in[i], need_in), "staging in")) return false;
             if (!cuda_ok(cudaMalloc(&I.stage_out[i], need_out), "staging out")) return false;
             if (need_tap && !cuda_ok(cudaMalloc(&I.stage_tap[i], need_tap), "staging tap")) return false;
         }
-        I.stage_in_bytes = need_in; I.stage_out_bytes = need_out; I.stage_tap_bytes = need_tap;
+        I.stage_in_bytes = need_in; I.stage_out_bytes = need_out; I.stage_tap_bytes = need_tap; I.stage_stride = dstride;
     }
     if (!I.h2d) {
         if (!cuda_ok(cudaStreamCreateWithFlags(&I.h2d, cudaStreamNonBlocking), "h2d stream")) return false;
@@ -184,24 +207,31 @@ static bool process_host(Instance& I, const float* params, int npb, const float*
         }
     }
     int c = 0;
-    for (int s0 = 0; s0 < I.n_streams; s0 += cs, ++c) {
-        const int ns = std::min(cs, I.n_streams - s0), slot = c % 3;
+    for (int64_t f0 = 0; f0 < n_frames; f0 += cf, ++c) {
+        const int64_t nf = std::min<int64_t>(cf, n_frames - f0);
+        const int slot = c % 3;
         if (c >= 3) cudaStreamWaitEvent(I.h2d, I.ev_d2h[slot], 0);     // slot drained
-        if (!cuda_ok(cudaMemcpy2DAsync(I.stage_in[slot], dstride * 4, in + (size_t)s0 * n_in * stride, stride * 4,
-                                       n_frames * 4, (size_t)ns * n_in, cudaMemcpyHostToDevice, I.h2d), "H2D"))
+        if (!cuda_ok(cudaMemcpy2DAsync(I.stage_in[slot], dstride * 4, in + f0, stride * 4, nf * 4,
+                                       (size_t)I.n_streams * n_in, cudaMemcpyHostToDevice, I.h2d), "H2D"))
             return false;
         cudaEventRecord(I.ev_h2d[slot], I.h2d);
         cudaStreamWaitEvent(I.stream, I.ev_h2d[slot], 0);
-        if (!process_range(I, params, npb, s0, ns, I.stage_in[slot], I.stage_out[slot], tap ? I.stage_tap[slot] : nullptr,
-                           n_frames, dstride))
+        if (c >= 3) cudaStreamWaitEvent(I.stream, I.ev_d2h[slot], 0);  // its previous output has left
+        // automation rows of this chunk: row b of the call applies to host block b (the last row persists)
+        const int64_t b0 = f0 / bl;
+        const float* p = nullptr;
+        int np = 0;
+        if (params && npb > 0 && b0 < npb) { p = params + (size_t)b0 * I.n_streams * nd; np = (int)(npb - b0); }
+        if (!process_range(I, p, np, 0, I.n_streams, I.stage_in[slot], I.stage_out[slot], tap ? I.stage_tap[slot] : nullptr,
+                           nf, dstride))
             return false;
         cudaEventRecord(I.ev_comp[slot], I.stream);
         cudaStreamWaitEvent(I.d2h, I.ev_comp[slot], 0);
-        if (!cuda_ok(cudaMemcpy2DAsync(out + (size_t)s0 * n_out * stride, stride * 4, I.stage_out[slot], dstride * 4,
-                                       n_frames * 4, (size_t)ns * n_out, cudaMemcpyDeviceToHost, I.d2h), "D2H"))
+        if (!cuda_ok(cudaMemcpy2DAsync(out + f0, stride * 4, I.stage_out[slot], dstride * 4, nf * 4,
+                                       (size_t)I.n_streams * n_out, cudaMemcpyDeviceToHost, I.d2h), "D2H"))
             return false;
-        if (tap && !cuda_ok(cudaMemcpy2DAsync(tap + (size_t)s0 * n_out * stride, stride * 8, I.stage_tap[slot], dstride * 8,
-                                              n_frames * 8, (size_t)ns * n_out, cudaMemcpyDeviceToHost, I.d2h), "D2H tap"))
+        if (tap && !cuda_ok(cudaMemcpy2DAsync(tap + f0, stride * 8, I.stage_tap[slot], dstride * 8, nf * 8,
+                                              (size_t)I.n_streams * n_out, cudaMemcpyDeviceToHost, I.d2h), "D2H tap"))
             return false;
         cudaEventRecord(I.ev_d2h[slot], I.d2h);
     }
@@ -426,7 +456,7 @@ ZA_API int za_gpu_set_option(za_gpu_handle h, const char* name, int value)
     Instance& I = h->I;
     if (!std::strcmp(name, "force_generic_io")) I.opt_force_generic = value;
     else if (!std::strcmp(name, "warps_per_stream")) I.opt_warps = value;
-    else if (!std::strcmp(name, "host_chunk_streams")) I.opt_host_chunk = value;
+    else if (!std::strcmp(name, "host_chunk_frames")) I.opt_host_chunk = value;
     else if (!std::strcmp(name, "tile_buffers")) I.opt_nbuf = value;
     else if (!std::strcmp(name, "scalar_f32")) I.opt_scalar_f32 = value;
     else { set_error(std::string("unknown option ") + name); return ZA_ERR_ARG; }

@@ -36,6 +36,12 @@ public:
     virtual bool run(Instance& inst, int s0, int ns, const float* in, float* out, double* tap,
                      int64_t n, int64_t stride) = 0;
     virtual bool read_state(Instance& inst, const char* name, double* out) = 0;
+    // Whole-call form for plugins that take per-block automation on the device: q = quantised slider
+    // values [nbq][ns][n_decl] (host doubles, stream range s0..s0+ns), row b applies from host block b on,
+    // the last row persists.  One launch renders all n frames; @slider semantics (recompute derived
+    // coefficients when a value changed, src/JSFXJuceProcessor.cpp:3545-3547) are the plugin's job.
+    virtual bool takes_block_params() const { return false; }
+    virtual bool run_blocks(Instance&, int, int, const double*, int, const float*, float*, double*, int64_t, int64_t) { return false; }
 };
 
 struct PluginDesc {
@@ -71,9 +77,11 @@ struct Instance {
     float* stage_out[3] = {nullptr, nullptr, nullptr};
     double* stage_tap[3] = {nullptr, nullptr, nullptr};
     size_t stage_in_bytes = 0, stage_out_bytes = 0, stage_tap_bytes = 0;
+    int64_t stage_stride = 0;
     cudaEvent_t ev_h2d[3] = {}, ev_comp[3] = {}, ev_d2h[3] = {};
 };
 
 PluginImpl* make_cascade8();
+PluginImpl* make_easyexpander();
 
 }  // namespace za

@@ -48,4 +48,25 @@ bool cascade8_x2_build_tables(const double* d_coef, void* d_tables, int n_stream
 bool cascade8_x2_launch(const C8Launch& a);
 void cascade8_x2_pick(int n_streams, int device, int* warps, int* nbuf);
 
+// ---- EasyExpander (nonlinear dynamics class) -----------------------------------------------------
+constexpr int kEEState = 32;     // per stream: ic1[8], ic2[8], env[8], hpf_lp, lpf_y, det_slow, expanding,
+                                 // gain_db_s, det_db_m, gr_db_m, pad; stored [var][stream] (double)
+struct EEConsts {                // @init results (EasyExpander.jsfx:27-171), identical for all streams
+    double g[8], k[8], den[8], w[8];
+    double band_c, open_c, close_fast_c, close_slow_c, slow_c;
+};
+struct EECoef {                  // @slider results (:154-170) of one stream for one host block
+    double thresh_db, depth_db, ratio_base, hpf_c, lpf_c;
+    int hpf_on, lpf_on;
+};
+struct EEArgs {
+    const float* in; float* out; double* tap;      // [stream][2][row_stride]
+    int64_t row_stride, n_frames;
+    int n_streams, block_len, n_coef_blocks;
+    const EECoef* coef;                            // [n_coef_blocks][n_streams]
+    double* state;                                 // [kEEState][n_streams]
+    EEConsts k;
+};
+bool easyexpander_launch(const EEArgs& a, int precision, cudaStream_t stream);
+
 }  // namespace za
