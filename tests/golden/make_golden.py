@@ -45,4 +45,7 @@ if __name__ == "__main__":
     # EasyExpander (cfg3 shape): threshold / depth automated every block, programme-like bursts
     ee = zo.RefPlugin("EasyExpander")
     nf = 48000
+    st = zo.RefPlugin("stft_mask2048")
+    nfs = 24000 + 77
+    golden("stft_mask2048", wl.automation(st.sliders, (nfs + 511) // 512, 3, which=[0, 1, 4]), wl.programme_bursts(3, nfs), tag="_auto")
     golden("EasyExpander", wl.automation(ee.sliders, (nf + 511) // 512, 6, which=[0, 1]), wl.programme_bursts(6, nf), tag="_auto")

@@ -84,3 +84,20 @@ def test_easyexpander_reference_build_matches_golden():
     assert np.array_equal(sha(yd), g["y64_sha256"])
     assert np.array_equal(sha(y), g["y32_sha256"])
     assert set(np.unique(v["expanding"])) <= {0.0, 1.0}
+
+
+@pytest.mark.skipif(not zo.have_ref("stft_mask2048"), reason="oracle/_ref not built (needs /root/reference)")
+def test_stft_reference_build_matches_golden_and_reconstructs():
+    """The authored STFT workload through the reference's compiler + WDL FFT hooks (oracle/ref_fft_hooks.c):
+    reproduces the committed fixture, and with amount = 0 is a pure 2048-frame delay (window/OLA contract)."""
+    g = np.load(GOLD / "stft_mask2048_auto.npz")
+    ns, nf = int(g["n_streams"]), int(g["n_frames"])
+    x = wl.programme_bursts(ns, nf)
+    ref = zo.RefPlugin("stft_mask2048")
+    y, yd = ref.render(g["params"], x, block=int(g["block"]), want_f64=True, threads=2)
+    assert np.array_equal(sha(yd), g["y64_sha256"])
+    p0 = g["params"][0].copy()
+    p0[:, 0] = 0
+    y0, yd0, v = ref.render(p0, x, want_f64=True, want_vars=True)
+    assert np.abs(yd0[:, :, 2048:] - x[:, :, :-2048]).max() < 1e-14
+    assert np.array_equal(v["frames_done"], np.full(ns, nf // 512, np.float64))

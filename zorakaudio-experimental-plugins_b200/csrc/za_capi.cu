@@ -63,12 +63,14 @@ bool make_chunk_tensor_map(CUtensorMap* map, const float* base, int64_t n_chunks
 // ---- catalogue ----------------------------------------------------------------------------------
 const char* cascade8_slider_text();
 const char* easyexpander_slider_text();
+const char* stft_mask2048_slider_text();
 
 const std::vector<PluginDesc>& plugin_table()
 {
     static const std::vector<PluginDesc> t = {
         {"cascade8", 1, 1, 2, 0, cascade8_slider_text(), &make_cascade8},
         {"EasyExpander", 2, 2, 0, 0, easyexpander_slider_text(), &make_easyexpander},
+        {"stft_mask2048", 2, 2, 2, 2048, stft_mask2048_slider_text(), &make_stft_mask2048},
     };
     return t;
 }

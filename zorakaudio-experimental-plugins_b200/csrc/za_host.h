@@ -83,5 +83,6 @@ struct Instance {
 
 PluginImpl* make_cascade8();
 PluginImpl* make_easyexpander();
+PluginImpl* make_stft_mask2048();
 
 }  // namespace za

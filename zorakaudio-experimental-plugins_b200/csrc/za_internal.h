@@ -69,4 +69,26 @@ struct EEArgs {
 };
 bool easyexpander_launch(const EEArgs& a, int precision, cudaStream_t stream);
 
+// ---- stft_mask2048 (STFT class) ---------------------------------------------------------------------
+constexpr int kStftN = 2048, kStftHop = 512, kStftBins = 1025;
+struct StftState {               // per stream, persists across calls (the reference keeps these in mem[])
+    float xin[2][5 * kStftHop];  // last five hops of input (slot = absolute hop index mod 5)
+    double acc[2][kStftN];       // overlap-add accumulator (slot = absolute hop index mod 4)
+    double base[kStftBins + 3];  // per-bin baseline EMA
+    double prev[kStftBins + 3];  // per-bin previous magnitude
+};
+struct StftCoef {                // @slider results of one stream for one host block
+    double amt, thresh, ab, bb, floor_g, mixv;
+};
+struct StftArgs {
+    const float* in; float* out; double* tap;      // [stream][2][row_stride]
+    int64_t row_stride, n_frames, t0;              // t0 = frames rendered since prepare (hop phase)
+    int n_streams, block_len, n_coef_blocks;
+    const StftCoef* coef;                          // [n_coef_blocks][n_streams]
+    StftState* state;                              // [n_streams]
+    const double* win; const double* syn; const double* tw;    // [2048], [2048], [1024][2]
+};
+size_t stft_state_bytes();
+bool stft_launch(const StftArgs& a, int precision, cudaStream_t stream);
+
 }  // namespace za
