@@ -1,17 +1,19 @@
 #!/usr/bin/env python3
 """bench.py -- BASELINE.json metric on the B200 batch renderer.
 
-Workload at N=1 (BASELINE config 2, `configs[1]`): plugin `cascade8` (8-section biquad/one-pole EQ
-cascade), 1024 mono streams x 60 s at 48 kHz = 2.949e9 sample-frames per step, float32 planar I/O,
-per-stream seeded parameters.  One step = one za_gpu_process() pass over the whole batch (state
-carries from step to step, as in a continuing render).  N>1: every rank renders its own 1024
-streams on its own GPU (streams shard, no collective on the data path) -> weak scaling.
+Default workload at N=1 (BASELINE config 2, `configs[1]`, the one the metric is quoted on): plugin
+`cascade8` (8-section biquad/one-pole EQ cascade), 1024 mono streams x 60 s at 48 kHz = 2.949e9
+sample-frames per step, float32 planar I/O, per-stream seeded parameters.  One step = one
+za_gpu_process() pass over the whole batch (state carries from step to step, as in a continuing
+render).  N>1: every rank renders its own batch on its own GPU (streams shard, no collective on the
+data path) -> weak scaling.  `--workload cfg3|cfg4` runs the same contract on the other single-GPU
+configs (EasyExpander 4096 stereo x 60 s with per-block automation; stft_mask2048 512 stereo x 120 s).
 
   value     frames/s with inputs resident in HBM (CUDA events around K back-to-back steps)
   e2e       the same metric through the C ABI with HOST buffers: pinned input -> H2D -> kernels ->
             D2H -> pinned output inside the timed region (za_gpu_process(..., ZA_MEM_HOST))
-  roofline  algorithmic bytes (8 B per mono frame: 4 in + 4 out) / dominant-kernel time measured
-            with CUDA events inside the timed region, against MEASURED_PEAKS.json hbm_gbs
+  roofline  algorithmic bytes (4 B x (in + out channels) per frame) / dominant-kernel
+            time measured with CUDA events inside the timed region, against MEASURED_PEAKS.json hbm_gbs
   cpu_baseline  the reference's own compiled DSP-JSFX object (oracle/_ref, else the pinned C port)
             multithreaded over a bounded sample of the same workload on this box's host cores
 
@@ -34,11 +36,20 @@ REPO = Path(__file__).resolve().parent
 sys.path.insert(0, str(REPO / "zorakaudio-experimental-plugins_b200"))
 
 SRATE = 48000.0
-N_STREAMS = 1024
-SECONDS = 60
-BYTES_PER_FRAME = 8           # mono float32 in + out
-CPU_SAMPLE_STREAMS = 1024     # bounded CPU sample: all 1024 streams x 20 s (a third of the workload)
-CPU_SAMPLE_SECONDS = 20.0
+
+# name -> plugin, streams per GPU, seconds, channels in/out, automated slider columns, CPU sample (streams, seconds), kernel
+WORKLOADS = {
+    "cfg2": dict(plugin="cascade8", streams=1024, seconds=60.0, ch=(1, 1), automate=None, cpu=(1024, 20.0),
+                 kernel={"f32": "cascade8_x2_kernel", "f64": "cascade8_kernel"},
+                 text="cfg2: cascade8 (8-section biquad/one-pole cascade), {ns} mono streams x {sec:g} s @ 48 kHz per GPU"),
+    "cfg3": dict(plugin="EasyExpander", streams=4096, seconds=60.0, ch=(2, 2), automate=[0, 1], cpu=(256, 10.0),
+                 kernel={"f32": "easyexpander_kernel", "f64": "easyexpander_kernel"},
+                 text="cfg3: EasyExpander (nonlinear envelope + gain computer), {ns} stereo streams x {sec:g} s @ 48 kHz per GPU, "
+                      "threshold/depth automated every 512-frame block, in-place buffers"),
+    "cfg4": dict(plugin="stft_mask2048", streams=512, seconds=120.0, ch=(2, 2), automate=None, cpu=(64, 10.0),
+                 kernel={"f32": "stft_mask_kernel", "f64": "stft_mask_kernel"},
+                 text="cfg4: stft_mask2048 (2048-pt Hann STFT, hop 512, per-bin gain, overlap-add), {ns} stereo streams x {sec:g} s @ 48 kHz per GPU"),
+}
 
 
 def peaks():
@@ -52,7 +63,7 @@ def peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    """nvidia-smi clocks / throttle reasons sampled every 100 ms while the timed region runs."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
@@ -63,7 +74,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "200", "-i", str(self.idx)], stdout=subprocess.PIPE, text=True)
+                                          "-lms", "100", "-i", str(self.idx)], stdout=subprocess.PIPE, text=True)
             threading.Thread(target=self._read, daemon=True).start()
         except Exception:
             self.proc = None
@@ -75,7 +86,7 @@ class ClockSampler:
     def stop(self):
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.25)
+        time.sleep(0.15)
         self.proc.terminate()
         sm = [float(r[1]) for r in self.rows if len(r) >= 8 and r[1].replace(".", "").isdigit()]
         mx = [float(r[2]) for r in self.rows if len(r) >= 8 and r[2].replace(".", "").isdigit()]
@@ -85,47 +96,108 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(sm)}
 
 
-def cpu_reference_run(n_streams: int, seconds: float, threads: int):
+def workload_params(W, ns, nf, first_stream=0):
+    """Static [ns][n_sliders] parameters, or the per-block automation [n_blocks][ns][n_sliders] (host float32)."""
+    import za_gpu
+    from za_gpu import workloads as wl
+    base = wl.default_params(W["plugin"], ns, first_stream)
+    if not W["automate"]:
+        return base
+    sl = [dict(default=float(s.def_), min=float(s.min), max=float(s.max)) for s in za_gpu.slider_layout(W["plugin"])]
+    nb = (nf + 511) // 512
+    # trajectories of 64 seeded streams, tiled over the batch (the generator is a per-stream Python loop)
+    k = min(ns, 64)
+    a = wl.automation(sl, nb, k, which=W["automate"], first_stream=first_stream, base=base[0])
+    return np.ascontiguousarray(np.tile(a, (1, (ns + k - 1) // k, 1))[:, :ns])
+
+
+def host_input(W, n_streams, nf, first_stream=0):
+    """Seeded host input of the workload's shape for the CPU legs: 8 generated streams tiled over the batch."""
+    from za_gpu import workloads as wl
+    k = min(n_streams, 8)
+    if W["plugin"] == "cascade8":
+        x = wl.noise_two_sines(k, nf, first_stream)
+    else:
+        x = wl.programme_bursts(k, nf, first_stream, n_ch=W["ch"][0])
+    return np.ascontiguousarray(np.tile(x, ((n_streams + k - 1) // k, 1, 1))[:n_streams])
+
+
+def cpu_reference_run(W, n_streams: int, seconds: float, threads: int):
     """Reference CPU path on a bounded sample of the workload -> (frames/s, kind, seconds taken)."""
     sys.path.insert(0, str(REPO / "oracle"))
     import za_oracle as zo
-    from za_gpu import workloads as wl
-    orc = zo.best_oracle("cascade8")
+    orc = zo.best_oracle(W["plugin"])
     kind = "reference" if isinstance(orc, zo.RefPlugin) else "port"
     nf = int(seconds * SRATE)
-    p, x = wl.cascade8_params(n_streams), wl.noise_two_sines(min(n_streams, 8), nf)
-    x = np.ascontiguousarray(np.tile(x, ((n_streams + x.shape[0] - 1) // x.shape[0], 1, 1))[:n_streams])
-    orc.render(p[:threads], x[:threads, :, :4800], threads=threads)          # warm
+    p = workload_params(W, n_streams, nf)
+    x = host_input(W, n_streams, nf)
+    orc.render(p[..., :threads, :] if p.ndim == 3 else p[:threads], x[:threads, :, :4800], threads=threads)          # warm
     t0 = time.perf_counter()
     orc.render(p, x, block=512, threads=threads)
     dt = time.perf_counter() - t0
     return n_streams * nf / dt, kind, dt
 
 
-def run_reference_arm(args):
+def workload_text(W, ns, sec):
+    return W["text"].format(ns=ns, sec=sec)
+
+
+def run_reference_arm(args, W):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     threads = os.cpu_count() or 1
-    ns, secs = CPU_SAMPLE_STREAMS, CPU_SAMPLE_SECONDS
+    ns, secs = W["cpu"]
     vals = []
     for i in range(args.warmup + args.steps):
-        v, kind, dt = cpu_reference_run(ns, secs, threads)
+        v, kind, dt = cpu_reference_run(W, ns, secs, threads)
         if i >= args.warmup:
             vals.append((v, dt))
     v = float(np.mean([a for a, _ in vals]))
-    sample = f"{ns} streams x {secs:.0f} s per step (of {N_STREAMS} x {SECONDS} s), block 512, FTZ/DAZ on"
+    sample = f"{ns} streams x {secs:g} s per step (of {W['streams']} x {W['seconds']:g} s), block 512, FTZ/DAZ on"
     line = {
         "impl": "reference", "metric": "aggregate sample-frames/s", "value": v, "unit": "frames/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": float(np.mean([d for _, d in vals]) * 1e3),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "x_realtime": v / SRATE,
-        "config": {"workload": "cfg2: cascade8 (8-section biquad/one-pole cascade), 1024 mono streams x 60 s @ 48 kHz",
-                   "sample": sample},
+        "config": {"workload": workload_text(W, W["streams"], W["seconds"]), "sample": sample},
         "cpu_baseline": {"value": v, "unit": "frames/s", "cores": threads, "kind": kind, "sample": sample},
         "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
+
+
+def device_input(torch, W, ns, nf, seed):
+    """Synthetic input generated on the device, [ns][ch][nf] float32.
+    cascade8: uniform noise x0.25 + two sines per stream; dynamics / STFT: noise under a slow random
+    envelope (-60..-6 dBFS in 50 ms knots) so gain computers traverse knee and hysteresis."""
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    nch = W["ch"][0]
+    x = torch.empty((ns, nch, nf), dtype=torch.float32, device="cuda")
+    step = max(1, (256 << 20) // (nch * nf * 4))
+    if W["plugin"] == "cascade8":
+        t = torch.arange(nf, device="cuda", dtype=torch.float32) / SRATE
+        f = torch.rand((ns, 2), device="cuda", generator=g)
+        for s0 in range(0, ns, step):
+            s1 = min(ns, s0 + step)
+            blk = (torch.rand((s1 - s0, 1, nf), device="cuda", generator=g) - 0.5) * 0.5
+            f1 = (60.0 + 340.0 * f[s0:s1, 0]).view(-1, 1, 1)
+            f2 = (1000.0 + 5000.0 * f[s0:s1, 1]).view(-1, 1, 1)
+            blk += 0.125 * torch.sin(2 * np.pi * f1 * t) + 0.125 * torch.sin(2 * np.pi * f2 * t)
+            x[s0:s1] = blk
+    else:
+        seg = 2400
+        nk = nf // seg + 2
+        for s0 in range(0, ns, step):
+            s1 = min(ns, s0 + step)
+            knots = torch.rand((s1 - s0, 1, nk), device="cuda", generator=g) * 54.0 - 60.0
+            env = torch.nn.functional.interpolate(knots, size=nk * seg, mode="linear", align_corners=False)[:, :, :nf]
+            env = torch.pow(10.0, env / 20.0) * 0.7
+            mono = torch.rand((s1 - s0, 1, nf), device="cuda", generator=g) * 2.0 - 1.0
+            side = (torch.rand((s1 - s0, nch, nf), device="cuda", generator=g) * 2.0 - 1.0) * 0.3
+            x[s0:s1] = env * (mono + side)
+    torch.cuda.synchronize()
+    return x
 
 
 def main():
@@ -134,17 +206,20 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
     ap.add_argument("--precision", default="f32", choices=["f32", "f64"])
-    ap.add_argument("--streams", type=int, default=N_STREAMS)
-    ap.add_argument("--seconds", type=float, default=SECONDS)
-    ap.add_argument("--e2e-streams", type=int, default=0, help="0 = the full batch")
+    ap.add_argument("--streams", type=int, default=0)
+    ap.add_argument("--seconds", type=float, default=0.0)
+    ap.add_argument("--e2e-seconds", type=float, default=0.0, help="0 = the workload's length (cfg2) or 10 s (cfg3/cfg4)")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-f64", action="store_true")
     ap.add_argument("--warps", type=int, default=0)
     args = ap.parse_args()
+    W = WORKLOADS[args.workload]
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
 
     if args.impl == "reference":
-        run_reference_arm(args)
+        run_reference_arm(args, W)
         return
 
     import torch
@@ -168,69 +243,62 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    ns, nf = args.streams, int(args.seconds * SRATE)
-    from za_gpu import workloads as wl
-    params = wl.cascade8_params(ns, first_stream=rank * ns)
-
-    # ---- synthetic input, generated on the device: uniform noise x0.25 + two sines per stream -------
-    g = torch.Generator(device="cuda").manual_seed(5000 + rank)
-    x = torch.empty((ns, 1, nf), dtype=torch.float32, device="cuda")
-    t = torch.arange(nf, device="cuda", dtype=torch.float32) / SRATE
-    f = torch.rand((ns, 2), device="cuda", generator=g)
-    for s0 in range(0, ns, 64):
-        s1 = min(ns, s0 + 64)
-        blk = (torch.rand((s1 - s0, 1, nf), device="cuda", generator=g) - 0.5) * 0.5
-        f1 = (60.0 + 340.0 * f[s0:s1, 0]).view(-1, 1, 1)
-        f2 = (1000.0 + 5000.0 * f[s0:s1, 1]).view(-1, 1, 1)
-        blk += 0.125 * torch.sin(2 * np.pi * f1 * t) + 0.125 * torch.sin(2 * np.pi * f2 * t)
-        x[s0:s1] = blk
-    y = torch.empty_like(x)
-    del blk
-    torch.cuda.synchronize()
+    ns = args.streams or W["streams"]
+    sec = args.seconds or W["seconds"]
+    nf = int(sec * SRATE)
+    n_in, n_out = W["ch"]
+    bpf = 4 * (n_in + n_out)                      # algorithmic bytes per frame
+    params = workload_params(W, ns, nf, first_stream=rank * ns)
+    p0 = params if params.ndim == 2 else params[0]
+    pauto = params if params.ndim == 3 else None
+    x = device_input(torch, W, ns, nf, 5000 + rank)
+    inplace = n_in == n_out and ns * (n_in + n_out) * nf * 4 > 120e9      # cfg3: 94 GB in + 94 GB out would not fit
+    y = x if inplace else torch.empty((ns, n_out, nf), dtype=torch.float32, device="cuda")
 
     results = {}
-    for prec in ([args.precision] + (["f64"] if args.precision == "f32" else [])):
-        bp = za_gpu.BatchProcessor("cascade8", ns, SRATE, 512, prec, local)
+    precs = [args.precision] + (["f64"] if args.precision == "f32" and not args.no_f64 else [])
+    for prec in precs:
+        headline = prec == args.precision
+        bp = za_gpu.BatchProcessor(W["plugin"], ns, SRATE, 512, prec, local)
         if args.warps:
             bp.set_option("warps_per_stream", args.warps)
         bp.set_stream(torch.cuda.current_stream().cuda_stream)
-        bp.prepare(params)
-        headline = prec == args.precision
+        bp.prepare(p0)
         steps = args.steps if headline else max(2, args.steps // 2)
+        warm = args.warmup if headline else 1
         # parity spot check on the very first pass (fresh state): 4 streams x 1 s against the oracle
-        bp.process(x, out=y)
+        pick = [0, ns // 3, ns // 2, ns - 1]
+        xs = x[pick, :, :48000].cpu().numpy() if rank == 0 else None
+        bp.process(x, out=y, params=pauto)
         torch.cuda.synchronize()
         parity = None
         if rank == 0:
             try:
                 sys.path.insert(0, str(REPO / "oracle"))
                 import za_oracle as zo
-                pick = [0, ns // 3, ns // 2, ns - 1]
-                xs = x[pick, :, :48000].cpu().numpy()
-                yr, yrd = zo.best_oracle("cascade8").render(params[pick], xs, want_f64=True)
+                pp = params[:94, pick] if params.ndim == 3 else params[pick]
+                yr, yrd = zo.best_oracle(W["plugin"]).render(pp, xs, want_f64=True)
                 got = y[pick, :, :48000].cpu().numpy()
                 r = got.astype(np.float64) - yrd
                 parity = {"streams": pick, "frames": 48000, "float_equal_frac": float(np.mean(got == yr)),
                           "residual_dbfs_rms": float(20 * np.log10(np.sqrt(np.mean(r ** 2)) + 1e-300))}
             except Exception as e:      # the checker is optional for the measurement
                 parity = {"error": str(e)[:120]}
-        for _ in range(args.warmup - 1):
-            bp.process(x, out=y)
+        for _ in range(warm - 1):
+            bp.process(x, out=y, params=pauto)
         barrier()
         clk = ClockSampler(local)
         if headline and rank == 0:
             clk.start()
         l0 = bp.launch_count()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        kms, klaunch = 0.0, 0
         e0.record()
         for _ in range(steps):
-            bp.process(x, out=y)
+            bp.process(x, out=y, params=pauto)
         e1.record()
         torch.cuda.synchronize()
         ms = e0.elapsed_time(e1) / steps
-        k1, kn = bp.last_kernel_ms()           # dominant kernel of the LAST timed step (CUDA events on the stream)
-        kms, klaunch = k1, kn
+        kms, klaunch = bp.last_kernel_ms()     # dominant kernel of the LAST timed step (CUDA events on the stream)
         launches = bp.launch_count() - l0
         clocks = clk.stop() if (headline and rank == 0) else None
         tmax = torch.tensor([ms], device="cuda")
@@ -243,36 +311,35 @@ def main():
 
     # ---- e2e: HOST buffers through the C ABI, copies inside the timed region ---------------------------
     e2e = None
-    es = args.e2e_streams or ns
-    while es >= 16:
-        try:
-            hx = torch.empty((es, 1, nf), dtype=torch.float32, pin_memory=True)
-            hy = torch.empty((es, 1, nf), dtype=torch.float32, pin_memory=True)
-            break
-        except RuntimeError:
-            es //= 4
-            hx = hy = None
+    e_sec = args.e2e_seconds or (sec if args.workload == "cfg2" else min(sec, 10.0))
+    enf = int(e_sec * SRATE)
+    hx = hy = None
+    try:
+        hx = torch.empty((ns, n_in, enf), dtype=torch.float32, pin_memory=True)
+        hy = torch.empty((ns, n_out, enf), dtype=torch.float32, pin_memory=True)
+    except RuntimeError:
+        hx = hy = None
     if hx is not None:
-        hx.copy_(x[:es])
+        hx.copy_(x[:, :, :enf])
         torch.cuda.synchronize()
-        bp = za_gpu.BatchProcessor("cascade8", es, SRATE, 512, args.precision, local).prepare(params[:es])
+        ep = None if pauto is None else np.ascontiguousarray(pauto[:(enf + 511) // 512])
+        bp = za_gpu.BatchProcessor(W["plugin"], ns, SRATE, 512, args.precision, local).prepare(p0)
         for _ in range(2):
-            bp.process(hx, out=hy)
+            bp.process(hx, out=hy, params=ep)
         barrier()
         t0 = time.perf_counter()
         e_steps = max(2, args.steps // 2)
         for _ in range(e_steps):
-            bp.process(hx, out=hy)              # returns when `hy` is complete
+            bp.process(hx, out=hy, params=ep)   # returns when `hy` is complete
         torch.cuda.synchronize()
         dt = (time.perf_counter() - t0) / e_steps
         tm = torch.tensor([dt], device="cuda")
         if dist is not None:
             dist.all_reduce(tm, op=dist.ReduceOp.MAX)
         dt = float(tm.item())
-        same = bool(torch.equal(hy[:4].cuda(), y[:4])) if args.precision in results and False else None
-        e2e = {"value": world * es * nf / dt, "unit": "frames/s", "h2d_bytes_per_step": es * nf * 4,
-               "d2h_bytes_per_step": es * nf * 4, "ms_per_step": dt * 1e3, "streams_per_gpu": es,
-               "x_realtime": world * es * nf / dt / SRATE, "host_memory": "pinned"}
+        e2e = {"value": world * ns * enf / dt, "unit": "frames/s", "h2d_bytes_per_step": ns * n_in * enf * 4,
+               "d2h_bytes_per_step": ns * n_out * enf * 4, "ms_per_step": dt * 1e3, "streams_per_gpu": ns,
+               "seconds_per_step": e_sec, "x_realtime": world * ns * enf / dt / SRATE, "host_memory": "pinned"}
         bp.close()
         del hx, hy
 
@@ -285,29 +352,33 @@ def main():
     peak, peak_kind = peaks()
     r = results[args.precision]
     traffic = None
-    tp = REPO / "profiles" / "cascade8_traffic.json"
+    tp = REPO / "profiles" / "traffic.json"
     if tp.exists():
         try:
-            traffic = json.loads(tp.read_text()).get(args.precision, {}).get("dram_bytes_per_launch")
+            traffic = json.loads(tp.read_text()).get(args.workload, {}).get(args.precision)
         except Exception:
             traffic = None
 
-    def roof(rr):
+    def roof(rr, prec):
         if not rr["kernel_launches"] or rr["kernel_ms"] <= 0:
             return None
-        per_launch_ms = rr["kernel_ms"] / rr["kernel_launches"]
-        ach = ns * nf * BYTES_PER_FRAME / rr["kernel_launches"] * rr["kernel_launches"] / (rr["kernel_ms"] * 1e-3) / 1e9
+        alg = ns * nf * bpf                                     # algorithmic bytes of one step
+        ach = alg / (rr["kernel_ms"] * 1e-3) / 1e9
+        tr = None
+        if traffic and traffic.get("dram_bytes_per_frame"):
+            tr = traffic["dram_bytes_per_frame"] * ns * nf / rr["kernel_launches"]
         return {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "peak_source": peak_kind,
-                "traffic": traffic, "kernel": "cascade8_kernel", "kernel_ms_per_launch": per_launch_ms,
-                "algorithmic_bytes_per_launch": ns * nf * BYTES_PER_FRAME // max(rr["kernel_launches"], 1)}
+                "traffic": tr, "kernel": W["kernel"][prec], "kernel_ms_per_launch": rr["kernel_ms"] / rr["kernel_launches"],
+                "launches_per_step": rr["kernel_launches"], "algorithmic_bytes_per_launch": alg // max(rr["kernel_launches"], 1),
+                "algorithmic_bytes_per_frame": bpf}
 
     cpu = None
     if not args.no_cpu:
         threads = os.cpu_count() or 1
-        cns = CPU_SAMPLE_STREAMS
-        v, kind, dt = cpu_reference_run(cns, CPU_SAMPLE_SECONDS, threads)
+        cns, csec = W["cpu"]
+        v, kind, dt = cpu_reference_run(W, cns, csec, threads)
         cpu = {"value": v, "unit": "frames/s", "cores": threads, "kind": kind,
-               "sample": f"{cns} streams x {CPU_SAMPLE_SECONDS:g} s of the same workload ({dt:.1f} s of wall time), block 512",
+               "sample": f"{cns} streams x {csec:g} s of the same workload ({dt:.1f} s of wall time), block 512",
                "x_realtime": v / SRATE}
 
     line = {
@@ -315,15 +386,15 @@ def main():
         "steps": r["steps"], "warmup": args.warmup, "ms_per_step": r["ms"], "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": args.precision, "data": "synthetic",
         "x_realtime": r["value"] / SRATE,
-        "config": {"workload": f"cfg2: cascade8 (8-section biquad/one-pole cascade), {ns} mono streams x {args.seconds:g} s @ 48 kHz per GPU",
+        "config": {"workload": workload_text(W, ns, sec),
                    "streams_per_gpu": ns, "frames_per_stream": nf, "block_len": 512, "io": "float32 planar [stream][ch][frame]",
-                   "l2": "inputs (%.1f GB per step) larger than L2" % (ns * nf * 4 / 1e9), "parallelism": f"streams sharded x{world}"},
-        "clocks": r["clocks"], "e2e": e2e, "gpu_launches": r["launches"], "roofline": roof(r), "cpu_baseline": cpu,
+                   "l2": "inputs (%.1f GB per step) larger than L2" % (ns * n_in * nf * 4 / 1e9), "parallelism": f"streams sharded x{world}"},
+        "clocks": r["clocks"], "e2e": e2e, "gpu_launches": r["launches"], "roofline": roof(r, args.precision), "cpu_baseline": cpu,
         "parity_spot_check": r["parity"],
     }
     if "f64" in results and args.precision != "f64":
         q = results["f64"]
-        line["f64"] = {"value": q["value"], "ms_per_step": q["ms"], "x_realtime": q["value"] / SRATE, "roofline": roof(q),
+        line["f64"] = {"value": q["value"], "ms_per_step": q["ms"], "x_realtime": q["value"] / SRATE, "roofline": roof(q, "f64"),
                        "parity_spot_check": q["parity"], "gpu_launches": q["launches"]}
     print(json.dumps(line), flush=True)
     if dist is not None:
