@@ -5,80 +5,104 @@
 // (jsfx_fft / jsfx_fft_permute / jsfx_fft_ipermute / jsfx_ifft, src/JSFXJuceProcessor.cpp:1267-1447 over
 // src/WDL/fft.c) for n_streams instances at once.
 //
-// Mapping.  One CTA per stream, persistent over the call's time axis; everything between two hops lives in
-// shared memory: the last five hops of input (analysis window + dry delay), four hops of overlap-add
-// accumulator, the per-bin recursive state (baseline EMA, previous magnitude), the FFT buffer and twiddles.
-// Per hop: (1) stream 512 stereo frames in / out (out = finished accumulator slot, mixed with the delayed
-// dry signal), (2) window both channels into ONE complex buffer z = w (l + i r), (3) in-place radix-2 DIF
-// FFT in shared memory (natural in, bit-reversed out: the permutation the reference does with fft_permute is
-// folded into the bin addressing), (4) split the stereo spectra by conjugate symmetry, magnitudes,
-// per-bin gain rule with its recursive state, 3-tap smoothing, (5) scale Z[k] and Z[N-k] (a real,
-// symmetric gain commutes with the stereo packing), (6) in-place radix-2 DIT inverse FFT (bit-reversed in,
-// natural out), (7) x 1/N x synthesis window, overlap-add.  One complex FFT pair per stereo hop instead of
-// the reference's two: same mathematics, rounding differs at the 1e-15 level (criterion 1e-12).
-// Window / twiddle tables are computed on the host with glibc in the script's expression order.
+// Mapping.  128 threads per stream, NS streams per CTA (4 in fp32, 2 in fp64: one CTA per SM, the twiddle and
+// window tables are shared by the CTA's streams), persistent over the call's time axis.  Everything between two
+// hops lives on chip: the last four hops of input (analysis window + the 2048-frame dry delay), four hops of
+// overlap-add accumulator and the FFT exchange buffer in shared memory; the per-bin recursive state (baseline
+// EMA, previous magnitude) in registers of the thread that owns the bin.  Per hop (stft_core.h):
+//   (1) 512 stereo frames in / out as float4 per thread, next hop's input prefetched during the transforms;
+//   (2) window both channels into ONE complex signal z = w (l + i r), forward FFT 16 x 16 x 8 (registers,
+//       two shared-memory exchanges, padded so every access pattern is bank-conflict free);
+//   (3) stereo split by conjugate symmetry inside one thread's registers, magnitudes, per-bin gain rule with
+//       its recursive state, 3-tap smoothing (magnitudes and gains cross threads through shared memory),
+//       gains applied to Z[k] and Z[N-k] (a real, symmetric gain commutes with the stereo packing);
+//   (4) inverse FFT 8 x 16 x 16, x 1/N x synthesis window, overlap-add.
+// One complex FFT pair per stereo hop instead of the reference's two: same mathematics, rounding differs at
+// the 1e-15 level (criterion 1e-12).  Window / twiddle tables are computed on the host with glibc.
+#include "stft_core.h"
 #include "za_device.cuh"
 #include "za_internal.h"
 
 namespace za {
 
-namespace {
+using namespace stft;
 
-constexpr int kN = kStftN, kHop = kStftHop, kBins = kStftBins;
-
-template <typename R> struct Cx { R re, im; };
-
-template <typename R> __device__ __forceinline__ R sqrt_r(R v);
-template <> __device__ __forceinline__ double sqrt_r<double>(double v) { return __dsqrt_rn(v); }
-template <> __device__ __forceinline__ float sqrt_r<float>(float v) { return sqrtf(v); }
-template <typename R> __device__ __forceinline__ R div_r(R a, R b);
-template <> __device__ __forceinline__ double div_r<double>(double a, double b) { return __ddiv_rn(a, b); }
-template <> __device__ __forceinline__ float div_r<float>(float a, float b) { return a / b; }
-template <typename R> __device__ __forceinline__ R max_r(R a, R b) { return a > b ? a : b; }   // ogt select (dsp_jsfx_aot.py:5223-5232)
-template <typename R> __device__ __forceinline__ R min_r(R a, R b) { return a < b ? a : b; }
-template <typename R> __device__ __forceinline__ R clamp01(R x) { return x < (R)0 ? (R)0 : (x > (R)1 ? (R)1 : x); }
-
-__device__ __forceinline__ int brev11(int k) { return (int)(__brev((unsigned)k) >> 21); }   // 2048 = 2^11
-
-template <typename R, int NT> struct StftSmem {
-    Cx<R> z[kN];               // FFT buffer
-    Cx<R> tw[kN / 2];          // exp(-2 pi i k / N)
-    R acc[2][kN];              // overlap-add accumulator: 4 slots of one hop per channel
-    R mag[kBins + 3];
-    R gain[kBins + 3];
-    R base[kBins + 3];
-    R prev[kBins + 3];
-    float xin[2][5 * kHop];    // last five hops of input per channel (slot = hop index mod 5)
-};
-
-}  // namespace
+static_assert(sizeof(Coef) == sizeof(StftCoef), "Coef layout");
 
 size_t stft_state_bytes() { return sizeof(StftState); }
 
-template <typename R, int NT, bool TAP>
-__global__ void __launch_bounds__(NT)
+namespace {
+
+__device__ __forceinline__ void bar_stream(int sub) { asm volatile("bar.sync %0, 128;" ::"r"(sub + 1) : "memory"); }
+
+template <typename R> __device__ __forceinline__ void ld4r(const R* p, R (&x)[4]);
+template <> __device__ __forceinline__ void ld4r<float>(const float* p, float (&x)[4])
+{
+    const float4 v = *reinterpret_cast<const float4*>(p);
+    x[0] = v.x; x[1] = v.y; x[2] = v.z; x[3] = v.w;
+}
+template <> __device__ __forceinline__ void ld4r<double>(const double* p, double (&x)[4])
+{
+    const double2 a = *reinterpret_cast<const double2*>(p), b = *reinterpret_cast<const double2*>(p + 2);
+    x[0] = a.x; x[1] = a.y; x[2] = b.x; x[3] = b.y;
+}
+template <typename R> __device__ __forceinline__ void zero4(R* p);
+template <> __device__ __forceinline__ void zero4<float>(float* p) { *reinterpret_cast<float4*>(p) = make_float4(0.f, 0.f, 0.f, 0.f); }
+template <> __device__ __forceinline__ void zero4<double>(double* p)
+{
+    *reinterpret_cast<double2*>(p) = make_double2(0.0, 0.0);
+    *reinterpret_cast<double2*>(p + 2) = make_double2(0.0, 0.0);
+}
+
+}  // namespace
+
+template <typename R, int NS, bool TAP>
+__global__ void __launch_bounds__(NS * kT, 1)
 stft_mask_kernel(const StftArgs a)
 {
     extern __shared__ __align__(16) uint8_t smem_raw[];
-    StftSmem<R, NT>& sm = *reinterpret_cast<StftSmem<R, NT>*>(smem_raw);
-    const int tid = threadIdx.x, stream = blockIdx.x;
+    Tables<R>& tb = *reinterpret_cast<Tables<R>*>(smem_raw);
+    const int sub = threadIdx.x >> 7, t = threadIdx.x & (kT - 1);
+    StreamSmem<R>& S = reinterpret_cast<StreamSmem<R>*>(smem_raw + sizeof(Tables<R>))[sub];
+
+    // ---- tables -> shared memory (whole CTA) ------------------------------------------------------------
+    for (int i = threadIdx.x; i < 15 * kT; i += NS * kT) { tb.tw1[i / kT][i % kT].re = (R)a.tw1[2 * i]; tb.tw1[i / kT][i % kT].im = (R)a.tw1[2 * i + 1]; }
+    for (int i = threadIdx.x; i < 15 * 8; i += NS * kT) { tb.tw2[i / 8][i % 8].re = (R)a.tw2[2 * i]; tb.tw2[i / 8][i % 8].im = (R)a.tw2[2 * i + 1]; }
+    for (int i = threadIdx.x; i < kN; i += NS * kT) { tb.win[i] = (R)a.win[i]; tb.syn[i] = (R)a.syn[i]; }
+    __syncthreads();
+    const int stream = blockIdx.x * NS + sub;
+    if (stream >= a.n_streams) return;
     StftState& gs = a.state[stream];
 
-    // ---- state and tables -> shared memory -----------------------------------------------------------
-    for (int i = tid; i < kN / 2; i += NT) { sm.tw[i].re = (R)a.tw[2 * i]; sm.tw[i].im = (R)a.tw[2 * i + 1]; }
-    for (int i = tid; i < 2 * kN; i += NT) sm.acc[i / kN][i % kN] = (R)gs.acc[i / kN][i % kN];
-    for (int i = tid; i < 2 * 5 * kHop; i += NT) sm.xin[i / (5 * kHop)][i % (5 * kHop)] = gs.xin[i / (5 * kHop)][i % (5 * kHop)];
-    for (int i = tid; i < kBins; i += NT) { sm.base[i] = (R)gs.base[i]; sm.prev[i] = (R)gs.prev[i]; }
-    __syncthreads();
+    // ---- per-stream state -> shared memory / registers ---------------------------------------------------
+    Regs<R> g;
+    for (int i = t; i < 2 * kN; i += kT) { S.acc[i / kN][i % kN] = (R)gs.acc[i / kN][i % kN]; S.xin[i / kN][i % kN] = gs.xin[i / kN][i % kN]; }
+#pragma unroll
+    for (int s = 0; s < 8; ++s) {
+        const int k = slot_bin_rt(t, s);
+        g.base[s] = k >= 0 ? (R)gs.base[k] : (R)0;
+        g.prev[s] = k >= 0 ? (R)gs.prev[k] : (R)0;
+        g.magr[s] = (R)0;
+    }
+    bar_stream(sub);
 
     const float* inL = a.in + (size_t)stream * 2 * a.row_stride;
     const float* inR = inL + a.row_stride;
     float* outL = a.out + (size_t)stream * 2 * a.row_stride;
     float* outR = outL + a.row_stride;
+    const bool aligned = ((a.row_stride & 3) == 0) && ((reinterpret_cast<uintptr_t>(a.in) & 15) == 0) &&
+                         ((reinterpret_cast<uintptr_t>(a.out) & 15) == 0) &&
+                         (!TAP || (reinterpret_cast<uintptr_t>(a.tap) & 15) == 0);
 
     int64_t pos = 0;
     int64_t hop = a.t0 / kHop;                 // absolute hop index of the frame position
     int off = (int)(a.t0 % kHop);              // offset inside the hop (= the script's hop_ctr)
+    float4 nl = make_float4(0.f, 0.f, 0.f, 0.f), nr = nl;
+    bool have_next = false;                    // nl / nr hold frames pos + 4t .. of a full, aligned hop
+    if (aligned && off == 0 && kHop <= a.n_frames) {
+        nl = *reinterpret_cast<const float4*>(inL + 4 * t); nr = *reinterpret_cast<const float4*>(inR + 4 * t);
+        have_next = true;
+    }
     while (pos < a.n_frames) {
         // segment = up to the next hop boundary, the next host-block boundary, or the end of the call
         const int64_t blk = pos / a.block_len;
@@ -88,141 +112,116 @@ stft_mask_kernel(const StftArgs a)
         const int len = (int)(end - pos);
         const StftCoef c = a.coef[(size_t)(blk < a.n_coef_blocks ? blk : a.n_coef_blocks - 1) * a.n_streams + stream];
         const R mixv = (R)c.mixv;
-        const int s_in = (int)(hop % 5), s_dry = (int)((hop + 1) % 5), s_acc = (int)(hop % 4);   // (hop - 4) mod 5 = (hop + 1) mod 5
+        const int slot = (int)(hop & 3) * kHop;     // input slot of this hop = dry slot (hop - 4) = accumulator slot
 
-        // ---- (1) stream the segment: input ring write, accumulator read + clear, dry/wet mix ------------
-        for (int i = tid; i < len; i += NT) {
-            const int o = off + i;
-            const float l = inL[pos + i], r = inR[pos + i];
-            const R dryL = (R)sm.xin[0][s_dry * kHop + o], dryR = (R)sm.xin[1][s_dry * kHop + o];
-            sm.xin[0][s_in * kHop + o] = l; sm.xin[1][s_in * kHop + o] = r;
-            const R rawL = sm.acc[0][s_acc * kHop + o], rawR = sm.acc[1][s_acc * kHop + o];
-            sm.acc[0][s_acc * kHop + o] = (R)0; sm.acc[1][s_acc * kHop + o] = (R)0;
-            const R o0 = add(dryL, mul(mixv, sub(rawL, dryL))), o1 = add(dryR, mul(mixv, sub(rawR, dryR)));
-            outL[pos + i] = (float)o0; outR[pos + i] = (float)o1;
+        // ---- (1) stream the segment: dry read, input ring write, accumulator read + clear, dry/wet mix ------
+        if (have_next && len == kHop) {
+            const int o = slot + 4 * t;
+            const float4 dl = *reinterpret_cast<const float4*>(&S.xin[0][o]), dr = *reinterpret_cast<const float4*>(&S.xin[1][o]);
+            *reinterpret_cast<float4*>(&S.xin[0][o]) = nl; *reinterpret_cast<float4*>(&S.xin[1][o]) = nr;
+            R rl[4], rr[4];
+            ld4r<R>(&S.acc[0][o], rl); ld4r<R>(&S.acc[1][o], rr);
+            zero4<R>(&S.acc[0][o]); zero4<R>(&S.acc[1][o]);
+            const R d0[4] = {(R)dl.x, (R)dl.y, (R)dl.z, (R)dl.w}, d1[4] = {(R)dr.x, (R)dr.y, (R)dr.z, (R)dr.w};
+            R o0[4], o1[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) { o0[i] = add_(d0[i], mul_(mixv, sub_(rl[i], d0[i]))); o1[i] = add_(d1[i], mul_(mixv, sub_(rr[i], d1[i]))); }
+            *reinterpret_cast<float4*>(outL + pos + 4 * t) = make_float4((float)o0[0], (float)o0[1], (float)o0[2], (float)o0[3]);
+            *reinterpret_cast<float4*>(outR + pos + 4 * t) = make_float4((float)o1[0], (float)o1[1], (float)o1[2], (float)o1[3]);
             if (TAP) {
-                double* tp = a.tap + (size_t)stream * 2 * a.row_stride + pos + i;
-                tp[0] = (double)o0; tp[a.row_stride] = (double)o1;
+                double* tp = a.tap + (size_t)stream * 2 * a.row_stride + pos + 4 * t;
+                *reinterpret_cast<double2*>(tp) = make_double2((double)o0[0], (double)o0[1]);
+                *reinterpret_cast<double2*>(tp + 2) = make_double2((double)o0[2], (double)o0[3]);
+                *reinterpret_cast<double2*>(tp + a.row_stride) = make_double2((double)o1[0], (double)o1[1]);
+                *reinterpret_cast<double2*>(tp + a.row_stride + 2) = make_double2((double)o1[2], (double)o1[3]);
+            }
+        } else {
+            for (int i = t; i < len; i += kT) {
+                const int o = slot + off + i;
+                const float l = inL[pos + i], r = inR[pos + i];
+                const R dryL = (R)S.xin[0][o], dryR = (R)S.xin[1][o];
+                S.xin[0][o] = l; S.xin[1][o] = r;
+                const R rawL = S.acc[0][o], rawR = S.acc[1][o];
+                S.acc[0][o] = (R)0; S.acc[1][o] = (R)0;
+                const R o0 = add_(dryL, mul_(mixv, sub_(rawL, dryL))), o1 = add_(dryR, mul_(mixv, sub_(rawR, dryR)));
+                outL[pos + i] = (float)o0; outR[pos + i] = (float)o1;
+                if (TAP) {
+                    double* tp = a.tap + (size_t)stream * 2 * a.row_stride + pos + i;
+                    tp[0] = (double)o0; tp[a.row_stride] = (double)o1;
+                }
             }
         }
         pos = end; off += len;
-        __syncthreads();
+        // prefetch the next hop's input when the next segment is a full aligned hop inside one host block
+        have_next = false;
+        if (aligned && off == kHop && (pos & 3) == 0 && pos + kHop <= a.n_frames &&
+            (pos / a.block_len) == ((pos + kHop - 1) / a.block_len)) {
+            nl = *reinterpret_cast<const float4*>(inL + pos + 4 * t); nr = *reinterpret_cast<const float4*>(inR + pos + 4 * t);
+            have_next = true;
+        }
+        bar_stream(sub);
         if (off < kHop) continue;
         off = 0;
 
-        // ---- (2) frame `hop`: window hops hop-3 .. hop into z = w (l + i r) ---------------------------------
-        for (int i = tid; i < kN; i += NT) {
-            const int hs = (int)((hop + 2 + (i >> 9)) % 5);            // (hop - 3 + i/512) mod 5
-            const R w = (R)a.win[i];
-            sm.z[i].re = mul((R)sm.xin[0][hs * kHop + (i & 511)], w);
-            sm.z[i].im = mul((R)sm.xin[1][hs * kHop + (i & 511)], w);
-        }
-        __syncthreads();
-        // ---- (3) forward FFT, radix-2 decimation in frequency: natural in, bit-reversed out ----------------
-        for (int half = kN / 2, tstep = 1; half >= 1; half >>= 1, tstep <<= 1) {
-            for (int j = tid; j < kN / 2; j += NT) {
-                const int p = j & (half - 1), i0 = ((j - p) << 1) + p, i1 = i0 + half;
-                const Cx<R> u = sm.z[i0], v = sm.z[i1], w = sm.tw[p * tstep];
-                const R dr = u.re - v.re, di = u.im - v.im;
-                sm.z[i0].re = u.re + v.re; sm.z[i0].im = u.im + v.im;
-                sm.z[i1].re = dr * w.re - di * w.im; sm.z[i1].im = dr * w.im + di * w.re;
-            }
-            __syncthreads();
-        }
-        // ---- (4) stereo split, magnitudes (stft_mask2048.jsfx process_frame; Sample.jsfx:3575-3585) ---------
-        for (int k = tid; k < kBins; k += NT) {
-            const Cx<R> p = sm.z[brev11(k)], q = sm.z[brev11((kN - k) & (kN - 1))];
-            const R reL = mul((R)0.5, add(p.re, q.re)), imL = mul((R)0.5, sub(p.im, q.im));
-            const R reR = mul((R)0.5, add(p.im, q.im)), imR = mul((R)0.5, sub(q.re, p.re));
-            const R m2L = max_r((R)0, add(mul(reL, reL), mul(imL, imL)));
-            const R m2R = max_r((R)0, add(mul(reR, reR), mul(imR, imR)));
-            sm.mag[k] = sqrt_r<R>(mul((R)0.5, add(m2L, m2R)));
-        }
-        __syncthreads();
-        // ---- per-bin gain rule with recursive state ----------------------------------------------------------
-        {
-            const R tiny = (R)1e-18, ab = (R)c.ab, bb = (R)c.bb, thresh = (R)c.thresh, amt = (R)c.amt, floor_g = (R)c.floor_g;
-            for (int k = tid; k < kBins; k += NT) {
-                if (k == 0 || k == kBins - 1) { sm.gain[k] = (R)1; continue; }
-                const R magbin = sm.mag[k];
-                R base_old = sm.base[k];
-                if (base_old < tiny) base_old = max_r(magbin, tiny);
-                sm.base[k] = add(mul(ab, base_old), mul(bb, magbin));
-                const R flux = div_r<R>(max_r((R)0, sub(magbin, sm.prev[k])), add(base_old, tiny));
-                sm.prev[k] = magbin;
-                R neigh = mul((R)0.25, add(add(add(sm.mag[k - 2 < 0 ? 0 : k - 2], sm.mag[k - 1]), sm.mag[k + 1]),
-                                           sm.mag[k + 2 > kBins - 1 ? kBins - 1 : k + 2]));
-                if (neigh < tiny) neigh = base_old;
-                const R peak = div_r<R>(magbin, add(neigh, tiny));
-                const R dp = clamp01(div_r<R>(sub(peak, thresh), max_r((R)0.18, thresh)));
-                const R df = clamp01(div_r<R>(sub(flux, (R)1), (R)2));
-                const R control = mul(amt, clamp01(add(mul((R)0.7, dp), mul((R)0.3, df))));
-                const R ref = add(mul((R)0.75, neigh), mul((R)0.25, base_old));
-                const R hard = min_r((R)1, div_r<R>(add(ref, tiny), add(magbin, tiny)));
-                R raw = sub((R)1, mul(control, sub((R)1, hard)));
-                raw = max_r(floor_g, min_r((R)1, raw));
-                sm.gain[k] = raw;
-            }
-        }
-        __syncthreads();
-        // ---- (5) 3-tap smoothing, applied to bins k and N-k of the packed spectrum ----------------------------
-        for (int k = tid + 1; k < kBins - 1; k += NT) {
-            const R sg = add(add(mul((R)0.16, sm.gain[k - 1]), mul((R)0.68, sm.gain[k])), mul((R)0.16, sm.gain[k + 1]));
-            const int i0 = brev11(k), i1 = brev11(kN - k);
-            sm.z[i0].re = mul(sm.z[i0].re, sg); sm.z[i0].im = mul(sm.z[i0].im, sg);
-            sm.z[i1].re = mul(sm.z[i1].re, sg); sm.z[i1].im = mul(sm.z[i1].im, sg);
-        }
-        __syncthreads();
-        // ---- (6) inverse FFT, radix-2 decimation in time: bit-reversed in, natural out (unscaled, like WDL) ----
-        for (int half = 1, tstep = kN / 2; half <= kN / 2; half <<= 1, tstep >>= 1) {
-            for (int j = tid; j < kN / 2; j += NT) {
-                const int p = j & (half - 1), i0 = ((j - p) << 1) + p, i1 = i0 + half;
-                const Cx<R> u = sm.z[i0], v = sm.z[i1], w = sm.tw[p * tstep];
-                const R tr = v.re * w.re + v.im * w.im, ti = v.im * w.re - v.re * w.im;      // v * conj(w)
-                sm.z[i0].re = u.re + tr; sm.z[i0].im = u.im + ti;
-                sm.z[i1].re = u.re - tr; sm.z[i1].im = u.im - ti;
-            }
-            __syncthreads();
-        }
-        // ---- (7) x 1/N x synthesis window, overlap-add into output hops hop+1 .. hop+4 -------------------------
-        {
-            const R scale = (R)(1.0 / kN);
-            for (int i = tid; i < kN; i += NT) {
-                const int slot = (int)((hop + 1 + (i >> 9)) % 4), o = slot * kHop + (i & 511);
-                const R sy = (R)a.syn[i];
-                sm.acc[0][o] = add(sm.acc[0][o], mul(mul(sm.z[i].re, scale), sy));
-                sm.acc[1][o] = add(sm.acc[1][o], mul(mul(sm.z[i].im, scale), sy));
-            }
-        }
+        // ---- (2)-(4) frame `hop` -----------------------------------------------------------------------------
+        Coef cc; cc.amt = c.amt; cc.thresh = c.thresh; cc.ab = c.ab; cc.bb = c.bb; cc.floor_g = c.floor_g; cc.mixv = c.mixv;
+        fwd1<R>(t, g, S, tb, hop);
+        bar_stream(sub);
+        fwd2<R>(t, g, S, tb);
+        bar_stream(sub);
+        fwd3<R>(t, g, S);
+        bar_stream(sub);                       // every Z read done: the buffer now carries magnitudes and gains
+        if (t == 0) mags<R, true>(t, g, S); else mags<R, false>(t, g, S);
+        bar_stream(sub);
+        if (t == 0) gains<R, true>(t, g, S, cc); else gains<R, false>(t, g, S, cc);
+        bar_stream(sub);
+        if (t == 0) apply_gains<R, true>(t, g, S); else apply_gains<R, false>(t, g, S);
+        bar_stream(sub);                       // every gain read done: the buffer carries Z again
+        inv3<R>(t, g, S);
+        bar_stream(sub);
+        inv2<R>(t, g, S, tb);
+        bar_stream(sub);
+        inv1_ola<R>(t, g, S, tb, hop);
         ++hop;
-        __syncthreads();
+        bar_stream(sub);
     }
 
     // ---- state -> HBM (carried into the next call) ------------------------------------------------------------
-    for (int i = tid; i < 2 * kN; i += NT) gs.acc[i / kN][i % kN] = (double)sm.acc[i / kN][i % kN];
-    for (int i = tid; i < 2 * 5 * kHop; i += NT) gs.xin[i / (5 * kHop)][i % (5 * kHop)] = sm.xin[i / (5 * kHop)][i % (5 * kHop)];
-    for (int i = tid; i < kBins; i += NT) { gs.base[i] = (double)sm.base[i]; gs.prev[i] = (double)sm.prev[i]; }
+    for (int i = t; i < 2 * kN; i += kT) { gs.acc[i / kN][i % kN] = (double)S.acc[i / kN][i % kN]; gs.xin[i / kN][i % kN] = S.xin[i / kN][i % kN]; }
+#pragma unroll
+    for (int s = 0; s < 8; ++s) {
+        const int k = slot_bin_rt(t, s);
+        if (k >= 0) { gs.base[k] = (double)g.base[s]; gs.prev[k] = (double)g.prev[s]; }
+    }
 }
 
-template <typename R, int NT, bool TAP>
+template <typename R, int NS, bool TAP>
 static bool launch_stft(const StftArgs& a, cudaStream_t stream)
 {
-    auto kern = stft_mask_kernel<R, NT, TAP>;
-    const size_t smem = sizeof(StftSmem<R, NT>);
+    auto kern = stft_mask_kernel<R, NS, TAP>;
+    const size_t smem = sizeof(Tables<R>) + NS * sizeof(StreamSmem<R>);
     static bool attr_done = false;
     if (!attr_done) {
         if (!cuda_ok(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "stft smem attr")) return false;
         attr_done = true;
     }
-    kern<<<a.n_streams, NT, smem, stream>>>(a);
+    kern<<<(a.n_streams + NS - 1) / NS, NS * kT, smem, stream>>>(a);
     return cuda_ok(cudaGetLastError(), "stft_mask_kernel launch");
 }
 
-bool stft_launch(const StftArgs& a, int precision, cudaStream_t stream)
+// streams per CTA: as many as fit one SM's shared memory, but no more than spreads n_streams over the SMs
+bool stft_launch(const StftArgs& a, int precision, int n_sm, cudaStream_t stream)
 {
     if (a.n_frames <= 0 || a.n_streams <= 0) return true;
-    if (precision) return a.tap ? launch_stft<double, 512, true>(a, stream) : launch_stft<double, 512, false>(a, stream);
-    return launch_stft<float, 256, false>(a, stream);
+    const int per_sm = (a.n_streams + n_sm - 1) / n_sm;
+    if (precision) {
+        if (a.tap) return per_sm >= 2 ? launch_stft<double, 2, true>(a, stream) : launch_stft<double, 1, true>(a, stream);
+        return per_sm >= 2 ? launch_stft<double, 2, false>(a, stream) : launch_stft<double, 1, false>(a, stream);
+    }
+    if (per_sm >= 4) return launch_stft<float, 4, false>(a, stream);
+    if (per_sm == 3) return launch_stft<float, 3, false>(a, stream);
+    if (per_sm == 2) return launch_stft<float, 2, false>(a, stream);
+    return launch_stft<float, 1, false>(a, stream);
 }
 
 }  // namespace za

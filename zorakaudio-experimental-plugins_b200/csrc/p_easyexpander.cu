@@ -107,22 +107,24 @@ public:
         if (s0 != 0 || ns != I.n_streams) { set_error("EasyExpander: stream sub-ranges are not supported"); return false; }
         const int nd = (int)I.decls.size();
         h_coef.resize((size_t)nbq * ns);
-        for (int s = 0; s < ns; ++s) {
-            // exp() only when the detector-filter sliders moved (it is the expensive part of @slider)
-            for (int b = 0; b < nbq; ++b) {
-                const double* sl = q + ((size_t)b * ns + s) * nd;
-                EECoef& c = h_coef[(size_t)b * ns + s];
-                if (b > 0 && sl[3] == sl[3 - (size_t)ns * nd] && sl[4] == sl[4 - (size_t)ns * nd]) {
-                    const EECoef& p = h_coef[(size_t)(b - 1) * ns + s];
-                    c = p;
-                    c.thresh_db = sl[0]; c.depth_db = sl[1];
-                    double rb = 1.5 + 2.5 * (sl[2] / 100.0);
-                    c.ratio_base = rb < 1.0 ? 1.0 : rb;
-                } else {
-                    ee_slider(sl, I.srate, c);
+        parallel_for(ns, 64, [&](int64_t sb, int64_t se) {
+            for (int64_t s = sb; s < se; ++s) {
+                // exp() only when the detector-filter sliders moved (it is the expensive part of @slider)
+                for (int b = 0; b < nbq; ++b) {
+                    const double* sl = q + ((size_t)b * ns + s) * nd;
+                    EECoef& c = h_coef[(size_t)b * ns + s];
+                    if (b > 0 && sl[3] == sl[3 - (size_t)ns * nd] && sl[4] == sl[4 - (size_t)ns * nd]) {
+                        const EECoef& p = h_coef[(size_t)(b - 1) * ns + s];
+                        c = p;
+                        c.thresh_db = sl[0]; c.depth_db = sl[1];
+                        double rb = 1.5 + 2.5 * (sl[2] / 100.0);
+                        c.ratio_base = rb < 1.0 ? 1.0 : rb;
+                    } else {
+                        ee_slider(sl, I.srate, c);
+                    }
                 }
             }
-        }
+        });
         if (h_coef.size() > coef_cap) {
             cudaFree(d_coef);
             if (!cuda_ok(cudaMalloc(&d_coef, h_coef.size() * sizeof(EECoef)), "EasyExpander coef")) { coef_cap = 0; d_coef = nullptr; return false; }

@@ -32,7 +32,8 @@ void stft_slider(const double* sl, double srate, StftCoef& c)
 class StftMask : public PluginImpl {
     StftState* d_state = nullptr;
     StftCoef* d_coef = nullptr;
-    double* d_tab = nullptr;          // win[2048] | syn[2048] | tw[1024][2]
+    double* d_tab = nullptr;          // win[2048] | syn[2048] | tw1[15][128][2] | tw2[15][8][2]
+    int n_sm = 148;
     size_t coef_cap = 0;
     std::vector<StftCoef> h_coef;
     int64_t t_abs = 0;                // frames rendered since prepare
@@ -43,8 +44,8 @@ public:
     bool create(Instance& I) override
     {
         // @init: symmetric Hann, synthesis window = w / sum of w^2 over the 4 overlaps (Sample.jsfx:3503-3528)
-        std::vector<double> tab(2 * kStftN + kStftN);
-        double* win = tab.data(); double* syn = win + kStftN; double* tw = syn + kStftN;
+        std::vector<double> tab(2 * kStftN + 2 * 15 * 128 + 2 * 15 * 8);
+        double* win = tab.data(); double* syn = win + kStftN; double* tw1 = syn + kStftN; double* tw2 = tw1 + 2 * 15 * 128;
         for (int i = 0; i < kStftN; ++i) win[i] = 0.5 - 0.5 * std::cos(6.283185307179586 * i / (kStftN - 1));
         const int overlaps = kStftN / kStftHop;
         for (int i = 0; i < kStftN; ++i) {
@@ -52,10 +53,22 @@ public:
             for (int j = 0; j < overlaps; ++j) { sum += win[idx] * win[idx]; idx += kStftHop; if (idx >= kStftN) idx -= kStftN; }
             syn[i] = sum > 0.000000000001 ? win[i] / sum : win[i];
         }
-        for (int k = 0; k < kStftN / 2; ++k) {
-            const double ang = 6.283185307179586 * (double)k / (double)kStftN;
-            tw[2 * k] = std::cos(ang); tw[2 * k + 1] = -std::sin(ang);
+        // the script's `x * scale * syn[i]` with scale = 1/2048: a power of two, so folding it into the table is exact
+        for (int i = 0; i < kStftN; ++i) syn[i] *= 1.0 / kStftN;
+        // twiddles of the 16 x 16 x 8 decomposition (k_stft.cu / stft_core.h)
+        for (int q = 1; q < 16; ++q) {
+            for (int t = 0; t < 128; ++t) {
+                const double ang = 6.283185307179586 * (double)(t * q) / 2048.0;
+                tw1[2 * ((q - 1) * 128 + t)] = std::cos(ang); tw1[2 * ((q - 1) * 128 + t) + 1] = -std::sin(ang);
+            }
+            for (int j = 0; j < 8; ++j) {
+                const double ang = 6.283185307179586 * (double)(j * q) / 128.0;
+                tw2[2 * ((q - 1) * 8 + j)] = std::cos(ang); tw2[2 * ((q - 1) * 8 + j) + 1] = -std::sin(ang);
+            }
         }
+        cudaDeviceProp prop;
+        if (!cuda_ok(cudaGetDeviceProperties(&prop, I.device), "device properties")) return false;
+        n_sm = prop.multiProcessorCount;
         return cuda_ok(cudaMalloc(&d_state, (size_t)I.n_streams * sizeof(StftState)), "stft state") &&
                cuda_ok(cudaMalloc(&d_tab, tab.size() * sizeof(double)), "stft tables") &&
                cuda_ok(cudaMemcpy(d_tab, tab.data(), tab.size() * sizeof(double), cudaMemcpyHostToDevice), "stft tables upload");
@@ -81,13 +94,15 @@ public:
         if (s0 != 0 || ns != I.n_streams) { set_error("stft_mask2048: stream sub-ranges are not supported"); return false; }
         const int nd = (int)I.decls.size();
         h_coef.resize((size_t)nbq * ns);
-        for (int b = 0; b < nbq; ++b)
-            for (int s = 0; s < ns; ++s) {
-                const double* sl = q + ((size_t)b * ns + s) * nd;
-                StftCoef& c = h_coef[(size_t)b * ns + s];
-                if (b > 0 && std::memcmp(sl, sl - (size_t)ns * nd, sizeof(double) * nd) == 0) c = h_coef[(size_t)(b - 1) * ns + s];
-                else stft_slider(sl, I.srate, c);
-            }
+        parallel_for(ns, 64, [&](int64_t sb, int64_t se) {
+            for (int b = 0; b < nbq; ++b)
+                for (int64_t s = sb; s < se; ++s) {
+                    const double* sl = q + ((size_t)b * ns + s) * nd;
+                    StftCoef& c = h_coef[(size_t)b * ns + s];
+                    if (b > 0 && std::memcmp(sl, sl - (size_t)ns * nd, sizeof(double) * nd) == 0) c = h_coef[(size_t)(b - 1) * ns + s];
+                    else stft_slider(sl, I.srate, c);
+                }
+        });
         if (h_coef.size() > coef_cap) {
             cudaFree(d_coef);
             if (!cuda_ok(cudaMalloc(&d_coef, h_coef.size() * sizeof(StftCoef)), "stft coef")) { coef_cap = 0; d_coef = nullptr; return false; }
@@ -98,9 +113,9 @@ public:
         StftArgs a{};
         a.in = in; a.out = out; a.tap = tap; a.row_stride = stride; a.n_frames = n; a.t0 = t_abs;
         a.n_streams = ns; a.block_len = I.block_len; a.n_coef_blocks = nbq; a.coef = d_coef; a.state = d_state;
-        a.win = d_tab; a.syn = d_tab + kStftN; a.tw = d_tab + 2 * kStftN;
+        a.win = d_tab; a.syn = d_tab + kStftN; a.tw1 = d_tab + 2 * kStftN; a.tw2 = a.tw1 + 2 * 15 * 128;
         const bool timed = I.time_begin();
-        if (!stft_launch(a, I.precision, I.stream)) return false;
+        if (!stft_launch(a, I.precision, n_sm, I.stream)) return false;
         if (timed) I.time_end();
         ++I.launches;
         t_abs += n;

@@ -113,12 +113,14 @@ static bool process_range(Instance& I, const float* params, int n_param_blocks, 
         // quantise the whole automation trajectory once (pushParamsToStateSliders per host block, :9286-9357)
         const int nbq = (params && n_param_blocks > 0) ? (int)std::min<int64_t>(n_param_blocks, n_blocks) : 1;
         std::vector<double> q((size_t)nbq * ns * nd);
-        for (int b = 0; b < nbq; ++b)
-            for (int s = 0; s < ns; ++s)
-                for (int j = 0; j < nd; ++j)
-                    q[((size_t)b * ns + s) * nd + j] = (params && n_param_blocks > 0)
-                        ? quantise_slider(I.decls[j], params[((size_t)b * I.n_streams + s0 + s) * nd + j])
-                        : I.sliders[(size_t)(s0 + s) * nd + j];
+        parallel_for(nbq, 8, [&](int64_t b0, int64_t b1) {
+            for (int64_t b = b0; b < b1; ++b)
+                for (int s = 0; s < ns; ++s)
+                    for (int j = 0; j < nd; ++j)
+                        q[((size_t)b * ns + s) * nd + j] = (params && n_param_blocks > 0)
+                            ? quantise_slider(I.decls[j], params[((size_t)b * I.n_streams + s0 + s) * nd + j])
+                            : I.sliders[(size_t)(s0 + s) * nd + j];
+        });
         for (int s = 0; s < ns; ++s) {
             for (int j = 0; j < nd; ++j) I.sliders[(size_t)(s0 + s) * nd + j] = q[((size_t)(nbq - 1) * ns + s) * nd + j];
             I.sliders_valid[s0 + s] = 1;

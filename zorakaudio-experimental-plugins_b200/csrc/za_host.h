@@ -2,8 +2,10 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <algorithm>
 #include <memory>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/za_gpu.h"
@@ -20,6 +22,25 @@ struct SliderDecl {          // JsfxSliderDecl, src/JSFXJuceProcessor.cpp:520-54
 
 std::vector<SliderDecl> parse_slider_decls(const char* jsfx_text);
 double quantise_slider(const SliderDecl& d, float host_value);
+
+// Host-side data parallelism for the parameter path (quantiser + @slider over [block][stream] rows):
+// f(begin, end) over [0, n) on up to 32 host threads; runs inline below `grain` items.
+template <class F>
+inline void parallel_for(int64_t n, int64_t grain, F&& f)
+{
+    unsigned hw = std::thread::hardware_concurrency();
+    int64_t nt = std::min<int64_t>(hw ? hw : 1, 32);
+    nt = std::min<int64_t>(nt, (n + grain - 1) / std::max<int64_t>(grain, 1));
+    if (nt <= 1) { f((int64_t)0, n); return; }
+    std::vector<std::thread> th;
+    const int64_t per = (n + nt - 1) / nt;
+    for (int64_t t = 0; t < nt; ++t) {
+        const int64_t b = t * per, e = std::min<int64_t>(n, b + per);
+        if (b >= e) break;
+        th.emplace_back([&f, b, e] { f(b, e); });
+    }
+    for (auto& x : th) x.join();
+}
 
 struct Instance;
 

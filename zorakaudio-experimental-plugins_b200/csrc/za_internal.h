@@ -72,7 +72,7 @@ bool easyexpander_launch(const EEArgs& a, int precision, cudaStream_t stream);
 // ---- stft_mask2048 (STFT class) ---------------------------------------------------------------------
 constexpr int kStftN = 2048, kStftHop = 512, kStftBins = 1025;
 struct StftState {               // per stream, persists across calls (the reference keeps these in mem[])
-    float xin[2][5 * kStftHop];  // last five hops of input (slot = absolute hop index mod 5)
+    float xin[2][4 * kStftHop];  // last four hops of input (slot = absolute hop index mod 4)
     double acc[2][kStftN];       // overlap-add accumulator (slot = absolute hop index mod 4)
     double base[kStftBins + 3];  // per-bin baseline EMA
     double prev[kStftBins + 3];  // per-bin previous magnitude
@@ -86,9 +86,10 @@ struct StftArgs {
     int n_streams, block_len, n_coef_blocks;
     const StftCoef* coef;                          // [n_coef_blocks][n_streams]
     StftState* state;                              // [n_streams]
-    const double* win; const double* syn; const double* tw;    // [2048], [2048], [1024][2]
+    const double* win; const double* syn;          // [2048] analysis window, [2048] synthesis window x 1/N
+    const double* tw1; const double* tw2;          // [15][128][2] exp(-2 pi i t q / 2048), [15][8][2] exp(-2 pi i j q / 128)
 };
 size_t stft_state_bytes();
-bool stft_launch(const StftArgs& a, int precision, cudaStream_t stream);
+bool stft_launch(const StftArgs& a, int precision, int n_sm, cudaStream_t stream);
 
 }  // namespace za
