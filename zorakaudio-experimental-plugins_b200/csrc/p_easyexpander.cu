@@ -72,6 +72,7 @@ class EasyExpander : public PluginImpl {
     double* d_state = nullptr;
     EECoef* d_coef = nullptr;
     size_t coef_cap = 0;
+    int n_sm = 148;
     std::vector<EECoef> h_coef;
 
 public:
@@ -80,6 +81,9 @@ public:
     bool create(Instance& I) override
     {
         ee_init(I.srate, k_);
+        cudaDeviceProp prop;
+        if (!cuda_ok(cudaGetDeviceProperties(&prop, I.device), "device properties")) return false;
+        n_sm = prop.multiProcessorCount;
         return cuda_ok(cudaMalloc(&d_state, (size_t)I.n_streams * kEEState * sizeof(double)), "EasyExpander state");
     }
 
@@ -136,7 +140,7 @@ public:
         a.in = in; a.out = out; a.tap = tap; a.row_stride = stride; a.n_frames = n;
         a.n_streams = ns; a.block_len = I.block_len; a.n_coef_blocks = nbq; a.coef = d_coef; a.state = d_state; a.k = k_;
         const bool timed = I.time_begin();
-        if (!easyexpander_launch(a, I.precision, I.stream)) return false;
+        if (!easyexpander_launch(a, I.precision, n_sm, I.stream)) return false;
         if (timed) I.time_end();
         ++I.launches;
         // h_coef is pageable: the async copy was staged by the runtime before returning
