@@ -36,12 +36,13 @@ constexpr int kInBufs = 4;        // a batch's input lives from S0 to S4
 constexpr int kPitchF = kF + 1;   // [stream][frame] rows read with lane = stream
 constexpr int kInPitch = 2 * kPitchF + 1;
 constexpr int kBpStream = kF * 9 + 8;
+constexpr int kCoefRing = 4;      // host blocks alive between the filter warp (first) and the gain warp (last) when block_len >= kF
 
 template <typename R> __device__ __forceinline__ R div_(R a, R b);
 template <> __device__ __forceinline__ double div_<double>(double a, double b) { return __ddiv_rn(a, b); }
 template <> __device__ __forceinline__ float div_<float>(float a, float b) { return __fdividef(a, b); }
 __device__ __forceinline__ double sqrt_(double a) { return __dsqrt_rn(a); }
-__device__ __forceinline__ float sqrt_(float a) { return sqrtf(a); }
+__device__ __forceinline__ float sqrt_(float a) { return a * rsqrtf(a); }    // a >= 1e-12 here; 2 ulp, no slow-path branch
 __device__ __forceinline__ double log_(double a) { return log(a); }
 __device__ __forceinline__ float log_(float a) { return __logf(a); }
 __device__ __forceinline__ double exp_(double a) { return exp(a); }
@@ -56,6 +57,7 @@ template <typename R> struct EESmem {
     R db[2][kMaxS * kPitchF];                     // det_db
     R tg[2][kMaxS * kPitchF];                     // target reduction if expanding
     R gain[2][kMaxS * kPitchF];                   // gain_db_s after the frame
+    R cs[kCoefRing][3][kMaxS];                    // thresh_db, depth_db, ratio_base of the last host blocks (slot = block & 3)
 };
 
 // host block of frame f (relative to the call), clamped to the coefficient rows there are
@@ -69,6 +71,81 @@ struct BlockMap {
 };
 
 }  // namespace
+
+// ---- stage bodies over one group of 8 frames; FULL = every frame of the group exists (no per-frame branches, so the
+// ---- compiler can interleave the frames' off-chain work with the recurrence) ---------------------------------------
+template <typename R> struct BandK { R g, den, wj, band_c, a1, a2, bx, g2; };
+
+template <typename R, bool FULL>
+__device__ __forceinline__ void band_group(const R* xd, R* bpw, int f0, int nv, const BandK<R>& c, R& ic1, R& ic2, R& env)
+{
+    R xv[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) xv[k] = xd[f0 + k];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        if (FULL || f0 + k < nv) {
+            // svf_bp (:74-93)
+            R v1;
+            if (sizeof(R) == 4) {
+                // float: the same recurrence in state-space form (shorter dependent chain)
+                v1 = fma_(c.a1, ic1, fma_(c.a2, ic2, mul(c.bx, xv[k])));
+                ic1 = fma_((R)2.0, v1, -ic1);
+                ic2 = fma_(c.g2, v1, ic2);
+            } else {
+                v1 = div_<R>(add(mul(c.g, sub(xv[k], ic2)), ic1), c.den);
+                const R v2 = add(ic2, mul(c.g, v1));
+                ic1 = sub(mul((R)2.0, v1), ic1);
+                ic2 = sub(mul((R)2.0, v2), ic2);
+            }
+            const R p = mul(v1, v1);
+            env = add(env, mul(c.band_c, sub(p, env)));
+            bpw[(f0 + k) * 9] = mul(c.wj, env);
+        }
+    }
+}
+
+template <typename R> struct FiltS { R hpf_lp, lpf_y, hpf_c, lpf_c; int hpf_on, lpf_on; };
+
+template <typename R, bool FULL>
+__device__ __forceinline__ void filter_group(const float* ib, R* xd, int f0, int nv, FiltS<R>& s)
+{
+    float lv[8], rv[8];
+    R xo[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { lv[k] = ib[f0 + k]; rv[k] = ib[kPitchF + f0 + k]; }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        R x_det = mul((R)0.5, add((R)lv[k], (R)rv[k]));
+        if (FULL || f0 + k < nv) {                                  // state must not advance past the end of the call
+            if (s.hpf_on) { s.hpf_lp = add(s.hpf_lp, mul(s.hpf_c, sub(x_det, s.hpf_lp))); x_det = sub(x_det, s.hpf_lp); }
+            if (s.lpf_on) { s.lpf_y = add(s.lpf_y, mul(s.lpf_c, sub(x_det, s.lpf_y))); x_det = s.lpf_y; }
+        }
+        xo[k] = x_det;
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) xd[f0 + k] = xo[k];
+}
+
+template <typename R> struct GainS { R det_slow, gain_db_s, det_db_m, gr_db_m, thresh_db, thresh_hi; int expanding; };
+template <typename R> struct GainK { R open_c, close_fast_c, close_slow_c, slow_c; };
+
+template <typename R>
+__device__ __forceinline__ void gain_frame(R det_lin, R det_db, R tgv, const GainK<R>& c, GainS<R>& s)
+{
+    s.det_db_m = add(s.det_db_m, mul((R)0.02, sub(det_db, s.det_db_m)));
+    s.det_slow = add(s.det_slow, mul(c.slow_c, sub(det_lin, s.det_slow)));
+    if (s.expanding == 0) { if (det_db < s.thresh_db) s.expanding = 1; }
+    else                  { if (det_db > s.thresh_hi) s.expanding = 0; }
+    const R target_gr = s.expanding ? tgv : (R)0.0;
+    const R target_gain_db = -target_gr;
+    s.gr_db_m = add(s.gr_db_m, mul((R)0.05, sub(target_gr, s.gr_db_m)));
+    const R close_c = (det_lin < mul(s.det_slow, (R)0.92)) ? c.close_fast_c : c.close_slow_c;
+    // gain_db_s += (target > gain ? open_c : close_c) * (target - gain): both candidates, then select
+    const R dlt = sub(target_gain_db, s.gain_db_s);
+    const R g_open = add(s.gain_db_s, mul(c.open_c, dlt)), g_close = add(s.gain_db_s, mul(close_c, dlt));
+    s.gain_db_s = (target_gain_db > s.gain_db_s) ? g_open : g_close;
+}
 
 // state layout in HBM: double [kEEState][n_streams] (structure of arrays, stream-minor)
 //   0..7 ic1[b], 8..15 ic2[b], 16..23 env[b], 24 hpf_lp, 25 lpf_y, 26 det_slow, 27 expanding,
@@ -86,6 +163,7 @@ easyexpander_kernel(const EEArgs a, const int spc /* streams per CTA, multiple o
     const int64_t n = a.n_frames;
     const int64_t n_batches = (n + kF - 1) / kF;
     const BlockMap bm{a.block_len, a.n_coef_blocks};
+    const bool smem_coef = a.block_len >= kF;                  // else a batch may span more host blocks than the ring holds
 
     const R eps = (R)1e-12, db_per_ln = (R)8.685889638065037, ln_per_db = (R)0.115129254649702;
     const R knee_db = (R)6.0, hys_db = (R)2.0;
@@ -97,92 +175,107 @@ easyexpander_kernel(const EEArgs a, const int spc /* streams per CTA, multiple o
         const bool act = 4 * warp < ns_cta;                    // warp has streams at all
         const bool live = ls < ns_cta;
         const int sg = s_base + (live ? ls : (ns_cta - 1));    // clamped global stream (loads stay in range)
-        const R g = (R)a.k.g[j], den = (R)a.k.den[j], wj = (R)a.k.w[j], band_c = (R)a.k.band_c;
+        // float state-space form of svf_bp: v1 = a1 ic1 + a2 ic2 + bx x; ic1' = 2 v1 - ic1; ic2' = ic2 + 2 g v1
+        const BandK<R> bk{(R)a.k.g[j], (R)a.k.den[j], (R)a.k.w[j], (R)a.k.band_c, (R)(1.0 / a.k.den[j]),
+                          (R)(-a.k.g[j] / a.k.den[j]), (R)(a.k.g[j] / a.k.den[j]), (R)(2.0 * a.k.g[j])};
         double* st = a.state + sg;
         R ic1 = (R)st[(0 + j) * ns], ic2 = (R)st[(8 + j) * ns], env = (R)st[(16 + j) * ns];
         R* bp = sm.bp[warp];
         float hold[4][2];
+        int64_t next2 = a.block_len;                          // first frame of host block blk2 + 1 (S2's own block tracking)
+        int blk2 = 0;
+        // lane = frame stages: rows of this warp's four streams (clamped so loads stay in range)
+        const float* irow[4]; float* orow[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const size_t s = (size_t)(s_base + min(4 * warp + q, max(ns_cta - 1, 0)));
+            irow[q] = a.in + s * 2 * a.row_stride + lane; orow[q] = a.out + s * 2 * a.row_stride + lane;
+        }
 
         for (int64_t i = 0; i < n_batches + 4; ++i) {
             if (act) {
                 // ---- S0 (issue): batch i, lane = frame ------------------------------------------------
-                const int64_t f0 = i * kF + lane;
+                {
+                    const int64_t fo = i * kF;
+                    const bool ok = i < n_batches && fo + lane < n;
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    const int s = s_base + min(4 * warp + q, ns_cta - 1);
-                    const float* row = a.in + (size_t)s * 2 * a.row_stride;
-                    const bool ok = i < n_batches && f0 < n;
-                    hold[q][0] = ok ? row[f0] : 0.f;
-                    hold[q][1] = ok ? row[a.row_stride + f0] : 0.f;
+                    for (int q = 0; q < 4; ++q) {
+                        hold[q][0] = ok ? irow[q][fo] : 0.f;
+                        hold[q][1] = ok ? irow[q][a.row_stride + fo] : 0.f;
+                    }
                 }
                 // ---- S2: batch i-2, lane = (stream, band), frames in order ------------------------------
                 if (i >= 2 && i - 2 < n_batches) {
                     const int64_t b = i - 2;
                     const R* xd = sm.xd[b & 1] + ls * kPitchF;
                     const int nv = (int)min((int64_t)kF, n - b * kF);
-#pragma unroll 8
-                    for (int f = 0; f < kF; ++f) {
-                        if (f < nv) {
-                            const R x_det = xd[f];
-                            // svf_bp (:74-93)
-                            const R v1 = div_<R>(add(mul(g, sub(x_det, ic2)), ic1), den);
-                            const R v2 = add(ic2, mul(g, v1));
-                            ic1 = sub(mul((R)2.0, v1), ic1);
-                            ic2 = sub(mul((R)2.0, v2), ic2);
-                            const R p = mul(v1, v1);
-                            env = add(env, mul(band_c, sub(p, env)));
-                            bp[sl * kBpStream + f * 9 + j] = mul(wj, env);
-                        }
+                    R* bpw = bp + sl * kBpStream + j;
+                    if (nv == kF) {
+#pragma unroll 1
+                        for (int f0 = 0; f0 < kF; f0 += 8) band_group<R, true>(xd, bpw, f0, nv, bk, ic1, ic2, env);
+                    } else {
+#pragma unroll 1
+                        for (int f0 = 0; f0 < kF; f0 += 8) band_group<R, false>(xd, bpw, f0, nv, bk, ic1, ic2, env);
                     }
                     __syncwarp();
                     // lane = frame: band sum in reference order, sqrt, log, memoryless gain computer
-                    const int64_t fr = b * kF + lane;
-                    const int row = bm.row(fr < n ? fr : n - 1);
+                    const int64_t F0 = b * kF;
+                    while (F0 >= next2) { ++blk2; next2 += a.block_len; }
+                    const int64_t fr = F0 + lane;
+                    const int blk = smem_coef ? (blk2 + (fr >= next2 ? 1 : 0)) : bm.row(fr < n ? fr : n - 1);
+                    R det_lin[4], det_db[4], thr[4], dep[4], rat[4];
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
                         const int lq = 4 * warp + q;
-                        const int s = s_base + min(lq, ns_cta - 1);
                         R sum = (R)0.0;
 #pragma unroll
                         for (int bnd = 0; bnd < 8; ++bnd) sum = add(sum, bp[q * kBpStream + lane * 9 + bnd]);
-                        const R det_lin = sqrt_(jmax(sum, eps));
-                        const R det_db = mul(db_per_ln, log_(jmax(det_lin, eps)));
-                        const EECoef& c = a.coef[(size_t)row * ns + s];
-                        const R thresh_db = (R)c.thresh_db, depth_db = (R)c.depth_db, ratio_base = (R)c.ratio_base;
-                        R d = sub(thresh_db, det_db);
-                        if (d < (R)0.0) d = (R)0.0;
-                        R ratio_eff;
-                        if (d < knee_db) {
-                            const R xk = div_<R>(d, knee_db);
-                            const R smo = mul(mul(xk, xk), sub((R)3.0, mul((R)2.0, xk)));
-                            ratio_eff = add((R)1.0, mul(sub(ratio_base, (R)1.0), smo));
+                        det_lin[q] = sqrt_(jmax(sum, eps));
+                        if (smem_coef) {
+                            thr[q] = sm.cs[blk & (kCoefRing - 1)][0][lq]; dep[q] = sm.cs[blk & (kCoefRing - 1)][1][lq];
+                            rat[q] = sm.cs[blk & (kCoefRing - 1)][2][lq];
                         } else {
-                            ratio_eff = ratio_base;
+                            const EECoef& c = a.coef[(size_t)blk * ns + s_base + min(lq, ns_cta - 1)];
+                            thr[q] = (R)c.thresh_db; dep[q] = (R)c.depth_db; rat[q] = (R)c.ratio_base;
                         }
+                    }
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) det_db[q] = mul(db_per_ln, log_(jmax(det_lin[q], eps)));
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        R d = sub(thr[q], det_db[q]);
+                        if (d < (R)0.0) d = (R)0.0;
+                        const R xk = div_<R>(d, knee_db);
+                        const R smo = mul(mul(xk, xk), sub((R)3.0, mul((R)2.0, xk)));
+                        const R ratio_eff = (d < knee_db) ? add((R)1.0, mul(sub(rat[q], (R)1.0), smo)) : rat[q];
                         R target_gr = mul(d, sub(ratio_eff, (R)1.0));
-                        if (target_gr > depth_db) target_gr = depth_db;
-                        const int o = lq * kPitchF + lane;
-                        sm.lin[b & 1][o] = det_lin; sm.db[b & 1][o] = det_db; sm.tg[b & 1][o] = target_gr;
+                        if (target_gr > dep[q]) target_gr = dep[q];
+                        const int o = (4 * warp + q) * kPitchF + lane;
+                        sm.lin[b & 1][o] = det_lin[q]; sm.db[b & 1][o] = det_db[q]; sm.tg[b & 1][o] = target_gr;
                     }
                     __syncwarp();
                 }
                 // ---- S4: batch i-4, lane = frame: exp and the output multiplies ----------------------------
                 if (i >= 4) {
                     const int64_t b = i - 4;
-                    const int64_t fr = b * kF + lane;
+                    const int64_t fo = b * kF;
+                    const bool okf = fo + lane < n;
                     const float* ib = sm.in[b & (kInBufs - 1)];
+                    R o0[4], o1[4];
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
                         const int lq = 4 * warp + q;
-                        if (lq < ns_cta && fr < n) {
-                            const R gain_lin = exp_(mul(sm.gain[b & 1][lq * kPitchF + lane], ln_per_db));
-                            const R o0 = mul((R)ib[lq * kInPitch + lane], gain_lin);
-                            const R o1 = mul((R)ib[lq * kInPitch + kPitchF + lane], gain_lin);
-                            float* orow = a.out + (size_t)(s_base + lq) * 2 * a.row_stride;
-                            orow[fr] = (float)o0; orow[a.row_stride + fr] = (float)o1;
+                        const R gain_lin = exp_(mul(sm.gain[b & 1][lq * kPitchF + lane], ln_per_db));
+                        o0[q] = mul((R)ib[lq * kInPitch + lane], gain_lin);
+                        o1[q] = mul((R)ib[lq * kInPitch + kPitchF + lane], gain_lin);
+                    }
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        if (okf && 4 * warp + q < ns_cta) {
+                            orow[q][fo] = (float)o0[q]; orow[q][a.row_stride + fo] = (float)o1[q];
                             if (TAP) {
-                                double* tp = a.tap + (size_t)(s_base + lq) * 2 * a.row_stride + fr;
-                                tp[0] = (double)o0; tp[a.row_stride] = (double)o1;
+                                double* tp = a.tap + (orow[q] - a.out) + fo;
+                                tp[0] = (double)o0[q]; tp[a.row_stride] = (double)o1[q];
                             }
                         }
                     }
@@ -208,9 +301,7 @@ easyexpander_kernel(const EEArgs a, const int spc /* streams per CTA, multiple o
         const bool live = lane < ns_cta;
         const int sg = s_base + (live ? lane : 0);
         double* st = a.state + sg;
-        R hpf_lp = (R)st[24 * ns], lpf_y = (R)st[25 * ns];
-        R hpf_c = 0, lpf_c = 0;
-        int hpf_on = 0, lpf_on = 0;
+        FiltS<R> fs{(R)st[24 * ns], (R)st[25 * ns], (R)0, (R)0, 0, 0};
         int64_t next_block_frame = 0;
         int blk = 0;
         for (int64_t i = 0; i < n_batches + 4; ++i) {
@@ -219,36 +310,44 @@ easyexpander_kernel(const EEArgs a, const int spc /* streams per CTA, multiple o
                 const float* ib = sm.in[b & (kInBufs - 1)] + lane * kInPitch;
                 R* xd = sm.xd[b & 1] + lane * kPitchF;
                 const int nv = (int)min((int64_t)kF, n - b * kF);
-                int fb = (int)min((int64_t)kF, next_block_frame - b * kF);    // frame of the batch where the next host block starts
-#pragma unroll 8
-                for (int f = 0; f < kF; ++f) {
-                    if (f < nv) {
-                        if (f == fb) {                                 // host-block boundary: sliders sampled once per block
-                            const EECoef& c = a.coef[(size_t)(blk < a.n_coef_blocks ? blk : a.n_coef_blocks - 1) * ns + sg];
-                            hpf_c = (R)c.hpf_c; lpf_c = (R)c.lpf_c; hpf_on = c.hpf_on; lpf_on = c.lpf_on;
-                            ++blk; next_block_frame += a.block_len;
-                            fb = (int)min((int64_t)kF, next_block_frame - b * kF);
+#pragma unroll 1
+                for (int f0 = 0; f0 < kF; f0 += 8) {
+                    // host-block boundaries inside this group? (sliders are sampled once per block)
+                    const int64_t g0 = b * kF + f0;
+                    if (next_block_frame >= g0 + 8 && f0 + 8 <= nv) {
+                        filter_group<R, true>(ib, xd, f0, nv, fs);
+                    } else {
+                        // at most the group's frames individually, reloading the coefficients where a block starts
+                        for (int k = 0; k < 8; ++k) {
+                            const int f = f0 + k;
+                            if (f < nv && b * kF + f >= next_block_frame) {
+                                const EECoef& c = a.coef[(size_t)(blk < a.n_coef_blocks ? blk : a.n_coef_blocks - 1) * ns + sg];
+                                fs.hpf_c = (R)c.hpf_c; fs.lpf_c = (R)c.lpf_c; fs.hpf_on = c.hpf_on; fs.lpf_on = c.lpf_on;
+                                sm.cs[blk & (kCoefRing - 1)][0][lane] = (R)c.thresh_db;
+                                sm.cs[blk & (kCoefRing - 1)][1][lane] = (R)c.depth_db;
+                                sm.cs[blk & (kCoefRing - 1)][2][lane] = (R)c.ratio_base;
+                                ++blk; next_block_frame += a.block_len;
+                            }
+                            R x_det = mul((R)0.5, add((R)ib[f], (R)ib[kPitchF + f]));
+                            if (f < nv) {
+                                if (fs.hpf_on) { fs.hpf_lp = add(fs.hpf_lp, mul(fs.hpf_c, sub(x_det, fs.hpf_lp))); x_det = sub(x_det, fs.hpf_lp); }
+                                if (fs.lpf_on) { fs.lpf_y = add(fs.lpf_y, mul(fs.lpf_c, sub(x_det, fs.lpf_y))); x_det = fs.lpf_y; }
+                            }
+                            xd[f] = x_det;
                         }
-                        R x_det = mul((R)0.5, add((R)ib[f], (R)ib[kPitchF + f]));
-                        if (hpf_on) { hpf_lp = add(hpf_lp, mul(hpf_c, sub(x_det, hpf_lp))); x_det = sub(x_det, hpf_lp); }
-                        if (lpf_on) { lpf_y = add(lpf_y, mul(lpf_c, sub(x_det, lpf_y))); x_det = lpf_y; }
-                        xd[f] = x_det;
                     }
                 }
             }
             __syncthreads();
         }
-        if (live) { st[24 * ns] = (double)hpf_lp; st[25 * ns] = (double)lpf_y; }
+        if (live) { st[24 * ns] = (double)fs.hpf_lp; st[25 * ns] = (double)fs.lpf_y; }
     } else {
         // ============================ gain warp: lane = stream ============================================
         const bool live = lane < ns_cta;
         const int sg = s_base + (live ? lane : 0);
         double* st = a.state + sg;
-        const R open_c = (R)a.k.open_c, close_fast_c = (R)a.k.close_fast_c, close_slow_c = (R)a.k.close_slow_c, slow_c = (R)a.k.slow_c;
-        R det_slow = (R)st[26 * ns];
-        int expanding = st[27 * ns] != 0.0;
-        R gain_db_s = (R)st[28 * ns], det_db_m = (R)st[29 * ns], gr_db_m = (R)st[30 * ns];
-        R thresh_db = 0, thresh_hi = 0;
+        const GainK<R> gk{(R)a.k.open_c, (R)a.k.close_fast_c, (R)a.k.close_slow_c, (R)a.k.slow_c};
+        GainS<R> gs{(R)st[26 * ns], (R)st[28 * ns], (R)st[29 * ns], (R)st[30 * ns], (R)0, (R)0, st[27 * ns] != 0.0};
         int64_t next_block_frame = 0;
         int blk = 0;
         for (int64_t i = 0; i < n_batches + 4; ++i) {
@@ -258,36 +357,40 @@ easyexpander_kernel(const EEArgs a, const int spc /* streams per CTA, multiple o
                 const R* lin = sm.lin[b & 1] + o; const R* db = sm.db[b & 1] + o; const R* tg = sm.tg[b & 1] + o;
                 R* gout = sm.gain[b & 1] + o;
                 const int nv = (int)min((int64_t)kF, n - b * kF);
-                int fb = (int)min((int64_t)kF, next_block_frame - b * kF);
-#pragma unroll 8
-                for (int f = 0; f < kF; ++f) {
-                    if (f < nv) {
-                        if (f == fb) {
-                            const EECoef& c = a.coef[(size_t)(blk < a.n_coef_blocks ? blk : a.n_coef_blocks - 1) * ns + sg];
-                            thresh_db = (R)c.thresh_db; thresh_hi = add(thresh_db, hys_db);
-                            ++blk; next_block_frame += a.block_len;
-                            fb = (int)min((int64_t)kF, next_block_frame - b * kF);
+#pragma unroll 1
+                for (int f0 = 0; f0 < kF; f0 += 8) {
+                    R lv[8], dv[8], tv[8], go[8];
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) { lv[k] = lin[f0 + k]; dv[k] = db[f0 + k]; tv[k] = tg[f0 + k]; }
+                    const int64_t g0 = b * kF + f0;
+                    if (next_block_frame >= g0 + 8 && f0 + 8 <= nv) {
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) { gain_frame<R>(lv[k], dv[k], tv[k], gk, gs); go[k] = gs.gain_db_s; }
+                    } else {
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) {
+                            const int f = f0 + k;
+                            if (f < nv) {
+                                if (g0 + k >= next_block_frame) {
+                                    if (smem_coef) gs.thresh_db = sm.cs[blk & (kCoefRing - 1)][0][lane];
+                                    else gs.thresh_db = (R)a.coef[(size_t)(blk < a.n_coef_blocks ? blk : a.n_coef_blocks - 1) * ns + sg].thresh_db;
+                                    gs.thresh_hi = add(gs.thresh_db, hys_db);
+                                    ++blk; next_block_frame += a.block_len;
+                                }
+                                gain_frame<R>(lv[k], dv[k], tv[k], gk, gs);
+                            }
+                            go[k] = gs.gain_db_s;
                         }
-                        const R det_lin = lin[f], det_db = db[f];
-                        det_db_m = add(det_db_m, mul((R)0.02, sub(det_db, det_db_m)));
-                        det_slow = add(det_slow, mul(slow_c, sub(det_lin, det_slow)));
-                        if (expanding == 0) { if (det_db < thresh_db) expanding = 1; }
-                        else                { if (det_db > thresh_hi) expanding = 0; }
-                        const R target_gr = expanding ? tg[f] : (R)0.0;
-                        const R target_gain_db = -target_gr;
-                        gr_db_m = add(gr_db_m, mul((R)0.05, sub(target_gr, gr_db_m)));
-                        const R close_c = (det_lin < mul(det_slow, (R)0.92)) ? close_fast_c : close_slow_c;
-                        const R cc = (target_gain_db > gain_db_s) ? open_c : close_c;
-                        gain_db_s = add(gain_db_s, mul(cc, sub(target_gain_db, gain_db_s)));
-                        gout[f] = gain_db_s;
                     }
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) gout[f0 + k] = go[k];
                 }
             }
             __syncthreads();
         }
         if (live) {
-            st[26 * ns] = (double)det_slow; st[27 * ns] = expanding ? 1.0 : 0.0; st[28 * ns] = (double)gain_db_s;
-            st[29 * ns] = (double)det_db_m; st[30 * ns] = (double)gr_db_m;
+            st[26 * ns] = (double)gs.det_slow; st[27 * ns] = gs.expanding ? 1.0 : 0.0; st[28 * ns] = (double)gs.gain_db_s;
+            st[29 * ns] = (double)gs.det_db_m; st[30 * ns] = (double)gs.gr_db_m;
         }
     }
 }
