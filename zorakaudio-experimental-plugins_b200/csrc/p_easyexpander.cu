@@ -67,16 +67,62 @@ void ee_slider(const double* sl, double srate, EECoef& c)
     c.lpf_c = c.lpf_on ? (1.0 - std::exp(-2.0 * kPi * sl[4] / srate)) : 0.0;
 }
 
+// ---- device-side parameter path ------------------------------------------------------------------------------
+struct SliderQ { double mn, mx, step; int is_choice; };          // quantise_slider's inputs (za_params.cpp)
+
+__device__ __forceinline__ double quantise_dev(const SliderQ& d, float host_value)   // = za::quantise_slider, same operations
+{
+    double v = (double)host_value;
+    if (d.is_choice) v = __dadd_rn(d.mn, __dmul_rn((double)llround(v), d.step));
+    v = v < d.mn ? d.mn : (v > d.mx ? d.mx : v);
+    if (!d.is_choice && d.step > 0.0) {
+        const double q = (double)llround(__ddiv_rn(__dsub_rn(v, d.mn), d.step));
+        v = __dadd_rn(d.mn, __dmul_rn(q, d.step));
+        v = v < d.mn ? d.mn : (v > d.mx ? d.mx : v);
+    }
+    return v;
+}
+
+struct EEParamArgs {
+    const float* params;       // [nb][ns][5] raw host values (device copy)
+    const EECoef* per_stream;  // [ns]: hpf/lpf part of @slider, computed on the host with glibc (constant over the call)
+    EECoef* out;               // [nb][ns]
+    int nb, ns;
+    SliderQ q[5];
+};
+
+// One thread per (block, stream): quantise threshold / depth / contour exactly as the host does and derive the
+// @slider values that need no libm (EasyExpander.jsfx:154-160).
+__global__ void ee_param_kernel(const EEParamArgs a)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (int64_t)a.nb * a.ns) return;
+    const int s = (int)(i % a.ns);
+    const float* p = a.params + i * 5;
+    EECoef c = a.per_stream[s];
+    c.thresh_db = quantise_dev(a.q[0], p[0]);
+    c.depth_db = quantise_dev(a.q[1], p[1]);
+    const double cont = __ddiv_rn(quantise_dev(a.q[2], p[2]), 100.0);
+    const double rb = __dadd_rn(1.5, __dmul_rn(2.5, cont));
+    c.ratio_base = rb < 1.0 ? 1.0 : rb;
+    a.out[i] = c;
+}
+
 class EasyExpander : public PluginImpl {
     EEConsts k_{};
     double* d_state = nullptr;
     EECoef* d_coef = nullptr;
     size_t coef_cap = 0;
+    float* d_params = nullptr;        // raw automation rows of the current call
+    size_t params_cap = 0;
+    EECoef* d_per_stream = nullptr;
+    cudaEvent_t ev_params = nullptr, ev_consumed = nullptr;   // upload done / previous rows consumed
+    cudaStream_t up_stream = nullptr; // uploads overlap the previous call's kernel
     int n_sm = 148;
     std::vector<EECoef> h_coef;
 
 public:
-    ~EasyExpander() override { cudaFree(d_state); cudaFree(d_coef); }
+    ~EasyExpander() override { cudaFree(d_state); cudaFree(d_coef); cudaFree(d_params); cudaFree(d_per_stream); if (ev_params) cudaEventDestroy(ev_params); if (ev_consumed) cudaEventDestroy(ev_consumed); if (up_stream) cudaStreamDestroy(up_stream); }
 
     bool create(Instance& I) override
     {
@@ -145,6 +191,75 @@ public:
         ++I.launches;
         // h_coef is pageable: the async copy was staged by the runtime before returning
         return true;
+    }
+
+    // Automation on the device: upload the raw float rows, quantise + derive there.  Applicable when the detector
+    // filter sliders (the only @slider inputs that go through exp()) do not move inside the call, so their
+    // coefficients come from the host's glibc once per stream and every value stays bit-identical to the host path.
+    int run_blocks_raw(Instance& I, const float* params, int nb, const float* in, float* out, double* tap,
+                       int64_t n, int64_t stride) override
+    {
+        const int ns = I.n_streams, nd = (int)I.decls.size();
+        if (nd != 5) return 0;
+        std::vector<uint8_t> moved(ns, 0);
+        parallel_for(ns, 64, [&](int64_t sb, int64_t se) {
+            for (int64_t s = sb; s < se; ++s) {
+                const float h = params[(size_t)s * nd + 3], l = params[(size_t)s * nd + 4];
+                for (int b = 1; b < nb; ++b) {
+                    const float* p = params + ((size_t)b * ns + s) * nd;
+                    if (p[3] != h || p[4] != l) { moved[s] = 1; break; }
+                }
+            }
+        });
+        for (int s = 0; s < ns; ++s) if (moved[s]) return 0;
+        std::vector<EECoef> ps(ns);
+        for (int s = 0; s < ns; ++s) {
+            double sl[5];
+            for (int j = 0; j < 5; ++j) sl[j] = quantise_slider(I.decls[j], params[(size_t)s * nd + j]);
+            ee_slider(sl, I.srate, ps[s]);
+        }
+        const size_t rows = (size_t)nb * ns;
+        if (rows * nd > params_cap) {
+            cudaFree(d_params); d_params = nullptr; params_cap = 0;
+            if (!cuda_ok(cudaMalloc(&d_params, rows * nd * sizeof(float)), "EasyExpander params")) return -1;
+            params_cap = rows * nd;
+        }
+        if (rows > coef_cap) {
+            cudaFree(d_coef); d_coef = nullptr; coef_cap = 0;
+            if (!cuda_ok(cudaMalloc(&d_coef, rows * sizeof(EECoef)), "EasyExpander coef")) return -1;
+            coef_cap = rows;
+        }
+        if (!d_per_stream && !cuda_ok(cudaMalloc(&d_per_stream, (size_t)ns * sizeof(EECoef)), "EasyExpander per-stream coef")) return -1;
+        if (!up_stream) {
+            if (!cuda_ok(cudaStreamCreateWithFlags(&up_stream, cudaStreamNonBlocking), "param upload stream")) return -1;
+            cudaEventCreateWithFlags(&ev_params, cudaEventDisableTiming);
+            cudaEventCreateWithFlags(&ev_consumed, cudaEventDisableTiming);
+        } else {
+            cudaStreamWaitEvent(up_stream, ev_consumed, 0);      // the previous call's parameter kernel has read the buffers
+        }
+        if (!cuda_ok(cudaMemcpyAsync(d_per_stream, ps.data(), ps.size() * sizeof(EECoef), cudaMemcpyHostToDevice, up_stream), "per-stream coef upload") ||
+            !cuda_ok(cudaMemcpyAsync(d_params, params, rows * nd * sizeof(float), cudaMemcpyHostToDevice, up_stream), "params upload"))
+            return -1;
+        cudaEventRecord(ev_params, up_stream);
+        cudaStreamWaitEvent(I.stream, ev_params, 0);
+        EEParamArgs pa{};
+        pa.params = d_params; pa.per_stream = d_per_stream; pa.out = d_coef; pa.nb = nb; pa.ns = ns;
+        for (int j = 0; j < 5; ++j) {
+            const SliderDecl& d = I.decls[j];
+            pa.q[j] = SliderQ{(double)d.min, (double)d.max, (double)(d.step > 0.0f ? d.step : 1.0f), d.is_choice ? 1 : 0};
+        }
+        ee_param_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, I.stream>>>(pa);
+        if (!cuda_ok(cudaGetLastError(), "ee_param_kernel launch")) return -1;
+        cudaEventRecord(ev_consumed, I.stream);
+        ++I.launches;
+        EEArgs a{};
+        a.in = in; a.out = out; a.tap = tap; a.row_stride = stride; a.n_frames = n;
+        a.n_streams = ns; a.block_len = I.block_len; a.n_coef_blocks = nb; a.coef = d_coef; a.state = d_state; a.k = k_;
+        const bool timed = I.time_begin();
+        if (!easyexpander_launch(a, I.precision, n_sm, I.stream)) return -1;
+        if (timed) I.time_end();
+        ++I.launches;
+        return 1;
     }
 
     bool read_state(Instance& I, const char* name, double* out) override

@@ -112,6 +112,18 @@ static bool process_range(Instance& I, const float* params, int n_param_blocks, 
     if (I.impl->takes_block_params()) {
         // quantise the whole automation trajectory once (pushParamsToStateSliders per host block, :9286-9357)
         const int nbq = (params && n_param_blocks > 0) ? (int)std::min<int64_t>(n_param_blocks, n_blocks) : 1;
+        if (params && n_param_blocks > 0 && nbq > 1 && s0 == 0 && ns == I.n_streams) {
+            const int r = I.impl->run_blocks_raw(I, params, nbq, in, out, tap, n_frames, stride);
+            if (r < 0) return false;
+            if (r > 0) {   // st.sliders after the call = the last row, quantised
+                for (int s = 0; s < ns; ++s) {
+                    for (int j = 0; j < nd; ++j)
+                        I.sliders[(size_t)s * nd + j] = quantise_slider(I.decls[j], params[((size_t)(nbq - 1) * ns + s) * nd + j]);
+                    I.sliders_valid[s] = 1;
+                }
+                return true;
+            }
+        }
         std::vector<double> q((size_t)nbq * ns * nd);
         parallel_for(nbq, 8, [&](int64_t b0, int64_t b1) {
             for (int64_t b = b0; b < b1; ++b)

@@ -62,6 +62,10 @@ public:
     // the last row persists.  One launch renders all n frames; @slider semantics (recompute derived
     // coefficients when a value changed, src/JSFXJuceProcessor.cpp:3545-3547) are the plugin's job.
     virtual bool takes_block_params() const { return false; }
+    // Device-side parameter path: the raw host float rows [nb][n_streams][n_decl] of the call are uploaded
+    // and quantised + turned into @slider results by a kernel.  Returns 1 = done, 0 = not applicable for
+    // this call (the caller falls back to the host path), -1 = error.
+    virtual int run_blocks_raw(Instance&, const float*, int, const float*, float*, double*, int64_t, int64_t) { return 0; }
     virtual bool run_blocks(Instance&, int, int, const double*, int, const float*, float*, double*, int64_t, int64_t) { return false; }
 };
 

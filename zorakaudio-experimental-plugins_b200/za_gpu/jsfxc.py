@@ -1,0 +1,714 @@
+"""jsfxc.py -- DSP-JSFX -> CUDA translator for the catalogue's self-contained leaves.
+
+Build-time tool.  Reads a .jsfx script and writes one .cu translation unit holding the script's four
+sections (@init / @slider / @block / @sample) and its user functions as device code for ONE stream per
+thread (register / local-memory resident variables, mem[] as a stream-minor structure-of-arrays heap in
+HBM), plus the descriptor the generic plugin back end (csrc/p_generic.cu) registers.  The product never
+runs this at run time; generated files are committed under csrc/gen/ so the GPU box only compiles them.
+
+Semantics restated from the reference's AOT compiler (file:line in /root/reference/dsp_jsfx_aot.py):
+  * tokens / grammar: newline and ';' separate statements, a newline followed by an infix operator
+    continues the expression (:594-630); precedence table :370-389; prefix + - ! bind tighter than any
+    binary operator (:680-689); `c ? a` without ':' yields 0 (:658-675); ( a; b ) sequences (:790-819);
+    loop(n, body) (:703-739); while (c) body and if (c) a else b keywords (:473-498);
+    function f(a b) local(x) ( body ) (:500-577)
+  * expressions (:4263-5590): all values double; truthiness is `!= 0` exactly (:3725); compares yield
+    1.0 / 0.0 ordered; | & << >> % work on trunc-to-int64 wrapped to int32 (:4107-4110, :4355-4381), shift
+    count & 31, >> arithmetic; ^ is pow(); unary minus is 0 - x; min / max are olt / ogt selects
+    (:5223-5232); sqr, sign (:5234-5247); invsqrt keeps the float bit trick (:5256-5277); rand() is a
+    per-instance MT19937 seeded 0x4141F00D (:3880-4060, :5294-5323); gfx_* / sprintf / str* evaluate
+    their arguments and return 0 (:5200-5212); && || short-circuit and return 1.0 / 0.0 (:5592-5633)
+  * a[b] = mem[trunc(a + b + 1e-5)], negative -> 0 (:4062-4103); assignment evaluates the right-hand side
+    first, then the target address (:4386-4492); memset returns dest (:5439-5495)
+  * loop count: trunc toward 0, negative -> 0, evaluated once (:5663-5707)
+  * user functions are specialised per calling SECTION; local() variables are persistent state named by
+    (section, function, local) (:1844-1848, :1905-2048); parameters are by value
+Not supported (translation fails loudly): instance()/this. namespaces, gmem, fft hooks, midi, file and
+message builtins, sliderchange / slider_automate inside DSP sections, string slider files.
+"""
+from __future__ import annotations
+
+import re
+import sys
+from pathlib import Path
+
+# ------------------------------------------------------------------------------------------------------
+# lexer
+# ------------------------------------------------------------------------------------------------------
+OPS3 = ()
+OPS2 = ("+=", "-=", "*=", "/=", "%=", "^=", "|=", "&=", "~=", "==", "!=", "<=", ">=", "&&", "||", "<<", ">>")
+OPS1 = "+-*/%^|&<>=!?:~"
+KEYWORDS = ("if", "else", "while")
+
+
+class Tok:
+    __slots__ = ("kind", "text", "line")
+
+    def __init__(self, kind, text, line):
+        self.kind, self.text, self.line = kind, text, line
+
+    def __repr__(self):
+        return f"{self.kind}:{self.text!r}@{self.line}"
+
+
+def lex(src: str, line0: int = 1):
+    toks, i, n, line = [], 0, len(src), line0
+    while i < n:
+        c = src[i]
+        if c == "\n":
+            toks.append(Tok("eol", "\n", line)); line += 1; i += 1
+        elif c in " \t\r":
+            i += 1
+        elif src.startswith("//", i):
+            while i < n and src[i] != "\n":
+                i += 1
+        elif src.startswith("/*", i):
+            j = src.find("*/", i + 2)
+            j = n if j < 0 else j + 2
+            line += src.count("\n", i, j); i = j
+        elif c.isdigit() or (c == "." and i + 1 < n and src[i + 1].isdigit()):
+            m = re.match(r"0[xX][0-9a-fA-F]+|(?:\d+\.?\d*|\.\d+)(?:[eE][-+]?\d+)?", src[i:])
+            toks.append(Tok("num", m.group(0), line)); i += len(m.group(0))
+        elif c.isalpha() or c in "_#$":
+            if c == "$" and i + 1 < n and src[i + 1] == "'":          # $'c' character constant
+                toks.append(Tok("num", str(ord(src[i + 2])), line)); i += 4
+                continue
+            m = re.match(r"[A-Za-z_#$][A-Za-z0-9_.#$]*", src[i:])
+            t = m.group(0)
+            toks.append(Tok("kw" if t in KEYWORDS else "ident", t, line)); i += len(t)
+        elif c == '"' or c == "'":
+            j = i + 1
+            while j < n and src[j] != c:
+                j += 2 if src[j] == "\\" else 1
+            toks.append(Tok("str", src[i + 1:j], line)); line += src.count("\n", i, j); i = j + 1
+        elif src[i:i + 2] in OPS2:
+            toks.append(Tok("op", src[i:i + 2], line)); i += 2
+        elif c in OPS1:
+            toks.append(Tok("op", c, line)); i += 1
+        elif c in "()[],":
+            toks.append(Tok("punc", c, line)); i += 1
+        elif c == ";":
+            toks.append(Tok("semi", ";", line)); i += 1
+        else:
+            raise SyntaxError(f"line {line}: unexpected character {c!r}")
+    toks.append(Tok("eof", "", line))
+    return toks
+
+
+# ------------------------------------------------------------------------------------------------------
+# parser (nodes are tuples: (kind, ...))
+# ------------------------------------------------------------------------------------------------------
+PREC = {"=": 1, "+=": 1, "-=": 1, "*=": 1, "/=": 1, "%=": 1, "^=": 1, "|=": 1, "&=": 1, "~=": 1,
+        "||": 3, "|": 3, "&&": 4, "==": 5, "!=": 5, "&": 5, "<": 6, "<=": 6, ">": 6, ">=": 6, "<<": 6, ">>": 6,
+        "+": 7, "-": 7, "*": 8, "/": 8, "%": 8, "^": 9}
+ASSIGN = {"=", "+=", "-=", "*=", "/=", "%=", "^=", "|=", "&=", "~="}
+TERN = 2
+
+
+class Parser:
+    def __init__(self, src, line0=1):
+        self.t = lex(src, line0)
+        self.i = 0
+
+    @property
+    def cur(self):
+        return self.t[self.i]
+
+    @property
+    def nxt(self):
+        return self.t[min(self.i + 1, len(self.t) - 1)]
+
+    def adv(self):
+        self.i += 1
+
+    def err(self, msg):
+        raise SyntaxError(f"line {self.cur.line}: {msg} (at {self.cur!r})")
+
+    def eat(self, kind, text=None):
+        c = self.cur
+        if c.kind != kind or (text is not None and c.text != text):
+            self.err(f"expected {text or kind}")
+        self.adv()
+        return c
+
+    def is_p(self, ch):
+        return self.cur.kind == "punc" and self.cur.text == ch
+
+    def skip_seps(self):
+        while self.cur.kind in ("eol", "semi"):
+            self.adv()
+
+    def skip_eol(self):
+        while self.cur.kind == "eol":
+            self.adv()
+
+    def program(self):
+        out = []
+        self.skip_seps()
+        while self.cur.kind != "eof":
+            out.append(self.stmt())
+            self.skip_seps()
+        return out
+
+    def stmt(self):
+        if self.cur.kind == "kw" and self.cur.text == "if":
+            return self.p_if()
+        if self.cur.kind == "kw" and self.cur.text == "while":
+            return self.p_while()
+        if self.cur.kind == "ident" and self.cur.text == "function":
+            return self.p_function()
+        return self.expr(0)
+
+    def p_if(self):
+        self.eat("kw", "if"); self.eat("punc", "(")
+        c = self.expr(0)
+        self.skip_seps(); self.eat("punc", ")"); self.skip_seps()
+        a = self.expr(0); self.skip_seps()
+        b = None
+        if self.cur.kind == "kw" and self.cur.text == "else":
+            self.adv(); self.skip_seps()
+            b = self.expr(0); self.skip_seps()
+        return ("if", c, a, b)
+
+    def p_while(self):
+        self.eat("kw", "while"); self.eat("punc", "(")
+        c = self.expr(0)
+        self.skip_seps(); self.eat("punc", ")"); self.skip_seps()
+        return ("while", c, self.expr(0))
+
+    def name_list(self):
+        out = []
+        self.eat("punc", "("); self.skip_seps()
+        while not self.is_p(")"):
+            out.append(self.eat("ident").text)
+            self.skip_seps()
+            if self.is_p(","):
+                self.adv(); self.skip_seps()
+        self.eat("punc", ")")
+        return out
+
+    def p_function(self):
+        self.eat("ident", "function")
+        name = self.eat("ident").text
+        params = self.name_list()
+        locals_, instances = [], []
+        self.skip_seps()
+        while self.cur.kind == "ident" and self.cur.text in ("local", "instance", "global", "static"):
+            q = self.cur.text
+            self.adv()
+            names = self.name_list()
+            if q == "local":
+                locals_ += names
+            elif q == "instance":
+                instances += names
+            self.skip_seps()
+        if not self.is_p("("):
+            self.err("expected '(' to start function body")
+        body = self.primary()
+        return ("fundef", name, params, locals_, instances, body)
+
+    def cont_op(self, tok, min_prec):
+        if tok.kind != "op":
+            return False
+        if tok.text == "?":
+            return TERN >= min_prec
+        if tok.text in (":", "+", "-", "!"):
+            return False
+        p = PREC.get(tok.text)
+        return p is not None and p >= min_prec
+
+    def expr(self, min_prec):
+        lhs = self.prefix()
+        while True:
+            while self.cur.kind == "eol" and (self.nxt.kind == "eol" or self.cont_op(self.nxt, min_prec)):
+                self.adv()
+            if self.cur.kind != "op":
+                break
+            op = self.cur.text
+            if op in ("?", ":"):
+                break
+            p = PREC.get(op)
+            if p is None or p < min_prec:
+                break
+            self.adv()
+            rhs = self.expr(p if op in ASSIGN else p + 1)
+            if op in ASSIGN:
+                if lhs[0] not in ("var", "index") and not (lhs[0] == "call" and lhs[1] in ("slider", "spl")):
+                    self.err("bad assignment target")
+                lhs = ("assign", op, lhs, rhs)
+            else:
+                lhs = ("bin", op, lhs, rhs)
+        while self.cur.kind == "eol" and (self.nxt.kind == "eol" or (self.nxt.kind == "op" and self.nxt.text == "?")):
+            self.adv()
+        if self.cur.kind == "op" and self.cur.text == "?" and TERN >= min_prec:
+            self.adv(); self.skip_seps()
+            a = self.expr(0); self.skip_seps()
+            if self.cur.kind == "op" and self.cur.text == ":":
+                self.adv(); self.skip_seps()
+                b = self.expr(0)
+            else:
+                b = ("num", 0.0)
+            lhs = ("tern", lhs, a, b)
+        return lhs
+
+    def prefix(self):
+        self.skip_eol()
+        if self.cur.kind == "op" and self.cur.text in ("+", "-", "!"):
+            op = self.cur.text
+            self.adv()
+            return ("un", op, self.prefix())
+        return self.postfix()
+
+    def seq_item(self):
+        if self.cur.kind == "kw" and self.cur.text == "if":
+            return self.p_if()
+        if self.cur.kind == "kw" and self.cur.text == "while":
+            return self.p_while()
+        return self.expr(0)
+
+    def postfix(self):
+        node = self.primary()
+        while True:
+            if self.is_p("("):
+                if node[0] != "var":
+                    self.err("can only call a named function")
+                fn = node[1]
+                self.adv()
+                if fn == "loop":
+                    self.skip_seps()
+                    count = self.expr(0); self.skip_seps()
+                    if self.is_p(","):
+                        self.adv()
+                    self.skip_seps()
+                    items = []
+                    while not self.is_p(")"):
+                        items.append(self.seq_item()); self.skip_seps()
+                    self.adv()
+                    node = ("loop", count, ("seq", items) if len(items) != 1 else items[0])
+                    continue
+                args = []
+                self.skip_seps()
+                while not self.is_p(")"):
+                    args.append(self.expr(0)); self.skip_seps()
+                    if self.is_p(","):
+                        self.adv(); self.skip_seps()
+                self.adv()
+                node = ("call", fn, args)
+                continue
+            if self.is_p("["):
+                self.adv(); self.skip_seps()
+                idx = ("num", 0.0) if self.is_p("]") else self.expr(0)
+                self.skip_seps(); self.eat("punc", "]")
+                node = ("index", node, idx)
+                continue
+            return node
+
+    def primary(self):
+        c = self.cur
+        if c.kind == "num":
+            self.adv()
+            return ("num", float(int(c.text, 16)) if c.text[:2].lower() == "0x" else float(c.text))
+        if c.kind == "str":
+            self.adv()
+            return ("str", c.text)
+        if c.kind == "ident":
+            self.adv()
+            return ("var", c.text)
+        if self.is_p("("):
+            self.adv(); self.skip_seps()
+            items = []
+            while not self.is_p(")"):
+                items.append(self.seq_item()); self.skip_seps()
+            self.adv()
+            return items[0] if len(items) == 1 else ("seq", items)
+        self.err("expected number, identifier or '('")
+
+
+# ------------------------------------------------------------------------------------------------------
+# script = header + sections
+# ------------------------------------------------------------------------------------------------------
+SECTIONS = ("init", "slider", "block", "sample")
+
+
+def split_script(text: str):
+    header, secs, cur, start = [], {}, None, {}
+    for ln, line in enumerate(text.splitlines(), 1):
+        m = re.match(r"^@(\w+)", line)
+        if m:
+            cur = m.group(1)
+            secs.setdefault(cur, []); start.setdefault(cur, ln + 1)
+            continue
+        (header if cur is None else secs[cur]).append(line)
+    return "\n".join(header), {k: ("\n".join(v), start[k]) for k, v in secs.items()}
+
+
+def pin_counts(header: str, used_spl: set):
+    ins = [l for l in header.splitlines() if re.match(r"^\s*in_pin\s*:", l)]
+    outs = [l for l in header.splitlines() if re.match(r"^\s*out_pin\s*:", l)]
+    none = lambda ls: any(re.match(r"^\s*\w+\s*:\s*none\s*$", l) for l in ls)
+    hi = (max(used_spl) + 1) if used_spl else 0
+    n_in = 0 if none(ins) else (len(ins) if ins else hi)
+    n_out = 0 if none(outs) else (len(outs) if outs else hi)
+    return n_in, n_out
+
+
+MATH1 = {"sin", "cos", "tan", "asin", "acos", "atan", "exp", "log", "log10", "sqrt", "floor", "ceil", "abs"}
+MATH2 = {"pow", "atan2"}
+NOOP_CALLS = {"sprintf", "printf", "strcpy", "strcat", "strcmp", "strlen", "str_getchar", "str_setchar", "str_insert",
+              "str_delete", "str_mid", "strncpy", "file_read", "file_write", "file_string"}
+UNSUPPORTED = {"fft", "ifft", "fft_real", "ifft_real", "fft_permute", "fft_ipermute", "convolve_c", "sliderchange",
+               "slider_automate", "slider_next_chg", "midisend", "midirecv", "midisend_buf", "midirecv_buf",
+               "file_open", "file_close", "file_mem", "file_riff", "file_avail"}
+STATE_BUILTINS = {"srate": "srate", "samplesblock": "samplesblock"}
+
+
+def cname(name: str) -> str:
+    return "v_" + re.sub(r"[^A-Za-z0-9_]", lambda m: "_%02x" % ord(m.group(0)), name)
+
+
+class Unit:
+    """One script: variable table, function specialisations, emitted section bodies."""
+
+    def __init__(self, key: str, text: str):
+        self.key = key
+        header, secs = split_script(text)
+        self.header = header
+        self.slider_lines = [l for l in header.splitlines() if re.match(r"^\s*slider\d+\s*:", l)]
+        self.fundefs = {}
+        self.progs = {}
+        for s in SECTIONS:
+            src, l0 = secs.get(s, ("", 1))
+            prog = Parser(src, l0).program()
+            keep = []
+            for n in prog:
+                if n[0] == "fundef":
+                    if n[4]:
+                        raise NotImplementedError(f"{key}: instance() in function {n[1]}")
+                    self.fundefs[n[1]] = n
+                else:
+                    keep.append(n)
+            self.progs[s] = keep
+        self.vars = {}            # jsfx name -> slot
+        self.used_spl = set()
+        self.used_sliders = set()
+        self.spec = {}            # (section, fn) -> C name
+        self.spec_code = []       # emitted function definitions, callee first
+        self.in_progress = set()
+        self.body = {s: Emitter(self, s, {}, set()).run(self.progs[s]) for s in SECTIONS}
+        self.n_in, self.n_out = pin_counts(header, self.used_spl)
+        self.alias = {}           # slider index0 -> var name
+        for l in self.slider_lines:
+            m = re.match(r"^\s*slider(\d+)\s*:\s*([A-Za-z_][A-Za-z0-9_.]*)\s*=", l)
+            if m:
+                self.alias[int(m.group(1)) - 1] = m.group(2)
+                self.slot(m.group(2))
+
+    def slot(self, name: str) -> int:
+        if name not in self.vars:
+            self.vars[name] = len(self.vars)
+        return self.vars[name]
+
+    def specialise(self, section: str, fn: str) -> str:
+        key = (section, fn)
+        if key in self.spec:
+            return self.spec[key]
+        if key in self.in_progress:
+            raise NotImplementedError(f"{self.key}: recursive user function {fn}")
+        self.in_progress.add(key)
+        _, name, params, locals_, _, body = self.fundefs[fn]
+        cn = f"fn_{section}_{re.sub(r'[^A-Za-z0-9_]', '_', name)}"
+        local_map = {l: f"__fnlocal__{section}__{name}__{l}" for l in locals_}
+        em = Emitter(self, section, local_map, set(params))
+        val = em.ex(body)
+        args = "".join(f", R p_{re.sub(r'[^A-Za-z0-9_]', '_', p)}" for p in params)
+        code = [f"template <typename R> __device__ __noinline__ R {cn}(Rt<R>& c, R* v{args})", "{"] + em.lines + [f"    return {val};", "}", ""]
+        self.spec_code += code
+        self.in_progress.discard(key)
+        self.spec[key] = cn
+        return cn
+
+
+def lit(v: float) -> str:
+    if v != v or v in (float("inf"), float("-inf")):
+        raise ValueError("non-finite literal")
+    return f"R({v!r})"
+
+
+class Emitter:
+    """Expression tree -> straight-line C++ statements with explicit temporaries (evaluation order = the
+    reference's: left operand, right operand; right-hand side before the assignment target)."""
+
+    def __init__(self, unit: Unit, section: str, local_map: dict, params: set):
+        self.u, self.section, self.local_map, self.params = unit, section, local_map, params
+        self.lines, self.n, self.ind = [], 0, 1
+
+    def run(self, prog):
+        for n in prog:
+            self.ex(n)
+        return self.lines
+
+    def w(self, s):
+        self.lines.append("    " * self.ind + s)
+
+    def tmp(self, expr=None):
+        self.n += 1
+        t = f"t{self.n}"
+        self.w(f"R {t}{'' if expr is None else ' = ' + expr};")
+        return t
+
+    # ---- variables --------------------------------------------------------------------------------------
+    def ref(self, name: str) -> str:
+        if name in self.params:
+            return "p_" + re.sub(r"[^A-Za-z0-9_]", "_", name)
+        name = self.local_map.get(name, name)
+        if name == "this" or name.startswith("this."):
+            raise NotImplementedError(f"{self.u.key}: this. namespaces")
+        m = re.fullmatch(r"spl(\d+)", name)
+        if m:
+            i = int(m.group(1))
+            if i >= 64:
+                raise NotImplementedError("spl index >= 64")
+            self.u.used_spl.add(i)
+            return f"c.spl[{i}]"
+        m = re.fullmatch(r"slider(\d+)", name)
+        if m and 1 <= int(m.group(1)) <= 64:
+            self.u.used_sliders.add(int(m.group(1)) - 1)
+            return f"c.sliders[{int(m.group(1)) - 1}]"
+        if name in STATE_BUILTINS:
+            return f"c.{STATE_BUILTINS[name]}"
+        if name.startswith("gmem") or name == "mem":
+            raise NotImplementedError(f"{self.u.key}: {name}")
+        return f"v[{self.u.slot(name)}] /*{name}*/"
+
+    # ---- expressions ------------------------------------------------------------------------------------
+    def ex(self, n) -> str:
+        k = n[0]
+        if k == "num":
+            return lit(n[1])
+        if k == "str":
+            return "R(0)"
+        if k == "var":
+            name = n[1]
+            if name == "$pi":
+                return "R(3.141592653589793)"
+            if name == "$e":
+                return "R(2.718281828459045)"
+            if name == "$phi":
+                return "R(1.618033988749895)"
+            if name.startswith("$x"):
+                return lit(float(int(name[2:], 16)))
+            return self.tmp(self.ref(name))
+        if k == "index":
+            b = self.ex(n[1]); i = self.ex(n[2])
+            return self.tmp(f"c.ld({b}, {i})")
+        if k == "un":
+            a = self.ex(n[2])
+            if n[1] == "+":
+                return a
+            if n[1] == "-":
+                return self.tmp(f"sub_(R(0), {a})")
+            return self.tmp(f"({a} == R(0)) ? R(1) : R(0)")
+        if k == "tern" or k == "if":
+            c = self.ex(n[1])
+            t = self.tmp()
+            self.w(f"if ({c} != R(0)) {{"); self.ind += 1
+            a = self.ex(n[2]); self.w(f"{t} = {a};"); self.ind -= 1
+            self.w("} else {"); self.ind += 1
+            b = self.ex(n[3]) if n[3] is not None else "R(0)"
+            self.w(f"{t} = {b};"); self.ind -= 1
+            self.w("}")
+            return t
+        if k == "seq":
+            v = "R(0)"
+            for it in n[1]:
+                v = self.ex(it)
+            return v
+        if k == "loop":
+            cnt = self.ex(n[1])
+            t = self.tmp("R(0)")
+            self.n += 1
+            i = f"i{self.n}"
+            self.w(f"for (long long {i} = 0, n{i} = to_count({cnt}); {i} < n{i}; ++{i}) {{"); self.ind += 1
+            v = self.ex(n[2]); self.w(f"{t} = {v};"); self.ind -= 1
+            self.w("}")
+            return t
+        if k == "while":
+            self.w("for (;;) {"); self.ind += 1
+            c = self.ex(n[1]); self.w(f"if (!({c} != R(0))) break;")
+            self.ex(n[2]); self.ind -= 1
+            self.w("}")
+            return "R(0)"
+        if k == "bin":
+            op = n[1]
+            if op in ("&&", "||"):
+                l = self.ex(n[2])
+                t = self.tmp("R(1)" if op == "||" else "R(0)")
+                self.w(f"if ({'!' if op == '||' else ''}({l} != R(0))) {{"); self.ind += 1
+                r = self.ex(n[3]); self.w(f"{t} = ({r} != R(0)) ? R(1) : R(0);"); self.ind -= 1
+                self.w("}")
+                return t
+            l = self.ex(n[2]); r = self.ex(n[3])
+            return self.tmp(self.binop(op, l, r))
+        if k == "assign":
+            op, tgt = n[1], n[2]
+            rhs = self.ex(n[3])
+            if tgt[0] == "var":
+                lv = self.ref(tgt[1])
+                if op == "=":
+                    self.w(f"{lv} = {rhs};")
+                    return rhs
+                out = self.tmp(self.binop(op[:-1] if op != "~=" else "~", lv, rhs))
+                self.w(f"{lv} = {out};")
+                return out
+            if tgt[0] == "index":
+                b = self.ex(tgt[1]); i = self.ex(tgt[2])
+                self.n += 1
+                a = f"a{self.n}"
+                self.w(f"const long long {a} = c.addr({b}, {i});")
+                if op == "=":
+                    self.w(f"c.st({a}, {rhs});")
+                    return rhs
+                cur = self.tmp(f"c.ldi({a})")
+                out = self.tmp(self.binop(op[:-1] if op != "~=" else "~", cur, rhs))
+                self.w(f"c.st({a}, {out});")
+                return out
+            # slider(i) / spl(i)
+            idx = self.ex(tgt[2][0])
+            arr = "sliders" if tgt[1] == "slider" else "spl"
+            base = "to_i32(%s) - 1" % idx if tgt[1] == "slider" else "to_i32(%s)" % idx
+            self.n += 1
+            a = f"a{self.n}"
+            self.w(f"const int {a} = {base};")
+            if op == "=":
+                self.w(f"if ({a} >= 0 && {a} < 64) c.{arr}[{a}] = {rhs};")
+                return rhs
+            cur = self.tmp(f"({a} >= 0 && {a} < 64) ? c.{arr}[{a}] : R(0)")
+            out = self.tmp(self.binop(op[:-1] if op != "~=" else "~", cur, rhs))
+            self.w(f"if ({a} >= 0 && {a} < 64) c.{arr}[{a}] = {out};")
+            return out
+        if k == "call":
+            return self.call(n[1], n[2])
+        if k == "fundef":
+            raise NotImplementedError("nested function definition")
+        raise NotImplementedError(k)
+
+    def binop(self, op, l, r):
+        if op == "+":
+            return f"add_({l}, {r})"
+        if op == "-":
+            return f"sub_({l}, {r})"
+        if op == "*":
+            return f"mul_({l}, {r})"
+        if op == "/":
+            return f"div_({l}, {r})"
+        if op == "^":
+            return f"pow_({l}, {r})"
+        if op in ("<", "<=", ">", ">=", "==", "!="):
+            return f"({l} {op} {r}) ? R(1) : R(0)"
+        if op == "|":
+            return f"R(to_i32({l}) | to_i32({r}))"
+        if op == "&":
+            return f"R(to_i32({l}) & to_i32({r}))"
+        if op == "~":
+            return f"R(to_i32({l}) ^ to_i32({r}))"
+        if op == "<<":
+            return f"R(shl_i32(to_i32({l}), to_i32({r})))"
+        if op == ">>":
+            return f"R(to_i32({l}) >> (to_i32({r}) & 31))"
+        if op == "%":
+            return f"R(rem_i32(to_i32({l}), to_i32({r})))"
+        raise NotImplementedError(op)
+
+    def call(self, fn, args):
+        if fn in self.u.fundefs:
+            av = [self.ex(a) for a in args]
+            want = len(self.u.fundefs[fn][2])
+            av = (av + ["R(0)"] * want)[:want]
+            cn = self.u.specialise(self.section, fn)
+            return self.tmp(f"{cn}<R>(c, v{''.join(', ' + a for a in av)})")
+        if fn.startswith("gfx_") or fn in NOOP_CALLS or fn in ("slider_show", "freembuf"):
+            for a in args:
+                self.ex(a)
+            return "R(0)"
+        if fn in UNSUPPORTED or fn.startswith(("gmem", "msg_", "sample_", "midi", "file_")) or "." in fn:
+            raise NotImplementedError(f"{self.u.key}: builtin {fn}")
+        av = [self.ex(a) for a in args]
+        if fn in ("min", "max") and len(av) == 2:
+            return self.tmp(f"({av[0]} {'<' if fn == 'min' else '>'} {av[1]}) ? {av[0]} : {av[1]}")
+        if fn == "sqr" and len(av) == 1:
+            return self.tmp(f"mul_({av[0]}, {av[0]})")
+        if fn == "sign" and len(av) == 1:
+            return self.tmp(f"({av[0]} > R(0)) ? R(1) : (({av[0]} < R(0)) ? R(-1) : R(0))")
+        if fn in MATH1 and len(av) == 1:
+            return self.tmp(f"m_{fn}({av[0]})")
+        if fn in MATH2 and len(av) == 2:
+            return self.tmp(f"m_{fn}({av[0]}, {av[1]})")
+        if fn == "invsqrt" and len(av) == 1:
+            return self.tmp(f"m_invsqrt({av[0]})")
+        if fn == "rand" and len(av) <= 1:
+            return self.tmp(f"c.rand({av[0] if av else 'R(1)'}, {1 if av else 0})")
+        if fn == "memset" and len(av) == 3:
+            self.w(f"c.memset({av[0]}, {av[1]}, {av[2]});")
+            return av[0]
+        if fn == "memcpy" and len(av) == 3:
+            self.w(f"c.memcpy({av[0]}, {av[1]}, {av[2]});")
+            return "R(0)"
+        if fn == "spl" and len(av) == 1:
+            return self.tmp(f"c.spl_dyn({av[0]})")
+        if fn == "slider" and len(av) == 1:
+            return self.tmp(f"c.slider_dyn({av[0]})")
+        raise NotImplementedError(f"{self.u.key}: call {fn}/{len(av)}")
+
+
+# ------------------------------------------------------------------------------------------------------
+# translation unit
+# ------------------------------------------------------------------------------------------------------
+def c_string(s: str) -> str:
+    return '"' + s.replace("\\", "\\\\").replace('"', '\\"') + '\\n"'
+
+
+def generate(key: str, jsfx_path: str, mem_slots: int, source_label: str) -> str:
+    text = Path(jsfx_path).read_text(errors="replace")
+    u = Unit(key, text)
+    ident = re.sub(r"[^A-Za-z0-9_]", "_", key)
+    names = sorted(u.vars, key=lambda k: u.vars[k])
+    alias_slots = [-1] * 64
+    for i0, nm in u.alias.items():
+        alias_slots[i0] = u.vars[nm]
+    nch = max(u.n_in, u.n_out, (max(u.used_spl) + 1) if u.used_spl else 0, 1)
+    out = []
+    out.append(f"// g_{ident}.cu -- GENERATED by za_gpu/jsfxc.py from {source_label}; do not edit.")
+    out.append("// One stream per thread: the script's sections and user functions as device code (see jsfxc.py for the")
+    out.append("// semantics restated from the reference's AOT compiler) + the descriptor p_generic.cu registers.")
+    out.append('#include "../jsfx_rt.cuh"')
+    out.append("")
+    out.append(f"namespace za {{ namespace jsfx {{ namespace g_{ident} {{")
+    out.append("")
+    out.append(f"constexpr int kVars = {max(len(names), 1)}, kIn = {u.n_in}, kOut = {u.n_out}, kCh = {nch};")
+    out.append("")
+    out += u.spec_code
+    for s in SECTIONS:
+        out.append(f"template <typename R> __device__ __forceinline__ void sec_{s}(Rt<R>& c, R* v)")
+        out.append("{")
+        out += u.body[s]
+        out.append("}")
+        out.append("")
+    out.append("static const char* const kVarNames[] = {" + ", ".join('"%s"' % n.replace('"', "") for n in names) + (", " if names else "") + "nullptr};")
+    out.append("static const int kAlias[64] = {" + ", ".join(map(str, alias_slots)) + "};")
+    out.append("static const char kSliderText[] =")
+    for l in u.slider_lines:
+        out.append("    " + c_string(l.strip()))
+    if not u.slider_lines:
+        out.append('    ""')
+    out.append("    ;")
+    out.append("")
+    out.append(f"ZA_JSFX_DEFINE_PLUGIN({ident}, \"{key}\", {mem_slots}, {1 if u.body['block'] else 0}, {1 if u.body['slider'] else 0})")
+    out.append("")
+    out.append("}}}  // namespace")
+    out.append("")
+    return "\n".join(out)
+
+
+if __name__ == "__main__":
+    key, path, mem = sys.argv[1], sys.argv[2], int(sys.argv[3])
+    sys.stdout.write(generate(key, path, mem, sys.argv[4] if len(sys.argv) > 4 else path))
