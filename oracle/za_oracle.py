@@ -155,6 +155,11 @@ def plugin_source_text(key: str) -> str:
             return p.read_text()
     if key in CATALOG_SLIDERS:
         return CATALOG_SLIDERS[key]
+    cat = HERE / "catalog_sliders.json"        # written by tools/gen_plugins.py from the plugin sources
+    if cat.exists():
+        d = json.loads(cat.read_text())
+        if key in d:
+            return d[key]
     raise KeyError(key)
 
 

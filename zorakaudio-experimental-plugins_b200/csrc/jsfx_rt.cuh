@@ -1,0 +1,398 @@
+// jsfx_rt.cuh -- device runtime under the translated DSP-JSFX scripts (csrc/gen/g_*.cu, written by
+// za_gpu/jsfxc.py): the per-thread context (one stream per thread), mem[] as a stream-minor
+// structure-of-arrays heap in HBM, the arithmetic the reference compiler pins (dsp_jsfx_aot.py:4263-5590),
+// its per-instance MT19937 (:3880-4060), and the two kernels every script instantiates:
+//   jsfx_prepare_kernel  = prepareToPlay: sliders pushed, @init, alias re-apply, @slider
+//                          (src/JSFXJuceProcessor.cpp:3297-3318)
+//   jsfx_process_kernel  = processBlock -> jsfx_process_block for every host block of the call: push the
+//                          block's quantised sliders, @slider if one changed (:3536-3556), samplesblock,
+//                          @block, then per frame float -> spl[], @sample, spl[] -> float
+//                          (dsp_jsfx_aot.py:5766-5892)
+// Audio moves through shared memory in [32 streams] x [32 frames] tiles so HBM sees 128-byte rows although a
+// thread walks along its own stream.
+#pragma once
+#include <math.h>
+
+#ifdef ZA_JSFX_HOST_EMU
+// Host emulation (tools/emu_jsfx.py): the generated translation units compiled as plain C++ so the translator's
+// semantics can be checked against the reference build on the CPU, one stream at a time.  Development / test aid only.
+#include <stdint.h>
+#include <string.h>
+#include <algorithm>
+#include <vector>
+#define __device__
+#define __host__
+#define __global__
+#define __forceinline__ inline
+#define __noinline__
+inline double __dadd_rn(double a, double b) { return a + b; }
+inline double __dsub_rn(double a, double b) { return a - b; }
+inline double __dmul_rn(double a, double b) { return a * b; }
+inline double __ddiv_rn(double a, double b) { return a / b; }
+inline double __dsqrt_rn(double a) { return sqrt(a); }
+inline float __fadd_rn(float a, float b) { return a + b; }
+inline float __fsub_rn(float a, float b) { return a - b; }
+inline float __fmul_rn(float a, float b) { return a * b; }
+inline float __fdiv_rn(float a, float b) { return a / b; }
+inline float __fsqrt_rn(float a) { return sqrtf(a); }
+inline int __float_as_int(float f) { int i; memcpy(&i, &f, 4); return i; }
+inline float __int_as_float(int i) { float f; memcpy(&f, &i, 4); return f; }
+using std::min;
+using std::max;
+namespace za {
+struct GenLaunch {
+    const float* in; float* out; double* tap;
+    int64_t row_stride, n_frames, mem_slots;
+    int n_streams, block_len, n_rows, n_decl;
+    const double* q; const int* decl_index0;
+    void* state; void* mem; unsigned* mt; int* err; double srate;
+};
+}
+#else
+#include "za_device.cuh"
+#include "za_internal.h"
+#endif
+
+namespace za {
+namespace jsfx {
+
+// ---- arithmetic (fp64: separate, never contracted operations in the reference's order; fp32: plain float) ----
+__device__ __forceinline__ double add_(double a, double b) { return __dadd_rn(a, b); }
+__device__ __forceinline__ double sub_(double a, double b) { return __dsub_rn(a, b); }
+__device__ __forceinline__ double mul_(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ double div_(double a, double b) { return __ddiv_rn(a, b); }
+__device__ __forceinline__ float add_(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float sub_(float a, float b) { return __fsub_rn(a, b); }
+__device__ __forceinline__ float mul_(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float div_(float a, float b) { return __fdiv_rn(a, b); }
+__device__ __forceinline__ double pow_(double a, double b) { return pow(a, b); }
+__device__ __forceinline__ float pow_(float a, float b) { return powf(a, b); }
+
+#define ZA_M1(name, fd, ff)                                                  \
+    __device__ __forceinline__ double m_##name(double a) { return fd(a); }   \
+    __device__ __forceinline__ float m_##name(float a) { return ff(a); }
+ZA_M1(sin, sin, sinf) ZA_M1(cos, cos, cosf) ZA_M1(tan, tan, tanf) ZA_M1(asin, asin, asinf) ZA_M1(acos, acos, acosf)
+ZA_M1(atan, atan, atanf) ZA_M1(exp, exp, expf) ZA_M1(log, log, logf) ZA_M1(log10, log10, log10f)
+ZA_M1(floor, floor, floorf) ZA_M1(ceil, ceil, ceilf) ZA_M1(abs, fabs, fabsf)
+#undef ZA_M1
+__device__ __forceinline__ double m_sqrt(double a) { return __dsqrt_rn(a); }
+__device__ __forceinline__ float m_sqrt(float a) { return __fsqrt_rn(a); }
+__device__ __forceinline__ double m_pow(double a, double b) { return pow(a, b); }
+__device__ __forceinline__ float m_pow(float a, float b) { return powf(a, b); }
+__device__ __forceinline__ double m_atan2(double a, double b) { return atan2(a, b); }
+__device__ __forceinline__ float m_atan2(float a, float b) { return atan2f(a, b); }
+template <typename R> __device__ __forceinline__ R m_invsqrt(R x)      // dsp_jsfx_aot.py:5256-5277
+{
+    const int bits = __float_as_int((float)x);
+    const R y0 = (R)__int_as_float(0x5f3759df - (bits >> 1));
+    return mul_(y0, sub_((R)1.5, mul_(mul_((R)0.5, x), mul_(y0, y0))));
+}
+
+template <typename R> __device__ __forceinline__ int to_i32(R x) { return (int)(long long)x; }      // :4107-4110
+__device__ __forceinline__ int shl_i32(int a, int b) { return (int)((unsigned)a << (b & 31)); }
+__device__ __forceinline__ int rem_i32(int a, int b) { return (b == 0 || (a == (int)0x80000000 && b == -1)) ? 0 : a % b; }
+template <typename R> __device__ __forceinline__ long long to_count(R x) { const long long n = (long long)x; return n < 0 ? 0 : n; }
+
+// ---- per-thread context ---------------------------------------------------------------------------------------
+template <typename R> struct Rt {
+    R* mem;                 // this stream's column of the heap: slot i at mem[i * stride]
+    long long stride, cap;  // n_streams, slots per stream
+    unsigned* mt;           // this stream's column of the MT19937 state: word k at mt[k * stride], index at word 624
+    int* err;               // device error flag: 1 = mem[] index beyond the heap the plugin was sized for
+    R srate, samplesblock;
+    R sliders[64];
+    R spl[64];
+
+    __device__ __forceinline__ long long addr(R base, R idx) const        // a[b] = mem[trunc(a + b + 1e-5)], negative -> 0 (:4062-4103)
+    {
+        const double s = __dadd_rn(__dadd_rn((double)base, (double)idx), 1.0e-5);
+        const long long a = (long long)s;
+        return a < 0 ? 0 : a;
+    }
+    __device__ __forceinline__ R ldi(long long a) const
+    {
+        if (a >= cap) { *err = 1; return (R)0; }      // the reference grows the heap and reads 0
+        return mem[a * stride];
+    }
+    __device__ __forceinline__ R ld(R base, R idx) const { return ldi(addr(base, idx)); }
+    __device__ __forceinline__ void st(long long a, R v)
+    {
+        if (a >= cap) { *err = 1; return; }
+        mem[a * stride] = v;
+    }
+    __device__ void memset(R dest, R value, R len)                         // :5439-5495
+    {
+        long long d = (long long)__dadd_rn((double)dest, 1.0e-5);
+        if (d < 0) d = 0;
+        long long n = (long long)len;
+        if (n < 0) n = 0;
+        if (d + n > cap) { *err = 1; n = cap > d ? cap - d : 0; }
+        for (long long i = 0; i < n; ++i) mem[(d + i) * stride] = value;
+    }
+    __device__ void memcpy(R dest, R src, R len)                           // overlap permitted (memmove), returns 0
+    {
+        long long d = (long long)__dadd_rn((double)dest, 1.0e-5), s = (long long)__dadd_rn((double)src, 1.0e-5);
+        if (d < 0) d = 0;
+        if (s < 0) s = 0;
+        long long n = (long long)len;
+        if (n < 0) n = 0;
+        if (d + n > cap || s + n > cap) { *err = 1; return; }
+        if (d <= s) for (long long i = 0; i < n; ++i) mem[(d + i) * stride] = mem[(s + i) * stride];
+        else        for (long long i = n - 1; i >= 0; --i) mem[(d + i) * stride] = mem[(s + i) * stride];
+    }
+    __device__ __forceinline__ R spl_dyn(R i) const { const int k = to_i32(i); return (k >= 0 && k < 64) ? spl[k] : (R)0; }
+    __device__ __forceinline__ R slider_dyn(R i) const { const int k = to_i32(i) - 1; return (k >= 0 && k < 64) ? sliders[k] : (R)0; }
+
+    // MT19937, seed 0x4141F00D, lazily initialised while the index is 0 (:3880-4060); rand([max]) = genrand_int32 *
+    // (1 / 0xFFFFFFFF) * max(1, floor(arg)) (:5294-5323)
+    __device__ unsigned genrand()
+    {
+        const int N = 624, M = 397;
+        unsigned idx = mt[624 * stride];
+        if (idx == 0) {
+            unsigned prev = 0x4141F00Du;
+            mt[0] = prev;
+            for (int k = 1; k < N; ++k) { prev = 1812433253u * (prev ^ (prev >> 30)) + (unsigned)k; mt[k * stride] = prev; }
+            idx = N;
+        }
+        if (idx >= (unsigned)N) {
+            for (int k = 0; k < N; ++k) {
+                const unsigned y = (mt[k * stride] & 0x80000000u) | (mt[((k + 1) % N) * stride] & 0x7fffffffu);
+                mt[k * stride] = mt[((k + M) % N) * stride] ^ (y >> 1) ^ ((y & 1u) ? 0x9908B0DFu : 0u);
+            }
+            idx = 0;
+        }
+        unsigned y = mt[idx * stride];
+        mt[624 * stride] = idx + 1;
+        y ^= y >> 11; y ^= (y << 7) & 0x9D2C5680u; y ^= (y << 15) & 0xEFC60000u; y ^= y >> 18;
+        return y;
+    }
+    __device__ R rand(R arg, int has_arg)
+    {
+        R mx = has_arg ? m_floor(arg) : (R)1;
+        if (mx < (R)1) mx = (R)1;
+        const double r = __dmul_rn((double)genrand(), 1.0 / 4294967295.0);
+        return (R)__dmul_rn(r, (double)mx);
+    }
+};
+
+// state rows per stream (all R, [row][n_streams]): the script's variables, then st.sliders[64], then lastSlidersValid
+template <class S> constexpr int state_rows() { return S::kVars + 64 + 1; }
+
+template <class S, typename R>
+__device__ __forceinline__ void ctx_open(Rt<R>& c, R* v, const GenLaunch& a, int sc)
+{
+    const long long ns = a.n_streams;
+    c.mem = reinterpret_cast<R*>(a.mem) + sc; c.stride = ns; c.cap = a.mem_slots;
+    c.mt = a.mt + sc; c.err = a.err;
+    c.srate = (R)a.srate; c.samplesblock = (R)0;
+    const R* st = reinterpret_cast<const R*>(a.state) + sc;
+    for (int k = 0; k < S::kVars; ++k) v[k] = st[(long long)k * ns];
+    for (int k = 0; k < 64; ++k) { c.sliders[k] = st[(long long)(S::kVars + k) * ns]; c.spl[k] = (R)0; }
+}
+template <class S, typename R>
+__device__ __forceinline__ void ctx_close(const Rt<R>& c, const R* v, const GenLaunch& a, int s, R valid)
+{
+    const long long ns = a.n_streams;
+    R* st = reinterpret_cast<R*>(a.state) + s;
+    for (int k = 0; k < S::kVars; ++k) st[(long long)k * ns] = v[k];
+    for (int k = 0; k < 64; ++k) st[(long long)(S::kVars + k) * ns] = c.sliders[k];
+    st[(long long)(S::kVars + 64) * ns] = valid;
+}
+
+// push one row of quantised slider values (pushParamsToStateSliders, :9286-9357): returns "changed"
+template <class S, typename R>
+__device__ __forceinline__ bool push_sliders(Rt<R>& c, R* v, const GenLaunch& a, int row, int sc, bool valid)
+{
+    bool changed = !valid;
+    const double* q = a.q + ((size_t)row * a.n_streams + sc) * a.n_decl;
+    for (int j = 0; j < a.n_decl; ++j) {
+        const int i0 = a.decl_index0[j];
+        const R nv = (R)q[j];
+        if (nv != c.sliders[i0]) changed = true;
+        c.sliders[i0] = nv;
+        const int al = S::alias(i0);
+        if (al >= 0) v[al] = nv;
+    }
+    return changed;
+}
+
+#ifndef ZA_JSFX_HOST_EMU
+template <class S, typename R>
+__global__ void __launch_bounds__(32) jsfx_prepare_kernel(const GenLaunch a)
+{
+    const int s = blockIdx.x * 32 + threadIdx.x;
+    if (s >= a.n_streams) return;
+    Rt<R> c;
+    R v[S::kVars];
+    ctx_open<S, R>(c, v, a, s);                    // state and heap were zeroed by the host (resetStateStructOnly)
+    push_sliders<S, R>(c, v, a, 0, s, false);
+    S::template init<R>(c, v);
+    for (int j = 0; j < a.n_decl; ++j) {           // alias re-apply after @init (:3308-3316)
+        const int al = S::alias(a.decl_index0[j]);
+        if (al >= 0) v[al] = c.sliders[a.decl_index0[j]];
+    }
+    S::template slider<R>(c, v);
+    ctx_close<S, R>(c, v, a, s, (R)1);
+}
+
+template <class S, typename R, bool TAP>
+__global__ void __launch_bounds__(32) jsfx_process_kernel(const GenLaunch a)
+{
+    extern __shared__ float tile[];                // [kCh][32 streams][33]
+    constexpr int kP = 33;
+    const int lane = threadIdx.x, s0 = blockIdx.x * 32, s = s0 + lane;
+    const bool live = s < a.n_streams;
+    const int sc = live ? s : a.n_streams - 1;     // dead lanes shadow the last stream and never store
+    const int ns_cta = min(32, a.n_streams - s0);
+    Rt<R> c;
+    R v[S::kVars];
+    ctx_open<S, R>(c, v, a, sc);
+    bool valid = reinterpret_cast<const R*>(a.state)[(long long)(S::kVars + 64) * a.n_streams + sc] != (R)0;
+
+    int64_t pos = 0;
+    for (int blk = 0; pos < a.n_frames; ++blk) {
+        const int nb = (int)min((int64_t)a.block_len, a.n_frames - pos);
+        if (a.n_rows > 0) {
+            const bool changed = push_sliders<S, R>(c, v, a, blk < a.n_rows ? blk : a.n_rows - 1, sc, valid);
+            valid = true;
+            if (changed) S::template slider<R>(c, v);
+        }
+        c.samplesblock = (R)nb;
+        S::template block<R>(c, v);
+        for (int f0 = 0; f0 < nb; f0 += 32) {
+            const int nf = min(32, nb - f0);
+            // tile in: lane = frame, 128-byte rows
+            for (int r = 0; r < ns_cta; ++r)
+                for (int ch = 0; ch < S::kIn; ++ch)
+                    tile[(ch * 32 + r) * kP + lane] = lane < nf ? a.in[((size_t)(s0 + r) * S::kIn + ch) * a.row_stride + pos + f0 + lane] : 0.f;
+            __syncwarp();
+            for (int f = 0; f < nf; ++f) {
+#pragma unroll
+                for (int ch = 0; ch < S::kCh; ++ch) c.spl[ch] = ch < S::kIn ? (R)tile[(ch * 32 + lane) * kP + f] : (R)0;
+                S::template sample<R>(c, v);
+#pragma unroll
+                for (int ch = 0; ch < S::kOut; ++ch) {
+                    if (TAP && live) a.tap[((size_t)s * S::kOut + ch) * a.row_stride + pos + f0 + f] = (double)c.spl[ch];
+                    tile[(ch * 32 + lane) * kP + f] = (float)c.spl[ch];
+                }
+            }
+            __syncwarp();
+            for (int r = 0; r < ns_cta; ++r)
+                for (int ch = 0; ch < S::kOut; ++ch)
+                    if (lane < nf) a.out[((size_t)(s0 + r) * S::kOut + ch) * a.row_stride + pos + f0 + lane] = tile[(ch * 32 + r) * kP + lane];
+            __syncwarp();
+        }
+        pos += nb;
+    }
+    if (live) ctx_close<S, R>(c, v, a, s, valid ? (R)1 : (R)0);
+}
+
+template <class S> bool launch_prepare(const GenLaunch& a, int precision, cudaStream_t st)
+{
+    const int blocks = (a.n_streams + 31) / 32;
+    if (precision) jsfx_prepare_kernel<S, double><<<blocks, 32, 0, st>>>(a);
+    else jsfx_prepare_kernel<S, float><<<blocks, 32, 0, st>>>(a);
+    return cuda_ok(cudaGetLastError(), "jsfx_prepare_kernel launch");
+}
+template <class S> bool launch_process(const GenLaunch& a, int precision, cudaStream_t st)
+{
+    const int blocks = (a.n_streams + 31) / 32;
+    const size_t smem = (size_t)S::kCh * 32 * 33 * sizeof(float);
+    if (precision) {
+        if (a.tap) jsfx_process_kernel<S, double, true><<<blocks, 32, smem, st>>>(a);
+        else jsfx_process_kernel<S, double, false><<<blocks, 32, smem, st>>>(a);
+    } else {
+        jsfx_process_kernel<S, float, false><<<blocks, 32, smem, st>>>(a);
+    }
+    return cuda_ok(cudaGetLastError(), "jsfx_process_kernel launch");
+}
+
+#else   // ZA_JSFX_HOST_EMU: the same two entry points for ONE stream on the host
+template <class S, typename R> void emu_prepare(const GenLaunch& a)
+{
+    Rt<R> c;
+    std::vector<R> v(S::kVars);
+    ctx_open<S, R>(c, v.data(), a, 0);
+    push_sliders<S, R>(c, v.data(), a, 0, 0, false);
+    S::template init<R>(c, v.data());
+    for (int j = 0; j < a.n_decl; ++j) {
+        const int al = S::alias(a.decl_index0[j]);
+        if (al >= 0) v[al] = c.sliders[a.decl_index0[j]];
+    }
+    S::template slider<R>(c, v.data());
+    ctx_close<S, R>(c, v.data(), a, 0, (R)1);
+}
+template <class S, typename R> void emu_process(const GenLaunch& a)
+{
+    Rt<R> c;
+    std::vector<R> v(S::kVars);
+    ctx_open<S, R>(c, v.data(), a, 0);
+    bool valid = reinterpret_cast<const R*>(a.state)[S::kVars + 64] != (R)0;
+    int64_t pos = 0;
+    for (int blk = 0; pos < a.n_frames; ++blk) {
+        const int nb = (int)std::min<int64_t>(a.block_len, a.n_frames - pos);
+        if (a.n_rows > 0) {
+            const bool changed = push_sliders<S, R>(c, v.data(), a, blk < a.n_rows ? blk : a.n_rows - 1, 0, valid);
+            valid = true;
+            if (changed) S::template slider<R>(c, v.data());
+        }
+        c.samplesblock = (R)nb;
+        S::template block<R>(c, v.data());
+        for (int f = 0; f < nb; ++f) {
+            for (int ch = 0; ch < S::kCh; ++ch) c.spl[ch] = ch < S::kIn ? (R)a.in[ch * a.row_stride + pos + f] : (R)0;
+            S::template sample<R>(c, v.data());
+            for (int ch = 0; ch < S::kOut; ++ch) {
+                if (a.tap) a.tap[ch * a.row_stride + pos + f] = (double)c.spl[ch];
+                a.out[ch * a.row_stride + pos + f] = (float)c.spl[ch];
+            }
+        }
+        pos += nb;
+    }
+    ctx_close<S, R>(c, v.data(), a, 0, valid ? (R)1 : (R)0);
+}
+#endif
+
+}  // namespace jsfx
+}  // namespace za
+
+// Emitted at the end of every generated translation unit.
+#ifdef ZA_JSFX_HOST_EMU
+#define ZA_JSFX_DEFINE_PLUGIN(IDENT, KEY, MEM_SLOTS, HAS_BLOCK, HAS_SLIDER)                                            \
+    struct Script {                                                                                                     \
+        static constexpr int kVars = g_##IDENT::kVars, kIn = g_##IDENT::kIn, kOut = g_##IDENT::kOut, kCh = g_##IDENT::kCh; \
+        static constexpr int alias(int i0) { return g_##IDENT::alias_slot(i0); }                                        \
+        template <typename R> static void init(Rt<R>& c, R* v) { sec_init<R>(c, v); }                                   \
+        template <typename R> static void slider(Rt<R>& c, R* v) { sec_slider<R>(c, v); }                               \
+        template <typename R> static void block(Rt<R>& c, R* v) { sec_block<R>(c, v); }                                 \
+        template <typename R> static void sample(Rt<R>& c, R* v) { sec_sample<R>(c, v); }                               \
+    };                                                                                                                  \
+    }  /* namespace g_IDENT */                                                                                          \
+    }}                                                                                                                  \
+    extern "C" {                                                                                                        \
+    int emu_info(int what) { using S = za::jsfx::g_##IDENT::Script; return what == 0 ? S::kVars : what == 1 ? S::kIn : what == 2 ? S::kOut : (int)(MEM_SLOTS); } \
+    const char* emu_var_name(int k) { return za::jsfx::g_##IDENT::kVarNames[k]; }                                       \
+    void emu_prepare(const za::GenLaunch* a, int f64) { using S = za::jsfx::g_##IDENT::Script; if (f64) za::jsfx::emu_prepare<S, double>(*a); else za::jsfx::emu_prepare<S, float>(*a); } \
+    void emu_process(const za::GenLaunch* a, int f64) { using S = za::jsfx::g_##IDENT::Script; if (f64) za::jsfx::emu_process<S, double>(*a); else za::jsfx::emu_process<S, float>(*a); } \
+    }                                                                                                                   \
+    namespace za { namespace jsfx { namespace g_##IDENT {
+#else
+#define ZA_JSFX_DEFINE_PLUGIN(IDENT, KEY, MEM_SLOTS, HAS_BLOCK, HAS_SLIDER)                                            \
+    struct Script {                                                                                                     \
+        static constexpr int kVars = g_##IDENT::kVars, kIn = g_##IDENT::kIn, kOut = g_##IDENT::kOut, kCh = g_##IDENT::kCh; \
+        static __host__ __device__ constexpr int alias(int i0) { return g_##IDENT::alias_slot(i0); }                    \
+        template <typename R> static __device__ __forceinline__ void init(Rt<R>& c, R* v) { sec_init<R>(c, v); }       \
+        template <typename R> static __device__ __forceinline__ void slider(Rt<R>& c, R* v) { sec_slider<R>(c, v); }   \
+        template <typename R> static __device__ __forceinline__ void block(Rt<R>& c, R* v) { sec_block<R>(c, v); }     \
+        template <typename R> static __device__ __forceinline__ void sample(Rt<R>& c, R* v) { sec_sample<R>(c, v); }   \
+    };                                                                                                                  \
+    }  /* namespace g_IDENT */                                                                                          \
+    const ::za::GenDesc* desc_##IDENT()                                                                                 \
+    {                                                                                                                   \
+        using S = g_##IDENT::Script;                                                                                    \
+        static const ::za::GenDesc d = {KEY, g_##IDENT::kSliderText, S::kIn, S::kOut, S::kVars, (int64_t)(MEM_SLOTS),   \
+                                        g_##IDENT::kVarNames, g_##IDENT::kAlias, &launch_prepare<S>, &launch_process<S>}; \
+        return &d;                                                                                                      \
+    }                                                                                                                   \
+    namespace g_##IDENT {
+#endif

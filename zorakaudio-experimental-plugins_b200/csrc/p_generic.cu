@@ -1,0 +1,136 @@
+// p_generic.cu -- host half of every translated DSP-JSFX leaf (csrc/gen/g_*.cu): device state sized at create
+// (vars / sliders / mem[] heap / MT19937 columns, all stream-minor structure of arrays), prepareToPlay and
+// processBlock as one kernel launch each (jsfx_rt.cuh).  The quantised automation rows of a call are uploaded
+// as doubles; @init / @slider / @block / @sample all run on the device.
+#include <cstring>
+
+#include "za_host.h"
+#include "gen/gen_list.h"
+
+namespace za {
+
+namespace jsfx {
+#define ZA_X(IDENT) const GenDesc* desc_##IDENT();
+ZA_GEN_PLUGINS(ZA_X)
+#undef ZA_X
+}  // namespace jsfx
+
+namespace {
+
+class GenericPlugin : public PluginImpl {
+    const GenDesc* d_;
+    void* d_state = nullptr; void* d_mem = nullptr; unsigned* d_mt = nullptr; int* d_err = nullptr;
+    double* d_q = nullptr; size_t q_cap = 0;
+    int* d_index0 = nullptr;
+    size_t rsize = 8;
+
+    GenLaunch base(Instance& I) const
+    {
+        GenLaunch a{};
+        a.mem_slots = d_->mem_slots; a.n_streams = I.n_streams; a.block_len = I.block_len; a.n_decl = (int)I.decls.size();
+        a.decl_index0 = d_index0; a.state = d_state; a.mem = d_mem; a.mt = d_mt; a.err = d_err; a.srate = I.srate;
+        return a;
+    }
+    bool upload_q(Instance& I, const double* q, size_t count)
+    {
+        if (count > q_cap) {
+            cudaFree(d_q); d_q = nullptr; q_cap = 0;
+            if (!cuda_ok(cudaMalloc(&d_q, count * sizeof(double)), "slider rows")) return false;
+            q_cap = count;
+        }
+        return cuda_ok(cudaMemcpyAsync(d_q, q, count * sizeof(double), cudaMemcpyHostToDevice, I.stream), "slider rows upload");
+    }
+    bool check_err(Instance& I)
+    {
+        int e = 0;
+        if (!cuda_ok(cudaMemcpyAsync(&e, d_err, sizeof e, cudaMemcpyDeviceToHost, I.stream), "err read") ||
+            !cuda_ok(cudaStreamSynchronize(I.stream), "sync")) return false;
+        if (e) { set_error(std::string(d_->key) + ": mem[] index beyond the heap this plugin was sized for"); return false; }
+        return true;
+    }
+
+public:
+    explicit GenericPlugin(const GenDesc* d) : d_(d) {}
+    ~GenericPlugin() override { cudaFree(d_state); cudaFree(d_mem); cudaFree(d_mt); cudaFree(d_err); cudaFree(d_q); cudaFree(d_index0); }
+
+    bool create(Instance& I) override
+    {
+        rsize = I.precision ? 8 : 4;
+        const size_t ns = (size_t)I.n_streams;
+        std::vector<int> idx;
+        for (const auto& s : I.decls) idx.push_back(s.index0);
+        return cuda_ok(cudaMalloc(&d_state, (size_t)(d_->n_vars + 65) * ns * rsize), "state") &&
+               cuda_ok(cudaMalloc(&d_mem, (size_t)std::max<int64_t>(d_->mem_slots, 1) * ns * rsize), "mem[] heap") &&
+               cuda_ok(cudaMalloc(&d_mt, 625 * ns * sizeof(unsigned)), "rand state") &&
+               cuda_ok(cudaMalloc(&d_err, sizeof(int)), "err flag") &&
+               cuda_ok(cudaMalloc(&d_index0, std::max<size_t>(idx.size(), 1) * sizeof(int)), "slider index") &&
+               cuda_ok(cudaMemcpy(d_index0, idx.data(), idx.size() * sizeof(int), cudaMemcpyHostToDevice), "slider index upload");
+    }
+
+    bool reset(Instance& I) override   // resetStateStructOnly + zeroed heap, then sliders, @init, alias re-apply, @slider
+    {
+        const size_t ns = (size_t)I.n_streams;
+        if (!cuda_ok(cudaMemsetAsync(d_state, 0, (size_t)(d_->n_vars + 65) * ns * rsize, I.stream), "state reset") ||
+            !cuda_ok(cudaMemsetAsync(d_mem, 0, (size_t)std::max<int64_t>(d_->mem_slots, 1) * ns * rsize, I.stream), "heap reset") ||
+            !cuda_ok(cudaMemsetAsync(d_mt, 0, 625 * ns * sizeof(unsigned), I.stream), "rand reset") ||
+            !cuda_ok(cudaMemsetAsync(d_err, 0, sizeof(int), I.stream), "err reset"))
+            return false;
+        if (!upload_q(I, I.sliders.data(), I.sliders.size())) return false;
+        GenLaunch a = base(I);
+        a.q = d_q; a.n_rows = 1;
+        if (!d_->prepare(a, I.precision, I.stream)) return false;
+        ++I.launches;
+        return check_err(I);
+    }
+
+    bool sliders_changed(Instance&, int, int, const std::vector<int>&) override { return true; }   // @slider runs on the device
+    bool takes_block_params() const override { return true; }
+
+    bool run(Instance& I, int s0, int ns, const float* in, float* out, double* tap, int64_t n, int64_t stride) override
+    {
+        return run_blocks(I, s0, ns, &I.sliders[(size_t)s0 * I.decls.size()], 1, in, out, tap, n, stride);
+    }
+
+    bool run_blocks(Instance& I, int s0, int ns, const double* q, int nbq, const float* in, float* out, double* tap,
+                    int64_t n, int64_t stride) override
+    {
+        if (s0 != 0 || ns != I.n_streams) { set_error("translated plugins: stream sub-ranges are not supported"); return false; }
+        if (!upload_q(I, q, (size_t)nbq * ns * I.decls.size())) return false;
+        GenLaunch a = base(I);
+        a.in = in; a.out = out; a.tap = tap; a.row_stride = stride; a.n_frames = n; a.q = d_q; a.n_rows = nbq;
+        const bool timed = I.time_begin();
+        if (!d_->process(a, I.precision, I.stream)) return false;
+        if (timed) I.time_end();
+        ++I.launches;
+        return true;
+    }
+
+    bool read_state(Instance& I, const char* name, double* out) override
+    {
+        int slot = -1;
+        for (int k = 0; d_->var_names[k]; ++k) if (!std::strcmp(d_->var_names[k], name)) { slot = k; break; }
+        if (slot < 0) { set_error(std::string(d_->key) + ": unknown state variable " + name); return false; }
+        if (!check_err(I)) return false;
+        const size_t ns = (size_t)I.n_streams;
+        if (I.precision) return cuda_ok(cudaMemcpy(out, (const double*)d_state + slot * ns, ns * 8, cudaMemcpyDeviceToHost), "state read");
+        std::vector<float> t(ns);
+        if (!cuda_ok(cudaMemcpy(t.data(), (const float*)d_state + slot * ns, ns * 4, cudaMemcpyDeviceToHost), "state read")) return false;
+        for (size_t s = 0; s < ns; ++s) out[s] = (double)t[s];
+        return true;
+    }
+};
+
+}  // namespace
+
+#define ZA_X(IDENT) static PluginImpl* make_gen_##IDENT() { return new GenericPlugin(jsfx::desc_##IDENT()); }
+ZA_GEN_PLUGINS(ZA_X)
+#undef ZA_X
+
+void append_generated_plugins(std::vector<PluginDesc>& t)
+{
+#define ZA_X(IDENT) { const GenDesc* d = jsfx::desc_##IDENT(); t.push_back(PluginDesc{d->key, d->n_in, d->n_out, 0, 0, d->slider_text, &make_gen_##IDENT}); }
+    ZA_GEN_PLUGINS(ZA_X)
+#undef ZA_X
+}
+
+}  // namespace za

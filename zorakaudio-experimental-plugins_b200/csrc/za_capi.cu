@@ -65,13 +65,19 @@ const char* cascade8_slider_text();
 const char* easyexpander_slider_text();
 const char* stft_mask2048_slider_text();
 
+void append_generated_plugins(std::vector<PluginDesc>& t);    // p_generic.cu: the translated DSP-JSFX leaves
+
 const std::vector<PluginDesc>& plugin_table()
 {
-    static const std::vector<PluginDesc> t = {
-        {"cascade8", 1, 1, 2, 0, cascade8_slider_text(), &make_cascade8},
-        {"EasyExpander", 2, 2, 0, 0, easyexpander_slider_text(), &make_easyexpander},
-        {"stft_mask2048", 2, 2, 2, 2048, stft_mask2048_slider_text(), &make_stft_mask2048},
-    };
+    static const std::vector<PluginDesc> t = [] {
+        std::vector<PluginDesc> v = {
+            {"cascade8", 1, 1, 2, 0, cascade8_slider_text(), &make_cascade8},
+            {"EasyExpander", 2, 2, 0, 0, easyexpander_slider_text(), &make_easyexpander},
+            {"stft_mask2048", 2, 2, 2, 2048, stft_mask2048_slider_text(), &make_stft_mask2048},
+        };
+        append_generated_plugins(v);
+        return v;
+    }();
     return t;
 }
 const PluginDesc* find_plugin(const char* key)

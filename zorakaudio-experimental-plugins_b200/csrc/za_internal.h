@@ -92,4 +92,26 @@ struct StftArgs {
 size_t stft_state_bytes();
 bool stft_launch(const StftArgs& a, int precision, int n_sm, cudaStream_t stream);
 
+// ---- translated DSP-JSFX leaves (csrc/gen/g_*.cu from za_gpu/jsfxc.py, runtime in jsfx_rt.cuh) -------------------
+struct GenLaunch {
+    const float* in; float* out; double* tap;      // [stream][ch][row_stride]
+    int64_t row_stride, n_frames, mem_slots;
+    int n_streams, block_len, n_rows, n_decl;
+    const double* q;                               // device [n_rows][n_streams][n_decl] quantised slider values
+    const int* decl_index0;                        // device [n_decl]: slider number - 1 of each column
+    void* state;                                   // [n_vars + 64 + 1][n_streams] of R: vars, st.sliders, lastSlidersValid
+    void* mem;                                     // [mem_slots][n_streams] of R: the script's mem[] heap
+    unsigned* mt;                                  // [625][n_streams]: MT19937 words + index
+    int* err;                                      // device flag: 1 = mem[] access beyond mem_slots
+    double srate;
+};
+struct GenDesc {
+    const char* key; const char* slider_text;
+    int n_in, n_out, n_vars; int64_t mem_slots;
+    const char* const* var_names;                  // n_vars names (DSPJSFX_VARS order of this translation), null-terminated
+    const int* alias;                              // [64]: vars slot mirrored by slider i0, or -1
+    bool (*prepare)(const GenLaunch&, int precision, cudaStream_t);
+    bool (*process)(const GenLaunch&, int precision, cudaStream_t);
+};
+
 }  // namespace za

@@ -19,14 +19,14 @@ COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-fvisibility=hi
 
 
 def sources():
-    return sorted(list(CSRC.glob("*.cu")) + list(CSRC.glob("*.cpp")))
+    return sorted(list(CSRC.glob("*.cu")) + list(CSRC.glob("*.cpp")) + list((CSRC / "gen").glob("*.cu")))
 
 
 def _stale(obj: Path, src: Path) -> bool:
     if not obj.exists():
         return True
     t = obj.stat().st_mtime
-    deps = [src] + list(CSRC.glob("*.h")) + list(CSRC.glob("*.cuh")) + [PKG.parent / "include" / "za_gpu.h"]
+    deps = [src] + list(CSRC.glob("*.h")) + list(CSRC.glob("*.cuh")) + list((CSRC / "gen").glob("*.h")) + [PKG.parent / "include" / "za_gpu.h"]
     return any(d.stat().st_mtime > t for d in deps)
 
 

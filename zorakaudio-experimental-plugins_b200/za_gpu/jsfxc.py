@@ -342,14 +342,37 @@ def split_script(text: str):
     return "\n".join(header), {k: ("\n".join(v), start[k]) for k, v in secs.items()}
 
 
-def pin_counts(header: str, used_spl: set):
-    ins = [l for l in header.splitlines() if re.match(r"^\s*in_pin\s*:", l)]
-    outs = [l for l in header.splitlines() if re.match(r"^\s*out_pin\s*:", l)]
-    none = lambda ls: any(re.match(r"^\s*\w+\s*:\s*none\s*$", l) for l in ls)
-    hi = (max(used_spl) + 1) if used_spl else 0
-    n_in = 0 if none(ins) else (len(ins) if ins else hi)
-    n_out = 0 if none(outs) else (len(outs) if outs else hi)
-    return n_in, n_out
+def pin_counts(header: str, reads: set, writes: set):
+    """Channel counts as the reference infers them (dsp_jsfx_aot.py parse_pin_hints :1110-1136, infer_spl_io :1662):
+    in_pin / out_pin lines win ('none' = 0 pins); else a read of splN needs N+1 inputs, a write N+1 outputs; an
+    undeclared empty side mirrors the other; nothing at all = stereo."""
+    saw, cnt = {"in_pin": False, "out_pin": False}, {"in_pin": 0, "out_pin": 0}
+    for raw in header.splitlines():
+        line = raw.split("//", 1)[0].split(";", 1)[0]
+        m = re.match(r"^\s*(in_pin|out_pin)\s*:\s*(.*?)\s*$", line, re.I)
+        if not m:
+            continue
+        k = m.group(1).lower()
+        saw[k] = True
+        if m.group(2).strip().lower() == "none":
+            cnt[k] = 0
+        else:
+            cnt[k] += 1
+    d_in = cnt["in_pin"] if saw["in_pin"] else None
+    d_out = cnt["out_pin"] if saw["out_pin"] else None
+    n_in = (max(reads) + 1) if reads else 0
+    n_out = (max(writes) + 1) if writes else 0
+    if d_in is not None:
+        n_in = d_in
+    if d_out is not None:
+        n_out = d_out
+    if d_in is None and d_out is None and n_in == 0 and n_out == 0:
+        n_in = n_out = 2
+    if d_in is None and n_in == 0 and n_out > 0:
+        n_in = n_out
+    if d_out is None and n_out == 0 and n_in > 0:
+        n_out = n_in
+    return min(n_in, 64), min(n_out, 64)
 
 
 MATH1 = {"sin", "cos", "tan", "asin", "acos", "atan", "exp", "log", "log10", "sqrt", "floor", "ceil", "abs"}
@@ -390,12 +413,13 @@ class Unit:
             self.progs[s] = keep
         self.vars = {}            # jsfx name -> slot
         self.used_spl = set()
+        self.spl_reads, self.spl_writes = set(), set()
         self.used_sliders = set()
         self.spec = {}            # (section, fn) -> C name
         self.spec_code = []       # emitted function definitions, callee first
         self.in_progress = set()
         self.body = {s: Emitter(self, s, {}, set()).run(self.progs[s]) for s in SECTIONS}
-        self.n_in, self.n_out = pin_counts(header, self.used_spl)
+        self.n_in, self.n_out = pin_counts(header, self.spl_reads, self.spl_writes)
         self.alias = {}           # slider index0 -> var name
         for l in self.slider_lines:
             m = re.match(r"^\s*slider(\d+)\s*:\s*([A-Za-z_][A-Za-z0-9_.]*)\s*=", l)
@@ -457,7 +481,7 @@ class Emitter:
         return t
 
     # ---- variables --------------------------------------------------------------------------------------
-    def ref(self, name: str) -> str:
+    def ref(self, name: str, write: bool = False, read: bool = True) -> str:
         if name in self.params:
             return "p_" + re.sub(r"[^A-Za-z0-9_]", "_", name)
         name = self.local_map.get(name, name)
@@ -469,6 +493,10 @@ class Emitter:
             if i >= 64:
                 raise NotImplementedError("spl index >= 64")
             self.u.used_spl.add(i)
+            if write:
+                self.u.spl_writes.add(i)
+            if read:
+                self.u.spl_reads.add(i)
             return f"c.spl[{i}]"
         m = re.fullmatch(r"slider(\d+)", name)
         if m and 1 <= int(m.group(1)) <= 64:
@@ -497,6 +525,8 @@ class Emitter:
                 return "R(1.618033988749895)"
             if name.startswith("$x"):
                 return lit(float(int(name[2:], 16)))
+            if name == "mem":                      # mem[i]: the heap itself is base 0 (:4273-4275)
+                return "R(0)"
             return self.tmp(self.ref(name))
         if k == "index":
             b = self.ex(n[1]); i = self.ex(n[2])
@@ -553,7 +583,7 @@ class Emitter:
             op, tgt = n[1], n[2]
             rhs = self.ex(n[3])
             if tgt[0] == "var":
-                lv = self.ref(tgt[1])
+                lv = self.ref(tgt[1], write=True, read=(op != "="))
                 if op == "=":
                     self.w(f"{lv} = {rhs};")
                     return rhs
@@ -695,6 +725,8 @@ def generate(key: str, jsfx_path: str, mem_slots: int, source_label: str) -> str
         out.append("")
     out.append("static const char* const kVarNames[] = {" + ", ".join('"%s"' % n.replace('"', "") for n in names) + (", " if names else "") + "nullptr};")
     out.append("static const int kAlias[64] = {" + ", ".join(map(str, alias_slots)) + "};")
+    sel = "".join(f"i0 == {i} ? {a} : " for i, a in enumerate(alias_slots) if a >= 0)
+    out.append(f"__host__ __device__ constexpr int alias_slot(int i0) {{ return {sel}-1; }}")
     out.append("static const char kSliderText[] =")
     for l in u.slider_lines:
         out.append("    " + c_string(l.strip()))
