@@ -1,0 +1,117 @@
+"""GPU parity tests for the translated DSP-JSFX leaves (csrc/gen/g_*.cu written by za_gpu/jsfxc.py, runtime
+csrc/jsfx_rt.cuh): the CUDA path through the C ABI against the reference's own compiled DSP (oracle/_ref) on the
+same seeded inputs.
+
+Criteria (BASELINE.json north_star / SURVEY.md section 8c):
+  fp64 mode: |gpu - ref| <= 1e-12 * max(|ref|, block peak) on the doubles before the float store;
+  integer / indexing state (counters, ring positions, flags): exact;
+  fp32 mode: residual vs the reference render below -100 dBFS RMS where the leaf's logic is stable in float."""
+import numpy as np
+import pytest
+
+import za_oracle as zo
+from za_gpu import workloads as wl
+
+pytestmark = pytest.mark.gpu
+KEYS = ["RTT", "SOMA", "ATTACK", "ERBTilt", "SpectralStabilizer", "DDT"]
+TOL64 = 1e-12
+
+
+def block_peak(ref, block=512):
+    ns, nc, nf = ref.shape
+    nb = (nf + block - 1) // block
+    pad = np.zeros((ns, nc, nb * block))
+    pad[:, :, :nf] = np.abs(ref)
+    pk = pad.reshape(ns, nc, nb, block).max(axis=3)
+    return np.repeat(pk, block, axis=2)[:, :, :nf]
+
+
+def rel_err(got, ref):
+    floor = np.maximum(block_peak(ref), 1e-3 * np.abs(ref).max(axis=2, keepdims=True))
+    return np.abs(got - ref) / np.maximum(np.maximum(np.abs(ref), floor), 1e-300)
+
+
+@pytest.fixture(scope="module")
+def gpu(built_lib):
+    import za_gpu
+    if za_gpu.lib().za_gpu_device_count() < 1:
+        pytest.fail("GPU test run without a CUDA device")
+    return za_gpu
+
+
+def make_case(ref, ns, nf, automate, block=512):
+    x = wl.programme_bursts(ns, nf, n_ch=ref.n_in)
+    base = np.array([s["default"] for s in ref.sliders], np.float32)
+    if automate:
+        p = wl.automation(ref.sliders, (nf + block - 1) // block, ns, which=list(range(min(3, len(base)))), base=base)
+    else:
+        p = np.tile(base, (ns, 1))
+    return p, x
+
+
+@pytest.mark.parametrize("key", KEYS)
+@pytest.mark.parametrize("automate", [False, True])
+def test_fp64_parity_and_state(gpu, key, automate):
+    ref = zo.RefPlugin(key)
+    ns, nf = 37, 24000 + 77                      # two warps of streams (one ragged), ragged last block
+    p, x = make_case(ref, ns, nf, automate)
+    y, yd, v = ref.render(p, x, want_f64=True, want_vars=True)
+    info = gpu.plugin_info(key)
+    assert (info.n_in, info.n_out) == (ref.n_in, ref.n_out)
+    bp = gpu.BatchProcessor(key, ns, precision="f64").prepare(p if p.ndim == 2 else p[0])
+    tap = np.zeros_like(yd)
+    out = bp.process(x, tap64=tap, params=p if p.ndim == 3 else None)
+    e = rel_err(tap, yd).max()
+    assert e <= TOL64, e
+    assert np.mean(out == y) > 0.9999
+    # every variable the reference holds: integer-valued ones exact, the rest to rounding of libm
+    checked = 0
+    for name, want in v.items():
+        try:
+            got = bp.read_state(name)
+        except Exception:
+            continue                              # compiler-internal names of the reference build
+        checked += 1
+        if np.all(want == np.round(want)) and np.abs(want).max() < 2 ** 40:
+            assert np.array_equal(got, want), name
+        else:
+            assert np.abs(got - want).max() <= 1e-9 * max(1.0, np.abs(want).max()), name
+    assert checked > 10
+    bp.close()
+
+
+@pytest.mark.parametrize("key", ["RTT", "SOMA"])
+def test_split_calls_match_one_shot(gpu, key):
+    """State (vars, mem[] rings, rand state, slider memory) carries across calls."""
+    ref = zo.RefPlugin(key)
+    ns, nf = 5, 512 * 30 + 100
+    p, x = make_case(ref, ns, nf, True)
+    y, yd = ref.render(p, x, want_f64=True)
+    bp = gpu.BatchProcessor(key, ns, precision="f64").prepare(p[0])
+    tap = np.zeros_like(yd)
+    for a, b in ((0, 512 * 2), (512 * 2, 512 * 19), (512 * 19, nf)):
+        t = np.zeros((ns, ref.n_out, b - a))
+        bp.process(np.ascontiguousarray(x[:, :, a:b]), tap64=t, params=p[a // 512:])
+        tap[:, :, a:b] = t
+    assert rel_err(tap, yd).max() <= TOL64
+    bp.close()
+
+
+# float mode: leaves whose state is well conditioned in float meet the -100 dBFS criterion; leaves with long
+# phase / delay-position accumulators do not and are documented as fp64-only in DESIGN.md (xfail, not hidden).
+FP32_UNSTABLE = {"DDT", "SOMA", "SpectralStabilizer", "ATTACK"}
+
+
+@pytest.mark.parametrize("key", [pytest.param(k, marks=pytest.mark.xfail(strict=False, reason="fp32 state conditioning")) if k in FP32_UNSTABLE else k for k in KEYS])
+def test_fp32_mode_residual(gpu, key):
+    ref = zo.RefPlugin(key)
+    ns, nf = 8, 48000
+    p, x = make_case(ref, ns, nf, False)
+    y, yd = ref.render(p, x, want_f64=True)
+    bp = gpu.BatchProcessor(key, ns, precision="f32").prepare(p)
+    out = bp.process(x)
+    r = out.astype(np.float64) - yd
+    db = 20 * np.log10(np.sqrt(np.mean(r ** 2)) + 1e-300)
+    print(f"{key}: fp32 residual {db:.1f} dBFS rms")
+    assert db < -100.0, db
+    bp.close()

@@ -242,24 +242,28 @@ __global__ void __launch_bounds__(32) jsfx_process_kernel(const GenLaunch a)
     extern __shared__ float tile[];                // [kCh][32 streams][33]
     constexpr int kP = 33;
     const int lane = threadIdx.x, s0 = blockIdx.x * 32, s = s0 + lane;
-    const bool live = s < a.n_streams;
-    const int sc = live ? s : a.n_streams - 1;     // dead lanes shadow the last stream and never store
+    const bool live = s < a.n_streams;             // dead lanes only help move the audio tiles
     const int ns_cta = min(32, a.n_streams - s0);
     Rt<R> c;
     R v[S::kVars];
-    ctx_open<S, R>(c, v, a, sc);
-    bool valid = reinterpret_cast<const R*>(a.state)[(long long)(S::kVars + 64) * a.n_streams + sc] != (R)0;
+    bool valid = false;
+    if (live) {
+        ctx_open<S, R>(c, v, a, s);
+        valid = reinterpret_cast<const R*>(a.state)[(long long)(S::kVars + 64) * a.n_streams + s] != (R)0;
+    }
 
     int64_t pos = 0;
     for (int blk = 0; pos < a.n_frames; ++blk) {
         const int nb = (int)min((int64_t)a.block_len, a.n_frames - pos);
-        if (a.n_rows > 0) {
-            const bool changed = push_sliders<S, R>(c, v, a, blk < a.n_rows ? blk : a.n_rows - 1, sc, valid);
-            valid = true;
-            if (changed) S::template slider<R>(c, v);
+        if (live) {
+            if (a.n_rows > 0) {
+                const bool changed = push_sliders<S, R>(c, v, a, blk < a.n_rows ? blk : a.n_rows - 1, s, valid);
+                valid = true;
+                if (changed) S::template slider<R>(c, v);
+            }
+            c.samplesblock = (R)nb;
+            S::template block<R>(c, v);
         }
-        c.samplesblock = (R)nb;
-        S::template block<R>(c, v);
         for (int f0 = 0; f0 < nb; f0 += 32) {
             const int nf = min(32, nb - f0);
             // tile in: lane = frame, 128-byte rows
@@ -267,14 +271,16 @@ __global__ void __launch_bounds__(32) jsfx_process_kernel(const GenLaunch a)
                 for (int ch = 0; ch < S::kIn; ++ch)
                     tile[(ch * 32 + r) * kP + lane] = lane < nf ? a.in[((size_t)(s0 + r) * S::kIn + ch) * a.row_stride + pos + f0 + lane] : 0.f;
             __syncwarp();
-            for (int f = 0; f < nf; ++f) {
+            if (live) {
+                for (int f = 0; f < nf; ++f) {
 #pragma unroll
-                for (int ch = 0; ch < S::kCh; ++ch) c.spl[ch] = ch < S::kIn ? (R)tile[(ch * 32 + lane) * kP + f] : (R)0;
-                S::template sample<R>(c, v);
+                    for (int ch = 0; ch < S::kCh; ++ch) c.spl[ch] = ch < S::kIn ? (R)tile[(ch * 32 + lane) * kP + f] : (R)0;
+                    S::template sample<R>(c, v);
 #pragma unroll
-                for (int ch = 0; ch < S::kOut; ++ch) {
-                    if (TAP && live) a.tap[((size_t)s * S::kOut + ch) * a.row_stride + pos + f0 + f] = (double)c.spl[ch];
-                    tile[(ch * 32 + lane) * kP + f] = (float)c.spl[ch];
+                    for (int ch = 0; ch < S::kOut; ++ch) {
+                        if (TAP) a.tap[((size_t)s * S::kOut + ch) * a.row_stride + pos + f0 + f] = (double)c.spl[ch];
+                        tile[(ch * 32 + lane) * kP + f] = (float)c.spl[ch];
+                    }
                 }
             }
             __syncwarp();
