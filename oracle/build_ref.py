@@ -37,6 +37,12 @@ PLUGINS = {
     "ERBTilt": (REF / "plugins/Spectral/ERBTilt/src/ERB Tilt.jsfx", False),
     "SpectralStabilizer": (REF / "plugins/Spectral/SpectralStabilizer/src/Spectral Stabilizer.jsfx", False),
     "DDT": (REF / "plugins/Spatialization/DDT/src/DDT.jsfx", False),
+    "DPT": (REF / "plugins/Spatialization/DPT/src/DPT.jsfx", False),
+    "SaliencePush": (REF / "plugins/Spatialization/SaliencePush/src/SP.jsfx", False),
+    "ADS": (REF / "plugins/Ambience/ADS/src/ADS.jsfx", False),
+    "BedRock": (REF / "plugins/Spectral/BedRock/src/BedRock.jsfx", False),
+    "Roomalizer": (REF / "plugins/Spatialization/Roomalizer/src/Roomalizer.jsfx", False),
+    "TSEQ": (REF / "plugins/Spectral/TSEQ/src/TSEQ.jsfx", False),
 }
 
 

@@ -12,7 +12,8 @@ import za_oracle as zo
 
 
 @pytest.mark.parametrize("key,auto", [("RTT", True), ("SOMA", False), ("ATTACK", True), ("ERBTilt", False),
-                                      ("SpectralStabilizer", True), ("DDT", False)])
+                                      ("SpectralStabilizer", True), ("DDT", False), ("DPT", True), ("SaliencePush", False),
+                                      ("ADS", True), ("BedRock", False), ("Roomalizer", True), ("TSEQ", False)])
 def test_translation_is_bit_identical_on_host(key, auto):
     if not zo.have_ref(key):
         pytest.skip("oracle/_ref not built")
