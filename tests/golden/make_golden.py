@@ -49,3 +49,17 @@ if __name__ == "__main__":
     nfs = 24000 + 77
     golden("stft_mask2048", wl.automation(st.sliders, (nfs + 511) // 512, 3, which=[0, 1, 4]), wl.programme_bursts(3, nfs), tag="_auto")
     golden("EasyExpander", wl.automation(ee.sliders, (nf + 511) // 512, 6, which=[0, 1]), wl.programme_bursts(6, nf), tag="_auto")
+    # translated leaves (csrc/gen): one stream, 9000 frames, first three sliders automated every block
+    leaves = {}
+    for key in ("RTT", "SOMA", "ATTACK", "ERBTilt", "SpectralStabilizer", "DDT", "DPT", "SaliencePush", "ADS", "BedRock",
+                "Roomalizer", "TSEQ"):
+        ref = zo.RefPlugin(key)
+        nfl = 9000
+        base = np.array([s["default"] for s in ref.sliders], np.float32)
+        p = wl.automation(ref.sliders, (nfl + 511) // 512, 1, which=list(range(min(3, len(base)))), base=base)
+        x = wl.programme_bursts(1, nfl, n_ch=ref.n_in)
+        y, yd = ref.render(p, x, want_f64=True, threads=1)
+        leaves[key + "_y64_tail"] = yd[0, :2, -1024:]
+        leaves[key + "_y64_sha256"] = np.frombuffer(hashlib.sha256(yd.tobytes()).digest(), np.uint8)
+    np.savez_compressed(HERE / "translated_leaves.npz", **leaves)
+    print(HERE / "translated_leaves.npz", (HERE / "translated_leaves.npz").stat().st_size)
