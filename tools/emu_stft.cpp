@@ -50,9 +50,10 @@ static void run(const float* in, float* out, double* tap, int64_t n, const doubl
         for (int t = 0; t < kT; ++t) fwd1<R>(t, g[t], S, tb, hop);
         for (int t = 0; t < kT; ++t) fwd2<R>(t, g[t], S, tb);
         for (int t = 0; t < kT; ++t) fwd3<R>(t, g[t], S);
-        for (int t = 0; t < kT; ++t) { if (t == 0) mags<R, true>(t, g[t], S); else mags<R, false>(t, g[t], S); }
-        for (int t = 0; t < kT; ++t) { if (t == 0) gains<R, true>(t, g[t], S, c); else gains<R, false>(t, g[t], S, c); }
-        for (int t = 0; t < kT; ++t) { if (t == 0) apply_gains<R, true>(t, g[t], S); else apply_gains<R, false>(t, g[t], S); }
+        for (int t = 0; t < kT; ++t) t0_permute<R>(t == 0, g[t]);
+        for (int t = 0; t < kT; ++t) mags_u<R>(t, g[t], S);
+        for (int t = 0; t < kT; ++t) gains_u<R>(t, g[t], S, c);
+        for (int t = 0; t < kT; ++t) { apply_gains_u<R>(t, g[t], S); t0_unpermute<R>(t == 0, g[t]); }
         for (int t = 0; t < kT; ++t) inv3<R>(t, g[t], S);
         for (int t = 0; t < kT; ++t) inv2<R>(t, g[t], S, tb);
         for (int t = 0; t < kT; ++t) inv1_ola<R>(t, g[t], S, tb, hop);

@@ -135,8 +135,9 @@ __device__ __forceinline__ void gain_frame(R det_lin, R det_db, R tgv, const Gai
 {
     s.det_db_m = add(s.det_db_m, mul((R)0.02, sub(det_db, s.det_db_m)));
     s.det_slow = add(s.det_slow, mul(c.slow_c, sub(det_lin, s.det_slow)));
-    if (s.expanding == 0) { if (det_db < s.thresh_db) s.expanding = 1; }
-    else                  { if (det_db > s.thresh_hi) s.expanding = 0; }
+    // hysteresis flag (:230-234) as predicate logic: lanes are different streams, a branch here would serialise them
+    const int below = det_db < s.thresh_db ? 1 : 0, above = det_db > s.thresh_hi ? 1 : 0;
+    s.expanding = (s.expanding & (above ^ 1)) | ((s.expanding ^ 1) & below);
     const R target_gr = s.expanding ? tgv : (R)0.0;
     const R target_gain_db = -target_gr;
     s.gr_db_m = add(s.gr_db_m, mul((R)0.05, sub(target_gr, s.gr_db_m)));
@@ -395,6 +396,256 @@ easyexpander_kernel(const EEArgs a, const int spc /* streams per CTA, multiple o
     }
 }
 
+// ======================================================================================================================
+// fp32 variant with the frame-parallel stages on their own warps.  In the kernel above the band warps are the critical
+// path (ncu, profiles/r01_easyexpander_ncu.md: they never wait at the barrier): besides the band recurrence they also
+// load the batch, run the frame-parallel detector / gain-computer stage and write the output.  Here those lane = frame
+// stages move to 8 helper warps, so a band warp only runs the recurrence; one more pipeline step separates them:
+//   S0 helpers (batch i) | S1 filter (i-1) | P1 band warps (i-2) | P2 helpers (i-3) | S3 gain warp (i-4) | S4 helpers (i-5)
+// Needs block_len >= 32 (coefficient ring) -- other shapes use the kernel above.
+namespace {
+constexpr int kHelpWarps = 8;
+constexpr int kSplitThreads = (kBandWarps + 2 + kHelpWarps) * 32;
+constexpr int kInBufsS = 8;       // a batch's input lives from S0 (i) to S4 (i-5)
+constexpr int kCoefRingS = 8;     // host blocks alive between the filter warp (i-1) and the gain warp (i-4)
+struct EESmemS {
+    float in[kInBufsS][kMaxS * kInPitch];
+    float xd[2][kMaxS * kPitchF];
+    float bp[2][kBandWarps][4 * kBpStream];
+    float lin[2][kMaxS * kPitchF], db[2][kMaxS * kPitchF], tg[2][kMaxS * kPitchF], gain[2][kMaxS * kPitchF];
+    float cs[kCoefRingS][3][kMaxS];
+};
+}  // namespace
+
+__global__ void __launch_bounds__(kSplitThreads, 1)
+easyexpander_split_kernel(const EEArgs a, const int spc)
+{
+    typedef float R;
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    EESmemS& sm = *reinterpret_cast<EESmemS*>(smem_raw);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int s_base = blockIdx.x * spc;
+    const int ns_cta = min(spc, a.n_streams - s_base);
+    const size_t ns = (size_t)a.n_streams;
+    const int64_t n = a.n_frames;
+    const int64_t n_batches = (n + kF - 1) / kF;
+    const int64_t n_iter = n_batches + 5;
+    const R eps = (R)1e-12, db_per_ln = (R)8.685889638065037, ln_per_db = (R)0.115129254649702;
+    const R knee_db = (R)6.0, hys_db = (R)2.0;
+
+    if (warp < kBandWarps) {
+        // ============================ band warps: the SVF + power-follower recurrence only =========================
+        const int sl = lane >> 3, j = lane & 7;
+        const int ls = 4 * warp + sl;
+        const bool act = 4 * warp < ns_cta, live = ls < ns_cta;
+        const int sg = s_base + (live ? ls : (ns_cta - 1));
+        const BandK<R> bk{(R)a.k.g[j], (R)a.k.den[j], (R)a.k.w[j], (R)a.k.band_c, (R)(1.0 / a.k.den[j]),
+                          (R)(-a.k.g[j] / a.k.den[j]), (R)(a.k.g[j] / a.k.den[j]), (R)(2.0 * a.k.g[j])};
+        double* st = a.state + sg;
+        R ic1 = (R)st[(0 + j) * ns], ic2 = (R)st[(8 + j) * ns], env = (R)st[(16 + j) * ns];
+        for (int64_t i = 0; i < n_iter; ++i) {
+            if (act && i >= 2 && i - 2 < n_batches) {
+                const int64_t b = i - 2;
+                const R* xd = sm.xd[b & 1] + ls * kPitchF;
+                const int nv = (int)min((int64_t)kF, n - b * kF);
+                R* bpw = sm.bp[b & 1][warp] + sl * kBpStream + j;
+                if (nv == kF) {
+#pragma unroll 1
+                    for (int f0 = 0; f0 < kF; f0 += 8) band_group<R, true>(xd, bpw, f0, nv, bk, ic1, ic2, env);
+                } else {
+#pragma unroll 1
+                    for (int f0 = 0; f0 < kF; f0 += 8) band_group<R, false>(xd, bpw, f0, nv, bk, ic1, ic2, env);
+                }
+            }
+            __syncthreads();
+        }
+        if (live) {
+            st = a.state + s_base + ls;
+            st[(0 + j) * ns] = (double)ic1; st[(8 + j) * ns] = (double)ic2; st[(16 + j) * ns] = (double)env;
+        }
+    } else if (warp == kBandWarps) {
+        // ============================ filter warp: lane = stream (batch i-1) =======================================
+        const bool live = lane < ns_cta;
+        const int sg = s_base + (live ? lane : 0);
+        double* st = a.state + sg;
+        FiltS<R> fs{(R)st[24 * ns], (R)st[25 * ns], (R)0, (R)0, 0, 0};
+        int64_t next_block_frame = 0;
+        int blk = 0;
+        for (int64_t i = 0; i < n_iter; ++i) {
+            if (live && i >= 1 && i - 1 < n_batches) {
+                const int64_t b = i - 1;
+                const float* ib = sm.in[b & (kInBufsS - 1)] + lane * kInPitch;
+                R* xd = sm.xd[b & 1] + lane * kPitchF;
+                const int nv = (int)min((int64_t)kF, n - b * kF);
+#pragma unroll 1
+                for (int f0 = 0; f0 < kF; f0 += 8) {
+                    const int64_t g0 = b * kF + f0;
+                    if (next_block_frame >= g0 + 8 && f0 + 8 <= nv) {
+                        filter_group<R, true>(ib, xd, f0, nv, fs);
+                    } else {
+                        for (int k = 0; k < 8; ++k) {
+                            const int f = f0 + k;
+                            if (f < nv && b * kF + f >= next_block_frame) {      // host-block boundary: sliders sampled once per block
+                                const EECoef& c = a.coef[(size_t)(blk < a.n_coef_blocks ? blk : a.n_coef_blocks - 1) * ns + sg];
+                                fs.hpf_c = (R)c.hpf_c; fs.lpf_c = (R)c.lpf_c; fs.hpf_on = c.hpf_on; fs.lpf_on = c.lpf_on;
+                                sm.cs[blk & (kCoefRingS - 1)][0][lane] = (R)c.thresh_db;
+                                sm.cs[blk & (kCoefRingS - 1)][1][lane] = (R)c.depth_db;
+                                sm.cs[blk & (kCoefRingS - 1)][2][lane] = (R)c.ratio_base;
+                                ++blk; next_block_frame += a.block_len;
+                            }
+                            R x_det = mul((R)0.5, add((R)ib[f], (R)ib[kPitchF + f]));
+                            if (f < nv) {
+                                if (fs.hpf_on) { fs.hpf_lp = add(fs.hpf_lp, mul(fs.hpf_c, sub(x_det, fs.hpf_lp))); x_det = sub(x_det, fs.hpf_lp); }
+                                if (fs.lpf_on) { fs.lpf_y = add(fs.lpf_y, mul(fs.lpf_c, sub(x_det, fs.lpf_y))); x_det = fs.lpf_y; }
+                            }
+                            xd[f] = x_det;
+                        }
+                    }
+                }
+            }
+            __syncthreads();
+        }
+        if (live) { st[24 * ns] = (double)fs.hpf_lp; st[25 * ns] = (double)fs.lpf_y; }
+    } else if (warp == kBandWarps + 1) {
+        // ============================ gain warp: lane = stream (batch i-4) =========================================
+        const bool live = lane < ns_cta;
+        const int sg = s_base + (live ? lane : 0);
+        double* st = a.state + sg;
+        const GainK<R> gk{(R)a.k.open_c, (R)a.k.close_fast_c, (R)a.k.close_slow_c, (R)a.k.slow_c};
+        GainS<R> gs{(R)st[26 * ns], (R)st[28 * ns], (R)st[29 * ns], (R)st[30 * ns], (R)0, (R)0, st[27 * ns] != 0.0};
+        int64_t next_block_frame = 0;
+        int blk = 0;
+        for (int64_t i = 0; i < n_iter; ++i) {
+            if (live && i >= 4 && i - 4 < n_batches) {
+                const int64_t b = i - 4;
+                const int o = lane * kPitchF;
+                const R* lin = sm.lin[b & 1] + o; const R* db = sm.db[b & 1] + o; const R* tg = sm.tg[b & 1] + o;
+                R* gout = sm.gain[b & 1] + o;
+                const int nv = (int)min((int64_t)kF, n - b * kF);
+#pragma unroll 1
+                for (int f0 = 0; f0 < kF; f0 += 8) {
+                    R lv[8], dv[8], tv[8], go[8];
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) { lv[k] = lin[f0 + k]; dv[k] = db[f0 + k]; tv[k] = tg[f0 + k]; }
+                    const int64_t g0 = b * kF + f0;
+                    if (next_block_frame >= g0 + 8 && f0 + 8 <= nv) {
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) { gain_frame<R>(lv[k], dv[k], tv[k], gk, gs); go[k] = gs.gain_db_s; }
+                    } else {
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) {
+                            if (f0 + k < nv) {
+                                if (g0 + k >= next_block_frame) {
+                                    gs.thresh_db = sm.cs[blk & (kCoefRingS - 1)][0][lane];
+                                    gs.thresh_hi = add(gs.thresh_db, hys_db);
+                                    ++blk; next_block_frame += a.block_len;
+                                }
+                                gain_frame<R>(lv[k], dv[k], tv[k], gk, gs);
+                            }
+                            go[k] = gs.gain_db_s;
+                        }
+                    }
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) gout[f0 + k] = go[k];
+                }
+            }
+            __syncthreads();
+        }
+        if (live) {
+            st[26 * ns] = (double)gs.det_slow; st[27 * ns] = gs.expanding ? 1.0 : 0.0; st[28 * ns] = (double)gs.gain_db_s;
+            st[29 * ns] = (double)gs.det_db_m; st[30 * ns] = (double)gs.gr_db_m;
+        }
+    } else {
+        // ============================ helper warps: lane = frame; streams h, h + 8, h + 16, h + 24 of the CTA ========
+        const int h = warp - (kBandWarps + 2);
+        const float* irow[4]; float* orow[4];
+        bool has[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int lq = h + kHelpWarps * q;
+            has[q] = lq < ns_cta;
+            const size_t s = (size_t)(s_base + (has[q] ? lq : 0));
+            irow[q] = a.in + s * 2 * a.row_stride + lane; orow[q] = a.out + s * 2 * a.row_stride + lane;
+        }
+        float hold[4][2];
+        int64_t next2 = a.block_len;                          // first frame of host block blk2 + 1 (P2's block tracking)
+        int blk2 = 0;
+        for (int64_t i = 0; i < n_iter; ++i) {
+            // ---- S0 (issue): batch i ---------------------------------------------------------------------------
+            {
+                const int64_t fo = i * kF;
+                const bool ok = i < n_batches && fo + lane < n;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    hold[q][0] = (ok && has[q]) ? irow[q][fo] : 0.f;
+                    hold[q][1] = (ok && has[q]) ? irow[q][a.row_stride + fo] : 0.f;
+                }
+            }
+            // ---- P2: batch i-3: band sum in reference order, sqrt, log, memoryless gain computer --------------------
+            if (i >= 3 && i - 3 < n_batches) {
+                const int64_t b = i - 3;
+                const int64_t F0 = b * kF;
+                while (F0 >= next2) { ++blk2; next2 += a.block_len; }
+                const int slot = (blk2 + (F0 + lane >= next2 ? 1 : 0)) & (kCoefRingS - 1);
+                R det_lin[4], det_db[4], thr[4], dep[4], rat[4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int lq = h + kHelpWarps * q;
+                    const R* bp = sm.bp[b & 1][lq >> 2] + (lq & 3) * kBpStream + lane * 9;
+                    R sum = (R)0.0;
+#pragma unroll
+                    for (int bnd = 0; bnd < 8; ++bnd) sum = add(sum, bp[bnd]);
+                    det_lin[q] = sqrt_(jmax(sum, eps));
+                    thr[q] = sm.cs[slot][0][lq]; dep[q] = sm.cs[slot][1][lq]; rat[q] = sm.cs[slot][2][lq];
+                }
+#pragma unroll
+                for (int q = 0; q < 4; ++q) det_db[q] = mul(db_per_ln, log_(jmax(det_lin[q], eps)));
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    R d = sub(thr[q], det_db[q]);
+                    if (d < (R)0.0) d = (R)0.0;
+                    const R xk = div_<R>(d, knee_db);
+                    const R smo = mul(mul(xk, xk), sub((R)3.0, mul((R)2.0, xk)));
+                    const R ratio_eff = (d < knee_db) ? add((R)1.0, mul(sub(rat[q], (R)1.0), smo)) : rat[q];
+                    R target_gr = mul(d, sub(ratio_eff, (R)1.0));
+                    if (target_gr > dep[q]) target_gr = dep[q];
+                    const int o = (h + kHelpWarps * q) * kPitchF + lane;
+                    sm.lin[b & 1][o] = det_lin[q]; sm.db[b & 1][o] = det_db[q]; sm.tg[b & 1][o] = target_gr;
+                }
+            }
+            // ---- S4: batch i-5: exp and the output multiplies --------------------------------------------------------
+            if (i >= 5) {
+                const int64_t b = i - 5;
+                const int64_t fo = b * kF;
+                const bool okf = fo + lane < n;
+                const float* ib = sm.in[b & (kInBufsS - 1)];
+                R o0[4], o1[4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int lq = h + kHelpWarps * q;
+                    const R gain_lin = exp_(mul(sm.gain[b & 1][lq * kPitchF + lane], ln_per_db));
+                    o0[q] = mul((R)ib[lq * kInPitch + lane], gain_lin);
+                    o1[q] = mul((R)ib[lq * kInPitch + kPitchF + lane], gain_lin);
+                }
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                    if (okf && has[q]) { orow[q][fo] = (float)o0[q]; orow[q][a.row_stride + fo] = (float)o1[q]; }
+            }
+            // ---- S0 (commit): batch i -> shared memory ------------------------------------------------------------------
+            {
+                float* ib = sm.in[i & (kInBufsS - 1)];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int lq = h + kHelpWarps * q;
+                    ib[lq * kInPitch + lane] = hold[q][0];
+                    ib[lq * kInPitch + kPitchF + lane] = hold[q][1];
+                }
+            }
+            __syncthreads();
+        }
+    }
+}
+
 template <typename R, bool TAP>
 static bool launch_ee(const EEArgs& a, int n_sm, cudaStream_t stream)
 {
@@ -415,10 +666,28 @@ static bool launch_ee(const EEArgs& a, int n_sm, cudaStream_t stream)
     return cuda_ok(cudaGetLastError(), "easyexpander_kernel launch");
 }
 
-bool easyexpander_launch(const EEArgs& a, int precision, int n_sm, cudaStream_t stream)
+static bool launch_ee_split(const EEArgs& a, int n_sm, cudaStream_t stream)
+{
+    const size_t smem = sizeof(EESmemS);
+    static bool attr_done = false;
+    if (!attr_done) {
+        if (!cuda_ok(cudaFuncSetAttribute(easyexpander_split_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "EasyExpander smem attr")) return false;
+        attr_done = true;
+    }
+    int spc = (a.n_streams + n_sm - 1) / n_sm;
+    spc = (spc + 3) / 4 * 4;
+    if (spc > kMaxS) spc = kMaxS;
+    if (spc < 4) spc = 4;
+    const int blocks = (a.n_streams + spc - 1) / spc;
+    easyexpander_split_kernel<<<blocks, kSplitThreads, smem, stream>>>(a, spc);
+    return cuda_ok(cudaGetLastError(), "easyexpander_split_kernel launch");
+}
+
+bool easyexpander_launch(const EEArgs& a, int precision, int n_sm, cudaStream_t stream, int variant)
 {
     if (a.n_frames <= 0 || a.n_streams <= 0) return true;
     if (precision) return a.tap ? launch_ee<double, true>(a, n_sm, stream) : launch_ee<double, false>(a, n_sm, stream);
+    if (variant != 1 && a.block_len >= kF) return launch_ee_split(a, n_sm, stream);      // variant 1 = the single-role kernel
     return launch_ee<float, false>(a, n_sm, stream);
 }
 

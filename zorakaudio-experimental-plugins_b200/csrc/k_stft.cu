@@ -170,12 +170,14 @@ stft_mask_kernel(const StftArgs a)
         fwd2<R>(t, g, S, tb);
         bar_stream(sub);
         fwd3<R>(t, g, S);
+        t0_permute<R>(t == 0, g);              // thread 0's self-paired blocks into the regular pair layout
         bar_stream(sub);                       // every Z read done: the buffer now carries magnitudes and gains
-        if (t == 0) mags<R, true>(t, g, S); else mags<R, false>(t, g, S);
+        mags_u<R>(t, g, S);
         bar_stream(sub);
-        if (t == 0) gains<R, true>(t, g, S, cc); else gains<R, false>(t, g, S, cc);
+        gains_u<R>(t, g, S, cc);
         bar_stream(sub);
-        if (t == 0) apply_gains<R, true>(t, g, S); else apply_gains<R, false>(t, g, S);
+        apply_gains_u<R>(t, g, S);
+        t0_unpermute<R>(t == 0, g);
         bar_stream(sub);                       // every gain read done: the buffer carries Z again
         inv3<R>(t, g, S);
         bar_stream(sub);

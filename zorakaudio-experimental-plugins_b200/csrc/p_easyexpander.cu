@@ -119,7 +119,8 @@ class EasyExpander : public PluginImpl {
     cudaEvent_t ev_params = nullptr, ev_consumed = nullptr;   // upload done / previous rows consumed
     cudaStream_t up_stream = nullptr; // uploads overlap the previous call's kernel
     int n_sm = 148;
-    std::vector<EECoef> h_coef;
+    std::vector<EECoef> h_coef, h_coef_dev;   // host rows of this call / rows currently in d_coef
+    bool coef_valid = false;
 
 public:
     ~EasyExpander() override { cudaFree(d_state); cudaFree(d_coef); cudaFree(d_params); cudaFree(d_per_stream); if (ev_params) cudaEventDestroy(ev_params); if (ev_consumed) cudaEventDestroy(ev_consumed); if (up_stream) cudaStreamDestroy(up_stream); }
@@ -175,18 +176,26 @@ public:
                 }
             }
         });
-        if (h_coef.size() > coef_cap) {
-            cudaFree(d_coef);
-            if (!cuda_ok(cudaMalloc(&d_coef, h_coef.size() * sizeof(EECoef)), "EasyExpander coef")) { coef_cap = 0; d_coef = nullptr; return false; }
-            coef_cap = h_coef.size();
+        // unchanged coefficient rows stay on the device (a pageable upload would synchronise the stream first)
+        const bool same = coef_valid && h_coef.size() == h_coef_dev.size() &&
+                          std::memcmp(h_coef.data(), h_coef_dev.data(), h_coef.size() * sizeof(EECoef)) == 0;
+        if (!same) {
+            coef_valid = false;
+            if (h_coef.size() > coef_cap) {
+                cudaFree(d_coef);
+                if (!cuda_ok(cudaMalloc(&d_coef, h_coef.size() * sizeof(EECoef)), "EasyExpander coef")) { coef_cap = 0; d_coef = nullptr; return false; }
+                coef_cap = h_coef.size();
+            }
+            if (!cuda_ok(cudaMemcpyAsync(d_coef, h_coef.data(), h_coef.size() * sizeof(EECoef), cudaMemcpyHostToDevice, I.stream), "EasyExpander coef upload"))
+                return false;
+            coef_valid = h_coef.size() <= (1u << 20);      // cache small (static) tables only
+            if (coef_valid) h_coef_dev = h_coef;
         }
-        if (!cuda_ok(cudaMemcpyAsync(d_coef, h_coef.data(), h_coef.size() * sizeof(EECoef), cudaMemcpyHostToDevice, I.stream), "EasyExpander coef upload"))
-            return false;
         EEArgs a{};
         a.in = in; a.out = out; a.tap = tap; a.row_stride = stride; a.n_frames = n;
         a.n_streams = ns; a.block_len = I.block_len; a.n_coef_blocks = nbq; a.coef = d_coef; a.state = d_state; a.k = k_;
         const bool timed = I.time_begin();
-        if (!easyexpander_launch(a, I.precision, n_sm, I.stream)) return false;
+        if (!easyexpander_launch(a, I.precision, n_sm, I.stream, I.opt_scalar_f32)) return false;
         if (timed) I.time_end();
         ++I.launches;
         // h_coef is pageable: the async copy was staged by the runtime before returning
@@ -219,6 +228,7 @@ public:
             ee_slider(sl, I.srate, ps[s]);
         }
         const size_t rows = (size_t)nb * ns;
+        coef_valid = false;                                // d_coef is rewritten by the parameter kernel
         if (rows * nd > params_cap) {
             cudaFree(d_params); d_params = nullptr; params_cap = 0;
             if (!cuda_ok(cudaMalloc(&d_params, rows * nd * sizeof(float)), "EasyExpander params")) return -1;
@@ -256,7 +266,7 @@ public:
         a.in = in; a.out = out; a.tap = tap; a.row_stride = stride; a.n_frames = n;
         a.n_streams = ns; a.block_len = I.block_len; a.n_coef_blocks = nb; a.coef = d_coef; a.state = d_state; a.k = k_;
         const bool timed = I.time_begin();
-        if (!easyexpander_launch(a, I.precision, n_sm, I.stream)) return -1;
+        if (!easyexpander_launch(a, I.precision, n_sm, I.stream, I.opt_scalar_f32)) return -1;
         if (timed) I.time_end();
         ++I.launches;
         return 1;

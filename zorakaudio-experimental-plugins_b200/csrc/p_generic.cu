@@ -31,8 +31,13 @@ class GenericPlugin : public PluginImpl {
         a.decl_index0 = d_index0; a.state = d_state; a.mem = d_mem; a.mt = d_mt; a.err = d_err; a.srate = I.srate;
         return a;
     }
+    std::vector<double> q_last;     // rows already on the device: static parameters are not uploaded again (a pageable
+                                    // cudaMemcpyAsync synchronises the stream first, which would serialise leaves that
+                                    // render concurrently on their own streams)
     bool upload_q(Instance& I, const double* q, size_t count)
     {
+        if (count == q_last.size() && count > 0 && std::memcmp(q, q_last.data(), count * sizeof(double)) == 0) return true;
+        q_last.assign(q, q + count);
         if (count > q_cap) {
             cudaFree(d_q); d_q = nullptr; q_cap = 0;
             if (!cuda_ok(cudaMalloc(&d_q, count * sizeof(double)), "slider rows")) return false;

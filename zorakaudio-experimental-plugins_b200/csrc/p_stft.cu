@@ -35,7 +35,8 @@ class StftMask : public PluginImpl {
     double* d_tab = nullptr;          // win[2048] | syn[2048] | tw1[15][128][2] | tw2[15][8][2]
     int n_sm = 148;
     size_t coef_cap = 0;
-    std::vector<StftCoef> h_coef;
+    std::vector<StftCoef> h_coef, h_coef_dev;   // host rows of this call / rows currently in d_coef
+    bool coef_valid = false;
     int64_t t_abs = 0;                // frames rendered since prepare
 
 public:
@@ -103,13 +104,21 @@ public:
                     else stft_slider(sl, I.srate, c);
                 }
         });
-        if (h_coef.size() > coef_cap) {
-            cudaFree(d_coef);
-            if (!cuda_ok(cudaMalloc(&d_coef, h_coef.size() * sizeof(StftCoef)), "stft coef")) { coef_cap = 0; d_coef = nullptr; return false; }
-            coef_cap = h_coef.size();
+        // unchanged coefficient rows stay on the device (a pageable upload would synchronise the stream first)
+        const bool same = coef_valid && h_coef.size() == h_coef_dev.size() &&
+                          std::memcmp(h_coef.data(), h_coef_dev.data(), h_coef.size() * sizeof(StftCoef)) == 0;
+        if (!same) {
+            coef_valid = false;
+            if (h_coef.size() > coef_cap) {
+                cudaFree(d_coef);
+                if (!cuda_ok(cudaMalloc(&d_coef, h_coef.size() * sizeof(StftCoef)), "stft coef")) { coef_cap = 0; d_coef = nullptr; return false; }
+                coef_cap = h_coef.size();
+            }
+            if (!cuda_ok(cudaMemcpyAsync(d_coef, h_coef.data(), h_coef.size() * sizeof(StftCoef), cudaMemcpyHostToDevice, I.stream), "stft coef upload"))
+                return false;
+            coef_valid = h_coef.size() <= (1u << 20);      // cache small (static) tables only
+            if (coef_valid) h_coef_dev = h_coef;
         }
-        if (!cuda_ok(cudaMemcpyAsync(d_coef, h_coef.data(), h_coef.size() * sizeof(StftCoef), cudaMemcpyHostToDevice, I.stream), "stft coef upload"))
-            return false;
         StftArgs a{};
         a.in = in; a.out = out; a.tap = tap; a.row_stride = stride; a.n_frames = n; a.t0 = t_abs;
         a.n_streams = ns; a.block_len = I.block_len; a.n_coef_blocks = nbq; a.coef = d_coef; a.state = d_state;

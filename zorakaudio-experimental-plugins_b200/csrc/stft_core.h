@@ -264,6 +264,94 @@ ZA_HD void apply_gains(int t, Regs<R>& g, StreamSmem<R>& S)
     }
 }
 
+// ---- uniform bins path: thread 0 first renames its registers into the regular pair layout (slot s < 4: P = v[s],
+// Q = v[15 - s]; s >= 4: P = v[4 + s], Q = v[11 - s]) so all 128 threads run ONE instruction stream; its slot 3 holds
+// the self-paired bins 0 (v[3]) and 1024 (v[12]), which only contribute magnitudes --------------------------------------
+template <typename R>
+ZA_HD void t0_permute(bool t0, Regs<R>& g)       // v' = [v1 v2 v3 v0 | v12..v15 | v8..v11 | v4..v7]
+{
+    Cx<R> n[16];
+    n[0] = g.v[1]; n[1] = g.v[2]; n[2] = g.v[3]; n[3] = g.v[0];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { n[4 + i] = g.v[12 + i]; n[8 + i] = g.v[8 + i]; n[12 + i] = g.v[4 + i]; }
+#pragma unroll
+    for (int i = 0; i < 16; ++i) { g.v[i].re = t0 ? n[i].re : g.v[i].re; g.v[i].im = t0 ? n[i].im : g.v[i].im; }
+}
+template <typename R>
+ZA_HD void t0_unpermute(bool t0, Regs<R>& g)
+{
+    Cx<R> n[16];
+    n[1] = g.v[0]; n[2] = g.v[1]; n[3] = g.v[2]; n[0] = g.v[3];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { n[12 + i] = g.v[4 + i]; n[8 + i] = g.v[8 + i]; n[4 + i] = g.v[12 + i]; }
+#pragma unroll
+    for (int i = 0; i < 16; ++i) { g.v[i].re = t0 ? n[i].re : g.v[i].re; g.v[i].im = t0 ? n[i].im : g.v[i].im; }
+}
+template <typename R>
+ZA_HD void mags_u(int t, Regs<R>& g, StreamSmem<R>& S)
+{
+    R* mag = S.mag();
+    const bool t0 = t == 0;
+#pragma unroll
+    for (int s = 0; s < 8; ++s) {
+        // thread 0, slot 3: bin 0 is self-paired (P = Q = v[3]); bin 1024 (v[12]) follows below
+        const Cx<R> p = g.v[slot_p<false>(s)];
+        const Cx<R> q = (t0 && s == 3) ? p : g.v[slot_q<false>(s)];
+        const R m = mag_of<R>(p, q);
+        g.magr[s] = m;
+        const int k = slot_bin_rt(t, s);
+        mag[k < 0 ? 0 : k] = m;
+    }
+    if (t0) mag[1024] = mag_of<R>(g.v[12], g.v[12]);
+}
+template <typename R>
+ZA_HD void gains_u(int t, Regs<R>& g, StreamSmem<R>& S, const Coef& c)
+{
+    const R* mag = S.mag();
+    R* gain = S.gain();
+    const R tiny = (R)1e-18, ab = (R)c.ab, bb = (R)c.bb, thresh = (R)c.thresh, amt = (R)c.amt, floor_g = (R)c.floor_g;
+    const R thr_den = max_((R)0.18, thresh);
+#pragma unroll
+    for (int s = 0; s < 8; ++s) {
+        const int k = slot_bin_rt(t, s);
+        if (k < 0) continue;                               // thread 0, slot 3: bins 0 / 1024 keep gain 1 and no state
+        const R magbin = g.magr[s];
+        R base_old = g.base[s];
+        if (base_old < tiny) base_old = max_(magbin, tiny);
+        g.base[s] = add_(mul_(ab, base_old), mul_(bb, magbin));
+        const R flux = div_(max_((R)0, sub_(magbin, g.prev[s])), add_(base_old, tiny));
+        g.prev[s] = magbin;
+        R neigh = mul_((R)0.25, add_(add_(add_(mag[k - 2 < 0 ? 0 : k - 2], mag[k - 1]), mag[k + 1]),
+                                     mag[k + 2 > kBins - 1 ? kBins - 1 : k + 2]));
+        if (neigh < tiny) neigh = base_old;
+        const R peak = div_(magbin, add_(neigh, tiny));
+        const R dp = clamp01(div_(sub_(peak, thresh), thr_den));
+        const R df = clamp01(div_(sub_(flux, (R)1), (R)2));
+        const R control = mul_(amt, clamp01(add_(mul_((R)0.7, dp), mul_((R)0.3, df))));
+        const R ref = add_(mul_((R)0.75, neigh), mul_((R)0.25, base_old));
+        const R hard = min_((R)1, div_(add_(ref, tiny), add_(magbin, tiny)));
+        R raw = sub_((R)1, mul_(control, sub_((R)1, hard)));
+        raw = max_(floor_g, min_((R)1, raw));
+        gain[k] = raw;
+    }
+    if (t == 0) { gain[0] = (R)1; gain[1024] = (R)1; }
+}
+template <typename R>
+ZA_HD void apply_gains_u(int t, Regs<R>& g, StreamSmem<R>& S)
+{
+    const R* gain = S.gain();
+#pragma unroll
+    for (int s = 0; s < 8; ++s) {
+        const int k = slot_bin_rt(t, s);
+        if (k < 0) continue;
+        const R sg = add_(add_(mul_((R)0.16, gain[k - 1]), mul_((R)0.68, gain[k])), mul_((R)0.16, gain[k + 1]));
+        Cx<R>& p = g.v[slot_p<false>(s)];
+        Cx<R>& q = g.v[slot_q<false>(s)];
+        p.re = mul_(p.re, sg); p.im = mul_(p.im, sg);
+        q.re = mul_(q.re, sg); q.im = mul_(q.im, sg);
+    }
+}
+
 // ---- inverse transform (unscaled, like WDL's) + overlap-add ---------------------------------------------------------
 template <typename R>
 ZA_HD void inv3(int t, Regs<R>& g, StreamSmem<R>& S)

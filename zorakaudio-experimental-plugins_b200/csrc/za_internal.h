@@ -67,7 +67,7 @@ struct EEArgs {
     double* state;                                 // [kEEState][n_streams]
     EEConsts k;
 };
-bool easyexpander_launch(const EEArgs& a, int precision, int n_sm, cudaStream_t stream);
+bool easyexpander_launch(const EEArgs& a, int precision, int n_sm, cudaStream_t stream, int variant = 0);
 
 // ---- stft_mask2048 (STFT class) ---------------------------------------------------------------------
 constexpr int kStftN = 2048, kStftHop = 512, kStftBins = 1025;
