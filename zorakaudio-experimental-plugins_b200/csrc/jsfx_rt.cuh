@@ -53,6 +53,13 @@ struct GenLaunch {
 #include "za_internal.h"
 #endif
 
+// User functions of a script: inlined by default, so the variable file v[] (constant indices only) is promoted to
+// registers; a leaf whose straight-line code then outgrows the instruction cache can be built with
+// -DZA_JSFX_FN=__noinline__ (v[] goes to local memory, calls are real calls).
+#ifndef ZA_JSFX_FN
+#define ZA_JSFX_FN __forceinline__
+#endif
+
 namespace za {
 namespace jsfx {
 
@@ -103,10 +110,17 @@ template <typename R> struct Rt {
     R sliders[64];
     R spl[64];
 
-    __device__ __forceinline__ long long addr(R base, R idx) const        // a[b] = mem[trunc(a + b + 1e-5)], negative -> 0 (:4062-4103)
+    // a[b] = mem[trunc(a + b + 1e-5)], negative -> 0 (:4062-4103).  fp64 mode follows the reference's double
+    // arithmetic; fp32 mode keeps the whole index computation in float / int32 (heaps are far below 2^24 slots, so
+    // integer-valued offsets are exact either way) instead of paying two F2F, two DADD and an F2I.S64 per access.
+    __device__ __forceinline__ long long addr(double base, double idx) const
     {
-        const double s = __dadd_rn(__dadd_rn((double)base, (double)idx), 1.0e-5);
-        const long long a = (long long)s;
+        const long long a = (long long)__dadd_rn(__dadd_rn(base, idx), 1.0e-5);
+        return a < 0 ? 0 : a;
+    }
+    __device__ __forceinline__ int addr(float base, float idx) const
+    {
+        const int a = (int)__fadd_rn(__fadd_rn(base, idx), 1.0e-5f);     // saturating conversion, NaN -> 0
         return a < 0 ? 0 : a;
     }
     __device__ __forceinline__ R ldi(long long a) const
@@ -114,13 +128,23 @@ template <typename R> struct Rt {
         if (a >= cap) { *err = 1; return (R)0; }      // the reference grows the heap and reads 0
         return mem[a * stride];
     }
+    __device__ __forceinline__ R ldi(int a) const     // fp32 mode: 32-bit index, one IMAD.WIDE to the address
+    {
+        if (a >= (int)cap) { *err = 1; return (R)0; }
+        return mem[(long long)a * (int)stride];
+    }
+    __device__ __forceinline__ void st(int a, R v)
+    {
+        if (a >= (int)cap) { *err = 1; return; }
+        mem[(long long)a * (int)stride] = v;
+    }
     __device__ __forceinline__ R ld(R base, R idx) const { return ldi(addr(base, idx)); }
     __device__ __forceinline__ void st(long long a, R v)
     {
         if (a >= cap) { *err = 1; return; }
         mem[a * stride] = v;
     }
-    __device__ void memset(R dest, R value, R len)                         // :5439-5495
+    __device__ __forceinline__ void memset(R dest, R value, R len)                         // :5439-5495
     {
         long long d = (long long)__dadd_rn((double)dest, 1.0e-5);
         if (d < 0) d = 0;
@@ -129,7 +153,7 @@ template <typename R> struct Rt {
         if (d + n > cap) { *err = 1; n = cap > d ? cap - d : 0; }
         for (long long i = 0; i < n; ++i) mem[(d + i) * stride] = value;
     }
-    __device__ void memcpy(R dest, R src, R len)                           // overlap permitted (memmove), returns 0
+    __device__ __forceinline__ void memcpy(R dest, R src, R len)                           // overlap permitted (memmove), returns 0
     {
         long long d = (long long)__dadd_rn((double)dest, 1.0e-5), s = (long long)__dadd_rn((double)src, 1.0e-5);
         if (d < 0) d = 0;
@@ -145,7 +169,8 @@ template <typename R> struct Rt {
 
     // MT19937, seed 0x4141F00D, lazily initialised while the index is 0 (:3880-4060); rand([max]) = genrand_int32 *
     // (1 / 0xFFFFFFFF) * max(1, floor(arg)) (:5294-5323)
-    __device__ unsigned genrand()
+    // (static: the context object itself never has its address taken, so its arrays can live in registers)
+    static __device__ __noinline__ unsigned genrand(unsigned* mt, long long stride)
     {
         const int N = 624, M = 397;
         unsigned idx = mt[624 * stride];
@@ -167,11 +192,11 @@ template <typename R> struct Rt {
         y ^= y >> 11; y ^= (y << 7) & 0x9D2C5680u; y ^= (y << 15) & 0xEFC60000u; y ^= y >> 18;
         return y;
     }
-    __device__ R rand(R arg, int has_arg)
+    __device__ __forceinline__ R rand(R arg, int has_arg)
     {
         R mx = has_arg ? m_floor(arg) : (R)1;
         if (mx < (R)1) mx = (R)1;
-        const double r = __dmul_rn((double)genrand(), 1.0 / 4294967295.0);
+        const double r = __dmul_rn((double)genrand(mt, stride), 1.0 / 4294967295.0);
         return (R)__dmul_rn(r, (double)mx);
     }
 };
@@ -187,7 +212,9 @@ __device__ __forceinline__ void ctx_open(Rt<R>& c, R* v, const GenLaunch& a, int
     c.mt = a.mt + sc; c.err = a.err;
     c.srate = (R)a.srate; c.samplesblock = (R)0;
     const R* st = reinterpret_cast<const R*>(a.state) + sc;
+#pragma unroll
     for (int k = 0; k < S::kVars; ++k) v[k] = st[(long long)k * ns];
+#pragma unroll
     for (int k = 0; k < 64; ++k) { c.sliders[k] = st[(long long)(S::kVars + k) * ns]; c.spl[k] = (R)0; }
 }
 template <class S, typename R>
@@ -195,7 +222,9 @@ __device__ __forceinline__ void ctx_close(const Rt<R>& c, const R* v, const GenL
 {
     const long long ns = a.n_streams;
     R* st = reinterpret_cast<R*>(a.state) + s;
+#pragma unroll
     for (int k = 0; k < S::kVars; ++k) st[(long long)k * ns] = v[k];
+#pragma unroll
     for (int k = 0; k < 64; ++k) st[(long long)(S::kVars + k) * ns] = c.sliders[k];
     st[(long long)(S::kVars + 64) * ns] = valid;
 }
@@ -205,9 +234,10 @@ template <class S, typename R>
 __device__ __forceinline__ bool push_sliders(Rt<R>& c, R* v, const GenLaunch& a, int row, int sc, bool valid)
 {
     bool changed = !valid;
-    const double* q = a.q + ((size_t)row * a.n_streams + sc) * a.n_decl;
-    for (int j = 0; j < a.n_decl; ++j) {
-        const int i0 = a.decl_index0[j];
+    const double* q = a.q + ((size_t)row * a.n_streams + sc) * S::kDecl;
+#pragma unroll
+    for (int j = 0; j < S::kDecl; ++j) {             // compile-time slider slots: sliders[] / vars stay in registers
+        const int i0 = S::decl(j);
         const R nv = (R)q[j];
         if (nv != c.sliders[i0]) changed = true;
         c.sliders[i0] = nv;
@@ -228,9 +258,10 @@ __global__ void __launch_bounds__(32) jsfx_prepare_kernel(const GenLaunch a)
     ctx_open<S, R>(c, v, a, s);                    // state and heap were zeroed by the host (resetStateStructOnly)
     push_sliders<S, R>(c, v, a, 0, s, false);
     S::template init<R>(c, v);
-    for (int j = 0; j < a.n_decl; ++j) {           // alias re-apply after @init (:3308-3316)
-        const int al = S::alias(a.decl_index0[j]);
-        if (al >= 0) v[al] = c.sliders[a.decl_index0[j]];
+#pragma unroll
+    for (int j = 0; j < S::kDecl; ++j) {           // alias re-apply after @init (:3308-3316)
+        const int al = S::alias(S::decl(j));
+        if (al >= 0) v[al] = c.sliders[S::decl(j)];
     }
     S::template slider<R>(c, v);
     ctx_close<S, R>(c, v, a, s, (R)1);
@@ -366,8 +397,9 @@ template <class S, typename R> void emu_process(const GenLaunch& a)
 #ifdef ZA_JSFX_HOST_EMU
 #define ZA_JSFX_DEFINE_PLUGIN(IDENT, KEY, MEM_SLOTS, HAS_BLOCK, HAS_SLIDER)                                            \
     struct Script {                                                                                                     \
-        static constexpr int kVars = g_##IDENT::kVars, kIn = g_##IDENT::kIn, kOut = g_##IDENT::kOut, kCh = g_##IDENT::kCh; \
+        static constexpr int kVars = g_##IDENT::kVars, kIn = g_##IDENT::kIn, kOut = g_##IDENT::kOut, kCh = g_##IDENT::kCh, kDecl = g_##IDENT::kDecl; \
         static constexpr int alias(int i0) { return g_##IDENT::alias_slot(i0); }                                        \
+        static constexpr int decl(int j) { return g_##IDENT::decl_slot(j); }                                            \
         template <typename R> static void init(Rt<R>& c, R* v) { sec_init<R>(c, v); }                                   \
         template <typename R> static void slider(Rt<R>& c, R* v) { sec_slider<R>(c, v); }                               \
         template <typename R> static void block(Rt<R>& c, R* v) { sec_block<R>(c, v); }                                 \
@@ -385,8 +417,9 @@ template <class S, typename R> void emu_process(const GenLaunch& a)
 #else
 #define ZA_JSFX_DEFINE_PLUGIN(IDENT, KEY, MEM_SLOTS, HAS_BLOCK, HAS_SLIDER)                                            \
     struct Script {                                                                                                     \
-        static constexpr int kVars = g_##IDENT::kVars, kIn = g_##IDENT::kIn, kOut = g_##IDENT::kOut, kCh = g_##IDENT::kCh; \
+        static constexpr int kVars = g_##IDENT::kVars, kIn = g_##IDENT::kIn, kOut = g_##IDENT::kOut, kCh = g_##IDENT::kCh, kDecl = g_##IDENT::kDecl; \
         static __host__ __device__ constexpr int alias(int i0) { return g_##IDENT::alias_slot(i0); }                    \
+        static __host__ __device__ constexpr int decl(int j) { return g_##IDENT::decl_slot(j); }                        \
         template <typename R> static __device__ __forceinline__ void init(Rt<R>& c, R* v) { sec_init<R>(c, v); }       \
         template <typename R> static __device__ __forceinline__ void slider(Rt<R>& c, R* v) { sec_slider<R>(c, v); }   \
         template <typename R> static __device__ __forceinline__ void block(Rt<R>& c, R* v) { sec_block<R>(c, v); }     \
@@ -397,7 +430,8 @@ template <class S, typename R> void emu_process(const GenLaunch& a)
     {                                                                                                                   \
         using S = g_##IDENT::Script;                                                                                    \
         static const ::za::GenDesc d = {KEY, g_##IDENT::kSliderText, S::kIn, S::kOut, S::kVars, (int64_t)(MEM_SLOTS),   \
-                                        g_##IDENT::kVarNames, g_##IDENT::kAlias, &launch_prepare<S>, &launch_process<S>}; \
+                                        g_##IDENT::kVarNames, g_##IDENT::kAlias, &launch_prepare<S>, &launch_process<S>,  \
+                                        S::kDecl, g_##IDENT::kDeclIndex0};                                             \
         return &d;                                                                                                      \
     }                                                                                                                   \
     namespace g_##IDENT {

@@ -402,19 +402,70 @@ easyexpander_kernel(const EEArgs a, const int spc /* streams per CTA, multiple o
 // load the batch, run the frame-parallel detector / gain-computer stage and write the output.  Here those lane = frame
 // stages move to 8 helper warps, so a band warp only runs the recurrence; one more pipeline step separates them:
 //   S0 helpers (batch i) | S1 filter (i-1) | P1 band warps (i-2) | P2 helpers (i-3) | S3 gain warp (i-4) | S4 helpers (i-5)
+// The band recurrence itself is issue-bound (ncu, profiles/r01_easyexpander_split_ncu.md: `not_selected` dominates),
+// so it runs on Blackwell's packed fp32 pipe: a lane owns TWO bands of a stream in the halves of 64-bit registers
+// (`fma.rn.f32x2`, SASS FFMA2), 4 lanes per stream, 8 streams per band warp, 4 band warps; the SVF is advanced in the
+// state-space form  u = 2 a2 ic2 + 2 bx x,  ic1' = (2 a1 - 1) ic1 + u,  s = 2 a1 ic1 + u (= 2 v1),  ic2' = ic2 + g s,
+// env' = (1 - c) env + (c / 4) s^2  -- 10 packed instructions per frame for two bands.
+// Warp roles are placed by scheduler (warp id & 3): every scheduler gets one band warp; the gain warp shares its
+// scheduler with nothing else, the filter warp with two helpers, the other six helpers sit three to a scheduler.
 // Needs block_len >= 32 (coefficient ring) -- other shapes use the kernel above.
 namespace {
 constexpr int kHelpWarps = 8;
-constexpr int kSplitThreads = (kBandWarps + 2 + kHelpWarps) * 32;
+constexpr int kBandWarpsS = 4;
+constexpr int kSplitWarps = 16;                       // launched; two of them have no role and leave at once
+constexpr int kSplitLive = kBandWarpsS + 2 + kHelpWarps;
+constexpr int kSplitThreads = kSplitWarps * 32;
 constexpr int kInBufsS = 8;       // a batch's input lives from S0 (i) to S4 (i-5)
 constexpr int kCoefRingS = 8;     // host blocks alive between the filter warp (i-1) and the gain warp (i-4)
+constexpr int kBpPitch = 12;      // floats per (stream, frame): 8 weighted band powers + pad, so the two LDS.128 of a
+                                  // lane = frame reader and the STS.64 of the band lanes are bank-conflict free
+constexpr int kBpStreamS = kF * kBpPitch + 8;
+enum { ROLE_BAND = 0, ROLE_FILTER = 4, ROLE_GAIN = 5, ROLE_NONE = 6, ROLE_HELP = 8 };
+//                                   sched:  0              1              2          3
+__constant__ int kRole[kSplitWarps] = {0,             1,             2,         3,
+                                       ROLE_HELP + 0, ROLE_HELP + 1, ROLE_GAIN, ROLE_FILTER,
+                                       ROLE_HELP + 2, ROLE_HELP + 3, ROLE_NONE, ROLE_HELP + 4,
+                                       ROLE_HELP + 5, ROLE_HELP + 6, ROLE_NONE, ROLE_HELP + 7};
 struct EESmemS {
     float in[kInBufsS][kMaxS * kInPitch];
     float xd[2][kMaxS * kPitchF];
-    float bp[2][kBandWarps][4 * kBpStream];
+    alignas(16) float bp[2][kMaxS * kBpStreamS];       // [stream][frame][band]
     float lin[2][kMaxS * kPitchF], db[2][kMaxS * kPitchF], tg[2][kMaxS * kPitchF], gain[2][kMaxS * kPitchF];
     float cs[kCoefRingS][3][kMaxS];
 };
+__device__ __forceinline__ void split_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kSplitLive * 32) : "memory"); }
+
+// two floats in one 64-bit register
+typedef unsigned long long p2;
+__device__ __forceinline__ p2 pk(float lo, float hi) { p2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ void unpk(p2 a, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(a)); }
+__device__ __forceinline__ p2 fma2(p2 a, p2 b, p2 c) { p2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
+__device__ __forceinline__ p2 mul2(p2 a, p2 b) { p2 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ p2 add2(p2 a, p2 b) { p2 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ p2 mul2s(float s, p2 b) { p2 r; asm("{.reg .b64 t; mov.b64 t, {%1, %1}; mul.rn.f32x2 %0, t, %2;}" : "=l"(r) : "f"(s), "l"(b)); return r; }
+
+struct BandK2 { p2 c1, a12, a22, bx2, g, omc, cq, wj; };
+struct BandS2 { p2 ic1, ic2, env; };
+
+template <bool FULL>
+__device__ __forceinline__ void band_group2(const float* xd, float* bpw, int f0, int nv, const BandK2& c, BandS2& s)
+{
+    float xv[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) xv[k] = xd[f0 + k];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        if (FULL || f0 + k < nv) {
+            const p2 u2 = fma2(c.a22, s.ic2, mul2s(xv[k], c.bx2));
+            const p2 sv = fma2(c.a12, s.ic1, u2);                  // 2 v1
+            s.ic1 = fma2(c.c1, s.ic1, u2);
+            s.ic2 = fma2(c.g, sv, s.ic2);
+            s.env = fma2(c.cq, mul2(sv, sv), mul2(c.omc, s.env));
+            *reinterpret_cast<p2*>(bpw + (f0 + k) * kBpPitch) = mul2(c.wj, s.env);
+        }
+    }
+}
 }  // namespace
 
 __global__ void __launch_bounds__(kSplitThreads, 1)
@@ -424,6 +475,8 @@ easyexpander_split_kernel(const EEArgs a, const int spc)
     extern __shared__ __align__(16) uint8_t smem_raw[];
     EESmemS& sm = *reinterpret_cast<EESmemS*>(smem_raw);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int role = kRole[warp];
+    if (role == ROLE_NONE) return;
     const int s_base = blockIdx.x * spc;
     const int ns_cta = min(spc, a.n_streams - s_base);
     const size_t ns = (size_t)a.n_streams;
@@ -433,37 +486,46 @@ easyexpander_split_kernel(const EEArgs a, const int spc)
     const R eps = (R)1e-12, db_per_ln = (R)8.685889638065037, ln_per_db = (R)0.115129254649702;
     const R knee_db = (R)6.0, hys_db = (R)2.0;
 
-    if (warp < kBandWarps) {
-        // ============================ band warps: the SVF + power-follower recurrence only =========================
-        const int sl = lane >> 3, j = lane & 7;
-        const int ls = 4 * warp + sl;
-        const bool act = 4 * warp < ns_cta, live = ls < ns_cta;
+    if (role < kBandWarpsS) {
+        // ============================ band warps: the SVF + power-follower recurrence only, two bands per lane ========
+        const int bw = role, sl = lane >> 2, jj = lane & 3;
+        const int ls = 8 * bw + sl;
+        const bool act = 8 * bw < ns_cta, live = ls < ns_cta;
         const int sg = s_base + (live ? ls : (ns_cta - 1));
-        const BandK<R> bk{(R)a.k.g[j], (R)a.k.den[j], (R)a.k.w[j], (R)a.k.band_c, (R)(1.0 / a.k.den[j]),
-                          (R)(-a.k.g[j] / a.k.den[j]), (R)(a.k.g[j] / a.k.den[j]), (R)(2.0 * a.k.g[j])};
+        const int jA = 2 * jj, jB = jA + 1;
+        const double gA = a.k.g[jA], gB = a.k.g[jB], dA = a.k.den[jA], dB = a.k.den[jB], bc = a.k.band_c;
+        const BandK2 bk{pk((float)(2.0 / dA - 1.0), (float)(2.0 / dB - 1.0)), pk((float)(2.0 / dA), (float)(2.0 / dB)),
+                        pk((float)(-2.0 * gA / dA), (float)(-2.0 * gB / dB)),
+                        pk((float)(2.0 * gA / dA), (float)(2.0 * gB / dB)), pk((float)gA, (float)gB),
+                        pk((float)(1.0 - bc), (float)(1.0 - bc)), pk((float)(0.25 * bc), (float)(0.25 * bc)),
+                        pk((float)a.k.w[jA], (float)a.k.w[jB])};
         double* st = a.state + sg;
-        R ic1 = (R)st[(0 + j) * ns], ic2 = (R)st[(8 + j) * ns], env = (R)st[(16 + j) * ns];
+        BandS2 bs{pk((float)st[(0 + jA) * ns], (float)st[(0 + jB) * ns]), pk((float)st[(8 + jA) * ns], (float)st[(8 + jB) * ns]),
+                  pk((float)st[(16 + jA) * ns], (float)st[(16 + jB) * ns])};
         for (int64_t i = 0; i < n_iter; ++i) {
             if (act && i >= 2 && i - 2 < n_batches) {
                 const int64_t b = i - 2;
-                const R* xd = sm.xd[b & 1] + ls * kPitchF;
+                const float* xd = sm.xd[b & 1] + ls * kPitchF;
                 const int nv = (int)min((int64_t)kF, n - b * kF);
-                R* bpw = sm.bp[b & 1][warp] + sl * kBpStream + j;
+                float* bpw = sm.bp[b & 1] + ls * kBpStreamS + jA;
                 if (nv == kF) {
 #pragma unroll 1
-                    for (int f0 = 0; f0 < kF; f0 += 8) band_group<R, true>(xd, bpw, f0, nv, bk, ic1, ic2, env);
+                    for (int f0 = 0; f0 < kF; f0 += 8) band_group2<true>(xd, bpw, f0, nv, bk, bs);
                 } else {
 #pragma unroll 1
-                    for (int f0 = 0; f0 < kF; f0 += 8) band_group<R, false>(xd, bpw, f0, nv, bk, ic1, ic2, env);
+                    for (int f0 = 0; f0 < kF; f0 += 8) band_group2<false>(xd, bpw, f0, nv, bk, bs);
                 }
             }
-            __syncthreads();
+            split_sync();
         }
         if (live) {
             st = a.state + s_base + ls;
-            st[(0 + j) * ns] = (double)ic1; st[(8 + j) * ns] = (double)ic2; st[(16 + j) * ns] = (double)env;
+            float lo_, hi_;
+            unpk(bs.ic1, lo_, hi_); st[(0 + jA) * ns] = (double)lo_; st[(0 + jB) * ns] = (double)hi_;
+            unpk(bs.ic2, lo_, hi_); st[(8 + jA) * ns] = (double)lo_; st[(8 + jB) * ns] = (double)hi_;
+            unpk(bs.env, lo_, hi_); st[(16 + jA) * ns] = (double)lo_; st[(16 + jB) * ns] = (double)hi_;
         }
-    } else if (warp == kBandWarps) {
+    } else if (role == ROLE_FILTER) {
         // ============================ filter warp: lane = stream (batch i-1) =======================================
         const bool live = lane < ns_cta;
         const int sg = s_base + (live ? lane : 0);
@@ -503,10 +565,10 @@ easyexpander_split_kernel(const EEArgs a, const int spc)
                     }
                 }
             }
-            __syncthreads();
+            split_sync();
         }
         if (live) { st[24 * ns] = (double)fs.hpf_lp; st[25 * ns] = (double)fs.lpf_y; }
-    } else if (warp == kBandWarps + 1) {
+    } else if (role == ROLE_GAIN) {
         // ============================ gain warp: lane = stream (batch i-4) =========================================
         const bool live = lane < ns_cta;
         const int sg = s_base + (live ? lane : 0);
@@ -549,7 +611,7 @@ easyexpander_split_kernel(const EEArgs a, const int spc)
                     for (int k = 0; k < 8; ++k) gout[f0 + k] = go[k];
                 }
             }
-            __syncthreads();
+            split_sync();
         }
         if (live) {
             st[26 * ns] = (double)gs.det_slow; st[27 * ns] = gs.expanding ? 1.0 : 0.0; st[28 * ns] = (double)gs.gain_db_s;
@@ -557,7 +619,7 @@ easyexpander_split_kernel(const EEArgs a, const int spc)
         }
     } else {
         // ============================ helper warps: lane = frame; streams h, h + 8, h + 16, h + 24 of the CTA ========
-        const int h = warp - (kBandWarps + 2);
+        const int h = role - ROLE_HELP;
         const float* irow[4]; float* orow[4];
         bool has[4];
 #pragma unroll
@@ -591,10 +653,9 @@ easyexpander_split_kernel(const EEArgs a, const int spc)
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     const int lq = h + kHelpWarps * q;
-                    const R* bp = sm.bp[b & 1][lq >> 2] + (lq & 3) * kBpStream + lane * 9;
-                    R sum = (R)0.0;
-#pragma unroll
-                    for (int bnd = 0; bnd < 8; ++bnd) sum = add(sum, bp[bnd]);
+                    const float4* bp = reinterpret_cast<const float4*>(sm.bp[b & 1] + lq * kBpStreamS + lane * kBpPitch);
+                    const float4 b03 = bp[0], b47 = bp[1];
+                    R sum = add(add(add(add(add(add(add(add((R)0.0, b03.x), b03.y), b03.z), b03.w), b47.x), b47.y), b47.z), b47.w);
                     det_lin[q] = sqrt_(jmax(sum, eps));
                     thr[q] = sm.cs[slot][0][lq]; dep[q] = sm.cs[slot][1][lq]; rat[q] = sm.cs[slot][2][lq];
                 }
@@ -641,7 +702,7 @@ easyexpander_split_kernel(const EEArgs a, const int spc)
                     ib[lq * kInPitch + kPitchF + lane] = hold[q][1];
                 }
             }
-            __syncthreads();
+            split_sync();
         }
     }
 }

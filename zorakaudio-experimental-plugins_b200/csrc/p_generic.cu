@@ -64,6 +64,9 @@ public:
         const size_t ns = (size_t)I.n_streams;
         std::vector<int> idx;
         for (const auto& s : I.decls) idx.push_back(s.index0);
+        bool same = (int)idx.size() == d_->n_decl;     // the kernels address sliders by compile-time slot
+        for (int j = 0; same && j < d_->n_decl; ++j) same = idx[j] == d_->decl_index0[j];
+        if (!same) { set_error(std::string(d_->key) + ": slider declarations differ from the ones the generated code was built for"); return false; }
         return cuda_ok(cudaMalloc(&d_state, (size_t)(d_->n_vars + 65) * ns * rsize), "state") &&
                cuda_ok(cudaMalloc(&d_mem, (size_t)std::max<int64_t>(d_->mem_slots, 1) * ns * rsize), "mem[] heap") &&
                cuda_ok(cudaMalloc(&d_mt, 625 * ns * sizeof(unsigned)), "rand state") &&

@@ -263,7 +263,7 @@ static bool process_host(Instance& I, const float* params, int npb, const float*
 static int do_process(Instance* I, const float* params, int npb, const float* in, float* out, double* tap,
                       int64_t n_frames, int64_t stride, int mem)
 {
-    if (!I || !in || !out || n_frames < 0 || stride < n_frames || npb < 0 || (npb > 0 && !params)) {
+    if (!I || (!in && I->desc->n_in > 0) || !out || n_frames < 0 || stride < n_frames || npb < 0 || (npb > 0 && !params)) {
         set_error("za_gpu_process: bad argument");
         return ZA_ERR_ARG;
     }

@@ -112,6 +112,7 @@ struct GenDesc {
     const int* alias;                              // [64]: vars slot mirrored by slider i0, or -1
     bool (*prepare)(const GenLaunch&, int precision, cudaStream_t);
     bool (*process)(const GenLaunch&, int precision, cudaStream_t);
+    int n_decl; const int* decl_index0;            // declared sliders the generated code was compiled for (declaration order)
 };
 
 }  // namespace za

@@ -8,12 +8,13 @@ if the library is missing or no CUDA device exists, construction raises.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from pathlib import Path
 
 import numpy as np
 
 PKG = Path(__file__).resolve().parent.parent
-LIB_PATH = PKG / "libza_gpu.so"
+LIB_PATH = Path(os.environ.get("ZA_GPU_LIB", PKG / "libza_gpu.so"))   # override: A/B builds of the same ABI
 
 ZA_F32, ZA_F64 = 0, 1
 ZA_MEM_HOST, ZA_MEM_DEVICE = 0, 1

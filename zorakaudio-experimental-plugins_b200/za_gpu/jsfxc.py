@@ -445,7 +445,7 @@ class Unit:
         em = Emitter(self, section, local_map, set(params))
         val = em.ex(body)
         args = "".join(f", R p_{re.sub(r'[^A-Za-z0-9_]', '_', p)}" for p in params)
-        code = [f"template <typename R> __device__ __noinline__ R {cn}(Rt<R>& c, R* v{args})", "{"] + em.lines + [f"    return {val};", "}", ""]
+        code = [f"template <typename R> __device__ ZA_JSFX_FN R {cn}(Rt<R>& c, R* v{args})", "{"] + em.lines + [f"    return {val};", "}", ""]
         self.spec_code += code
         self.in_progress.discard(key)
         self.spec[key] = cn
@@ -594,7 +594,7 @@ class Emitter:
                 b = self.ex(tgt[1]); i = self.ex(tgt[2])
                 self.n += 1
                 a = f"a{self.n}"
-                self.w(f"const long long {a} = c.addr({b}, {i});")
+                self.w(f"const auto {a} = c.addr({b}, {i});")
                 if op == "=":
                     self.w(f"c.st({a}, {rhs});")
                     return rhs
@@ -727,6 +727,11 @@ def generate(key: str, jsfx_path: str, mem_slots: int, source_label: str) -> str
     out.append("static const int kAlias[64] = {" + ", ".join(map(str, alias_slots)) + "};")
     sel = "".join(f"i0 == {i} ? {a} : " for i, a in enumerate(alias_slots) if a >= 0)
     out.append(f"__host__ __device__ constexpr int alias_slot(int i0) {{ return {sel}-1; }}")
+    decl = [int(m.group(1)) - 1 for m in (re.match(r"\s*slider(\d+)\s*:", l) for l in u.slider_lines) if m and 1 <= int(m.group(1)) <= 64]
+    out.append(f"constexpr int kDecl = {len(decl)};     // declared sliders, in declaration order (index0)")
+    out.append("static const int kDeclIndex0[] = {" + ", ".join(map(str, decl or [0])) + "};")
+    dsel = "".join(f"j == {j} ? {i0} : " for j, i0 in enumerate(decl))
+    out.append(f"__host__ __device__ constexpr int decl_slot(int j) {{ return {dsel}0; }}")
     out.append("static const char kSliderText[] =")
     for l in u.slider_lines:
         out.append("    " + c_string(l.strip()))
