@@ -121,3 +121,28 @@ def test_fp32_mode_residual(gpu, key):
     if key in FP32_OK:
         assert db < -100.0, db
     bp.close()
+
+
+def test_cfg1_ddt(gpu):
+    """BASELINE config 1 (the reference's own CPU-runnable case): DDT, 10 s x 2 ch x 48 kHz, host block 512, sliders
+    at their declared defaults, the survey's gated-noise + sine input; fp64 mode against the compiled reference."""
+    ref = zo.RefPlugin("DDT")
+    x = wl.cfg1_input()
+    assert x.shape == (1, 2, 480000)
+    p = np.array([[s["default"] for s in ref.sliders]], np.float32)
+    assert list(p[0]) == [30, 50, 40, 55, 2, 100, 0, 0, 50]
+    y, yd, v = ref.render(p, x, want_f64=True, want_vars=True)
+    bp = gpu.BatchProcessor("DDT", 1, precision="f64").prepare(p)
+    tap = np.zeros_like(yd)
+    out = bp.process(x, tap64=tap)
+    e = rel_err(tap, yd).max()
+    assert e <= TOL64, e
+    assert np.mean(out == y) > 0.9999
+    for name, want in v.items():
+        if np.all(want == np.round(want)) and np.abs(want).max() < 2 ** 40:
+            try:
+                got = bp.read_state(name)
+            except Exception:
+                continue
+            assert np.array_equal(got, want), name
+    bp.close()

@@ -297,10 +297,21 @@ __global__ void __launch_bounds__(32) jsfx_process_kernel(const GenLaunch a)
         }
         for (int f0 = 0; f0 < nb; f0 += 32) {
             const int nf = min(32, nb - f0);
-            // tile in: lane = frame, 128-byte rows
-            for (int r = 0; r < ns_cta; ++r)
-                for (int ch = 0; ch < S::kIn; ++ch)
-                    tile[(ch * 32 + r) * kP + lane] = lane < nf ? a.in[((size_t)(s0 + r) * S::kIn + ch) * a.row_stride + pos + f0 + lane] : 0.f;
+            // tile in: lane = frame, 128-byte rows; the loads go out in groups of 8 rows before their shared-memory
+            // stores, so one DRAM latency covers a group (ncu: a load-store pair per row left the only warp of the SM
+            // waiting on the long scoreboard for half of its time)
+            const int nq = ns_cta * S::kIn;
+            for (int q0 = 0; q0 < nq; q0 += 8) {
+                float t[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u)
+                    t[u] = (q0 + u < nq && lane < nf) ? a.in[((size_t)s0 * S::kIn + q0 + u) * a.row_stride + pos + f0 + lane] : 0.f;
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    const int q = q0 + u;
+                    if (q < nq) tile[((q % S::kIn) * 32 + q / S::kIn) * kP + lane] = t[u];
+                }
+            }
             __syncwarp();
             if (live) {
                 for (int f = 0; f < nf; ++f) {
@@ -315,9 +326,9 @@ __global__ void __launch_bounds__(32) jsfx_process_kernel(const GenLaunch a)
                 }
             }
             __syncwarp();
-            for (int r = 0; r < ns_cta; ++r)
-                for (int ch = 0; ch < S::kOut; ++ch)
-                    if (lane < nf) a.out[((size_t)(s0 + r) * S::kOut + ch) * a.row_stride + pos + f0 + lane] = tile[(ch * 32 + r) * kP + lane];
+#pragma unroll 4
+            for (int q = 0; q < ns_cta * S::kOut; ++q)
+                if (lane < nf) a.out[((size_t)s0 * S::kOut + q) * a.row_stride + pos + f0 + lane] = tile[((q % S::kOut) * 32 + q / S::kOut) * kP + lane];
             __syncwarp();
         }
         pos += nb;

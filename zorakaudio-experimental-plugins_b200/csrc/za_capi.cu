@@ -304,7 +304,7 @@ ZA_API const char* za_gpu_plugin_key(int i)
 ZA_API int za_gpu_plugin_info(const char* key, za_plugin_info* out)
 {
     const PluginDesc* d = find_plugin(key);
-    if (!d) { set_error("unknown plugin_key"); return ZA_ERR_PLUGIN; }
+    if (!d) { set_error(std::string("unknown plugin_key: ") + (key ? key : "(null)")); return ZA_ERR_PLUGIN; }
     if (!out) return ZA_ERR_ARG;
     out->n_in = d->n_in; out->n_out = d->n_out; out->kind = d->kind; out->latency = d->latency;
     out->n_sliders = (int)parse_slider_decls(d->slider_text).size();
@@ -320,7 +320,7 @@ static void fill_slider(const SliderDecl& s, za_slider_info* o)
 ZA_API int za_gpu_slider_info(const char* key, int column, za_slider_info* out)
 {
     const PluginDesc* d = find_plugin(key);
-    if (!d) { set_error("unknown plugin_key"); return ZA_ERR_PLUGIN; }
+    if (!d) { set_error(std::string("unknown plugin_key: ") + (key ? key : "(null)")); return ZA_ERR_PLUGIN; }
     const auto decls = parse_slider_decls(d->slider_text);
     if (!out || column < 0 || column >= (int)decls.size()) return ZA_ERR_ARG;
     fill_slider(decls[column], out);

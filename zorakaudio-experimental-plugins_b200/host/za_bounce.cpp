@@ -1,0 +1,225 @@
+// za_bounce.cpp -- offline bounce driver over the C ABI of include/za_gpu.h.
+//
+// Every input WAV file is one stream (one plugin instance / bounce job).  The files are rendered together through
+// ONE za_gpu handle in time chunks (state is carried by the library between chunks), the way an offline host would
+// have looped `prepareToPlay(sr, block); for each block: processBlock(...)` over every instance
+// (src/JSFXJuceProcessor.cpp:3239, :3435), and each result is written as 24-bit PCM WAV next to a report.json -- the
+// format of the reference's own exporter (src/JSFXCorrectnessCheck.h:1177-1255).
+//
+// Host C++ only: no CUDA, no torch; links libza_gpu.so.  There is no CPU rendering path -- without a CUDA device the
+// library's create call fails and so does this program.
+#include <sys/stat.h>
+
+#include <algorithm>
+#include <chrono>
+#include <cstdlib>
+#include <map>
+
+#include "../../include/za_gpu.h"
+#include "za_wav.h"
+
+namespace {
+
+int usage(const char* argv0)
+{
+    std::fprintf(stderr,
+                 "usage: %s --plugin KEY [--precision f32|f64] [--block N] [--chunk-seconds S] [--tail-seconds S]\n"
+                 "          [--set SLIDER=VALUE ...] [--device D] [--out-dir DIR] IN.wav [IN2.wav ...]\n"
+                 "       %s --list                 plugin keys, channel counts and sliders the library renders\n"
+                 "       %s --wav-info FILE.wav    header + checksum of the decoded samples (no GPU needed)\n",
+                 argv0, argv0, argv0);
+    return 2;
+}
+
+int fail(const std::string& what)
+{
+    std::fprintf(stderr, "za_bounce: %s\n", what.c_str());
+    return 1;
+}
+
+std::string base_name(const std::string& p)
+{
+    const size_t s = p.find_last_of('/');
+    std::string b = s == std::string::npos ? p : p.substr(s + 1);
+    const size_t d = b.find_last_of('.');
+    return d == std::string::npos ? b : b.substr(0, d);
+}
+
+std::string json_escape(const std::string& s)
+{
+    std::string o;
+    for (char c : s) {
+        if (c == '"' || c == '\\') { o += '\\'; o += c; }
+        else if ((unsigned char)c < 0x20) { char b[8]; std::snprintf(b, sizeof b, "\\u%04x", c); o += b; }
+        else o += c;
+    }
+    return o;
+}
+
+int list_plugins()
+{
+    for (int i = 0; i < za_gpu_plugin_count(); ++i) {
+        const char* key = za_gpu_plugin_key(i);
+        za_plugin_info pi;
+        if (za_gpu_plugin_info(key, &pi) != ZA_OK) return fail(za_gpu_last_error());
+        std::printf("%s: %d in, %d out, %d sliders, latency %d\n", key, pi.n_in, pi.n_out, pi.n_sliders, pi.latency);
+        for (int c = 0; c < pi.n_sliders; ++c) {
+            za_slider_info si;
+            if (za_gpu_slider_info(key, c, &si) != ZA_OK) return fail(za_gpu_last_error());
+            std::printf("    slider%d%s%s = %g  <%g, %g, %g>\n", si.index0 + 1, si.alias[0] ? ":" : "", si.alias, si.def, si.min, si.max, si.step);
+        }
+    }
+    return 0;
+}
+
+int wav_info(const std::string& path)
+{
+    za_wav::Audio a;
+    const std::string e = za_wav::read(path, a);
+    if (!e.empty()) return fail(e);
+    uint64_t h = 1469598103934665603ull;                   // FNV-1a over the decoded floats, channel-major
+    for (const auto& c : a.ch)
+        for (float v : c) {
+            uint32_t u;
+            std::memcpy(&u, &v, 4);
+            for (int k = 0; k < 4; ++k) { h ^= (u >> (8 * k)) & 0xffu; h *= 1099511628211ull; }
+        }
+    std::printf("{\"channels\": %d, \"sample_rate\": %.3f, \"frames\": %lld, \"bits\": %d, \"float\": %s, \"fnv1a\": \"%016llx\"}\n", a.channels,
+                a.sample_rate, (long long)a.frames, a.bits, a.is_float ? "true" : "false", (unsigned long long)h);
+    return 0;
+}
+
+}  // namespace
+
+int main(int argc, char** argv)
+{
+    std::string plugin, out_dir = "bounce_out", precision = "f64";
+    int block = 512, device = 0;
+    double chunk_seconds = 10.0, tail_seconds = 0.0;
+    std::map<int, float> sets;
+    std::vector<std::string> inputs;
+    for (int i = 1; i < argc; ++i) {
+        const std::string a = argv[i];
+        auto need = [&](const char* name) -> const char* {
+            if (i + 1 >= argc) { std::fprintf(stderr, "za_bounce: %s needs a value\n", name); std::exit(2); }
+            return argv[++i];
+        };
+        if (a == "--list") return list_plugins();
+        else if (a == "--wav-info") return wav_info(need("--wav-info"));
+        else if (a == "--plugin") plugin = need("--plugin");
+        else if (a == "--precision") precision = need("--precision");
+        else if (a == "--block") block = std::atoi(need("--block"));
+        else if (a == "--device") device = std::atoi(need("--device"));
+        else if (a == "--chunk-seconds") chunk_seconds = std::atof(need("--chunk-seconds"));
+        else if (a == "--tail-seconds") tail_seconds = std::atof(need("--tail-seconds"));
+        else if (a == "--out-dir") out_dir = need("--out-dir");
+        else if (a == "--set") {
+            const std::string kv = need("--set");
+            const size_t eq = kv.find('=');
+            if (eq == std::string::npos) return usage(argv[0]);
+            sets[std::atoi(kv.substr(0, eq).c_str())] = (float)std::atof(kv.substr(eq + 1).c_str());
+        } else if (a == "-h" || a == "--help") { usage(argv[0]); return 0; }
+        else if (a.size() > 2 && a[0] == '-' && a[1] == '-') return usage(argv[0]);
+        else inputs.push_back(a);
+    }
+    if (plugin.empty() || inputs.empty() || block <= 0 || chunk_seconds <= 0.0 || (precision != "f32" && precision != "f64")) return usage(argv[0]);
+
+    za_plugin_info pi;
+    if (za_gpu_plugin_info(plugin.c_str(), &pi) != ZA_OK) return fail(za_gpu_last_error());
+    const int ns = (int)inputs.size();
+
+    // ---- read every job; one sample rate per batch (one handle = one srate, like one prepareToPlay) -------------------
+    std::vector<za_wav::Audio> wav((size_t)ns);
+    int64_t longest = 0;
+    for (int s = 0; s < ns; ++s) {
+        const std::string e = za_wav::read(inputs[(size_t)s], wav[(size_t)s]);
+        if (!e.empty()) return fail(e);
+        if (wav[(size_t)s].sample_rate != wav[0].sample_rate)
+            return fail(inputs[(size_t)s] + ": sample rate differs from " + inputs[0] + " (render such files in separate batches)");
+        longest = std::max(longest, wav[(size_t)s].frames);
+    }
+    const double sr = wav[0].sample_rate;
+    const int64_t tail = (int64_t)std::llround(tail_seconds * sr);
+    const int64_t total = longest + tail;
+    int64_t chunk = (int64_t)std::llround(chunk_seconds * sr);
+    chunk = std::max<int64_t>(block, chunk / block * block);            // chunks end on host-block boundaries
+
+    // ---- parameters: declared defaults, --set overrides by slider number, same row for every stream ---------------------
+    std::vector<float> row((size_t)pi.n_sliders);
+    for (int c = 0; c < pi.n_sliders; ++c) {
+        za_slider_info si;
+        if (za_gpu_slider_info(plugin.c_str(), c, &si) != ZA_OK) return fail(za_gpu_last_error());
+        row[(size_t)c] = si.def;
+        const auto it = sets.find(si.index0 + 1);
+        if (it != sets.end()) { row[(size_t)c] = it->second; sets.erase(it); }
+    }
+    if (!sets.empty()) return fail("--set: plugin " + plugin + " declares no slider" + std::to_string(sets.begin()->first));
+    std::vector<float> params((size_t)ns * (size_t)std::max(pi.n_sliders, 1));
+    for (int s = 0; s < ns; ++s) std::copy(row.begin(), row.end(), params.begin() + (size_t)s * (size_t)pi.n_sliders);
+
+    za_gpu_handle h = nullptr;
+    if (za_gpu_create(plugin.c_str(), ns, sr, block, precision == "f64" ? ZA_F64 : ZA_F32, device, &h) != ZA_OK) return fail(za_gpu_last_error());
+    if (za_gpu_prepare(h, params.data()) != ZA_OK) return fail(za_gpu_last_error());
+
+    // ---- outputs: header now (lengths are known), samples appended chunk by chunk -----------------------------------------
+    ::mkdir(out_dir.c_str(), 0777);
+    std::vector<std::string> out_path((size_t)ns);
+    std::vector<double> peak((size_t)ns, 0.0);
+    for (int s = 0; s < ns; ++s) {
+        out_path[(size_t)s] = out_dir + "/" + base_name(inputs[(size_t)s]) + (ns > 1 ? "." + std::to_string(s) : "") + ".wav";
+        FILE* f = std::fopen(out_path[(size_t)s].c_str(), "wb");
+        if (!f || !za_wav::write24_header(f, pi.n_out, wav[(size_t)s].frames + tail, sr)) return fail("cannot create " + out_path[(size_t)s]);
+        std::fclose(f);
+    }
+
+    const int n_in = std::max(pi.n_in, 0), n_out = pi.n_out;
+    std::vector<float> in((size_t)ns * (size_t)std::max(n_in, 1) * (size_t)chunk), out((size_t)ns * (size_t)n_out * (size_t)chunk);
+    const auto t0 = std::chrono::steady_clock::now();
+    for (int64_t f0 = 0; f0 < total; f0 += chunk) {
+        const int64_t n = std::min(chunk, total - f0);
+        for (int s = 0; s < ns; ++s) {
+            const za_wav::Audio& w = wav[(size_t)s];
+            for (int c = 0; c < n_in; ++c) {                     // channels the file does not have, and frames past its end, are silence
+                float* dst = in.data() + ((size_t)s * (size_t)n_in + (size_t)c) * (size_t)chunk;
+                const int64_t have = c < w.channels ? std::max<int64_t>(0, std::min(n, w.frames - f0)) : 0;
+                if (have > 0) std::memcpy(dst, w.ch[(size_t)c].data() + f0, (size_t)have * sizeof(float));
+                std::fill(dst + have, dst + n, 0.0f);
+            }
+        }
+        if (za_gpu_process(h, nullptr, 0, n_in ? in.data() : nullptr, out.data(), n, chunk, ZA_MEM_HOST) != ZA_OK) return fail(za_gpu_last_error());
+        for (int s = 0; s < ns; ++s) {
+            const int64_t keep = std::max<int64_t>(0, std::min(n, wav[(size_t)s].frames + tail - f0));
+            if (keep == 0) continue;
+            const float* src = out.data() + (size_t)s * (size_t)n_out * (size_t)chunk;
+            for (int c = 0; c < n_out; ++c)
+                for (int64_t i = 0; i < keep; ++i) peak[(size_t)s] = std::max(peak[(size_t)s], (double)std::fabs(src[(size_t)c * (size_t)chunk + (size_t)i]));
+            FILE* f = std::fopen(out_path[(size_t)s].c_str(), "ab");
+            if (!f || !za_wav::append24(f, src, n_out, keep, chunk)) return fail("write error on " + out_path[(size_t)s]);
+            std::fclose(f);
+        }
+    }
+    const double wall = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    int64_t launches = 0;
+    za_gpu_launch_count(h, &launches);
+    za_gpu_destroy(h);
+
+    // ---- report.json (the reference's exporter writes one beside its WAVs, JSFXCorrectnessCheck.h:1230-1255) ---------------
+    const std::string rp = out_dir + "/report.json";
+    FILE* r = std::fopen(rp.c_str(), "w");
+    if (!r) return fail("cannot create " + rp);
+    int64_t sum_frames = 0;
+    for (int s = 0; s < ns; ++s) sum_frames += wav[(size_t)s].frames + tail;
+    std::fprintf(r, "{\n  \"plugin\": \"%s\",\n  \"sampleRate\": %.3f,\n  \"frames\": %lld,\n  \"streams\": %d,\n  \"precision\": \"%s\",\n  \"block\": %d,\n"
+                    "  \"chunkFrames\": %lld,\n  \"tailFrames\": %lld,\n  \"kernelLaunches\": %lld,\n  \"wallSeconds\": %.6f,\n  \"xRealtime\": %.3f,\n  \"files\": [\n",
+                 json_escape(plugin).c_str(), sr, (long long)total, ns, precision.c_str(), block, (long long)chunk, (long long)tail, (long long)launches, wall,
+                 wall > 0 ? (double)sum_frames / sr / wall : 0.0);
+    for (int s = 0; s < ns; ++s)
+        std::fprintf(r, "    {\"in\": \"%s\", \"out\": \"%s\", \"channelsIn\": %d, \"channelsOut\": %d, \"frames\": %lld, \"peakOut\": %.9g}%s\n",
+                     json_escape(inputs[(size_t)s]).c_str(), json_escape(out_path[(size_t)s]).c_str(), wav[(size_t)s].channels, n_out,
+                     (long long)(wav[(size_t)s].frames + tail), peak[(size_t)s], s + 1 < ns ? "," : "");
+    std::fprintf(r, "  ]\n}\n");
+    std::fclose(r);
+    std::printf("za_bounce: %d stream(s) x %.3f s of %s in %.3f s (%.0f x realtime), %lld kernel launches -> %s\n", ns, (double)total / sr, plugin.c_str(), wall,
+                wall > 0 ? (double)sum_frames / sr / wall : 0.0, (long long)launches, out_dir.c_str());
+    return 0;
+}

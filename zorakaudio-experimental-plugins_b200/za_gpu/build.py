@@ -55,7 +55,22 @@ def build_lib(force: bool = False, verbose: bool = False) -> Path:
             print(l)
     if jobs or not LIB.exists():
         run([NVCC, *ARCH, "-shared", "-o", str(LIB), *map(str, objs), "-Xcompiler", "-fPIC", "-cudart", "static"])
+    build_bounce()
     return LIB
+
+
+BOUNCE = PKG / "za_bounce"
+
+
+def build_bounce(force: bool = False) -> Path:
+    """The offline bounce driver (host/za_bounce.cpp): plain C++ over the C ABI, linked against the in-tree library."""
+    srcs = [PKG / "host" / "za_bounce.cpp", PKG / "host" / "za_wav.h", PKG.parent / "include" / "za_gpu.h"]
+    if force or not BOUNCE.exists() or any(x.stat().st_mtime > BOUNCE.stat().st_mtime for x in srcs + [LIB]):
+        r = subprocess.run([os.environ.get("CXX", "g++"), "-O2", "-std=c++17", "-Wall", str(srcs[0]), "-o", str(BOUNCE),
+                            "-L" + str(PKG), "-lza_gpu", "-Wl,-rpath,$ORIGIN"], capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError("g++ failed:\n" + r.stdout + r.stderr)
+    return BOUNCE
 
 
 if __name__ == "__main__":

@@ -88,3 +88,33 @@ def default_params(plugin_key: str, n_streams: int, first_stream: int = 0) -> np
     import za_gpu
     d = np.array([s.def_ for s in za_gpu.slider_layout(plugin_key)], np.float32)
     return np.tile(d, (n_streams, 1))
+
+
+def cfg1_input(n_frames: int = 480000, n_ch: int = 2, srate: float = 48000.0, seed: int = 12345) -> np.ndarray:
+    """BASELINE config 1 input: seeded LCG white noise in [-0.5, 0.5) gated 100 ms on / 200 ms
+    off plus a 1 kHz sine at -12 dBFS; one stream, [1][ch][frame] f32 (channel c uses seed + c)."""
+    x = np.empty((1, n_ch, n_frames), np.float32)
+    t = np.arange(n_frames)
+    gate = (t % int(0.3 * srate)) < int(0.1 * srate)
+    sine = 10.0 ** (-12.0 / 20.0) * np.sin(2.0 * np.pi * 1000.0 * t / srate)
+    for c in range(n_ch):
+        st = np.uint64(seed + c)
+        a, inc, mask = np.uint64(6364136223846793005), np.uint64(1442695040888963407), np.uint64(0xFFFFFFFFFFFFFFFF)
+        # 64-bit LCG advanced in closed form per frame: state_n = a^n s + inc (a^n - 1)/(a - 1); done iteratively in
+        # chunks with Python ints would be slow, so jump tables of (a^k, c_k) for k = 1 .. chunk are built once
+        chunk = 4096
+        ak, ck = np.empty(chunk, np.uint64), np.empty(chunk, np.uint64)
+        pa, pc = 1, 0
+        for k in range(chunk):
+            pa, pc = (pa * int(a)) & int(mask), (pc * int(a) + int(inc)) & int(mask)
+            ak[k], ck[k] = pa, pc
+        noise = np.empty(n_frames, np.float64)
+        cur = int(st)
+        with np.errstate(over="ignore"):
+            for f0 in range(0, n_frames, chunk):
+                n = min(chunk, n_frames - f0)
+                stt = ak[:n] * np.uint64(cur) + ck[:n]
+                noise[f0:f0 + n] = (stt >> np.uint64(40)).astype(np.float64) / float(1 << 24) - 0.5
+                cur = int(stt[n - 1])
+        x[0, c] = (noise * gate + sine).astype(np.float32)
+    return x
