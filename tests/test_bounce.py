@@ -108,6 +108,25 @@ def test_list_names_every_plugin(bounce):
         assert f"\n{key}: " in "\n" + r.stdout
 
 
+def test_preset_and_plugin_json(bounce, tmp_path):
+    """APVTS-style state (<PARAM id="sliderN" value=...>, the reference's getStateInformation XML) and plugin.json slug:
+    parsed on the host before any GPU work; --save-preset writes back the values the bounce uses."""
+    write_wav(tmp_path / "a.wav", np.zeros((2, 64)), 48000, "i16")
+    (tmp_path / "plugin.json").write_text(json.dumps({"name": "Easy Expander", "slug": "EasyExpander", "version": "1.0"}))
+    (tmp_path / "state.xml").write_text('<?xml version="1.0"?><PARAMETERS><PARAM id="slider1" value="-41.5"/>'
+                                        '<PARAM id="slider2" value="24"/><FILES f0="x.wav"/></PARAMETERS>')
+    r = subprocess.run([bounce, "--plugin-json", str(tmp_path / "plugin.json"), "--preset", str(tmp_path / "state.xml"), "--set", "2=30",
+                        "--save-preset", str(tmp_path / "used.xml"), "--out-dir", str(tmp_path / "o"), str(tmp_path / "a.wav")],
+                       capture_output=True, text=True)
+    used = (tmp_path / "used.xml").read_text()
+    assert 'plugin="EasyExpander"' in used
+    assert '<PARAM id="slider1" value="-41.5"/>' in used and '<PARAM id="slider2" value="30"/>' in used      # --set wins over the preset
+    assert r.returncode in (0, 1)                        # 1 here = no CUDA device (see test_no_cpu_fallback)
+    (tmp_path / "empty.xml").write_text("<PARAMETERS/>")
+    r = subprocess.run([bounce, "--plugin", "EasyExpander", "--preset", str(tmp_path / "empty.xml"), str(tmp_path / "a.wav")], capture_output=True, text=True)
+    assert r.returncode == 1 and "PARAM" in r.stderr
+
+
 def test_no_cpu_fallback(bounce, tmp_path):
     """Without a CUDA device a bounce fails with the library's message instead of rendering on the host."""
     import ctypes
@@ -140,7 +159,11 @@ def test_bounce_matches_reference_render(bounce, tmp_path, key, precision):
     extra = []
     if key == "EasyExpander":
         p[:, 0] = -35.0
-        extra = ["--set", "1=-35"]
+        if precision == "f64":
+            extra = ["--set", "1=-35"]
+        else:
+            (tmp_path / "state.xml").write_text('<PARAMETERS><PARAM id="slider1" value="-35.0"/></PARAMETERS>')
+            extra = ["--preset", str(tmp_path / "state.xml")]
     y, _ = ref.render(p, x, srate=float(sr), block=512)
     out = tmp_path / "out"
     r = subprocess.run([bounce, "--plugin", key, "--precision", precision, "--chunk-seconds", "0.25", "--out-dir", str(out), *extra, *files],

@@ -23,8 +23,9 @@ namespace {
 int usage(const char* argv0)
 {
     std::fprintf(stderr,
-                 "usage: %s --plugin KEY [--precision f32|f64] [--block N] [--chunk-seconds S] [--tail-seconds S]\n"
-                 "          [--set SLIDER=VALUE ...] [--device D] [--out-dir DIR] IN.wav [IN2.wav ...]\n"
+                 "usage: %s (--plugin KEY | --plugin-json plugin.json) [--precision f32|f64] [--block N] [--chunk-seconds S]\n"
+                 "          [--tail-seconds S] [--preset STATE.xml] [--set SLIDER=VALUE ...] [--save-preset OUT.xml] [--device D]\n"
+                 "          [--out-dir DIR] IN.wav [IN2.wav ...]\n"
                  "       %s --list                 plugin keys, channel counts and sliders the library renders\n"
                  "       %s --wav-info FILE.wav    header + checksum of the decoded samples (no GPU needed)\n",
                  argv0, argv0, argv0);
@@ -54,6 +55,67 @@ std::string json_escape(const std::string& s)
         else o += c;
     }
     return o;
+}
+
+bool slurp(const std::string& path, std::string& out)
+{
+    FILE* f = std::fopen(path.c_str(), "rb");
+    if (!f) return false;
+    char buf[4096];
+    size_t n;
+    out.clear();
+    while ((n = std::fread(buf, 1, sizeof buf, f)) > 0) out.append(buf, n);
+    std::fclose(f);
+    return true;
+}
+
+// value of attribute `name` inside the tag text [b, e)
+bool attr(const std::string& t, size_t b, size_t e, const char* name, std::string& out)
+{
+    const std::string key = std::string(name) + "=\"";
+    const size_t k = t.find(key, b);
+    if (k == std::string::npos || k >= e) return false;
+    const size_t q = t.find('"', k + key.size());
+    if (q == std::string::npos || q > e) return false;
+    out = t.substr(k + key.size(), q - k - key.size());
+    return true;
+}
+
+// APVTS state as the reference saves it (getStateInformation, src/JSFXJuceProcessor.cpp:3777-3880: the ValueTree's XML,
+// one <PARAM id="sliderN" value="..."/> per parameter, ids from :775): slider number -> host value.  Other children
+// (FILES, FILE_UI, SMART_IDLE, string sliders) are host-only state and are ignored.
+bool read_preset(const std::string& path, std::map<int, float>& out, std::string& err)
+{
+    std::string t;
+    if (!slurp(path, t)) { err = "cannot open " + path; return false; }
+    size_t pos = 0;
+    int found = 0;
+    while ((pos = t.find("<PARAM", pos)) != std::string::npos) {
+        const size_t e = t.find('>', pos);
+        if (e == std::string::npos) break;
+        std::string id, val;
+        if (attr(t, pos, e, "id", id) && attr(t, pos, e, "value", val) && id.compare(0, 6, "slider") == 0) {
+            out[std::atoi(id.c_str() + 6)] = (float)std::atof(val.c_str());
+            ++found;
+        }
+        pos = e;
+    }
+    if (!found) { err = path + ": no <PARAM id=\"sliderN\" value=...> elements"; return false; }
+    return true;
+}
+
+// "slug" of a plugin.json (the key the catalog tooling identifies a plugin by, pluginlib.py:105-212)
+bool read_slug(const std::string& path, std::string& slug, std::string& err)
+{
+    std::string t;
+    if (!slurp(path, t)) { err = "cannot open " + path; return false; }
+    const size_t k = t.find("\"slug\"");
+    const size_t c = k == std::string::npos ? k : t.find(':', k);
+    const size_t q0 = c == std::string::npos ? c : t.find('"', c);
+    const size_t q1 = q0 == std::string::npos ? q0 : t.find('"', q0 + 1);
+    if (q1 == std::string::npos) { err = path + ": no \"slug\""; return false; }
+    slug = t.substr(q0 + 1, q1 - q0 - 1);
+    return true;
 }
 
 int list_plugins()
@@ -98,6 +160,7 @@ int main(int argc, char** argv)
     double chunk_seconds = 10.0, tail_seconds = 0.0;
     std::map<int, float> sets;
     std::vector<std::string> inputs;
+    std::string save_preset, err;
     for (int i = 1; i < argc; ++i) {
         const std::string a = argv[i];
         auto need = [&](const char* name) -> const char* {
@@ -107,6 +170,9 @@ int main(int argc, char** argv)
         if (a == "--list") return list_plugins();
         else if (a == "--wav-info") return wav_info(need("--wav-info"));
         else if (a == "--plugin") plugin = need("--plugin");
+        else if (a == "--plugin-json") { if (!read_slug(need("--plugin-json"), plugin, err)) return fail(err); }
+        else if (a == "--preset") { if (!read_preset(need("--preset"), sets, err)) return fail(err); }
+        else if (a == "--save-preset") save_preset = need("--save-preset");
         else if (a == "--precision") precision = need("--precision");
         else if (a == "--block") block = std::atoi(need("--block"));
         else if (a == "--device") device = std::atoi(need("--device"));
@@ -152,6 +218,18 @@ int main(int argc, char** argv)
         row[(size_t)c] = si.def;
         const auto it = sets.find(si.index0 + 1);
         if (it != sets.end()) { row[(size_t)c] = it->second; sets.erase(it); }
+    }
+    if (!save_preset.empty()) {                      // the values this bounce used, in the form --preset reads
+        FILE* f = std::fopen(save_preset.c_str(), "w");
+        if (!f) return fail("cannot create " + save_preset);
+        std::fprintf(f, "<?xml version=\"1.0\" encoding=\"UTF-8\"?>\n<PARAMS plugin=\"%s\">\n", json_escape(plugin).c_str());
+        for (int c = 0; c < pi.n_sliders; ++c) {
+            za_slider_info si;
+            za_gpu_slider_info(plugin.c_str(), c, &si);
+            std::fprintf(f, "  <PARAM id=\"slider%d\" value=\"%.9g\"/>\n", si.index0 + 1, (double)row[(size_t)c]);
+        }
+        std::fprintf(f, "</PARAMS>\n");
+        std::fclose(f);
     }
     if (!sets.empty()) return fail("--set: plugin " + plugin + " declares no slider" + std::to_string(sets.begin()->first));
     std::vector<float> params((size_t)ns * (size_t)std::max(pi.n_sliders, 1));
