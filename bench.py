@@ -418,5 +418,15 @@ def main():
         dist.destroy_process_group()
 
 
+def _only_json_on_stdout():
+    """The contract is ONE JSON line on stdout.  Libraries print there too (NCCL's version banner under torchrun), so
+    file descriptor 1 is pointed at stderr for the whole run and `print` keeps the real stdout."""
+    sys.stdout.flush()
+    real = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real, "w", buffering=1)
+
+
 if __name__ == "__main__":
+    _only_json_on_stdout()
     main()
