@@ -41,7 +41,7 @@ class Emu:
         self.n_vars, self.n_in, self.n_out, self.mem_slots = (self.lib.emu_info(i) for i in range(4))
         self.names = [self.lib.emu_var_name(k).decode() for k in range(self.n_vars)] if self.n_vars > 0 else []
 
-    def render(self, sliders, params, x, block=512, srate=48000.0):
+    def render(self, sliders, params, x, block=512, srate=48000.0, mem_slots=None):
         """sliders: oracle layout (list of dicts); params [n_sliders] or [nb][n_sliders]; x [n_in][nf] -> y f32, tap f64, vars."""
         import za_oracle as zo
         dt = np.float64 if self.f64 else np.float32
@@ -49,11 +49,12 @@ class Emu:
         p = np.atleast_2d(np.asarray(params, np.float32))
         q = np.ascontiguousarray(zo.quantise(sliders, p))
         idx = np.array([s["index0"] for s in sliders], np.int32)
-        state = np.zeros(self.n_vars + 65, dt); mem = np.zeros(max(self.mem_slots, 1), dt)
+        slots = self.mem_slots if mem_slots is None else mem_slots          # (tests shrink the heap to provoke the overflow path)
+        state = np.zeros(self.n_vars + 65, dt); mem = np.zeros(slots + 1, dt)          # + the spare slot out-of-range accesses land in
         mt = np.zeros(625, np.uint32); err = np.zeros(1, np.int32)
         xin = np.ascontiguousarray(x, np.float32)
         y = np.zeros((max(self.n_out, 1), nf), np.float32); tap = np.zeros((max(self.n_out, 1), nf), np.float64)
-        a = GenLaunch(xin.ctypes.data, y.ctypes.data, tap.ctypes.data, nf, nf, self.mem_slots, 1, block, 1, len(sliders),
+        a = GenLaunch(xin.ctypes.data, y.ctypes.data, tap.ctypes.data, nf, nf, slots, 1, block, 1, len(sliders),
                       q.ctypes.data, idx.ctypes.data, state.ctypes.data, mem.ctypes.data, mt.ctypes.data, err.ctypes.data, srate)
         self.lib.emu_prepare(C.byref(a), int(self.f64))
         a.n_rows = q.shape[0]

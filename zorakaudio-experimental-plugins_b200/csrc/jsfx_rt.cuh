@@ -34,6 +34,7 @@ inline float __fadd_rn(float a, float b) { return a + b; }
 inline float __fsub_rn(float a, float b) { return a - b; }
 inline float __fmul_rn(float a, float b) { return a * b; }
 inline float __fdiv_rn(float a, float b) { return a / b; }
+inline float __fdividef(float a, float b) { return a / b; }
 inline float __fsqrt_rn(float a) { return sqrtf(a); }
 inline int __float_as_int(float f) { int i; memcpy(&i, &f, 4); return i; }
 inline float __int_as_float(int i) { float f; memcpy(&f, &i, 4); return f; }
@@ -71,7 +72,7 @@ __device__ __forceinline__ double div_(double a, double b) { return __ddiv_rn(a,
 __device__ __forceinline__ float add_(float a, float b) { return __fadd_rn(a, b); }
 __device__ __forceinline__ float sub_(float a, float b) { return __fsub_rn(a, b); }
 __device__ __forceinline__ float mul_(float a, float b) { return __fmul_rn(a, b); }
-__device__ __forceinline__ float div_(float a, float b) { return __fdiv_rn(a, b); }
+__device__ __forceinline__ float div_(float a, float b) { return __fdividef(a, b); }      // fp32 mode: MUFU.RCP + FMUL (2 ulp), no slow-path call
 __device__ __forceinline__ double pow_(double a, double b) { return pow(a, b); }
 __device__ __forceinline__ float pow_(float a, float b) { return powf(a, b); }
 
@@ -106,6 +107,8 @@ template <typename R> struct Rt {
     long long stride, cap;  // n_streams, slots per stream
     unsigned* mt;           // this stream's column of the MT19937 state: word k at mt[k * stride], index at word 624
     int* err;               // device error flag: 1 = mem[] index beyond the heap the plugin was sized for
+    long long amax;         // largest mem[] index this thread has touched in this launch (fp64 mode)
+    int amax32;             // the same, fp32 mode
     R srate, samplesblock;
     R sliders[64];
     R spl[64];
@@ -123,27 +126,42 @@ template <typename R> struct Rt {
         const int a = (int)__fadd_rn(__fadd_rn(base, idx), 1.0e-5f);     // saturating conversion, NaN -> 0
         return a < 0 ? 0 : a;
     }
-    __device__ __forceinline__ R ldi(long long a) const
+    // mem[x] with no base (the common form): 0 + x is x for every x the truncation can tell apart
+    __device__ __forceinline__ long long addr1(double idx) const
     {
-        if (a >= cap) { *err = 1; return (R)0; }      // the reference grows the heap and reads 0
-        return mem[a * stride];
+        const long long a = (long long)__dadd_rn(idx, 1.0e-5);
+        return a < 0 ? 0 : a;
     }
-    __device__ __forceinline__ R ldi(int a) const     // fp32 mode: 32-bit index, one IMAD.WIDE to the address
+    __device__ __forceinline__ int addr1(float idx) const
     {
-        if (a >= (int)cap) { *err = 1; return (R)0; }
-        return mem[(long long)a * (int)stride];
+        const int a = (int)__fadd_rn(idx, 1.0e-5f);
+        return a < 0 ? 0 : a;
+    }
+    // Accesses beyond the heap the plugin was sized for (the reference would grow it, :1452-1491): the index is
+    // clamped to the spare slot `cap` every heap carries and the largest index seen is kept in a register; the kernel
+    // raises the device error flag once, when it stores the context back -- no branch, flag store or constant load
+    // on the per-access path.
+    __device__ __forceinline__ R ldi(long long a)
+    {
+        amax = a > amax ? a : amax;
+        return mem[(a < cap ? a : cap) * stride];
+    }
+    __device__ __forceinline__ void st(long long a, R v)
+    {
+        amax = a > amax ? a : amax;
+        mem[(a < cap ? a : cap) * stride] = v;
+    }
+    __device__ __forceinline__ R ldi(int a)     // fp32 mode: 32-bit index, one IMAD.WIDE to the address
+    {
+        amax32 = max(amax32, a);
+        return mem[(long long)min(a, (int)cap) * (int)stride];
     }
     __device__ __forceinline__ void st(int a, R v)
     {
-        if (a >= (int)cap) { *err = 1; return; }
-        mem[(long long)a * (int)stride] = v;
+        amax32 = max(amax32, a);
+        mem[(long long)min(a, (int)cap) * (int)stride] = v;
     }
-    __device__ __forceinline__ R ld(R base, R idx) const { return ldi(addr(base, idx)); }
-    __device__ __forceinline__ void st(long long a, R v)
-    {
-        if (a >= cap) { *err = 1; return; }
-        mem[a * stride] = v;
-    }
+    __device__ __forceinline__ R ld(R base, R idx) { return ldi(addr(base, idx)); }
     __device__ __forceinline__ void memset(R dest, R value, R len)                         // :5439-5495
     {
         long long d = (long long)__dadd_rn((double)dest, 1.0e-5);
@@ -209,7 +227,7 @@ __device__ __forceinline__ void ctx_open(Rt<R>& c, R* v, const GenLaunch& a, int
 {
     const long long ns = a.n_streams;
     c.mem = reinterpret_cast<R*>(a.mem) + sc; c.stride = ns; c.cap = a.mem_slots;
-    c.mt = a.mt + sc; c.err = a.err;
+    c.mt = a.mt + sc; c.err = a.err; c.amax = -1; c.amax32 = -1;
     c.srate = (R)a.srate; c.samplesblock = (R)0;
     const R* st = reinterpret_cast<const R*>(a.state) + sc;
 #pragma unroll
@@ -227,6 +245,7 @@ __device__ __forceinline__ void ctx_close(const Rt<R>& c, const R* v, const GenL
 #pragma unroll
     for (int k = 0; k < 64; ++k) st[(long long)(S::kVars + k) * ns] = c.sliders[k];
     st[(long long)(S::kVars + 64) * ns] = valid;
+    if (c.amax >= c.cap || c.amax32 >= (int)c.cap) *c.err = 1;
 }
 
 // push one row of quantised slider values (pushParamsToStateSliders, :9286-9357): returns "changed"
@@ -267,11 +286,22 @@ __global__ void __launch_bounds__(32) jsfx_prepare_kernel(const GenLaunch a)
     ctx_close<S, R>(c, v, a, s, (R)1);
 }
 
+// 4-byte asynchronous global -> shared copy (LDGSTS); `ok` false = write zero without reading
+__device__ __forceinline__ void cp_async4(float* smem_dst, const float* gmem_src, bool ok)
+{
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    const int n = ok ? 4 : 0;
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(d), "l"(gmem_src), "r"(n) : "memory");
+}
+
 template <class S, typename R, bool TAP>
 __global__ void __launch_bounds__(32) jsfx_process_kernel(const GenLaunch a)
 {
-    extern __shared__ float tile[];                // [kCh][32 streams][33]
-    constexpr int kP = 33;
+    // Audio tiles, [2 buffers][kCh][32 streams][33]: the tile after the one being computed is already on its way from
+    // HBM (cp.async), so the only warp of the SM does not sit out a DRAM latency per tile (ncu, profiles/
+    // r01_generic_rtt_ncu.md: 26 % of the samples were the tile-in stores waiting for their loads).
+    extern __shared__ float tiles[];
+    constexpr int kP = 33, kTile = S::kCh * 32 * kP;
     const int lane = threadIdx.x, s0 = blockIdx.x * 32, s = s0 + lane;
     const bool live = s < a.n_streams;             // dead lanes only help move the audio tiles
     const int ns_cta = min(32, a.n_streams - s0);
@@ -283,9 +313,19 @@ __global__ void __launch_bounds__(32) jsfx_process_kernel(const GenLaunch a)
         valid = reinterpret_cast<const R*>(a.state)[(long long)(S::kVars + 64) * a.n_streams + s] != (R)0;
     }
 
+    // tile in: lane = frame, 128-byte rows of every (stream, channel) of the CTA
+    auto fetch = [&](float* tile, int64_t frame0, int nf) {
+        const float* src = a.in + (size_t)s0 * S::kIn * a.row_stride + frame0 + (lane < nf ? lane : 0);
+        for (int q = 0; q < ns_cta * S::kIn; ++q)
+            cp_async4(tile + ((q % S::kIn) * 32 + q / S::kIn) * kP + lane, src + (size_t)q * a.row_stride, lane < nf);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+
     int64_t pos = 0;
+    int nb = (int)min((int64_t)a.block_len, a.n_frames - pos);
+    int buf = 0;
+    if (a.n_frames > 0) fetch(tiles, 0, min(32, nb));
     for (int blk = 0; pos < a.n_frames; ++blk) {
-        const int nb = (int)min((int64_t)a.block_len, a.n_frames - pos);
         if (live) {
             if (a.n_rows > 0) {
                 const bool changed = push_sliders<S, R>(c, v, a, blk < a.n_rows ? blk : a.n_rows - 1, s, valid);
@@ -295,22 +335,19 @@ __global__ void __launch_bounds__(32) jsfx_process_kernel(const GenLaunch a)
             c.samplesblock = (R)nb;
             S::template block<R>(c, v);
         }
+        const int nb_next = (int)min((int64_t)a.block_len, a.n_frames - (pos + nb));      // <= 0 after the last block
         for (int f0 = 0; f0 < nb; f0 += 32) {
             const int nf = min(32, nb - f0);
-            // tile in: lane = frame, 128-byte rows; the loads go out in groups of 8 rows before their shared-memory
-            // stores, so one DRAM latency covers a group (ncu: a load-store pair per row left the only warp of the SM
-            // waiting on the long scoreboard for half of its time)
-            const int nq = ns_cta * S::kIn;
-            for (int q0 = 0; q0 < nq; q0 += 8) {
-                float t[8];
-#pragma unroll
-                for (int u = 0; u < 8; ++u)
-                    t[u] = (q0 + u < nq && lane < nf) ? a.in[((size_t)s0 * S::kIn + q0 + u) * a.row_stride + pos + f0 + lane] : 0.f;
-#pragma unroll
-                for (int u = 0; u < 8; ++u) {
-                    const int q = q0 + u;
-                    if (q < nq) tile[((q % S::kIn) * 32 + q / S::kIn) * kP + lane] = t[u];
-                }
+            float* tile = tiles + buf * kTile;
+            // the next tile of this block, else the first of the next block
+            const bool more_here = f0 + 32 < nb;
+            const int64_t nx0 = more_here ? pos + f0 + 32 : pos + nb;
+            const int nxf = more_here ? min(32, nb - f0 - 32) : min(32, nb_next);
+            if (nxf > 0) {
+                fetch(tiles + (buf ^ 1) * kTile, nx0, nxf);
+                asm volatile("cp.async.wait_group 1;" ::: "memory");
+            } else {
+                asm volatile("cp.async.wait_group 0;" ::: "memory");
             }
             __syncwarp();
             if (live) {
@@ -330,8 +367,10 @@ __global__ void __launch_bounds__(32) jsfx_process_kernel(const GenLaunch a)
             for (int q = 0; q < ns_cta * S::kOut; ++q)
                 if (lane < nf) a.out[((size_t)s0 * S::kOut + q) * a.row_stride + pos + f0 + lane] = tile[((q % S::kOut) * 32 + q / S::kOut) * kP + lane];
             __syncwarp();
+            buf ^= 1;
         }
         pos += nb;
+        nb = nb_next;
     }
     if (live) ctx_close<S, R>(c, v, a, s, valid ? (R)1 : (R)0);
 }
@@ -346,14 +385,14 @@ template <class S> bool launch_prepare(const GenLaunch& a, int precision, cudaSt
 template <class S> bool launch_process(const GenLaunch& a, int precision, cudaStream_t st)
 {
     const int blocks = (a.n_streams + 31) / 32;
-    const size_t smem = (size_t)S::kCh * 32 * 33 * sizeof(float);
-    if (precision) {
-        if (a.tap) jsfx_process_kernel<S, double, true><<<blocks, 32, smem, st>>>(a);
-        else jsfx_process_kernel<S, double, false><<<blocks, 32, smem, st>>>(a);
-    } else {
-        jsfx_process_kernel<S, float, false><<<blocks, 32, smem, st>>>(a);
-    }
-    return cuda_ok(cudaGetLastError(), "jsfx_process_kernel launch");
+    const size_t smem = (size_t)2 * S::kCh * 32 * 33 * sizeof(float);
+    auto go = [&](auto kern) {
+        if (smem > 48 * 1024 && !cuda_ok(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "jsfx_process_kernel smem attr")) return false;
+        kern<<<blocks, 32, smem, st>>>(a);
+        return cuda_ok(cudaGetLastError(), "jsfx_process_kernel launch");
+    };
+    if (precision) return a.tap ? go(jsfx_process_kernel<S, double, true>) : go(jsfx_process_kernel<S, double, false>);
+    return go(jsfx_process_kernel<S, float, false>);
 }
 
 #else   // ZA_JSFX_HOST_EMU: the same two entry points for ONE stream on the host

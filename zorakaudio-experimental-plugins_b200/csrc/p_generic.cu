@@ -68,7 +68,7 @@ public:
         for (int j = 0; same && j < d_->n_decl; ++j) same = idx[j] == d_->decl_index0[j];
         if (!same) { set_error(std::string(d_->key) + ": slider declarations differ from the ones the generated code was built for"); return false; }
         return cuda_ok(cudaMalloc(&d_state, (size_t)(d_->n_vars + 65) * ns * rsize), "state") &&
-               cuda_ok(cudaMalloc(&d_mem, (size_t)std::max<int64_t>(d_->mem_slots, 1) * ns * rsize), "mem[] heap") &&
+               cuda_ok(cudaMalloc(&d_mem, (size_t)(d_->mem_slots + 1) * ns * rsize), "mem[] heap") /* + the spare slot out-of-range accesses land in */ &&
                cuda_ok(cudaMalloc(&d_mt, 625 * ns * sizeof(unsigned)), "rand state") &&
                cuda_ok(cudaMalloc(&d_err, sizeof(int)), "err flag") &&
                cuda_ok(cudaMalloc(&d_index0, std::max<size_t>(idx.size(), 1) * sizeof(int)), "slider index") &&
@@ -79,7 +79,7 @@ public:
     {
         const size_t ns = (size_t)I.n_streams;
         if (!cuda_ok(cudaMemsetAsync(d_state, 0, (size_t)(d_->n_vars + 65) * ns * rsize, I.stream), "state reset") ||
-            !cuda_ok(cudaMemsetAsync(d_mem, 0, (size_t)std::max<int64_t>(d_->mem_slots, 1) * ns * rsize, I.stream), "heap reset") ||
+            !cuda_ok(cudaMemsetAsync(d_mem, 0, (size_t)(d_->mem_slots + 1) * ns * rsize, I.stream), "heap reset") ||
             !cuda_ok(cudaMemsetAsync(d_mt, 0, 625 * ns * sizeof(unsigned), I.stream), "rand reset") ||
             !cuda_ok(cudaMemsetAsync(d_err, 0, sizeof(int), I.stream), "err reset"))
             return false;

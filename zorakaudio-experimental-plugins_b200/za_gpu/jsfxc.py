@@ -530,7 +530,7 @@ class Emitter:
             return self.tmp(self.ref(name))
         if k == "index":
             b = self.ex(n[1]); i = self.ex(n[2])
-            return self.tmp(f"c.ld({b}, {i})")
+            return self.tmp(f"c.ldi(c.addr1({i}))" if b == "R(0)" else f"c.ld({b}, {i})")
         if k == "un":
             a = self.ex(n[2])
             if n[1] == "+":
@@ -594,7 +594,7 @@ class Emitter:
                 b = self.ex(tgt[1]); i = self.ex(tgt[2])
                 self.n += 1
                 a = f"a{self.n}"
-                self.w(f"const auto {a} = c.addr({b}, {i});")
+                self.w(f"const auto {a} = c.addr1({i});" if b == "R(0)" else f"const auto {a} = c.addr({b}, {i});")
                 if op == "=":
                     self.w(f"c.st({a}, {rhs});")
                     return rhs
