@@ -295,7 +295,7 @@ __device__ __forceinline__ void cp_async4(float* smem_dst, const float* gmem_src
 }
 
 template <class S, typename R, bool TAP>
-__global__ void __launch_bounds__(32) jsfx_process_kernel(const GenLaunch a)
+__global__ void __launch_bounds__(32, 1) jsfx_process_kernel(const GenLaunch a)
 {
     // Audio tiles, [2 buffers][kCh][32 streams][33]: the tile after the one being computed is already on its way from
     // HBM (cp.async), so the only warp of the SM does not sit out a DRAM latency per tile (ncu, profiles/
