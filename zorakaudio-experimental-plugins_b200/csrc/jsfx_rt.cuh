@@ -109,6 +109,8 @@ template <typename R> struct Rt {
     int* err;               // device error flag: 1 = mem[] index beyond the heap the plugin was sized for
     long long amax;         // largest mem[] index this thread has touched in this launch (fp64 mode)
     int amax32;             // the same, fp32 mode
+    int cap32;              // cap as int
+    unsigned stride_bytes;  // n_streams * sizeof(R): distance between two slots of one stream
     R srate, samplesblock;
     R sliders[64];
     R spl[64];
@@ -141,25 +143,31 @@ template <typename R> struct Rt {
     // clamped to the spare slot `cap` every heap carries and the largest index seen is kept in a register; the kernel
     // raises the device error flag once, when it stores the context back -- no branch, flag store or constant load
     // on the per-access path.
+    // slot a (already clamped to [0, cap]) of this stream's column: base + a * (n_streams * sizeof(R)) as a
+    // 32 x 32 -> 64 bit multiply (IMAD.WIDE.U32) + add; a generic 64-bit index * 64-bit stride costs seven instructions
+    __device__ __forceinline__ R* slot(unsigned a) const
+    {
+        return reinterpret_cast<R*>(reinterpret_cast<char*>(mem) + (unsigned long long)a * stride_bytes);
+    }
     __device__ __forceinline__ R ldi(long long a)
     {
         amax = a > amax ? a : amax;
-        return mem[(a < cap ? a : cap) * stride];
+        return *slot((unsigned)(a < cap ? a : cap));
     }
     __device__ __forceinline__ void st(long long a, R v)
     {
         amax = a > amax ? a : amax;
-        mem[(a < cap ? a : cap) * stride] = v;
+        *slot((unsigned)(a < cap ? a : cap)) = v;
     }
-    __device__ __forceinline__ R ldi(int a)     // fp32 mode: 32-bit index, one IMAD.WIDE to the address
+    __device__ __forceinline__ R ldi(int a)     // fp32 mode: 32-bit index
     {
         amax32 = max(amax32, a);
-        return mem[(long long)min(a, (int)cap) * (int)stride];
+        return *slot((unsigned)min(a, cap32));
     }
     __device__ __forceinline__ void st(int a, R v)
     {
         amax32 = max(amax32, a);
-        mem[(long long)min(a, (int)cap) * (int)stride] = v;
+        *slot((unsigned)min(a, cap32)) = v;
     }
     __device__ __forceinline__ R ld(R base, R idx) { return ldi(addr(base, idx)); }
     __device__ __forceinline__ void memset(R dest, R value, R len)                         // :5439-5495
@@ -228,6 +236,7 @@ __device__ __forceinline__ void ctx_open(Rt<R>& c, R* v, const GenLaunch& a, int
     const long long ns = a.n_streams;
     c.mem = reinterpret_cast<R*>(a.mem) + sc; c.stride = ns; c.cap = a.mem_slots;
     c.mt = a.mt + sc; c.err = a.err; c.amax = -1; c.amax32 = -1;
+    c.cap32 = (int)a.mem_slots; c.stride_bytes = (unsigned)a.n_streams * (unsigned)sizeof(R);
     c.srate = (R)a.srate; c.samplesblock = (R)0;
     const R* st = reinterpret_cast<const R*>(a.state) + sc;
 #pragma unroll
