@@ -7,7 +7,8 @@ run (streams / N per GPU, strong scaling over a fixed batch is NOT what is measu
 65,536 / N streams, so the whole-job batch is fixed and `scaling` is "strong").  One step = one 1 s time chunk
 of every stream (the 10 min bounce is 600 such chunks with state carried; inputs are generated on the device
 per leaf, outside the timed region, and reused).  Every leaf has its own handle and CUDA stream, so the eight
-kernels of a step overlap on the device; the step is timed with CUDA events bracketing all of them.
+kernels of a step overlap on the device (launch order and stream priorities: see LEAVES below); the step is timed
+with CUDA events bracketing all of them.
 """
 from __future__ import annotations
 
@@ -21,7 +22,14 @@ import numpy as np
 
 REPO = Path(__file__).resolve().parent
 SRATE = 48000.0
-LEAVES = ["EasyExpander", "RTT", "SOMA", "ATTACK", "ERBTilt", "SpectralStabilizer", "cascade8", "stft_mask2048"]
+# Schedule of one step: every leaf on its own CUDA stream, launched longest kernel first (the translated leaves hold
+# their SM slots for the whole launch, so the two long ones must not queue behind short ones).  The hand-written kernels
+# take milliseconds but each of their CTAs needs a whole SM (shared-memory tiles), so their streams get the highest
+# priority: when an SM drains they go first instead of starving behind the next step's long kernels.  Measured
+# alternatives (B200, ms per step): catalog order without priorities 578; longest first 510; + priorities 479; two
+# phases (hand-written leaves, then the translated ones) 669-721.
+LEAVES = ["SpectralStabilizer", "ERBTilt", "SOMA", "RTT", "ATTACK", "stft_mask2048", "EasyExpander", "cascade8"]
+PRIORITY = {"stft_mask2048": -3, "EasyExpander": -3, "cascade8": -3, "SpectralStabilizer": -2, "ERBTilt": -2, "SOMA": -1}
 NOT_BUILT = ["VAR", "ModTilt", "ClickBeGoneSG", "GTS", "RED"]
 TOTAL_STREAMS = 65536
 
@@ -60,7 +68,7 @@ def main(args):
     for li, key in enumerate(LEAVES):
         info = za_gpu.plugin_info(key)
         W = dict(plugin=key, ch=(info.n_in, info.n_out))
-        st = torch.cuda.Stream()
+        st = torch.cuda.Stream(priority=PRIORITY.get(key, 0))
         bp = za_gpu.BatchProcessor(key, per_leaf, SRATE, 512, prec, local)
         bp.set_stream(st.cuda_stream)
         p = wl.default_params(key, per_leaf, first_stream=rank * per_leaf)
@@ -155,7 +163,7 @@ def main(args):
                                f"({', '.join(LEAVES)}), one step = a {sec:g} s time chunk of every stream (the 10 min bounce = 600 chunks, state carried)",
                    "leaves_not_built": NOT_BUILT, "streams_per_gpu": per_leaf * len(LEAVES), "streams_per_leaf_per_gpu": per_leaf,
                    "frames_per_stream_per_step": nf, "block_len": 512, "l2": "inputs (%.1f GB per step per GPU) larger than L2" % (alg_bytes / 2e9),
-                   "parallelism": f"streams sharded x{world}, one CUDA stream per leaf"},
+                   "parallelism": f"streams sharded x{world}, one CUDA stream per leaf (longest kernel first, hand-written leaves at high stream priority)"},
         "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
         "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "peak_source": peak_kind,
                      "traffic": None, "kernel": "all leaves' kernels of one step, overlapped", "kernel_ms_per_launch": ms,

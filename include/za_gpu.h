@@ -123,7 +123,9 @@ ZA_API int za_gpu_launch_count(za_gpu_handle h, int64_t* kernels_launched);   /*
  * most recent za_gpu_process call, and how many launches that covers. */
 ZA_API int za_gpu_last_kernel_ms(za_gpu_handle h, double* ms, int* launches);
 /* Tuning knobs for experiments: name = "force_generic_io" | "warps_per_stream" | "host_chunk_frames" |
- * "tile_buffers" (1|2, packed fp32 kernel) | "scalar_f32" (1 = fp32 on the scalar-FFMA kernel). */
+ * "tile_buffers" (1|2, packed fp32 kernel) | "scalar_f32" (1 = fp32 on the scalar-FFMA kernel) |
+ * "heap_slots" (translated leaves: use a smaller mem[] heap than the plugin was sized for; an access beyond it fails the
+ * call -- ZA_ERR_STATE, "mem[] index beyond the heap" -- on that call (host memory) or on the next call / za_gpu_sync). */
 ZA_API int za_gpu_set_option(za_gpu_handle h, const char* name, int value);
 
 /* ---- one-shot form sketched in BASELINE.json north_star ------------------------------------ */

@@ -146,3 +146,22 @@ def test_cfg1_ddt(gpu):
                 continue
             assert np.array_equal(got, want), name
     bp.close()
+
+
+def test_heap_overflow_fails_the_call(gpu):
+    """A translated leaf that indexes mem[] beyond its heap must fail loudly (the reference would grow the heap): with the
+    heap shrunk below what SpectralStabilizer uses, the host-memory call returns an error, and a device-memory call
+    surfaces it at the following synchronisation."""
+    import za_gpu
+    ref = zo.RefPlugin("SpectralStabilizer")
+    ns, nf = 5, 4096
+    p, x = make_case(ref, ns, nf, False)
+    bp = gpu.BatchProcessor("SpectralStabilizer", ns, precision="f32")
+    bp.set_option("heap_slots", 1000)
+    with pytest.raises(za_gpu.ZaError, match="beyond the heap"):
+        bp.prepare(p)                                  # @init already writes state up to slot ~2080
+        bp.process(x)
+    bp.close()
+    bp = gpu.BatchProcessor("SpectralStabilizer", ns, precision="f32").prepare(p)
+    bp.process(x)                                      # the real heap: fine
+    bp.close()

@@ -295,6 +295,8 @@ __global__ void __launch_bounds__(32) jsfx_prepare_kernel(const GenLaunch a)
     ctx_close<S, R>(c, v, a, s, (R)1);
 }
 
+constexpr int kTileFrames = 32;      // frames per audio tile of jsfx_process_kernel (16 or 32)
+
 // 4-byte asynchronous global -> shared copy (LDGSTS); `ok` false = write zero without reading
 __device__ __forceinline__ void cp_async4(float* smem_dst, const float* gmem_src, bool ok)
 {
@@ -306,14 +308,17 @@ __device__ __forceinline__ void cp_async4(float* smem_dst, const float* gmem_src
 template <class S, typename R, bool TAP>
 __global__ void __launch_bounds__(32, 1) jsfx_process_kernel(const GenLaunch a)
 {
-    // Audio tiles, [2 buffers][kCh][32 streams][33]: the tile after the one being computed is already on its way from
-    // HBM (cp.async), so the only warp of the SM does not sit out a DRAM latency per tile (ncu, profiles/
-    // r01_generic_rtt_ncu.md: 26 % of the samples were the tile-in stores waiting for their loads).
+    // Audio tiles, [2 buffers][kCh][32 streams][kF frames + 1]: the tile after the one being computed is already on
+    // its way from HBM (cp.async), so the only warp of the SM does not sit out a DRAM latency per tile (ncu, profiles/
+    // r01_generic_rtt_ncu.md: 26 % of the samples were the tile-in stores waiting for their loads).  kF = 32 (128-byte
+    // row segments, one row per copy instruction) measured 25-50 % faster than kF = 16 (two rows per instruction, half
+    // the shared memory) on the short leaves, so it is the one built.
     extern __shared__ float tiles[];
-    constexpr int kP = 33, kTile = S::kCh * 32 * kP;
+    constexpr int kF = kTileFrames, kP = kF + 1, kTile = S::kCh * 32 * kP, kRows = 32 / kF;   // rows per copy instruction
     const int lane = threadIdx.x, s0 = blockIdx.x * 32, s = s0 + lane;
     const bool live = s < a.n_streams;             // dead lanes only help move the audio tiles
     const int ns_cta = min(32, a.n_streams - s0);
+    const int half = lane / kF, fl = lane % kF;    // tile I/O: kF lanes per row, lane = frame
     Rt<R> c;
     R v[S::kVars];
     bool valid = false;
@@ -322,18 +327,20 @@ __global__ void __launch_bounds__(32, 1) jsfx_process_kernel(const GenLaunch a)
         valid = reinterpret_cast<const R*>(a.state)[(long long)(S::kVars + 64) * a.n_streams + s] != (R)0;
     }
 
-    // tile in: lane = frame, 128-byte rows of every (stream, channel) of the CTA
     auto fetch = [&](float* tile, int64_t frame0, int nf) {
-        const float* src = a.in + (size_t)s0 * S::kIn * a.row_stride + frame0 + (lane < nf ? lane : 0);
-        for (int q = 0; q < ns_cta * S::kIn; ++q)
-            cp_async4(tile + ((q % S::kIn) * 32 + q / S::kIn) * kP + lane, src + (size_t)q * a.row_stride, lane < nf);
+        const int nq = ns_cta * S::kIn;
+        const float* src = a.in + (size_t)s0 * S::kIn * a.row_stride + frame0 + (fl < nf ? fl : 0);
+        for (int q0 = 0; q0 < nq; q0 += kRows) {
+            const int q = q0 + half;
+            if (q < nq) cp_async4(tile + ((q % S::kIn) * 32 + q / S::kIn) * kP + fl, src + (size_t)q * a.row_stride, fl < nf);
+        }
         asm volatile("cp.async.commit_group;" ::: "memory");
     };
 
     int64_t pos = 0;
     int nb = (int)min((int64_t)a.block_len, a.n_frames - pos);
     int buf = 0;
-    if (a.n_frames > 0) fetch(tiles, 0, min(32, nb));
+    if (a.n_frames > 0) fetch(tiles, 0, min(kF, nb));
     for (int blk = 0; pos < a.n_frames; ++blk) {
         if (live) {
             if (a.n_rows > 0) {
@@ -345,13 +352,13 @@ __global__ void __launch_bounds__(32, 1) jsfx_process_kernel(const GenLaunch a)
             S::template block<R>(c, v);
         }
         const int nb_next = (int)min((int64_t)a.block_len, a.n_frames - (pos + nb));      // <= 0 after the last block
-        for (int f0 = 0; f0 < nb; f0 += 32) {
-            const int nf = min(32, nb - f0);
+        for (int f0 = 0; f0 < nb; f0 += kF) {
+            const int nf = min(kF, nb - f0);
             float* tile = tiles + buf * kTile;
             // the next tile of this block, else the first of the next block
-            const bool more_here = f0 + 32 < nb;
-            const int64_t nx0 = more_here ? pos + f0 + 32 : pos + nb;
-            const int nxf = more_here ? min(32, nb - f0 - 32) : min(32, nb_next);
+            const bool more_here = f0 + kF < nb;
+            const int64_t nx0 = more_here ? pos + f0 + kF : pos + nb;
+            const int nxf = more_here ? min(kF, nb - f0 - kF) : min(kF, nb_next);
             if (nxf > 0) {
                 fetch(tiles + (buf ^ 1) * kTile, nx0, nxf);
                 asm volatile("cp.async.wait_group 1;" ::: "memory");
@@ -372,9 +379,15 @@ __global__ void __launch_bounds__(32, 1) jsfx_process_kernel(const GenLaunch a)
                 }
             }
             __syncwarp();
+            {
+                const int nq = ns_cta * S::kOut;
+                float* dst = a.out + (size_t)s0 * S::kOut * a.row_stride + pos + f0 + fl;
 #pragma unroll 4
-            for (int q = 0; q < ns_cta * S::kOut; ++q)
-                if (lane < nf) a.out[((size_t)s0 * S::kOut + q) * a.row_stride + pos + f0 + lane] = tile[((q % S::kOut) * 32 + q / S::kOut) * kP + lane];
+                for (int q0 = 0; q0 < nq; q0 += kRows) {
+                    const int q = q0 + half;
+                    if (q < nq && fl < nf) dst[(size_t)q * a.row_stride] = tile[((q % S::kOut) * 32 + q / S::kOut) * kP + fl];
+                }
+            }
             __syncwarp();
             buf ^= 1;
         }
@@ -394,7 +407,7 @@ template <class S> bool launch_prepare(const GenLaunch& a, int precision, cudaSt
 template <class S> bool launch_process(const GenLaunch& a, int precision, cudaStream_t st)
 {
     const int blocks = (a.n_streams + 31) / 32;
-    const size_t smem = (size_t)2 * S::kCh * 32 * 33 * sizeof(float);
+    const size_t smem = (size_t)2 * S::kCh * 32 * (kTileFrames + 1) * sizeof(float);
     auto go = [&](auto kern) {
         if (smem > 48 * 1024 && !cuda_ok(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "jsfx_process_kernel smem attr")) return false;
         kern<<<blocks, 32, smem, st>>>(a);

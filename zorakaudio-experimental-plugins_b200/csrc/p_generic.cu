@@ -22,12 +22,14 @@ class GenericPlugin : public PluginImpl {
     void* d_state = nullptr; void* d_mem = nullptr; unsigned* d_mt = nullptr; int* d_err = nullptr;
     double* d_q = nullptr; size_t q_cap = 0;
     int* d_index0 = nullptr;
+    int* h_err = nullptr;           // pinned mirror of d_err, refreshed by an async copy behind every launch
     size_t rsize = 8;
 
     GenLaunch base(Instance& I) const
     {
         GenLaunch a{};
-        a.mem_slots = d_->mem_slots; a.n_streams = I.n_streams; a.block_len = I.block_len; a.n_decl = (int)I.decls.size();
+        a.mem_slots = I.opt_heap_slots > 0 ? std::min<int64_t>(I.opt_heap_slots, d_->mem_slots) : d_->mem_slots;   // (tests shrink the heap to provoke the overflow path)
+        a.n_streams = I.n_streams; a.block_len = I.block_len; a.n_decl = (int)I.decls.size();
         a.decl_index0 = d_index0; a.state = d_state; a.mem = d_mem; a.mt = d_mt; a.err = d_err; a.srate = I.srate;
         return a;
     }
@@ -56,7 +58,7 @@ class GenericPlugin : public PluginImpl {
 
 public:
     explicit GenericPlugin(const GenDesc* d) : d_(d) {}
-    ~GenericPlugin() override { cudaFree(d_state); cudaFree(d_mem); cudaFree(d_mt); cudaFree(d_err); cudaFree(d_q); cudaFree(d_index0); }
+    ~GenericPlugin() override { cudaFree(d_state); cudaFree(d_mem); cudaFree(d_mt); cudaFree(d_err); cudaFree(d_q); cudaFree(d_index0); cudaFreeHost(h_err); }
 
     bool create(Instance& I) override
     {
@@ -71,6 +73,7 @@ public:
                cuda_ok(cudaMalloc(&d_mem, (size_t)(d_->mem_slots + 1) * ns * rsize), "mem[] heap") /* + the spare slot out-of-range accesses land in */ &&
                cuda_ok(cudaMalloc(&d_mt, 625 * ns * sizeof(unsigned)), "rand state") &&
                cuda_ok(cudaMalloc(&d_err, sizeof(int)), "err flag") &&
+               cuda_ok(cudaHostAlloc(&h_err, sizeof(int), cudaHostAllocDefault), "err mirror") && ((*h_err = 0), true) &&
                cuda_ok(cudaMalloc(&d_index0, std::max<size_t>(idx.size(), 1) * sizeof(int)), "slider index") &&
                cuda_ok(cudaMemcpy(d_index0, idx.data(), idx.size() * sizeof(int), cudaMemcpyHostToDevice), "slider index upload");
     }
@@ -88,7 +91,9 @@ public:
         a.q = d_q; a.n_rows = 1;
         if (!d_->prepare(a, I.precision, I.stream)) return false;
         ++I.launches;
-        return check_err(I);
+        if (!check_err(I)) return false;
+        *h_err = 0;
+        return true;
     }
 
     bool sliders_changed(Instance&, int, int, const std::vector<int>&) override { return true; }   // @slider runs on the device
@@ -110,6 +115,13 @@ public:
         if (!d_->process(a, I.precision, I.stream)) return false;
         if (timed) I.time_end();
         ++I.launches;
+        return cuda_ok(cudaMemcpyAsync(h_err, d_err, sizeof(int), cudaMemcpyDeviceToHost, I.stream), "err mirror copy");
+    }
+
+    bool deferred_error(Instance&) override
+    {
+        if (!h_err || *(volatile int*)h_err == 0) return false;
+        set_error(std::string(d_->key) + ": mem[] index beyond the heap this plugin was sized for");
         return true;
     }
 

@@ -271,11 +271,13 @@ static int do_process(Instance* I, const float* params, int npb, const float* in
     if (tap && I->precision != ZA_F64) { set_error("za_gpu_process_tap64 needs precision ZA_F64"); return ZA_ERR_ARG; }
     if (!cuda_ok(cudaSetDevice(I->device), "cudaSetDevice")) return ZA_ERR_CUDA;
     I->ev_used = 0;
+    if (I->impl->deferred_error(*I)) return ZA_ERR_STATE;           // flagged by a kernel of an earlier call
     if (n_frames == 0) return ZA_OK;
     bool ok;
     if (mem == ZA_MEM_DEVICE) ok = process_range(*I, params, npb, 0, I->n_streams, in, out, tap, n_frames, stride);
     else if (mem == ZA_MEM_HOST) ok = process_host(*I, params, npb, in, out, tap, n_frames, stride);
     else { set_error("za_gpu_process: unknown memory kind"); return ZA_ERR_ARG; }
+    if (ok && mem == ZA_MEM_HOST && I->impl->deferred_error(*I)) return ZA_ERR_STATE;   // host calls have synchronised
     return ok ? ZA_OK : ZA_ERR_CUDA;
 }
 
@@ -449,7 +451,8 @@ ZA_API int za_gpu_sync(za_gpu_handle h)
 {
     if (!h) return ZA_ERR_ARG;
     cudaSetDevice(h->I.device);
-    return cuda_ok(cudaStreamSynchronize(h->I.stream), "sync") ? ZA_OK : ZA_ERR_CUDA;
+    if (!cuda_ok(cudaStreamSynchronize(h->I.stream), "sync")) return ZA_ERR_CUDA;
+    return h->I.impl && h->I.impl->deferred_error(h->I) ? ZA_ERR_STATE : ZA_OK;
 }
 ZA_API int za_gpu_launch_count(za_gpu_handle h, int64_t* n)
 {
@@ -481,6 +484,7 @@ ZA_API int za_gpu_set_option(za_gpu_handle h, const char* name, int value)
     else if (!std::strcmp(name, "host_chunk_frames")) I.opt_host_chunk = value;
     else if (!std::strcmp(name, "tile_buffers")) I.opt_nbuf = value;
     else if (!std::strcmp(name, "scalar_f32")) I.opt_scalar_f32 = value;
+    else if (!std::strcmp(name, "heap_slots")) I.opt_heap_slots = value;
     else { set_error(std::string("unknown option ") + name); return ZA_ERR_ARG; }
     return ZA_OK;
 }

@@ -65,6 +65,10 @@ public:
     // Device-side parameter path: the raw host float rows [nb][n_streams][n_decl] of the call are uploaded
     // and quantised + turned into @slider results by a kernel.  Returns 1 = done, 0 = not applicable for
     // this call (the caller falls back to the host path), -1 = error.
+    // A failure a kernel could only flag on the device (e.g. a translated leaf ran past its mem[] heap): true + error
+    // text if one has been seen.  Polled without synchronising at the start of every process call and after every
+    // synchronisation the C ABI performs, so the failure surfaces on that call or, for device-memory calls, on the next.
+    virtual bool deferred_error(Instance&) { return false; }
     virtual int run_blocks_raw(Instance&, const float*, int, const float*, float*, double*, int64_t, int64_t) { return 0; }
     virtual bool run_blocks(Instance&, int, int, const double*, int, const float*, float*, double*, int64_t, int64_t) { return false; }
 };
@@ -91,7 +95,7 @@ struct Instance {
     std::unique_ptr<PluginImpl> impl;
     int64_t launches = 0;
     // options
-    int opt_force_generic = 0, opt_warps = 0, opt_host_chunk = 0, opt_nbuf = 0, opt_scalar_f32 = 0;
+    int opt_force_generic = 0, opt_warps = 0, opt_host_chunk = 0, opt_nbuf = 0, opt_scalar_f32 = 0, opt_heap_slots = 0;
     // timing of the dominant kernel
     std::vector<cudaEvent_t> ev;             // pairs
     int ev_used = 0;
