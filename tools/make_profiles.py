@@ -6,15 +6,18 @@ REPO = Path(__file__).resolve().parent.parent
 G, P = REPO / "gpurun_out", REPO / "profiles"
 RND = "r01"
 CAPS = [
-    ("ee_v7", "easyexpander_split", "EasyExpander fp32 (`easyexpander_split_kernel`: band / filter / gain / helper warps)",
+    ("ee_v8", "easyexpander_split", "EasyExpander fp32 (`easyexpander_split_kernel`: band / filter / gain / helper warps)",
      "ncu --set full --clock-control none --import-source on -k regex:easyexpander_split -c 1 python tools/prof_run.py --plugin EasyExpander --streams 4096 --seconds 2 --reps 1",
      "4096 stereo streams x 96 000 frames; algorithmic bytes = 6.29 GB per launch"),
     ("stft_v4", "stft", "stft_mask2048 fp32 (`stft_mask_kernel<float,4>`)",
      "ncu --set full --clock-control none --import-source on -k regex:stft_mask -c 1 python tools/prof_run.py --plugin stft_mask2048 --streams 512 --seconds 4 --reps 1",
      "512 stereo streams x 192 000 frames; algorithmic bytes = 1.57 GB per launch"),
-    ("gen_rtt_v3", "generic_rtt", "translated leaf RTT fp32 (`jsfx_process_kernel<g_RTT::Script,float>`)",
+    ("gen_rtt_v4", "generic_rtt", "translated leaf RTT fp32 (`jsfx_process_kernel<g_RTT::Script,float>`)",
      "ncu --set full --clock-control none --import-source on -k regex:jsfx_process_kernel -c 1 python tools/prof_run.py --plugin RTT --streams 4096 --seconds 1 --reps 1",
      "4096 streams (8 in / 2 out) x 48 000 frames; algorithmic bytes = 7.86 GB per launch"),
+    ("gen_ss_v2", "generic_spectralstabilizer", "translated leaf SpectralStabilizer fp32 (`jsfx_process_kernel<g_SpectralStabilizer::Script,float>`), a mem[]-heavy band loop",
+     "ncu --set full --clock-control none --import-source on -k regex:jsfx_process_kernel -c 1 python tools/prof_run.py --plugin SpectralStabilizer --streams 4096 --seconds 0.5 --reps 1",
+     "4096 stereo streams x 24 000 frames; algorithmic bytes = 1.57 GB per launch"),
     ("c8_v3", "cascade8_x2_v3", "cascade8 fp32 (`cascade8_x2_kernel<2,1>`), re-captured at the end of the round",
      "ncu --set full --clock-control none --import-source on -k regex:cascade8_x2_kernel -c 1 python tools/prof_run.py --plugin cascade8 --streams 1024 --seconds 10 --reps 1",
      "1024 mono streams x 480 000 frames; algorithmic bytes = 3.93 GB per launch"),
@@ -39,6 +42,10 @@ def main():
                                                        "smsp__inst_executed.sum", "sm__throughput.avg.pct_of_peak_sustained_elapsed"))
         body = f"# Round 1: {title}, ncu --set full\n\nCommand (after the same command exited 0 without ncu):\n`{cmd}`\n({what}.)\n\n## Summary\n\n" + \
                "\n".join("    " + l for l in summ.splitlines()) + "\n\n" + extra + "\n\n## Source page (warp-stall samples)\n\n" + "\n".join("    " + l for l in src.splitlines()) + "\n"
+        if name == "easyexpander_split":
+            roles = sh(sys.executable, str(REPO / "tools/ncu_roles.py"), str(f))
+            body += "\n## Per warp role (tools/ncu_roles.py: SASS cut at every BAR.SYNC; a role's loop body = one segment, the short\nsegment after it = that role's wait at the batch barrier; order: band warps, filter warp, helper warps, gain warp)\n\n" + \
+                    "\n".join("    " + l for l in roles.splitlines()) + "\n"
         (P / f"{RND}_{name}_ncu.md").write_text(body)
         print("wrote", P / f"{RND}_{name}_ncu.md")
     # launch lists: our kernels only (-k filter), share of the dominant kernel inside the benched command
