@@ -295,7 +295,21 @@ __global__ void __launch_bounds__(32) jsfx_prepare_kernel(const GenLaunch a)
     ctx_close<S, R>(c, v, a, s, (R)1);
 }
 
-constexpr int kTileFrames = 32;      // frames per audio tile of jsfx_process_kernel (16 or 32)
+// CTA shape of jsfx_process_kernel: independent warps of 32 streams each.
+//  * Leaves without a mem[] heap and at most four channels: FOUR warps per CTA.  The warps of one CTA are spread over the
+//    SM's four schedulers, whereas single-warp CTAs were all placed on the same one (measured with RTT: solo time flat
+//    up to 2 warps per SM, then growing linearly -- 24.7 ms at 8192 streams, 72 ms at 37 888; with 4-warp CTAs flat up
+//    to 4 warps per SM).
+//  * Leaves WITH a heap: one warp per CTA.  Their hot heap lines (SpectralStabilizer: ~34 KB per warp) live in L1,
+//    which shares the SM's 228 KB with the audio tiles; four such warps on one SM thrash it (SpectralStabilizer
+//    8192 streams x 0.5 s: 113 ms in 1-warp CTAs, 245 ms in 4-warp CTAs).
+//  * Leaves with more than four channels (RTT, 8 inputs): one warp per CTA, because four warps' double-buffered
+//    32-frame tiles do not fit an SM and 16-frame tiles measured 35-45 % slower.
+template <class S> struct GenWarps { static constexpr int value = (S::kMemSlots == 0 && S::kCh <= 4) ? 4 : 1; };
+// Frames per audio tile: 32 (128-byte row segments).  16 (half the shared memory, two rows per copy instruction) was
+// measured too: RTT / ATTACK lose 35-45 % alone, SpectralStabilizer 5 %, ERBTilt 5 %, Roomalizer 16 %, and the mixed
+// cfg5 batch does not gain from the smaller tiles.
+template <class S> struct TileFrames { static constexpr int value = 32; };
 
 // 4-byte asynchronous global -> shared copy (LDGSTS); `ok` false = write zero without reading
 __device__ __forceinline__ void cp_async4(float* smem_dst, const float* gmem_src, bool ok)
@@ -306,16 +320,16 @@ __device__ __forceinline__ void cp_async4(float* smem_dst, const float* gmem_src
 }
 
 template <class S, typename R, bool TAP>
-__global__ void __launch_bounds__(32, 1) jsfx_process_kernel(const GenLaunch a)
+__global__ void __launch_bounds__(32 * GenWarps<S>::value, 1) jsfx_process_kernel(const GenLaunch a)
 {
     // Audio tiles, [2 buffers][kCh][32 streams][kF frames + 1]: the tile after the one being computed is already on
     // its way from HBM (cp.async), so the only warp of the SM does not sit out a DRAM latency per tile (ncu, profiles/
-    // r01_generic_rtt_ncu.md: 26 % of the samples were the tile-in stores waiting for their loads).  kF = 32 (128-byte
-    // row segments, one row per copy instruction) measured 25-50 % faster than kF = 16 (two rows per instruction, half
-    // the shared memory) on the short leaves, so it is the one built.
-    extern __shared__ float tiles[];
-    constexpr int kF = kTileFrames, kP = kF + 1, kTile = S::kCh * 32 * kP, kRows = 32 / kF;   // rows per copy instruction
-    const int lane = threadIdx.x, s0 = blockIdx.x * 32, s = s0 + lane;
+    // r01_generic_rtt_ncu.md: 26 % of the samples were the tile-in stores waiting for their loads).  kF: see TileFrames.
+    extern __shared__ float tiles_cta[];
+    constexpr int kF = TileFrames<S>::value, kP = kF + 1, kTile = S::kCh * 32 * kP, kRows = 32 / kF;   // rows per copy instruction
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, s0 = (blockIdx.x * GenWarps<S>::value + warp) * 32, s = s0 + lane;
+    if (s0 >= a.n_streams) return;                 // the warps of a CTA never synchronise with each other
+    float* const tiles = tiles_cta + warp * 2 * kTile;
     const bool live = s < a.n_streams;             // dead lanes only help move the audio tiles
     const int ns_cta = min(32, a.n_streams - s0);
     const int half = lane / kF, fl = lane % kF;    // tile I/O: kF lanes per row, lane = frame
@@ -406,11 +420,12 @@ template <class S> bool launch_prepare(const GenLaunch& a, int precision, cudaSt
 }
 template <class S> bool launch_process(const GenLaunch& a, int precision, cudaStream_t st)
 {
-    const int blocks = (a.n_streams + 31) / 32;
-    const size_t smem = (size_t)2 * S::kCh * 32 * (kTileFrames + 1) * sizeof(float);
+    constexpr int kGenWarps = GenWarps<S>::value;
+    const int blocks = (a.n_streams + 32 * kGenWarps - 1) / (32 * kGenWarps);
+    const size_t smem = (size_t)kGenWarps * 2 * S::kCh * 32 * (TileFrames<S>::value + 1) * sizeof(float);
     auto go = [&](auto kern) {
         if (smem > 48 * 1024 && !cuda_ok(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "jsfx_process_kernel smem attr")) return false;
-        kern<<<blocks, 32, smem, st>>>(a);
+        kern<<<blocks, 32 * kGenWarps, smem, st>>>(a);
         return cuda_ok(cudaGetLastError(), "jsfx_process_kernel launch");
     };
     if (precision) return a.tap ? go(jsfx_process_kernel<S, double, true>) : go(jsfx_process_kernel<S, double, false>);
@@ -470,6 +485,7 @@ template <class S, typename R> void emu_process(const GenLaunch& a)
 #define ZA_JSFX_DEFINE_PLUGIN(IDENT, KEY, MEM_SLOTS, HAS_BLOCK, HAS_SLIDER)                                            \
     struct Script {                                                                                                     \
         static constexpr int kVars = g_##IDENT::kVars, kIn = g_##IDENT::kIn, kOut = g_##IDENT::kOut, kCh = g_##IDENT::kCh, kDecl = g_##IDENT::kDecl; \
+        static constexpr long long kMemSlots = (MEM_SLOTS);                                                             \
         static constexpr int alias(int i0) { return g_##IDENT::alias_slot(i0); }                                        \
         static constexpr int decl(int j) { return g_##IDENT::decl_slot(j); }                                            \
         template <typename R> static void init(Rt<R>& c, R* v) { sec_init<R>(c, v); }                                   \
@@ -490,6 +506,7 @@ template <class S, typename R> void emu_process(const GenLaunch& a)
 #define ZA_JSFX_DEFINE_PLUGIN(IDENT, KEY, MEM_SLOTS, HAS_BLOCK, HAS_SLIDER)                                            \
     struct Script {                                                                                                     \
         static constexpr int kVars = g_##IDENT::kVars, kIn = g_##IDENT::kIn, kOut = g_##IDENT::kOut, kCh = g_##IDENT::kCh, kDecl = g_##IDENT::kDecl; \
+        static constexpr long long kMemSlots = (MEM_SLOTS);                                                             \
         static __host__ __device__ constexpr int alias(int i0) { return g_##IDENT::alias_slot(i0); }                    \
         static __host__ __device__ constexpr int decl(int j) { return g_##IDENT::decl_slot(j); }                        \
         template <typename R> static __device__ __forceinline__ void init(Rt<R>& c, R* v) { sec_init<R>(c, v); }       \
