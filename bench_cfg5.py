@@ -7,8 +7,8 @@ run (streams / N per GPU, strong scaling over a fixed batch is NOT what is measu
 65,536 / N streams, so the whole-job batch is fixed and `scaling` is "strong").  One step = one 1 s time chunk
 of every stream (the 10 min bounce is 600 such chunks with state carried; inputs are generated on the device
 per leaf, outside the timed region, and reused).  Every leaf has its own handle and CUDA stream, so the eight
-kernels of a step overlap on the device (launch order and stream priorities: see LEAVES below); the step is timed
-with CUDA events bracketing all of them.
+kernels of a step overlap on the device inside the two phases described at LEAVES below; the step is timed with
+CUDA events bracketing all of them.
 """
 from __future__ import annotations
 
@@ -22,14 +22,15 @@ import numpy as np
 
 REPO = Path(__file__).resolve().parent
 SRATE = 48000.0
-# Schedule of one step: every leaf on its own CUDA stream, launched longest kernel first (the translated leaves hold
-# their SM slots for the whole launch, so the two long ones must not queue behind short ones).  The hand-written kernels
-# take milliseconds but each of their CTAs needs a whole SM (shared-memory tiles), so their streams get the highest
-# priority: when an SM drains they go first instead of starving behind the next step's long kernels.  Measured
-# alternatives (B200, ms per step): catalog order without priorities 578; longest first 510; + priorities 479; two
-# phases (hand-written leaves, then the translated ones) 669-721.
-LEAVES = ["SpectralStabilizer", "ERBTilt", "SOMA", "RTT", "ATTACK", "stft_mask2048", "EasyExpander", "cascade8"]
-PRIORITY = {"stft_mask2048": -3, "EasyExpander": -3, "cascade8": -3, "SpectralStabilizer": -2, "ERBTilt": -2, "SOMA": -1}
+# Schedule of one step, two phases, every leaf on its own CUDA stream inside a phase:
+#   A: the hand-written leaves and the heap-less translated leaves (RTT, ATTACK) -- short kernels with big shared-memory
+#      tiles;
+#   B: the translated leaves that keep their state in a mem[] heap (SpectralStabilizer, ERBTilt, SOMA) -- long kernels
+#      that live off the L1.  Shared memory is carved out of the same 228 KB as the L1, so while phase-A kernels are
+#      resident on an SM the heap leaves' lines are evicted (measured: SpectralStabilizer / ERBTilt 3x slower inside a
+#      free-for-all mix, 600-650 ms per step; catalog order 578, longest first 510, + stream priorities 479-646).
+LEAVES = ["stft_mask2048", "EasyExpander", "cascade8", "RTT", "ATTACK", "SpectralStabilizer", "ERBTilt", "SOMA"]
+PHASE_B = {"SpectralStabilizer", "ERBTilt", "SOMA"}
 NOT_BUILT = ["VAR", "ModTilt", "ClickBeGoneSG", "GTS", "RED"]
 TOTAL_STREAMS = 65536
 
@@ -68,7 +69,7 @@ def main(args):
     for li, key in enumerate(LEAVES):
         info = za_gpu.plugin_info(key)
         W = dict(plugin=key, ch=(info.n_in, info.n_out))
-        st = torch.cuda.Stream(priority=PRIORITY.get(key, 0))
+        st = torch.cuda.Stream()
         bp = za_gpu.BatchProcessor(key, per_leaf, SRATE, 512, prec, local)
         bp.set_stream(st.cuda_stream)
         p = wl.default_params(key, per_leaf, first_stream=rank * per_leaf)
@@ -80,9 +81,22 @@ def main(args):
         frames += per_leaf * nf
     torch.cuda.synchronize()
 
+    sa = [j[2] for j in jobs if j[0] not in PHASE_B]
+    sb = [j[2] for j in jobs if j[0] in PHASE_B]
+
     def step():
-        for _, bp, _, x, y, _ in jobs:
-            bp.process(x, out=y)
+        for a_ in sa:                                # phase A starts when the previous step's phase B is done
+            for b_ in sb:
+                a_.wait_stream(b_)
+        for key, bp, _, x, y, _ in jobs:
+            if key not in PHASE_B:
+                bp.process(x, out=y)
+        for b_ in sb:                                # phase B
+            for a_ in sa:
+                b_.wait_stream(a_)
+        for key, bp, _, x, y, _ in jobs:
+            if key in PHASE_B:
+                bp.process(x, out=y)
 
     def fence(ev_stream):
         for _, _, st, _, _, _ in jobs:          # the timing stream waits for every leaf's stream
@@ -163,7 +177,7 @@ def main(args):
                                f"({', '.join(LEAVES)}), one step = a {sec:g} s time chunk of every stream (the 10 min bounce = 600 chunks, state carried)",
                    "leaves_not_built": NOT_BUILT, "streams_per_gpu": per_leaf * len(LEAVES), "streams_per_leaf_per_gpu": per_leaf,
                    "frames_per_stream_per_step": nf, "block_len": 512, "l2": "inputs (%.1f GB per step per GPU) larger than L2" % (alg_bytes / 2e9),
-                   "parallelism": f"streams sharded x{world}, one CUDA stream per leaf (longest kernel first, hand-written leaves at high stream priority)"},
+                   "parallelism": f"streams sharded x{world}; per step two phases (hand-written + heap-less leaves, then the mem[]-heap leaves), one CUDA stream per leaf inside a phase"},
         "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
         "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "peak_source": peak_kind,
                      "traffic": None, "kernel": "all leaves' kernels of one step, overlapped", "kernel_ms_per_launch": ms,

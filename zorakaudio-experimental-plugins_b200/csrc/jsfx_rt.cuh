@@ -425,6 +425,11 @@ template <class S> bool launch_process(const GenLaunch& a, int precision, cudaSt
     const size_t smem = (size_t)kGenWarps * 2 * S::kCh * 32 * (TileFrames<S>::value + 1) * sizeof(float);
     auto go = [&](auto kern) {
         if (smem > 48 * 1024 && !cuda_ok(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "jsfx_process_kernel smem attr")) return false;
+        // Leaves with a heap live off the L1 (their hot mem[] lines; SpectralStabilizer ~34 KB per warp).  Left alone, the
+        // driver sizes the shared-memory carve-out for the 8 CTAs per SM the register file allows (164 KB), which leaves
+        // 64 KB of L1: fine for 2 warps per SM, thrashing beyond (ncu at 16 384 streams: L1 hit rate 98.8 % -> 89.8 %,
+        // long_scoreboard 2 % -> 31 %, 2.3x the time per frame).  Ask for a 100 KB carve-out instead: 5 CTAs per SM, 128 KB L1 (64 KB / 3 CTAs measured too: see DESIGN.md 4.5).
+        if (S::kMemSlots > 0 && !cuda_ok(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 44), "jsfx_process_kernel carve-out")) return false;
         kern<<<blocks, 32 * kGenWarps, smem, st>>>(a);
         return cuda_ok(cudaGetLastError(), "jsfx_process_kernel launch");
     };
