@@ -23,10 +23,10 @@ timeout 500 ncu --set full --clock-control none --import-source on -k regex:easy
   python tools/prof_run.py --plugin EasyExpander --streams 4096 --seconds 2 --reps 1 > gpurun_out/ncu_ee.log 2>&1
 timeout 500 ncu --set full --clock-control none --import-source on -k regex:stft_mask -c 1 -f -o gpurun_out/r01_stft_v4 \
   python tools/prof_run.py --plugin stft_mask2048 --streams 512 --seconds 4 --reps 1 > gpurun_out/ncu_stft.log 2>&1
-timeout 500 ncu --set full --clock-control none --import-source on -k regex:jsfx_process_kernel -c 1 -f -o gpurun_out/r01_gen_rtt_v5 \
+timeout 500 ncu --set full --clock-control none --import-source on -k regex:jsfx_process_kernel -c 1 -f -o gpurun_out/r01_gen_rtt_v6 \
   python tools/prof_run.py --plugin RTT --streams 4096 --seconds 1 --reps 1 > gpurun_out/ncu_rtt.log 2>&1
 timeout 500 ncu --set full --clock-control none --import-source on -k regex:cascade8_x2_kernel -c 1 -f -o gpurun_out/r01_c8_v3 \
   python tools/prof_run.py --plugin cascade8 --streams 1024 --seconds 10 --reps 1 > gpurun_out/ncu_c8.log 2>&1
 cat gpurun_out/smoke.log gpurun_out/tests.log gpurun_out/gen_times.log; for f in gpurun_out/bench_*.json; do echo "== $f"; cut -c1-300 $f; done; tail -3 gpurun_out/bench_cfg5.err
-timeout 600 ncu --set full --clock-control none --import-source on -k regex:jsfx_process_kernel -c 1 -f -o gpurun_out/r01_gen_ss_v3 \
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:jsfx_process_kernel -c 1 -f -o gpurun_out/r01_gen_ss_v4 \
   python tools/prof_run.py --plugin SpectralStabilizer --streams 4096 --seconds 0.5 --reps 1 > gpurun_out/ncu_ss.log 2>&1

@@ -12,10 +12,10 @@ CAPS = [
     ("stft_v4", "stft", "stft_mask2048 fp32 (`stft_mask_kernel<float,4>`)",
      "ncu --set full --clock-control none --import-source on -k regex:stft_mask -c 1 python tools/prof_run.py --plugin stft_mask2048 --streams 512 --seconds 4 --reps 1",
      "512 stereo streams x 192 000 frames; algorithmic bytes = 1.57 GB per launch"),
-    ("gen_rtt_v5", "generic_rtt", "translated leaf RTT fp32 (`jsfx_process_kernel<g_RTT::Script,float>`)",
+    ("gen_rtt_v6", "generic_rtt", "translated leaf RTT fp32 (`jsfx_process_kernel<g_RTT::Script,float>`)",
      "ncu --set full --clock-control none --import-source on -k regex:jsfx_process_kernel -c 1 python tools/prof_run.py --plugin RTT --streams 4096 --seconds 1 --reps 1",
      "4096 streams (8 in / 2 out) x 48 000 frames; algorithmic bytes = 7.86 GB per launch"),
-    ("gen_ss_v3", "generic_spectralstabilizer", "translated leaf SpectralStabilizer fp32 (`jsfx_process_kernel<g_SpectralStabilizer::Script,float>`), a mem[]-heavy band loop",
+    ("gen_ss_v4", "generic_spectralstabilizer", "translated leaf SpectralStabilizer fp32 (`jsfx_process_kernel<g_SpectralStabilizer::Script,float>`), a mem[]-heavy band loop",
      "ncu --set full --clock-control none --import-source on -k regex:jsfx_process_kernel -c 1 python tools/prof_run.py --plugin SpectralStabilizer --streams 4096 --seconds 0.5 --reps 1",
      "4096 stereo streams x 24 000 frames; algorithmic bytes = 1.57 GB per launch"),
     ("c8_v3", "cascade8_x2_v3", "cascade8 fp32 (`cascade8_x2_kernel<2,1>`), re-captured at the end of the round",
