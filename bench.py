@@ -49,6 +49,11 @@ WORKLOADS = {
     "cfg4": dict(plugin="stft_mask2048", streams=512, seconds=120.0, ch=(2, 2), automate=None, cpu=(64, 10.0),
                  kernel={"f32": "stft_mask_kernel", "f64": "stft_mask_kernel"},
                  text="cfg4: stft_mask2048 (2048-pt Hann STFT, hop 512, per-bin gain, overlap-add), {ns} stereo streams x {sec:g} s @ 48 kHz per GPU"),
+    # cfg3's shape on the Faust leaf of the Dynamics category (float32 only; CPU side = the restatement, parity unpinned)
+    "modtilt": dict(plugin="ModTilt", streams=4096, seconds=60.0, ch=(2, 2), automate=[0], cpu=(512, 20.0), f32_only=True,
+                    kernel={"f32": "modtilt_kernel"},
+                    text="cfg3 shape on the Faust leaf ModTilt (envelope tilt shaper: 5 one-poles + sqrt/div/log10/10^x per frame), "
+                         "{ns} stereo streams x {sec:g} s @ 48 kHz per GPU, tilt automated every 512-frame block, in-place buffers"),
 }
 
 
@@ -158,7 +163,7 @@ def run_reference_arm(args, W):
     line = {
         "impl": "reference", "metric": "aggregate sample-frames/s", "value": v, "unit": "frames/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": float(np.mean([d for _, d in vals]) * 1e3),
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32" if W.get("f32_only") else "f64", "data": "synthetic",
         "x_realtime": v / SRATE,
         "config": {"workload": workload_text(W, W["streams"], W["seconds"]), "sample": sample},
         "cpu_baseline": {"value": v, "unit": "frames/s", "cores": threads, "kind": kind, "sample": sample},
@@ -260,7 +265,9 @@ def main():
     y = x if inplace else torch.empty((ns, n_out, nf), dtype=torch.float32, device="cuda")
 
     results = {}
-    precs = [args.precision] + (["f64"] if args.precision == "f32" and not args.no_f64 else [])
+    if W.get("f32_only") and args.precision != "f32":
+        raise SystemExit(f"{args.workload}: float32 only (Faust leaf)")
+    precs = [args.precision] + (["f64"] if args.precision == "f32" and not args.no_f64 and not W.get("f32_only") else [])
     for prec in precs:
         headline = prec == args.precision
         bp = za_gpu.BatchProcessor(W["plugin"], ns, SRATE, 512, prec, local)

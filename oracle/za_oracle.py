@@ -172,6 +172,12 @@ CATALOG_SLIDERS = {
         "slider3:contour=50<0,100,1>Contour (0=gentle, 100=hard)\n"
         "slider4:det_hpf_hz=0<0,20000,1:log=1000>Detector HPF (Hz, 0=Off)\n"
         "slider5:det_lpf_hz=20000<20,20000,1:log=1000>Detector LPF (Hz, 20k=Off)\n"),
+    # Faust leaf: hslider(label, init, min, max, step) in buildUserInterface order (ModTilt.dsp:9-19), written in the
+    # slider-line form the library's parameter API uses
+    "ModTilt": (
+        "slider1:tilt_db=0<-6,3,0.1>Tilt (dB)\n"
+        "slider2:pivot_hz=3<2,5,0.01>Pivot (Hz)\n"
+        "slider3:mix=1<0,1,0.001>Mix\n"),
 }
 
 
@@ -242,8 +248,22 @@ def have_ref(key: str) -> bool:
 PORT_SO = HERE / "libza_oracle_port.so"
 
 
+FAUST_PORT_SO = HERE / "libza_faust_port.so"
+FAUST_KEYS = ("ModTilt",)            # Faust leaves: restatement only (parity unpinned, see za_faust_port.c)
+
+
+def build_faust_port(force: bool = False) -> Path:
+    import subprocess
+    src = HERE / "za_faust_port.c"
+    if force or not FAUST_PORT_SO.exists() or FAUST_PORT_SO.stat().st_mtime < src.stat().st_mtime:
+        subprocess.run(["gcc", "-O2", "-fPIC", "-shared", "-fvisibility=hidden", "-ffp-contract=off",
+                        str(src), "-o", str(FAUST_PORT_SO), "-lm", "-lpthread"], check=True)
+    return FAUST_PORT_SO
+
+
 def build_port(force: bool = False) -> Path:
     import subprocess
+    build_faust_port(force)
     src = HERE / "za_oracle_port.c"
     if force or not PORT_SO.exists() or PORT_SO.stat().st_mtime < src.stat().st_mtime:
         subprocess.run(["gcc", "-O2", "-fPIC", "-shared", "-fvisibility=hidden", "-ffp-contract=off",
@@ -254,11 +274,11 @@ def build_port(force: bool = False) -> Path:
 class PortPlugin:
     """Plain-C restatement of one plugin; same render() contract as RefPlugin."""
 
-    CHANNELS = {"cascade8": (1, 1), "EasyExpander": (2, 2), "stft_mask2048": (2, 2)}
+    CHANNELS = {"cascade8": (1, 1), "EasyExpander": (2, 2), "stft_mask2048": (2, 2), "ModTilt": (2, 2)}
 
     def __init__(self, key: str, sliders=None, var_index=None):
         self.key = key
-        self.lib = C.CDLL(str(build_port()))
+        self.lib = C.CDLL(str(build_faust_port() if key in FAUST_KEYS else build_port()))
         self.fn = getattr(self.lib, f"zo_{key.lower()}_render")
         self.fn.argtypes = [C.POINTER(SliderLayout), C.c_double, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
                             C.c_void_p, C.c_int, C.c_int64, C.c_int64, C.c_int, C.c_int]
@@ -280,6 +300,14 @@ class PortPlugin:
                      yd.ctypes.data if want_f64 else None, ns, nf, nf, block, th)
         assert rc == 0
         return y, yd
+
+    def coefs(self, srate, *zone_values):
+        """Slider-rate values of a Faust leaf for given zone values (tests of the product's host half)."""
+        fn = getattr(self.lib, f"zo_{self.key.lower()}_coefs")
+        out = np.zeros(8, np.float32)
+        fn.argtypes = [C.c_double] + [C.c_float] * len(zone_values) + [C.c_void_p]
+        fn(srate, *map(float, zone_values), out.ctypes.data)
+        return out
 
 
 def best_oracle(key: str):

@@ -64,6 +64,7 @@ bool make_chunk_tensor_map(CUtensorMap* map, const float* base, int64_t n_chunks
 const char* cascade8_slider_text();
 const char* easyexpander_slider_text();
 const char* stft_mask2048_slider_text();
+const char* modtilt_slider_text();
 
 void append_generated_plugins(std::vector<PluginDesc>& t);    // p_generic.cu: the translated DSP-JSFX leaves
 
@@ -74,6 +75,7 @@ const std::vector<PluginDesc>& plugin_table()
             {"cascade8", 1, 1, 2, 0, cascade8_slider_text(), &make_cascade8},
             {"EasyExpander", 2, 2, 0, 0, easyexpander_slider_text(), &make_easyexpander},
             {"stft_mask2048", 2, 2, 2, 2048, stft_mask2048_slider_text(), &make_stft_mask2048},
+            {"ModTilt", 2, 2, 1, 0, modtilt_slider_text(), &make_modtilt},
         };
         append_generated_plugins(v);
         return v;

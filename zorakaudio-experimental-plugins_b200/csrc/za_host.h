@@ -113,5 +113,6 @@ struct Instance {
 PluginImpl* make_cascade8();
 PluginImpl* make_easyexpander();
 PluginImpl* make_stft_mask2048();
+PluginImpl* make_modtilt();
 
 }  // namespace za

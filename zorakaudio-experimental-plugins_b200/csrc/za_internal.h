@@ -92,6 +92,22 @@ struct StftArgs {
 size_t stft_state_bytes();
 bool stft_launch(const StftArgs& a, int precision, int n_sm, cudaStream_t stream);
 
+// ---- ModTilt (Faust leaf, float32; plugins/Dynamics/ModTilt/src/ModTilt.dsp) ---------------------------------------
+constexpr int kMTState = 5;      // per stream: the five onepole() states env2, base, lp_piv, ratio, mean_rdb; [var][stream] float
+struct alignas(16) MTCoef {      // slider-rate values of one stream for one compute() call (ModTilt.dsp:37,44-45,17-19)
+    float a_piv, na_piv, g_lo, g_hi, mix, nmix, pad0, pad1;
+};
+struct MTArgs {
+    const float* in; float* out;                   // [stream][2][row_stride]
+    int64_t row_stride, n_frames;
+    int n_streams, block_len, n_coef_blocks;
+    const MTCoef* coef;                            // [n_coef_blocks][n_streams]
+    float* state;                                  // [kMTState][n_streams]
+    float a_env, a_base, a_trim;                   // sample-rate constants (:35-36,40)
+};
+int modtilt_pick_lanes(int n_streams, int n_sm);   // streams per warp: 8, 16 or 32
+bool modtilt_launch(const MTArgs& a, int lanes, cudaStream_t stream);
+
 // ---- translated DSP-JSFX leaves (csrc/gen/g_*.cu from za_gpu/jsfxc.py, runtime in jsfx_rt.cuh) -------------------
 struct GenLaunch {
     const float* in; float* out; double* tap;      // [stream][ch][row_stride]
