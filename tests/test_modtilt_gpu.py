@@ -115,3 +115,24 @@ def test_f64_refused(gpu):
     with pytest.raises(Exception) as e:
         gpu.BatchProcessor("ModTilt", 4, precision="f64")
     assert "float32" in str(e.value)
+
+
+def test_device_parameter_path_equals_host_path(gpu, port):
+    """Automation rows go through the device quantiser + host-built tables by default; `force_generic_io` takes the
+    host quantiser + host libm per row.  Same grid index, same table entry -> identical output bits."""
+    ns, nf, block = 50, 24000 + 3, 64
+    nb = (nf + block - 1) // block
+    x = wl.programme_bursts(ns, nf)
+    p = wl.automation(port.sliders, nb, ns, which=[0, 1, 2], base=np.array([-3.0, 3.0, 0.7], np.float32))
+    rng = np.random.default_rng(5)
+    p[::7] += rng.uniform(-8, 8, p[::7].shape).astype(np.float32)          # out-of-range and off-grid host values
+    outs = []
+    for force in (0, 1):
+        bp = gpu.BatchProcessor("ModTilt", ns, 48000.0, block, "f32")
+        bp.set_option("force_generic_io", force)
+        bp.prepare(p[0])
+        outs.append(bp.process(x, params=p))
+        bp.close()
+    assert np.array_equal(outs[0], outs[1])
+    y, _ = port.render(p, x, block=block)
+    assert dbfs_rms(outs[0].astype(np.float64) - y) < -100.0

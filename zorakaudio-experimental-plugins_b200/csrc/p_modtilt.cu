@@ -38,7 +38,38 @@ void modtilt_slow(const double* q, float fs, MTCoef& c)
     c.pad0 = c.pad1 = 0.0f;
 }
 
+// ---- device-side parameter path -----------------------------------------------------------------------------------
+// A slider's quantised value is min + k * step for an integer k (the host grid, za_params.cpp): the slider-rate
+// expressions are tabulated on the host with the host libm for every k, and a kernel maps the raw host floats of a
+// whole automation trajectory to k with the quantiser's own double arithmetic (clamp, llround((v - min) / step)) and
+// copies the table entries into coefficient rows.  Same bits as the host path, no per-row exp / pow on host cores.
+struct MTGrid { double mn[3], mx[3], step[3]; int n[3]; };
+
+__global__ void modtilt_param_kernel(const float* __restrict__ raw, MTCoef* __restrict__ coef, size_t rows, MTGrid g,
+                                     const float2* __restrict__ t_tilt, const float2* __restrict__ t_piv, const float2* __restrict__ t_mix)
+{
+    for (size_t r = (size_t)blockIdx.x * blockDim.x + threadIdx.x; r < rows; r += (size_t)gridDim.x * blockDim.x) {
+        int k[3];
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+            double v = (double)raw[r * 3 + j];
+            v = v < g.mn[j] ? g.mn[j] : (v > g.mx[j] ? g.mx[j] : v);
+            long long q = llround(__ddiv_rn(__dsub_rn(v, g.mn[j]), g.step[j]));
+            k[j] = (int)(q < 0 ? 0 : (q > g.n[j] - 1 ? g.n[j] - 1 : q));
+        }
+        const float2 a = t_tilt[k[0]], b = t_piv[k[1]], c = t_mix[k[2]];
+        float4* o = reinterpret_cast<float4*>(coef + r);
+        o[0] = make_float4(b.x, b.y, a.x, a.y);        // a_piv, na_piv, g_lo, g_hi
+        o[1] = make_float4(c.x, c.y, 0.f, 0.f);        // mix, nmix
+    }
+}
+
 class ModTilt : public PluginImpl {
+    float* d_raw = nullptr; size_t raw_cap = 0;
+    float2* d_tab = nullptr;                          // tilt | pivot | mix tables
+    MTGrid grid{};
+    bool grid_ok = false;
+
     float* d_state = nullptr;
     MTCoef* d_coef = nullptr;
     size_t coef_cap = 0;
@@ -48,7 +79,72 @@ class ModTilt : public PluginImpl {
     float fs = 48000.0f;
 
 public:
-    ~ModTilt() override { cudaFree(d_state); cudaFree(d_coef); }
+    ~ModTilt() override { cudaFree(d_state); cudaFree(d_coef); cudaFree(d_raw); cudaFree(d_tab); }
+
+    bool build_tables(Instance& I)
+    {
+        std::vector<float2> tab;
+        for (int j = 0; j < 3; ++j) {
+            const SliderDecl& d = I.decls[j];
+            grid.mn[j] = (double)d.min; grid.mx[j] = (double)d.max; grid.step[j] = (double)d.step;
+            if (!(d.step > 0.0f) || d.is_choice) return true;                  // no grid: host path only
+            const long long n = llround((grid.mx[j] - grid.mn[j]) / grid.step[j]) + 2;
+            if (n > (1 << 20)) return true;
+            grid.n[j] = (int)n;
+            for (long long k = 0; k < n; ++k) {
+                // every k the device can produce equals llround((v - min) / step) of a clamped v, so this is the
+                // quantiser's own second half (za_params.cpp / JSFXJuceProcessor.cpp:5583-5594)
+                double v = grid.mn[j] + (double)k * grid.step[j];
+                v = v < grid.mn[j] ? grid.mn[j] : (v > grid.mx[j] ? grid.mx[j] : v);
+                double q[3] = {0.0, 3.0, 1.0};
+                q[j] = v;
+                MTCoef c; modtilt_slow(q, fs, c);
+                tab.push_back(j == 0 ? make_float2(c.g_lo, c.g_hi) : j == 1 ? make_float2(c.a_piv, c.na_piv) : make_float2(c.mix, c.nmix));
+            }
+        }
+        if (!cuda_ok(cudaMalloc(&d_tab, tab.size() * sizeof(float2)), "modtilt tables") ||
+            !cuda_ok(cudaMemcpy(d_tab, tab.data(), tab.size() * sizeof(float2), cudaMemcpyHostToDevice), "modtilt tables upload")) return false;
+        grid_ok = true;
+        return true;
+    }
+
+    int run_blocks_raw(Instance& I, const float* params, int nbq, const float* in, float* out, double* tap,
+                       int64_t n, int64_t stride) override
+    {
+        if (!grid_ok || tap || I.opt_force_generic) return 0;      // "force_generic_io": the host parameter path (tests compare the two)
+        const size_t rows = (size_t)nbq * I.n_streams;
+        if (rows > raw_cap) {
+            cudaFree(d_raw); d_raw = nullptr; raw_cap = 0;
+            if (!cuda_ok(cudaMalloc(&d_raw, rows * 3 * sizeof(float)), "modtilt raw params")) return -1;
+            raw_cap = rows;
+        }
+        if (rows > coef_cap) {
+            cudaFree(d_coef); d_coef = nullptr; coef_cap = 0;
+            if (!cuda_ok(cudaMalloc(&d_coef, rows * sizeof(MTCoef)), "modtilt coef")) return -1;
+            coef_cap = rows;
+        }
+        coef_valid = false;
+        if (!cuda_ok(cudaMemcpyAsync(d_raw, params, rows * 3 * sizeof(float), cudaMemcpyHostToDevice, I.stream), "modtilt params upload")) return -1;
+        const unsigned blocks = (unsigned)std::min<size_t>((rows + 255) / 256, (size_t)n_sm * 8);
+        modtilt_param_kernel<<<blocks, 256, 0, I.stream>>>(d_raw, d_coef, rows, grid, d_tab, d_tab + grid.n[0], d_tab + grid.n[0] + grid.n[1]);
+        if (!cuda_ok(cudaGetLastError(), "modtilt param kernel")) return -1;
+        ++I.launches;
+        return launch(I, nbq, in, out, n, stride) ? 1 : -1;
+    }
+
+    bool launch(Instance& I, int nbq, const float* in, float* out, int64_t n, int64_t stride)
+    {
+        MTArgs a{};
+        a.in = in; a.out = out; a.row_stride = stride; a.n_frames = n;
+        a.n_streams = I.n_streams; a.block_len = I.block_len; a.n_coef_blocks = nbq; a.coef = d_coef; a.state = d_state;
+        a.a_env = a_from_hz(25.0f, fs); a.a_base = a_from_hz(1.0f, fs); a.a_trim = a_from_hz(0.2f, fs);   // :35-36,40
+        const int lanes = (I.opt_warps == 8 || I.opt_warps == 16 || I.opt_warps == 32) ? I.opt_warps : modtilt_pick_lanes(I.n_streams, n_sm);
+        const bool timed = I.time_begin();
+        if (!modtilt_launch(a, lanes, I.stream)) return false;
+        if (timed) I.time_end();
+        ++I.launches;
+        return true;
+    }
 
     bool create(Instance& I) override
     {
@@ -57,7 +153,8 @@ public:
         if (!cuda_ok(cudaGetDeviceProperties(&prop, I.device), "device properties")) return false;
         n_sm = prop.multiProcessorCount;
         fs = std::fmin(192000.0f, std::fmax(1.0f, (float)(int)I.srate));   // ma.SR
-        return cuda_ok(cudaMalloc(&d_state, (size_t)kMTState * I.n_streams * sizeof(float)), "modtilt state");
+        if (I.decls.size() != 3) { set_error("ModTilt: three parameters expected"); return false; }
+        return cuda_ok(cudaMalloc(&d_state, (size_t)kMTState * I.n_streams * sizeof(float)), "modtilt state") && build_tables(I);
     }
 
     bool reset(Instance& I) override   // mydsp::init -> instanceClear: every recursive signal starts at 0
@@ -103,16 +200,7 @@ public:
             coef_valid = h_coef.size() <= (1u << 20);
             if (coef_valid) h_coef_dev = h_coef;
         }
-        MTArgs a{};
-        a.in = in; a.out = out; a.row_stride = stride; a.n_frames = n;
-        a.n_streams = ns; a.block_len = I.block_len; a.n_coef_blocks = nbq; a.coef = d_coef; a.state = d_state;
-        a.a_env = a_from_hz(25.0f, fs); a.a_base = a_from_hz(1.0f, fs); a.a_trim = a_from_hz(0.2f, fs);   // :35-36,40
-        const int lanes = (I.opt_warps == 8 || I.opt_warps == 16 || I.opt_warps == 32) ? I.opt_warps : modtilt_pick_lanes(ns, n_sm);
-        const bool timed = I.time_begin();
-        if (!modtilt_launch(a, lanes, I.stream)) return false;
-        if (timed) I.time_end();
-        ++I.launches;
-        return true;
+        return launch(I, nbq, in, out, n, stride);
     }
 
     bool read_state(Instance& I, const char* name, double* out) override
