@@ -99,3 +99,28 @@ def test_library_lists_the_faust_leaf():
     lay = za_gpu.slider_layout("ModTilt")
     ref = zo.parse_sliders(zo.plugin_source_text("ModTilt"))
     assert [float(s.def_) for s in lay] == [s["default"] for s in ref] == [0.0, 3.0, 1.0]
+
+
+def test_kernel_arithmetic_on_host_equals_restatement(tmp_path):
+    """csrc/modtilt_core.h (the CUDA kernel's per-frame code) compiled by g++ with libm in place of the MUFU
+    approximations: same expression order as the restatement -> the same float output, except where the branch-free
+    square root rounds differently from sqrtf (a 1-ulp case about once in 10^7 operands)."""
+    import ctypes as C
+    import subprocess
+    from pathlib import Path
+    repo = Path(__file__).resolve().parent.parent
+    so = tmp_path / "libemu_modtilt.so"
+    subprocess.run(["g++", "-O2", "-std=c++17", "-ffp-contract=off", "-mfma", "-shared", "-fPIC",
+                    "-I" + str(repo / "zorakaudio-experimental-plugins_b200" / "csrc"), "-I/usr/local/cuda/include",
+                    str(repo / "tools" / "emu_modtilt.cpp"), "-o", str(so)], check=True)
+    emu = C.CDLL(str(so))
+    port = zo.PortPlugin("ModTilt")
+    ns, nf = 6, 48000
+    x = wl.programme_bursts(ns, nf)
+    p = np.array([[-6.0, 2.0, 1.0], [3.0, 5.0, 0.5], [-4.5, 3.0, 0.8], [-0.1, 2.01, 0.001], [1.5, 4.2, 0.25], [-6.0, 5.0, 0.0]], np.float32)
+    y, _ = port.render(p, x)
+    coef = np.stack([port.coefs(48000.0, *p[s]) for s in range(ns)]).astype(np.float32)
+    out = np.zeros_like(y)
+    emu.emu_modtilt_render(C.c_void_p(coef.ctypes.data), C.c_void_p(x.ctypes.data), C.c_void_p(out.ctypes.data), ns, C.c_long(nf))
+    assert np.mean(out == y) > 0.999
+    assert np.abs(out.astype(np.float64) - y).max() <= 1e-6 * np.abs(y).max()

@@ -5,7 +5,7 @@ mkdir -p gpurun_out
 timeout 600 python __graft_entry__.py smoke 2>&1 | tail -6 > gpurun_out/smoke12.log
 timeout 600 python -m pytest tests/test_modtilt_gpu.py -m gpu -q 2>&1 | tail -15 > gpurun_out/tests_modtilt.log
 rm -f gpurun_out/modtilt_sweep.log
-for cfg in "4096 10 8" "4096 10 16" "4096 10 32" "16384 4 0" "65536 2 0" "1024 10 8"; do
+for cfg in "4096 10 4" "4096 10 8" "4096 10 16" "4096 10 32" "16384 4 0" "65536 2 0" "65536 2 16" "1024 10 4"; do
   set -- $cfg
   echo "== streams $1 seconds $2 lanes $3: $(timeout 300 python tools/prof_run.py --plugin ModTilt --streams $1 --seconds $2 --reps 3 --warps $3 2>&1 | tail -1 | cut -c1-300)" >> gpurun_out/modtilt_sweep.log
 done
