@@ -3,7 +3,7 @@
 # line (+ reference arm), launch list of the benched command, one full ncu capture of the kernel.
 mkdir -p gpurun_out
 timeout 600 python __graft_entry__.py smoke 2>&1 | tail -6 > gpurun_out/smoke12.log
-timeout 600 python -m pytest tests/test_modtilt_gpu.py -m gpu -q 2>&1 | tail -15 > gpurun_out/tests_modtilt.log
+timeout 600 python -m pytest tests/test_zfaust_modtilt_gpu.py -m gpu -q 2>&1 | tail -15 > gpurun_out/tests_modtilt.log
 rm -f gpurun_out/modtilt_sweep.log
 for cfg in "4096 10 4" "4096 10 8" "4096 10 16" "4096 10 32" "16384 4 0" "65536 2 0" "65536 2 16" "1024 10 4"; do
   set -- $cfg
