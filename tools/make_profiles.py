@@ -18,6 +18,9 @@ CAPS = [
     ("gen_ss_v4", "generic_spectralstabilizer", "translated leaf SpectralStabilizer fp32 (`jsfx_process_kernel<g_SpectralStabilizer::Script,float>`), a mem[]-heavy band loop",
      "ncu --set full --clock-control none --import-source on -k regex:jsfx_process_kernel -c 1 python tools/prof_run.py --plugin SpectralStabilizer --streams 4096 --seconds 0.5 --reps 1",
      "4096 stereo streams x 24 000 frames; algorithmic bytes = 1.57 GB per launch"),
+    ("modtilt_v1", "modtilt", "Faust leaf ModTilt fp32 (`modtilt_kernel<8>`: one thread per stream, 8 streams per warp)",
+     "ncu --set full --clock-control none --import-source on -k regex:modtilt_kernel -c 1 python tools/prof_run.py --plugin ModTilt --streams 4096 --seconds 2 --reps 1",
+     "4096 stereo streams x 96 000 frames; algorithmic bytes = 6.29 GB per launch"),
     ("c8_v3", "cascade8_x2_v3", "cascade8 fp32 (`cascade8_x2_kernel<2,1>`), re-captured at the end of the round",
      "ncu --set full --clock-control none --import-source on -k regex:cascade8_x2_kernel -c 1 python tools/prof_run.py --plugin cascade8 --streams 1024 --seconds 10 --reps 1",
      "1024 mono streams x 480 000 frames; algorithmic bytes = 3.93 GB per launch"),
@@ -29,7 +32,10 @@ def sh(*a):
 
 
 def main():
+    only = sys.argv[1:]            # e.g. `make_profiles.py modtilt`: that capture / launch list / bench line only, others untouched
     for rep, name, title, cmd, what in CAPS:
+        if only and name not in only:
+            continue
         f = G / f"{RND}_{rep}.ncu-rep"
         if not f.exists():
             print("missing", f); continue
@@ -50,7 +56,7 @@ def main():
         print("wrote", P / f"{RND}_{name}_ncu.md")
     # launch lists: our kernels only (-k filter), share of the dominant kernel inside the benched command
     lines = []
-    for w in ("cfg2", "cfg3", "cfg4"):
+    for w in (only or ("cfg2", "cfg3", "cfg4")):
         f = G / f"launches_{w}.csv"
         if not f.exists():
             continue
@@ -70,10 +76,23 @@ def main():
         lines.append(f"{w}: {sum(n.values())} launches of our kernels, {tot:.2f} ms under ncu (cold-cache, serialised)")
         for k, val in agg.most_common(6):
             lines.append(f"    {k:60s} n={n[k]:3d}  {val:10.3f} ms  share {100 * val / tot:5.1f} %")
-    (P / f"{RND}_launch_shares.txt").write_text("\n".join(lines) + "\n")
+    if only:
+        with open(P / f"{RND}_launch_shares.txt", "a") as fh:
+            fh.write("\n".join(lines) + "\n")
+    else:
+        (P / f"{RND}_launch_shares.txt").write_text("\n".join(lines) + "\n")
     print("\n".join(lines))
     # bench lines
     out = {}
+    if only:
+        for w in only:
+            for tag in (w, "ref_" + w):
+                f = G / f"bench_{tag}.json"
+                if f.exists() and f.read_text().strip():
+                    out[tag] = json.loads(f.read_text().strip().splitlines()[-1])
+        (P / f"{RND}_bench_lines_{'_'.join(only)}.json").write_text(json.dumps(out, indent=1))
+        print("bench lines:", list(out))
+        return
     for w in ("ref_cfg2", "cfg2", "cfg3", "cfg4", "cfg5"):
         f = G / f"bench_{w}.json"
         if f.exists() and f.read_text().strip():
