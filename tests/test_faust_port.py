@@ -115,12 +115,16 @@ def test_kernel_arithmetic_on_host_equals_restatement(tmp_path):
                     str(repo / "tools" / "emu_modtilt.cpp"), "-o", str(so)], check=True)
     emu = C.CDLL(str(so))
     port = zo.PortPlugin("ModTilt")
-    ns, nf = 6, 48000
+    ns, nf = 6, 48000 + 5
     x = wl.programme_bursts(ns, nf)
     p = np.array([[-6.0, 2.0, 1.0], [3.0, 5.0, 0.5], [-4.5, 3.0, 0.8], [-0.1, 2.01, 0.001], [1.5, 4.2, 0.25], [-6.0, 5.0, 0.0]], np.float32)
     y, _ = port.render(p, x)
     coef = np.stack([port.coefs(48000.0, *p[s]) for s in range(ns)]).astype(np.float32)
     out = np.zeros_like(y)
-    emu.emu_modtilt_render(C.c_void_p(coef.ctypes.data), C.c_void_p(x.ctypes.data), C.c_void_p(out.ctypes.data), ns, C.c_long(nf))
+    emu.emu_modtilt_render(C.c_void_p(coef.ctypes.data), C.c_void_p(x.ctypes.data), C.c_void_p(out.ctypes.data), ns, C.c_long(nf), 0)
+    # the stage-by-stage 16-frame form the kernel runs inside a host block is the same arithmetic
+    out16 = np.zeros_like(y)
+    emu.emu_modtilt_render(C.c_void_p(coef.ctypes.data), C.c_void_p(x.ctypes.data), C.c_void_p(out16.ctypes.data), ns, C.c_long(nf), 1)
+    assert np.array_equal(out16, out)
     assert np.mean(out == y) > 0.999
     assert np.abs(out.astype(np.float64) - y).max() <= 1e-6 * np.abs(y).max()

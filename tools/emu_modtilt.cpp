@@ -8,7 +8,7 @@
 
 extern "C" __attribute__((visibility("default")))
 void emu_modtilt_render(const float* coef8 /* [ns][8]: a_env a_base a_trim a_piv g_hi g_lo mix fs */, const float* in, float* out,
-                        int n_streams, long n_frames)
+                        int n_streams, long n_frames, int use_run16)
 {
     _MM_SET_FLUSH_ZERO_MODE(_MM_FLUSH_ZERO_ON);
     _MM_SET_DENORMALS_ZERO_MODE(_MM_DENORMALS_ZERO_ON);
@@ -19,6 +19,12 @@ void emu_modtilt_render(const float* coef8 /* [ns][8]: a_env a_base a_trim a_piv
         za::MTRegs r{0.f, 0.f, 0.f, 0.f, 0.f};
         const float* xl = in + (size_t)s * 2 * n_frames; const float* xr = xl + n_frames;
         float* yl = out + (size_t)s * 2 * n_frames; float* yr = yl + n_frames;
-        for (long i = 0; i < n_frames; ++i) za::mt_frame(r, k, c, xl[i], xr[i], yl[i], yr[i]);
+        long i = 0;
+        if (use_run16)
+            for (; i + 16 <= n_frames; i += 16) {
+                for (int j = 0; j < 16; ++j) { yl[i + j] = xl[i + j]; yr[i + j] = xr[i + j]; }
+                za::mt_run16(r, k, c, yl + i, yr + i);
+            }
+        for (; i < n_frames; ++i) za::mt_frame(r, k, c, xl[i], xr[i], yl[i], yr[i]);
     }
 }
