@@ -18,7 +18,7 @@ CAPS = [
     ("gen_ss_v4", "generic_spectralstabilizer", "translated leaf SpectralStabilizer fp32 (`jsfx_process_kernel<g_SpectralStabilizer::Script,float>`), a mem[]-heavy band loop",
      "ncu --set full --clock-control none --import-source on -k regex:jsfx_process_kernel -c 1 python tools/prof_run.py --plugin SpectralStabilizer --streams 4096 --seconds 0.5 --reps 1",
      "4096 stereo streams x 24 000 frames; algorithmic bytes = 1.57 GB per launch"),
-    ("modtilt_v1", "modtilt", "Faust leaf ModTilt fp32 (`modtilt_kernel<8>`: one thread per stream, 8 streams per warp)",
+    ("modtilt_v2", "modtilt", "Faust leaf ModTilt fp32 (`modtilt_kernel<8>`: one thread per stream, 8 streams per warp, stage-by-stage 16-frame runs)",
      "ncu --set full --clock-control none --import-source on -k regex:modtilt_kernel -c 1 python tools/prof_run.py --plugin ModTilt --streams 4096 --seconds 2 --reps 1",
      "4096 stereo streams x 96 000 frames; algorithmic bytes = 6.29 GB per launch"),
     ("c8_v3", "cascade8_x2_v3", "cascade8 fp32 (`cascade8_x2_kernel<2,1>`), re-captured at the end of the round",
