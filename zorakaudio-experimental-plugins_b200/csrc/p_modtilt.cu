@@ -138,9 +138,11 @@ public:
         a.in = in; a.out = out; a.row_stride = stride; a.n_frames = n;
         a.n_streams = I.n_streams; a.block_len = I.block_len; a.n_coef_blocks = nbq; a.coef = d_coef; a.state = d_state;
         a.a_env = a_from_hz(25.0f, fs); a.a_base = a_from_hz(1.0f, fs); a.a_trim = a_from_hz(0.2f, fs);   // :35-36,40
-        const int lanes = (I.opt_warps == 4 || I.opt_warps == 8 || I.opt_warps == 16 || I.opt_warps == 32) ? I.opt_warps : modtilt_pick_lanes(I.n_streams, n_sm);
+        // option "warps_per_stream" = streams per warp (4 / 8 / 16 / 32) + 100 x frames per run (default 8; 4 / 16 / 32 are measurement variants)
+        const int ol = I.opt_warps % 100, run = I.opt_warps / 100 ? I.opt_warps / 100 : 8;
+        const int lanes = (ol == 4 || ol == 8 || ol == 16 || ol == 32) ? ol : modtilt_pick_lanes(I.n_streams, n_sm);
         const bool timed = I.time_begin();
-        if (!modtilt_launch(a, lanes, I.stream)) return false;
+        if (!modtilt_launch(a, lanes, I.stream, run)) return false;
         if (timed) I.time_end();
         ++I.launches;
         return true;

@@ -106,7 +106,7 @@ struct MTArgs {
     float a_env, a_base, a_trim;                   // sample-rate constants (:35-36,40)
 };
 int modtilt_pick_lanes(int n_streams, int n_sm);   // streams per warp: 8, 16 or 32
-bool modtilt_launch(const MTArgs& a, int lanes, cudaStream_t stream);
+bool modtilt_launch(const MTArgs& a, int lanes, cudaStream_t stream, int run = 8);   // run = frames per straight-line run
 
 // ---- translated DSP-JSFX leaves (csrc/gen/g_*.cu from za_gpu/jsfxc.py, runtime in jsfx_rt.cuh) -------------------
 struct GenLaunch {
