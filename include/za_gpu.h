@@ -27,6 +27,7 @@
 #ifndef ZA_GPU_H
 #define ZA_GPU_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -117,6 +118,11 @@ ZA_API int za_gpu_process_tap64(za_gpu_handle h, const float* param_block, int n
 ZA_API int za_gpu_read_state(za_gpu_handle h, const char* var_name, double* out);
 ZA_API int za_gpu_sync(za_gpu_handle h);
 
+/* Page-locked host buffers for ZA_MEM_HOST calls (the staged copies of za_gpu_process reach PCIe rate only from pinned
+ * memory).  Allocated on the calling thread's NUMA node: bind the thread to the GPU's node first on multi-socket boxes. */
+ZA_API int za_gpu_host_alloc(size_t bytes, void** out);
+ZA_API int za_gpu_host_free(void* p);
+
 /* ---- introspection for benches ------------------------------------------------------------- */
 ZA_API int za_gpu_launch_count(za_gpu_handle h, int64_t* kernels_launched);   /* our kernels, cumulative */
 /* Device time (ms, CUDA events on the handle's stream) of the dominant kernel launches of the
@@ -133,6 +139,21 @@ ZA_API int za_gpu_set_option(za_gpu_handle h, const char* name, int value);
  * process (host buffers, static parameters, 48 kHz, block 512, fp64) + destroy. */
 ZA_API int za_gpu_render(const char* plugin_key, const float* param_block, const float* in, float* out,
                          int n_streams, int64_t n_frames);
+
+/* ---- synthetic programme material + checksums ------------------- */
+/* Bench / sampled-parity tooling beside the render path: the inputs of a large bounce are generated ON THE DEVICE from a
+ * counter-based hash of (seed, first_stream + s, channel, t0 + frame), so no PCIe or host storage is on the path, and
+ * any stream can be regenerated on the CPU bit for bit (za_gpu/workloads.py::synth; integer hashing, two host-made
+ * tables, individually rounded float operations).  kind 0 = 0.25 x uniform noise + two sines (the cfg2 input),
+ * kind 1 = noise bursts under a -60 .. -6 dBFS piecewise-linear envelope (the cfg3 "programme-like" input).
+ * dev_out: device rows [stream][channel][frame_stride]; enqueued on cuda_stream (NULL = default), not synchronised. */
+ZA_API int za_gpu_synth(int kind, uint32_t seed, int first_stream, int n_streams, int n_ch, int64_t n_frames,
+                        int64_t frame_stride, int64_t t0, float* dev_out, int device, void* cuda_stream);
+ZA_API int za_gpu_synth_tables(float* sine4096, float* amp256);      /* the generator's two host tables (no GPU needed) */
+/* Per-row reduction of device rows: host_sum[r] = sum_i (bits(x[r][i]) + 1) * (mix32(i) | 1) mod 2^64 (order
+ * independent, bit-exact) and host_energy[r] = sum_i x^2 (double).  Synchronises cuda_stream. */
+ZA_API int za_gpu_checksum(const float* dev, int n_rows, int64_t n_frames, int64_t frame_stride, uint64_t* host_sum,
+                           double* host_energy, int device, void* cuda_stream);
 
 ZA_API const char* za_gpu_last_error(void);
 ZA_API int za_gpu_device_count(void);

@@ -238,6 +238,45 @@ class RefPlugin:
         return y, yd
 
 
+class RefInstance:
+    """ONE reference instance kept alive across prepare / process calls (zref_new / zref_prepare /
+    zref_process_block_f64 of oracle/ref_shim.c): what a host does when it calls prepareToPlay twice on a plugin."""
+
+    def __init__(self, ref: RefPlugin):
+        self.ref, L = ref, ref.lib
+        L.zref_process_block_f64.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int]
+        self.h = L.zref_new(C.byref(ref.layout))
+
+    def prepare(self, params, srate=48000.0):
+        p = np.ascontiguousarray(params, np.float32)
+        self.ref.lib.zref_prepare(self.h, srate, p.ctypes.data)
+
+    def process(self, params, x, block=512):
+        """params [n_sliders] or [n_blocks][n_sliders]; x [n_in][n_frames] -> (y f32, y f64) [n_out][n_frames]."""
+        x = np.ascontiguousarray(x, np.float32)
+        nch = max(self.ref.n_in, self.ref.n_out)
+        nf = x.shape[1]
+        p = np.ascontiguousarray(params, np.float32)
+        p = p[None] if p.ndim == 1 else p
+        y, yd = np.zeros((nch, nf), np.float32), np.zeros((nch, nf), np.float64)
+        xin = np.zeros((nch, nf), np.float32)
+        xin[:self.ref.n_in] = x
+        PF, PD = C.POINTER(C.c_float), C.POINTER(C.c_double)
+        for b, f0 in enumerate(range(0, nf, block)):
+            n = min(block, nf - f0)
+            ins = (PF * nch)(*[C.cast(xin[c, f0:].ctypes.data, PF) for c in range(nch)])
+            outs = (PF * nch)(*[C.cast(y[c, f0:].ctypes.data, PF) for c in range(nch)])
+            outd = (PD * nch)(*[C.cast(yd[c, f0:].ctypes.data, PD) for c in range(nch)])
+            row = p[min(b, len(p) - 1)]
+            self.ref.lib.zref_process_block_f64(self.h, row.ctypes.data, ins, outs, outd, nch, n)
+        return y[:self.ref.n_out], yd[:self.ref.n_out]
+
+    def close(self):
+        if self.h:
+            self.ref.lib.zref_free(self.h)
+            self.h = None
+
+
 def have_ref(key: str) -> bool:
     return (REF_DIR / f"libref_{key}.so").exists()
 

@@ -12,27 +12,10 @@ import pytest
 
 import za_oracle as zo
 from za_gpu import workloads as wl
+from parity import TOL64, block_peak, dbfs_rms, rel_err  # noqa: F401  (the one criterion definition, tests/parity.py)
 
 pytestmark = pytest.mark.gpu
 GOLD = Path(__file__).parent / "golden"
-TOL64 = 1e-12
-
-
-def block_peak(ref, block=512):
-    ns, nc, nf = ref.shape
-    nb = (nf + block - 1) // block
-    pad = np.zeros((ns, nc, nb * block))
-    pad[:, :, :nf] = np.abs(ref)
-    pk = pad.reshape(ns, nc, nb, block).max(axis=3)
-    return np.repeat(pk, block, axis=2)[:, :, :nf]
-
-
-def rel_err(got, ref):
-    return np.abs(got - ref) / np.maximum(np.maximum(np.abs(ref), block_peak(ref)), 1e-300)
-
-
-def dbfs_rms(r):
-    return 20 * np.log10(np.sqrt(np.mean(r ** 2)) + 1e-300)
 
 
 @pytest.fixture(scope="module")
@@ -142,4 +125,30 @@ def test_device_buffers_large_batch(gpu, ref):
     got = y[torch.from_numpy(gsel).cuda()].cpu().numpy()
     assert np.mean(got == yr) > 0.9999
     assert np.abs(got.astype(np.float64) - yr).max() <= 2.0 ** -22 * np.abs(yr).max()
+    bp.close()
+
+
+def test_fp32_split_kernel_at_bench_shape_sampled(gpu, ref):
+    """The fp32 split kernel at the cfg3 launch shape (4096 stereo streams -> 28 streams per CTA, device buffers, per-block
+    automation through the device parameter path), 2 s; 24 streams spread over the batch re-rendered by the reference:
+    residual of every sampled stream below -100 dBFS."""
+    torch = pytest.importorskip("torch")
+    ns, nf = 4096, 96000
+    x = torch.empty((ns, 2, nf), dtype=torch.float32, device="cuda")
+    gpu.synth_into(x, 1, 5000, 0)
+    nb = (nf + 511) // 512
+    k = 64
+    a = wl.automation(ref.sliders, nb, k, which=[0, 1])
+    p = np.ascontiguousarray(np.tile(a, (1, ns // k, 1)))
+    bp = gpu.BatchProcessor("EasyExpander", ns, precision="f32").prepare(p[0])
+    y = bp.process(x, params=p)
+    bp.sync()
+    pick = sorted(set(np.random.default_rng(11).choice(ns, 22, replace=False).tolist()) | {0, ns - 1})
+    xs = wl.synth(1, 5000, pick, 2, nf)
+    _, yd = ref.render(np.ascontiguousarray(p[:, pick]), xs, want_f64=True)
+    got = y[torch.tensor(pick).cuda()].cpu().numpy().astype(np.float64)
+    worst = max(dbfs_rms(got[i] - yd[i]) for i in range(len(pick)))
+    print("fp32 split kernel, 4096 streams: worst sampled stream residual %.1f dBFS" % worst)
+    assert worst < -100.0, worst
+    assert bp.last_kernel_ms()[1] >= 1
     bp.close()

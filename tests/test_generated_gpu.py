@@ -11,25 +11,11 @@ import pytest
 
 import za_oracle as zo
 from za_gpu import workloads as wl
+from parity import TOL64, block_peak, dbfs_rms, rel_err  # noqa: F401  (the one criterion definition, tests/parity.py)
 
 pytestmark = pytest.mark.gpu
 KEYS = ["RTT", "SOMA", "ATTACK", "ERBTilt", "SpectralStabilizer", "DDT", "DPT", "SaliencePush", "ADS", "BedRock",
         "Roomalizer", "TSEQ"]
-TOL64 = 1e-12
-
-
-def block_peak(ref, block=512):
-    ns, nc, nf = ref.shape
-    nb = (nf + block - 1) // block
-    pad = np.zeros((ns, nc, nb * block))
-    pad[:, :, :nf] = np.abs(ref)
-    pk = pad.reshape(ns, nc, nb, block).max(axis=3)
-    return np.repeat(pk, block, axis=2)[:, :, :nf]
-
-
-def rel_err(got, ref):
-    floor = np.maximum(block_peak(ref), 1e-3 * np.abs(ref).max(axis=2, keepdims=True))
-    return np.abs(got - ref) / np.maximum(np.maximum(np.abs(ref), floor), 1e-300)
 
 
 @pytest.fixture(scope="module")
@@ -50,7 +36,7 @@ def make_case(ref, ns, nf, automate, block=512):
     return p, x
 
 
-@pytest.mark.parametrize("key", KEYS)
+@pytest.mark.parametrize("key", KEYS + ["semprobe"])
 @pytest.mark.parametrize("automate", [False, True])
 def test_fp64_parity_and_state(gpu, key, automate):
     ref = zo.RefPlugin(key)
@@ -63,9 +49,11 @@ def test_fp64_parity_and_state(gpu, key, automate):
     tap = np.zeros_like(yd)
     out = bp.process(x, tap64=tap, params=p if p.ndim == 3 else None)
     e = rel_err(tap, yd).max()
-    # BedRock is ill conditioned: the reference's own compiled and interpreted paths differ by 1.1e-7 relative on it
-    # (SURVEY.md section 8c); device libm vs glibc last-bit differences reach a few 1e-12 there
-    assert e <= (1e-10 if key == "BedRock" else TOL64), e
+    # BedRock does NOT meet the 1e-12 criterion: measured floor 5.5e-12 on B200 (device libm vs glibc last-bit differences
+    # amplified by an ill-conditioned recursion; the reference's own compiled and interpreted paths differ by 1.1e-7
+    # relative on it).  Stated as such in README / DESIGN; asserted here at its measured floor x2.
+    print(f"FP64-PARITY {key}: {e:.2e}")
+    assert e <= (1.1e-11 if key == "BedRock" else TOL64), e
     assert np.mean(out == y) > 0.9999
     # every variable the reference holds: integer-valued ones exact, the rest to rounding of libm
     checked = 0
@@ -100,26 +88,28 @@ def test_split_calls_match_one_shot(gpu, key):
     bp.close()
 
 
-# float mode: leaves whose state is well conditioned in float meet the -100 dBFS criterion and are asserted; the
-# residual of the others (long phase / delay-position accumulators, threshold logic on float-rounded detectors) is
-# printed for the record and those leaves are listed as fp64-only in DESIGN.md.
-FP32_OK = set(KEYS) - {"DDT", "BedRock"}     # measured on B200: -104 .. -177 dBFS for the asserted ones, -50 / -53 for these two
+# float mode is offered only where it meets the -100 dBFS criterion; the two leaves that miss it (long phase / delay-position
+# accumulators: DDT -50 dBFS, BedRock -53 dBFS measured on B200) are REFUSED at create (ZA_ERR_UNSUPPORTED) instead of
+# rendering silently wrong.
+FP32_OK = set(KEYS) - {"DDT", "BedRock"}
 
 
 @pytest.mark.parametrize("key", KEYS)
 def test_fp32_mode_residual(gpu, key):
+    if key not in FP32_OK:
+        with pytest.raises(gpu.ZaError, match="ZA_F64"):
+            gpu.BatchProcessor(key, 8, precision="f32")
+        return
     ref = zo.RefPlugin(key)
     ns, nf = 8, 48000
     p, x = make_case(ref, ns, nf, False)
     y, yd = ref.render(p, x, want_f64=True)
     bp = gpu.BatchProcessor(key, ns, precision="f32").prepare(p)
     out = bp.process(x)
-    r = out.astype(np.float64) - yd
-    db = 20 * np.log10(np.sqrt(np.mean(r ** 2)) + 1e-300)
-    print(f"FP32-RESIDUAL {key}: {db:.1f} dBFS rms (asserted: {key in FP32_OK})")
+    db = dbfs_rms(out.astype(np.float64) - yd)
+    print(f"FP32-RESIDUAL {key}: {db:.1f} dBFS rms")
     assert np.isfinite(out).all()
-    if key in FP32_OK:
-        assert db < -100.0, db
+    assert db < -100.0, db
     bp.close()
 
 

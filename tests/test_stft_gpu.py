@@ -12,29 +12,10 @@ import pytest
 
 import za_oracle as zo
 from za_gpu import workloads as wl
+from parity import TOL64, block_peak, dbfs_rms, rel_err  # noqa: F401  (the one criterion definition, tests/parity.py)
 
 pytestmark = pytest.mark.gpu
 GOLD = Path(__file__).parent / "golden"
-TOL64 = 1e-12
-
-
-def block_peak(ref, block=512):
-    ns, nc, nf = ref.shape
-    nb = (nf + block - 1) // block
-    pad = np.zeros((ns, nc, nb * block))
-    pad[:, :, :nf] = np.abs(ref)
-    pk = pad.reshape(ns, nc, nb, block).max(axis=3)
-    return np.repeat(pk, block, axis=2)[:, :, :nf]
-
-
-def rel_err(got, ref):
-    # frames of silence in the reference (the first 2048 of latency) are compared against the stream peak
-    floor = np.maximum(block_peak(ref), 1e-3 * np.abs(ref).max(axis=2, keepdims=True))
-    return np.abs(got - ref) / np.maximum(np.maximum(np.abs(ref), floor), 1e-300)
-
-
-def dbfs_rms(r):
-    return 20 * np.log10(np.sqrt(np.mean(r ** 2)) + 1e-300)
 
 
 @pytest.fixture(scope="module")

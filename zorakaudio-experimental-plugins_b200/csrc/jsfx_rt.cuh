@@ -73,6 +73,12 @@ __device__ __forceinline__ float add_(float a, float b) { return __fadd_rn(a, b)
 __device__ __forceinline__ float sub_(float a, float b) { return __fsub_rn(a, b); }
 __device__ __forceinline__ float mul_(float a, float b) { return __fmul_rn(a, b); }
 __device__ __forceinline__ float div_(float a, float b) { return __fdividef(a, b); }      // fp32 mode: MUFU.RCP + FMUL (2 ulp), no slow-path call
+// Conditions and `!=` are ORDERED compares in the reference compiler (fcmp one: dsp_jsfx_aot.py:3725-3726 `_truthy`,
+// :4349-4352 `!=` -> "one"), so a NaN is false / compares "not different"; C++'s != is unordered (true on NaN).
+__device__ __forceinline__ bool truthy_(double x) { return x < 0.0 || x > 0.0; }
+__device__ __forceinline__ bool truthy_(float x) { return x < 0.0f || x > 0.0f; }
+__device__ __forceinline__ bool ne_(double a, double b) { return a < b || a > b; }
+__device__ __forceinline__ bool ne_(float a, float b) { return a < b || a > b; }
 __device__ __forceinline__ double pow_(double a, double b) { return pow(a, b); }
 __device__ __forceinline__ float pow_(float a, float b) { return powf(a, b); }
 

@@ -62,6 +62,14 @@ public:
 
     bool create(Instance& I) override
     {
+        // float32 mode is offered only where it meets the north_star criterion (residual below -100 dBFS against the
+        // reference render).  DDT and BedRock keep long phase / delay-position accumulators that lose it in float
+        // (-50 / -53 dBFS measured on B200, tests/test_generated_gpu.py), so ZA_F32 is refused for them.
+        if (I.precision == ZA_F32 && (!std::strcmp(d_->key, "DDT") || !std::strcmp(d_->key, "BedRock"))) {
+            set_error(std::string(d_->key) + ": float32 mode does not meet the -100 dBFS criterion for this leaf; create it with ZA_F64");
+            I.create_status = ZA_ERR_UNSUPPORTED;
+            return false;
+        }
         rsize = I.precision ? 8 : 4;
         const size_t ns = (size_t)I.n_streams;
         std::vector<int> idx;
@@ -78,11 +86,18 @@ public:
                cuda_ok(cudaMemcpy(d_index0, idx.data(), idx.size() * sizeof(int), cudaMemcpyHostToDevice), "slider index upload");
     }
 
-    bool reset(Instance& I) override   // resetStateStructOnly + zeroed heap, then sliders, @init, alias re-apply, @slider
+    bool heap_zeroed = false;
+    bool reset(Instance& I) override   // resetStateStructOnly, then sliders, @init, alias re-apply, @slider
     {
         const size_t ns = (size_t)I.n_streams;
+        // The heap is zero-filled when it is first allocated (jsfx_ensure_mem, JSFXJuceProcessor.cpp:1452-1491) and KEPT
+        // across prepareToPlay (resetStateStructOnly, :8972-8980, preserves st.mem / st.memN): a second prepare on a
+        // handle sees the delay lines the previous render left, exactly as the reference instance would.
+        if (!heap_zeroed) {
+            if (!cuda_ok(cudaMemsetAsync(d_mem, 0, (size_t)(d_->mem_slots + 1) * ns * rsize, I.stream), "heap reset")) return false;
+            heap_zeroed = true;
+        }
         if (!cuda_ok(cudaMemsetAsync(d_state, 0, (size_t)(d_->n_vars + 65) * ns * rsize, I.stream), "state reset") ||
-            !cuda_ok(cudaMemsetAsync(d_mem, 0, (size_t)(d_->mem_slots + 1) * ns * rsize, I.stream), "heap reset") ||
             !cuda_ok(cudaMemsetAsync(d_mt, 0, 625 * ns * sizeof(unsigned), I.stream), "rand reset") ||
             !cuda_ok(cudaMemsetAsync(d_err, 0, sizeof(int), I.stream), "err reset"))
             return false;

@@ -150,7 +150,7 @@ public:
 
     bool create(Instance& I) override
     {
-        if (I.precision != ZA_F32) { set_error("ModTilt: Faust leaves compute in float32 (no -double in the reference build); create it with ZA_F32"); return false; }
+        if (I.precision != ZA_F32) { set_error("ModTilt: Faust leaves compute in float32 (no -double in the reference build); create it with ZA_F32"); I.create_status = ZA_ERR_UNSUPPORTED; return false; }
         cudaDeviceProp prop;
         if (!cuda_ok(cudaGetDeviceProperties(&prop, I.device), "device properties")) return false;
         n_sm = prop.multiProcessorCount;

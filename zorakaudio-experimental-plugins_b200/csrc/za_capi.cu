@@ -230,6 +230,12 @@ static bool process_host(Instance& I, const float* params, int npb, const float*
             cudaEventCreateWithFlags(&I.ev_d2h[i], cudaEventDisableTiming);
         }
     }
+    // On any failure the copies already enqueued still target the caller's buffers: drain the three streams before
+    // returning, so `out` is never written after the call has reported its error.
+    struct Drain {
+        Instance& I; bool armed = true;
+        ~Drain() { if (armed) { cudaStreamSynchronize(I.h2d); cudaStreamSynchronize(I.stream); cudaStreamSynchronize(I.d2h); } }
+    } drain{I};
     int c = 0;
     for (int64_t f0 = 0; f0 < n_frames; f0 += cf, ++c) {
         const int64_t nf = std::min<int64_t>(cf, n_frames - f0);
@@ -246,7 +252,9 @@ static bool process_host(Instance& I, const float* params, int npb, const float*
         const float* p = nullptr;
         int np = 0;
         if (params && npb > 0 && b0 < npb) { p = params + (size_t)b0 * I.n_streams * nd; np = (int)(npb - b0); }
-        if (!process_range(I, p, np, 0, I.n_streams, I.stage_in[slot], I.stage_out[slot], tap ? I.stage_tap[slot] : nullptr,
+        // "copy_only" (bench: the box's H2D + D2H ceiling for this exact copy pattern) skips the kernels
+        if (!I.opt_copy_only &&
+            !process_range(I, p, np, 0, I.n_streams, I.stage_in[slot], I.stage_out[slot], tap ? I.stage_tap[slot] : nullptr,
                            nf, dstride))
             return false;
         cudaEventRecord(I.ev_comp[slot], I.stream);
@@ -259,7 +267,9 @@ static bool process_host(Instance& I, const float* params, int npb, const float*
             return false;
         cudaEventRecord(I.ev_d2h[slot], I.d2h);
     }
-    return cuda_ok(cudaStreamSynchronize(I.d2h), "D2H sync") && cuda_ok(cudaStreamSynchronize(I.stream), "compute sync");
+    drain.armed = false;
+    const bool ok_d2h = cuda_ok(cudaStreamSynchronize(I.d2h), "D2H sync");
+    return cuda_ok(cudaStreamSynchronize(I.stream), "compute sync") && ok_d2h;
 }
 
 static int do_process(Instance* I, const float* params, int npb, const float* in, float* out, double* tap,
@@ -271,6 +281,13 @@ static int do_process(Instance* I, const float* params, int npb, const float* in
     }
     if (!I->prepared) { set_error("za_gpu_process before za_gpu_prepare"); return ZA_ERR_STATE; }
     if (tap && I->precision != ZA_F64) { set_error("za_gpu_process_tap64 needs precision ZA_F64"); return ZA_ERR_ARG; }
+    if (I->desc->n_in != I->desc->n_out && in && n_frames > 0) {
+        // rows of stream s sit at (s * n_ch + c) * stride: with different channel counts the two layouts interleave, so
+        // overlapping buffers would let one stream's output land in another stream's unread input
+        const char* a0 = (const char*)in;  const char* a1 = a0 + ((size_t)I->n_streams * I->desc->n_in - 1) * stride * 4 + n_frames * 4;
+        const char* b0 = (const char*)out; const char* b1 = b0 + ((size_t)I->n_streams * I->desc->n_out - 1) * stride * 4 + n_frames * 4;
+        if (a0 < b1 && b0 < a1) { set_error("za_gpu_process: in and out overlap but the plugin's channel counts differ"); return ZA_ERR_ARG; }
+    }
     if (!cuda_ok(cudaSetDevice(I->device), "cudaSetDevice")) return ZA_ERR_CUDA;
     I->ev_used = 0;
     if (I->impl->deferred_error(*I)) return ZA_ERR_STATE;           // flagged by a kernel of an earlier call
@@ -376,7 +393,7 @@ ZA_API int za_gpu_create(const char* key, int n_streams, double srate, int block
     if (!cuda_ok(cudaStreamCreateWithFlags(&I.own_stream, cudaStreamNonBlocking), "stream create")) { delete h; return ZA_ERR_CUDA; }
     I.stream = I.own_stream;
     I.impl.reset(d->make());
-    if (!I.impl->create(I)) { za_gpu_destroy(h); return ZA_ERR_CUDA; }
+    if (!I.impl->create(I)) { const int rc = I.create_status; za_gpu_destroy(h); return rc; }
     *out = h;
     return ZA_OK;
 }
@@ -456,6 +473,17 @@ ZA_API int za_gpu_sync(za_gpu_handle h)
     if (!cuda_ok(cudaStreamSynchronize(h->I.stream), "sync")) return ZA_ERR_CUDA;
     return h->I.impl && h->I.impl->deferred_error(h->I) ? ZA_ERR_STATE : ZA_OK;
 }
+ZA_API int za_gpu_host_alloc(size_t bytes, void** out)
+{
+    if (!out || bytes == 0) return ZA_ERR_ARG;
+    *out = nullptr;
+    return cuda_ok(cudaHostAlloc(out, bytes, cudaHostAllocPortable), "cudaHostAlloc") ? ZA_OK : ZA_ERR_CUDA;
+}
+ZA_API int za_gpu_host_free(void* p)
+{
+    if (!p) return ZA_OK;
+    return cuda_ok(cudaFreeHost(p), "cudaFreeHost") ? ZA_OK : ZA_ERR_CUDA;
+}
 ZA_API int za_gpu_launch_count(za_gpu_handle h, int64_t* n)
 {
     if (!h || !n) return ZA_ERR_ARG;
@@ -487,6 +515,7 @@ ZA_API int za_gpu_set_option(za_gpu_handle h, const char* name, int value)
     else if (!std::strcmp(name, "tile_buffers")) I.opt_nbuf = value;
     else if (!std::strcmp(name, "scalar_f32")) I.opt_scalar_f32 = value;
     else if (!std::strcmp(name, "heap_slots")) I.opt_heap_slots = value;
+    else if (!std::strcmp(name, "copy_only")) I.opt_copy_only = value;
     else { set_error(std::string("unknown option ") + name); return ZA_ERR_ARG; }
     return ZA_OK;
 }
@@ -494,7 +523,9 @@ ZA_API int za_gpu_set_option(za_gpu_handle h, const char* name, int value)
 ZA_API int za_gpu_render(const char* key, const float* params, const float* in, float* out, int n_streams, int64_t n_frames)
 {
     za_gpu_handle h = nullptr;
-    int rc = za_gpu_create(key, n_streams, 48000.0, 512, ZA_F64, 0, &h);
+    const PluginDesc* d = find_plugin(key);
+    // Faust leaves compute in float32 (cmake/plugin/CMakeLists.txt:144 passes no -double); DSP-JSFX computes in double
+    int rc = za_gpu_create(key, n_streams, 48000.0, 512, (d && d->kind == 1) ? ZA_F32 : ZA_F64, 0, &h);
     if (rc != ZA_OK) return rc;
     rc = za_gpu_prepare(h, params);
     if (rc == ZA_OK) rc = za_gpu_process(h, nullptr, 0, in, out, n_frames, n_frames, ZA_MEM_HOST);

@@ -40,6 +40,7 @@ SYMBOLS = [
     "za_gpu_quantise", "za_gpu_create", "za_gpu_destroy", "za_gpu_set_stream", "za_gpu_prepare", "za_gpu_process",
     "za_gpu_process_tap64", "za_gpu_read_state", "za_gpu_sync", "za_gpu_launch_count", "za_gpu_last_kernel_ms",
     "za_gpu_set_option", "za_gpu_render", "za_gpu_last_error", "za_gpu_device_count", "za_gpu_version",
+    "za_gpu_synth", "za_gpu_synth_tables", "za_gpu_checksum", "za_gpu_host_alloc", "za_gpu_host_free",
 ]
 
 _lib = None
@@ -73,6 +74,12 @@ def lib() -> C.CDLL:
         L.za_gpu_last_kernel_ms.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int)]
         L.za_gpu_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
         L.za_gpu_render.argtypes = [C.c_char_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int64]
+        L.za_gpu_host_alloc.argtypes = [C.c_size_t, C.POINTER(C.c_void_p)]
+        L.za_gpu_host_free.argtypes = [C.c_void_p]
+        L.za_gpu_synth.argtypes = [C.c_int, C.c_uint32, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int64, C.c_int64, C.c_void_p,
+                                   C.c_int, C.c_void_p]
+        L.za_gpu_synth_tables.argtypes = [C.c_void_p, C.c_void_p]
+        L.za_gpu_checksum.argtypes = [C.c_void_p, C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         _lib = L
     return _lib
 
@@ -115,6 +122,49 @@ def quantise(slider: SliderInfo, value: float) -> float:
     out = C.c_double()
     _check(lib().za_gpu_quantise(C.byref(slider), C.c_float(value), C.byref(out)), "za_gpu_quantise")
     return out.value
+
+
+class HostBuffer:
+    """Page-locked float32 host array [shape] from za_gpu_host_alloc (exact size; torch's pinned allocator rounds up to a
+    power of two).  `.array` is the numpy view; free() or garbage collection releases it."""
+
+    def __init__(self, shape):
+        self.shape = tuple(int(v) for v in shape)
+        n = int(np.prod(self.shape))
+        self._p = C.c_void_p()
+        _check(lib().za_gpu_host_alloc(n * 4, C.byref(self._p)), "za_gpu_host_alloc")
+        self.array = np.ctypeslib.as_array(C.cast(self._p, C.POINTER(C.c_float)), shape=(n,)).reshape(self.shape)
+
+    def free(self):
+        if self._p:
+            self.array = None
+            lib().za_gpu_host_free(self._p)
+            self._p = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+def synth_into(out, kind: int, seed: int, first_stream: int = 0, t0: int = 0, cuda_stream=None):
+    """Fill the CUDA tensor out[n_streams][n_ch][n_frames] with the library's device generator (za_gpu_synth)."""
+    ns, nch, nf = out.shape
+    assert out.is_cuda and out.is_contiguous()
+    _check(lib().za_gpu_synth(kind, seed, first_stream, ns, nch, nf, nf, t0, out.data_ptr(), out.device.index or 0, cuda_stream),
+           "za_gpu_synth")
+    return out
+
+
+def checksum(x, cuda_stream=None):
+    """Per-row (stream, channel) order-independent checksum (uint64) and energy (float64) of a CUDA tensor [ns][nch][nf]."""
+    ns, nch, nf = x.shape
+    assert x.is_cuda and x.is_contiguous()
+    s, e = np.zeros(ns * nch, np.uint64), np.zeros(ns * nch, np.float64)
+    _check(lib().za_gpu_checksum(x.data_ptr(), ns * nch, nf, nf, s.ctypes.data, e.ctypes.data, x.device.index or 0, cuda_stream),
+           "za_gpu_checksum")
+    return s.reshape(ns, nch), e.reshape(ns, nch)
 
 
 def _ptr(a):

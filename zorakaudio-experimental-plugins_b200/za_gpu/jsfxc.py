@@ -541,7 +541,7 @@ class Emitter:
         if k == "tern" or k == "if":
             c = self.ex(n[1])
             t = self.tmp()
-            self.w(f"if ({c} != R(0)) {{"); self.ind += 1
+            self.w(f"if (truthy_({c})) {{"); self.ind += 1
             a = self.ex(n[2]); self.w(f"{t} = {a};"); self.ind -= 1
             self.w("} else {"); self.ind += 1
             b = self.ex(n[3]) if n[3] is not None else "R(0)"
@@ -564,7 +564,7 @@ class Emitter:
             return t
         if k == "while":
             self.w("for (;;) {"); self.ind += 1
-            c = self.ex(n[1]); self.w(f"if (!({c} != R(0))) break;")
+            c = self.ex(n[1]); self.w(f"if (!truthy_({c})) break;")
             self.ex(n[2]); self.ind -= 1
             self.w("}")
             return "R(0)"
@@ -573,8 +573,8 @@ class Emitter:
             if op in ("&&", "||"):
                 l = self.ex(n[2])
                 t = self.tmp("R(1)" if op == "||" else "R(0)")
-                self.w(f"if ({'!' if op == '||' else ''}({l} != R(0))) {{"); self.ind += 1
-                r = self.ex(n[3]); self.w(f"{t} = ({r} != R(0)) ? R(1) : R(0);"); self.ind -= 1
+                self.w(f"if ({'!' if op == '||' else ''}truthy_({l})) {{"); self.ind += 1
+                r = self.ex(n[3]); self.w(f"{t} = truthy_({r}) ? R(1) : R(0);"); self.ind -= 1
                 self.w("}")
                 return t
             l = self.ex(n[2]); r = self.ex(n[3])
@@ -633,7 +633,9 @@ class Emitter:
             return f"div_({l}, {r})"
         if op == "^":
             return f"pow_({l}, {r})"
-        if op in ("<", "<=", ">", ">=", "==", "!="):
+        if op == "!=":                      # ordered, like every compare of the reference (fcmp one, dsp_jsfx_aot.py:4349-4352)
+            return f"ne_({l}, {r}) ? R(1) : R(0)"
+        if op in ("<", "<=", ">", ">=", "=="):
             return f"({l} {op} {r}) ? R(1) : R(0)"
         if op == "|":
             return f"R(to_i32({l}) | to_i32({r}))"

@@ -118,3 +118,84 @@ def cfg1_input(n_frames: int = 480000, n_ch: int = 2, srate: float = 48000.0, se
                 cur = int(stt[n - 1])
         x[0, c] = (noise * gate + sine).astype(np.float32)
     return x
+
+
+# ---- the library's device generator (csrc/k_synth.cu), restated in numpy: bit-identical by construction ------------------
+def _mix32(x):
+    x = np.asarray(x, np.uint32).copy()
+    x ^= x >> np.uint32(16); x *= np.uint32(0x7feb352d); x ^= x >> np.uint32(15); x *= np.uint32(0x846ca68b); x ^= x >> np.uint32(16)
+    return x
+
+
+def _stream_key(seed, stream, ch):
+    with np.errstate(over="ignore"):
+        return _mix32(np.uint32(seed) * np.uint32(0x9E3779B1) + np.asarray(stream, np.uint32) * np.uint32(0x85EBCA77)
+                      + np.uint32(ch) * np.uint32(0xC2B2AE3D) + np.uint32(0x27D4EB2F))
+
+
+def _uni(h):
+    return (h >> np.uint32(8)).astype(np.float32) * np.float32(2.0 ** -23) + np.float32(-1.0)
+
+
+def _frame_hash(key, t):
+    lo = (t & 0xFFFFFFFF).astype(np.uint32)
+    hi = (t >> 32).astype(np.uint32)
+    with np.errstate(over="ignore"):
+        return _mix32((lo * np.uint32(0x9E3779B1) + hi * np.uint32(0x632BE5AB)) ^ key)
+
+
+_TABLES = None
+
+
+def synth_tables():
+    global _TABLES
+    if _TABLES is None:
+        import za_gpu
+        sine, amp = np.empty(4096, np.float32), np.empty(256, np.float32)
+        za_gpu._check(za_gpu.lib().za_gpu_synth_tables(sine.ctypes.data, amp.ctypes.data), "za_gpu_synth_tables")
+        _TABLES = (sine, amp)
+    return _TABLES
+
+
+def synth(kind: int, seed: int, streams, n_ch: int, n_frames: int, t0: int = 0) -> np.ndarray:
+    """CPU twin of za_gpu_synth for the listed absolute stream numbers -> float32 [len(streams)][n_ch][n_frames]."""
+    sine, amp = synth_tables()
+    streams = list(streams)
+    out = np.empty((len(streams), n_ch, n_frames), np.float32)
+    t = np.arange(t0, t0 + n_frames, dtype=np.int64)
+    t32 = (t & 0xFFFFFFFF).astype(np.uint32)
+    with np.errstate(over="ignore"):
+        for a, s in enumerate(streams):
+            key_m = _stream_key(seed, s, 255)
+            if kind == 0:
+                inc1 = np.uint32(5368709 + int(_mix32(key_m ^ np.uint32(0x1111))) % 30422000)
+                inc2 = np.uint32(89478485 + int(_mix32(key_m ^ np.uint32(0x2222))) % 447392000)
+                s1 = sine[(t32 * inc1) >> np.uint32(20)]
+                s2 = sine[(t32 * inc2) >> np.uint32(20)]
+            else:
+                k = t // 2400
+                r = (t - k * 2400).astype(np.float32)
+                k32 = (k & 0xFFFFFFFF).astype(np.uint32)
+                a0 = amp[_mix32(key_m ^ np.uint32(0xA5A5A5A5) ^ (k32 * np.uint32(0x9E3779B1))) & np.uint32(255)]
+                a1 = amp[_mix32(key_m ^ np.uint32(0xA5A5A5A5) ^ ((k32 + np.uint32(1)) * np.uint32(0x9E3779B1))) & np.uint32(255)]
+                e = a0 + (a1 - a0) * (r * np.float32(4.1666667675599456e-04))
+                mono = _uni(_frame_hash(key_m, t))
+            for c in range(n_ch):
+                key = _stream_key(seed, s, c)
+                u = _uni(_frame_hash(key, t))
+                if kind == 0:
+                    out[a, c] = (np.float32(0.25) * u + np.float32(0.125) * s1) + np.float32(0.125) * s2
+                else:
+                    out[a, c] = e * (mono + np.float32(0.3) * u)
+    return out
+
+
+def checksum(x: np.ndarray):
+    """CPU twin of za_gpu_checksum: per-row wrapping-uint64 checksum and energy of float32 [rows...][frames]."""
+    x = np.ascontiguousarray(x, np.float32)
+    nf = x.shape[-1]
+    with np.errstate(over="ignore"):
+        w = (_mix32(np.arange(nf, dtype=np.uint32)) | np.uint32(1)).astype(np.uint64)
+        bits = x.view(np.uint32).astype(np.uint64) + np.uint64(1)
+        s = (bits * w).sum(axis=-1, dtype=np.uint64)
+    return s, (x.astype(np.float64) ** 2).sum(axis=-1)
