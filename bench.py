@@ -62,6 +62,20 @@ WORKLOADS = {
                     kernel={"f32": "modtilt_kernel"},
                     text="cfg3 shape on the Faust leaf ModTilt (envelope tilt shaper: 5 one-poles + sqrt/div/log10/10^x per frame), "
                          "{ns} stereo streams x {sec:g} s @ 48 kHz per GPU, tilt automated every 512-frame block, in-place buffers"),
+    # the other leaves of the three classes at the cfg3 batch shape (4096 stereo streams); shorter renders while they run on
+    # the translated stream-per-thread path
+    "erbtilt": dict(plugin="ERBTilt", streams=4096, seconds=10.0, ch=(2, 2), automate=[0], cpu=(256, 5.0), synth=1,
+                    kernel={"f32": "erbtilt / jsfx_process_kernel", "f64": "erbtilt / jsfx_process_kernel"},
+                    text="ERB Tilt (15 one-poles x 2 ch + energy followers + guard), {ns} stereo streams x {sec:g} s @ 48 kHz per GPU, tilt automated every 512-frame block"),
+    "specstab": dict(plugin="SpectralStabilizer", streams=4096, seconds=10.0, ch=(2, 2), automate=[1], cpu=(256, 5.0), synth=1,
+                     kernel={"f32": "specstab / jsfx_process_kernel", "f64": "specstab / jsfx_process_kernel"},
+                     text="Spectral Stabilizer (12 band-pass biquads x 2 ch + per-band gain smoothing), {ns} stereo streams x {sec:g} s @ 48 kHz per GPU, depth automated every 512-frame block"),
+    "rtt": dict(plugin="RTT", streams=4096, seconds=10.0, ch=(8, 2), automate=[0, 1], cpu=(256, 5.0), synth=1,
+                kernel={"f32": "jsfx_process_kernel", "f64": "jsfx_process_kernel"},
+                text="cfg3 on RTT (Reverb Tail Tamer, 8 in / 2 out), {ns} streams x {sec:g} s @ 48 kHz per GPU, amount/sensitivity automated every 512-frame block"),
+    "soma": dict(plugin="SOMA", streams=4096, seconds=10.0, ch=(2, 2), automate=[0, 3], cpu=(256, 5.0), synth=1,
+                 kernel={"f32": "jsfx_process_kernel", "f64": "jsfx_process_kernel"},
+                 text="cfg3 on SOMA (lookahead limiter), {ns} stereo streams x {sec:g} s @ 48 kHz per GPU, drive/release automated every 512-frame block"),
 }
 SUBS_DEFAULT = ["cfg2", "cfg4", "modtilt", "cfg5"]
 

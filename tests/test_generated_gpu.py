@@ -66,7 +66,8 @@ def test_fp64_parity_and_state(gpu, key, automate):
         if np.all(want == np.round(want)) and np.abs(want).max() < 2 ** 40:
             assert np.array_equal(got, want), name
         else:
-            assert np.abs(got - want).max() <= 1e-9 * max(1.0, np.abs(want).max()), name
+            both_nan = np.isnan(got) & np.isnan(want)          # (semprobe keeps NaNs in its variables on purpose)
+            assert np.all(both_nan | (np.abs(got - want) <= 1e-9 * max(1.0, np.nanmax(np.abs(want))))), name
     assert checked > 5
     bp.close()
 

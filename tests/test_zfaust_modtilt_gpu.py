@@ -137,3 +137,37 @@ def test_device_parameter_path_equals_host_path(gpu, port):
     assert np.array_equal(outs[0], outs[1])
     y, _ = port.render(p, x, block=block)
     assert dbfs_rms(outs[0].astype(np.float64) - y) < -100.0
+
+
+@pytest.mark.parametrize("ns,nf,block", [(37, 512 * 40 + 77, 512), (5, 256 * 9, 256), (130, 1024 * 6 + 1023, 1024), (3, 511, 512)])
+def test_scan_kernel_against_restatement_and_scalar_kernel(gpu, port, ns, nf, block):
+    """The time-parallel scan kernel (k_modtilt_scan.cu: one warp per stream, 256-frame tiles) renders the whole host
+    blocks of a call, the stream-per-thread kernel the ragged tail: against the restatement (criterion) and against the
+    stream-per-thread kernel alone (option scalar_f32), with every parameter moving per block; states handed over."""
+    p, x = make_case(port, ns, nf, True, block)
+    y, _ = port.render(p, x, block=block)
+    outs, states = {}, {}
+    for scalar in (0, 1):
+        bp = gpu.BatchProcessor("ModTilt", ns, 48000.0, block, "f32")
+        bp.set_option("scalar_f32", scalar)
+        bp.prepare(p[0])
+        # two calls: the second starts from the state the first left (scan kernel -> tail kernel -> scan kernel)
+        cut = (nf // 2) // block * block + (block // 2 if nf > 2 * block else 0)
+        o = np.zeros_like(x)
+        if cut > 0:
+            o[:, :, :cut] = bp.process(np.ascontiguousarray(x[:, :, :cut]), params=p)
+        if cut % block == 0:
+            o[:, :, cut:] = bp.process(np.ascontiguousarray(x[:, :, cut:]), params=p[cut // block:])
+        else:                                    # a call boundary inside a host block restarts the block grid: render in one go
+            bp.prepare(p[0])
+            o = bp.process(x, params=p)
+        outs[scalar] = o
+        states[scalar] = np.stack([bp.read_state(n) for n in ("env2", "base", "lp_piv", "ratio", "mean_rdb")])
+        bp.close()
+    for scalar in (0, 1):
+        r = outs[scalar].astype(np.float64) - y
+        assert dbfs_rms(r) < -100.0, (scalar, dbfs_rms(r))
+    d = outs[0].astype(np.float64) - outs[1]
+    print(f"scan vs scalar kernel: {dbfs_rms(d):.1f} dBFS, equal {np.mean(outs[0] == outs[1]):.3f}")
+    assert dbfs_rms(d) < -120.0
+    assert np.allclose(states[0], states[1], rtol=2e-4, atol=1e-7)

@@ -11,6 +11,7 @@
 #include <cstring>
 
 #include "za_host.h"
+#include "modtilt_scan_core.h"
 
 namespace za {
 
@@ -27,7 +28,14 @@ float a_from_hz(float hz, float fs)                    // :25-26
     return 1.0f - std::exp(((-2.0f * pi) * std::fmax(hz, 0.001f)) / fs);
 }
 
-void modtilt_slow(const double* q, float fs, MTCoef& c)
+int piv_grid_index(double q_pivot, double mn, double step, int n)     // the pivot slider's grid index: row of the scan kernel's power table
+{
+    if (!(step > 0.0) || n <= 0) return 0;
+    const long long k = std::llround((q_pivot - mn) / step);
+    return (int)(k < 0 ? 0 : (k > n - 1 ? n - 1 : k));
+}
+
+void modtilt_slow(const double* q, float fs, MTCoef& c, int piv_index = 0)
 {
     const float tilt = (float)q[0], pivot = (float)q[1], mix = (float)q[2];
     c.a_piv = a_from_hz(pivot, fs);                                // :37
@@ -35,7 +43,8 @@ void modtilt_slow(const double* q, float fs, MTCoef& c)
     c.g_hi = std::pow(10.0f, (tilt * 0.5f) / 20.0f);               // :44  ba.db2linear(x) = pow(10, x/20)
     c.g_lo = std::pow(10.0f, ((-tilt) * 0.5f) / 20.0f);            // :45
     c.mix = mix; c.nmix = 1.0f - mix;
-    c.pad0 = c.pad1 = 0.0f;
+    std::memcpy(&c.piv_index, &piv_index, sizeof(float));
+    c.pad1 = 0.0f;
 }
 
 // ---- device-side parameter path -----------------------------------------------------------------------------------
@@ -60,7 +69,7 @@ __global__ void modtilt_param_kernel(const float* __restrict__ raw, MTCoef* __re
         const float2 a = t_tilt[k[0]], b = t_piv[k[1]], c = t_mix[k[2]];
         float4* o = reinterpret_cast<float4*>(coef + r);
         o[0] = make_float4(b.x, b.y, a.x, a.y);        // a_piv, na_piv, g_lo, g_hi
-        o[1] = make_float4(c.x, c.y, 0.f, 0.f);        // mix, nmix
+        o[1] = make_float4(c.x, c.y, __int_as_float(k[1]), 0.f);        // mix, nmix, pivot grid index
     }
 }
 
@@ -69,6 +78,10 @@ class ModTilt : public PluginImpl {
     float2* d_tab = nullptr;                          // tilt | pivot | mix tables
     MTGrid grid{};
     bool grid_ok = false;
+
+    float* d_q = nullptr;                              // scan kernel: Q rows [4 fixed stages][32] then [pivot grid][32]
+    mtscan::Consts scanK{};
+    bool scan_ready = false;
 
     float* d_state = nullptr;
     MTCoef* d_coef = nullptr;
@@ -79,7 +92,7 @@ class ModTilt : public PluginImpl {
     float fs = 48000.0f;
 
 public:
-    ~ModTilt() override { cudaFree(d_state); cudaFree(d_coef); cudaFree(d_raw); cudaFree(d_tab); }
+    ~ModTilt() override { cudaFree(d_state); cudaFree(d_coef); cudaFree(d_raw); cudaFree(d_tab); cudaFree(d_q); }
 
     bool build_tables(Instance& I)
     {
@@ -105,6 +118,19 @@ public:
         if (!cuda_ok(cudaMalloc(&d_tab, tab.size() * sizeof(float2)), "modtilt tables") ||
             !cuda_ok(cudaMemcpy(d_tab, tab.data(), tab.size() * sizeof(float2), cudaMemcpyHostToDevice), "modtilt tables upload")) return false;
         grid_ok = true;
+        // the scan kernel's powers: (na^8)^j, j = 0 .. 31, for the four fixed stages and for every pivot grid value
+        const float a_env = a_from_hz(25.0f, fs), a_base = a_from_hz(1.0f, fs), a_trim = a_from_hz(0.2f, fs);
+        scanK.env = mtscan::make_stage(a_env, 1.0f - a_env);
+        scanK.base = mtscan::make_stage(a_base, 1.0f - a_base);
+        scanK.ratio = mtscan::make_stage(0.05f, 1.0f - 0.05f);
+        scanK.trim = mtscan::make_stage(a_trim, 1.0f - a_trim);
+        std::vector<float> q((size_t)(4 + grid.n[1]) * 32);
+        mtscan::power_row(scanK.env.na, &q[0]); mtscan::power_row(scanK.base.na, &q[32]);
+        mtscan::power_row(scanK.ratio.na, &q[64]); mtscan::power_row(scanK.trim.na, &q[96]);
+        for (int k = 0; k < grid.n[1]; ++k) mtscan::power_row(tab[(size_t)grid.n[0] + k].y, &q[(size_t)(4 + k) * 32]);
+        if (!cuda_ok(cudaMalloc(&d_q, q.size() * sizeof(float)), "modtilt scan tables") ||
+            !cuda_ok(cudaMemcpy(d_q, q.data(), q.size() * sizeof(float), cudaMemcpyHostToDevice), "modtilt scan tables upload")) return false;
+        scan_ready = true;
         return true;
     }
 
@@ -141,7 +167,29 @@ public:
         // option "warps_per_stream" = streams per warp (4 / 8 / 16 / 32) + 100 x frames per run (default 8; 4 / 16 / 32 are measurement variants)
         const int ol = I.opt_warps % 100, run = I.opt_warps / 100 ? I.opt_warps / 100 : 8;
         const int lanes = (ol == 4 || ol == 8 || ol == 16 || ol == 32) ? ol : modtilt_pick_lanes(I.n_streams, n_sm);
-        const bool timed = I.time_begin();
+        // Time-parallel scan kernel for the whole host blocks of the call when they are whole 256-frame tiles; the
+        // stream-per-thread kernel renders the ragged tail (and every other shape).  "scalar_f32" = 1 forces the latter.
+        int64_t n_main = 0;
+        if (scan_ready && !I.opt_scalar_f32 && a.block_len % mtscan::kTile == 0 && n >= a.block_len) {
+            MTScanArgs S{};
+            S.a = a; S.a.n_frames = n / a.block_len * a.block_len;
+            if (modtilt_scan_ok(S.a)) {
+                S.K = scanK; S.qfix = d_q; S.qpiv = d_q + 4 * 32;
+                const bool timed = I.time_begin();
+                if (!modtilt_scan_launch(S, I.stream)) return false;
+                if (timed) I.time_end();
+                ++I.launches;
+                n_main = S.a.n_frames;
+            }
+        }
+        if (n_main == n) return true;
+        if (n_main > 0) {                                   // the tail starts on a host-block boundary: advance the rows
+            const int64_t b0 = n_main / a.block_len;
+            const int skip = (int)std::min<int64_t>(b0, nbq - 1);
+            a.in += n_main; a.out += n_main; a.n_frames = n - n_main;
+            a.coef += (size_t)skip * I.n_streams; a.n_coef_blocks = nbq - skip;
+        }
+        const bool timed = n_main == 0 && I.time_begin();
         if (!modtilt_launch(a, lanes, I.stream, run)) return false;
         if (timed) I.time_end();
         ++I.launches;
@@ -185,7 +233,7 @@ public:
                     const double* sl = q + ((size_t)b * ns + s) * nd;
                     MTCoef& c = h_coef[(size_t)b * ns + s];
                     if (b > 0 && std::memcmp(sl, sl - (size_t)ns * nd, sizeof(double) * nd) == 0) c = h_coef[(size_t)(b - 1) * ns + s];
-                    else modtilt_slow(sl, fs, c);
+                    else modtilt_slow(sl, fs, c, piv_grid_index(sl[1], grid.mn[1], grid.step[1], grid_ok ? grid.n[1] : 0));
                 }
         });
         const bool same = coef_valid && h_coef.size() == h_coef_dev.size() &&

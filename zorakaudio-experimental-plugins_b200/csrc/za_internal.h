@@ -95,7 +95,7 @@ bool stft_launch(const StftArgs& a, int precision, int n_sm, cudaStream_t stream
 // ---- ModTilt (Faust leaf, float32; plugins/Dynamics/ModTilt/src/ModTilt.dsp) ---------------------------------------
 constexpr int kMTState = 5;      // per stream: the five onepole() states env2, base, lp_piv, ratio, mean_rdb; [var][stream] float
 struct alignas(16) MTCoef {      // slider-rate values of one stream for one compute() call (ModTilt.dsp:37,44-45,17-19)
-    float a_piv, na_piv, g_lo, g_hi, mix, nmix, pad0, pad1;
+    float a_piv, na_piv, g_lo, g_hi, mix, nmix, piv_index, pad1;     // piv_index: grid index of the pivot slider (int bits) -> power table row
 };
 struct MTArgs {
     const float* in; float* out;                   // [stream][2][row_stride]
@@ -105,6 +105,11 @@ struct MTArgs {
     float* state;                                  // [kMTState][n_streams]
     float a_env, a_base, a_trim;                   // sample-rate constants (:35-36,40)
 };
+// time-parallel form (k_modtilt_scan.cu, modtilt_scan_core.h): one warp per stream, five blocked scans per 256-frame tile
+namespace mtscan { struct Consts; }
+struct MTScanArgs;
+bool modtilt_scan_ok(const MTArgs& a);             // shape the scan kernel takes: host blocks of whole tiles, 16-byte aligned rows
+bool modtilt_scan_launch(const MTScanArgs& A, cudaStream_t stream);
 int modtilt_pick_lanes(int n_streams, int n_sm);   // streams per warp: 8, 16 or 32
 bool modtilt_launch(const MTArgs& a, int lanes, cudaStream_t stream, int run = 8);   // run = frames per straight-line run
 
