@@ -309,6 +309,9 @@ def measure(name, ctx, args, headline):
         bp = za_gpu.BatchProcessor(W["plugin"], ns, SRATE, 512, prec, local)
         if headline and args.warps:
             bp.set_option("warps_per_stream", args.warps)
+        if headline:
+            for ov in args.option:
+                bp.set_option(ov.split("=")[0], int(ov.split("=")[1]))
         bp.set_stream(stream_ptr)
         bp.prepare(p0)
         steps = (args.steps if headline else max(3, args.steps // 4)) if main_prec else max(2, args.steps // (2 if headline else 8))
@@ -528,6 +531,7 @@ def main():
     ap.add_argument("--no-parity", action="store_true")
     ap.add_argument("--latency", action="store_true", help="print the small-block latency report (1000 calls per shape) and exit")
     ap.add_argument("--warps", type=int, default=0)
+    ap.add_argument("--option", action="append", default=[], help="name=value passed to za_gpu_set_option on the headline handle (experiments)")
     args = ap.parse_args()
     head = args.workload or "cfg3"
     subs = ([] if args.workload else SUBS_DEFAULT) if args.subs is None else [s for s in args.subs.split(",") if s]

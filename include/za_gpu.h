@@ -118,6 +118,15 @@ ZA_API int za_gpu_process_tap64(za_gpu_handle h, const float* param_block, int n
 ZA_API int za_gpu_read_state(za_gpu_handle h, const char* var_name, double* out);
 ZA_API int za_gpu_sync(za_gpu_handle h);
 
+/* Checkpoint / resume (the renderer's per-stream SoA state IS its checkpoint).  The blob holds
+ * everything a continuing render depends on: current sliders, every per-stream DSP variable, mem[] heaps, rand state,
+ * hop phases -- DSPJSFX_State for all streams.  A blob loads only into a handle of the same plugin, stream count,
+ * block length, sample rate and precision (any device), so a 10-minute bounce can resume after a fault or a stream
+ * range can move to another GPU; rendering after load continues bit-identically to the uninterrupted render. */
+ZA_API int za_gpu_state_size(za_gpu_handle h, size_t* bytes);
+ZA_API int za_gpu_state_save(za_gpu_handle h, void* host_blob, size_t bytes);
+ZA_API int za_gpu_state_load(za_gpu_handle h, const void* host_blob, size_t bytes);
+
 /* Page-locked host buffers for ZA_MEM_HOST calls (the staged copies of za_gpu_process reach PCIe rate only from pinned
  * memory).  Allocated on the calling thread's NUMA node: bind the thread to the GPU's node first on multi-socket boxes. */
 ZA_API int za_gpu_host_alloc(size_t bytes, void** out);

@@ -166,17 +166,18 @@ def test_scan_kernel_tile_code_on_host_nulls_against_the_restatement(tmp_path):
             c = port.coefs(48000.0, *p[b, 0])            # a_env a_base a_trim a_piv g_hi g_lo mix fs
             coef[b, :6] = [c[3], np.float32(1.0) - c[3], c[5], c[4], c[6], np.float32(1.0) - c[6]]
         fixed3 = np.array(c[:3], np.float32)
-        state = np.zeros(5, np.float32)
-        out = np.zeros_like(x)
-        # two calls: state carries across calls exactly like across tiles
-        cut = block * 200
-        for a, b_ in ((0, cut), (cut, nf)):
-            emu.emu_modtilt_scan(C.c_void_p(coef[a // block:].ctypes.data), nb - a // block, block, C.c_void_p(fixed3.ctypes.data),
-                                 C.c_void_p(state.ctypes.data), C.c_void_p(x[0, 0, a:].ctypes.data), C.c_void_p(out[0, 0, a:].ctypes.data),
-                                 C.c_long(b_ - a), C.c_long(nf))
-        r = out.astype(np.float64) - y
-        db = 20 * np.log10(np.sqrt(np.mean(r ** 2)) + 1e-300)
-        rel = np.abs(r).max() / np.abs(y).max()
-        print(f"scan emulation vs restatement (level {level}): residual {db:.1f} dBFS rms, max |d| / peak {rel:.2e}, equal {np.mean(out == y):.3f}")
-        assert db < -120.0, db
-        assert rel < 2e-5
+        for fast in (0, 1):                  # correctly rounded maps / the kernel's throughput forms (host: libm stand-ins)
+            state = np.zeros(5, np.float32)
+            out = np.zeros_like(x)
+            # two calls: state carries across calls exactly like across tiles
+            cut = block * 200
+            for a, b_ in ((0, cut), (cut, nf)):
+                emu.emu_modtilt_scan(C.c_void_p(coef[a // block:].ctypes.data), nb - a // block, block, C.c_void_p(fixed3.ctypes.data),
+                                     C.c_void_p(state.ctypes.data), C.c_void_p(x[0, 0, a:].ctypes.data), C.c_void_p(out[0, 0, a:].ctypes.data),
+                                     C.c_long(b_ - a), C.c_long(nf), fast)
+            r = out.astype(np.float64) - y
+            db = 20 * np.log10(np.sqrt(np.mean(r ** 2)) + 1e-300)
+            rel = np.abs(r).max() / np.abs(y).max()
+            print(f"scan emulation vs restatement (level {level}, fast {fast}): residual {db:.1f} dBFS rms, max |d| / peak {rel:.2e}, equal {np.mean(out == y):.3f}")
+            assert db < -120.0, db
+            assert rel < 2e-5

@@ -172,3 +172,30 @@ def test_two_devices_render_their_shards(gpu):
         bp.process(np.ascontiguousarray(x[a:b]), params=np.ascontiguousarray(p[:, a:b]), tap64=tap)
         assert rel_err(tap, yd[a:b]).max() <= TOL64, dev
         bp.close()
+
+
+@pytest.mark.parametrize("key,prec", [("cascade8", "f32"), ("cascade8", "f64"), ("EasyExpander", "f64"), ("stft_mask2048", "f32"),
+                                      ("SOMA", "f64"), ("RTT", "f32"), ("ModTilt", "f32")])
+def test_checkpoint_resume_is_bit_identical(gpu, key, prec):
+    """za_gpu_state_save / za_gpu_state_load: a render interrupted after its first part and resumed in a FRESH handle from
+    the saved blob continues bit-identically (outputs and, for translated leaves, the rand()-driven state included)."""
+    block = 512
+    ns, nf = 7, block * 20 + 300
+    cut = block * 9
+    p0, pauto, x = _case(gpu, key, ns, nf, block, automate=True)
+    info = gpu.plugin_info(key)
+    bp = gpu.BatchProcessor(key, ns, 48000.0, block, prec).prepare(pauto[0])
+    y1 = bp.process(np.ascontiguousarray(x[:, :, :cut]), params=pauto)
+    blob = bp.save_state()
+    y2 = bp.process(np.ascontiguousarray(x[:, :, cut:]), params=pauto[cut // block:])
+    bp.close()
+    fresh = gpu.BatchProcessor(key, ns, 48000.0, block, prec).prepare(None)      # defaults: everything must come from the blob
+    fresh.load_state(blob)
+    y2b = fresh.process(np.ascontiguousarray(x[:, :, cut:]), params=pauto[cut // block:])
+    assert np.array_equal(y2, y2b), key
+    # a blob from another batch shape is refused
+    other = gpu.BatchProcessor(key, ns + 1, 48000.0, block, prec).prepare(None)
+    with pytest.raises(gpu.ZaError, match="different plugin"):
+        other.load_state(blob)
+    other.close(); fresh.close()
+    assert np.isfinite(y1).all() and info.n_out == y2.shape[1]

@@ -83,17 +83,28 @@ def test_state_carry_inplace_and_states(gpu, port):
     ns, nf = 40, 30000
     p, x = make_case(port, ns, nf, False)
     y, _ = port.render(p, x)
-    bp = gpu.BatchProcessor("ModTilt", ns, precision="f32").prepare(p)
+    bp = gpu.BatchProcessor("ModTilt", ns, precision="f32")
+    bp.set_option("scalar_f32", 1)                        # the stream-per-thread kernel for every frame
+    bp.prepare(p)
     cuts = [0, 1, 33, 5000, 5017, 20000, nf]
     parts = [bp.process(np.ascontiguousarray(x[:, :, a:b])) for a, b in zip(cuts[:-1], cuts[1:])]
     out = np.concatenate(parts, axis=2)
     assert dbfs_rms(out.astype(np.float64) - y) < -100.0
     bp.close()
-    # one call and chunked calls are the same arithmetic: bit-identical
-    bp = gpu.BatchProcessor("ModTilt", ns, precision="f32").prepare(p)
+    # one call and chunked calls are the same arithmetic on that kernel: bit-identical
+    bp = gpu.BatchProcessor("ModTilt", ns, precision="f32")
+    bp.set_option("scalar_f32", 1)
+    bp.prepare(p)
     buf = x.copy()
     whole = bp.process(buf, out=buf)         # in place
     assert np.array_equal(whole, out)
+    bp.close()
+    # the default path (scan kernel for the whole host blocks, in place) re-associates chunk start states only
+    bp = gpu.BatchProcessor("ModTilt", ns, precision="f32").prepare(p)
+    buf = x.copy()
+    whole = bp.process(buf, out=buf)
+    assert dbfs_rms(whole.astype(np.float64) - out) < -120.0
+    assert dbfs_rms(whole.astype(np.float64) - y) < -100.0
     env2 = bp.read_state("env2")
     assert env2.shape == (ns,) and np.all(env2 >= 0) and np.any(env2 > 0)
     bp.close()

@@ -33,7 +33,7 @@ struct HostIO {
 // Renders n_frames (a multiple of block_len, block_len a multiple of 256) of one stream.
 extern "C" __attribute__((visibility("default")))
 void emu_modtilt_scan(const float* coef, int n_blocks, int block_len, const float* fixed3, float* state5, const float* in, float* out,
-                      long n_frames, long stride)
+                      long n_frames, long stride, int fast)
 {
     _MM_SET_FLUSH_ZERO_MODE(_MM_FLUSH_ZERO_ON);
     _MM_SET_DENORMALS_ZERO_MODE(_MM_DENORMALS_ZERO_ON);
@@ -51,7 +51,8 @@ void emu_modtilt_scan(const float* coef, int n_blocks, int block_len, const floa
         MTCoef c{c8[0], c8[1], c8[2], c8[3], c8[4], c8[5], 0.f, 0.f};
         power_row(c.na_piv, q_piv.v);
         HostIO io{in + t * kTile, in + stride + t * kTile, out + t * kTile, out + stride + t * kTile};
-        tile(cy, K, q_env, q_base, q_ratio, q_trim, q_piv, c, io);
+        if (fast) tile<true>(cy, K, q_env, q_base, q_ratio, q_trim, q_piv, c, io);
+        else tile<false>(cy, K, q_env, q_base, q_ratio, q_trim, q_piv, c, io);
     }
     state5[0] = cy.env2; state5[1] = cy.base; state5[2] = cy.lp; state5[3] = cy.rs; state5[4] = cy.mean;
 }

@@ -53,6 +53,7 @@ struct TileIO {
 
 constexpr int kWarps = 4;
 
+template <bool FAST>
 __global__ void __launch_bounds__(32 * kWarps, 7) modtilt_scan_kernel(const MTScanArgs A)
 {
     __shared__ __align__(16) float sm[kWarps][2][2 * kTile];
@@ -107,7 +108,7 @@ __global__ void __launch_bounds__(32 * kWarps, 7) modtilt_scan_kernel(const MTSc
         }
         if (++in_block == tpb) { in_block = 0; ++blk; }
         TileIO io{sm[warp][t & 1], lane};
-        tile(cy, A.K, q_env, q_base, q_ratio, q_trim, q_piv, c, io);
+        tile<FAST>(cy, A.K, q_env, q_base, q_ratio, q_trim, q_piv, c, io);
         __syncwarp();
         {
             const float* buf = sm[warp][t & 1];
@@ -136,11 +137,12 @@ bool modtilt_scan_ok(const MTArgs& a)
            ((uintptr_t)a.in & 15) == 0 && ((uintptr_t)a.out & 15) == 0;
 }
 
-bool modtilt_scan_launch(const MTScanArgs& A, cudaStream_t stream)
+bool modtilt_scan_launch(const MTScanArgs& A, cudaStream_t stream, bool exact_maps)
 {
     if (A.a.n_streams <= 0 || A.a.n_frames <= 0) return true;
     const unsigned grid = (unsigned)((A.a.n_streams + kWarps - 1) / kWarps);
-    modtilt_scan_kernel<<<grid, 32 * kWarps, 0, stream>>>(A);
+    if (exact_maps) modtilt_scan_kernel<false><<<grid, 32 * kWarps, 0, stream>>>(A);
+    else modtilt_scan_kernel<true><<<grid, 32 * kWarps, 0, stream>>>(A);
     return cuda_ok(cudaGetLastError(), "modtilt scan launch");
 }
 

@@ -27,6 +27,8 @@ ZA_LN LF abs_(LF a) { return fabsf(a); }
 ZA_LN LF neg(LF a) { return -a; }
 ZA_LN LF rcp_approx(LF b) { float r; asm("rcp.approx.f32 %0, %1;" : "=f"(r) : "f"(b)); return r; }
 ZA_LN LF rsqrt_approx(LF x) { float y; asm("rsqrt.approx.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+ZA_LN LF lg2_approx(LF x) { float y; asm("lg2.approx.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }     // MUFU.LG2, abs err <= 2^-22 near 1
+ZA_LN LF ex2_approx(LF x) { float y; asm("ex2.approx.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }     // MUFU.EX2, 2 ulp
 ZA_LN LF log10_(LF x) { return log10f(x); }
 ZA_LN LF exp10_(LF x) { return exp10f(x); }
 ZA_LN LF log_(LF x) { return logf(x); }
@@ -45,6 +47,7 @@ ZA_LN float lane_value(LF v, int l) { return __shfl_sync(0xffffffffu, v, l); }  
 }  // namespace za
 #else
 #include <cmath>
+#include <type_traits>
 namespace za {
 namespace lanes {
 
@@ -67,6 +70,8 @@ ZA_LANES_OP1(abs_, std::fabs(x))
 ZA_LANES_OP1(neg, -x)
 ZA_LANES_OP1(rcp_approx, 1.0f / x)
 ZA_LANES_OP1(rsqrt_approx, (float)(1.0 / std::sqrt((double)x)))
+ZA_LANES_OP1(lg2_approx, std::log2(x))
+ZA_LANES_OP1(ex2_approx, std::exp2(x))
 ZA_LANES_OP1(log10_, std::log10(x))
 ZA_LANES_OP1(exp10_, std::pow(10.0f, x))
 ZA_LANES_OP1(log_, std::log(x))

@@ -140,6 +140,14 @@ public:
         return true;
     }
 
+    void state_io(Instance& I, StateIO& io) override { io.dev(d_state, (size_t)I.n_streams * kC8State * sizeof(double)); }
+    bool after_state_load(Instance& I) override      // coefficients and scan tables are functions of the restored sliders
+    {
+        std::vector<int> all(I.n_streams);
+        for (int s = 0; s < I.n_streams; ++s) all[s] = s;
+        return sliders_changed(I, 0, I.n_streams, all);
+    }
+
     bool read_state(Instance& I, const char* name, double* out) override
     {
         static const char* names[14] = {"z11", "z12", "z21", "z22", "z31", "z32", "z41", "z42", "z51", "z52", "z61", "z62", "lp7", "lp8"};

@@ -272,6 +272,9 @@ public:
         return 1;
     }
 
+    void state_io(Instance& I, StateIO& io) override { io.dev(d_state, (size_t)I.n_streams * kEEState * sizeof(double)); }
+    bool after_state_load(Instance&) override { coef_valid = false; return true; }
+
     bool read_state(Instance& I, const char* name, double* out) override
     {
         static const char* names[7] = {"hpf_lp", "lpf_y", "det_slow", "expanding", "gain_db_s", "det_db_m", "gr_db_m"};

@@ -140,6 +140,16 @@ public:
         return true;
     }
 
+    void state_io(Instance& I, StateIO& io) override        // DSPJSFX_State: vars + sliders + lastSlidersValid, mem[], randMT + index
+    {
+        const size_t ns = (size_t)I.n_streams;
+        io.dev(d_state, (size_t)(d_->n_vars + 65) * ns * rsize);
+        io.dev(d_mem, (size_t)(d_->mem_slots + 1) * ns * rsize);
+        io.dev(d_mt, 625 * ns * sizeof(unsigned));
+        io.host(&heap_zeroed, sizeof heap_zeroed);
+    }
+    bool after_state_load(Instance&) override { q_last.clear(); return true; }
+
     bool read_state(Instance& I, const char* name, double* out) override
     {
         int slot = -1;

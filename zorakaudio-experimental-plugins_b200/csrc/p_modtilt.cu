@@ -74,7 +74,9 @@ __global__ void modtilt_param_kernel(const float* __restrict__ raw, MTCoef* __re
 }
 
 class ModTilt : public PluginImpl {
-    float* d_raw = nullptr; size_t raw_cap = 0;
+    float* d_raw2[2] = {nullptr, nullptr}; MTCoef* d_coef2[2] = {nullptr, nullptr}; size_t raw_cap = 0;   // per-segment raw rows / coefficient rows, double buffered
+    cudaStream_t up_stream = nullptr;
+    cudaEvent_t ev_ready[2] = {}, ev_consumed[2] = {};
     float2* d_tab = nullptr;                          // tilt | pivot | mix tables
     MTGrid grid{};
     bool grid_ok = false;
@@ -92,7 +94,16 @@ class ModTilt : public PluginImpl {
     float fs = 48000.0f;
 
 public:
-    ~ModTilt() override { cudaFree(d_state); cudaFree(d_coef); cudaFree(d_raw); cudaFree(d_tab); cudaFree(d_q); }
+    ~ModTilt() override
+    {
+        cudaFree(d_state); cudaFree(d_coef); cudaFree(d_tab); cudaFree(d_q);
+        for (int k = 0; k < 2; ++k) {
+            cudaFree(d_raw2[k]); cudaFree(d_coef2[k]);
+            if (ev_ready[k]) cudaEventDestroy(ev_ready[k]);
+            if (ev_consumed[k]) cudaEventDestroy(ev_consumed[k]);
+        }
+        if (up_stream) cudaStreamDestroy(up_stream);
+    }
 
     bool build_tables(Instance& I)
     {
@@ -134,35 +145,63 @@ public:
         return true;
     }
 
+    // Device-side parameter path, pipelined over TIME SEGMENTS of the call: the raw rows of segment k + 1 are uploaded
+    // and turned into coefficient rows on a side stream (two buffers) while the render kernel of segment k runs, so a
+    // 60 s call with per-block automation (5625 x 4096 rows, 276 MB of host floats) does not wait for its parameters
+    // before the first frame (the one-shot upload was 8.4 ms of a 26.8 ms step at 4096 x 20 s).
     int run_blocks_raw(Instance& I, const float* params, int nbq, const float* in, float* out, double* tap,
                        int64_t n, int64_t stride) override
     {
         if (!grid_ok || tap || I.opt_force_generic) return 0;      // "force_generic_io": the host parameter path (tests compare the two)
-        const size_t rows = (size_t)nbq * I.n_streams;
-        if (rows > raw_cap) {
-            cudaFree(d_raw); d_raw = nullptr; raw_cap = 0;
-            if (!cuda_ok(cudaMalloc(&d_raw, rows * 3 * sizeof(float)), "modtilt raw params")) return -1;
-            raw_cap = rows;
+        const int64_t bl = I.block_len;
+        const int64_t n_blocks = (n + bl - 1) / bl;
+        // >= 4 segments of >= 32 host blocks each (short calls: one segment)
+        const int64_t seg_blocks = std::max<int64_t>(32, (n_blocks + 7) / 8);
+        const size_t seg_rows = (size_t)std::min<int64_t>(seg_blocks, nbq) * I.n_streams;
+        if (seg_rows > raw_cap) {
+            for (int k = 0; k < 2; ++k) { cudaFree(d_raw2[k]); cudaFree(d_coef2[k]); d_raw2[k] = nullptr; d_coef2[k] = nullptr; }
+            raw_cap = 0;
+            for (int k = 0; k < 2; ++k)
+                if (!cuda_ok(cudaMalloc(&d_raw2[k], seg_rows * 3 * sizeof(float)), "modtilt raw params") ||
+                    !cuda_ok(cudaMalloc(&d_coef2[k], seg_rows * sizeof(MTCoef)), "modtilt coef")) return -1;
+            raw_cap = seg_rows;
         }
-        if (rows > coef_cap) {
-            cudaFree(d_coef); d_coef = nullptr; coef_cap = 0;
-            if (!cuda_ok(cudaMalloc(&d_coef, rows * sizeof(MTCoef)), "modtilt coef")) return -1;
-            coef_cap = rows;
+        if (!up_stream) {
+            if (!cuda_ok(cudaStreamCreateWithFlags(&up_stream, cudaStreamNonBlocking), "modtilt upload stream")) return -1;
+            for (int k = 0; k < 2; ++k) {
+                cudaEventCreateWithFlags(&ev_ready[k], cudaEventDisableTiming);
+                cudaEventCreateWithFlags(&ev_consumed[k], cudaEventDisableTiming);
+            }
         }
         coef_valid = false;
-        if (!cuda_ok(cudaMemcpyAsync(d_raw, params, rows * 3 * sizeof(float), cudaMemcpyHostToDevice, I.stream), "modtilt params upload")) return -1;
-        const unsigned blocks = (unsigned)std::min<size_t>((rows + 255) / 256, (size_t)n_sm * 8);
-        modtilt_param_kernel<<<blocks, 256, 0, I.stream>>>(d_raw, d_coef, rows, grid, d_tab, d_tab + grid.n[0], d_tab + grid.n[0] + grid.n[1]);
-        if (!cuda_ok(cudaGetLastError(), "modtilt param kernel")) return -1;
-        ++I.launches;
-        return launch(I, nbq, in, out, n, stride) ? 1 : -1;
+        int k = 0;
+        for (int64_t b0 = 0; b0 < n_blocks; b0 += seg_blocks, ++k) {
+            const int buf = k & 1;
+            const int64_t b1 = std::min<int64_t>(n_blocks, b0 + seg_blocks);
+            const int64_t r0 = std::min<int64_t>(b0, nbq - 1);                      // the last row persists beyond nbq
+            const int rows_here = (int)std::max<int64_t>(1, std::min<int64_t>(b1, nbq) - r0);
+            const size_t rows = (size_t)rows_here * I.n_streams;
+            cudaStreamWaitEvent(up_stream, ev_consumed[buf], 0);                   // the kernel two segments back has read this buffer
+            if (!cuda_ok(cudaMemcpyAsync(d_raw2[buf], params + (size_t)r0 * I.n_streams * 3, rows * 3 * sizeof(float), cudaMemcpyHostToDevice, up_stream),
+                         "modtilt params upload")) return -1;
+            const unsigned blocks = (unsigned)std::min<size_t>((rows + 255) / 256, (size_t)n_sm * 8);
+            modtilt_param_kernel<<<blocks, 256, 0, up_stream>>>(d_raw2[buf], d_coef2[buf], rows, grid, d_tab, d_tab + grid.n[0], d_tab + grid.n[0] + grid.n[1]);
+            if (!cuda_ok(cudaGetLastError(), "modtilt param kernel")) return -1;
+            ++I.launches;
+            cudaEventRecord(ev_ready[buf], up_stream);
+            cudaStreamWaitEvent(I.stream, ev_ready[buf], 0);
+            const int64_t f0 = b0 * bl, f1 = std::min<int64_t>(n, b1 * bl);
+            if (!launch(I, d_coef2[buf], rows_here, in + f0, out + f0, f1 - f0, stride)) return -1;
+            cudaEventRecord(ev_consumed[buf], I.stream);
+        }
+        return 1;
     }
 
-    bool launch(Instance& I, int nbq, const float* in, float* out, int64_t n, int64_t stride)
+    bool launch(Instance& I, const MTCoef* coef, int nbq, const float* in, float* out, int64_t n, int64_t stride)
     {
         MTArgs a{};
         a.in = in; a.out = out; a.row_stride = stride; a.n_frames = n;
-        a.n_streams = I.n_streams; a.block_len = I.block_len; a.n_coef_blocks = nbq; a.coef = d_coef; a.state = d_state;
+        a.n_streams = I.n_streams; a.block_len = I.block_len; a.n_coef_blocks = nbq; a.coef = coef; a.state = d_state;
         a.a_env = a_from_hz(25.0f, fs); a.a_base = a_from_hz(1.0f, fs); a.a_trim = a_from_hz(0.2f, fs);   // :35-36,40
         // option "warps_per_stream" = streams per warp (4 / 8 / 16 / 32) + 100 x frames per run (default 8; 4 / 16 / 32 are measurement variants)
         const int ol = I.opt_warps % 100, run = I.opt_warps / 100 ? I.opt_warps / 100 : 8;
@@ -176,7 +215,7 @@ public:
             if (modtilt_scan_ok(S.a)) {
                 S.K = scanK; S.qfix = d_q; S.qpiv = d_q + 4 * 32;
                 const bool timed = I.time_begin();
-                if (!modtilt_scan_launch(S, I.stream)) return false;
+                if (!modtilt_scan_launch(S, I.stream, I.opt_nbuf == 2)) return false;     // option "tile_buffers" = 2: the correctly rounded maps (measurement / cross-check)
                 if (timed) I.time_end();
                 ++I.launches;
                 n_main = S.a.n_frames;
@@ -250,8 +289,11 @@ public:
             coef_valid = h_coef.size() <= (1u << 20);
             if (coef_valid) h_coef_dev = h_coef;
         }
-        return launch(I, nbq, in, out, n, stride);
+        return launch(I, d_coef, nbq, in, out, n, stride);
     }
+
+    void state_io(Instance& I, StateIO& io) override { io.dev(d_state, (size_t)kMTState * I.n_streams * sizeof(float)); }
+    bool after_state_load(Instance&) override { coef_valid = false; return true; }
 
     bool read_state(Instance& I, const char* name, double* out) override
     {

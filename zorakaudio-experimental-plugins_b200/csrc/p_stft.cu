@@ -131,6 +131,13 @@ public:
         return true;
     }
 
+    void state_io(Instance& I, StateIO& io) override
+    {
+        io.dev(d_state, (size_t)I.n_streams * sizeof(StftState));
+        io.host(&t_abs, sizeof t_abs);                       // the hop phase (frames rendered since prepare)
+    }
+    bool after_state_load(Instance&) override { coef_valid = false; return true; }
+
     bool read_state(Instance& I, const char* name, double* out) override
     {
         // integer state of the script: hop_ctr, ringpos, frames_done follow from the frame count

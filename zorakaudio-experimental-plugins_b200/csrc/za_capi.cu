@@ -90,6 +90,37 @@ const PluginDesc* find_plugin(const char* key)
     return nullptr;
 }
 
+// ---- checkpoint visitor ---------------------------------------------------------------------------
+void StateIO::dev(void* d_ptr, size_t bytes)
+{
+    if (mode == Save && ok) ok = cuda_ok(cudaMemcpyAsync(blob + pos, d_ptr, bytes, cudaMemcpyDeviceToHost, stream), "state save");
+    if (mode == Load && ok) ok = cuda_ok(cudaMemcpyAsync(d_ptr, blob + pos, bytes, cudaMemcpyHostToDevice, stream), "state load");
+    pos += (bytes + 15) & ~(size_t)15;
+}
+void StateIO::host(void* h_ptr, size_t bytes)
+{
+    if (mode == Save) std::memcpy(blob + pos, h_ptr, bytes);
+    if (mode == Load) std::memcpy(h_ptr, blob + pos, bytes);
+    pos += (bytes + 15) & ~(size_t)15;
+}
+
+struct StateHeader {              // 64 bytes; everything a blob must agree on with the handle it is loaded into
+    char magic[8];                // "ZAGPUST1"
+    char key[32];
+    int32_t n_streams, block_len, precision, n_decl;
+    double srate;
+};
+
+static size_t state_walk(Instance& I, StateIO& io)
+{
+    io.pos = sizeof(StateHeader);
+    io.host(I.sliders.data(), I.sliders.size() * sizeof(double));
+    io.host(I.sliders_valid.data(), I.sliders_valid.size());
+    io.host(&I.prepared, sizeof(I.prepared));
+    I.impl->state_io(I, io);
+    return io.pos;
+}
+
 // ---- kernel timing ------------------------------------------------------------------------------
 bool Instance::time_begin()
 {
@@ -472,6 +503,50 @@ ZA_API int za_gpu_sync(za_gpu_handle h)
     cudaSetDevice(h->I.device);
     if (!cuda_ok(cudaStreamSynchronize(h->I.stream), "sync")) return ZA_ERR_CUDA;
     return h->I.impl && h->I.impl->deferred_error(h->I) ? ZA_ERR_STATE : ZA_OK;
+}
+ZA_API int za_gpu_state_size(za_gpu_handle h, size_t* bytes)
+{
+    if (!h || !bytes) return ZA_ERR_ARG;
+    StateIO io; io.mode = StateIO::Size;
+    *bytes = state_walk(h->I, io);
+    return ZA_OK;
+}
+ZA_API int za_gpu_state_save(za_gpu_handle h, void* blob, size_t bytes)
+{
+    if (!h || !blob) return ZA_ERR_ARG;
+    Instance& I = h->I;
+    if (!cuda_ok(cudaSetDevice(I.device), "cudaSetDevice")) return ZA_ERR_CUDA;
+    StateIO sz; sz.mode = StateIO::Size;
+    if (bytes < state_walk(I, sz)) { set_error("za_gpu_state_save: blob too small (za_gpu_state_size)"); return ZA_ERR_ARG; }
+    if (I.impl->deferred_error(I)) return ZA_ERR_STATE;
+    StateHeader hd{};
+    std::memcpy(hd.magic, "ZAGPUST1", 8);
+    std::strncpy(hd.key, I.desc->key, sizeof(hd.key) - 1);
+    hd.n_streams = I.n_streams; hd.block_len = I.block_len; hd.precision = I.precision; hd.n_decl = (int)I.decls.size(); hd.srate = I.srate;
+    std::memcpy(blob, &hd, sizeof hd);
+    StateIO io; io.mode = StateIO::Save; io.blob = (char*)blob; io.stream = I.stream;
+    state_walk(I, io);
+    if (!io.ok || !cuda_ok(cudaStreamSynchronize(I.stream), "state save sync")) return ZA_ERR_CUDA;
+    return ZA_OK;
+}
+ZA_API int za_gpu_state_load(za_gpu_handle h, const void* blob, size_t bytes)
+{
+    if (!h || !blob || bytes < sizeof(StateHeader)) return ZA_ERR_ARG;
+    Instance& I = h->I;
+    if (!cuda_ok(cudaSetDevice(I.device), "cudaSetDevice")) return ZA_ERR_CUDA;
+    StateHeader hd;
+    std::memcpy(&hd, blob, sizeof hd);
+    StateIO sz; sz.mode = StateIO::Size;
+    if (std::memcmp(hd.magic, "ZAGPUST1", 8) != 0 || std::strncmp(hd.key, I.desc->key, sizeof hd.key) != 0 || hd.n_streams != I.n_streams ||
+        hd.block_len != I.block_len || hd.precision != I.precision || hd.n_decl != (int)I.decls.size() || hd.srate != I.srate ||
+        bytes < state_walk(I, sz)) {
+        set_error("za_gpu_state_load: the blob was saved from a different plugin / batch shape / precision");
+        return ZA_ERR_ARG;
+    }
+    StateIO io; io.mode = StateIO::Load; io.blob = (char*)const_cast<void*>(blob); io.stream = I.stream;
+    state_walk(I, io);
+    if (!io.ok || !cuda_ok(cudaStreamSynchronize(I.stream), "state load sync")) return ZA_ERR_CUDA;
+    return I.impl->after_state_load(I) ? ZA_OK : ZA_ERR_CUDA;
 }
 ZA_API int za_gpu_host_alloc(size_t bytes, void** out)
 {

@@ -44,6 +44,19 @@ inline void parallel_for(int64_t n, int64_t grain, F&& f)
 
 struct Instance;
 
+// Checkpoint visitor (za_gpu_state_size / save / load): a plugin lists the buffers that ARE its per-stream DSP state --
+// device arrays and the few host scalars beside them (e.g. a hop phase) -- in a fixed order; derived data (coefficient
+// tables, scan tables) is rebuilt from the restored sliders by after_state_load().
+struct StateIO {
+    enum Mode { Size, Save, Load } mode = Size;
+    char* blob = nullptr;            // host blob cursor base
+    size_t pos = 0;
+    cudaStream_t stream = nullptr;
+    bool ok = true;
+    void dev(void* d_ptr, size_t bytes);
+    void host(void* h_ptr, size_t bytes);
+};
+
 // Per-plugin device back end.  All state lives in SoA device buffers owned by the implementation.
 // Streams [s0, s0+ns) may be driven independently of other ranges (host-memory pipelining).
 class PluginImpl {
@@ -57,6 +70,8 @@ public:
     virtual bool run(Instance& inst, int s0, int ns, const float* in, float* out, double* tap,
                      int64_t n, int64_t stride) = 0;
     virtual bool read_state(Instance& inst, const char* name, double* out) = 0;
+    virtual void state_io(Instance& inst, StateIO& io) = 0;                     // every buffer of the per-stream DSP state
+    virtual bool after_state_load(Instance&) { return true; }                   // rebuild what is derived from the sliders
     // Whole-call form for plugins that take per-block automation on the device: q = quantised slider
     // values [nbq][ns][n_decl] (host doubles, stream range s0..s0+ns), row b applies from host block b on,
     // the last row persists.  One launch renders all n frames; @slider semantics (recompute derived

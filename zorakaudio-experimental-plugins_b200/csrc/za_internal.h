@@ -109,7 +109,7 @@ struct MTArgs {
 namespace mtscan { struct Consts; }
 struct MTScanArgs;
 bool modtilt_scan_ok(const MTArgs& a);             // shape the scan kernel takes: host blocks of whole tiles, 16-byte aligned rows
-bool modtilt_scan_launch(const MTScanArgs& A, cudaStream_t stream);
+bool modtilt_scan_launch(const MTScanArgs& A, cudaStream_t stream, bool exact_maps = false);   // exact_maps: correctly rounded sqrt / div / log10 / 10^x
 int modtilt_pick_lanes(int n_streams, int n_sm);   // streams per warp: 8, 16 or 32
 bool modtilt_launch(const MTArgs& a, int lanes, cudaStream_t stream, int run = 8);   // run = frames per straight-line run
 

@@ -41,6 +41,7 @@ SYMBOLS = [
     "za_gpu_process_tap64", "za_gpu_read_state", "za_gpu_sync", "za_gpu_launch_count", "za_gpu_last_kernel_ms",
     "za_gpu_set_option", "za_gpu_render", "za_gpu_last_error", "za_gpu_device_count", "za_gpu_version",
     "za_gpu_synth", "za_gpu_synth_tables", "za_gpu_checksum", "za_gpu_host_alloc", "za_gpu_host_free",
+    "za_gpu_state_size", "za_gpu_state_save", "za_gpu_state_load",
 ]
 
 _lib = None
@@ -74,6 +75,9 @@ def lib() -> C.CDLL:
         L.za_gpu_last_kernel_ms.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int)]
         L.za_gpu_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
         L.za_gpu_render.argtypes = [C.c_char_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int64]
+        L.za_gpu_state_size.argtypes = [C.c_void_p, C.POINTER(C.c_size_t)]
+        L.za_gpu_state_save.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
+        L.za_gpu_state_load.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
         L.za_gpu_host_alloc.argtypes = [C.c_size_t, C.POINTER(C.c_void_p)]
         L.za_gpu_host_free.argtypes = [C.c_void_p]
         L.za_gpu_synth.argtypes = [C.c_int, C.c_uint32, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int64, C.c_int64, C.c_void_p,
@@ -235,6 +239,19 @@ class BatchProcessor:
         out = np.empty(self.n_streams, np.float64)
         _check(lib().za_gpu_read_state(self._h, name.encode(), out.ctypes.data), "za_gpu_read_state")
         return out
+
+    def save_state(self) -> np.ndarray:
+        """Checkpoint: the whole per-stream DSP state of the handle as one host blob (za_gpu_state_save)."""
+        n = C.c_size_t()
+        _check(lib().za_gpu_state_size(self._h, C.byref(n)), "za_gpu_state_size")
+        blob = np.zeros(n.value, np.uint8)
+        _check(lib().za_gpu_state_save(self._h, blob.ctypes.data, n.value), "za_gpu_state_save")
+        return blob
+
+    def load_state(self, blob: np.ndarray):
+        blob = np.ascontiguousarray(blob, np.uint8)
+        _check(lib().za_gpu_state_load(self._h, blob.ctypes.data, blob.size), "za_gpu_state_load")
+        return self
 
     def set_stream(self, cuda_stream_ptr):
         _check(lib().za_gpu_set_stream(self._h, cuda_stream_ptr), "za_gpu_set_stream")
