@@ -33,7 +33,7 @@ def _case(gpu, key, ns, nf, block, automate):
 
 
 @pytest.mark.parametrize("key,prec", [("cascade8", "f64"), ("cascade8", "f32"), ("EasyExpander", "f32"), ("EasyExpander", "f64"),
-                                      ("stft_mask2048", "f64"), ("RTT", "f64"), ("ModTilt", "f32")])
+                                      ("stft_mask2048", "f64"), ("RTT", "f64"), ("ModTilt", "f32"), ("ERBTilt", "f64"), ("ERBTilt", "f32")])
 def test_multi_chunk_host_render_equals_single_chunk(gpu, key, prec):
     block = 512
     ns, nf = 9, block * 13 + 131                     # ragged: the last chunk and the last block are short
@@ -175,7 +175,7 @@ def test_two_devices_render_their_shards(gpu):
 
 
 @pytest.mark.parametrize("key,prec", [("cascade8", "f32"), ("cascade8", "f64"), ("EasyExpander", "f64"), ("stft_mask2048", "f32"),
-                                      ("SOMA", "f64"), ("RTT", "f32"), ("ModTilt", "f32")])
+                                      ("SOMA", "f64"), ("RTT", "f32"), ("ModTilt", "f32"), ("ERBTilt", "f32"), ("ERBTilt", "f64")])
 def test_checkpoint_resume_is_bit_identical(gpu, key, prec):
     """za_gpu_state_save / za_gpu_state_load: a render interrupted after its first part and resumed in a FRESH handle from
     the saved blob continues bit-identically (outputs and, for translated leaves, the rand()-driven state included)."""

@@ -56,3 +56,82 @@ void emu_modtilt_scan(const float* coef, int n_blocks, int block_len, const floa
     }
     state5[0] = cy.env2; state5[1] = cy.base; state5[2] = cy.lp; state5[3] = cy.rs; state5[4] = cy.mean;
 }
+
+// ---- ERB Tilt: csrc/erbtilt_core.h on the host (same tile / prologue source as k_erbtilt.cu) ---------------------------------------
+#include "erbtilt_args.h"
+#include "erbtilt_tables.h"
+
+namespace {
+template <class T, int C>
+struct ErbHostIO {
+    const float* inL; const float* inR; float* outL; float* outR; double* tapL; double* tapR; int m;     // at the tile's first frame
+    void load(za::lanes::LV<T> (&l)[C], za::lanes::LV<T> (&r)[C]) const
+    {
+        for (int i = 0; i < C; ++i)
+            for (int lane = 0; lane < 32; ++lane) {
+                const bool live = lane < m;
+                l[i].v[lane] = live ? (T)inL[lane * C + i] : T(0); r[i].v[lane] = live ? (T)inR[lane * C + i] : T(0);
+            }
+    }
+    void store(const za::lanes::LV<T> (&l)[C], const za::lanes::LV<T> (&r)[C]) const
+    {
+        for (int i = 0; i < C; ++i)
+            for (int lane = 0; lane < m; ++lane) {
+                outL[lane * C + i] = (float)l[i].v[lane]; outR[lane * C + i] = (float)r[i].v[lane];
+                if (tapL) { tapL[lane * C + i] = (double)l[i].v[lane]; tapR[lane * C + i] = (double)r[i].v[lane]; }
+            }
+    }
+};
+
+template <class T, int CM>
+void erb_render(double srate, const double* q, int n_rows, int block_len, double* state, const float* in, float* out, double* tap,
+                long n_frames, long stride)
+{
+    using za::erb::Init; using za::erb::Tables; using za::erb::BlockVars; using za::erb::Block; using za::erb::kNB; using za::erb::kNBm1;
+    using za::erb::build_filterbank; using za::erb::build_tables; using za::erb::block_prologue;
+    const Init init = build_filterbank(srate);
+    static Tables<T, CM> tbm; static Tables<T, 1> tbt;
+    build_tables<T, CM>(init, tbm); build_tables<T, 1>(init, tbt);
+    za::erb::Carry<T> cy{};
+    auto ld = [&](za::lanes::LV<T>& v, int slot0, int n) { for (int l = 0; l < 32; ++l) v.v[l] = l < n ? (T)state[slot0 + l] : T(0); };
+    ld(cy.lpL, za::kErbLpL, kNBm1); ld(cy.lpR, za::kErbLpR, kNBm1); ld(cy.envF, za::kErbEnvF, kNB); ld(cy.envS, za::kErbEnvS, kNB);
+    ld(cy.preE, za::kErbPreE, kNB); ld(cy.postE, za::kErbPostE, kNB);
+    BlockVars bv{}; bv.global_gain = state[za::kErbGlobalGain];
+    Block<T> bk{};
+    long pos = 0;
+    for (int blk = 0; pos < n_frames; ++blk) {
+        const int nb = (int)std::min<long>(block_len, n_frames - pos);
+        const int row = blk < n_rows ? blk : n_rows - 1;
+        const double alpha = std::exp(-(double)nb / (init.gain_tau * srate + 0.000001));
+        block_prologue<T>(init.bc, q + (size_t)row * 4, alpha, cy, bv, bk);
+        int f = 0;
+        for (; f + 32 * CM <= nb; f += 32 * CM) {
+            const long g0 = pos + f;
+            ErbHostIO<T, CM> io{in + g0, in + stride + g0, out + g0, out + stride + g0, tap ? tap + g0 : nullptr, tap ? tap + stride + g0 : nullptr, 32};
+            za::erb::tile<T, CM, false>(tbm, cy, bk, 32, io);
+        }
+        for (; f < nb; f += 32) {
+            const int m = std::min(32, nb - f);
+            const long g0 = pos + f;
+            ErbHostIO<T, 1> io{in + g0, in + stride + g0, out + g0, out + stride + g0, tap ? tap + g0 : nullptr, tap ? tap + stride + g0 : nullptr, m};
+            za::erb::tile<T, 1, false>(tbt, cy, bk, m, io);
+        }
+        pos += nb;
+    }
+    auto st = [&](const za::lanes::LV<T>& v, int slot0, int n) { for (int l = 0; l < n; ++l) state[slot0 + l] = (double)v.v[l]; };
+    st(cy.lpL, za::kErbLpL, kNBm1); st(cy.lpR, za::kErbLpR, kNBm1); st(cy.envF, za::kErbEnvF, kNB); st(cy.envS, za::kErbEnvS, kNB);
+    st(cy.preE, za::kErbPreE, kNB); st(cy.postE, za::kErbPostE, kNB);
+    state[za::kErbGlobalGain] = bv.global_gain;
+}
+}
+
+// q [n_rows][4] quantised sliders; state [kErbSlots] doubles (zero + global_gain = 1 after prepare); f64 = 1: double arithmetic.
+extern "C" __attribute__((visibility("default")))
+void emu_erbtilt(double srate, const double* q, int n_rows, int block_len, double* state, const float* in, float* out, double* tap,
+                 long n_frames, long stride, int f64)
+{
+    _MM_SET_FLUSH_ZERO_MODE(_MM_FLUSH_ZERO_ON);
+    _MM_SET_DENORMALS_ZERO_MODE(_MM_DENORMALS_ZERO_ON);
+    if (f64) erb_render<double, za::kErbChunkF64>(srate, q, n_rows, block_len, state, in, out, tap, n_frames, stride);
+    else erb_render<float, za::kErbChunkF32>(srate, q, n_rows, block_len, state, in, out, tap, n_frames, stride);
+}

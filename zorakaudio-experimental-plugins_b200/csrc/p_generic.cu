@@ -3,6 +3,7 @@
 // processBlock as one kernel launch each (jsfx_rt.cuh).  The quantised automation rows of a call are uploaded
 // as doubles; @init / @slider / @block / @sample all run on the device.
 #include <cstring>
+#include <string>
 
 #include "za_host.h"
 #include "gen/gen_list.h"
@@ -173,7 +174,12 @@ ZA_GEN_PLUGINS(ZA_X)
 
 void append_generated_plugins(std::vector<PluginDesc>& t)
 {
-#define ZA_X(IDENT) { const GenDesc* d = jsfx::desc_##IDENT(); t.push_back(PluginDesc{d->key, d->n_in, d->n_out, 0, 0, d->slider_text, &make_gen_##IDENT}); }
+    // A leaf that also has a hand-written kernel class keeps its machine translation under "<key>.translated" (cross-check)
+    static std::vector<std::string> names;
+    names.reserve(64);
+#define ZA_X(IDENT) { const GenDesc* d = jsfx::desc_##IDENT(); bool taken = false; for (const auto& e : t) taken = taken || !std::strcmp(e.key, d->key); \
+                      names.push_back(std::string(d->key) + (taken ? ".translated" : "")); \
+                      t.push_back(PluginDesc{names.back().c_str(), d->n_in, d->n_out, 0, 0, d->slider_text, &make_gen_##IDENT}); }
     ZA_GEN_PLUGINS(ZA_X)
 #undef ZA_X
 }

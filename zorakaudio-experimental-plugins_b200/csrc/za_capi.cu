@@ -65,6 +65,7 @@ const char* cascade8_slider_text();
 const char* easyexpander_slider_text();
 const char* stft_mask2048_slider_text();
 const char* modtilt_slider_text();
+const char* erbtilt_slider_text();
 
 void append_generated_plugins(std::vector<PluginDesc>& t);    // p_generic.cu: the translated DSP-JSFX leaves
 
@@ -76,6 +77,7 @@ const std::vector<PluginDesc>& plugin_table()
             {"EasyExpander", 2, 2, 0, 0, easyexpander_slider_text(), &make_easyexpander},
             {"stft_mask2048", 2, 2, 2, 2048, stft_mask2048_slider_text(), &make_stft_mask2048},
             {"ModTilt", 2, 2, 1, 0, modtilt_slider_text(), &make_modtilt},
+            {"ERBTilt", 2, 2, 0, 0, erbtilt_slider_text(), &make_erbtilt},
         };
         append_generated_plugins(v);
         return v;

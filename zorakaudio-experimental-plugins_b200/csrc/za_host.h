@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <algorithm>
+#include <cstring>
 #include <memory>
 #include <string>
 #include <thread>
@@ -126,7 +127,20 @@ struct Instance {
     cudaEvent_t ev_h2d[3] = {}, ev_comp[3] = {}, ev_d2h[3] = {};
 };
 
+// Device copy of a call's parameter rows as quantised doubles [rows][n_sliders] (k_params.cu).
+struct RawRows {
+    float* d_raw = nullptr; double* d_q = nullptr; size_t cap = 0;      // cap counts values
+    cudaStream_t up = nullptr; cudaEvent_t ev_ready = nullptr, ev_consumed = nullptr;
+    std::vector<double> last;                                           // host-quantised rows currently on the device
+    ~RawRows();
+    const double* upload(Instance& I, const float* raw_host_rows, size_t rows);          // raw floats -> device quantiser; I.stream waits for it
+    const double* upload_quantised(Instance& I, const double* q, size_t count);          // host-quantised doubles (skipped when unchanged)
+    void consumed(Instance& I);                                                          // call after the kernel that read the rows was launched
+    void invalidate() { last.clear(); }
+};
+
 PluginImpl* make_cascade8();
+PluginImpl* make_erbtilt();
 PluginImpl* make_easyexpander();
 PluginImpl* make_stft_mask2048();
 PluginImpl* make_modtilt();

@@ -113,6 +113,12 @@ bool modtilt_scan_launch(const MTScanArgs& A, cudaStream_t stream, bool exact_ma
 int modtilt_pick_lanes(int n_streams, int n_sm);   // streams per warp: 8, 16 or 32
 bool modtilt_launch(const MTArgs& a, int lanes, cudaStream_t stream, int run = 8);   // run = frames per straight-line run
 
+// ---- ERB Tilt (IIR class, hand-written scan kernel: k_erbtilt.cu / erbtilt_core.h) -------------------------------------
+constexpr int kErbChunkF32 = 8, kErbChunkF64 = 4;       // frames per lane of a main tile (tile = 32 x chunk frames)
+// state slots, [slot][stream] doubles: the script's mem[] arrays lpL, lpR, envF, envS, preE, postE, then block-rate variables
+constexpr int kErbLpL = 0, kErbLpR = 15, kErbEnvF = 30, kErbEnvS = 46, kErbPreE = 62, kErbPostE = 78, kErbGlobalGain = 94,
+              kErbGBand = 106, kErbSlots = 122;
+
 // ---- translated DSP-JSFX leaves (csrc/gen/g_*.cu from za_gpu/jsfxc.py, runtime in jsfx_rt.cuh) -------------------
 struct GenLaunch {
     const float* in; float* out; double* tap;      // [stream][ch][row_stride]
