@@ -80,8 +80,38 @@ def build_one(key: str, force: bool = False) -> Path | None:
     return so
 
 
+def build_shadow(force: bool = False) -> Path | None:
+    """The secondary oracle: oracle/shadow_eel.cpp over the reference's own WDL EEL2 interpreter (portable target), compiled
+    from /root/reference/src/WDL where it lies into oracle/_ref/libshadow_eel.so."""
+    so = OUT / "libshadow_eel.so"
+    src = HERE / "shadow_eel.cpp"
+    wdl = REF / "src" / "WDL"
+    if not REF.exists() or not (wdl / "eel2" / "nseel-compiler.c").exists():
+        return so if so.exists() else None
+    if not force and _newer(so, src):
+        return so
+    OUT.mkdir(exist_ok=True)
+    objs = []
+    flags = ["-O2", "-fPIC", "-DEEL_TARGET_PORTABLE=1", "-DWDL_FFT_REALSIZE=8", f"-I{REF / 'src'}", "-w"]
+    for name in ("nseel-compiler", "nseel-eval", "nseel-lextab", "nseel-ram", "nseel-yylex", "nseel-cfunc"):
+        o = OUT / f"eel2_{name}.o"
+        subprocess.run(["gcc", *flags, "-c", str(wdl / "eel2" / f"{name}.c"), "-o", str(o)], check=True)
+        objs.append(str(o))
+    o = OUT / "eel2_fft.o"
+    subprocess.run(["gcc", *flags, "-c", str(wdl / "fft.c"), "-o", str(o)], check=True)
+    objs.append(str(o))
+    subprocess.run(["g++", *flags, "-std=c++17", "-fvisibility=hidden", "-shared", str(src), *objs, "-o", str(so), "-lm"], check=True)
+    return so
+
+
 def build_all(keys=None, force: bool = False) -> dict:
     res = {}
+    if keys is None:
+        try:
+            res["shadow_eel"] = build_shadow(force)
+        except subprocess.CalledProcessError as e:
+            print(f"[build_ref] shadow_eel: FAILED ({e})", file=sys.stderr)
+            res["shadow_eel"] = None
     for k in (keys or PLUGINS):
         try:
             res[k] = build_one(k, force)

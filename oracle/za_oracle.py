@@ -277,6 +277,73 @@ class RefInstance:
             self.h = None
 
 
+class ShadowPlugin:
+    """The SECONDARY oracle: the plugin's .jsfx source run by the reference's own WDL EEL2 interpreter (oracle/shadow_eel.cpp,
+    built into oracle/_ref/libshadow_eel.so), driven like the reference's --correctness-check shadow VM.  One stream at a
+    time (the interpreter is ~18x slower than the compiled path)."""
+
+    def __init__(self, key: str, source_text: str, n_in: int, n_out: int, sliders=None):
+        so = REF_DIR / "libshadow_eel.so"
+        if not so.exists():
+            raise FileNotFoundError(f"{so} (run oracle/build_ref.py where /root/reference exists)")
+        # EEL2's rand() keeps ONE process-global Mersenne state (a function-static in nseel-cfunc.c), the compiled path one per
+        # instance (dsp_jsfx_aot.py:5302-5305): every ShadowPlugin loads its own private copy of the library, so a script
+        # that calls rand() starts from the generator's initial state like a fresh compiled instance does (render once).
+        import shutil
+        import tempfile
+        self._tmp = tempfile.NamedTemporaryFile(prefix="libshadow_eel_", suffix=".so", delete=False)
+        self._tmp.close()
+        shutil.copyfile(so, self._tmp.name)
+        self.lib = L = C.CDLL(self._tmp.name)
+        L.zsh_new.restype = C.c_void_p
+        L.zsh_new.argtypes = [C.c_char_p, C.c_void_p, C.c_void_p]
+        L.zsh_error.restype = C.c_char_p
+        L.zsh_error.argtypes = [C.c_void_p]
+        L.zsh_free.argtypes = [C.c_void_p]
+        L.zsh_prepare.argtypes = [C.c_void_p, C.c_double, C.c_void_p]
+        L.zsh_process_block.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int]
+        L.zsh_var.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_double)]
+        self.key, self.n_in, self.n_out = key, n_in, n_out
+        self.sliders = sliders if sliders is not None else parse_sliders(source_text)
+        self.layout = make_layout(self.sliders, lambda name: -1)
+        names = (C.c_char_p * 64)(*[(s["var"].encode() if s["var"] else None) for s in self.sliders])
+        self.h = L.zsh_new(source_text.encode("utf-8", "replace"), C.byref(self.layout), names)
+        err = L.zsh_error(self.h).decode()
+        if err:
+            raise RuntimeError(f"shadow EEL2 compile of {key}: {err}")
+
+    def render_one(self, params, x, srate=48000.0, block=512):
+        """params [n_sliders] or [n_blocks][n_sliders]; x [n_in][n_frames] -> (y f32, y f64) [n_out][n_frames]."""
+        x = np.ascontiguousarray(x, np.float32)
+        nf = x.shape[1]
+        p = np.ascontiguousarray(params, np.float32)
+        p = p[None] if p.ndim == 1 else p
+        assert self.lib.zsh_prepare(self.h, srate, p[0].ctypes.data) == 0, self.lib.zsh_error(self.h)
+        y, yd = np.zeros((self.n_out, nf), np.float32), np.zeros((self.n_out, nf), np.float64)
+        PF, PD = C.POINTER(C.c_float), C.POINTER(C.c_double)
+        for b, f0 in enumerate(range(0, nf, block)):
+            n = min(block, nf - f0)
+            ins = (PF * max(self.n_in, 1))(*[C.cast(x[c, f0:].ctypes.data, PF) for c in range(self.n_in)])
+            outs = (PF * self.n_out)(*[C.cast(y[c, f0:].ctypes.data, PF) for c in range(self.n_out)])
+            outd = (PD * self.n_out)(*[C.cast(yd[c, f0:].ctypes.data, PD) for c in range(self.n_out)])
+            row = p[min(b, len(p) - 1)]
+            self.lib.zsh_process_block(self.h, row.ctypes.data, ins, outs, outd, self.n_in, self.n_out, n)
+        return y, yd
+
+    def var(self, name: str) -> float:
+        out = C.c_double()
+        return out.value if self.lib.zsh_var(self.h, name.encode(), C.byref(out)) == 0 else float("nan")
+
+    def close(self):
+        if self.h:
+            self.lib.zsh_free(self.h)
+            self.h = None
+        try:
+            os.unlink(self._tmp.name)
+        except OSError:
+            pass
+
+
 def have_ref(key: str) -> bool:
     return (REF_DIR / f"libref_{key}.so").exists()
 

@@ -196,3 +196,30 @@ def test_erbtilt_scan_kernel_against_its_translation(gpu):
     assert np.array_equal(o2, out)
     assert np.allclose(bp.read_state("preE[3]"), bp.read_state("preE[3]"))
     bp.close()
+
+
+@pytest.mark.parametrize("key", ["RTT", "SOMA", "semprobe"])
+def test_device_quantiser_equals_host_quantiser(gpu, key):
+    """Automation rows of translated leaves are quantised on the device (k_params.cu::quantise_rows_kernel) by default;
+    `force_generic_io` takes the host quantiser (za_params.cpp).  Off-grid, out-of-range and choice-slider values: the two
+    paths must give identical output bits."""
+    ref = zo.RefPlugin(key)
+    ns, nf = 9, 512 * 12 + 100
+    x = wl.programme_bursts(ns, nf, n_ch=ref.n_in)
+    base = np.array([s["default"] for s in ref.sliders], np.float32)
+    nb = (nf + 511) // 512
+    rng = np.random.default_rng(5)
+    p = np.tile(base, (nb, ns, 1)).astype(np.float32)
+    for j, s in enumerate(ref.sliders):
+        span = float(s["max"] - s["min"])
+        p[:, :, j] = (s["min"] - 0.1 * span + rng.random((nb, ns)) * 1.2 * span).astype(np.float32)     # off grid, 10 % beyond both ends
+    outs = []
+    for host in (0, 1):
+        bp = gpu.BatchProcessor(key, ns, precision="f64")
+        bp.set_option("force_generic_io", host)
+        bp.prepare(p[0])
+        outs.append(bp.process(x, params=p))
+        bp.close()
+    assert np.array_equal(outs[0], outs[1], equal_nan=True)
+    y, _ = ref.render(p, x)
+    assert np.mean(outs[0] == y) > 0.999

@@ -134,6 +134,25 @@ public:
         return cuda_ok(cudaMemcpyAsync(h_err, d_err, sizeof(int), cudaMemcpyDeviceToHost, I.stream), "err mirror copy");
     }
 
+    // Whole-call automation without a host pass: the raw float rows are uploaded on a side stream and quantised by
+    // quantise_rows_kernel (k_params.cu) with the host quantiser's own operations.
+    RawRows rows_;
+    int run_blocks_raw(Instance& I, const float* params, int nbq, const float* in, float* out, double* tap, int64_t n, int64_t stride) override
+    {
+        if (I.opt_force_generic) return 0;                      // "force_generic_io": the host quantiser path (tests compare the two)
+        const double* dq = rows_.upload(I, params, (size_t)nbq * I.n_streams);
+        if (!dq) return -1;
+        q_last.clear();
+        GenLaunch a = base(I);
+        a.in = in; a.out = out; a.tap = tap; a.row_stride = stride; a.n_frames = n; a.q = dq; a.n_rows = nbq;
+        const bool timed = I.time_begin();
+        if (!d_->process(a, I.precision, I.stream)) return -1;
+        if (timed) I.time_end();
+        ++I.launches;
+        rows_.consumed(I);
+        return cuda_ok(cudaMemcpyAsync(h_err, d_err, sizeof(int), cudaMemcpyDeviceToHost, I.stream), "err mirror copy") ? 1 : -1;
+    }
+
     bool deferred_error(Instance&) override
     {
         if (!h_err || *(volatile int*)h_err == 0) return false;
