@@ -70,6 +70,12 @@ WORKLOADS = {
     "specstab": dict(plugin="SpectralStabilizer", streams=4096, seconds=10.0, ch=(2, 2), automate=[1], cpu=(256, 5.0), synth=1,
                      kernel={"f32": "specstab / jsfx_process_kernel", "f64": "specstab / jsfx_process_kernel"},
                      text="Spectral Stabilizer (12 band-pass biquads x 2 ch + per-band gain smoothing), {ns} stereo streams x {sec:g} s @ 48 kHz per GPU, depth automated every 512-frame block"),
+    "gts": dict(plugin="GTS", streams=4096, seconds=10.0, ch=(2, 2), automate=[0, 1], cpu=(64, 2.0), f32_only=True, synth=1,
+                kernel={"f32": "gts_kernel"},
+                text="Faust leaf GTS (257-tap Gaussian FIR rebuilt every sample from a smoothed sigma), {ns} stereo streams x {sec:g} s @ 48 kHz per GPU, sigma/attack automated every 512-frame block"),
+    "var": dict(plugin="VAR", streams=4096, seconds=10.0, ch=(2, 2), automate=[0], cpu=(256, 5.0), f32_only=True, synth=1,
+                kernel={"f32": "faust_leaf_kernel"},
+                text="Faust leaf VAR (4 biquads x 2 ch + curvature detector + switching follower), {ns} stereo streams x {sec:g} s @ 48 kHz per GPU, amount automated every 512-frame block"),
     "rtt": dict(plugin="RTT", streams=4096, seconds=10.0, ch=(8, 2), automate=[0, 1], cpu=(256, 5.0), synth=1,
                 kernel={"f32": "jsfx_process_kernel", "f64": "jsfx_process_kernel"},
                 text="cfg3 on RTT (Reverb Tail Tamer, 8 in / 2 out), {ns} streams x {sec:g} s @ 48 kHz per GPU, amount/sensitivity automated every 512-frame block"),

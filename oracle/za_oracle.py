@@ -178,6 +178,26 @@ CATALOG_SLIDERS = {
         "slider1:tilt_db=0<-6,3,0.1>Tilt (dB)\n"
         "slider2:pivot_hz=3<2,5,0.01>Pivot (Hz)\n"
         "slider3:mix=1<0,1,0.001>Mix\n"),
+    "RED": (                                                   # RED.dsp:8-10
+        "slider1:amount_db=12<0,24,0.1>Amount (max duck dB)\n"
+        "slider2:sens_pct=50<0,100,1>Sensitivity (%)\n"
+        "slider3:rel_ms=350<50,1200,1>Release (ms)\n"),
+    "ClickBeGoneSG": (                                         # Click-Be-Gone (SG).dsp:11-15
+        "slider1:amount=50<0,100,1>Amount [%]\n"
+        "slider2:sensitivity=50<0,100,1>Sensitivity [%]\n"
+        "slider3:hpf_hz=1500<300,6000,10>HPF [Hz]\n"
+        "slider4:mode=1<0,2,1{Fast,Medium,Slow}>Mode\n"
+        "slider5:monitor=0<0,1,1{Output,Delta}>Monitor\n"),
+    "VAR": (                                                   # VAR.dsp:88-90
+        "slider1:amount=35<0,100,1>Air Amount [%]\n"
+        "slider2:sens=50<0,100,1>Sensitivity [%]\n"
+        "slider3:floor_db=-60<-90,-30,1>Detector Floor [dB]\n"),
+    "GTS": (                                                   # GTS.dsp:52-64
+        "slider1:sigma_ms=2<0.1,8,0.01>Gaussian Sigma [ms]\n"
+        "slider2:attack_db=0<-12,12,0.1>Attack Gain [dB]\n"
+        "slider3:sustain_db=0<-12,12,0.1>Sustain Gain [dB]\n"
+        "slider4:mix=1<0,1,0.01>Mix\n"
+        "slider5:out_db=0<-12,12,0.1>Output Gain [dB]\n"),
 }
 
 
@@ -355,7 +375,7 @@ PORT_SO = HERE / "libza_oracle_port.so"
 
 
 FAUST_PORT_SO = HERE / "libza_faust_port.so"
-FAUST_KEYS = ("ModTilt",)            # Faust leaves: restatement only (parity unpinned, see za_faust_port.c)
+FAUST_KEYS = ("ModTilt", "RED", "ClickBeGoneSG", "VAR", "GTS")            # Faust leaves: restatement only (parity unpinned, see za_faust_port.c)
 
 
 def build_faust_port(force: bool = False) -> Path:
@@ -380,7 +400,8 @@ def build_port(force: bool = False) -> Path:
 class PortPlugin:
     """Plain-C restatement of one plugin; same render() contract as RefPlugin."""
 
-    CHANNELS = {"cascade8": (1, 1), "EasyExpander": (2, 2), "stft_mask2048": (2, 2), "ModTilt": (2, 2)}
+    CHANNELS = {"cascade8": (1, 1), "EasyExpander": (2, 2), "stft_mask2048": (2, 2), "ModTilt": (2, 2),
+                "RED": (6, 6), "ClickBeGoneSG": (2, 2), "VAR": (2, 2), "GTS": (2, 2)}
 
     def __init__(self, key: str, sliders=None, var_index=None):
         self.key = key

@@ -1,0 +1,88 @@
+"""GPU parity tests for the Faust leaves RED, ClickBeGoneSG, VAR (generic stream-per-thread kernel, p_faust.cu) and GTS
+(time-parallel kernel, k_gts.cu): the CUDA path through the C ABI against the float32 CPU restatements
+(oracle/za_faust_port.c -- PARITY UNPINNED) on the same seeded inputs.
+Criterion: fp32 residual below -100 dBFS RMS; parameter changes on the exact host block for any block length; state
+carried across calls; ZA_F64 refused."""
+import numpy as np
+import pytest
+
+import za_oracle as zo
+from za_gpu import workloads as wl
+from parity import dbfs_rms
+
+pytestmark = pytest.mark.gpu
+KEYS = ["RED", "ClickBeGoneSG", "VAR", "GTS"]
+
+
+@pytest.fixture(scope="module")
+def gpu(built_lib):
+    import za_gpu
+    if za_gpu.lib().za_gpu_device_count() < 1:
+        pytest.fail("GPU test run without a CUDA device")
+    return za_gpu
+
+
+def make_input(key, port, ns, nf):
+    x = wl.programme_bursts(ns, nf, n_ch=port.n_in)
+    if key == "RED":                                                        # loud dense wet signal, reference mostly quiet: the leaf ducks
+        x[:, 0:2] = 0.3 * np.sign(x[:, 0:2]) * np.abs(x[:, 0:2]) ** 0.3
+        x[:, 4:6] *= np.where((np.arange(nf) // 12000) % 2 == 0, 0.001, 1.0).astype(np.float32)
+    if key == "ClickBeGoneSG":                                              # needle clicks on programme material
+        rng = np.random.default_rng(3)
+        for s in range(ns):
+            for f in rng.choice(nf - 100, size=max(3, nf // 4000), replace=False) + 50:
+                x[s, :, f] += rng.choice([-0.6, 0.6])
+    return x
+
+
+@pytest.mark.parametrize("key", KEYS)
+@pytest.mark.parametrize("ns,nf,block,automate", [(37, 24000 + 77, 512, True), (5, 9000 + 1, 100, True), (70, 6000, 7, False), (1, 31, 512, False)])
+def test_fp32_parity(gpu, key, ns, nf, block, automate):
+    port = zo.PortPlugin(key)
+    x = make_input(key, port, ns, nf)
+    base = np.array([s["default"] for s in port.sliders], np.float32)
+    if automate:
+        which = [0, 1, 2] if key != "ClickBeGoneSG" else [0, 1, 2, 3]
+        p = wl.automation(port.sliders, (nf + block - 1) // block, ns, which=which, base=base)
+    else:
+        p = np.tile(base, (ns, 1))
+    y, _ = port.render(p, x, block=block)
+    info = gpu.plugin_info(key)
+    assert (info.n_in, info.n_out, info.kind) == (port.n_in, port.n_out, 1)
+    bp = gpu.BatchProcessor(key, ns, 48000.0, block, "f32").prepare(p if p.ndim == 2 else p[0])
+    out = bp.process(x, params=p if p.ndim == 3 else None)
+    assert bp.launch_count() > 0
+    r = out.astype(np.float64) - y
+    print(f"{key} ns={ns} nf={nf} block={block}: residual {dbfs_rms(r):.1f} dBFS, equal {np.mean(out == y):.3f}")
+    assert dbfs_rms(r) < -100.0, dbfs_rms(r)
+    if nf >= 6000 and key != "VAR":
+        assert dbfs_rms(out.astype(np.float64) - x[:, :port.n_out]) > -80.0   # the effect did something: not a vacuous comparison
+    bp.close()
+
+
+@pytest.mark.parametrize("key", KEYS)
+def test_state_carries_across_calls_and_in_place(gpu, key):
+    port = zo.PortPlugin(key)
+    ns, nf, block = 9, 512 * 11 + 300, 512
+    x = make_input(key, port, ns, nf)
+    p = wl.automation(port.sliders, (nf + block - 1) // block, ns, which=[0, 1])
+    y, _ = port.render(p, x, block=block)
+    bp = gpu.BatchProcessor(key, ns, 48000.0, block, "f32").prepare(p[0])
+    cuts = [0, 512 * 3, 512 * 8, nf]
+    buf = x.copy()
+    parts = []
+    for a, b in zip(cuts[:-1], cuts[1:]):
+        seg = np.ascontiguousarray(buf[:, :, a:b])
+        parts.append(bp.process(seg, out=seg if port.n_in == port.n_out else None, params=p[a // block:]))      # in place
+    out = np.concatenate(parts, axis=2)
+    assert dbfs_rms(out.astype(np.float64) - y) < -100.0
+    bp.prepare(p[0])
+    whole = bp.process(x, params=p)
+    assert dbfs_rms(whole.astype(np.float64) - out) < -130.0
+    bp.close()
+
+
+def test_f64_refused(gpu):
+    for key in KEYS:
+        with pytest.raises(gpu.ZaError, match="float32"):
+            gpu.BatchProcessor(key, 4, precision="f64")

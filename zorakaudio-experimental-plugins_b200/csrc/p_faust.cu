@@ -1,0 +1,187 @@
+// p_faust.cu -- the sequential Faust leaves RED, ClickBeGoneSG and VAR behind the C ABI: one generic stream-per-thread
+// kernel over the leaf structs of faust_leaves.cuh plus its host half.  Path replaced: FaustJuceProcessor::prepareToPlay /
+// processBlock (src/FaustJuceProcessor.cpp:430-440, 463-482) around mydsp::init / mydsp::compute
+// (src/faust_support_min.h:41-53), for a batch of independent instances.  Float32 only (the reference builds Faust leaves
+// without -double); compiled with -fmad=false (za_gpu/build.py) so the .dsp's operation order is not contracted.
+//   * kernel: one warp per CTA, lane = stream, state in registers / local memory for the whole call; audio moves as
+//     [channels x 32 streams] x 32-frame tiles through shared memory so HBM sees 128-byte row segments (in == out legal);
+//   * slider-rate values (Faust's fSlow expressions) are evaluated on the HOST with the host libm once per (host block,
+//     stream) whose zone values changed, uploaded as rows;
+//   * zones: the quantised value narrowed to float (FaustJuceProcessor.cpp:467-471).
+// These leaves are sequential by nature (switching followers, max-hold envelopes, hysteresis): the kernel is
+// latency-bound at 4096 streams like every stream-per-thread kernel here; parity target = the float restatement
+// (oracle/za_faust_port.c, PARITY UNPINNED).
+#include <cstring>
+
+#include "za_host.h"
+#include "faust_leaves.cuh"
+
+namespace za {
+
+namespace {
+
+struct FaustArgs {
+    const float* in; float* out;
+    int64_t row_stride, n_frames;
+    int n_streams, block_len, n_rows;
+    const void* slow;           // [n_rows][n_streams] Leaf::Slow
+    unsigned* state;            // [words][n_streams]
+};
+
+constexpr int kP = 33;
+
+template <class L>
+__global__ void __launch_bounds__(32) faust_leaf_kernel(const FaustArgs a, const typename L::Konst k)
+{
+    constexpr int kCh = L::kIn > L::kOut ? L::kIn : L::kOut;
+    constexpr int kWords = (int)(sizeof(typename L::State) / 4);
+    __shared__ float tile[kCh * 32 * kP];
+    const int lane = threadIdx.x, s0 = blockIdx.x * 32, s = s0 + lane;
+    const bool live = s < a.n_streams;
+    const size_t ns = (size_t)a.n_streams;
+    typename L::State st;
+    unsigned* sw = reinterpret_cast<unsigned*>(&st);
+#pragma unroll 1
+    for (int w = 0; w < kWords; ++w) sw[w] = live ? a.state[(size_t)w * ns + s] : 0u;
+    const typename L::Slow* rows = reinterpret_cast<const typename L::Slow*>(a.slow);
+    typename L::Slow c = rows[live ? s : 0];
+    int blk = 0;
+    int64_t blk_end = a.block_len;
+    for (int64_t f0 = 0; f0 < a.n_frames; f0 += 32) {
+        const int nv = (int)min((int64_t)32, a.n_frames - f0);
+        for (int q = 0; q < 32 * L::kIn; ++q) {                 // row q of the CTA: stream q / kIn, channel q % kIn; lane = frame
+            const int si = q / L::kIn, ch = q - si * L::kIn;
+            const bool ok = s0 + si < a.n_streams && lane < nv;
+            tile[(ch * 32 + si) * kP + lane] = ok ? a.in[((size_t)(s0 + si) * L::kIn + ch) * a.row_stride + f0 + lane] : 0.0f;
+        }
+        __syncwarp();
+        if (live) {
+            for (int f = 0; f < nv; ++f) {
+                if (f0 + f >= blk_end) {                        // a new host block: its slider-rate row (the last row persists)
+                    ++blk; blk_end += a.block_len;
+                    c = rows[(size_t)(blk < a.n_rows ? blk : a.n_rows - 1) * ns + s];
+                }
+                float iv[L::kIn], ov[L::kOut];
+#pragma unroll
+                for (int ch = 0; ch < L::kIn; ++ch) iv[ch] = tile[(ch * 32 + lane) * kP + f];
+                L::frame(st, c, k, iv, ov);
+#pragma unroll
+                for (int ch = 0; ch < L::kOut; ++ch) tile[(ch * 32 + lane) * kP + f] = ov[ch];
+            }
+        }
+        __syncwarp();
+        for (int q = 0; q < 32 * L::kOut; ++q) {
+            const int si = q / L::kOut, ch = q - si * L::kOut;
+            if (s0 + si < a.n_streams && lane < nv)
+                a.out[((size_t)(s0 + si) * L::kOut + ch) * a.row_stride + f0 + lane] = tile[(ch * 32 + si) * kP + lane];
+        }
+        __syncwarp();
+    }
+    if (live)
+#pragma unroll 1
+        for (int w = 0; w < kWords; ++w) a.state[(size_t)w * ns + s] = sw[w];
+}
+
+template <class L>
+class FaustLeaf : public PluginImpl {
+    typename L::Konst k_{};
+    unsigned* d_state = nullptr;
+    typename L::Slow* d_slow = nullptr;
+    size_t slow_cap = 0;
+    std::vector<typename L::Slow> h_slow, h_slow_dev;
+    bool slow_valid = false;
+    float fs = 48000.0f;
+    static constexpr int kWords = (int)(sizeof(typename L::State) / 4);
+
+public:
+    ~FaustLeaf() override { cudaFree(d_state); cudaFree(d_slow); }
+
+    bool create(Instance& I) override
+    {
+        if (I.precision != ZA_F32) {
+            set_error(std::string(L::key()) + ": Faust leaves compute in float32 (no -double in the reference build); create it with ZA_F32");
+            I.create_status = ZA_ERR_UNSUPPORTED;
+            return false;
+        }
+        if ((int)I.decls.size() != L::kSliders) { set_error(std::string(L::key()) + ": slider layout mismatch"); return false; }
+        fs = std::fmin(192000.0f, std::fmax(1.0f, (float)(int)I.srate));      // ma.SR
+        L::konst(fs, k_);
+        return cuda_ok(cudaMalloc(&d_state, (size_t)kWords * I.n_streams * 4), "Faust leaf state");
+    }
+    bool reset(Instance& I) override    // mydsp::init -> instanceClear: every recursive signal starts at 0
+    {
+        slow_valid = false;
+        return cuda_ok(cudaMemsetAsync(d_state, 0, (size_t)kWords * I.n_streams * 4, I.stream), "Faust leaf reset");
+    }
+    bool sliders_changed(Instance&, int, int, const std::vector<int>&) override { return true; }
+    bool takes_block_params() const override { return true; }
+    bool run(Instance& I, int s0, int ns, const float* in, float* out, double* tap, int64_t n, int64_t stride) override
+    {
+        return run_blocks(I, s0, ns, &I.sliders[(size_t)s0 * I.decls.size()], 1, in, out, tap, n, stride);
+    }
+    bool run_blocks(Instance& I, int s0, int ns, const double* q, int nbq, const float* in, float* out, double* tap, int64_t n,
+                    int64_t stride) override
+    {
+        if (s0 != 0 || ns != I.n_streams) { set_error(std::string(L::key()) + ": stream sub-ranges are not supported"); return false; }
+        if (tap) { set_error(std::string(L::key()) + ": no double tap (float32 leaf)"); return false; }
+        constexpr int nd = L::kSliders;
+        h_slow.resize((size_t)nbq * ns);
+        parallel_for(ns, 64, [&](int64_t sb, int64_t se) {
+            for (int b = 0; b < nbq; ++b)
+                for (int64_t s = sb; s < se; ++s) {
+                    const double* sl = q + ((size_t)b * ns + s) * nd;
+                    typename L::Slow& c = h_slow[(size_t)b * ns + s];
+                    if (b > 0 && std::memcmp(sl, sl - (size_t)ns * nd, sizeof(double) * nd) == 0) { c = h_slow[(size_t)(b - 1) * ns + s]; continue; }
+                    float z[nd];
+                    for (int j = 0; j < nd; ++j) z[j] = (float)sl[j];              // *zone = (FAUSTFLOAT) value
+                    L::slow(z, fs, c);
+                }
+        });
+        const bool same = slow_valid && h_slow.size() == h_slow_dev.size() &&
+                          std::memcmp(h_slow.data(), h_slow_dev.data(), h_slow.size() * sizeof(typename L::Slow)) == 0;
+        if (!same) {
+            slow_valid = false;
+            if (h_slow.size() > slow_cap) {
+                cudaFree(d_slow); d_slow = nullptr; slow_cap = 0;
+                if (!cuda_ok(cudaMalloc(&d_slow, h_slow.size() * sizeof(typename L::Slow)), "Faust leaf rows")) return false;
+                slow_cap = h_slow.size();
+            }
+            if (!cuda_ok(cudaMemcpyAsync(d_slow, h_slow.data(), h_slow.size() * sizeof(typename L::Slow), cudaMemcpyHostToDevice, I.stream), "Faust leaf rows upload"))
+                return false;
+            slow_valid = h_slow.size() <= (1u << 20);
+            if (slow_valid) h_slow_dev = h_slow;
+        }
+        if (n <= 0) return true;
+        FaustArgs a{in, out, stride, n, I.n_streams, I.block_len, nbq, d_slow, d_state};
+        const bool timed = I.time_begin();
+        faust_leaf_kernel<L><<<(unsigned)((I.n_streams + 31) / 32), 32, 0, I.stream>>>(a, k_);
+        if (!cuda_ok(cudaGetLastError(), "faust_leaf_kernel")) return false;
+        if (timed) I.time_end();
+        ++I.launches;
+        return true;
+    }
+    void state_io(Instance& I, StateIO& io) override { io.dev(d_state, (size_t)kWords * I.n_streams * 4); }
+    bool after_state_load(Instance&) override { slow_valid = false; return true; }
+    bool read_state(Instance& I, const char* name, double* out) override     // "state[k]": word k of the leaf's State as float
+    {
+        int k = -1;
+        if (!std::strncmp(name, "state[", 6)) k = std::atoi(name + 6);
+        if (k < 0 || k >= kWords) { set_error(std::string(L::key()) + ": unknown state variable " + name); return false; }
+        std::vector<float> t((size_t)I.n_streams);
+        if (!cuda_ok(cudaStreamSynchronize(I.stream), "sync") ||
+            !cuda_ok(cudaMemcpy(t.data(), d_state + (size_t)k * I.n_streams, t.size() * 4, cudaMemcpyDeviceToHost), "state read")) return false;
+        for (int s = 0; s < I.n_streams; ++s) out[s] = (double)t[s];
+        return true;
+    }
+};
+
+}  // namespace
+
+PluginImpl* make_red() { return new FaustLeaf<faust::Red>(); }
+PluginImpl* make_clickbegonesg() { return new FaustLeaf<faust::Cbg>(); }
+PluginImpl* make_var() { return new FaustLeaf<faust::Var>(); }
+const char* red_slider_text() { return faust::Red::slider_text(); }
+const char* clickbegonesg_slider_text() { return faust::Cbg::slider_text(); }
+const char* var_slider_text() { return faust::Var::slider_text(); }
+
+}  // namespace za

@@ -66,6 +66,14 @@ const char* easyexpander_slider_text();
 const char* stft_mask2048_slider_text();
 const char* modtilt_slider_text();
 const char* erbtilt_slider_text();
+const char* red_slider_text();
+const char* clickbegonesg_slider_text();
+const char* var_slider_text();
+const char* gts_slider_text();
+PluginImpl* make_red();
+PluginImpl* make_clickbegonesg();
+PluginImpl* make_var();
+PluginImpl* make_gts();
 
 void append_generated_plugins(std::vector<PluginDesc>& t);    // p_generic.cu: the translated DSP-JSFX leaves
 
@@ -78,6 +86,10 @@ const std::vector<PluginDesc>& plugin_table()
             {"stft_mask2048", 2, 2, 2, 2048, stft_mask2048_slider_text(), &make_stft_mask2048},
             {"ModTilt", 2, 2, 1, 0, modtilt_slider_text(), &make_modtilt},
             {"ERBTilt", 2, 2, 0, 0, erbtilt_slider_text(), &make_erbtilt},
+            {"RED", 6, 6, 1, 0, red_slider_text(), &make_red},
+            {"ClickBeGoneSG", 2, 2, 1, 15, clickbegonesg_slider_text(), &make_clickbegonesg},
+            {"VAR", 2, 2, 1, 0, var_slider_text(), &make_var},
+            {"GTS", 2, 2, 1, 128, gts_slider_text(), &make_gts},
         };
         append_generated_plugins(v);
         return v;

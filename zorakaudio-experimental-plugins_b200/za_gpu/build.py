@@ -18,6 +18,10 @@ COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-fvisibility=hi
           "-ftz=false", "-prec-div=true", "-prec-sqrt=true"]
 
 
+# Faust leaves restate the .dsp's separate float multiplies and adds: no FMA contraction in those translation units
+PER_FILE = {"p_faust.cu": ["-fmad=false"], "k_gts.cu": ["-fmad=false"]}
+
+
 def sources():
     return sorted(list(CSRC.glob("*.cu")) + list(CSRC.glob("*.cpp")) + list((CSRC / "gen").glob("*.cu")))
 
@@ -37,7 +41,7 @@ def build_lib(force: bool = False, verbose: bool = False) -> Path:
         obj = BUILD / (src.stem + ".o")
         objs.append(obj)
         if force or _stale(obj, src):
-            cmd = [NVCC, *ARCH, *COMMON, "-x", "cu", "-c", str(src), "-o", str(obj)]
+            cmd = [NVCC, *ARCH, *COMMON, *PER_FILE.get(src.name, []), "-x", "cu", "-c", str(src), "-o", str(obj)]
             if verbose:
                 cmd.insert(1, "-Xptxas=-v")
             jobs.append(cmd)
