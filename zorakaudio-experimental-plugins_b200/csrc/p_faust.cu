@@ -10,7 +10,7 @@
 //   * zones: the quantised value narrowed to float (FaustJuceProcessor.cpp:467-471).
 // These leaves are sequential by nature (switching followers, max-hold envelopes, hysteresis): the kernel is
 // latency-bound at 4096 streams like every stream-per-thread kernel here; parity target = the float restatement
-// (oracle/za_faust_port.c, PARITY UNPINNED).
+// (the test-side C port of the .dsp; PARITY UNPINNED).
 #include <cstring>
 
 #include "za_host.h"
