@@ -149,6 +149,27 @@ ZA_API int za_gpu_set_option(za_gpu_handle h, const char* name, int value);
 ZA_API int za_gpu_render(const char* plugin_key, const float* param_block, const float* in, float* out,
                          int n_streams, int64_t n_frames);
 
+/* ---- serial plugin chains on the device -------------------------------- */
+/* n_plugins stages rendered one after the other for every stream, stage k's float32 output being stage k + 1's input
+ * without leaving the GPU -- what a host does when it hands one AudioBuffer<float> from plugin to plugin
+ * (src/JSFXJuceProcessor.cpp:3456-3528).  Routing: input channel c of stage k > 0 = output channel c of stage k - 1 where
+ * that exists, else channel c of the CHAIN input (side-chain keys, e.g. RTT's channels 4-7,
+ * plugins/Dynamics/RTT/src/Reverb Tail Tamer.jsfx:3-6), else silence.  The chain input has max(n_in of all stages)
+ * channels, the chain output the last stage's n_out.  The call is cut into time chunks of `chunk_blocks` host blocks
+ * (default 4) so the intermediates stay small; state carries across chunks and calls in every stage.
+ * params[k]: stage k's automation rows [n_param_blocks[k]][n_streams][n_sliders of stage k] (host floats) or NULL. */
+typedef struct za_chain* za_chain_handle;
+ZA_API int za_chain_create(const char* const* plugin_keys, int n_plugins, int n_streams, double sample_rate, int block_len,
+                           int precision, int device, za_chain_handle* out);
+ZA_API int za_chain_destroy(za_chain_handle c);
+ZA_API int za_chain_info(za_chain_handle c, int* n_in, int* n_out, int* n_stages);
+ZA_API int za_chain_stage(za_chain_handle c, int k, za_gpu_handle* stage);    /* the stage's handle (read_state, options; owned by the chain) */
+ZA_API int za_chain_set_chunk_blocks(za_chain_handle c, int blocks);
+ZA_API int za_chain_prepare(za_chain_handle c, const float* const* param_block0);
+ZA_API int za_chain_process(za_chain_handle c, const float* const* params, const int* n_param_blocks, const float* in, float* out,
+                            int64_t n_frames, int64_t frame_stride, int mem);
+ZA_API int za_chain_sync(za_chain_handle c);
+
 /* ---- synthetic programme material + checksums ------------------- */
 /* Bench / sampled-parity tooling beside the render path: the inputs of a large bounce are generated ON THE DEVICE from a
  * counter-based hash of (seed, first_stream + s, channel, t0 + frame), so no PCIe or host storage is on the path, and

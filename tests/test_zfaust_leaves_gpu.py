@@ -30,7 +30,7 @@ def make_input(key, port, ns, nf):
     if key == "ClickBeGoneSG":                                              # needle clicks on programme material
         rng = np.random.default_rng(3)
         for s in range(ns):
-            for f in rng.choice(nf - 100, size=max(3, nf // 4000), replace=False) + 50:
+            for f in (rng.choice(nf - 100, size=max(3, nf // 4000), replace=False) + 50 if nf > 200 else []):
                 x[s, :, f] += rng.choice([-0.6, 0.6])
     return x
 

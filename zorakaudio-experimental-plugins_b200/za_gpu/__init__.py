@@ -42,6 +42,8 @@ SYMBOLS = [
     "za_gpu_set_option", "za_gpu_render", "za_gpu_last_error", "za_gpu_device_count", "za_gpu_version",
     "za_gpu_synth", "za_gpu_synth_tables", "za_gpu_checksum", "za_gpu_host_alloc", "za_gpu_host_free",
     "za_gpu_state_size", "za_gpu_state_save", "za_gpu_state_load",
+    "za_chain_create", "za_chain_destroy", "za_chain_info", "za_chain_stage", "za_chain_set_chunk_blocks", "za_chain_prepare",
+    "za_chain_process", "za_chain_sync",
 ]
 
 _lib = None
@@ -78,6 +80,14 @@ def lib() -> C.CDLL:
         L.za_gpu_state_size.argtypes = [C.c_void_p, C.POINTER(C.c_size_t)]
         L.za_gpu_state_save.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
         L.za_gpu_state_load.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
+        L.za_chain_create.argtypes = [C.POINTER(C.c_char_p), C.c_int, C.c_int, C.c_double, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
+        L.za_chain_destroy.argtypes = [C.c_void_p]
+        L.za_chain_info.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        L.za_chain_stage.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p)]
+        L.za_chain_set_chunk_blocks.argtypes = [C.c_void_p, C.c_int]
+        L.za_chain_prepare.argtypes = [C.c_void_p, C.c_void_p]
+        L.za_chain_process.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int]
+        L.za_chain_sync.argtypes = [C.c_void_p]
         L.za_gpu_host_alloc.argtypes = [C.c_size_t, C.POINTER(C.c_void_p)]
         L.za_gpu_host_free.argtypes = [C.c_void_p]
         L.za_gpu_synth.argtypes = [C.c_int, C.c_uint32, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int64, C.c_int64, C.c_void_p,
@@ -275,6 +285,67 @@ class BatchProcessor:
     def close(self):
         if self._h:
             lib().za_gpu_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Chain:
+    """A serial plugin chain rendered on one B200 (za_chain_*): stage k's output feeds stage k + 1 on the device."""
+
+    def __init__(self, plugin_keys, n_streams: int, sample_rate: float = 48000.0, block_len: int = 512, precision: str = "f64", device: int = 0):
+        self.keys = list(plugin_keys)
+        self.n_streams, self.block_len = n_streams, block_len
+        arr = (C.c_char_p * len(self.keys))(*[k.encode() for k in self.keys])
+        self._h = C.c_void_p()
+        _check(lib().za_chain_create(arr, len(self.keys), n_streams, sample_rate, block_len, ZA_F64 if precision in ("f64", ZA_F64) else ZA_F32,
+                                     device, C.byref(self._h)), "za_chain_create")
+        a, b, c = C.c_int(), C.c_int(), C.c_int()
+        _check(lib().za_chain_info(self._h, C.byref(a), C.byref(b), C.byref(c)), "za_chain_info")
+        self.n_in, self.n_out = a.value, b.value
+        self.infos = [plugin_info(k) for k in self.keys]
+
+    def set_chunk_blocks(self, blocks: int):
+        _check(lib().za_chain_set_chunk_blocks(self._h, blocks), "za_chain_set_chunk_blocks")
+
+    def prepare(self, params0=None):
+        if params0 is None:
+            _check(lib().za_chain_prepare(self._h, None), "za_chain_prepare")
+            return self
+        keep = [None if p is None else np.ascontiguousarray(p, np.float32) for p in params0]
+        ptrs = (C.c_void_p * len(keep))(*[None if p is None else p.ctypes.data for p in keep])
+        _check(lib().za_chain_prepare(self._h, ptrs), "za_chain_prepare")
+        return self
+
+    def process(self, x, params=None, out=None):
+        """x [n_streams][chain n_in][frames] numpy (host) or torch CUDA tensor; params: per stage None or [n_blocks][n_streams][n_sliders]."""
+        is_np = isinstance(x, np.ndarray)
+        nf = x.shape[-1]
+        if out is None:
+            if is_np:
+                out = np.empty((self.n_streams, self.n_out, nf), np.float32)
+            else:
+                import torch
+                out = torch.empty((self.n_streams, self.n_out, nf), dtype=torch.float32, device=x.device)
+        n = len(self.keys)
+        keep = [None] * n if params is None else [None if p is None else np.ascontiguousarray(p, np.float32) for p in params]
+        keep = [p[None] if p is not None and p.ndim == 2 else p for p in keep]
+        ptrs = (C.c_void_p * n)(*[None if p is None else p.ctypes.data for p in keep])
+        cnt = (C.c_int * n)(*[0 if p is None else p.shape[0] for p in keep])
+        mem = ZA_MEM_HOST if is_np else ZA_MEM_DEVICE
+        _check(lib().za_chain_process(self._h, ptrs, cnt, _ptr(x), _ptr(out), nf, nf, mem), "za_chain_process")
+        return out
+
+    def sync(self):
+        _check(lib().za_chain_sync(self._h), "za_chain_sync")
+
+    def close(self):
+        if self._h:
+            lib().za_chain_destroy(self._h)
             self._h = C.c_void_p()
 
     def __del__(self):
