@@ -16,7 +16,7 @@ REPO = Path(__file__).resolve().parent.parent
 def test_exports_every_declared_symbol(built_lib):
     import za_gpu
     hdr = (REPO / "include" / "za_gpu.h").read_text()
-    declared = set(re.findall(r"ZA_API\s+[\w\s\*]+?\b(za_gpu_\w+)\s*\(", hdr))
+    declared = set(re.findall(r"ZA_API\s+[\w\s\*]+?\b(za_(?:gpu|chain|batch)_\w+)\s*\(", hdr))
     assert declared == set(za_gpu.SYMBOLS), declared ^ set(za_gpu.SYMBOLS)
     L = C.CDLL(str(built_lib))
     for s in declared:
