@@ -65,10 +65,10 @@ WORKLOADS = {
     # the other leaves of the three classes at the cfg3 batch shape (4096 stereo streams); shorter renders while they run on
     # the translated stream-per-thread path
     "erbtilt": dict(plugin="ERBTilt", streams=4096, seconds=10.0, ch=(2, 2), automate=[0], cpu=(256, 5.0), synth=1,
-                    kernel={"f32": "erbtilt / jsfx_process_kernel", "f64": "erbtilt / jsfx_process_kernel"},
+                    kernel={"f32": "erbtilt_kernel", "f64": "erbtilt_kernel"},
                     text="ERB Tilt (15 one-poles x 2 ch + energy followers + guard), {ns} stereo streams x {sec:g} s @ 48 kHz per GPU, tilt automated every 512-frame block"),
     "specstab": dict(plugin="SpectralStabilizer", streams=4096, seconds=10.0, ch=(2, 2), automate=[1], cpu=(256, 5.0), synth=1,
-                     kernel={"f32": "specstab / jsfx_process_kernel", "f64": "specstab / jsfx_process_kernel"},
+                     kernel={"f32": "specstab_kernel", "f64": "specstab_kernel"},
                      text="Spectral Stabilizer (12 band-pass biquads x 2 ch + per-band gain smoothing), {ns} stereo streams x {sec:g} s @ 48 kHz per GPU, depth automated every 512-frame block"),
     "gts": dict(plugin="GTS", streams=4096, seconds=10.0, ch=(2, 2), automate=[0, 1], cpu=(64, 2.0), f32_only=True, synth=1,
                 kernel={"f32": "gts_kernel"},

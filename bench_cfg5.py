@@ -30,11 +30,11 @@ CFG5_LEAVES = ["EasyExpander", "RTT", "SOMA", "ATTACK", "ERBTilt", "SpectralStab
                "VAR", "ModTilt", "ClickBeGoneSG", "GTS", "RED"]
 # Schedule of one step, two phases, every leaf on its own CUDA stream inside a phase:
 #   A: the hand-written leaves and the heap-less translated leaves -- short kernels with big shared-memory tiles;
-#   B: the translated leaves that keep their state in a mem[] heap (SOMA, and SpectralStabilizer / ERBTilt while they run
-#      on the translated path) -- long kernels that live off the L1.  Shared memory is carved out of the same 228 KB as
+#   B: the translated leaf that keeps its state in a mem[] heap (SOMA; SpectralStabilizer and ERBTilt were in this phase
+#      until they got their own scan kernels) -- a long kernel that lives off the L1.  Shared memory is carved out of the same 228 KB as
 #      the L1, so while phase-A kernels are resident on an SM the heap leaves' lines are evicted (measured in round 1:
 #      SpectralStabilizer / ERBTilt 3x slower inside a free-for-all mix).
-PHASE_B = {"SpectralStabilizer", "ERBTilt", "SOMA"}
+PHASE_B = {"SOMA"}
 TOTAL_STREAMS = 65536
 FAUST = {"VAR", "ModTilt", "ClickBeGoneSG", "GTS", "RED"}
 

@@ -158,6 +158,43 @@ def test_heap_overflow_fails_the_call(gpu):
     bp.close()
 
 
+def test_specstab_scan_kernel_against_its_translation(gpu):
+    """"SpectralStabilizer" is the hand-written time-parallel kernel (k_specstab.cu); its machine translation stays in the
+    library as "SpectralStabilizer.translated".  Both against the reference and against each other; float mode; split calls."""
+    ref = zo.RefPlugin("SpectralStabilizer")
+    for ns, nf, block in ((37, 24000 + 77, 512), (5, 4000 + 3, 100), (3, 1000, 7), (33, 512 * 6, 256)):
+        x = wl.programme_bursts(ns, nf, n_ch=2)
+        base = np.array([s["default"] for s in ref.sliders], np.float32)
+        p = wl.automation(ref.sliders, (nf + block - 1) // block, ns, which=[0, 1, 2], base=base)
+        y, yd = ref.render(p, x, want_f64=True, block=block)
+        taps = {}
+        for key in ("SpectralStabilizer", "SpectralStabilizer.translated"):
+            bp = gpu.BatchProcessor(key, ns, 48000.0, block, "f64").prepare(p[0])
+            tap = np.zeros_like(yd)
+            out = bp.process(x, tap64=tap, params=p)
+            assert rel_err(tap, yd).max() <= TOL64, (key, block)
+            assert np.mean(out == y) > 0.9999
+            taps[key] = tap
+            bp.close()
+        assert rel_err(taps["SpectralStabilizer"], taps["SpectralStabilizer.translated"]).max() <= TOL64
+    ns, nf = 64, 48000 * 2
+    x = wl.synth(1, 5000, range(ns), 2, nf)
+    base = np.array([s["default"] for s in ref.sliders], np.float32)
+    p = wl.automation(ref.sliders, (nf + 511) // 512, ns, which=[1], base=base)
+    _, yd = ref.render(p, x, want_f64=True)
+    bp = gpu.BatchProcessor("SpectralStabilizer", ns, precision="f32").prepare(p[0])
+    out = bp.process(x, params=p)
+    worst = max(dbfs_rms(out[s].astype(np.float64) - yd[s]) for s in range(ns))
+    print(f"SpectralStabilizer scan kernel fp32: worst stream residual {worst:.1f} dBFS")
+    assert worst < -100.0
+    bp.prepare(p[0])
+    bp.set_option("force_generic_io", 1)
+    o2 = np.concatenate([bp.process(np.ascontiguousarray(x[:, :, :512 * 50]), params=p), bp.process(np.ascontiguousarray(x[:, :, 512 * 50:]), params=p[50:])], axis=2)
+    assert np.array_equal(o2, out)
+    assert np.all(bp.read_state("gs[3]") <= 1.0) and np.all(bp.read_state("action_amt") > 0)
+    bp.close()
+
+
 def test_erbtilt_scan_kernel_against_its_translation(gpu):
     """"ERBTilt" is the hand-written time-parallel kernel (k_erbtilt.cu); the machine translation of the same script stays in
     the library as "ERBTilt.translated".  Both against the reference (criterion) and against each other, every slider

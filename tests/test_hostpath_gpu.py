@@ -175,7 +175,8 @@ def test_two_devices_render_their_shards(gpu):
 
 
 @pytest.mark.parametrize("key,prec", [("cascade8", "f32"), ("cascade8", "f64"), ("EasyExpander", "f64"), ("stft_mask2048", "f32"),
-                                      ("SOMA", "f64"), ("RTT", "f32"), ("ModTilt", "f32"), ("ERBTilt", "f32"), ("ERBTilt", "f64")])
+                                      ("SOMA", "f64"), ("RTT", "f32"), ("ModTilt", "f32"), ("ERBTilt", "f32"), ("ERBTilt", "f64"), ("SpectralStabilizer", "f64"),
+                                      ("VAR", "f32"), ("GTS", "f32"), ("ClickBeGoneSG", "f32")])
 def test_checkpoint_resume_is_bit_identical(gpu, key, prec):
     """za_gpu_state_save / za_gpu_state_load: a render interrupted after its first part and resumed in a FRESH handle from
     the saved blob continues bit-identically (outputs and, for translated leaves, the rand()-driven state included)."""

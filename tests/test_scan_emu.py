@@ -64,3 +64,44 @@ def test_erbtilt_scan_tile_code_fp32_meets_the_criterion(emu, seed, automate):
     y, yd, out, tap, _ = _erb_case(ref, emu, 48000 * 3, 512, False, automate, seed)
     db = dbfs_rms(out.astype(np.float64) - yd)
     assert db < -100.0, db
+
+
+def _ss_case(ref, emu, nf, block, f64, automate, seed=0):
+    x = wl.programme_bursts(1, nf, first_stream=seed)
+    base = np.array([s["default"] for s in ref.sliders], np.float32)
+    nb = (nf + block - 1) // block
+    if automate:
+        p = wl.automation(ref.sliders, nb, 1, which=[0, 1, 2], base=base, first_stream=seed)
+    else:
+        p = np.tile(base, (1, 1, 1))
+        p[0, 0, 1] = 80.0
+    y, yd = ref.render(p, x, want_f64=True, block=block)
+    q = np.ascontiguousarray(zo.quantise(ref.sliders, p[:, 0]))
+    state = np.zeros(120)
+    state[9 * 12:] = 1.0                                     # gs = 1 after @init
+    out, tap = np.zeros((2, nf), np.float32), np.zeros((2, nf))
+    emu.emu_specstab(C.c_double(48000.0), C.c_void_p(q.ctypes.data), q.shape[0], block, C.c_void_p(state.ctypes.data),
+                     C.c_void_p(x[0].ctypes.data), C.c_void_p(out.ctypes.data), C.c_void_p(tap.ctypes.data), C.c_long(nf), C.c_long(nf), int(f64))
+    return y[0], yd[0], out, tap
+
+
+@pytest.mark.parametrize("nf,block,automate", [(24000 + 77, 512, True), (24000 + 77, 512, False), (9000 + 1, 100, True), (3000, 7, True)])
+def test_specstab_scan_tile_code_fp64_against_reference(emu, nf, block, automate):
+    """2-state biquad scans, energy scan, lane-shift differences, closed-form gain smoothing, end-state-only motion EMA and
+    the lane = band @block prologue of csrc/specstab_core.h against the reference's compiled Spectral Stabilizer."""
+    if not zo.have_ref("SpectralStabilizer"):
+        pytest.skip("oracle/_ref not built")
+    ref = zo.RefPlugin("SpectralStabilizer")
+    y, yd, out, tap = _ss_case(ref, emu, nf, block, True, automate)
+    e = rel_err(tap[None], yd[None]).max()
+    assert e <= TOL64, e
+    assert np.mean(out == y) > 0.9999
+
+
+@pytest.mark.parametrize("seed", [0, 1365])
+def test_specstab_scan_tile_code_fp32_meets_the_criterion(emu, seed):
+    if not zo.have_ref("SpectralStabilizer"):
+        pytest.skip("oracle/_ref not built")
+    ref = zo.RefPlugin("SpectralStabilizer")
+    y, yd, out, tap = _ss_case(ref, emu, 48000 * 2, 512, False, True, seed)
+    assert dbfs_rms(out.astype(np.float64) - yd) < -100.0

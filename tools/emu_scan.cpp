@@ -135,3 +135,55 @@ void emu_erbtilt(double srate, const double* q, int n_rows, int block_len, doubl
     if (f64) erb_render<double, za::kErbChunkF64>(srate, q, n_rows, block_len, state, in, out, tap, n_frames, stride);
     else erb_render<float, za::kErbChunkF32>(srate, q, n_rows, block_len, state, in, out, tap, n_frames, stride);
 }
+
+// ---- Spectral Stabilizer: csrc/specstab_core.h on the host (same tile / prologue source as k_specstab.cu) ------------------------
+#include "specstab_tables.h"
+
+namespace {
+template <class T, int CM>
+void sstab_render(double srate, const double* q, int n_rows, int block_len, double* state /* [10][12] carries */, const float* in, float* out,
+                  double* tap, long n_frames, long stride)
+{
+    namespace S = za::sstab;
+    const S::Init init = S::build_init(srate);
+    static S::Tables<T, CM> tbm; static S::Tables<T, 1> tbt;
+    S::build_tables<T, CM>(init, tbm); S::build_tables<T, 1>(init, tbt);
+    const std::vector<T> pwA = S::power_table<T>(init.k.atk_a, block_len), pwR = S::power_table<T>(init.k.rel_a, block_len);
+    S::Carry<T> cy{};
+    za::lanes::LV<T>* cv[10] = {&cy.z1L, &cy.z2L, &cy.z1R, &cy.z2R, &cy.env, &cy.elog, &cy.d1, &cy.d2, &cy.mot, &cy.gs};
+    for (int v = 0; v < 10; ++v) for (int l = 0; l < 32; ++l) cv[v]->v[l] = l < S::kBands ? (T)state[v * S::kBands + l] : T(0);
+    S::Prolog pv{}; S::Block<T> bk{};
+    long pos = 0;
+    for (int blk = 0; pos < n_frames; ++blk) {
+        const int nb = (int)std::min<long>(block_len, n_frames - pos);
+        const int row = blk < n_rows ? blk : n_rows - 1;
+        S::block_prologue<T>(init.k, q + (size_t)row * 3, cy, pv, bk);
+        int f = 0;
+        for (; f + 32 * CM <= nb; f += 32 * CM) {
+            const long g0 = pos + f;
+            ErbHostIO<T, CM> io{in + g0, in + stride + g0, out + g0, out + stride + g0, tap ? tap + g0 : nullptr, tap ? tap + stride + g0 : nullptr, 32};
+            S::tile<T, CM, false>(tbm, pwA.data(), pwR.data(), cy, bk, f, 32, io);
+        }
+        for (; f < nb; f += 32) {
+            const int m = std::min(32, nb - f);
+            const long g0 = pos + f;
+            ErbHostIO<T, 1> io{in + g0, in + stride + g0, out + g0, out + stride + g0, tap ? tap + g0 : nullptr, tap ? tap + stride + g0 : nullptr, m};
+            S::tile<T, 1, false>(tbt, pwA.data(), pwR.data(), cy, bk, f, m, io);
+        }
+        S::block_epilogue<T>(cy, bk, pwA[nb], pwR[nb]);
+        pos += nb;
+    }
+    for (int v = 0; v < 10; ++v) for (int l = 0; l < S::kBands; ++l) state[v * S::kBands + l] = (double)cv[v]->v[l];
+}
+}
+
+// q [n_rows][3] quantised sliders; state [10][12] doubles (z1L z2L z1R z2R env elog d1 d2 mot gs; gs = 1 after @init).
+extern "C" __attribute__((visibility("default")))
+void emu_specstab(double srate, const double* q, int n_rows, int block_len, double* state, const float* in, float* out, double* tap,
+                  long n_frames, long stride, int f64)
+{
+    _MM_SET_FLUSH_ZERO_MODE(_MM_FLUSH_ZERO_ON);
+    _MM_SET_DENORMALS_ZERO_MODE(_MM_DENORMALS_ZERO_ON);
+    if (f64) sstab_render<double, 4>(srate, q, n_rows, block_len, state, in, out, tap, n_frames, stride);
+    else sstab_render<float, 8>(srate, q, n_rows, block_len, state, in, out, tap, n_frames, stride);
+}

@@ -11,55 +11,13 @@
 // The kernel is FP32/FP64-issue bound by construction (~660 thread-operations per frame): its roofline is the FMA pipe,
 // the HBM fraction is reported beside it.
 #include "erbtilt_args.h"
+#include "scan_io.cuh"
 
 namespace za {
 
 namespace {
 
 using namespace erb;
-
-template <class T, int C, bool TAP>
-struct ErbIO {
-    const float* inL; const float* inR; float* outL; float* outR; double* tapL; double* tapR;   // at this lane's first frame
-    bool live, vec;
-    __device__ __forceinline__ void load(T (&l)[C], T (&r)[C]) const
-    {
-        if (!live) {
-#pragma unroll
-            for (int i = 0; i < C; ++i) { l[i] = T(0); r[i] = T(0); }
-            return;
-        }
-        if (C % 4 == 0 && vec) {
-#pragma unroll
-            for (int j = 0; j < C / 4; ++j) {
-                const float4 a = __ldg(reinterpret_cast<const float4*>(inL) + j), b = __ldg(reinterpret_cast<const float4*>(inR) + j);
-                l[4 * j] = (T)a.x; l[4 * j + 1] = (T)a.y; l[4 * j + 2] = (T)a.z; l[4 * j + 3] = (T)a.w;
-                r[4 * j] = (T)b.x; r[4 * j + 1] = (T)b.y; r[4 * j + 2] = (T)b.z; r[4 * j + 3] = (T)b.w;
-            }
-        } else {
-#pragma unroll
-            for (int i = 0; i < C; ++i) { l[i] = (T)__ldg(inL + i); r[i] = (T)__ldg(inR + i); }
-        }
-    }
-    __device__ __forceinline__ void store(const T (&l)[C], const T (&r)[C]) const
-    {
-        if (!live) return;
-        if (TAP) {
-#pragma unroll
-            for (int i = 0; i < C; ++i) { tapL[i] = (double)l[i]; tapR[i] = (double)r[i]; }
-        }
-        if (C % 4 == 0 && vec) {
-#pragma unroll
-            for (int j = 0; j < C / 4; ++j) {
-                reinterpret_cast<float4*>(outL)[j] = make_float4((float)l[4 * j], (float)l[4 * j + 1], (float)l[4 * j + 2], (float)l[4 * j + 3]);
-                reinterpret_cast<float4*>(outR)[j] = make_float4((float)r[4 * j], (float)r[4 * j + 1], (float)r[4 * j + 2], (float)r[4 * j + 3]);
-            }
-        } else {
-#pragma unroll
-            for (int i = 0; i < C; ++i) { outL[i] = (float)l[i]; outR[i] = (float)r[i]; }
-        }
-    }
-};
 
 constexpr int kWarps = 4;
 
@@ -93,14 +51,14 @@ __global__ void __launch_bounds__(32 * kWarps, 4) erbtilt_kernel(const ErbArgs a
         int f = 0;
         for (; f + 32 * CM <= nb; f += 32 * CM) {
             const int64_t g0 = pos + f + lane * CM;
-            ErbIO<T, CM, TAP> io{in0 + g0, in0 + a.row_stride + g0, out0 + g0, out0 + a.row_stride + g0,
+            ScanIO<T, CM, TAP> io{in0 + g0, in0 + a.row_stride + g0, out0 + g0, out0 + a.row_stride + g0,
                                  TAP ? tap0 + g0 : nullptr, TAP ? tap0 + a.row_stride + g0 : nullptr, true, base_vec && ((pos + f) & 3) == 0};
             tile<T, CM, FAST>(tbm, cy, bk, 32, io);
         }
         for (; f < nb; f += 32) {
             const int m = min(32, nb - f);
             const int64_t g0 = pos + f + lane;
-            ErbIO<T, 1, TAP> io{in0 + g0, in0 + a.row_stride + g0, out0 + g0, out0 + a.row_stride + g0,
+            ScanIO<T, 1, TAP> io{in0 + g0, in0 + a.row_stride + g0, out0 + g0, out0 + a.row_stride + g0,
                                 TAP ? tap0 + g0 : nullptr, TAP ? tap0 + a.row_stride + g0 : nullptr, lane < m, false};
             tile<T, 1, FAST>(tbt, cy, bk, m, io);
         }

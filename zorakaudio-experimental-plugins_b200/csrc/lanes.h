@@ -82,6 +82,10 @@ template <class T> ZA_LN T lane_load_rev(const T* table, int m)                 
     return l < m ? table[m - 1 - l] : T(0);
 }
 template <class T, class F> ZA_LN T lane_generate(F f) { return f((int)(threadIdx.x & 31)); }              // f(lane)
+template <class F> ZA_LN float lane_gather(float v, F idx) { return __shfl_sync(0xffffffffu, v, idx((int)(threadIdx.x & 31))); }    // v[idx(lane)]
+template <class F> ZA_LN double lane_gather(double v, F idx) { return __shfl_sync(0xffffffffu, v, idx((int)(threadIdx.x & 31))); }
+ZA_LN bool lane_any(bool p) { return __any_sync(0xffffffffu, p); }
+template <class To, class From> ZA_LN To lane_cast(From v) { return (To)v; }
 
 }  // namespace lanes
 }  // namespace za
@@ -152,6 +156,11 @@ ZA_LN typename lv_of<A, B, Cc>::type fma_rn(const A& a, const B& b, const Cc& c)
     for (int l = 0; l < 32; ++l) r.v[l] = std::fma(lane_at<T>(a, l), lane_at<T>(b, l), lane_at<T>(c, l));
     return r;
 }
+template <class To, class From> ZA_LN LV<To> lane_cast(const LV<From>& a) { LV<To> r; for (int l = 0; l < 32; ++l) r.v[l] = (To)a.v[l]; return r; }
+ZA_LN float neg(float a) { return -a; }
+ZA_LN double neg(double a) { return -a; }
+ZA_LN float abs_(float a) { return std::fabs(a); }
+ZA_LN double abs_(double a) { return std::fabs(a); }
 ZA_LN float fma_rn(float a, float b, float c) { return std::fmaf(a, b, c); }
 ZA_LN double fma_rn(double a, double b, double c) { return std::fma(a, b, c); }
 #define ZA_LANES_CMP(name, op)                                                                                                             \
@@ -178,6 +187,7 @@ template <class T> ZA_LN LV<T> lane_zero() { LV<T> r; for (int l = 0; l < 32; ++
 template <class T> ZA_LN LV<T> lane_load(const T* table) { LV<T> r; for (int l = 0; l < 32; ++l) r.v[l] = table[l]; return r; }
 template <class T> ZA_LN LV<T> lane_load_rev(const T* table, int m) { LV<T> r; for (int l = 0; l < 32; ++l) r.v[l] = l < m ? table[m - 1 - l] : T(0); return r; }
 template <class T, class F> ZA_LN LV<T> lane_generate(F f) { LV<T> r; for (int l = 0; l < 32; ++l) r.v[l] = f(l); return r; }
+template <class T, class F> ZA_LN LV<T> lane_gather(const LV<T>& a, F idx) { LV<T> r; for (int l = 0; l < 32; ++l) r.v[l] = a.v[idx(l) & 31]; return r; }
 
 }  // namespace lanes
 }  // namespace za

@@ -66,6 +66,8 @@ const char* easyexpander_slider_text();
 const char* stft_mask2048_slider_text();
 const char* modtilt_slider_text();
 const char* erbtilt_slider_text();
+const char* specstab_slider_text();
+PluginImpl* make_specstab();
 const char* red_slider_text();
 const char* clickbegonesg_slider_text();
 const char* var_slider_text();
@@ -86,6 +88,7 @@ const std::vector<PluginDesc>& plugin_table()
             {"stft_mask2048", 2, 2, 2, 2048, stft_mask2048_slider_text(), &make_stft_mask2048},
             {"ModTilt", 2, 2, 1, 0, modtilt_slider_text(), &make_modtilt},
             {"ERBTilt", 2, 2, 0, 0, erbtilt_slider_text(), &make_erbtilt},
+            {"SpectralStabilizer", 2, 2, 0, 0, specstab_slider_text(), &make_specstab},
             {"RED", 6, 6, 1, 0, red_slider_text(), &make_red},
             {"ClickBeGoneSG", 2, 2, 1, 15, clickbegonesg_slider_text(), &make_clickbegonesg},
             {"VAR", 2, 2, 1, 0, var_slider_text(), &make_var},

@@ -119,6 +119,12 @@ constexpr int kErbChunkF32 = 8, kErbChunkF64 = 4;       // frames per lane of a 
 constexpr int kErbLpL = 0, kErbLpR = 15, kErbEnvF = 30, kErbEnvS = 46, kErbPreE = 62, kErbPostE = 78, kErbGlobalGain = 94,
               kErbGBand = 106, kErbSlots = 122;
 
+// ---- Spectral Stabilizer (IIR class, hand-written scan kernel: k_specstab.cu / specstab_core.h) ---------------------------
+constexpr int kSsChunkF32 = 8, kSsChunkF64 = 4;
+// state slots, [slot][stream] doubles: ten per-band carries (12 bands each: z1L z2L z1R z2R envlin envlog d1 d2 mot gs), then the
+// block-rate values gn[11] gw[11] res[12] gt[12] depth mb low_min_gain action_amt
+constexpr int kSsCarry = 0, kSsGn = 120, kSsGw = 131, kSsRes = 142, kSsGt = 154, kSsScalars = 166, kSsSlots = 170;
+
 // ---- translated DSP-JSFX leaves (csrc/gen/g_*.cu from za_gpu/jsfxc.py, runtime in jsfx_rt.cuh) -------------------
 struct GenLaunch {
     const float* in; float* out; double* tap;      // [stream][ch][row_stride]
