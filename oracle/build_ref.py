@@ -30,7 +30,10 @@ PKG = REPO / "zorakaudio-experimental-plugins_b200"
 PLUGINS = {
     "cascade8": (PKG / "plugins/Workloads/cascade8/src/cascade8.jsfx", False),
     "stft_mask2048": (PKG / "plugins/Workloads/stft_mask2048/src/stft_mask2048.jsfx", True),
+    "decrust512": (PKG / "plugins/Workloads/decrust512/src/decrust512.jsfx", True),
+    "fftprobe": (PKG / "plugins/Workloads/fftprobe/src/fftprobe.jsfx", True),
     "semprobe": (PKG / "plugins/Workloads/semprobe/src/semprobe.jsfx", False),
+    "Alias": (REF / "plugins/Spectral/Alias/src/Alias.jsfx", False),
     "EasyExpander": (REF / "plugins/Dynamics/EasyExpander/src/EasyExpander.jsfx", False),
     "RTT": (REF / "plugins/Dynamics/RTT/src/Reverb Tail Tamer.jsfx", False),
     "SOMA": (REF / "plugins/Dynamics/SOMA/src/SOMA.jsfx", False),

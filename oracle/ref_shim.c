@@ -48,8 +48,22 @@ void jsfx_ensure_mem(DSPJSFX_State* st, int64_t needed)
     if (newBytes > oldBytes) memset((uint8_t*)p + oldBytes, 0, newBytes - oldBytes);
     st->memN = newN;
 }
-/* slider-change notifications go to the GUI host in the reference (:2448); no DSP effect */
-__attribute__((weak)) int jsfx_sliderchange(DSPJSFX_State* st, double mask) { (void)st; (void)mask; return 0; }
+/* src/JSFXJuceProcessor.cpp:2448-2476 */
+int jsfx_sliderchange(DSPJSFX_State* st, double sliderMask)
+{
+    const int64_t mask = (sliderMask > 0.0) ? (int64_t)llround(sliderMask) : 0;
+    if (!st || mask <= 0) return 0;
+    st->pendingSliderChangeMask |= mask;
+    return 1;
+}
+int jsfx_slider_automate(DSPJSFX_State* st, double sliderMask, double endTouch)
+{
+    const int64_t mask = (sliderMask > 0.0) ? (int64_t)llround(sliderMask) : 0;
+    if (!st || mask <= 0) return 0;
+    st->pendingSliderChangeMask |= mask;
+    if (endTouch != 0.0) st->pendingSliderAutomateEndMask |= mask; else st->pendingSliderAutomateMask |= mask;
+    return 1;
+}
 
 /* ---- slider layout passed in by the caller (parsed from the .jsfx text by the test host) -- */
 typedef struct ZrefSliders {
@@ -155,6 +169,19 @@ ZREF_API void zref_prepare(void* h, double srate, const float* host_values)
     jsfx_slider(&z->st);
 }
 
+/* consumeDspSliderChanges (src/JSFXJuceProcessor.cpp:5665-5738) after every block: sliders the DSP changed itself
+ * (sliderchange / slider_automate) become the host's view of them (lastSliders), the pending masks are cleared. */
+static void consume_dsp_slider_changes(Zref* z)
+{
+    DSPJSFX_State* st = &z->st;
+    const uint64_t m = (uint64_t)(st->pendingSliderChangeMask > 0 ? st->pendingSliderChangeMask : 0) |
+                       (uint64_t)(st->pendingSliderAutomateMask > 0 ? st->pendingSliderAutomateMask : 0) |
+                       (uint64_t)(st->pendingSliderAutomateEndMask > 0 ? st->pendingSliderAutomateEndMask : 0);
+    for (int i = 0; i < 64; ++i)
+        if (m & ((uint64_t)1 << i)) z->last[i] = st->sliders[i];
+    st->pendingSliderChangeMask = 0; st->pendingSliderAutomateMask = 0; st->pendingSliderAutomateEndMask = 0;
+}
+
 /* processBlock, normal build: :3536-3562 then jsfx_process_block :3733.  Returns "sliders changed". */
 ZREF_API int zref_process_block(void* h, const float* host_values, const float* const* in, float* const* out,
                                 int nch, int n)
@@ -165,6 +192,7 @@ ZREF_API int zref_process_block(void* h, const float* host_values, const float* 
     if (host_values) { changed = push_sliders(z, host_values); if (changed) jsfx_slider(&z->st); }
     z->st.currentBlockSize = n; z->st.samplesblock = (double)n;
     jsfx_process_block(&z->st, in, out, nch, n);
+    consume_dsp_slider_changes(z);
     return changed;
 }
 
@@ -191,6 +219,7 @@ ZREF_API int zref_process_block_f64(void* h, const float* host_values, const flo
             if (out)   out[c][i]   = (float)st->spl[c];
         }
     }
+    consume_dsp_slider_changes(z);
     return changed;
 }
 
@@ -250,6 +279,7 @@ static void* worker(void* arg)
                         outp[c][i] = (float)st->spl[c];
                     }
                 }
+                consume_dsp_slider_changes(zz);
             } else {
                 zref_process_block(z, hv, inp, outp, nch, n);
             }

@@ -36,7 +36,7 @@ def make_case(ref, ns, nf, automate, block=512):
     return p, x
 
 
-@pytest.mark.parametrize("key", KEYS + ["semprobe"])
+@pytest.mark.parametrize("key", KEYS + ["semprobe", "Alias"])
 @pytest.mark.parametrize("automate", [False, True])
 def test_fp64_parity_and_state(gpu, key, automate):
     ref = zo.RefPlugin(key)
@@ -147,13 +147,13 @@ def test_heap_overflow_fails_the_call(gpu):
     ref = zo.RefPlugin("SpectralStabilizer")
     ns, nf = 5, 4096
     p, x = make_case(ref, ns, nf, False)
-    bp = gpu.BatchProcessor("SpectralStabilizer", ns, precision="f32")
+    bp = gpu.BatchProcessor("SpectralStabilizer.translated", ns, precision="f32")
     bp.set_option("heap_slots", 1000)
     with pytest.raises(za_gpu.ZaError, match="beyond the heap"):
         bp.prepare(p)                                  # @init already writes state up to slot ~2080
         bp.process(x)
     bp.close()
-    bp = gpu.BatchProcessor("SpectralStabilizer", ns, precision="f32").prepare(p)
+    bp = gpu.BatchProcessor("SpectralStabilizer.translated", ns, precision="f32").prepare(p)
     bp.process(x)                                      # the real heap: fine
     bp.close()
 
@@ -260,3 +260,48 @@ def test_device_quantiser_equals_host_quantiser(gpu, key):
     assert np.array_equal(outs[0], outs[1], equal_nan=True)
     y, _ = ref.render(p, x)
     assert np.mean(outs[0] == y) > 0.999
+
+
+@pytest.mark.parametrize("key,refkey", [("decrust512", "decrust512"), ("stft_mask2048.translated", "stft_mask2048")])
+def test_fft_hook_scripts_on_the_device(gpu, key, refkey):
+    """Translated scripts that call fft / ifft / fft_real / ifft_real / fft_permute / fft_ipermute / convolve_c: the device hooks
+    against the reference's compiled path over WDL's FFT; the translated STFT workload also against the hand-written kernel."""
+    ref = zo.RefPlugin(refkey)
+    ns, nf = 37, 12000 + 77
+    p, x = make_case(ref, ns, nf, True)
+    y, yd = ref.render(p, x, want_f64=True)
+    bp = gpu.BatchProcessor(key, ns, precision="f64").prepare(p[0])
+    tap = np.zeros_like(yd)
+    out = bp.process(x, tap64=tap, params=p)
+    e = rel_err(tap, yd).max()
+    print(f"FFT-HOOKS {key}: {e:.2e}")
+    assert e <= TOL64, e
+    assert np.mean(out == y) > 0.9999
+    bp.close()
+    bp = gpu.BatchProcessor(key, ns, precision="f32").prepare(p[0])
+    o32 = bp.process(x, params=p)
+    assert dbfs_rms(o32.astype(np.float64) - yd) < -100.0
+    bp.close()
+    if refkey == "stft_mask2048":
+        bp = gpu.BatchProcessor("stft_mask2048", ns, precision="f64").prepare(p[0])
+        tap2 = np.zeros_like(yd)
+        bp.process(x, tap64=tap2, params=p)
+        assert rel_err(tap2, tap).max() <= TOL64
+        bp.close()
+
+
+@pytest.mark.parametrize("log2n", [4, 9, 15])
+def test_every_fft_hook_on_the_device(gpu, log2n):
+    ref = zo.RefPlugin("fftprobe")
+    n = 1 << log2n
+    ns, nf = 3, 3 * n + 5
+    x = wl.programme_bursts(ns, nf, n_ch=2)
+    for mode in range(6):
+        p = np.tile(np.array([[log2n, mode]], np.float32), (ns, 1))
+        y, yd = ref.render(p, x, want_f64=True)
+        bp = gpu.BatchProcessor("fftprobe", ns, precision="f64").prepare(p)
+        tap = np.zeros_like(yd)
+        bp.process(x, tap64=tap)
+        d = np.abs(tap - yd).max() / np.abs(yd).max()
+        assert d <= (0.0 if mode == 5 else 5e-15), (mode, d)
+        bp.close()

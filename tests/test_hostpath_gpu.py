@@ -66,7 +66,7 @@ def test_error_inside_a_multi_chunk_call_leaves_no_copy_in_flight(gpu):
     """A translated leaf that runs past its heap fails the host call; every enqueued copy has drained when it returns."""
     ns, nf = 5, 512 * 8
     p0, _, x = _case(gpu, "SpectralStabilizer", ns, nf, 512, automate=False)
-    bp = gpu.BatchProcessor("SpectralStabilizer", ns, precision="f32")
+    bp = gpu.BatchProcessor("SpectralStabilizer.translated", ns, precision="f32")
     bp.set_option("heap_slots", 1000)
     bp.set_option("host_chunk_frames", 1024)
     y = np.zeros((ns, 2, nf), np.float32)

@@ -14,7 +14,7 @@ import za_oracle as zo
 @pytest.mark.parametrize("key,auto", [("RTT", True), ("SOMA", False), ("ATTACK", True), ("ERBTilt", False),
                                       ("SpectralStabilizer", True), ("DDT", False), ("DPT", True), ("SaliencePush", False),
                                       ("ADS", True), ("BedRock", False), ("Roomalizer", True), ("TSEQ", False),
-                                      ("semprobe", True)])
+                                      ("semprobe", True), ("Alias", True), ("Alias", False)])
 def test_translation_is_bit_identical_on_host(key, auto):
     if not zo.have_ref(key):
         pytest.skip("oracle/_ref not built")
@@ -50,6 +50,43 @@ def test_nan_conditions_and_ordered_compares_match_the_reference():
         assert v["f2"][0] == 0.0 and v["k"][0] == 0.0 and v["w"][0] == 0.0       # the ordered forms really were exercised
 
 
+@pytest.mark.parametrize("key,auto", [("decrust512", True), ("decrust512", False), ("stft_mask2048", True)])
+def test_fft_hook_scripts_match_the_reference_and_wdl(key, auto):
+    """Scripts that call the FFT runtime hooks: the translator's per-stream device transforms (csrc/jsfx_rt.cuh: Stockham
+    radix-2 + scatter into WDL's order, the two-for-one real split, convolve_c) against the reference's compiled path
+    over its own WDL FFT.  Not bit-identical (different butterfly order), far inside the 1e-12 criterion."""
+    if not zo.have_ref(key):
+        pytest.skip("oracle/_ref not built")
+    import emu_jsfx
+    err, bad = emu_jsfx.compare(key, nf=9000, automate=auto, verbose=False)
+    assert err <= 1e-13, err
+    assert not bad, bad[:4]
+
+
+@pytest.mark.parametrize("log2n", [4, 5, 7, 10, 13, 15])
+def test_every_fft_hook_at_every_size(log2n):
+    """plugins/Workloads/fftprobe: fft (WDL's permuted order visible), fft + fft_permute (natural order), fft + ifft,
+    fft_real, fft_real + ifft_real, permute + ipermute at sizes 16 .. 32768 against src/WDL/fft.c behind the reference's
+    hooks (oracle/ref_fft_hooks.c)."""
+    import numpy as np
+    import emu_jsfx
+    from za_gpu import workloads as wl
+    if not zo.have_ref("fftprobe"):
+        pytest.skip("oracle/_ref not built")
+    ref = zo.RefPlugin("fftprobe")
+    e = emu_jsfx.Emu("fftprobe")
+    n = 1 << log2n
+    nf = 3 * n + 5
+    x = wl.programme_bursts(1, nf, n_ch=2)
+    for mode in range(6):
+        p = np.array([[log2n, mode]], np.float32)
+        y, yd = ref.render(p, x, want_f64=True)
+        ye, te, ve = e.render(ref.sliders, p, x[0])
+        assert np.abs(yd).max() > 0
+        d = np.abs(te - yd[0]).max() / np.abs(yd).max()
+        assert d <= (0.0 if mode == 5 else 5e-15), (mode, d)
+
+
 def test_parser_precedence_and_forms():
     from za_gpu import jsfxc
     P = lambda s: jsfxc.Parser(s).program()
@@ -60,8 +97,11 @@ def test_parser_precedence_and_forms():
     assert len(P("a\n-b")) == 2                                                            # '-' may start a statement
     assert P("x & 3 == 3")[0][1] == "=="  or P("x & 3 == 3")[0][1] == "&"                 # same level, left to right
     assert P("loop(3, a += 1; b += 2)")[0][0] == "loop"
+    # instance() / this.: a namespaced call makes the instance variable a member of the call-site pseudo-object
+    u = jsfxc.Unit("t", "@init\nfunction f(x) instance(s) ( s += x; this.n += 1; s; );\n@sample\na.f(spl0); b.f(spl1); f(1);\n")
+    assert {"a.s", "a.n", "b.s", "b.n", "f.s", "f.n"} <= set(u.vars)
     with pytest.raises(NotImplementedError):
-        jsfxc.Unit("t", "@init\nfunction f() instance(s) ( s = 1; );\n")
+        jsfxc.Unit("t", "@sample\nx = gmem[3];\n")
 
 
 @pytest.mark.parametrize("key", ["RTT", "SOMA", "ATTACK", "ERBTilt", "SpectralStabilizer", "DDT", "DPT", "SaliencePush", "ADS",

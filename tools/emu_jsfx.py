@@ -20,7 +20,8 @@ class GenLaunch(C.Structure):
                 ("row_stride", C.c_int64), ("n_frames", C.c_int64), ("mem_slots", C.c_int64),
                 ("n_streams", C.c_int), ("block_len", C.c_int), ("n_rows", C.c_int), ("n_decl", C.c_int),
                 ("q", C.c_void_p), ("decl_index0", C.c_void_p),
-                ("state", C.c_void_p), ("mem", C.c_void_p), ("mt", C.c_void_p), ("err", C.c_void_p), ("srate", C.c_double)]
+                ("state", C.c_void_p), ("mem", C.c_void_p), ("mt", C.c_void_p), ("err", C.c_void_p), ("srate", C.c_double),
+                ("fft_scratch", C.c_int64), ("tw", C.c_void_p)]
 
 
 def build(key: str) -> Path:
@@ -38,7 +39,7 @@ class Emu:
         self.lib = C.CDLL(str(build(key)))
         self.lib.emu_var_name.restype = C.c_char_p
         self.f64 = f64
-        self.n_vars, self.n_in, self.n_out, self.mem_slots = (self.lib.emu_info(i) for i in range(4))
+        self.n_vars, self.n_in, self.n_out, self.mem_slots, self.fft_scratch = (self.lib.emu_info(i) for i in range(5))
         self.names = [self.lib.emu_var_name(k).decode() for k in range(self.n_vars)] if self.n_vars > 0 else []
 
     def render(self, sliders, params, x, block=512, srate=48000.0, mem_slots=None):
@@ -50,12 +51,15 @@ class Emu:
         q = np.ascontiguousarray(zo.quantise(sliders, p))
         idx = np.array([s["index0"] for s in sliders], np.int32)
         slots = self.mem_slots if mem_slots is None else mem_slots          # (tests shrink the heap to provoke the overflow path)
-        state = np.zeros(self.n_vars + 65, dt); mem = np.zeros(slots + 1, dt)          # + the spare slot out-of-range accesses land in
+        state = np.zeros(self.n_vars + 65, dt); mem = np.zeros(slots + 1 + self.fft_scratch, dt)   # + the spare slot out-of-range accesses land in + FFT scratch
+        kk = np.arange(16384) * (2 * np.pi / 32768.0)
+        tw = np.ascontiguousarray(np.stack([np.cos(kk), -np.sin(kk)], axis=1))
         mt = np.zeros(625, np.uint32); err = np.zeros(1, np.int32)
         xin = np.ascontiguousarray(x, np.float32)
         y = np.zeros((max(self.n_out, 1), nf), np.float32); tap = np.zeros((max(self.n_out, 1), nf), np.float64)
         a = GenLaunch(xin.ctypes.data, y.ctypes.data, tap.ctypes.data, nf, nf, slots, 1, block, 1, len(sliders),
-                      q.ctypes.data, idx.ctypes.data, state.ctypes.data, mem.ctypes.data, mt.ctypes.data, err.ctypes.data, srate)
+                      q.ctypes.data, idx.ctypes.data, state.ctypes.data, mem.ctypes.data, mt.ctypes.data, err.ctypes.data, srate,
+                      self.fft_scratch, tw.ctypes.data)
         self.lib.emu_prepare(C.byref(a), int(self.f64))
         a.n_rows = q.shape[0]
         self.lib.emu_process(C.byref(a), int(self.f64))

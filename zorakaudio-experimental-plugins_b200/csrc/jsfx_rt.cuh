@@ -47,6 +47,7 @@ struct GenLaunch {
     int n_streams, block_len, n_rows, n_decl;
     const double* q; const int* decl_index0;
     void* state; void* mem; unsigned* mt; int* err; double srate;
+    int64_t fft_scratch; const double* tw;
 };
 }
 #else
@@ -120,6 +121,176 @@ template <typename R> struct Rt {
     R srate, samplesblock;
     R sliders[64];
     R spl[64];
+    long long scr, scr_n;         // FFT scratch: slots [scr, scr + scr_n) of this stream's heap column, beyond the script's own slots
+    const double* tw;             // e^{-2 pi i k / 32768}, k = 0 .. 16383, as (cos, -sin) pairs (host libm)
+    unsigned long long pending;   // pendingSliderChange | Automate | AutomateEnd masks of this host block (DSPJSFX_State, :3321-3387)
+
+
+    // ---- FFT runtime hooks: jsfx_fft / ifft / fft_real / ifft_real / fft_permute / fft_ipermute / convolve_c
+    // (src/JSFXJuceProcessor.cpp:1267-1447 over src/WDL/fft.c), for ONE stream per thread on its heap column.
+    // Contract kept: sizes 16 .. 32768 powers of two, the region inside one 65536-slot page (:1131-1158), index rounding
+    // v +- 1e-5 (:1121-1124), invalid arguments do nothing and return 0; forward kernel e^{-2 pi i k n / N}, unscaled both
+    // ways (round trip gain N); between fft() and fft_permute() bin k lives at position WDL_fft_permute_tab(N)[k] =
+    // wdl_pos(k, N) below (fft.c:990-1025); real forward = 2 x DFT with the Nyquist bin in bin0.im (fft.h:62-71).
+    // The transform itself is a Stockham radix-2 autosort ping-ponging between the region and the per-stream scratch the
+    // heap carries, followed by a scatter into WDL's order: same values as WDL's split-radix code to rounding.
+    __device__ __forceinline__ static long long round_index(R v) { const double d = (double)v; return (long long)(d + (d >= 0.0 ? 1.0e-5 : -1.0e-5)); }
+    __device__ __forceinline__ static bool size_ok(long long n) { return n >= 16 && n <= 32768 && (n & (n - 1)) == 0; }
+    __device__ __forceinline__ static bool in_page(long long base, long long span)
+    {
+        if (base < 0 || span <= 0) return false;
+        return (base / 65536) == ((base + span - 1) / 65536);
+    }
+    __device__ __forceinline__ R& at(long long a) { return *slot((unsigned)a); }
+    // fftfreq_c (fft.c:990-1005) inverted: the buffer position of frequency j in djbfft's output order
+    __device__ static int pos_of_freq(unsigned j, unsigned n)
+    {
+        int p = 0;
+        while (n > 2) {
+            if (!(j & 1)) { j >>= 1; n >>= 1; }
+            else if ((j & 3) == 1) { p += n >> 1; j = (j - 1) >> 2; n >>= 2; }
+            else { p += (n >> 1) + (n >> 2); j = ((j + 1) & (n - 1)) >> 2; n >>= 2; }
+        }
+        return p + (int)j;
+    }
+    __device__ __forceinline__ static int wdl_pos(int k, int n) { return k == 0 ? 0 : pos_of_freq((unsigned)(n - k), (unsigned)n); }   // _idxperm[n - j] = i
+    __device__ __forceinline__ bool note(long long last)        // heap bounds: like every mem[] access
+    {
+        if (sizeof(R) == 8) amax = last > amax ? last : amax; else amax32 = max(amax32, (int)min(last, (long long)0x7fffffff));
+        return last < cap;
+    }
+    __device__ bool complex_region(R baseR, long long n, long long& base)
+    {
+        long long start = round_index(baseR);
+        if (start < 0) start = 0;
+        if (n <= 0 || n > 32768 || !in_page(start, 2 * n)) return false;
+        base = start;
+        return note(start + 2 * n - 1);
+    }
+    __device__ bool need_scratch(long long slots)
+    {
+        if (slots <= scr_n) return true;
+        *err = 1;                                  // the heap of this plugin was built without (enough) FFT scratch: fail the call loudly
+        return false;
+    }
+    // natural-order DFT of the N complex values at `src` (slot index), result left at `dst`; src / dst are the region and the
+    // scratch in either order; inverse = conjugate twiddles.
+    __device__ void stockham(long long a, long long b, int N, bool inverse, bool want_in_a)
+    {
+        long long src = a, dst = b;
+        const int half = N >> 1;
+        for (int Ns = 1; Ns < N; Ns <<= 1) {
+            const int tstep = 16384 / Ns;
+            for (int j = 0; j < half; ++j) {
+                const int k = j & (Ns - 1);
+                const double wr = tw[2 * (k * tstep)], wi = inverse ? -tw[2 * (k * tstep) + 1] : tw[2 * (k * tstep) + 1];
+                const R v0r = at(src + 2 * j), v0i = at(src + 2 * j + 1), xr = at(src + 2 * (j + half)), xi = at(src + 2 * (j + half) + 1);
+                const R v1r = sub_(mul_((R)wr, xr), mul_((R)wi, xi)), v1i = add_(mul_((R)wr, xi), mul_((R)wi, xr));
+                const long long j0 = (long long)(((j - k) << 1) + k);
+                at(dst + 2 * j0) = add_(v0r, v1r); at(dst + 2 * j0 + 1) = add_(v0i, v1i);
+                at(dst + 2 * (j0 + Ns)) = sub_(v0r, v1r); at(dst + 2 * (j0 + Ns) + 1) = sub_(v0i, v1i);
+            }
+            const long long t = src; src = dst; dst = t;
+        }
+        if ((src == a) != want_in_a)
+            for (int i = 0; i < 2 * N; ++i) at(dst + i) = at(src + i);
+    }
+    __device__ void fft_c(long long base, int N, bool inverse)
+    {
+        const long long s0 = scr;
+        if (!inverse) {         // region -> natural order in the scratch -> scattered to WDL's order in the region
+            stockham(base, s0, N, false, false);
+            for (int k = 0; k < N; ++k) { const int p = wdl_pos(k, N); at(base + 2 * p) = at(s0 + 2 * k); at(base + 2 * p + 1) = at(s0 + 2 * k + 1); }
+        } else {                // WDL's order in the region -> natural order in the scratch -> time samples in the region
+            for (int k = 0; k < N; ++k) { const int p = wdl_pos(k, N); at(s0 + 2 * k) = at(base + 2 * p); at(s0 + 2 * k + 1) = at(base + 2 * p + 1); }
+            stockham(s0, base, N, true, false);
+        }
+    }
+    __device__ R fft(R b, R sz, bool inverse)
+    {
+        const long long N = round_index(sz);
+        long long base;
+        if (!size_ok(N) || !complex_region(b, N, base) || !need_scratch(2 * N)) return R(0);
+        fft_c(base, (int)N, inverse);
+        return R(0);
+    }
+    __device__ R fft_permute(R b, R sz, bool inverse)
+    {
+        const long long N = round_index(sz);
+        long long base;
+        if (!size_ok(N) || !complex_region(b, N, base) || !need_scratch(2 * N)) return R(0);
+        for (int i = 0; i < (int)N; ++i) {
+            const int p = wdl_pos(i, (int)N);
+            if (!inverse) { at(scr + 2 * i) = at(base + 2 * p); at(scr + 2 * i + 1) = at(base + 2 * p + 1); }        // sc[i] = buf[perm[i]]
+            else { at(scr + 2 * p) = at(base + 2 * i); at(scr + 2 * p + 1) = at(base + 2 * i + 1); }               // sc[perm[i]] = buf[i]
+        }
+        for (int i = 0; i < 2 * (int)N; ++i) at(base + i) = at(scr + i);
+        return R(0);
+    }
+    // WDL_real_fft (fft.c:1110-1178): N reals as N/2 complex values, two-for-one split with tw = e^{2 pi i k / N}
+    __device__ R fft_real(R b, R sz, bool inverse)
+    {
+        const long long len = round_index(sz);
+        long long start = round_index(b);
+        if (start < 0) start = 0;
+        if (!size_ok(len) || !in_page(start, len) || !note(start + len - 1) || !need_scratch(len)) return R(0);
+        const int half = (int)len >> 1, quart = half >> 1;
+        if (!inverse) {
+            fft_c(start, half, false);
+            const R t1 = add_(at(start), at(start + 1)), t2 = sub_(at(start), at(start + 1));
+            at(start) = mul_(t1, R(2)); at(start + 1) = mul_(t2, R(2));                                          // r2
+        } else {
+            const R t1 = add_(at(start), at(start + 1)), t2 = sub_(at(start), at(start + 1));
+            at(start) = t1; at(start + 1) = t2;                                                                  // v2
+        }
+        const int tstep = 32768 / (int)len;
+        for (int i = 1; i < quart; ++i) {
+            const long long p = start + 2 * wdl_pos(i, half), q = start + 2 * wdl_pos(half - i, half);
+            double twr = tw[2 * (i * tstep)];                       // cos(2 pi i / len)
+            const double twi = -tw[2 * (i * tstep) + 1];            // sin(2 pi i / len)
+            if (!inverse) twr = -twr;
+            const R sr = add_(at(p), at(q)), si = add_(at(p + 1), at(q + 1)), dr = sub_(at(p), at(q)), di = sub_(at(p + 1), at(q + 1));
+            const R tw1 = add_(mul_((R)twr, si), mul_((R)twi, dr)), tw2 = sub_(mul_((R)twi, si), mul_((R)twr, dr));
+            at(p) = sub_(sr, tw1); at(p + 1) = sub_(di, tw2);
+            at(q) = add_(sr, tw1); at(q + 1) = sub_(R(0), add_(di, tw2));
+        }
+        {
+            const long long p = start + 2 * wdl_pos(quart, half);
+            at(p) = mul_(at(p), R(2)); at(p + 1) = mul_(at(p + 1), R(-2));
+        }
+        if (inverse) fft_c(start, half, true);
+        return R(0);
+    }
+    __device__ R convolve_c(R d, R sR, R nR)                      // dest[i] *= src[i] (complex), :1341-1383
+    {
+        const long long n = round_index(nR);
+        long long db, sb;
+        if (!complex_region(d, n, db) || !complex_region(sR, n, sb)) return R(0);
+        const bool overlaps = (db < sb + 2 * n) && (sb < db + 2 * n);
+        long long src = sb;
+        if (overlaps && db != sb) {
+            if (!need_scratch(2 * n)) return R(0);
+            for (long long i = 0; i < 2 * n; ++i) at(scr + i) = at(sb + i);
+            src = scr;
+        }
+        for (long long i = 0; i < n; ++i) {
+            const R ar = at(db + 2 * i), ai = at(db + 2 * i + 1), br = at(src + 2 * i), bi = at(src + 2 * i + 1);
+            at(db + 2 * i) = sub_(mul_(ar, br), mul_(ai, bi));
+            at(db + 2 * i + 1) = add_(mul_(ar, bi), mul_(ai, br));
+        }
+        return R(0);
+    }
+
+    // sliderchange(mask) / slider_automate(mask[, end]) inside a DSP section: the host hook ORs round(mask) into the pending
+    // masks and returns 1 (src/JSFXJuceProcessor.cpp:2448-2476); @slider then re-runs once after @block
+    // (dsp_jsfx_aot.py:5786-5804) and the host clears the masks after the block (consumeDspSliderChanges, :5665-5738).
+    __device__ __forceinline__ R sliderchange(R mask)
+    {
+        const long long m = mask > R(0) ? llround((double)mask) : 0;
+        if (m <= 0) return R(0);
+        pending |= (unsigned long long)m;
+        return R(1);
+    }
 
     // a[b] = mem[trunc(a + b + 1e-5)], negative -> 0 (:4062-4103).  fp64 mode follows the reference's double
     // arithmetic; fp32 mode keeps the whole index computation in float / int32 (heaps are far below 2^24 slots, so
@@ -243,7 +414,8 @@ __device__ __forceinline__ void ctx_open(Rt<R>& c, R* v, const GenLaunch& a, int
     c.mem = reinterpret_cast<R*>(a.mem) + sc; c.stride = ns; c.cap = a.mem_slots;
     c.mt = a.mt + sc; c.err = a.err; c.amax = -1; c.amax32 = -1;
     c.cap32 = (int)a.mem_slots; c.stride_bytes = (unsigned)a.n_streams * (unsigned)sizeof(R);
-    c.srate = (R)a.srate; c.samplesblock = (R)0;
+    c.srate = (R)a.srate; c.samplesblock = (R)0; c.pending = 0;
+    c.scr = a.mem_slots + 1; c.scr_n = a.fft_scratch; c.tw = a.tw;       // scratch sits behind the spare slot out-of-range accesses land in
     const R* st = reinterpret_cast<const R*>(a.state) + sc;
 #pragma unroll
     for (int k = 0; k < S::kVars; ++k) v[k] = st[(long long)k * ns];
@@ -369,7 +541,9 @@ __global__ void __launch_bounds__(32 * GenWarps<S>::value, 1) jsfx_process_kerne
                 if (changed) S::template slider<R>(c, v);
             }
             c.samplesblock = (R)nb;
+            c.pending = 0;                                   // cleared by the host after every block
             S::template block<R>(c, v);
+            if (c.pending) S::template slider<R>(c, v);      // @block changed sliders itself: @slider once before @sample
         }
         const int nb_next = (int)min((int64_t)a.block_len, a.n_frames - (pos + nb));      // <= 0 after the last block
         for (int f0 = 0; f0 < nb; f0 += kF) {
@@ -473,7 +647,9 @@ template <class S, typename R> void emu_process(const GenLaunch& a)
             if (changed) S::template slider<R>(c, v.data());
         }
         c.samplesblock = (R)nb;
+        c.pending = 0;
         S::template block<R>(c, v.data());
+        if (c.pending) S::template slider<R>(c, v.data());
         for (int f = 0; f < nb; ++f) {
             for (int ch = 0; ch < S::kCh; ++ch) c.spl[ch] = ch < S::kIn ? (R)a.in[ch * a.row_stride + pos + f] : (R)0;
             S::template sample<R>(c, v.data());
@@ -497,6 +673,7 @@ template <class S, typename R> void emu_process(const GenLaunch& a)
     struct Script {                                                                                                     \
         static constexpr int kVars = g_##IDENT::kVars, kIn = g_##IDENT::kIn, kOut = g_##IDENT::kOut, kCh = g_##IDENT::kCh, kDecl = g_##IDENT::kDecl; \
         static constexpr long long kMemSlots = (MEM_SLOTS);                                                             \
+        static constexpr long long kFftScratch = g_##IDENT::kFftScratch;                                                \
         static constexpr int alias(int i0) { return g_##IDENT::alias_slot(i0); }                                        \
         static constexpr int decl(int j) { return g_##IDENT::decl_slot(j); }                                            \
         template <typename R> static void init(Rt<R>& c, R* v) { sec_init<R>(c, v); }                                   \
@@ -507,7 +684,7 @@ template <class S, typename R> void emu_process(const GenLaunch& a)
     }  /* namespace g_IDENT */                                                                                          \
     }}                                                                                                                  \
     extern "C" {                                                                                                        \
-    int emu_info(int what) { using S = za::jsfx::g_##IDENT::Script; return what == 0 ? S::kVars : what == 1 ? S::kIn : what == 2 ? S::kOut : (int)(MEM_SLOTS); } \
+    int emu_info(int what) { using S = za::jsfx::g_##IDENT::Script; return what == 0 ? S::kVars : what == 1 ? S::kIn : what == 2 ? S::kOut : what == 3 ? (int)(MEM_SLOTS) : (int)S::kFftScratch; } \
     const char* emu_var_name(int k) { return za::jsfx::g_##IDENT::kVarNames[k]; }                                       \
     void emu_prepare(const za::GenLaunch* a, int f64) { using S = za::jsfx::g_##IDENT::Script; if (f64) za::jsfx::emu_prepare<S, double>(*a); else za::jsfx::emu_prepare<S, float>(*a); } \
     void emu_process(const za::GenLaunch* a, int f64) { using S = za::jsfx::g_##IDENT::Script; if (f64) za::jsfx::emu_process<S, double>(*a); else za::jsfx::emu_process<S, float>(*a); } \
@@ -518,6 +695,7 @@ template <class S, typename R> void emu_process(const GenLaunch& a)
     struct Script {                                                                                                     \
         static constexpr int kVars = g_##IDENT::kVars, kIn = g_##IDENT::kIn, kOut = g_##IDENT::kOut, kCh = g_##IDENT::kCh, kDecl = g_##IDENT::kDecl; \
         static constexpr long long kMemSlots = (MEM_SLOTS);                                                             \
+        static constexpr long long kFftScratch = g_##IDENT::kFftScratch;                                                \
         static __host__ __device__ constexpr int alias(int i0) { return g_##IDENT::alias_slot(i0); }                    \
         static __host__ __device__ constexpr int decl(int j) { return g_##IDENT::decl_slot(j); }                        \
         template <typename R> static __device__ __forceinline__ void init(Rt<R>& c, R* v) { sec_init<R>(c, v); }       \
@@ -531,7 +709,7 @@ template <class S, typename R> void emu_process(const GenLaunch& a)
         using S = g_##IDENT::Script;                                                                                    \
         static const ::za::GenDesc d = {KEY, g_##IDENT::kSliderText, S::kIn, S::kOut, S::kVars, (int64_t)(MEM_SLOTS),   \
                                         g_##IDENT::kVarNames, g_##IDENT::kAlias, &launch_prepare<S>, &launch_process<S>,  \
-                                        S::kDecl, g_##IDENT::kDeclIndex0};                                             \
+                                        S::kDecl, g_##IDENT::kDeclIndex0, (int64_t)S::kFftScratch};                    \
         return &d;                                                                                                      \
     }                                                                                                                   \
     namespace g_##IDENT {

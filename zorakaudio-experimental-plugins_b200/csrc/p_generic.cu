@@ -2,6 +2,7 @@
 // (vars / sliders / mem[] heap / MT19937 columns, all stream-minor structure of arrays), prepareToPlay and
 // processBlock as one kernel launch each (jsfx_rt.cuh).  The quantised automation rows of a call are uploaded
 // as doubles; @init / @slider / @block / @sample all run on the device.
+#include <cmath>
 #include <cstring>
 #include <string>
 
@@ -23,6 +24,7 @@ class GenericPlugin : public PluginImpl {
     void* d_state = nullptr; void* d_mem = nullptr; unsigned* d_mt = nullptr; int* d_err = nullptr;
     double* d_q = nullptr; size_t q_cap = 0;
     int* d_index0 = nullptr;
+    double* d_tw = nullptr;         // FFT twiddles e^{-2 pi i k / 32768}, k < 16384 (host libm), for leaves that call the FFT hooks
     int* h_err = nullptr;           // pinned mirror of d_err, refreshed by an async copy behind every launch
     size_t rsize = 8;
 
@@ -32,6 +34,7 @@ class GenericPlugin : public PluginImpl {
         a.mem_slots = I.opt_heap_slots > 0 ? std::min<int64_t>(I.opt_heap_slots, d_->mem_slots) : d_->mem_slots;   // (tests shrink the heap to provoke the overflow path)
         a.n_streams = I.n_streams; a.block_len = I.block_len; a.n_decl = (int)I.decls.size();
         a.decl_index0 = d_index0; a.state = d_state; a.mem = d_mem; a.mt = d_mt; a.err = d_err; a.srate = I.srate;
+        a.fft_scratch = d_->fft_scratch; a.tw = d_tw;
         return a;
     }
     std::vector<double> q_last;     // rows already on the device: static parameters are not uploaded again (a pageable
@@ -59,7 +62,7 @@ class GenericPlugin : public PluginImpl {
 
 public:
     explicit GenericPlugin(const GenDesc* d) : d_(d) {}
-    ~GenericPlugin() override { cudaFree(d_state); cudaFree(d_mem); cudaFree(d_mt); cudaFree(d_err); cudaFree(d_q); cudaFree(d_index0); cudaFreeHost(h_err); }
+    ~GenericPlugin() override { cudaFree(d_state); cudaFree(d_mem); cudaFree(d_mt); cudaFree(d_err); cudaFree(d_q); cudaFree(d_index0); cudaFree(d_tw); cudaFreeHost(h_err); }
 
     bool create(Instance& I) override
     {
@@ -79,7 +82,8 @@ public:
         for (int j = 0; same && j < d_->n_decl; ++j) same = idx[j] == d_->decl_index0[j];
         if (!same) { set_error(std::string(d_->key) + ": slider declarations differ from the ones the generated code was built for"); return false; }
         return cuda_ok(cudaMalloc(&d_state, (size_t)(d_->n_vars + 65) * ns * rsize), "state") &&
-               cuda_ok(cudaMalloc(&d_mem, (size_t)(d_->mem_slots + 1) * ns * rsize), "mem[] heap") /* + the spare slot out-of-range accesses land in */ &&
+               cuda_ok(cudaMalloc(&d_mem, (size_t)heap_slots() * ns * rsize), "mem[] heap") /* + the spare slot out-of-range accesses land in + FFT scratch */ &&
+               upload_twiddles() &&
                cuda_ok(cudaMalloc(&d_mt, 625 * ns * sizeof(unsigned)), "rand state") &&
                cuda_ok(cudaMalloc(&d_err, sizeof(int)), "err flag") &&
                cuda_ok(cudaHostAlloc(&h_err, sizeof(int), cudaHostAllocDefault), "err mirror") && ((*h_err = 0), true) &&
@@ -87,6 +91,15 @@ public:
                cuda_ok(cudaMemcpy(d_index0, idx.data(), idx.size() * sizeof(int), cudaMemcpyHostToDevice), "slider index upload");
     }
 
+    size_t heap_slots() const { return (size_t)(d_->mem_slots + 1 + d_->fft_scratch); }
+    bool upload_twiddles()
+    {
+        if (d_->fft_scratch <= 0) return true;
+        std::vector<double> t(2 * 16384);
+        for (int k = 0; k < 16384; ++k) { const double a = 6.283185307179586476925 * k / 32768.0; t[2 * k] = std::cos(a); t[2 * k + 1] = -std::sin(a); }
+        return cuda_ok(cudaMalloc(&d_tw, t.size() * sizeof(double)), "FFT twiddles") &&
+               cuda_ok(cudaMemcpy(d_tw, t.data(), t.size() * sizeof(double), cudaMemcpyHostToDevice), "FFT twiddles upload");
+    }
     bool heap_zeroed = false;
     bool reset(Instance& I) override   // resetStateStructOnly, then sliders, @init, alias re-apply, @slider
     {
@@ -95,7 +108,7 @@ public:
         // across prepareToPlay (resetStateStructOnly, :8972-8980, preserves st.mem / st.memN): a second prepare on a
         // handle sees the delay lines the previous render left, exactly as the reference instance would.
         if (!heap_zeroed) {
-            if (!cuda_ok(cudaMemsetAsync(d_mem, 0, (size_t)(d_->mem_slots + 1) * ns * rsize, I.stream), "heap reset")) return false;
+            if (!cuda_ok(cudaMemsetAsync(d_mem, 0, heap_slots() * ns * rsize, I.stream), "heap reset")) return false;
             heap_zeroed = true;
         }
         if (!cuda_ok(cudaMemsetAsync(d_state, 0, (size_t)(d_->n_vars + 65) * ns * rsize, I.stream), "state reset") ||
@@ -164,7 +177,7 @@ public:
     {
         const size_t ns = (size_t)I.n_streams;
         io.dev(d_state, (size_t)(d_->n_vars + 65) * ns * rsize);
-        io.dev(d_mem, (size_t)(d_->mem_slots + 1) * ns * rsize);
+        io.dev(d_mem, heap_slots() * ns * rsize);
         io.dev(d_mt, 625 * ns * sizeof(unsigned));
         io.host(&heap_zeroed, sizeof heap_zeroed);
     }

@@ -137,6 +137,8 @@ struct GenLaunch {
     unsigned* mt;                                  // [625][n_streams]: MT19937 words + index
     int* err;                                      // device flag: 1 = mem[] access beyond mem_slots
     double srate;
+    int64_t fft_scratch;                           // slots of FFT scratch per stream behind the heap (0: the script calls no FFT hook)
+    const double* tw;                              // device: e^{-2 pi i k / 32768}, k < 16384, (cos, -sin) pairs
 };
 struct GenDesc {
     const char* key; const char* slider_text;
@@ -146,6 +148,7 @@ struct GenDesc {
     bool (*prepare)(const GenLaunch&, int precision, cudaStream_t);
     bool (*process)(const GenLaunch&, int precision, cudaStream_t);
     int n_decl; const int* decl_index0;            // declared sliders the generated code was compiled for (declaration order)
+    int64_t fft_scratch;                           // FFT scratch slots per stream this script needs (2 x its largest transform)
 };
 
 }  // namespace za

@@ -23,8 +23,12 @@ Semantics restated from the reference's AOT compiler (file:line in /root/referen
   * loop count: trunc toward 0, negative -> 0, evaluated once (:5663-5707)
   * user functions are specialised per calling SECTION; local() variables are persistent state named by
     (section, function, local) (:1844-1848, :1905-2048); parameters are by value
-Not supported (translation fails loudly): instance()/this. namespaces, gmem, fft hooks, midi, file and
-message builtins, sliderchange / slider_automate inside DSP sections, string slider files.
+  * instance() / `this.` pseudo-objects (:1905-2048): a function that declares instance() variables or mentions `this` is
+    specialised per call-site namespace as well (`lp.f(x)`: instance s1 -> the global `lp.s1`; called bare, the function
+    is its own namespace); local() storage stays per (section, function)
+  * fft / ifft / fft_real / ifft_real / fft_permute / fft_ipermute / convolve_c (:5498-5564): the runtime hooks become
+    per-stream device transforms on the heap with WDL's ordering and scaling contract (csrc/jsfx_rt.cuh)
+Not supported (translation fails loudly): gmem, midi, file and message builtins, string slider files.
 """
 from __future__ import annotations
 
@@ -379,14 +383,27 @@ MATH1 = {"sin", "cos", "tan", "asin", "acos", "atan", "exp", "log", "log10", "sq
 MATH2 = {"pow", "atan2"}
 NOOP_CALLS = {"sprintf", "printf", "strcpy", "strcat", "strcmp", "strlen", "str_getchar", "str_setchar", "str_insert",
               "str_delete", "str_mid", "strncpy", "file_read", "file_write", "file_string"}
-UNSUPPORTED = {"fft", "ifft", "fft_real", "ifft_real", "fft_permute", "fft_ipermute", "convolve_c", "sliderchange",
-               "slider_automate", "slider_next_chg", "midisend", "midirecv", "midisend_buf", "midirecv_buf",
+FFT_CALLS = {"fft": "c.fft({0}, {1}, false)", "ifft": "c.fft({0}, {1}, true)", "fft_real": "c.fft_real({0}, {1}, false)",
+             "ifft_real": "c.fft_real({0}, {1}, true)", "fft_permute": "c.fft_permute({0}, {1}, false)",
+             "fft_ipermute": "c.fft_permute({0}, {1}, true)"}
+UNSUPPORTED = {"slider_next_chg", "midisend", "midirecv", "midisend_buf", "midirecv_buf",
                "file_open", "file_close", "file_mem", "file_riff", "file_avail"}
 STATE_BUILTINS = {"srate": "srate", "samplesblock": "samplesblock"}
 
 
 def cname(name: str) -> str:
     return "v_" + re.sub(r"[^A-Za-z0-9_]", lambda m: "_%02x" % ord(m.group(0)), name)
+
+
+def uses_this(n) -> bool:
+    """Does a parsed node mention `this` / `this.x` (as a variable or as a call prefix)?  (_node_uses_relative_namespace, :1860-1898)"""
+    if isinstance(n, tuple):
+        if n and n[0] in ("var", "call") and isinstance(n[1], str) and (n[1] == "this" or n[1].startswith("this.")):
+            return True
+        return any(uses_this(x) for x in n[1:])
+    if isinstance(n, list):
+        return any(uses_this(x) for x in n)
+    return False
 
 
 class Unit:
@@ -405,12 +422,13 @@ class Unit:
             keep = []
             for n in prog:
                 if n[0] == "fundef":
-                    if n[4]:
-                        raise NotImplementedError(f"{key}: instance() in function {n[1]}")
                     self.fundefs[n[1]] = n
                 else:
                     keep.append(n)
             self.progs[s] = keep
+        # a function is specialised per namespace when it declares instance() variables or mentions `this` (:1988-1991)
+        self.needs_ns = {name: bool(fd[4]) or uses_this(fd[5]) for name, fd in self.fundefs.items()}
+        self.uses_fft = False
         self.vars = {}            # jsfx name -> slot
         self.used_spl = set()
         self.spl_reads, self.spl_writes = set(), set()
@@ -432,17 +450,40 @@ class Unit:
             self.vars[name] = len(self.vars)
         return self.vars[name]
 
-    def specialise(self, section: str, fn: str) -> str:
-        key = (section, fn)
+    def resolve_call(self, fn: str, current_ns):
+        """User-function call name -> (base function, call namespace) as lower_user_functions does (:2017-2027): `f(...)` is a
+        plain call; `a.b.f(...)` calls f with namespace a.b, where a leading `this` is the caller's own namespace."""
+        if fn in self.fundefs:
+            return fn, None
+        parts = fn.split(".")
+        if len(parts) >= 2 and parts[-1] in self.fundefs:
+            prefix = ".".join(parts[:-1])
+            if prefix == "this":
+                ns = current_ns
+            elif prefix.startswith("this."):
+                suffix = prefix[5:]
+                ns = (f"{current_ns}.{suffix}" if suffix else current_ns) if current_ns else (suffix or current_ns)
+            else:
+                ns = prefix
+            return parts[-1], ns
+        return None, None
+
+    def specialise(self, section: str, fn: str, call_ns=None) -> str:
+        # per caller section, and per namespace where the function needs one; without a call namespace such a function is
+        # its own namespace (:2029-2040)
+        ns = call_ns if self.needs_ns.get(fn) else None
+        if self.needs_ns.get(fn) and not ns:
+            ns = fn
+        key = (section, fn, ns)
         if key in self.spec:
             return self.spec[key]
         if key in self.in_progress:
             raise NotImplementedError(f"{self.key}: recursive user function {fn}")
         self.in_progress.add(key)
-        _, name, params, locals_, _, body = self.fundefs[fn]
-        cn = f"fn_{section}_{re.sub(r'[^A-Za-z0-9_]', '_', name)}"
+        _, name, params, locals_, instances, body = self.fundefs[fn]
+        cn = f"fn_{section}_{re.sub(r'[^A-Za-z0-9_]', '_', name)}" + (f"__ns_{re.sub(r'[^A-Za-z0-9_]', '_', ns)}" if ns else "")
         local_map = {l: f"__fnlocal__{section}__{name}__{l}" for l in locals_}
-        em = Emitter(self, section, local_map, set(params))
+        em = Emitter(self, section, local_map, set(params), instance_map={i: f"{ns}.{i}" for i in instances} if ns else {}, namespace=ns)
         val = em.ex(body)
         args = "".join(f", R p_{re.sub(r'[^A-Za-z0-9_]', '_', p)}" for p in params)
         code = [f"template <typename R> __device__ ZA_JSFX_FN R {cn}(Rt<R>& c, R* v{args})", "{"] + em.lines + [f"    return {val};", "}", ""]
@@ -462,8 +503,9 @@ class Emitter:
     """Expression tree -> straight-line C++ statements with explicit temporaries (evaluation order = the
     reference's: left operand, right operand; right-hand side before the assignment target)."""
 
-    def __init__(self, unit: Unit, section: str, local_map: dict, params: set):
+    def __init__(self, unit: Unit, section: str, local_map: dict, params: set, instance_map: dict = None, namespace: str = None):
         self.u, self.section, self.local_map, self.params = unit, section, local_map, params
+        self.instance_map, self.namespace = instance_map or {}, namespace
         self.lines, self.n, self.ind = [], 0, 1
 
     def run(self, prog):
@@ -484,9 +526,15 @@ class Emitter:
     def ref(self, name: str, write: bool = False, read: bool = True) -> str:
         if name in self.params:
             return "p_" + re.sub(r"[^A-Za-z0-9_]", "_", name)
-        name = self.local_map.get(name, name)
-        if name == "this" or name.startswith("this."):
-            raise NotImplementedError(f"{self.u.key}: this. namespaces")
+        if name in self.local_map:
+            name = self.local_map[name]
+        elif name in self.instance_map:                     # instance(s1) called as ns.f() -> the global pseudo-object member ns.s1
+            name = self.instance_map[name]
+        elif name == "this":
+            name = self.namespace or name
+        elif name.startswith("this."):
+            suffix = name[5:]
+            name = (f"{self.namespace}.{suffix}" if suffix else self.namespace) if self.namespace else (suffix or name)
         m = re.fullmatch(r"spl(\d+)", name)
         if m:
             i = int(m.group(1))
@@ -652,12 +700,29 @@ class Emitter:
         raise NotImplementedError(op)
 
     def call(self, fn, args):
-        if fn in self.u.fundefs:
+        base, call_ns = self.u.resolve_call(fn, self.namespace)
+        if base is not None:
             av = [self.ex(a) for a in args]
-            want = len(self.u.fundefs[fn][2])
+            want = len(self.u.fundefs[base][2])
             av = (av + ["R(0)"] * want)[:want]
-            cn = self.u.specialise(self.section, fn)
+            cn = self.u.specialise(self.section, base, call_ns)
             return self.tmp(f"{cn}<R>(c, v{''.join(', ' + a for a in av)})")
+        if fn in ("sliderchange", "slider_automate") and 1 <= len(args) <= 2:
+            # a direct sliderN argument is its bit (_emit_slider_mask_arg, :4133-4144); both builtins OR the mask into the pending
+            # masks (the gesture begin / end hint of slider_automate only concerns the host UI)
+            m = re.fullmatch(r"slider([1-9][0-9]?)", args[0][1]) if args[0][0] == "var" else None
+            mask = lit(float(1 << (int(m.group(1)) - 1))) if m and 1 <= int(m.group(1)) <= 64 else self.ex(args[0])
+            if len(args) == 2:
+                self.ex(args[1])
+            return self.tmp(f"c.sliderchange({mask})")
+        if fn in FFT_CALLS and len(args) == 2:             # runtime hooks (:5498-5564) -> per-stream device FFT on the heap (jsfx_rt.cuh)
+            av = [self.ex(a) for a in args]
+            self.u.uses_fft = True
+            return self.tmp(FFT_CALLS[fn].format(*av))
+        if fn == "convolve_c" and len(args) == 3:
+            av = [self.ex(a) for a in args]
+            self.u.uses_fft = True
+            return self.tmp(f"c.convolve_c({av[0]}, {av[1]}, {av[2]})")
         if fn.startswith("gfx_") or fn in NOOP_CALLS or fn in ("slider_show", "freembuf"):
             for a in args:
                 self.ex(a)
@@ -699,7 +764,8 @@ def c_string(s: str) -> str:
     return '"' + s.replace("\\", "\\\\").replace('"', '\\"') + '\\n"'
 
 
-def generate(key: str, jsfx_path: str, mem_slots: int, source_label: str) -> str:
+def generate(key: str, jsfx_path: str, mem_slots: int, source_label: str, fft_max: int = 32768) -> str:
+    """fft_max: the largest transform size the script uses (sizes the per-stream FFT scratch: 2 x fft_max slots)."""
     text = Path(jsfx_path).read_text(errors="replace")
     u = Unit(key, text)
     ident = re.sub(r"[^A-Za-z0-9_]", "_", key)
@@ -717,6 +783,7 @@ def generate(key: str, jsfx_path: str, mem_slots: int, source_label: str) -> str
     out.append(f"namespace za {{ namespace jsfx {{ namespace g_{ident} {{")
     out.append("")
     out.append(f"constexpr int kVars = {max(len(names), 1)}, kIn = {u.n_in}, kOut = {u.n_out}, kCh = {nch};")
+    out.append(f"constexpr long long kFftScratch = {2 * fft_max if u.uses_fft else 0};     // slots of per-stream FFT scratch behind the heap")
     out.append("")
     out += u.spec_code
     for s in SECTIONS:
