@@ -86,6 +86,11 @@ ZA_API int za_gpu_quantise(const za_slider_info* slider, float host_value, doubl
  * reference would be driven with (samplesblock; parameters are sampled once per block). */
 ZA_API int za_gpu_create(const char* plugin_key, int n_streams, double sample_rate, int block_len,
                          int precision, int device, za_gpu_handle* out);
+/* The same with the reference's oversampling option (x1 / x2 / x4 / x8; src/JSFXJuceProcessor.cpp:3126-3146, 8704-8789): per host
+ * block the input is up-sampled linearly inside the block, the plugin runs at sample_rate x oversampling on blocks of
+ * block_len x oversampling frames, and the output is box-averaged back.  I/O stays at the host rate. */
+ZA_API int za_gpu_create_os(const char* plugin_key, int n_streams, double sample_rate, int block_len, int precision, int device,
+                            int oversampling, za_gpu_handle* out);
 ZA_API int za_gpu_destroy(za_gpu_handle h);
 /* Run on an existing CUDA stream (e.g. the caller's torch stream); NULL = the handle's own. */
 ZA_API int za_gpu_set_stream(za_gpu_handle h, void* cuda_stream);

@@ -200,3 +200,31 @@ def test_checkpoint_resume_is_bit_identical(gpu, key, prec):
         other.load_state(blob)
     other.close(); fresh.close()
     assert np.isfinite(y1).all() and info.n_out == y2.shape[1]
+
+
+@pytest.mark.parametrize("key,factor", [("EasyExpander", 2), ("cascade8", 4), ("RTT", 2), ("ERBTilt", 8)])
+def test_oversampling_like_the_reference_host(gpu, key, factor):
+    """za_gpu_create_os: per host block linear up-sampling inside the block (its last frame held), the plugin at srate x factor on
+    blocks of block_len x factor frames, box average back (src/JSFXJuceProcessor.cpp:8704-8789).  Checked against the reference's
+    compiled plugin driven the same way on the CPU."""
+    block = 512
+    ns, nf = 7, block * 9 + 77
+    p0, pauto, x = _case(gpu, key, ns, nf, block, automate=True)
+    orc = zo.best_oracle(key)
+    # the host's up-sampler, block-local, in float like upsampleLinearBlock (:8704-8727)
+    xu = np.empty((ns, x.shape[1], nf * factor), np.float32)
+    nxt = np.concatenate([x[:, :, 1:], x[:, :, -1:]], axis=2)
+    last = ((np.arange(nf) + 1) % block == 0) | (np.arange(nf) == nf - 1)
+    nxt[:, :, last] = x[:, :, last]
+    for sub in range(factor):
+        t = np.float32(sub) / np.float32(factor)
+        xu[:, :, sub::factor] = x + (nxt - x) * t
+    yu, _ = orc.render(pauto, xu, srate=48000.0 * factor, block=block * factor)
+    want = (yu.astype(np.float64).reshape(ns, yu.shape[1], nf, factor).sum(axis=3) / factor).astype(np.float32)
+    bp = gpu.BatchProcessor(key, ns, 48000.0, block, "f64", oversampling=factor).prepare(pauto[0])
+    got = bp.process(x, params=pauto)
+    db = dbfs_rms(got.astype(np.float64) - want)
+    print(f"oversampling x{factor} {key}: residual {db:.1f} dBFS, float-equal {np.mean(got == want):.4f}")
+    assert db < -140.0
+    assert np.mean(got == want) > 0.99
+    bp.close()

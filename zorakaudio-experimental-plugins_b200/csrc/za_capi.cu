@@ -159,8 +159,8 @@ void Instance::time_end()
 // ---- processBlock over a stream range with device buffers ----------------------------------------
 // params: [n_param_blocks][n_streams][n_decl] host floats (may be null with n_param_blocks == 0).
 // in/out/tap point at stream s0's first row.
-static bool process_range(Instance& I, const float* params, int n_param_blocks, int s0, int ns, const float* in,
-                          float* out, double* tap, int64_t n_frames, int64_t stride)
+static bool process_range_engine(Instance& I, const float* params, int n_param_blocks, int s0, int ns, const float* in,
+                                 float* out, double* tap, int64_t n_frames, int64_t stride)
 {
     const int nd = (int)I.decls.size();
     const int64_t bl = I.block_len;
@@ -230,6 +230,72 @@ static bool process_range(Instance& I, const float* params, int n_param_blocks, 
     return true;
 }
 
+// ---- oversampling x2 / x4 / x8 around any plugin (src/JSFXJuceProcessor.cpp:8704-8789) ---------------------------------
+// Per HOST block: linear up-sampling inside the block (the block's last frame is held: `b = (i + 1 < hostSamples) ? src[i + 1]
+// : a`, float arithmetic a + (b - a) * ((float) sub / (float) factor)), the engine renders block_len x factor frames at srate x
+// factor, then a box average back (sum in double over `factor` frames / factor -> float).
+__global__ void __launch_bounds__(256) os_up_kernel(const float* __restrict__ in, int64_t in_stride, float* __restrict__ out, int64_t out_stride,
+                                                   int64_t n_host, int host_block, int factor)
+{
+    const float* src = in + (size_t)blockIdx.y * in_stride;
+    float* dst = out + (size_t)blockIdx.y * out_stride;
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < n_host * factor; e += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t i = e / factor;
+        const int sub = (int)(e - i * factor);
+        const bool last = (i + 1 >= n_host) || ((i + 1) % host_block == 0);
+        const float a = src[i], b = last ? a : src[i + 1];
+        const float t = __fdiv_rn((float)sub, (float)factor);
+        dst[e] = __fadd_rn(a, __fmul_rn(__fsub_rn(b, a), t));
+    }
+}
+__global__ void __launch_bounds__(256) os_down_kernel(const float* __restrict__ eng, int64_t eng_stride, float* __restrict__ out, int64_t out_stride,
+                                                     int64_t n_host, int factor)
+{
+    const float* src = eng + (size_t)blockIdx.y * eng_stride;
+    float* dst = out + (size_t)blockIdx.y * out_stride;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_host; i += (int64_t)gridDim.x * blockDim.x) {
+        double sum = 0.0;
+        for (int sub = 0; sub < factor; ++sub) sum = __dadd_rn(sum, (double)src[i * factor + sub]);
+        dst[i] = (float)__ddiv_rn(sum, (double)factor);
+    }
+}
+
+static bool process_range(Instance& I, const float* params, int n_param_blocks, int s0, int ns, const float* in,
+                          float* out, double* tap, int64_t n_frames, int64_t stride)
+{
+    if (I.oversample <= 1) return process_range_engine(I, params, n_param_blocks, s0, ns, in, out, tap, n_frames, stride);
+    if (tap) { set_error("za_gpu_process_tap64: no double tap on an oversampled handle (the host-rate output is a box average of floats)"); return false; }
+    const int f = I.oversample, n_in = I.desc->n_in, n_out = I.desc->n_out, nd = (int)I.decls.size();
+    const int64_t hb = I.host_block, chunk_blocks = 64, cf = hb * chunk_blocks;      // host frames per chunk
+    const int64_t need = (cf * f + 31) / 32 * 32;
+    if (need != I.os_stride) {
+        cudaFree(I.os_in); cudaFree(I.os_out); I.os_in = I.os_out = nullptr; I.os_stride = 0;
+        if (!cuda_ok(cudaMalloc(&I.os_in, (size_t)I.n_streams * std::max(n_in, 1) * need * 4), "oversampling input") ||
+            !cuda_ok(cudaMalloc(&I.os_out, (size_t)I.n_streams * n_out * need * 4), "oversampling output")) return false;
+        I.os_stride = need;
+    }
+    for (int64_t f0 = 0; f0 < n_frames; f0 += cf) {
+        const int64_t nh = std::min<int64_t>(cf, n_frames - f0);
+        const unsigned gx = (unsigned)std::min<int64_t>((nh * f + 255) / 256, 32);
+        if (n_in > 0) {
+            os_up_kernel<<<dim3(gx, (unsigned)(ns * n_in)), 256, 0, I.stream>>>(in + f0, stride, I.os_in, need, nh, (int)hb, f);
+            if (!cuda_ok(cudaGetLastError(), "os_up_kernel")) return false;
+            ++I.launches;
+        }
+        const int64_t b0 = f0 / hb;
+        const float* p = nullptr; int np = 0;
+        if (params && n_param_blocks > 0) {
+            const int64_t r0 = std::min<int64_t>(b0, n_param_blocks - 1);
+            p = params + (size_t)r0 * I.n_streams * nd; np = (int)(n_param_blocks - r0);
+        }
+        if (!process_range_engine(I, p, np, s0, ns, I.os_in, I.os_out, nullptr, nh * f, need)) return false;
+        os_down_kernel<<<dim3(gx, (unsigned)(ns * n_out)), 256, 0, I.stream>>>(I.os_out, need, out + f0, stride, nh, f);
+        if (!cuda_ok(cudaGetLastError(), "os_down_kernel")) return false;
+        ++I.launches;
+    }
+    return true;
+}
+
 static void free_staging(Instance& I)
 {
     for (int i = 0; i < 3; ++i) {
@@ -247,7 +313,7 @@ static bool process_host(Instance& I, const float* params, int npb, const float*
                          int64_t n_frames, int64_t stride)
 {
     const int n_in = I.desc->n_in, n_out = I.desc->n_out, nd = (int)I.decls.size();
-    const int64_t bl = I.block_len;
+    const int64_t bl = I.host_block;
     int64_t cf;                                                        // frames per chunk
     if (I.opt_host_chunk > 0) {
         cf = (int64_t)I.opt_host_chunk;
@@ -414,8 +480,16 @@ ZA_API int za_gpu_quantise(const za_slider_info* s, float host_value, double* ou
 ZA_API int za_gpu_create(const char* key, int n_streams, double srate, int block_len, int precision, int device,
                          za_gpu_handle* out)
 {
+    return za_gpu_create_os(key, n_streams, srate, block_len, precision, device, 1, out);
+}
+
+ZA_API int za_gpu_create_os(const char* key, int n_streams, double srate, int block_len, int precision, int device, int oversampling,
+                            za_gpu_handle* out)
+{
     if (!out) return ZA_ERR_ARG;
     *out = nullptr;
+    if (oversampling != 1 && oversampling != 2 && oversampling != 4 && oversampling != 8) { set_error("za_gpu_create_os: oversampling must be 1, 2, 4 or 8"); return ZA_ERR_ARG; }
+    if (block_len > 0 && block_len > (1 << 28) / oversampling) { set_error("za_gpu_create_os: block too long"); return ZA_ERR_ARG; }
     const PluginDesc* d = find_plugin(key);
     if (!d) { set_error(std::string("unknown plugin_key: ") + (key ? key : "(null)")); return ZA_ERR_PLUGIN; }
     if (n_streams <= 0 || block_len <= 0 || !(srate > 0) || (precision != ZA_F32 && precision != ZA_F64)) {
@@ -433,7 +507,9 @@ ZA_API int za_gpu_create(const char* key, int n_streams, double srate, int block
     auto* h = new za_gpu_instance();
     Instance& I = h->I;
     I.desc = d; I.decls = parse_slider_decls(d->slider_text);
-    I.n_streams = n_streams; I.block_len = block_len; I.precision = precision; I.device = device; I.srate = srate;
+    // the engine (every plugin back end) sees the oversampled rate and block length (reinitialiseJsfxForCurrentEngineRate, :8791-8800)
+    I.oversample = oversampling; I.host_block = block_len;
+    I.n_streams = n_streams; I.block_len = block_len * oversampling; I.precision = precision; I.device = device; I.srate = srate * oversampling;
     I.sliders.assign((size_t)n_streams * I.decls.size(), 0.0);
     for (int s = 0; s < n_streams; ++s)
         for (size_t j = 0; j < I.decls.size(); ++j) I.sliders[(size_t)s * I.decls.size() + j] = (double)I.decls[j].def;
@@ -454,6 +530,7 @@ ZA_API int za_gpu_destroy(za_gpu_handle h)
     cudaDeviceSynchronize();
     I.impl.reset();
     free_staging(I);
+    cudaFree(I.os_in); cudaFree(I.os_out);
     for (auto e : I.ev) cudaEventDestroy(e);
     for (int i = 0; i < 3; ++i) {
         if (I.ev_h2d[i]) cudaEventDestroy(I.ev_h2d[i]);

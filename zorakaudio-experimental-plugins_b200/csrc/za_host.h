@@ -105,6 +105,10 @@ struct Instance {
     int n_streams = 0, block_len = 512, precision = 1, device = 0;
     double srate = 48000.0;
     cudaStream_t stream = nullptr, own_stream = nullptr, h2d = nullptr, d2h = nullptr;
+    // oversampling (src/JSFXJuceProcessor.cpp:3126-3146, 8704-8789): the engine runs at srate x factor on host blocks of
+    // block_len x factor frames; `srate` / `block_len` above are the ENGINE's, host_block the caller's block length
+    int oversample = 1, host_block = 512;
+    float* os_in = nullptr; float* os_out = nullptr; int64_t os_stride = 0;
     bool prepared = false;
     std::vector<double> sliders;             // [n_streams][n_decl] current quantised values (st.sliders)
     std::vector<uint8_t> sliders_valid;      // lastSlidersValid per stream

@@ -42,7 +42,7 @@ SYMBOLS = [
     "za_gpu_set_option", "za_gpu_render", "za_gpu_last_error", "za_gpu_device_count", "za_gpu_version",
     "za_gpu_synth", "za_gpu_synth_tables", "za_gpu_checksum", "za_gpu_host_alloc", "za_gpu_host_free",
     "za_gpu_state_size", "za_gpu_state_save", "za_gpu_state_load",
-    "za_chain_create", "za_chain_destroy", "za_chain_info", "za_chain_stage", "za_chain_set_chunk_blocks", "za_chain_prepare",
+    "za_gpu_create_os", "za_chain_create", "za_chain_destroy", "za_chain_info", "za_chain_stage", "za_chain_set_chunk_blocks", "za_chain_prepare",
     "za_chain_process", "za_chain_sync",
 ]
 
@@ -65,6 +65,7 @@ def lib() -> C.CDLL:
         L.za_gpu_parse_sliders.argtypes = [C.c_char_p, C.POINTER(SliderInfo), C.c_int]
         L.za_gpu_quantise.argtypes = [C.POINTER(SliderInfo), C.c_float, C.POINTER(C.c_double)]
         L.za_gpu_create.argtypes = [C.c_char_p, C.c_int, C.c_double, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
+        L.za_gpu_create_os.argtypes = [C.c_char_p, C.c_int, C.c_double, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
         L.za_gpu_destroy.argtypes = [C.c_void_p]
         L.za_gpu_set_stream.argtypes = [C.c_void_p, C.c_void_p]
         L.za_gpu_prepare.argtypes = [C.c_void_p, C.c_void_p]
@@ -194,15 +195,15 @@ class BatchProcessor:
     """n_streams instances of one plugin on one B200 (one za_gpu handle)."""
 
     def __init__(self, plugin_key: str, n_streams: int, sample_rate: float = 48000.0, block_len: int = 512,
-                 precision: str = "f64", device: int = 0):
+                 precision: str = "f64", device: int = 0, oversampling: int = 1):
         self.key = plugin_key
         self.info = plugin_info(plugin_key)
         self.n_streams = n_streams
         self.block_len = block_len
         self.precision = ZA_F64 if precision in ("f64", ZA_F64) else ZA_F32
         self._h = C.c_void_p()
-        _check(lib().za_gpu_create(plugin_key.encode(), n_streams, sample_rate, block_len, self.precision, device,
-                                   C.byref(self._h)), "za_gpu_create")
+        _check(lib().za_gpu_create_os(plugin_key.encode(), n_streams, sample_rate, block_len, self.precision, device, oversampling,
+                                      C.byref(self._h)), "za_gpu_create")
 
     # prepareToPlay
     def prepare(self, param_block0=None):
