@@ -175,6 +175,21 @@ ZA_API int za_chain_process(za_chain_handle c, const float* const* params, const
                             int64_t n_frames, int64_t frame_stride, int mem);
 ZA_API int za_chain_sync(za_chain_handle c);
 
+/* ---- one call, several GPUs --------------------------------------------------- */
+/* Streams shard as contiguous ranges over `devices` (stream s -> shard s * n_devices / n_streams), no collective on the data
+ * path.  za_batch_process takes HOST buffers for the whole batch and renders every shard from its own host thread (bound to
+ * its GPU's NUMA node) through that device's own copy / kernel pipeline.  za_batch_shard gives the per-device handle
+ * (checkpoints, read_state, options). */
+typedef struct za_batch* za_batch_handle;
+ZA_API int za_batch_create(const char* plugin_key, int n_streams, double sample_rate, int block_len, int precision,
+                           const int* devices, int n_devices, int oversampling, za_batch_handle* out);
+ZA_API int za_batch_destroy(za_batch_handle b);
+ZA_API int za_batch_shards(za_batch_handle b, int* n_shards, int* first_stream, int* n_streams, int* device, int cap);
+ZA_API int za_batch_shard(za_batch_handle b, int shard, za_gpu_handle* out);
+ZA_API int za_batch_prepare(za_batch_handle b, const float* param_block0);
+ZA_API int za_batch_process(za_batch_handle b, const float* param_block, int n_param_blocks, const float* in, float* out,
+                            int64_t n_frames, int64_t frame_stride);
+
 /* ---- synthetic programme material + checksums ------------------- */
 /* Bench / sampled-parity tooling beside the render path: the inputs of a large bounce are generated ON THE DEVICE from a
  * counter-based hash of (seed, first_stream + s, channel, t0 + frame), so no PCIe or host storage is on the path, and

@@ -112,7 +112,9 @@ def test_preset_and_plugin_json(bounce, tmp_path):
     """APVTS-style state (<PARAM id="sliderN" value=...>, the reference's getStateInformation XML) and plugin.json slug:
     parsed on the host before any GPU work; --save-preset writes back the values the bounce uses."""
     write_wav(tmp_path / "a.wav", np.zeros((2, 64)), 48000, "i16")
-    (tmp_path / "plugin.json").write_text(json.dumps({"name": "Easy Expander", "slug": "EasyExpander", "version": "1.0"}))
+    meta = {"name": "EasyExpander", "slug": "EasyExpander", "pluginCode": "EEXP", "pluginType": "jsfx", "entry": "src/EasyExpander.jsfx",
+            "clapFeatures": ["audio-effect"]}
+    (tmp_path / "plugin.json").write_text(json.dumps(meta, indent=2))
     (tmp_path / "state.xml").write_text('<?xml version="1.0"?><PARAMETERS><PARAM id="slider1" value="-41.5"/>'
                                         '<PARAM id="slider2" value="24"/><FILES f0="x.wav"/></PARAMETERS>')
     r = subprocess.run([bounce, "--plugin-json", str(tmp_path / "plugin.json"), "--preset", str(tmp_path / "state.xml"), "--set", "2=30",
@@ -125,6 +127,21 @@ def test_preset_and_plugin_json(bounce, tmp_path):
     (tmp_path / "empty.xml").write_text("<PARAMETERS/>")
     r = subprocess.run([bounce, "--plugin", "EasyExpander", "--preset", str(tmp_path / "empty.xml"), str(tmp_path / "a.wav")], capture_output=True, text=True)
     assert r.returncode == 1 and "PARAM" in r.stderr
+
+
+def test_plugin_json_is_validated_like_pluginlib(bounce, tmp_path):
+    """The fields scripts/pluginlib.py:105-212 requires of a plugin.json, refused with its messages before any GPU work."""
+    write_wav(tmp_path / "a.wav", np.zeros((2, 64)), 48000, "i16")
+    good = {"name": "EasyExpander", "slug": "EasyExpander", "pluginCode": "EEXP", "pluginType": "jsfx", "entry": "src/EasyExpander.jsfx"}
+    cases = [({"slug": ""}, "Missing 'slug'"), ({"pluginCode": "EEXPX"}, "exactly 4 characters"), ({"manufacturerCode": "Zo"}, "manufacturerCode"),
+             ({"installPath": "x"}, "installPath"), ({"pluginType": "vst"}, "Invalid pluginType"), ({"pluginType": "faust"}, ".dsp"),
+             ({"pluginType": "faust", "entry": "src/EasyExpander.dsp"}, "does not match")]
+    for patch, msg in cases:
+        (tmp_path / "plugin.json").write_text(json.dumps({**good, **patch}))
+        r = subprocess.run([bounce, "--plugin-json", str(tmp_path / "plugin.json"), str(tmp_path / "a.wav")], capture_output=True, text=True)
+        assert r.returncode == 1 and msg in r.stderr, (patch, r.stderr)
+    r = subprocess.run([bounce, "--plugin", "EasyExpander", "--devices", "0-x", str(tmp_path / "a.wav")], capture_output=True, text=True)
+    assert r.returncode == 2
 
 
 def test_no_cpu_fallback(bounce, tmp_path):
@@ -180,3 +197,31 @@ def test_bounce_matches_reference_render(bounce, tmp_path, key, precision):
             assert d.max() <= 1 and np.mean(d == 0) > 0.9999, (d.max(), np.mean(d == 0))
         else:                                           # fp32 mode: below -100 dBFS residual, i.e. well under one 24-bit step rms
             assert np.sqrt(np.mean((d / 8388607.0) ** 2)) < 1e-5
+
+
+@pytest.mark.gpu
+def test_bounce_resume_from_checkpoint_and_device_list(bounce, tmp_path):
+    """A bounce interrupted after its first part (--state-out) and resumed by a second run (--state-in) gives the samples of the
+    uninterrupted bounce; `--devices 0,0` shards the jobs over two handles (two GPUs where present) with identical results."""
+    from za_gpu import workloads as wl
+    sr, n1, n2 = 48000, 512 * 40, 512 * 33 + 100
+    src = wl.programme_bursts(3, n1 + n2, n_ch=2).astype(np.float64)
+    whole, first, second = [], [], []
+    for s in range(3):
+        write_wav(tmp_path / f"w{s}.wav", src[s], sr, "f32"); whole.append(str(tmp_path / f"w{s}.wav"))
+        write_wav(tmp_path / f"a{s}.wav", src[s, :, :n1], sr, "f32"); first.append(str(tmp_path / f"a{s}.wav"))
+        write_wav(tmp_path / f"b{s}.wav", src[s, :, n1:], sr, "f32"); second.append(str(tmp_path / f"b{s}.wav"))
+    run = lambda args: subprocess.run([bounce, "--plugin", "SOMA", "--precision", "f64", "--chunk-seconds", "0.25"] + args, capture_output=True, text=True)
+    r = run(["--out-dir", str(tmp_path / "ow")] + whole)
+    assert r.returncode == 0, r.stderr
+    r = run(["--out-dir", str(tmp_path / "oa"), "--state-out", str(tmp_path / "ck.bin"), "--devices", "0,0"] + first)
+    assert r.returncode == 0, r.stderr
+    r = run(["--out-dir", str(tmp_path / "ob"), "--state-in", str(tmp_path / "ck.bin"), "--devices", "0,0"] + second)
+    assert r.returncode == 0, r.stderr
+    for s in range(3):
+        w = read_wav24(tmp_path / "ow" / f"w{s}.{s}.wav")
+        a = read_wav24(tmp_path / "oa" / f"a{s}.{s}.wav")
+        b = read_wav24(tmp_path / "ob" / f"b{s}.{s}.wav")
+        assert np.array_equal(np.concatenate([a, b], axis=1), w), s
+    rep = json.loads((tmp_path / "oa" / "report.json").read_text())
+    assert rep["devices"] == 2 and rep["oversampling"] == 1

@@ -228,3 +228,20 @@ def test_oversampling_like_the_reference_host(gpu, key, factor):
     assert db < -140.0
     assert np.mean(got == want) > 0.99
     bp.close()
+
+
+def test_one_call_several_gpus(gpu):
+    """za_batch_*: one batch sharded over the visible GPUs (1 here unless run with `gpurun --gpus N`; with one GPU two shards on the
+    same device exercise the same sharding, threading and row arithmetic) against the reference."""
+    n_dev = gpu.lib().za_gpu_device_count()
+    devices = list(range(n_dev)) if n_dev > 1 else [0, 0, 0]
+    ns, nf = 50, 512 * 7 + 100
+    ref = zo.RefPlugin("EasyExpander")
+    x = wl.programme_bursts(ns, nf)
+    base = np.array([s["default"] for s in ref.sliders], np.float32)
+    p = wl.automation(ref.sliders, (nf + 511) // 512, ns, which=[0, 1], base=base)
+    y, _ = ref.render(p, x)
+    mb = gpu.MultiGpuBatch("EasyExpander", ns, devices, precision="f64").prepare(p[0])
+    got = mb.process(x, params=p)
+    assert np.mean(got == y) > 0.9999
+    mb.close()

@@ -24,7 +24,8 @@ int usage(const char* argv0)
 {
     std::fprintf(stderr,
                  "usage: %s (--plugin KEY | --plugin-json plugin.json) [--precision f32|f64] [--block N] [--chunk-seconds S]\n"
-                 "          [--tail-seconds S] [--preset STATE.xml] [--set SLIDER=VALUE ...] [--save-preset OUT.xml] [--device D]\n"
+                 "          [--tail-seconds S] [--preset STATE.xml] [--set SLIDER=VALUE ...] [--save-preset OUT.xml]\n"
+                 "          [--device D | --devices 0,1,..|0-7] [--oversampling 1|2|4|8] [--state-in CKPT] [--state-out CKPT]\n"
                  "          [--out-dir DIR] IN.wav [IN2.wav ...]\n"
                  "       %s --list                 plugin keys, channel counts and sliders the library renders\n"
                  "       %s --wav-info FILE.wav    header + checksum of the decoded samples (no GPU needed)\n",
@@ -104,18 +105,61 @@ bool read_preset(const std::string& path, std::map<int, float>& out, std::string
     return true;
 }
 
-// "slug" of a plugin.json (the key the catalog tooling identifies a plugin by, pluginlib.py:105-212)
-bool read_slug(const std::string& path, std::string& slug, std::string& err)
+// plugin.json of a catalogue leaf: the fields scripts/pluginlib.py:105-212 requires, checked the way load_plugin does (the
+// packaging-only checks -- README present, location under plugins/<Category>/<Key>/ -- are not this tool's business).
+bool json_string(const std::string& t, const char* key, std::string& out)
+{
+    const size_t k = t.find(std::string("\"") + key + "\"");
+    const size_t c = k == std::string::npos ? k : t.find(':', k);
+    if (c == std::string::npos) return false;
+    size_t q0 = c + 1;
+    while (q0 < t.size() && std::isspace((unsigned char)t[q0])) ++q0;
+    if (q0 >= t.size() || t[q0] != '"') return false;
+    const size_t q1 = t.find('"', q0 + 1);
+    if (q1 == std::string::npos) return false;
+    out = t.substr(q0 + 1, q1 - q0 - 1);
+    return true;
+}
+bool ends_with(const std::string& a, const char* suf) { const size_t n = std::strlen(suf); return a.size() >= n && a.compare(a.size() - n, n, suf) == 0; }
+
+bool read_plugin_json(const std::string& path, std::string& slug, std::string& err)
 {
     std::string t;
     if (!slurp(path, t)) { err = "cannot open " + path; return false; }
-    const size_t k = t.find("\"slug\"");
-    const size_t c = k == std::string::npos ? k : t.find(':', k);
-    const size_t q0 = c == std::string::npos ? c : t.find('"', c);
-    const size_t q1 = q0 == std::string::npos ? q0 : t.find('"', q0 + 1);
-    if (q1 == std::string::npos) { err = path + ": no \"slug\""; return false; }
-    slug = t.substr(q0 + 1, q1 - q0 - 1);
+    std::string name, code, mcode, type, entry, tmp;
+    if (!json_string(t, "slug", slug) || slug.empty()) { err = path + ": Missing 'slug'"; return false; }
+    if (!json_string(t, "pluginCode", code) || code.empty()) { err = path + ": Missing 'pluginCode'"; return false; }
+    if (code.size() != 4) { err = path + ": pluginCode must be exactly 4 characters"; return false; }
+    if (json_string(t, "manufacturerCode", mcode) && mcode.size() != 4) { err = path + ": manufacturerCode must be exactly 4 characters"; return false; }
+    if (t.find("\"installPath\"") != std::string::npos) { err = path + ": installPath overrides are no longer supported"; return false; }
+    json_string(t, "entry", entry);
+    if (json_string(t, "pluginType", type)) for (auto& ch : type) ch = (char)std::tolower((unsigned char)ch);
+    if (type.empty()) type = ends_with(entry, ".dsp") ? "faust" : (ends_with(entry, ".jsfx") ? "jsfx" : "");
+    if (type != "faust" && type != "jsfx") { err = path + ": Invalid pluginType (expected 'faust' or 'jsfx')"; return false; }
+    if (!entry.empty() && type == "faust" && !ends_with(entry, ".dsp")) { err = path + ": Faust plugin entry must be a .dsp file"; return false; }
+    if (!entry.empty() && type == "jsfx" && !ends_with(entry, ".jsfx")) { err = path + ": JSFX plugin entry must be a .jsfx file"; return false; }
+    za_plugin_info pi;                                   // and the library must render this leaf as the same kind of plugin
+    if (za_gpu_plugin_info(slug.c_str(), &pi) == ZA_OK && ((pi.kind == 1) != (type == "faust"))) {
+        err = path + ": pluginType '" + type + "' does not match the library's " + (pi.kind == 1 ? "Faust" : "DSP-JSFX") + " leaf " + slug;
+        return false;
+    }
     return true;
+}
+
+bool parse_devices(const std::string& spec, std::vector<int>& out)     // "0,1,2" or "0-7" or a mix
+{
+    size_t i = 0;
+    while (i < spec.size()) {
+        char* e = nullptr;
+        const long a = std::strtol(spec.c_str() + i, &e, 10);
+        if (e == spec.c_str() + i || a < 0) return false;
+        long b = a;
+        i = (size_t)(e - spec.c_str());
+        if (i < spec.size() && spec[i] == '-') { b = std::strtol(spec.c_str() + i + 1, &e, 10); if (b < a) return false; i = (size_t)(e - spec.c_str()); }
+        for (long d = a; d <= b; ++d) out.push_back((int)d);
+        if (i < spec.size()) { if (spec[i] != ',') return false; ++i; }
+    }
+    return !out.empty();
 }
 
 int list_plugins()
@@ -156,7 +200,9 @@ int wav_info(const std::string& path)
 int main(int argc, char** argv)
 {
     std::string plugin, out_dir = "bounce_out", precision = "f64";
-    int block = 512, device = 0;
+    int block = 512, device = 0, oversampling = 1;
+    std::vector<int> devices{0};
+    std::string state_in, state_out;
     double chunk_seconds = 10.0, tail_seconds = 0.0;
     std::map<int, float> sets;
     std::vector<std::string> inputs;
@@ -170,12 +216,16 @@ int main(int argc, char** argv)
         if (a == "--list") return list_plugins();
         else if (a == "--wav-info") return wav_info(need("--wav-info"));
         else if (a == "--plugin") plugin = need("--plugin");
-        else if (a == "--plugin-json") { if (!read_slug(need("--plugin-json"), plugin, err)) return fail(err); }
+        else if (a == "--plugin-json") { if (!read_plugin_json(need("--plugin-json"), plugin, err)) return fail(err); }
+        else if (a == "--devices") { devices.clear(); if (!parse_devices(need("--devices"), devices)) return usage(argv[0]); }
+        else if (a == "--oversampling") oversampling = std::atoi(need("--oversampling"));
+        else if (a == "--state-in") state_in = need("--state-in");
+        else if (a == "--state-out") state_out = need("--state-out");
         else if (a == "--preset") { if (!read_preset(need("--preset"), sets, err)) return fail(err); }
         else if (a == "--save-preset") save_preset = need("--save-preset");
         else if (a == "--precision") precision = need("--precision");
         else if (a == "--block") block = std::atoi(need("--block"));
-        else if (a == "--device") device = std::atoi(need("--device"));
+        else if (a == "--device") { device = std::atoi(need("--device")); devices.assign(1, device); }
         else if (a == "--chunk-seconds") chunk_seconds = std::atof(need("--chunk-seconds"));
         else if (a == "--tail-seconds") tail_seconds = std::atof(need("--tail-seconds"));
         else if (a == "--out-dir") out_dir = need("--out-dir");
@@ -235,9 +285,33 @@ int main(int argc, char** argv)
     std::vector<float> params((size_t)ns * (size_t)std::max(pi.n_sliders, 1));
     for (int s = 0; s < ns; ++s) std::copy(row.begin(), row.end(), params.begin() + (size_t)s * (size_t)pi.n_sliders);
 
-    za_gpu_handle h = nullptr;
-    if (za_gpu_create(plugin.c_str(), ns, sr, block, precision == "f64" ? ZA_F64 : ZA_F32, device, &h) != ZA_OK) return fail(za_gpu_last_error());
-    if (za_gpu_prepare(h, params.data()) != ZA_OK) return fail(za_gpu_last_error());
+    // one batch over the chosen devices: streams shard as contiguous ranges, one host thread per device inside za_batch_process
+    if ((int)devices.size() > ns) devices.resize((size_t)ns);
+    za_batch_handle h = nullptr;
+    if (za_batch_create(plugin.c_str(), ns, sr, block, precision == "f64" ? ZA_F64 : ZA_F32, devices.data(), (int)devices.size(), oversampling, &h) != ZA_OK)
+        return fail(za_gpu_last_error());
+    if (za_batch_prepare(h, params.data()) != ZA_OK) return fail(za_gpu_last_error());
+    // checkpoint / resume: the per-stream DSP state of every shard (za_gpu_state_save blobs, one after the other)
+    auto for_each_shard_state = [&](bool load, const std::string& path) -> std::string {
+        FILE* f = std::fopen(path.c_str(), load ? "rb" : "wb");
+        if (!f) return "cannot open " + path;
+        for (int g = 0; g < (int)devices.size(); ++g) {
+            za_gpu_handle sh = nullptr;
+            size_t bytes = 0;
+            if (za_batch_shard(h, g, &sh) != ZA_OK || za_gpu_state_size(sh, &bytes) != ZA_OK) { std::fclose(f); return za_gpu_last_error(); }
+            std::vector<char> blob(bytes);
+            if (load) {
+                if (std::fread(blob.data(), 1, bytes, f) != bytes) { std::fclose(f); return path + ": truncated or made for another batch shape"; }
+                if (za_gpu_state_load(sh, blob.data(), bytes) != ZA_OK) { std::fclose(f); return za_gpu_last_error(); }
+            } else {
+                if (za_gpu_state_save(sh, blob.data(), bytes) != ZA_OK) { std::fclose(f); return za_gpu_last_error(); }
+                if (std::fwrite(blob.data(), 1, bytes, f) != bytes) { std::fclose(f); return "write error on " + path; }
+            }
+        }
+        std::fclose(f);
+        return "";
+    };
+    if (!state_in.empty()) { const std::string e = for_each_shard_state(true, state_in); if (!e.empty()) return fail(e); }
 
     // ---- outputs: header now (lengths are known), samples appended chunk by chunk -----------------------------------------
     ::mkdir(out_dir.c_str(), 0777);
@@ -264,7 +338,7 @@ int main(int argc, char** argv)
                 std::fill(dst + have, dst + n, 0.0f);
             }
         }
-        if (za_gpu_process(h, nullptr, 0, n_in ? in.data() : nullptr, out.data(), n, chunk, ZA_MEM_HOST) != ZA_OK) return fail(za_gpu_last_error());
+        if (za_batch_process(h, nullptr, 0, n_in ? in.data() : nullptr, out.data(), n, chunk) != ZA_OK) return fail(za_gpu_last_error());
         for (int s = 0; s < ns; ++s) {
             const int64_t keep = std::max<int64_t>(0, std::min(n, wav[(size_t)s].frames + tail - f0));
             if (keep == 0) continue;
@@ -277,9 +351,14 @@ int main(int argc, char** argv)
         }
     }
     const double wall = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    if (!state_out.empty()) { const std::string e = for_each_shard_state(false, state_out); if (!e.empty()) return fail(e); }
     int64_t launches = 0;
-    za_gpu_launch_count(h, &launches);
-    za_gpu_destroy(h);
+    for (int g = 0; g < (int)devices.size(); ++g) {
+        za_gpu_handle sh = nullptr;
+        int64_t l = 0;
+        if (za_batch_shard(h, g, &sh) == ZA_OK && za_gpu_launch_count(sh, &l) == ZA_OK) launches += l;
+    }
+    za_batch_destroy(h);
 
     // ---- report.json (the reference's exporter writes one beside its WAVs, JSFXCorrectnessCheck.h:1230-1255) ---------------
     const std::string rp = out_dir + "/report.json";
@@ -288,8 +367,8 @@ int main(int argc, char** argv)
     int64_t sum_frames = 0;
     for (int s = 0; s < ns; ++s) sum_frames += wav[(size_t)s].frames + tail;
     std::fprintf(r, "{\n  \"plugin\": \"%s\",\n  \"sampleRate\": %.3f,\n  \"frames\": %lld,\n  \"streams\": %d,\n  \"precision\": \"%s\",\n  \"block\": %d,\n"
-                    "  \"chunkFrames\": %lld,\n  \"tailFrames\": %lld,\n  \"kernelLaunches\": %lld,\n  \"wallSeconds\": %.6f,\n  \"xRealtime\": %.3f,\n  \"files\": [\n",
-                 json_escape(plugin).c_str(), sr, (long long)total, ns, precision.c_str(), block, (long long)chunk, (long long)tail, (long long)launches, wall,
+                    "  \"chunkFrames\": %lld,\n  \"tailFrames\": %lld,\n  \"devices\": %d,\n  \"oversampling\": %d,\n  \"kernelLaunches\": %lld,\n  \"wallSeconds\": %.6f,\n  \"xRealtime\": %.3f,\n  \"files\": [\n",
+                 json_escape(plugin).c_str(), sr, (long long)total, ns, precision.c_str(), block, (long long)chunk, (long long)tail, (int)devices.size(), oversampling, (long long)launches, wall,
                  wall > 0 ? (double)sum_frames / sr / wall : 0.0);
     for (int s = 0; s < ns; ++s)
         std::fprintf(r, "    {\"in\": \"%s\", \"out\": \"%s\", \"channelsIn\": %d, \"channelsOut\": %d, \"frames\": %lld, \"peakOut\": %.9g}%s\n",

@@ -44,6 +44,7 @@ SYMBOLS = [
     "za_gpu_state_size", "za_gpu_state_save", "za_gpu_state_load",
     "za_gpu_create_os", "za_chain_create", "za_chain_destroy", "za_chain_info", "za_chain_stage", "za_chain_set_chunk_blocks", "za_chain_prepare",
     "za_chain_process", "za_chain_sync",
+    "za_batch_create", "za_batch_destroy", "za_batch_shards", "za_batch_shard", "za_batch_prepare", "za_batch_process",
 ]
 
 _lib = None
@@ -81,6 +82,12 @@ def lib() -> C.CDLL:
         L.za_gpu_state_size.argtypes = [C.c_void_p, C.POINTER(C.c_size_t)]
         L.za_gpu_state_save.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
         L.za_gpu_state_load.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
+        L.za_batch_create.argtypes = [C.c_char_p, C.c_int, C.c_double, C.c_int, C.c_int, C.POINTER(C.c_int), C.c_int, C.c_int, C.POINTER(C.c_void_p)]
+        L.za_batch_destroy.argtypes = [C.c_void_p]
+        L.za_batch_shards.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+        L.za_batch_shard.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p)]
+        L.za_batch_prepare.argtypes = [C.c_void_p, C.c_void_p]
+        L.za_batch_process.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64]
         L.za_chain_create.argtypes = [C.POINTER(C.c_char_p), C.c_int, C.c_int, C.c_double, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
         L.za_chain_destroy.argtypes = [C.c_void_p]
         L.za_chain_info.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]
@@ -347,6 +354,48 @@ class Chain:
     def close(self):
         if self._h:
             lib().za_chain_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class MultiGpuBatch:
+    """One batch sharded over several GPUs of the box (za_batch_*): host buffers in, host buffers out, one host thread per device."""
+
+    def __init__(self, plugin_key: str, n_streams: int, devices, sample_rate: float = 48000.0, block_len: int = 512, precision: str = "f64",
+                 oversampling: int = 1):
+        self.info = plugin_info(plugin_key)
+        self.n_streams = n_streams
+        devs = (C.c_int * len(devices))(*devices)
+        self._h = C.c_void_p()
+        _check(lib().za_batch_create(plugin_key.encode(), n_streams, sample_rate, block_len, ZA_F64 if precision in ("f64", ZA_F64) else ZA_F32,
+                                     devs, len(devices), oversampling, C.byref(self._h)), "za_batch_create")
+
+    def prepare(self, param_block0=None):
+        p = None if param_block0 is None else np.ascontiguousarray(param_block0, np.float32)
+        _check(lib().za_batch_prepare(self._h, _ptr(p)), "za_batch_prepare")
+        return self
+
+    def process(self, x, params=None, out=None):
+        x = np.ascontiguousarray(x, np.float32)
+        nf = x.shape[-1]
+        if out is None:
+            out = np.empty((self.n_streams, self.info.n_out, nf), np.float32)
+        p, npb = None, 0
+        if params is not None:
+            p = np.ascontiguousarray(params, np.float32)
+            p = p[None] if p.ndim == 2 else p
+            npb = p.shape[0]
+        _check(lib().za_batch_process(self._h, _ptr(p), npb, _ptr(x), _ptr(out), nf, nf), "za_batch_process")
+        return out
+
+    def close(self):
+        if self._h:
+            lib().za_batch_destroy(self._h)
             self._h = C.c_void_p()
 
     def __del__(self):
