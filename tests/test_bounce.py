@@ -219,9 +219,9 @@ def test_bounce_resume_from_checkpoint_and_device_list(bounce, tmp_path):
     r = run(["--out-dir", str(tmp_path / "ob"), "--state-in", str(tmp_path / "ck.bin"), "--devices", "0,0"] + second)
     assert r.returncode == 0, r.stderr
     for s in range(3):
-        w = read_wav24(tmp_path / "ow" / f"w{s}.{s}.wav")
-        a = read_wav24(tmp_path / "oa" / f"a{s}.{s}.wav")
-        b = read_wav24(tmp_path / "ob" / f"b{s}.{s}.wav")
+        w, _ = read_wav24(tmp_path / "ow" / f"w{s}.{s}.wav")
+        a, _ = read_wav24(tmp_path / "oa" / f"a{s}.{s}.wav")
+        b, _ = read_wav24(tmp_path / "ob" / f"b{s}.{s}.wav")
         assert np.array_equal(np.concatenate([a, b], axis=1), w), s
     rep = json.loads((tmp_path / "oa" / "report.json").read_text())
     assert rep["devices"] == 2 and rep["oversampling"] == 1
