@@ -152,3 +152,51 @@ def test_fp32_split_kernel_at_bench_shape_sampled(gpu, ref):
     assert worst < -100.0, worst
     assert bp.last_kernel_ms()[1] >= 1
     bp.close()
+
+
+@pytest.mark.parametrize("filters,ns,nf,cut", [(False, 37, 48000 + 13, 20480), (True, 37, 30000 + 7, 512 * 9), (True, 5, 31, 0)])
+def test_fp32_role_pipeline_v3_cases(gpu, ref, filters, ns, nf, cut):
+    """The default fp32 kernel (k_easyexpander_v3.cu: block_len a multiple of 32): partial CTAs, a ragged last batch, the
+    detector filters on and off, the state handed over between two calls (a checkpoint in between); against the float64
+    reference (< -100 dBFS per stream) and against the round-1 split kernel (option scalar_f32 = 2)."""
+    p, x = make_case(ref, ns, nf, True, detector_filters=filters)
+    _, yd = ref.render(p, x, want_f64=True)
+    outs = {}
+    for variant in (0, 2):
+        bp = gpu.BatchProcessor("EasyExpander", ns, precision="f32").prepare(p[0])
+        bp.set_option("scalar_f32", variant)
+        if cut:
+            y0 = bp.process(np.ascontiguousarray(x[:, :, :cut]), params=np.ascontiguousarray(p[:cut // 512]))
+            blob = bp.save_state()
+            bp.close()
+            bp = gpu.BatchProcessor("EasyExpander", ns, precision="f32").prepare(p[0])
+            bp.set_option("scalar_f32", variant)
+            bp.load_state(blob)
+            y1 = bp.process(np.ascontiguousarray(x[:, :, cut:]), params=np.ascontiguousarray(p[cut // 512:]))
+            outs[variant] = np.concatenate([y0, y1], axis=2)
+        else:
+            outs[variant] = bp.process(x, params=p)
+        flag = bp.read_state("expanding")
+        assert set(np.unique(flag)) <= {0.0, 1.0}
+        for name in ("det_slow", "gain_db_s", "det_db_m", "gr_db_m", "hpf_lp", "lpf_y"):
+            assert np.isfinite(bp.read_state(name)).all(), name
+        bp.close()
+    worst = max(dbfs_rms(outs[0][s].astype(np.float64) - yd[s]) for s in range(ns))
+    between = max(dbfs_rms(outs[0][s].astype(np.float64) - outs[2][s]) for s in range(ns))
+    print("fp32 v3: worst stream vs float64 reference %.1f dBFS; vs the split kernel %.1f dBFS" % (worst, between))
+    assert worst < -100.0 and between < -100.0, (worst, between)
+
+
+def test_fp32_v3_chunked_call_is_bit_identical(gpu, ref):
+    """Scaled band states round-trip exactly through the float64 state rows: one call == the same frames in three calls."""
+    ns, nf = 12, 512 * 30
+    p, x = make_case(ref, ns, nf, True)
+    bp = gpu.BatchProcessor("EasyExpander", ns, precision="f32").prepare(p[0])
+    whole = bp.process(x, params=p)
+    bp.close()
+    bp = gpu.BatchProcessor("EasyExpander", ns, precision="f32").prepare(p[0])
+    parts = []
+    for b0, b1 in ((0, 7), (7, 8), (8, 30)):
+        parts.append(bp.process(np.ascontiguousarray(x[:, :, b0 * 512:b1 * 512]), params=np.ascontiguousarray(p[b0:b1])))
+    bp.close()
+    assert np.array_equal(np.concatenate(parts, axis=2), whole)

@@ -422,10 +422,10 @@ static bool launch_variant(const C8Launch& L)
     }
     auto kern = cascade8_kernel<R, W, TMA, TAP>;
     const size_t smem = sizeof(C8Smem<R, W>) + 1024;
-    static bool attr_done = false;    // per template instantiation
-    if (!attr_done) {
+    static DeviceOnce attr_once;    // per template instantiation
+    if (attr_once.pending()) {
         if (!cuda_ok(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "smem attr")) return false;
-        attr_done = true;
+        attr_once.mark();
     }
     kern<<<L.n_streams, 32 * W, smem, L.stream>>>(in_map, out_map, a);
     return cuda_ok(cudaGetLastError(), "cascade8_kernel launch");

@@ -535,12 +535,12 @@ static bool launch_x2(const C8Launch& L)
     if (!make_chunk_tensor_map(&out_map, L.out, a.n_chunks, L.n_streams, L.row_stride, 64)) return false;
     auto kern = cascade8_x2_kernel<W, NBUF>;
     const size_t smem = sizeof(X2Smem<W, NBUF>) + 1024;
-    static bool attr_done = false;    // per template instantiation
-    if (!attr_done) {
+    static DeviceOnce attr_once;    // per template instantiation
+    if (attr_once.pending()) {
         if (!cuda_ok(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "smem attr")) return false;
         // all of L1 as shared memory: the kernel's only L1 traffic is TMA, and 8 CTAs x 26 KB must fit
         if (!cuda_ok(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared), "carveout")) return false;
-        attr_done = true;
+        attr_once.mark();
     }
     kern<<<L.n_streams, 32 * W, smem, L.stream>>>(in_map, out_map, a);
     return cuda_ok(cudaGetLastError(), "cascade8_x2_kernel launch");

@@ -712,10 +712,10 @@ static bool launch_ee(const EEArgs& a, int n_sm, cudaStream_t stream)
 {
     auto kern = easyexpander_kernel<R, TAP>;
     const size_t smem = sizeof(EESmem<R>);
-    static bool attr_done = false;
-    if (!attr_done) {
+    static DeviceOnce attr_once;
+    if (attr_once.pending()) {
         if (!cuda_ok(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "EasyExpander smem attr")) return false;
-        attr_done = true;
+        attr_once.mark();
     }
     // streams per CTA: spread the streams over all SMs, whole band warps (4 streams), at most one lane each
     int spc = (a.n_streams + n_sm - 1) / n_sm;
@@ -730,10 +730,10 @@ static bool launch_ee(const EEArgs& a, int n_sm, cudaStream_t stream)
 static bool launch_ee_split(const EEArgs& a, int n_sm, cudaStream_t stream)
 {
     const size_t smem = sizeof(EESmemS);
-    static bool attr_done = false;
-    if (!attr_done) {
+    static DeviceOnce attr_once;
+    if (attr_once.pending()) {
         if (!cuda_ok(cudaFuncSetAttribute(easyexpander_split_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "EasyExpander smem attr")) return false;
-        attr_done = true;
+        attr_once.mark();
     }
     int spc = (a.n_streams + n_sm - 1) / n_sm;
     spc = (spc + 3) / 4 * 4;
@@ -748,7 +748,9 @@ bool easyexpander_launch(const EEArgs& a, int precision, int n_sm, cudaStream_t 
 {
     if (a.n_frames <= 0 || a.n_streams <= 0) return true;
     if (precision) return a.tap ? launch_ee<double, true>(a, n_sm, stream) : launch_ee<double, false>(a, n_sm, stream);
-    if (variant != 1 && a.block_len >= kF) return launch_ee_split(a, n_sm, stream);      // variant 1 = the single-role kernel
+    // fp32: variant 0 = the v3 role pipeline where it applies, 2 = the round-1 split kernel, 1 = the single-role kernel
+    if (variant == 0 && easyexpander_v3_eligible(a)) return easyexpander_v3_launch(a, n_sm, stream);
+    if (variant != 1 && a.block_len >= kF) return launch_ee_split(a, n_sm, stream);
     return launch_ee<float, false>(a, n_sm, stream);
 }
 

@@ -1,0 +1,465 @@
+// k_easyexpander_v3.cu -- EasyExpander fp32, third cut of the role pipeline (BASELINE config 3, the headline workload).
+//
+// Same algorithm and the same stage idea as easyexpander_split_kernel (k_easyexpander.cu; EasyExpander.jsfx:177-281), rebuilt
+// around what its ncu capture showed (profiles/r01_easyexpander_split_ncu.md, tools/ncu_roles.py): nobody waits at the batch
+// barrier for long, every role is busy -- the lane = stream gain warp is the critical path (879 instructions per 32-frame
+// batch at ~0.4 IPC), and the lane = frame helper warps spend half their instructions on addresses, denormal guards and
+// per-frame block bookkeeping.  Changes:
+//   * host blocks are a whole number of 32-frame batches here (block_len % 32 == 0; other shapes keep the older kernels),
+//     so every coefficient is a per-batch constant and no stage tracks blocks per frame;
+//   * the sequential gain computer is cut into two warps one batch apart: G1 = slow detector follower + adaptive closing
+//     coefficient + detector meter, G2 = hysteresis flag + reduction meter + switching smoother;
+//   * rows that a lane = stream warp walks are [stream][36] (16-byte aligned, bank-conflict free both ways), read and written
+//     with 128-bit shared-memory accesses: 4x fewer LDS/STS in the filter / G1 / G2 warps and for the band warps' input;
+//   * band recurrence in scaled coordinates: states divided by the input gain 2 g/den, the power follower carried as
+//     w_j * env_j with w_j c (g/den)^2 folded into one constant -- 7 packed instructions per frame and band pair instead of
+//     10; the HBM state keeps the script's own variables (exact round trip through double);
+//   * helpers: MUFU forms without the denormal guards (every argument is >= 1e-12), 10 log10(sum) instead of
+//     sqrt -> log, pointers bumped instead of rebuilt, 7 helper warps own the 28 streams of a cfg3 CTA (no idle quarter);
+//   * the band-power tile is [stream][frame][8] with a 16-byte XOR swizzle instead of a 12-float pitch (32 KB less shared
+//     memory, which pays for the deeper db / tg rings G2 needs).
+// Pipeline per 32-frame batch b (iteration i):  S0 helpers load b = i | filter b = i-1 | bands i-2 | P2 helpers i-3 |
+// G1 i-4 | G2 i-5 | S4 helpers i-6 (exp, output multiplies, stores).  One named barrier per iteration.
+// fp32 criterion: residual below -100 dBFS against the float64 reference (tests/test_easyexpander_gpu.py).
+#include "za_device.cuh"
+#include "za_internal.h"
+
+namespace za {
+
+namespace {
+
+constexpr int kF = 32;             // frames per batch
+constexpr int kMaxS = 32;          // streams per CTA
+constexpr int kWarps = 16;
+constexpr int kThreads = kWarps * 32;
+constexpr int kRowP = 36;          // floats per [stream] row of a 32-frame tile
+constexpr int kInP = 2 * kRowP + 4;   // [stream][ch][36] + 4: 76 = 12 (mod 32) -> eight 128-bit lane = stream reads hit 32 banks
+constexpr int kBpP = kF * 8 + 8;   // [stream][frame][8 bands] + 8
+constexpr int kInSlots = 8;        // a batch's input lives from S0 (i) to S4 (i + 6)
+constexpr int kDbSlots = 4;        // det_db / target rows live from P2 (i) to G2 (i + 2)
+
+enum { R_FILTER = 4, R_G1 = 5, R_G2 = 6, R_NONE = 7, R_HELP = 8 };
+//                                  scheduler: 0            1            2            3
+__constant__ int kRoleV3[kWarps] = {0,           1,           2,           3,
+                                    R_G2,        R_G1,        R_FILTER,    R_HELP + 3,
+                                    R_HELP + 0,  R_HELP + 1,  R_HELP + 2,  R_HELP + 6,
+                                    R_NONE,      R_HELP + 4,  R_HELP + 5,  R_HELP + 7};
+constexpr int kLiveWarps = 15;
+
+struct SmemV3 {
+    alignas(16) float in[kInSlots][kMaxS * kInP];
+    alignas(16) float xd[2][kMaxS * kRowP];
+    alignas(16) float bp[2][kMaxS * kBpP];
+    alignas(16) float lin[2][kMaxS * kRowP];
+    alignas(16) float db[kDbSlots][kMaxS * kRowP];
+    alignas(16) float tg[kDbSlots][kMaxS * kRowP];
+    alignas(16) float cc[2][kMaxS * kRowP];
+    alignas(16) float gain[2][kMaxS * kRowP];
+};
+static_assert(sizeof(SmemV3) <= 227 * 1024, "EasyExpander v3 shared memory");
+
+__device__ __forceinline__ void v3_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kLiveWarps * 32) : "memory"); }
+
+typedef unsigned long long p2;     // two floats in one 64-bit register
+__device__ __forceinline__ p2 pk(float lo, float hi) { p2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ void unpk(p2 a, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(a)); }
+__device__ __forceinline__ p2 fma2(p2 a, p2 b, p2 c) { p2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
+__device__ __forceinline__ p2 mul2(p2 a, p2 b) { p2 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+
+__device__ __forceinline__ float rsqrt_fast(float a) { float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a)); return r; }
+__device__ __forceinline__ float lg2_fast(float a) { float r; asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a)); return r; }
+__device__ __forceinline__ float ex2_fast(float a) { float r; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a)); return r; }
+
+// first frame of the host block a batch starts in -> coefficient row (clamped to the rows there are)
+struct BlockWalk {
+    int64_t next;      // first frame of the next host block
+    int row;           // row of the current one (-1 before the first batch)
+    int block_len, n_rows;
+    __device__ __forceinline__ bool enter(int64_t F0)       // true when batch F0 starts a new host block
+    {
+        if (F0 < next) return false;
+        while (F0 >= next) { ++row; next += block_len; }
+        return true;
+    }
+    __device__ __forceinline__ int clamped() const { return row < n_rows ? row : n_rows - 1; }
+};
+
+struct BandK3 { p2 a22, a12, c1, g, omc, kq; };
+struct BandS3 { p2 i1, i2, e; };
+
+// eight frames of one band pair: u = 2 a2 i2 + x,  s = 2 a1 i1 + u (= 2 v1 / k),  i1' = (2 a1 - 1) i1 + u,  i2' = i2 + g s,
+// E' = (1 - c) E + (w c k^2 / 4) s^2, with k = 2 g / den the input gain the states are divided by (svf_bp, :74-93; :200-219)
+template <bool FULL>
+__device__ __forceinline__ void band_group3(const float* xd, float* pa, float* pb, int f0, int nv, const BandK3& c, BandS3& s)
+{
+    float xv[8];
+    if (FULL) {
+        const float4 x0 = *reinterpret_cast<const float4*>(xd + f0), x1 = *reinterpret_cast<const float4*>(xd + f0 + 4);
+        xv[0] = x0.x; xv[1] = x0.y; xv[2] = x0.z; xv[3] = x0.w; xv[4] = x1.x; xv[5] = x1.y; xv[6] = x1.z; xv[7] = x1.w;
+    } else {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) xv[k] = xd[f0 + k];
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        if (FULL || f0 + k < nv) {
+            const p2 u = fma2(c.a22, s.i2, pk(xv[k], xv[k]));
+            const p2 sv = fma2(c.a12, s.i1, u);
+            s.i1 = fma2(c.c1, s.i1, u);
+            s.i2 = fma2(c.g, sv, s.i2);
+            s.e = fma2(c.kq, mul2(sv, sv), mul2(c.omc, s.e));
+            *reinterpret_cast<p2*>((k < 4 ? pa : pb) + (f0 + k) * 8) = s.e;
+        }
+    }
+}
+
+// detector input + the detector-only one-poles (:180-194); MODE 0 = no stream of the warp has either filter on
+template <int MODE>
+__device__ __forceinline__ float filt_frame(float l, float r, float& hpf_lp, float& lpf_y, float hpf_c, float lpf_c, bool hpf_on, bool lpf_on)
+{
+    float x = 0.5f * (l + r);
+    if (MODE) {
+        const float lp = fmaf(hpf_c, x - hpf_lp, hpf_lp);
+        hpf_lp = hpf_on ? lp : hpf_lp;
+        x = hpf_on ? x - hpf_lp : x;
+        const float ly = fmaf(lpf_c, x - lpf_y, lpf_y);
+        lpf_y = lpf_on ? ly : lpf_y;
+        x = lpf_on ? lpf_y : x;
+    }
+    return x;
+}
+
+template <int MODE>
+__device__ __forceinline__ void filt_batch(const float* ib, float* xo, int nv, float& hpf_lp, float& lpf_y, float hpf_c, float lpf_c,
+                                           bool hpf_on, bool lpf_on)
+{
+    if (nv == kF) {
+#pragma unroll 1
+        for (int f0 = 0; f0 < kF; f0 += 8) {
+            const float4 l0 = *reinterpret_cast<const float4*>(ib + f0), l1 = *reinterpret_cast<const float4*>(ib + f0 + 4);
+            const float4 r0 = *reinterpret_cast<const float4*>(ib + kRowP + f0), r1 = *reinterpret_cast<const float4*>(ib + kRowP + f0 + 4);
+            float4 o0, o1;
+            o0.x = filt_frame<MODE>(l0.x, r0.x, hpf_lp, lpf_y, hpf_c, lpf_c, hpf_on, lpf_on);
+            o0.y = filt_frame<MODE>(l0.y, r0.y, hpf_lp, lpf_y, hpf_c, lpf_c, hpf_on, lpf_on);
+            o0.z = filt_frame<MODE>(l0.z, r0.z, hpf_lp, lpf_y, hpf_c, lpf_c, hpf_on, lpf_on);
+            o0.w = filt_frame<MODE>(l0.w, r0.w, hpf_lp, lpf_y, hpf_c, lpf_c, hpf_on, lpf_on);
+            o1.x = filt_frame<MODE>(l1.x, r1.x, hpf_lp, lpf_y, hpf_c, lpf_c, hpf_on, lpf_on);
+            o1.y = filt_frame<MODE>(l1.y, r1.y, hpf_lp, lpf_y, hpf_c, lpf_c, hpf_on, lpf_on);
+            o1.z = filt_frame<MODE>(l1.z, r1.z, hpf_lp, lpf_y, hpf_c, lpf_c, hpf_on, lpf_on);
+            o1.w = filt_frame<MODE>(l1.w, r1.w, hpf_lp, lpf_y, hpf_c, lpf_c, hpf_on, lpf_on);
+            *reinterpret_cast<float4*>(xo + f0) = o0; *reinterpret_cast<float4*>(xo + f0 + 4) = o1;
+        }
+    } else {
+        for (int f = 0; f < nv; ++f) xo[f] = filt_frame<MODE>(ib[f], ib[kRowP + f], hpf_lp, lpf_y, hpf_c, lpf_c, hpf_on, lpf_on);
+    }
+}
+
+struct G1S { float det_slow, det_db_m; };
+// :221-227 and :262: detector meter, slow follower, adaptive closing coefficient
+__device__ __forceinline__ float g1_frame(float lin, float db, G1S& s, float slow_c, float close_fast_c, float close_slow_c)
+{
+    s.det_db_m = fmaf(0.02f, db - s.det_db_m, s.det_db_m);
+    s.det_slow = fmaf(slow_c, lin - s.det_slow, s.det_slow);
+    return lin < s.det_slow * 0.92f ? close_fast_c : close_slow_c;
+}
+
+struct G2S { float gain_db_s, gr_db_m, thresh_db, thresh_hi; bool expanding; };
+// :229-236 hysteresis flag, :258-259 reduction meter, :264-268 switching smoother
+__device__ __forceinline__ float g2_frame(float db, float tgv, float close_c, G2S& s, float open_c)
+{
+    const bool keep = s.expanding && !(db > s.thresh_hi);
+    s.expanding = (db < s.thresh_db) || keep;
+    const float target_gr = s.expanding ? tgv : 0.0f;
+    s.gr_db_m = fmaf(0.05f, target_gr - s.gr_db_m, s.gr_db_m);
+    const float target_gain_db = -target_gr;
+    const float c = target_gain_db > s.gain_db_s ? open_c : close_c;
+    s.gain_db_s = fmaf(c, target_gain_db - s.gain_db_s, s.gain_db_s);
+    return s.gain_db_s;
+}
+
+}  // namespace
+
+__global__ void __launch_bounds__(kThreads, 1)
+easyexpander_v3_kernel(const EEArgs a, const int spc)
+{
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    SmemV3& sm = *reinterpret_cast<SmemV3*>(smem_raw);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int role = kRoleV3[warp];
+    if (role == R_NONE) return;
+    const int s_base = blockIdx.x * spc;
+    const int ns_cta = min(spc, a.n_streams - s_base);
+    const size_t ns = (size_t)a.n_streams;
+    const int64_t n = a.n_frames;
+    const int n_batches = (int)((n + kF - 1) / kF);
+    const int n_iter = n_batches + 7;
+
+    if (role < 4) {
+        // ============================ band warps: SVF + power follower, two bands per lane, eight streams per warp ========
+        const int sl = lane >> 2, jj = lane & 3;
+        const int ls = 8 * role + sl;
+        const bool act = 8 * role < ns_cta, live = ls < ns_cta;
+        const int sg = s_base + (live ? ls : (ns_cta - 1));
+        const int jA = 2 * jj, jB = jA + 1;
+        const double gA = a.k.g[jA], gB = a.k.g[jB], dA = a.k.den[jA], dB = a.k.den[jB], bc = a.k.band_c;
+        const float kA = (float)(2.0 * gA / dA), kB = (float)(2.0 * gB / dB);      // input gain of the unscaled recurrence
+        const float wA = (float)a.k.w[jA], wB = (float)a.k.w[jB];
+        const BandK3 bk{pk((float)(-2.0 * gA / dA), (float)(-2.0 * gB / dB)), pk((float)(2.0 / dA), (float)(2.0 / dB)),
+                        pk((float)(2.0 / dA - 1.0), (float)(2.0 / dB - 1.0)), pk((float)gA, (float)gB),
+                        pk((float)(1.0 - bc), (float)(1.0 - bc)),
+                        pk((float)((double)wA * bc * 0.25 * (double)kA * (double)kA), (float)((double)wB * bc * 0.25 * (double)kB * (double)kB))};
+        double* st = a.state + sg;
+        BandS3 bs{pk((float)(st[(0 + jA) * ns] / (double)kA), (float)(st[(0 + jB) * ns] / (double)kB)),
+                  pk((float)(st[(8 + jA) * ns] / (double)kA), (float)(st[(8 + jB) * ns] / (double)kB)),
+                  pk((float)(st[(16 + jA) * ns] * (double)wA), (float)(st[(16 + jB) * ns] * (double)wB))};
+        for (int i = 0; i < n_iter; ++i) {
+            if (act && i >= 2 && i - 2 < n_batches) {
+                const int b = i - 2;
+                const float* xd = sm.xd[b & 1] + ls * kRowP;
+                const int nv = (int)min((int64_t)kF, n - (int64_t)b * kF);
+                float* pa = sm.bp[b & 1] + ls * kBpP + jA;
+                float* pb = sm.bp[b & 1] + ls * kBpP + (jA ^ 4);
+                if (nv == kF) {
+#pragma unroll 1
+                    for (int f0 = 0; f0 < kF; f0 += 8) band_group3<true>(xd, pa, pb, f0, nv, bk, bs);
+                } else {
+#pragma unroll 1
+                    for (int f0 = 0; f0 < kF; f0 += 8) band_group3<false>(xd, pa, pb, f0, nv, bk, bs);
+                }
+            }
+            v3_sync();
+        }
+        if (live) {
+            float lo_, hi_;
+            unpk(bs.i1, lo_, hi_); st[(0 + jA) * ns] = (double)lo_ * (double)kA; st[(0 + jB) * ns] = (double)hi_ * (double)kB;
+            unpk(bs.i2, lo_, hi_); st[(8 + jA) * ns] = (double)lo_ * (double)kA; st[(8 + jB) * ns] = (double)hi_ * (double)kB;
+            unpk(bs.e, lo_, hi_); st[(16 + jA) * ns] = (double)lo_ / (double)wA; st[(16 + jB) * ns] = (double)hi_ / (double)wB;
+        }
+    } else if (role == R_FILTER) {
+        // ============================ filter warp: lane = stream (batch i - 1) ========================================
+        const bool live = lane < ns_cta;
+        const int sg = s_base + (live ? lane : 0);
+        double* st = a.state + sg;
+        float hpf_lp = (float)st[24 * ns], lpf_y = (float)st[25 * ns], hpf_c = 0.f, lpf_c = 0.f;
+        bool hpf_on = false, lpf_on = false, any_on = false;
+        BlockWalk bw{0, -1, a.block_len, a.n_coef_blocks};
+        for (int i = 0; i < n_iter; ++i) {
+            if (i >= 1 && i - 1 < n_batches) {
+                const int b = i - 1;
+                if (bw.enter((int64_t)b * kF)) {
+                    const EECoef& c = a.coef[(size_t)bw.clamped() * ns + sg];
+                    hpf_c = (float)c.hpf_c; lpf_c = (float)c.lpf_c; hpf_on = c.hpf_on != 0; lpf_on = c.lpf_on != 0;
+                    any_on = __any_sync(0xffffffffu, hpf_on || lpf_on);
+                }
+                const float* ib = sm.in[b & (kInSlots - 1)] + lane * kInP;
+                float* xo = sm.xd[b & 1] + lane * kRowP;
+                const int nv = (int)min((int64_t)kF, n - (int64_t)b * kF);
+                if (any_on) filt_batch<1>(ib, xo, nv, hpf_lp, lpf_y, hpf_c, lpf_c, hpf_on, lpf_on);
+                else filt_batch<0>(ib, xo, nv, hpf_lp, lpf_y, hpf_c, lpf_c, hpf_on, lpf_on);
+            }
+            v3_sync();
+        }
+        if (live) { st[24 * ns] = (double)hpf_lp; st[25 * ns] = (double)lpf_y; }
+    } else if (role == R_G1) {
+        // ============================ G1: lane = stream (batch i - 4): followers + closing coefficient ===================
+        const bool live = lane < ns_cta;
+        const int sg = s_base + (live ? lane : 0);
+        double* st = a.state + sg;
+        G1S gs{(float)st[26 * ns], (float)st[29 * ns]};
+        const float slow_c = (float)a.k.slow_c, cfast = (float)a.k.close_fast_c, cslow = (float)a.k.close_slow_c;
+        for (int i = 0; i < n_iter; ++i) {
+            if (i >= 4 && i - 4 < n_batches) {
+                const int b = i - 4;
+                const float* lin = sm.lin[b & 1] + lane * kRowP;
+                const float* db = sm.db[b & (kDbSlots - 1)] + lane * kRowP;
+                float* cc = sm.cc[b & 1] + lane * kRowP;
+                const int nv = (int)min((int64_t)kF, n - (int64_t)b * kF);
+                if (nv == kF) {
+#pragma unroll 1
+                    for (int f0 = 0; f0 < kF; f0 += 8) {
+                        const float4 l0 = *reinterpret_cast<const float4*>(lin + f0), l1 = *reinterpret_cast<const float4*>(lin + f0 + 4);
+                        const float4 d0 = *reinterpret_cast<const float4*>(db + f0), d1 = *reinterpret_cast<const float4*>(db + f0 + 4);
+                        float4 o0, o1;
+                        o0.x = g1_frame(l0.x, d0.x, gs, slow_c, cfast, cslow); o0.y = g1_frame(l0.y, d0.y, gs, slow_c, cfast, cslow);
+                        o0.z = g1_frame(l0.z, d0.z, gs, slow_c, cfast, cslow); o0.w = g1_frame(l0.w, d0.w, gs, slow_c, cfast, cslow);
+                        o1.x = g1_frame(l1.x, d1.x, gs, slow_c, cfast, cslow); o1.y = g1_frame(l1.y, d1.y, gs, slow_c, cfast, cslow);
+                        o1.z = g1_frame(l1.z, d1.z, gs, slow_c, cfast, cslow); o1.w = g1_frame(l1.w, d1.w, gs, slow_c, cfast, cslow);
+                        *reinterpret_cast<float4*>(cc + f0) = o0; *reinterpret_cast<float4*>(cc + f0 + 4) = o1;
+                    }
+                } else {
+                    for (int f = 0; f < nv; ++f) cc[f] = g1_frame(lin[f], db[f], gs, slow_c, cfast, cslow);
+                }
+            }
+            v3_sync();
+        }
+        if (live) { st[26 * ns] = (double)gs.det_slow; st[29 * ns] = (double)gs.det_db_m; }
+    } else if (role == R_G2) {
+        // ============================ G2: lane = stream (batch i - 5): hysteresis flag + switching smoother ==============
+        const bool live = lane < ns_cta;
+        const int sg = s_base + (live ? lane : 0);
+        double* st = a.state + sg;
+        G2S gs{(float)st[28 * ns], (float)st[30 * ns], 0.f, 0.f, st[27 * ns] != 0.0};
+        const float open_c = (float)a.k.open_c;
+        BlockWalk bw{0, -1, a.block_len, a.n_coef_blocks};
+        for (int i = 0; i < n_iter; ++i) {
+            if (i >= 5 && i - 5 < n_batches) {
+                const int b = i - 5;
+                if (bw.enter((int64_t)b * kF)) {
+                    gs.thresh_db = (float)a.coef[(size_t)bw.clamped() * ns + sg].thresh_db;
+                    gs.thresh_hi = gs.thresh_db + 2.0f;                                   // hys_db (:33)
+                }
+                const float* db = sm.db[b & (kDbSlots - 1)] + lane * kRowP;
+                const float* tg = sm.tg[b & (kDbSlots - 1)] + lane * kRowP;
+                const float* cc = sm.cc[b & 1] + lane * kRowP;
+                float* go = sm.gain[b & 1] + lane * kRowP;
+                const int nv = (int)min((int64_t)kF, n - (int64_t)b * kF);
+                if (nv == kF) {
+#pragma unroll 1
+                    for (int f0 = 0; f0 < kF; f0 += 8) {
+                        const float4 d0 = *reinterpret_cast<const float4*>(db + f0), d1 = *reinterpret_cast<const float4*>(db + f0 + 4);
+                        const float4 t0 = *reinterpret_cast<const float4*>(tg + f0), t1 = *reinterpret_cast<const float4*>(tg + f0 + 4);
+                        const float4 c0 = *reinterpret_cast<const float4*>(cc + f0), c1 = *reinterpret_cast<const float4*>(cc + f0 + 4);
+                        float4 o0, o1;
+                        o0.x = g2_frame(d0.x, t0.x, c0.x, gs, open_c); o0.y = g2_frame(d0.y, t0.y, c0.y, gs, open_c);
+                        o0.z = g2_frame(d0.z, t0.z, c0.z, gs, open_c); o0.w = g2_frame(d0.w, t0.w, c0.w, gs, open_c);
+                        o1.x = g2_frame(d1.x, t1.x, c1.x, gs, open_c); o1.y = g2_frame(d1.y, t1.y, c1.y, gs, open_c);
+                        o1.z = g2_frame(d1.z, t1.z, c1.z, gs, open_c); o1.w = g2_frame(d1.w, t1.w, c1.w, gs, open_c);
+                        *reinterpret_cast<float4*>(go + f0) = o0; *reinterpret_cast<float4*>(go + f0 + 4) = o1;
+                    }
+                } else {
+                    for (int f = 0; f < nv; ++f) go[f] = g2_frame(db[f], tg[f], cc[f], gs, open_c);
+                }
+            }
+            v3_sync();
+        }
+        if (live) {
+            st[27 * ns] = gs.expanding ? 1.0 : 0.0; st[28 * ns] = (double)gs.gain_db_s; st[30 * ns] = (double)gs.gr_db_m;
+        }
+    } else {
+        // ============================ helper warps: lane = frame; streams 4h .. 4h + 3 of the CTA ========================
+        const int h = role - R_HELP;
+        const bool act = 4 * h < ns_cta;
+        const float* pin[4]; float* pout[4];
+        bool has[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int lq = 4 * h + q;
+            has[q] = lq < ns_cta;
+            const size_t s = (size_t)(s_base + (has[q] ? lq : 0));
+            pin[q] = a.in + s * 2 * a.row_stride + lane;
+            pout[q] = a.out + s * 2 * a.row_stride + lane - 6 * kF;          // S4 runs six batches behind S0
+        }
+        const int64_t rs = a.row_stride;
+        const int swz = 4 * ((lane >> 2) & 1);
+        const int bpA = lane * 8 + swz, bpB = lane * 8 + (swz ^ 4);          // bands 0-3 / 4-7 of this lane's frame
+        float thr[4] = {0.f, 0.f, 0.f, 0.f}, dep[4] = {0.f, 0.f, 0.f, 0.f}, rm1[4] = {0.f, 0.f, 0.f, 0.f};
+        BlockWalk bw{0, -1, a.block_len, a.n_coef_blocks};
+        const float eps = 1e-12f;
+        const float db_per_lg2_pow = 3.0102999566398120f;                    // 10 log10(2): det_db = 10 log10(sum) = 20 log10(sqrt(sum))
+        const float lg2_per_db = 0.16609640474436813f;                       // ln(10)/20 / ln(2)
+        float hold[4][2];
+        for (int i = 0; i < n_iter; ++i) {
+            if (act) {
+                // ---- S0 (issue): batch i ---------------------------------------------------------------------------
+                {
+                    const bool ok = i < n_batches && (int64_t)i * kF + lane < n;
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        hold[q][0] = ok ? pin[q][0] : 0.f;
+                        hold[q][1] = ok ? pin[q][rs] : 0.f;
+                    }
+                }
+                // ---- P2: batch i - 3: band sum in the script's order, level, memoryless half of the gain computer ------
+                if (i >= 3 && i - 3 < n_batches) {
+                    const int b = i - 3;
+                    if (bw.enter((int64_t)b * kF)) {
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            const EECoef& c = a.coef[(size_t)bw.clamped() * ns + s_base + (has[q] ? 4 * h + q : 0)];
+                            thr[q] = (float)c.thresh_db; dep[q] = (float)c.depth_db; rm1[q] = (float)(c.ratio_base - 1.0);
+                        }
+                    }
+                    const float* bp = sm.bp[b & 1] + (4 * h) * kBpP;
+                    float* lin = sm.lin[b & 1] + (4 * h) * kRowP + lane;
+                    float* db = sm.db[b & (kDbSlots - 1)] + (4 * h) * kRowP + lane;
+                    float* tg = sm.tg[b & (kDbSlots - 1)] + (4 * h) * kRowP + lane;
+                    float sum[4];
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const float4 b03 = *reinterpret_cast<const float4*>(bp + q * kBpP + bpA);
+                        const float4 b47 = *reinterpret_cast<const float4*>(bp + q * kBpP + bpB);
+                        sum[q] = fmaxf(((((((b03.x + b03.y) + b03.z) + b03.w) + b47.x) + b47.y) + b47.z) + b47.w, eps);
+                    }
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const float det_lin = sum[q] * rsqrt_fast(sum[q]);
+                        const float det_db = db_per_lg2_pow * lg2_fast(sum[q]);
+                        float d = thr[q] - det_db;
+                        d = d < 0.f ? 0.f : d;
+                        const float xk = d * (1.0f / 6.0f);                              // knee_db = 6 (:34)
+                        const float smo = (xk * xk) * fmaf(-2.0f, xk, 3.0f);
+                        const float re1 = d < 6.0f ? rm1[q] * smo : rm1[q];               // ratio_eff - 1
+                        float target_gr = d * re1;
+                        target_gr = target_gr > dep[q] ? dep[q] : target_gr;
+                        lin[q * kRowP] = det_lin; db[q * kRowP] = det_db; tg[q * kRowP] = target_gr;
+                    }
+                }
+                // ---- S4: batch i - 6: exp and the output multiplies ------------------------------------------------------
+                if (i >= 6) {
+                    const int b = i - 6;
+                    const bool okf = (int64_t)b * kF + lane < n;
+                    const float* ib = sm.in[b & (kInSlots - 1)] + (4 * h) * kInP + lane;
+                    const float* gp = sm.gain[b & 1] + (4 * h) * kRowP + lane;
+                    float o0[4], o1[4];
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const float gain_lin = ex2_fast(gp[q * kRowP] * lg2_per_db);
+                        o0[q] = ib[q * kInP] * gain_lin;
+                        o1[q] = ib[q * kInP + kRowP] * gain_lin;
+                    }
+#pragma unroll
+                    for (int q = 0; q < 4; ++q)
+                        if (okf && has[q]) { pout[q][0] = o0[q]; pout[q][rs] = o1[q]; }
+                }
+                // ---- S0 (commit): batch i -> shared memory -----------------------------------------------------------------
+                {
+                    float* ib = sm.in[i & (kInSlots - 1)] + (4 * h) * kInP + lane;
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) { ib[q * kInP] = hold[q][0]; ib[q * kInP + kRowP] = hold[q][1]; }
+                }
+#pragma unroll
+                for (int q = 0; q < 4; ++q) { pin[q] += kF; pout[q] += kF; }
+            }
+            v3_sync();
+        }
+    }
+}
+
+bool easyexpander_v3_eligible(const EEArgs& a)
+{
+    if (a.block_len < kF || a.block_len % kF != 0) return false;
+    for (int j = 0; j < 8; ++j) {
+        const float w = (float)a.k.w[j], k = (float)(2.0 * a.k.g[j] / a.k.den[j]);
+        if (!(w > 1e-30f) || !(k > 1e-30f)) return false;                  // the scaled band states divide by these
+    }
+    return true;
+}
+
+bool easyexpander_v3_launch(const EEArgs& a, int n_sm, cudaStream_t stream)
+{
+    const size_t smem = sizeof(SmemV3);
+    static DeviceOnce attr_once;
+    if (attr_once.pending()) {
+        if (!cuda_ok(cudaFuncSetAttribute(easyexpander_v3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "EasyExpander v3 smem attr")) return false;
+        attr_once.mark();
+    }
+    int spc = (a.n_streams + n_sm - 1) / n_sm;
+    spc = (spc + 3) / 4 * 4;
+    if (spc > kMaxS) spc = kMaxS;
+    if (spc < 4) spc = 4;
+    const int blocks = (a.n_streams + spc - 1) / spc;
+    easyexpander_v3_kernel<<<blocks, kThreads, smem, stream>>>(a, spc);
+    return cuda_ok(cudaGetLastError(), "easyexpander_v3_kernel launch");
+}
+
+}  // namespace za

@@ -202,10 +202,10 @@ static bool launch_stft(const StftArgs& a, cudaStream_t stream)
 {
     auto kern = stft_mask_kernel<R, NS, TAP>;
     const size_t smem = sizeof(Tables<R>) + NS * sizeof(StreamSmem<R>);
-    static bool attr_done = false;
-    if (!attr_done) {
+    static DeviceOnce attr_once;
+    if (attr_once.pending()) {
         if (!cuda_ok(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "stft smem attr")) return false;
-        attr_done = true;
+        attr_once.mark();
     }
     kern<<<(a.n_streams + NS - 1) / NS, NS * kT, smem, stream>>>(a);
     return cuda_ok(cudaGetLastError(), "stft_mask_kernel launch");

@@ -3,12 +3,21 @@
 #include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <atomic>
 #include <string>
 
 namespace za {
 
 void set_error(const std::string& msg);          // thread-local text behind za_gpu_last_error()
 bool cuda_ok(cudaError_t e, const char* what);   // false + set_error on failure
+// cudaFuncSetAttribute is a per-device setting: one of these per kernel remembers which devices already have it
+// (a process may drive several GPUs -- za_batch_* runs one host thread per device).
+struct DeviceOnce {
+    std::atomic<unsigned long long> mask{0};
+    static unsigned long long bit() { int d = 0; cudaGetDevice(&d); return 1ull << (d & 63); }
+    bool pending() const { return !(mask.load(std::memory_order_acquire) & bit()); }
+    void mark() { mask.fetch_or(bit(), std::memory_order_release); }
+};
 
 // Encodes a 3-D SWIZZLE_128B tensor map over planar float rows:
 //   dim0 = 32 frames (one chunk), dim1 = n_chunks, dim2 = n_rows; box = {32, box_rows, 1}.
@@ -68,6 +77,8 @@ struct EEArgs {
     EEConsts k;
 };
 bool easyexpander_launch(const EEArgs& a, int precision, int n_sm, cudaStream_t stream, int variant = 0);
+bool easyexpander_v3_eligible(const EEArgs& a);          // k_easyexpander_v3.cu: fp32, block_len a multiple of 32
+bool easyexpander_v3_launch(const EEArgs& a, int n_sm, cudaStream_t stream);
 
 // ---- stft_mask2048 (STFT class) ---------------------------------------------------------------------
 constexpr int kStftN = 2048, kStftHop = 512, kStftBins = 1025;
