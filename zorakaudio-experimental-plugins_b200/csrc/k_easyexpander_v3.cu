@@ -30,24 +30,32 @@ namespace {
 
 constexpr int kF = 32;             // frames per batch
 constexpr int kMaxS = 32;          // streams per CTA
-constexpr int kWarps = 16;
+constexpr int kWarps = 24;
 constexpr int kThreads = kWarps * 32;
 constexpr int kRowP = 36;          // floats per [stream] row of a 32-frame tile
-constexpr int kInP = 2 * kRowP + 4;   // [stream][ch][36] + 4: 76 = 12 (mod 32) -> eight 128-bit lane = stream reads hit 32 banks
-constexpr int kBpP = kF * 8 + 8;   // [stream][frame][8 bands] + 8
-constexpr int kInSlots = 8;        // a batch's input lives from S0 (i) to S4 (i + 6)
-constexpr int kDbSlots = 4;        // det_db / target rows live from P2 (i) to G2 (i + 2)
+constexpr int kIoP = 64;           // I/O ring: [stream][ch][32 frames], 16-byte chunk c of a row stored at c ^ (stream & 7)
+constexpr int kBpP = kF * 4 + 4;   // [stream][frame][4 band pairs] + 4: pair sums w_j env_j + w_j+1 env_j+1 of lane jj
+constexpr int kSB = 4;             // batches per super-batch: global memory is read and written in 512-byte runs per row
+constexpr int kIoSlots = 16;       // I/O ring: a batch's slot is filled by cp.async six iterations early, read by the filter,
+                                   // overwritten in place by S4 (output) and released by the super-batch's 128-bit stores
+constexpr int kLead = 6;           // iterations between the cp.async issue of a super-batch and its first batch
+constexpr int kDbSlots = 3;        // det_db / target rows live from P2 (i) to G2 (i + 2)
 
+constexpr int kQ = 2;              // streams per helper warp
 enum { R_FILTER = 4, R_G1 = 5, R_G2 = 6, R_NONE = 7, R_HELP = 8 };
+// Warp w runs on scheduler w & 3.  Every scheduler gets one band warp; the sequential warps (G2, G1, filter) take one
+// scheduler each and the helpers fill up: with the 28 streams of a cfg3 CTA helpers 0..13 are active (14 and 15 idle).
 //                                  scheduler: 0            1            2            3
 __constant__ int kRoleV3[kWarps] = {0,           1,           2,           3,
-                                    R_G2,        R_G1,        R_FILTER,    R_HELP + 3,
-                                    R_HELP + 0,  R_HELP + 1,  R_HELP + 2,  R_HELP + 6,
-                                    R_NONE,      R_HELP + 4,  R_HELP + 5,  R_HELP + 7};
-constexpr int kLiveWarps = 15;
+                                    R_G2,        R_G1,        R_FILTER,    R_HELP + 0,
+                                    R_HELP + 1,  R_HELP + 2,  R_HELP + 3,  R_HELP + 4,
+                                    R_HELP + 5,  R_HELP + 6,  R_HELP + 7,  R_HELP + 8,
+                                    R_HELP + 14, R_HELP + 9,  R_HELP + 10, R_HELP + 11,
+                                    R_NONE,      R_HELP + 15, R_HELP + 12, R_HELP + 13};
+constexpr int kLiveWarps = 23;
 
 struct SmemV3 {
-    alignas(16) float in[kInSlots][kMaxS * kInP];
+    alignas(16) float io[kIoSlots][kMaxS * kIoP];
     alignas(16) float xd[2][kMaxS * kRowP];
     alignas(16) float bp[2][kMaxS * kBpP];
     alignas(16) float lin[2][kMaxS * kRowP];
@@ -81,7 +89,6 @@ struct BlockWalk {
         while (F0 >= next) { ++row; next += block_len; }
         return true;
     }
-    __device__ __forceinline__ int clamped() const { return row < n_rows ? row : n_rows - 1; }
 };
 
 struct BandK3 { p2 a22, a12, c1, g, omc, kq; };
@@ -90,7 +97,7 @@ struct BandS3 { p2 i1, i2, e; };
 // eight frames of one band pair: u = 2 a2 i2 + x,  s = 2 a1 i1 + u (= 2 v1 / k),  i1' = (2 a1 - 1) i1 + u,  i2' = i2 + g s,
 // E' = (1 - c) E + (w c k^2 / 4) s^2, with k = 2 g / den the input gain the states are divided by (svf_bp, :74-93; :200-219)
 template <bool FULL>
-__device__ __forceinline__ void band_group3(const float* xd, float* pa, float* pb, int f0, int nv, const BandK3& c, BandS3& s)
+__device__ __forceinline__ void band_group3(const float* xd, float* pa, float* pb, int f0, int nv, bool wr, const BandK3& c, BandS3& s)
 {
     float xv[8];
     if (FULL) {
@@ -108,7 +115,9 @@ __device__ __forceinline__ void band_group3(const float* xd, float* pa, float* p
             s.i1 = fma2(c.c1, s.i1, u);
             s.i2 = fma2(c.g, sv, s.i2);
             s.e = fma2(c.kq, mul2(sv, sv), mul2(c.omc, s.e));
-            *reinterpret_cast<p2*>((k < 4 ? pa : pb) + (f0 + k) * 8) = s.e;
+            float e0, e1;
+            unpk(s.e, e0, e1);
+            if (wr) pa[(f0 + k) * 4] = e0 + e1;
         }
     }
 }
@@ -130,14 +139,15 @@ __device__ __forceinline__ float filt_frame(float l, float r, float& hpf_lp, flo
 }
 
 template <int MODE>
-__device__ __forceinline__ void filt_batch(const float* ib, float* xo, int nv, float& hpf_lp, float& lpf_y, float hpf_c, float lpf_c,
+__device__ __forceinline__ void filt_batch(const float* ib, int sw, float* xo, int nv, bool wr, float& hpf_lp, float& lpf_y, float hpf_c, float lpf_c,
                                            bool hpf_on, bool lpf_on)
 {
     if (nv == kF) {
-#pragma unroll 1
-        for (int f0 = 0; f0 < kF; f0 += 8) {
-            const float4 l0 = *reinterpret_cast<const float4*>(ib + f0), l1 = *reinterpret_cast<const float4*>(ib + f0 + 4);
-            const float4 r0 = *reinterpret_cast<const float4*>(ib + kRowP + f0), r1 = *reinterpret_cast<const float4*>(ib + kRowP + f0 + 4);
+#pragma unroll
+        for (int c0 = 0; c0 < 8; c0 += 2) {
+            const int pa = ((c0 ^ sw) << 2), pb = (((c0 + 1) ^ sw) << 2);
+            const float4 l0 = *reinterpret_cast<const float4*>(ib + pa), l1 = *reinterpret_cast<const float4*>(ib + pb);
+            const float4 r0 = *reinterpret_cast<const float4*>(ib + 32 + pa), r1 = *reinterpret_cast<const float4*>(ib + 32 + pb);
             float4 o0, o1;
             o0.x = filt_frame<MODE>(l0.x, r0.x, hpf_lp, lpf_y, hpf_c, lpf_c, hpf_on, lpf_on);
             o0.y = filt_frame<MODE>(l0.y, r0.y, hpf_lp, lpf_y, hpf_c, lpf_c, hpf_on, lpf_on);
@@ -147,10 +157,14 @@ __device__ __forceinline__ void filt_batch(const float* ib, float* xo, int nv, f
             o1.y = filt_frame<MODE>(l1.y, r1.y, hpf_lp, lpf_y, hpf_c, lpf_c, hpf_on, lpf_on);
             o1.z = filt_frame<MODE>(l1.z, r1.z, hpf_lp, lpf_y, hpf_c, lpf_c, hpf_on, lpf_on);
             o1.w = filt_frame<MODE>(l1.w, r1.w, hpf_lp, lpf_y, hpf_c, lpf_c, hpf_on, lpf_on);
-            *reinterpret_cast<float4*>(xo + f0) = o0; *reinterpret_cast<float4*>(xo + f0 + 4) = o1;
+            if (wr) { *reinterpret_cast<float4*>(xo + 4 * c0) = o0; *reinterpret_cast<float4*>(xo + 4 * c0 + 4) = o1; }
         }
     } else {
-        for (int f = 0; f < nv; ++f) xo[f] = filt_frame<MODE>(ib[f], ib[kRowP + f], hpf_lp, lpf_y, hpf_c, lpf_c, hpf_on, lpf_on);
+        for (int f = 0; f < nv; ++f) {
+            const int o = (((f >> 2) ^ sw) << 2) + (f & 3);
+            const float v = filt_frame<MODE>(ib[o], ib[32 + o], hpf_lp, lpf_y, hpf_c, lpf_c, hpf_on, lpf_on);
+            if (wr) xo[f] = v;
+        }
     }
 }
 
@@ -213,18 +227,19 @@ easyexpander_v3_kernel(const EEArgs a, const int spc)
                   pk((float)(st[(8 + jA) * ns] / (double)kA), (float)(st[(8 + jB) * ns] / (double)kB)),
                   pk((float)(st[(16 + jA) * ns] * (double)wA), (float)(st[(16 + jB) * ns] * (double)wB))};
         for (int i = 0; i < n_iter; ++i) {
-            if (act && i >= 2 && i - 2 < n_batches) {
+            if (act && i >= 2 && i - 2 < n_batches && !(a.role_off & 1)) {
                 const int b = i - 2;
-                const float* xd = sm.xd[b & 1] + ls * kRowP;
+                const int lr = live ? ls : 0;                        // rows exist for kMaxS streams only; the others never store
+                const float* xd = sm.xd[b & 1] + lr * kRowP;
                 const int nv = (int)min((int64_t)kF, n - (int64_t)b * kF);
-                float* pa = sm.bp[b & 1] + ls * kBpP + jA;
-                float* pb = sm.bp[b & 1] + ls * kBpP + (jA ^ 4);
+                float* pa = sm.bp[b & 1] + lr * kBpP + jj;
+                float* pb = nullptr;
                 if (nv == kF) {
 #pragma unroll 1
-                    for (int f0 = 0; f0 < kF; f0 += 8) band_group3<true>(xd, pa, pb, f0, nv, bk, bs);
+                    for (int f0 = 0; f0 < kF; f0 += 8) band_group3<true>(xd, pa, pb, f0, nv, live, bk, bs);
                 } else {
 #pragma unroll 1
-                    for (int f0 = 0; f0 < kF; f0 += 8) band_group3<false>(xd, pa, pb, f0, nv, bk, bs);
+                    for (int f0 = 0; f0 < kF; f0 += 8) band_group3<false>(xd, pa, pb, f0, nv, live, bk, bs);
                 }
             }
             v3_sync();
@@ -243,19 +258,24 @@ easyexpander_v3_kernel(const EEArgs a, const int spc)
         float hpf_lp = (float)st[24 * ns], lpf_y = (float)st[25 * ns], hpf_c = 0.f, lpf_c = 0.f;
         bool hpf_on = false, lpf_on = false, any_on = false;
         BlockWalk bw{0, -1, a.block_len, a.n_coef_blocks};
+        const EECoef* crow = a.coef + sg;
+        double n_hc = crow[0].hpf_c, n_lc = crow[0].lpf_c;                    // the next host block's row, loaded one block ahead
+        int n_hon = crow[0].hpf_on, n_lon = crow[0].lpf_on;
         for (int i = 0; i < n_iter; ++i) {
-            if (i >= 1 && i - 1 < n_batches) {
+            if (i >= 1 && i - 1 < n_batches && !(a.role_off & 2)) {
                 const int b = i - 1;
                 if (bw.enter((int64_t)b * kF)) {
-                    const EECoef& c = a.coef[(size_t)bw.clamped() * ns + sg];
-                    hpf_c = (float)c.hpf_c; lpf_c = (float)c.lpf_c; hpf_on = c.hpf_on != 0; lpf_on = c.lpf_on != 0;
+                    hpf_c = (float)n_hc; lpf_c = (float)n_lc; hpf_on = n_hon != 0; lpf_on = n_lon != 0;
                     any_on = __any_sync(0xffffffffu, hpf_on || lpf_on);
+                    const EECoef& c = crow[(size_t)(bw.row + 1 < bw.n_rows ? bw.row + 1 : bw.n_rows - 1) * ns];
+                    n_hc = c.hpf_c; n_lc = c.lpf_c; n_hon = c.hpf_on; n_lon = c.lpf_on;
                 }
-                const float* ib = sm.in[b & (kInSlots - 1)] + lane * kInP;
-                float* xo = sm.xd[b & 1] + lane * kRowP;
+                const int lr = live ? lane : 0;                      // rows exist for kMaxS streams only; the others never store
+                const float* ib = sm.io[b & (kIoSlots - 1)] + lr * kIoP;
+                float* xo = sm.xd[b & 1] + lr * kRowP;
                 const int nv = (int)min((int64_t)kF, n - (int64_t)b * kF);
-                if (any_on) filt_batch<1>(ib, xo, nv, hpf_lp, lpf_y, hpf_c, lpf_c, hpf_on, lpf_on);
-                else filt_batch<0>(ib, xo, nv, hpf_lp, lpf_y, hpf_c, lpf_c, hpf_on, lpf_on);
+                if (any_on) filt_batch<1>(ib, lr & 7, xo, nv, live, hpf_lp, lpf_y, hpf_c, lpf_c, hpf_on, lpf_on);
+                else filt_batch<0>(ib, lr & 7, xo, nv, live, hpf_lp, lpf_y, hpf_c, lpf_c, hpf_on, lpf_on);
             }
             v3_sync();
         }
@@ -268,11 +288,12 @@ easyexpander_v3_kernel(const EEArgs a, const int spc)
         G1S gs{(float)st[26 * ns], (float)st[29 * ns]};
         const float slow_c = (float)a.k.slow_c, cfast = (float)a.k.close_fast_c, cslow = (float)a.k.close_slow_c;
         for (int i = 0; i < n_iter; ++i) {
-            if (i >= 4 && i - 4 < n_batches) {
+            if (i >= 4 && i - 4 < n_batches && !(a.role_off & 4)) {
                 const int b = i - 4;
-                const float* lin = sm.lin[b & 1] + lane * kRowP;
-                const float* db = sm.db[b & (kDbSlots - 1)] + lane * kRowP;
-                float* cc = sm.cc[b & 1] + lane * kRowP;
+                const int lr = live ? lane : 0;
+                const float* lin = sm.lin[b & 1] + lr * kRowP;
+                const float* db = sm.db[b % kDbSlots] + lr * kRowP;
+                float* cc = sm.cc[b & 1] + lr * kRowP;
                 const int nv = (int)min((int64_t)kF, n - (int64_t)b * kF);
                 if (nv == kF) {
 #pragma unroll 1
@@ -284,10 +305,10 @@ easyexpander_v3_kernel(const EEArgs a, const int spc)
                         o0.z = g1_frame(l0.z, d0.z, gs, slow_c, cfast, cslow); o0.w = g1_frame(l0.w, d0.w, gs, slow_c, cfast, cslow);
                         o1.x = g1_frame(l1.x, d1.x, gs, slow_c, cfast, cslow); o1.y = g1_frame(l1.y, d1.y, gs, slow_c, cfast, cslow);
                         o1.z = g1_frame(l1.z, d1.z, gs, slow_c, cfast, cslow); o1.w = g1_frame(l1.w, d1.w, gs, slow_c, cfast, cslow);
-                        *reinterpret_cast<float4*>(cc + f0) = o0; *reinterpret_cast<float4*>(cc + f0 + 4) = o1;
+                        if (live) { *reinterpret_cast<float4*>(cc + f0) = o0; *reinterpret_cast<float4*>(cc + f0 + 4) = o1; }
                     }
                 } else {
-                    for (int f = 0; f < nv; ++f) cc[f] = g1_frame(lin[f], db[f], gs, slow_c, cfast, cslow);
+                    for (int f = 0; f < nv; ++f) { const float v = g1_frame(lin[f], db[f], gs, slow_c, cfast, cslow); if (live) cc[f] = v; }
                 }
             }
             v3_sync();
@@ -301,17 +322,21 @@ easyexpander_v3_kernel(const EEArgs a, const int spc)
         G2S gs{(float)st[28 * ns], (float)st[30 * ns], 0.f, 0.f, st[27 * ns] != 0.0};
         const float open_c = (float)a.k.open_c;
         BlockWalk bw{0, -1, a.block_len, a.n_coef_blocks};
+        const EECoef* crow = a.coef + sg;
+        double n_thr = crow[0].thresh_db;                                     // the next host block's threshold, loaded one block ahead
         for (int i = 0; i < n_iter; ++i) {
-            if (i >= 5 && i - 5 < n_batches) {
+            if (i >= 5 && i - 5 < n_batches && !(a.role_off & 8)) {
                 const int b = i - 5;
                 if (bw.enter((int64_t)b * kF)) {
-                    gs.thresh_db = (float)a.coef[(size_t)bw.clamped() * ns + sg].thresh_db;
+                    gs.thresh_db = (float)n_thr;
+                    n_thr = crow[(size_t)(bw.row + 1 < bw.n_rows ? bw.row + 1 : bw.n_rows - 1) * ns].thresh_db;
                     gs.thresh_hi = gs.thresh_db + 2.0f;                                   // hys_db (:33)
                 }
-                const float* db = sm.db[b & (kDbSlots - 1)] + lane * kRowP;
-                const float* tg = sm.tg[b & (kDbSlots - 1)] + lane * kRowP;
-                const float* cc = sm.cc[b & 1] + lane * kRowP;
-                float* go = sm.gain[b & 1] + lane * kRowP;
+                const int lr = live ? lane : 0;
+                const float* db = sm.db[b % kDbSlots] + lr * kRowP;
+                const float* tg = sm.tg[b % kDbSlots] + lr * kRowP;
+                const float* cc = sm.cc[b & 1] + lr * kRowP;
+                float* go = sm.gain[b & 1] + lr * kRowP;
                 const int nv = (int)min((int64_t)kF, n - (int64_t)b * kF);
                 if (nv == kF) {
 #pragma unroll 1
@@ -324,10 +349,10 @@ easyexpander_v3_kernel(const EEArgs a, const int spc)
                         o0.z = g2_frame(d0.z, t0.z, c0.z, gs, open_c); o0.w = g2_frame(d0.w, t0.w, c0.w, gs, open_c);
                         o1.x = g2_frame(d1.x, t1.x, c1.x, gs, open_c); o1.y = g2_frame(d1.y, t1.y, c1.y, gs, open_c);
                         o1.z = g2_frame(d1.z, t1.z, c1.z, gs, open_c); o1.w = g2_frame(d1.w, t1.w, c1.w, gs, open_c);
-                        *reinterpret_cast<float4*>(go + f0) = o0; *reinterpret_cast<float4*>(go + f0 + 4) = o1;
+                        if (live) { *reinterpret_cast<float4*>(go + f0) = o0; *reinterpret_cast<float4*>(go + f0 + 4) = o1; }
                     }
                 } else {
-                    for (int f = 0; f < nv; ++f) go[f] = g2_frame(db[f], tg[f], cc[f], gs, open_c);
+                    for (int f = 0; f < nv; ++f) { const float v = g2_frame(db[f], tg[f], cc[f], gs, open_c); if (live) go[f] = v; }
                 }
             }
             v3_sync();
@@ -336,62 +361,99 @@ easyexpander_v3_kernel(const EEArgs a, const int spc)
             st[27 * ns] = gs.expanding ? 1.0 : 0.0; st[28 * ns] = (double)gs.gain_db_s; st[30 * ns] = (double)gs.gr_db_m;
         }
     } else {
-        // ============================ helper warps: lane = frame; streams 4h .. 4h + 3 of the CTA ========================
+        // ============================ helper warps: lane = frame; streams kQ h .. kQ h + kQ - 1 of the CTA ===============
+        // Global memory is touched in 512-byte runs per row: a super-batch (4 batches = 128 frames) of a helper's rows is
+        // fetched with one 16-byte cp.async per lane and row into the I/O ring kLead iterations before its first batch is
+        // due; S4 overwrites the ring slot in place with the output, and once the super-batch's last batch is through S4
+        // the same warp stores it with one 128-bit store per lane and row.
         const int h = role - R_HELP;
-        const bool act = 4 * h < ns_cta;
-        const float* pin[4]; float* pout[4];
-        bool has[4];
+        const bool act = kQ * h < ns_cta;
+        const float* irow[kQ]; float* orow[kQ];
+        const EECoef* crow[kQ];
+        bool has[kQ];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-            const int lq = 4 * h + q;
+        for (int q = 0; q < kQ; ++q) {
+            const int lq = kQ * h + q;
             has[q] = lq < ns_cta;
             const size_t s = (size_t)(s_base + (has[q] ? lq : 0));
-            pin[q] = a.in + s * 2 * a.row_stride + lane;
-            pout[q] = a.out + s * 2 * a.row_stride + lane - 6 * kF;          // S4 runs six batches behind S0
+            irow[q] = a.in + s * 2 * a.row_stride;
+            orow[q] = a.out + s * 2 * a.row_stride;
+            crow[q] = a.coef + s;
         }
         const int64_t rs = a.row_stride;
-        const int swz = 4 * ((lane >> 2) & 1);
-        const int bpA = lane * 8 + swz, bpB = lane * 8 + (swz ^ 4);          // bands 0-3 / 4-7 of this lane's frame
-        float thr[4] = {0.f, 0.f, 0.f, 0.f}, dep[4] = {0.f, 0.f, 0.f, 0.f}, rm1[4] = {0.f, 0.f, 0.f, 0.f};
+        const int bpA = lane * 4;                                            // the four pair sums of this lane's frame
+        // ring offsets of this lane: as frame `lane` of a batch (S4), and as 16-byte chunk `lane` of a super-batch (I/O)
+        int fo[kQ], co[kQ];
+#pragma unroll
+        for (int q = 0; q < kQ; ++q) {
+            const int lq = act ? (has[q] ? kQ * h + q : kQ * h) : 0;
+            fo[q] = lq * kIoP + ((((lane >> 2) ^ (lq & 7)) << 2) | (lane & 3));
+            co[q] = (lane >> 3) * (kMaxS * kIoP) + lq * kIoP + (((lane & 7) ^ (lq & 7)) << 2);
+        }
+        float thr[kQ], dep[kQ], rm1[kQ];
+        double nthr[kQ], ndep[kQ], nrat[kQ];                                 // the next host block's row, loaded one block ahead
         BlockWalk bw{0, -1, a.block_len, a.n_coef_blocks};
         const float eps = 1e-12f;
         const float db_per_lg2_pow = 3.0102999566398120f;                    // 10 log10(2): det_db = 10 log10(sum) = 20 log10(sqrt(sum))
         const float lg2_per_db = 0.16609640474436813f;                       // ln(10)/20 / ln(2)
-        float hold[4][2];
-        for (int i = 0; i < n_iter; ++i) {
-            if (act) {
-                // ---- S0 (issue): batch i ---------------------------------------------------------------------------
-                {
-                    const bool ok = i < n_batches && (int64_t)i * kF + lane < n;
+        const int n_sb = (n_batches + kSB - 1) / kSB;
+        // cp.async of super-batch k (frames 128 k + 4 lane .. + 3 of every row); bytes beyond the call are zero-filled
+        auto fetch = [&](const int k) {
+            if (act && k < n_sb && !(a.role_off & 32)) {
+                const int64_t f0 = (int64_t)k * (kSB * kF) + 4 * lane;
+                const int64_t left = n - f0;
+                const int bytes = left >= 4 ? 16 : (left > 0 ? 4 * (int)left : 0);
+                const int64_t fsrc = bytes ? f0 : 0;
+                float* ring = sm.io[(k * kSB) & (kIoSlots - 1)];
 #pragma unroll
-                    for (int q = 0; q < 4; ++q) {
-                        hold[q][0] = ok ? pin[q][0] : 0.f;
-                        hold[q][1] = ok ? pin[q][rs] : 0.f;
+                for (int q = 0; q < kQ; ++q) {
+                    if (has[q]) {
+#pragma unroll
+                        for (int ch = 0; ch < 2; ++ch)
+                            asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(ring + co[q] + 32 * ch)),
+                                         "l"(irow[q] + ch * rs + fsrc), "r"(bytes) : "memory");
                     }
                 }
+            }
+            asm volatile("cp.async.commit_group;" ::: "memory");
+        };
+#pragma unroll
+        for (int q = 0; q < kQ; ++q) {
+            thr[q] = dep[q] = rm1[q] = 0.f;
+            nthr[q] = crow[q][0].thresh_db; ndep[q] = crow[q][0].depth_db; nrat[q] = crow[q][0].ratio_base;
+        }
+        fetch(0); fetch(1);
+        for (int i = 0; i < n_iter; ++i) {
+            // ---- S0: super-batch i / 4 has to be in the ring when this iteration's barrier publishes batch i; the one
+            // ---- that starts kLead iterations from now is requested
+            if ((i & (kSB - 1)) == 0) asm volatile("cp.async.wait_group 1;" ::: "memory");
+            if (((i + kLead) & (kSB - 1)) == 0) fetch((i + kLead) / kSB);
+            if (act) {
                 // ---- P2: batch i - 3: band sum in the script's order, level, memoryless half of the gain computer ------
-                if (i >= 3 && i - 3 < n_batches) {
+                if (i >= 3 && i - 3 < n_batches && !(a.role_off & 16)) {
                     const int b = i - 3;
                     if (bw.enter((int64_t)b * kF)) {
+                        const int nr = bw.row + 1 < bw.n_rows ? bw.row + 1 : bw.n_rows - 1;
 #pragma unroll
-                        for (int q = 0; q < 4; ++q) {
-                            const EECoef& c = a.coef[(size_t)bw.clamped() * ns + s_base + (has[q] ? 4 * h + q : 0)];
-                            thr[q] = (float)c.thresh_db; dep[q] = (float)c.depth_db; rm1[q] = (float)(c.ratio_base - 1.0);
+                        for (int q = 0; q < kQ; ++q) {
+                            thr[q] = (float)nthr[q]; dep[q] = (float)ndep[q]; rm1[q] = (float)(nrat[q] - 1.0);
+                            const EECoef& c = crow[q][(size_t)nr * ns];
+                            nthr[q] = c.thresh_db; ndep[q] = c.depth_db; nrat[q] = c.ratio_base;
                         }
                     }
-                    const float* bp = sm.bp[b & 1] + (4 * h) * kBpP;
-                    float* lin = sm.lin[b & 1] + (4 * h) * kRowP + lane;
-                    float* db = sm.db[b & (kDbSlots - 1)] + (4 * h) * kRowP + lane;
-                    float* tg = sm.tg[b & (kDbSlots - 1)] + (4 * h) * kRowP + lane;
-                    float sum[4];
+                    const float* bp = sm.bp[b & 1] + (kQ * h) * kBpP;
+                    float* lin = sm.lin[b & 1] + (kQ * h) * kRowP + lane;
+                    float* db = sm.db[b % kDbSlots] + (kQ * h) * kRowP + lane;
+                    float* tg = sm.tg[b % kDbSlots] + (kQ * h) * kRowP + lane;
+                    float sum[kQ];
 #pragma unroll
-                    for (int q = 0; q < 4; ++q) {
-                        const float4 b03 = *reinterpret_cast<const float4*>(bp + q * kBpP + bpA);
-                        const float4 b47 = *reinterpret_cast<const float4*>(bp + q * kBpP + bpB);
-                        sum[q] = fmaxf(((((((b03.x + b03.y) + b03.z) + b03.w) + b47.x) + b47.y) + b47.z) + b47.w, eps);
+                    for (int q = 0; q < kQ; ++q) {
+                        const int qq = has[q] ? q : 0;
+                        const float4 pr = *reinterpret_cast<const float4*>(bp + qq * kBpP + bpA);
+                        sum[q] = fmaxf(((pr.x + pr.y) + pr.z) + pr.w, eps);
                     }
 #pragma unroll
-                    for (int q = 0; q < 4; ++q) {
+                    for (int q = 0; q < kQ; ++q) {
                         const float det_lin = sum[q] * rsqrt_fast(sum[q]);
                         const float det_db = db_per_lg2_pow * lg2_fast(sum[q]);
                         float d = thr[q] - det_db;
@@ -401,34 +463,22 @@ easyexpander_v3_kernel(const EEArgs a, const int spc)
                         const float re1 = d < 6.0f ? rm1[q] * smo : rm1[q];               // ratio_eff - 1
                         float target_gr = d * re1;
                         target_gr = target_gr > dep[q] ? dep[q] : target_gr;
-                        lin[q * kRowP] = det_lin; db[q * kRowP] = det_db; tg[q * kRowP] = target_gr;
+                        if (has[q]) { lin[q * kRowP] = det_lin; db[q * kRowP] = det_db; tg[q * kRowP] = target_gr; }
                     }
                 }
-                // ---- S4: batch i - 6: exp and the output multiplies ------------------------------------------------------
-                if (i >= 6) {
+                // ---- S4: batch i - 6: exp and the output multiplies; 128-byte row stores --------------------------------
+                if (i >= 6 && i - 6 < n_batches && !(a.role_off & 32)) {
                     const int b = i - 6;
-                    const bool okf = (int64_t)b * kF + lane < n;
-                    const float* ib = sm.in[b & (kInSlots - 1)] + (4 * h) * kInP + lane;
-                    const float* gp = sm.gain[b & 1] + (4 * h) * kRowP + lane;
-                    float o0[4], o1[4];
+                    const float* io = sm.io[b & (kIoSlots - 1)];
+                    const float* gp = sm.gain[b & 1] + (kQ * h) * kRowP + lane;
+                    const int64_t f = (int64_t)b * kF + lane;
 #pragma unroll
-                    for (int q = 0; q < 4; ++q) {
-                        const float gain_lin = ex2_fast(gp[q * kRowP] * lg2_per_db);
-                        o0[q] = ib[q * kInP] * gain_lin;
-                        o1[q] = ib[q * kInP + kRowP] * gain_lin;
+                    for (int q = 0; q < kQ; ++q) {
+                        const float gain_lin = ex2_fast(gp[(has[q] ? q : 0) * kRowP] * lg2_per_db);
+                        const float o0 = io[fo[q]] * gain_lin, o1 = io[fo[q] + 32] * gain_lin;
+                        if (has[q] && f < n) { orow[q][f] = o0; orow[q][rs + f] = o1; }
                     }
-#pragma unroll
-                    for (int q = 0; q < 4; ++q)
-                        if (okf && has[q]) { pout[q][0] = o0[q]; pout[q][rs] = o1[q]; }
                 }
-                // ---- S0 (commit): batch i -> shared memory -----------------------------------------------------------------
-                {
-                    float* ib = sm.in[i & (kInSlots - 1)] + (4 * h) * kInP + lane;
-#pragma unroll
-                    for (int q = 0; q < 4; ++q) { ib[q * kInP] = hold[q][0]; ib[q * kInP + kRowP] = hold[q][1]; }
-                }
-#pragma unroll
-                for (int q = 0; q < 4; ++q) { pin[q] += kF; pout[q] += kF; }
             }
             v3_sync();
         }
@@ -438,6 +488,8 @@ easyexpander_v3_kernel(const EEArgs a, const int spc)
 bool easyexpander_v3_eligible(const EEArgs& a)
 {
     if (a.block_len < kF || a.block_len % kF != 0) return false;
+    // 16-byte cp.async / 128-bit stores per row: rows have to start on 16-byte boundaries
+    if (a.row_stride % 4 != 0 || ((uintptr_t)a.in & 15) != 0 || ((uintptr_t)a.out & 15) != 0) return false;
     for (int j = 0; j < 8; ++j) {
         const float w = (float)a.k.w[j], k = (float)(2.0 * a.k.g[j] / a.k.den[j]);
         if (!(w > 1e-30f) || !(k > 1e-30f)) return false;                  // the scaled band states divide by these

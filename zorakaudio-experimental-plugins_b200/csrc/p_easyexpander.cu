@@ -193,7 +193,7 @@ public:
         }
         EEArgs a{};
         a.in = in; a.out = out; a.tap = tap; a.row_stride = stride; a.n_frames = n;
-        a.n_streams = ns; a.block_len = I.block_len; a.n_coef_blocks = nbq; a.coef = d_coef; a.state = d_state; a.k = k_;
+        a.n_streams = ns; a.block_len = I.block_len; a.n_coef_blocks = nbq; a.coef = d_coef; a.state = d_state; a.k = k_; a.role_off = I.opt_role_off;
         const bool timed = I.time_begin();
         if (!easyexpander_launch(a, I.precision, n_sm, I.stream, I.opt_scalar_f32)) return false;
         if (timed) I.time_end();
@@ -264,7 +264,7 @@ public:
         ++I.launches;
         EEArgs a{};
         a.in = in; a.out = out; a.tap = tap; a.row_stride = stride; a.n_frames = n;
-        a.n_streams = ns; a.block_len = I.block_len; a.n_coef_blocks = nb; a.coef = d_coef; a.state = d_state; a.k = k_;
+        a.n_streams = ns; a.block_len = I.block_len; a.n_coef_blocks = nb; a.coef = d_coef; a.state = d_state; a.k = k_; a.role_off = I.opt_role_off;
         const bool timed = I.time_begin();
         if (!easyexpander_launch(a, I.precision, n_sm, I.stream, I.opt_scalar_f32)) return -1;
         if (timed) I.time_end();

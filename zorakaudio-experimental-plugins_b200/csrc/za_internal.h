@@ -75,6 +75,7 @@ struct EEArgs {
     const EECoef* coef;                            // [n_coef_blocks][n_streams]
     double* state;                                 // [kEEState][n_streams]
     EEConsts k;
+    int role_off;                                  // measurement only (option "role_off"): 1 bands, 2 filter, 4 G1, 8 G2, 16 helpers' P2, 32 helpers' I/O skip their work
 };
 bool easyexpander_launch(const EEArgs& a, int precision, int n_sm, cudaStream_t stream, int variant = 0);
 bool easyexpander_v3_eligible(const EEArgs& a);          // k_easyexpander_v3.cu: fp32, block_len a multiple of 32
