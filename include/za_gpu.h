@@ -204,6 +204,18 @@ ZA_API int za_gpu_synth_tables(float* sine4096, float* amp256);      /* the gene
  * independent, bit-exact) and host_energy[r] = sum_i x^2 (double).  Synchronises cuda_stream. */
 ZA_API int za_gpu_checksum(const float* dev, int n_rows, int64_t n_frames, int64_t frame_stride, uint64_t* host_sum,
                            double* host_energy, int device, void* cuda_stream);
+/* The same per-row reduction for callers that may not allocate device memory (CUDA graph capture around them, tight
+ * serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Its accumulators live in a file-scope static device array of ZA_CHECKSUM_NOALLOC_MAX_ROWS rows (256 KB that
+ * every GPU loading the library holds until the process exits); the call makes no cudaMalloc / cudaFree.  n_rows beyond
+ * the maximum is refused with ZA_ERR_ARG and a message (split the rows over calls, or use za_gpu_checksum).  The array is
+ * shared by every call on a device and keeps the previous call's contents: each call clears the cells it uses on
+ * cuda_stream before its kernel, and calls that overlap on the GPU (different streams, different host threads) race --
+ * serialise them.  Results are bit-identical to za_gpu_checksum's sums; energies agree to double rounding of the
+ * atomics' order.  Synchronises cuda_stream. */
+#define ZA_CHECKSUM_NOALLOC_MAX_ROWS 16384
+ZA_API int za_gpu_checksum_noalloc(const float* dev, int n_rows, int64_t n_frames, int64_t frame_stride, uint64_t* host_sum,
+                                   double* host_energy, int device, void* cuda_stream);
 
 ZA_API const char* za_gpu_last_error(void);
 ZA_API int za_gpu_device_count(void);

@@ -120,6 +120,29 @@ const SynthTables* device_tables(int device)
     return g_tabs.d[device];
 }
 
+// ---- scratch of za_gpu_checksum_noalloc: a file-scope device array, so that entry point never allocates -----------------
+// Every GPU that loads the library holds these 256 KB until the process exits.  Layout: [0, kNoAllocMaxRows) the wrapping
+// 64-bit row sums, [kNoAllocMaxRows, 2 kNoAllocMaxRows) the row energies (doubles, same 8-byte cells).
+constexpr int kNoAllocMaxRows = 16384;
+static __device__ __align__(256) unsigned long long g_checksum_scratch[2 * kNoAllocMaxRows];
+
+// In host code `g_checksum_scratch` is only a stand-in for the symbol, not a device address: the address comes from
+// cudaGetSymbolAddress, asked once per device with that device current.
+struct ScratchAddr { unsigned long long* d[64] = {}; std::mutex m; };
+ScratchAddr g_scratch_addr;
+
+unsigned long long* checksum_scratch(int device)       // the caller has made `device` current
+{
+    if (device < 0 || device >= 64) { set_error("za_gpu_checksum_noalloc: device index out of range"); return nullptr; }
+    std::lock_guard<std::mutex> lk(g_scratch_addr.m);
+    if (!g_scratch_addr.d[device]) {
+        void* p = nullptr;
+        if (!cuda_ok(cudaGetSymbolAddress(&p, g_checksum_scratch), "cudaGetSymbolAddress(checksum scratch)") || !p) return nullptr;
+        g_scratch_addr.d[device] = (unsigned long long*)p;
+    }
+    return g_scratch_addr.d[device];
+}
+
 }  // namespace
 }  // namespace za
 
@@ -180,6 +203,40 @@ ZA_API int za_gpu_checksum(const float* dev, int n_rows, int64_t n_frames, int64
               cuda_ok(cudaMemcpyAsync(host_energy, d_e, (size_t)n_rows * 8, cudaMemcpyDeviceToHost, st), "energy read") &&
               cuda_ok(cudaStreamSynchronize(st), "checksum sync");
     cudaFree(d_sum); cudaFree(d_e);
+    return ok ? ZA_OK : ZA_ERR_CUDA;
+}
+
+// The same reduction as za_gpu_checksum with the accumulators in the static device array above: no cudaMalloc / cudaFree,
+// here or in anything it calls.  The array keeps the previous call's sums, so the cells this call uses are cleared first (on
+// the caller's stream, ahead of the kernel).  All calls on a device share the array: calls that overlap on the GPU race.
+ZA_API int za_gpu_checksum_noalloc(const float* dev, int n_rows, int64_t n_frames, int64_t frame_stride, uint64_t* host_sum,
+                                   double* host_energy, int device, void* cuda_stream)
+{
+    if (!dev || n_rows <= 0 || n_frames < 0 || frame_stride < n_frames || !host_sum || !host_energy) {
+        set_error("za_gpu_checksum_noalloc: bad argument");
+        return ZA_ERR_ARG;
+    }
+    if (n_rows > kNoAllocMaxRows) {
+        set_error("za_gpu_checksum_noalloc: " + std::to_string(n_rows) + " rows exceed the static scratch (" + std::to_string(kNoAllocMaxRows) +
+                  " rows per call); split the rows over several calls or use za_gpu_checksum");
+        return ZA_ERR_ARG;
+    }
+    if (!cuda_ok(cudaSetDevice(device), "cudaSetDevice")) return ZA_ERR_CUDA;
+    unsigned long long* scratch = checksum_scratch(device);
+    if (!scratch) return ZA_ERR_CUDA;
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    unsigned long long* d_sum = scratch;
+    double* d_e = reinterpret_cast<double*>(scratch + kNoAllocMaxRows);
+    if (!cuda_ok(cudaMemsetAsync(d_sum, 0, (size_t)n_rows * 8, st), "checksum scratch clear") ||
+        !cuda_ok(cudaMemsetAsync(d_e, 0, (size_t)n_rows * 8, st), "energy scratch clear")) return ZA_ERR_CUDA;
+    if (n_frames > 0) {
+        const int bx = (int)std::min<int64_t>((n_frames + 255) / 256, 64);
+        checksum_kernel<<<dim3(bx, n_rows), 256, 0, st>>>(dev, n_frames, frame_stride, d_sum, d_e);
+    }
+    const bool ok = cuda_ok(cudaGetLastError(), "checksum_kernel") &&
+                    cuda_ok(cudaMemcpyAsync(host_sum, d_sum, (size_t)n_rows * 8, cudaMemcpyDeviceToHost, st), "checksum read") &&
+                    cuda_ok(cudaMemcpyAsync(host_energy, d_e, (size_t)n_rows * 8, cudaMemcpyDeviceToHost, st), "energy read") &&
+                    cuda_ok(cudaStreamSynchronize(st), "checksum sync");
     return ok ? ZA_OK : ZA_ERR_CUDA;
 }
 

@@ -40,7 +40,7 @@ SYMBOLS = [
     "za_gpu_quantise", "za_gpu_create", "za_gpu_destroy", "za_gpu_set_stream", "za_gpu_prepare", "za_gpu_process",
     "za_gpu_process_tap64", "za_gpu_read_state", "za_gpu_sync", "za_gpu_launch_count", "za_gpu_last_kernel_ms",
     "za_gpu_set_option", "za_gpu_render", "za_gpu_last_error", "za_gpu_device_count", "za_gpu_version",
-    "za_gpu_synth", "za_gpu_synth_tables", "za_gpu_checksum", "za_gpu_host_alloc", "za_gpu_host_free",
+    "za_gpu_synth", "za_gpu_synth_tables", "za_gpu_checksum", "za_gpu_checksum_noalloc", "za_gpu_host_alloc", "za_gpu_host_free",
     "za_gpu_state_size", "za_gpu_state_save", "za_gpu_state_load",
     "za_gpu_create_os", "za_chain_create", "za_chain_destroy", "za_chain_info", "za_chain_stage", "za_chain_set_chunk_blocks", "za_chain_prepare",
     "za_chain_process", "za_chain_sync",
@@ -102,6 +102,7 @@ def lib() -> C.CDLL:
                                    C.c_int, C.c_void_p]
         L.za_gpu_synth_tables.argtypes = [C.c_void_p, C.c_void_p]
         L.za_gpu_checksum.argtypes = [C.c_void_p, C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        L.za_gpu_checksum_noalloc.argtypes = L.za_gpu_checksum.argtypes
         _lib = L
     return _lib
 
@@ -186,6 +187,20 @@ def checksum(x, cuda_stream=None):
     s, e = np.zeros(ns * nch, np.uint64), np.zeros(ns * nch, np.float64)
     _check(lib().za_gpu_checksum(x.data_ptr(), ns * nch, nf, nf, s.ctypes.data, e.ctypes.data, x.device.index or 0, cuda_stream),
            "za_gpu_checksum")
+    return s.reshape(ns, nch), e.reshape(ns, nch)
+
+
+CHECKSUM_NOALLOC_MAX_ROWS = 16384
+
+
+def checksum_noalloc(x, cuda_stream=None):
+    """checksum() through za_gpu_checksum_noalloc: accumulators in the library's static device array (no device allocation);
+    at most CHECKSUM_NOALLOC_MAX_ROWS rows per call, calls on one device must not overlap."""
+    ns, nch, nf = x.shape
+    assert x.is_cuda and x.is_contiguous()
+    s, e = np.zeros(ns * nch, np.uint64), np.zeros(ns * nch, np.float64)
+    _check(lib().za_gpu_checksum_noalloc(x.data_ptr(), ns * nch, nf, nf, s.ctypes.data, e.ctypes.data, x.device.index or 0, cuda_stream),
+           "za_gpu_checksum_noalloc")
     return s.reshape(ns, nch), e.reshape(ns, nch)
 
 
