@@ -48,7 +48,7 @@ SEED = 5000
 # synth = input generator kind of za_gpu_synth (0 = noise + two sines, 1 = programme bursts)
 WORKLOADS = {
     "cfg3": dict(plugin="EasyExpander", streams=4096, seconds=60.0, ch=(2, 2), automate=[0, 1], cpu=(256, 10.0), synth=1,
-                 kernel={"f32": "easyexpander_split_kernel", "f64": "easyexpander_kernel"},
+                 kernel={"f32": "easyexpander_v3_kernel", "f64": "easyexpander_kernel"},
                  text="cfg3: EasyExpander (nonlinear envelope + gain computer), {ns} stereo streams x {sec:g} s @ 48 kHz per GPU, "
                       "threshold/depth automated every 512-frame block, in-place buffers"),
     "cfg2": dict(plugin="cascade8", streams=1024, seconds=60.0, ch=(1, 1), automate=None, cpu=(1024, 20.0), synth=0,
@@ -62,8 +62,7 @@ WORKLOADS = {
                     kernel={"f32": "modtilt_kernel"},
                     text="cfg3 shape on the Faust leaf ModTilt (envelope tilt shaper: 5 one-poles + sqrt/div/log10/10^x per frame), "
                          "{ns} stereo streams x {sec:g} s @ 48 kHz per GPU, tilt automated every 512-frame block, in-place buffers"),
-    # the other leaves of the three classes at the cfg3 batch shape (4096 stereo streams); shorter renders while they run on
-    # the translated stream-per-thread path
+    # the other leaves of the three classes at the cfg3 batch shape (4096 stereo streams), 10 s per step
     "erbtilt": dict(plugin="ERBTilt", streams=4096, seconds=10.0, ch=(2, 2), automate=[0], cpu=(256, 5.0), synth=1,
                     kernel={"f32": "erbtilt_kernel", "f64": "erbtilt_kernel"},
                     text="ERB Tilt (15 one-poles x 2 ch + energy followers + guard), {ns} stereo streams x {sec:g} s @ 48 kHz per GPU, tilt automated every 512-frame block"),
@@ -83,7 +82,7 @@ WORKLOADS = {
                  kernel={"f32": "jsfx_process_kernel", "f64": "jsfx_process_kernel"},
                  text="cfg3 on SOMA (lookahead limiter), {ns} stereo streams x {sec:g} s @ 48 kHz per GPU, drive/release automated every 512-frame block"),
 }
-SUBS_DEFAULT = ["cfg2", "cfg4", "modtilt", "cfg5"]
+SUBS_DEFAULT = ["cfg2", "cfg4", "modtilt", "erbtilt", "specstab", "cfg5"]
 
 
 def peaks():
@@ -317,7 +316,8 @@ def measure(name, ctx, args, headline):
             bp.set_option("warps_per_stream", args.warps)
         if headline:
             for ov in args.option:
-                bp.set_option(ov.split("=")[0], int(ov.split("=")[1]))
+                if ":" not in ov:                                   # "Leaf:name=value" belongs to bench_cfg5's leaves
+                    bp.set_option(ov.split("=")[0], int(ov.split("=")[1]))
         bp.set_stream(stream_ptr)
         bp.prepare(p0)
         steps = (args.steps if headline else max(3, args.steps // 4)) if main_prec else max(2, args.steps // (2 if headline else 8))

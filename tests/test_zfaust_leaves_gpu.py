@@ -86,3 +86,37 @@ def test_f64_refused(gpu):
     for key in KEYS:
         with pytest.raises(gpu.ZaError, match="float32"):
             gpu.BatchProcessor(key, 4, precision="f64")
+
+
+@pytest.mark.parametrize("ns,block,cuts", [(37, 512, (0, 31, 31 + 45, 31 + 45 + 4096 + 13, 12000)), (70, 100, (0, 6000, 6001, 9000)),
+                                           (3, 7, (0, 64, 2000))])
+def test_clickbegonesg_tiled_kernel_is_bit_identical_to_the_generic_kernel(gpu, ns, block, cuts):
+    """cbg_tiled_kernel (p_faust.cu: predictors lane = frame out of a shared-memory ring, recurrences lane = stream) calls
+    the same Cbg::predict / Cbg::tail as the generic stream-per-thread kernel (option scalar_f32 = 1): outputs AND every
+    state word (delay-line ring, its position, the five followers) must be the same bits -- over several calls of ragged
+    lengths (the ring is handed over through the state), host blocks that do not divide the 32-frame tiles, partial CTAs,
+    and the Mode slider (which picks the predictor pair) moving per block."""
+    key = "ClickBeGoneSG"
+    port = zo.PortPlugin(key)
+    nf = cuts[-1]
+    x = make_input(key, port, ns, nf)
+    base = np.array([s["default"] for s in port.sliders], np.float32)
+    p = wl.automation(port.sliders, (nf + block - 1) // block, ns, which=[0, 1, 2, 3], base=base)
+    outs, states = [], []
+    for generic in (0, 1):
+        bp = gpu.BatchProcessor(key, ns, 48000.0, block, "f32").prepare(p[0])
+        bp.set_option("scalar_f32", generic)
+        parts = []
+        for c0, c1 in zip(cuts[:-1], cuts[1:]):
+            if c0 % block:                       # a call starts a host block: only cut on block boundaries for the parameter rows
+                b0 = c0 // block
+                parts.append(bp.process(np.ascontiguousarray(x[:, :, c0:c1]), params=np.ascontiguousarray(p[b0:b0 + 1])))
+            else:
+                parts.append(bp.process(np.ascontiguousarray(x[:, :, c0:c1]), params=np.ascontiguousarray(p[c0 // block:(c1 + block - 1) // block])))
+        outs.append(np.concatenate(parts, axis=2))
+        states.append(np.stack([bp.read_state(f"state[{k}]") for k in range(70)]))
+        bp.close()
+    assert np.array_equal(outs[0].view(np.uint32), outs[1].view(np.uint32))
+    assert np.array_equal(states[0][:64].astype(np.float32).view(np.uint32), states[1][:64].astype(np.float32).view(np.uint32))
+    assert np.array_equal(states[0][65:].astype(np.float32).view(np.uint32), states[1][65:].astype(np.float32).view(np.uint32))
+    assert np.abs(outs[0] - x[:, :2]).max() > 1e-3          # clicks were repaired: not a pass-through comparison

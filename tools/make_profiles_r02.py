@@ -15,7 +15,7 @@ CAPS = [
      "python bench.py --workload specstab --seconds 2 --steps 1 --warmup 3 --no-cpu --no-e2e --no-parity --no-f64", 4096 * 96000, "specstab"),
     ("r02_modtilt_fast", "modtilt_scan_fast", "Faust leaf ModTilt fp32, scan kernel with the MUFU forms of sqrt / div / log10 / 10^x (the default)",
      "python bench.py --workload modtilt --seconds 4 --steps 1 --warmup 3 --no-cpu --no-e2e --no-parity", None, "modtilt"),
-    ("r02_easyexpander", "easyexpander_split", "EasyExpander fp32 (`easyexpander_split_kernel`)",
+    ("r02_easyexpander", "easyexpander_v3", "EasyExpander fp32, v3 role pipeline (`easyexpander_v3_kernel`: 4 band warps, filter, G1, G2 and 14 active helper warps per CTA)",
      "python bench.py --workload cfg3 --seconds 2 --steps 1 --warmup 3 --no-cpu --no-e2e --no-parity --no-f64 --subs ''", 4096 * 96000, "cfg3"),
     ("r02_cascade8", "cascade8_x2", "cascade8 fp32 (`cascade8_x2_kernel`)",
      "python bench.py --workload cfg2 --seconds 10 --steps 1 --warmup 3 --no-cpu --no-e2e --no-parity --no-f64", 1024 * 480000, "cfg2"),

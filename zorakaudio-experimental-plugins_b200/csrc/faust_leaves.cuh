@@ -121,47 +121,82 @@ struct Cbg {
         c.relHold = std::exp(std::log(1e-3f) / (holdN + eps));                                                                // :102
         c.range = c.err_thr * 3.0f;                                                                                           // :108
     }
-    // Savitzky-Golay predictors on delayed taps (:53-59), summed left to right; which = 0..3 -> SG-11 / 15 / 21 / 31
-    ZA_FL static float sg(const float* h, int pos, int which)
+    // Savitzky-Golay predictors on delayed taps (:53-59), summed left to right; which = 0..3 -> SG-11 / 15 / 21 / 31.
+    // `x(d)` = the input d frames ago (d = 0: the frame just pushed).  With `which` a compile-time constant after inlining
+    // the tap loop unrolls and the coefficients become immediates (the tiled kernel of p_faust.cu relies on that).
+    template <class X> ZA_FL static float sg(const X& x, int which)
     {
         const float c11[11] = {-36, 9, 44, 69, 84, 89, 84, 69, 44, 9, -36};
         const float c15[15] = {-78, -13, 42, 87, 122, 147, 162, 167, 162, 147, 122, 87, 42, -13, -78};
         const float c21[21] = {-171, -76, 9, 84, 149, 204, 249, 284, 309, 324, 329, 324, 309, 284, 249, 204, 149, 84, 9, -76, -171};
         const float c31[31] = {-406, -261, -126, -1, 114, 219, 314, 399, 474, 539, 594, 639, 674, 699, 714, 719, 714, 699, 674, 639, 594, 539,
                                474, 399, 314, 219, 114, -1, -126, -261, -406};
-        const float* c; int n, d0; float den;
-        switch (which) { case 0: c = c11; n = 11; d0 = 20; den = 429.0f; break; case 1: c = c15; n = 15; d0 = 22; den = 1105.0f; break;
-                         case 2: c = c21; n = 21; d0 = 25; den = 3059.0f; break; default: c = c31; n = 31; d0 = 30; den = 9889.0f; break; }
-        float acc = c[0] * h[(pos - d0) & 31];
-        for (int k = 1; k < n; ++k) acc = acc + (c[k] * h[(pos - (d0 - k)) & 31]);
-        return acc / den;
+        if (which == 0) {
+            float acc = c11[0] * x(20);
+#pragma unroll
+            for (int k = 1; k < 11; ++k) acc = acc + (c11[k] * x(20 - k));
+            return acc / 429.0f;
+        }
+        if (which == 1) {
+            float acc = c15[0] * x(22);
+#pragma unroll
+            for (int k = 1; k < 15; ++k) acc = acc + (c15[k] * x(22 - k));
+            return acc / 1105.0f;
+        }
+        if (which == 2) {
+            float acc = c21[0] * x(25);
+#pragma unroll
+            for (int k = 1; k < 21; ++k) acc = acc + (c21[k] * x(25 - k));
+            return acc / 3059.0f;
+        }
+        float acc = c31[0] * x(30);
+#pragma unroll
+        for (int k = 1; k < 31; ++k) acc = acc + (c31[k] * x(30 - k));
+        return acc / 9889.0f;
     }
-    ZA_FL static void frame(State& m, const Slow& c, const Konst&, const float* in, float* out)
+    // the feed-forward half of a frame (:83-98): centre taps, the two predictors per channel, the better one and its error
+    struct Pred { float xC_L, xC_R, pred_L, pred_R, e_norm; };
+    template <class XL, class XR> ZA_FL static Pred predict(const XL& xl, const XR& xr, int mode)
+    {
+        Pred p;
+        p.xC_L = xl(15); p.xC_R = xr(15);                                                              // :83-84
+        const float small_L = sg(xl, mode), small_R = sg(xr, mode);                                   // :86-87
+        const float large_L = sg(xl, mode + 1), large_R = sg(xr, mode + 1);                           // :88-89
+        const float eA = fmaxf(fabsf(p.xC_L - small_L), fabsf(p.xC_R - small_R)) / (fmaxf(fabsf(small_L), fabsf(small_R)) + 1e-6f);
+        const float eB = fmaxf(fabsf(p.xC_L - large_L), fabsf(p.xC_R - large_R)) / (fmaxf(fabsf(large_L), fabsf(large_R)) + 1e-6f);
+        const bool useA = eA <= eB;
+        p.pred_L = useA ? small_L : large_L; p.pred_R = useA ? small_R : large_R; p.e_norm = useA ? eA : eB;
+        return p;
+    }
+    // the recurrent half (:67-79, :100-115): detector high-pass, max-hold envelope, baseline, trigger hold, mix
+    struct Rec { float hpL, hpR, env, base, holdEnv; };
+    ZA_FL static void tail(Rec& m, const Slow& c, float inL, float inR, float L1, float R1, const Pred& p, float* out)
     {
         const float eps = 1e-12f, T = 1e-3f;
-        const float L1 = m.hL[m.pos & 31], R1 = m.hR[m.pos & 31];               // x@1
-        m.pos = (m.pos + 1) & 31;
-        m.hL[m.pos] = in[0]; m.hR[m.pos] = in[1];
-        m.hpL = ((in[0] - L1) * c.a) + (m.hpL * c.a);                           // :67
-        m.hpR = ((in[1] - R1) * c.a) + (m.hpR * c.a);
+        m.hpL = ((inL - L1) * c.a) + (m.hpL * c.a);                             // :67
+        m.hpR = ((inR - R1) * c.a) + (m.hpR * c.a);
         const float ehf = fmaxf(fabsf(m.hpL), fabsf(m.hpR));                    // :76
         m.env = fmaxf(m.env * c.env_rel, ehf);                                  // :77
         m.base = (m.env * c.base_a) + (m.base * (1.0f - c.base_a));             // :78-79
         const float ratio = m.env / (m.base + eps);
-        const float xC_L = m.hL[(m.pos - 15) & 31], xC_R = m.hR[(m.pos - 15) & 31];   // :83-84
-        const float small_L = sg(m.hL, m.pos, c.mode), small_R = sg(m.hR, m.pos, c.mode);             // :86-87
-        const float large_L = sg(m.hL, m.pos, c.mode + 1), large_R = sg(m.hR, m.pos, c.mode + 1);     // :88-89
-        const float eA = fmaxf(fabsf(xC_L - small_L), fabsf(xC_R - small_R)) / (fmaxf(fabsf(small_L), fabsf(small_R)) + 1e-6f);
-        const float eB = fmaxf(fabsf(xC_L - large_L), fabsf(xC_R - large_R)) / (fmaxf(fabsf(large_L), fabsf(large_R)) + 1e-6f);
-        const bool useA = eA <= eB;
-        const float pred_L = useA ? small_L : large_L, pred_R = useA ? small_R : large_R, e_norm = useA ? eA : eB;
-        const float trig = (ratio > c.ratio_thr && e_norm > c.err_thr) ? 1.0f : 0.0f;                   // :100
+        const float trig = (ratio > c.ratio_thr && p.e_norm > c.err_thr) ? 1.0f : 0.0f;                 // :100
         m.holdEnv = fmaxf(m.holdEnv * c.relHold, trig);                                                // :103-104
         const bool active = m.holdEnv > T;
-        const float mix_base = active ? clampf_((e_norm - c.err_thr) / (c.range + eps), 0.0f, 1.0f) : 0.0f;
+        const float mix_base = active ? clampf_((p.e_norm - c.err_thr) / (c.range + eps), 0.0f, 1.0f) : 0.0f;
         const float mix = mix_base * c.mix_max;
-        const float outL = (xC_L * (1.0f - mix)) + (pred_L * mix), outR = (xC_R * (1.0f - mix)) + (pred_R * mix);
-        out[0] = c.monitor ? outL - xC_L : outL; out[1] = c.monitor ? outR - xC_R : outR;
+        const float outL = (p.xC_L * (1.0f - mix)) + (p.pred_L * mix), outR = (p.xC_R * (1.0f - mix)) + (p.pred_R * mix);
+        out[0] = c.monitor ? outL - p.xC_L : outL; out[1] = c.monitor ? outR - p.xC_R : outR;
+    }
+    struct Ring32 { const float* h; int pos; ZA_FL float operator()(int d) const { return h[(pos - d) & 31]; } };
+    ZA_FL static void frame(State& m, const Slow& c, const Konst&, const float* in, float* out)
+    {
+        const float L1 = m.hL[m.pos & 31], R1 = m.hR[m.pos & 31];               // x@1
+        m.pos = (m.pos + 1) & 31;
+        m.hL[m.pos] = in[0]; m.hR[m.pos] = in[1];
+        const Pred p = predict(Ring32{m.hL, m.pos}, Ring32{m.hR, m.pos}, c.mode);
+        Rec r{m.hpL, m.hpR, m.env, m.base, m.holdEnv};
+        tail(r, c, in[0], in[1], L1, R1, p, out);
+        m.hpL = r.hpL; m.hpR = r.hpR; m.env = r.env; m.base = r.base; m.holdEnv = r.holdEnv;
     }
 };
 

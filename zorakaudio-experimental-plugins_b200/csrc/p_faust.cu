@@ -82,6 +82,181 @@ __global__ void __launch_bounds__(32) faust_leaf_kernel(const FaustArgs a, const
         for (int w = 0; w < kWords; ++w) a.state[(size_t)w * ns + s] = sw[w];
 }
 
+// ---- ClickBeGoneSG, tiled ---------------------------------------------------------------------------------------------------
+// The leaf's cost is its feed-forward half: two Savitzky-Golay predictors per channel on delayed taps (72 .. 104 multiply-adds
+// per frame), which the generic kernel above evaluates lane = stream out of a dynamically indexed 32-entry delay line in
+// local memory (one warp per SM at 4096 streams, ~12 000 cycles per frame).  Here one CTA = 32 streams, 8 FIR warps + 1
+// recurrence warp, software-pipelined over 32-frame tiles with one __syncthreads per tile:
+//   FIR warp w (lane = frame), streams 4w .. 4w + 3:  store the outputs of tile i - 2 | load the inputs of tile i into a
+//     128-frame shared-memory ring | predictors of tile i with compile-time taps (Cbg::predict, mode from the frame's row);
+//   recurrence warp (lane = stream): the detector high-pass, max-hold envelope, baseline, trigger hold and mix of tile i - 1
+//     (Cbg::tail), frame after frame.
+// Both halves are the SAME functions the generic kernel calls, in the same operation order, so the outputs and the state rows
+// (delay-line ring included: same entries at the same indices) are bit-identical to the generic kernel's.
+namespace cbg {
+constexpr int kFirWarps = 8, kThreads = (kFirWarps + 1) * 32;
+constexpr int kRing = 128, kRingP = 2 * kRing + 1;      // [stream][ch][128 frames] + 1: conflict-free for lane = frame and lane = stream
+constexpr int kTP = 33;                                 // [stream][frame] tiles
+struct Smem {
+    float ring[32 * kRingP];
+    float fir[2][5][32 * kTP];                          // xC_L, xC_R, pred_L, pred_R, e_norm of a tile
+    float out[2][2][32 * kTP];
+};
+struct RingX { const float* row; int n; __device__ __forceinline__ float operator()(int d) const { return row[(n - d) & (kRing - 1)]; } };
+}  // namespace cbg
+
+__global__ void __launch_bounds__(cbg::kThreads) cbg_tiled_kernel(const FaustArgs a)
+{
+    using L = faust::Cbg;
+    using namespace cbg;
+    extern __shared__ __align__(16) unsigned char cbg_smem_raw[];
+    Smem& sm = *reinterpret_cast<Smem*>(cbg_smem_raw);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, s0 = blockIdx.x * 32;
+    const size_t ns = (size_t)a.n_streams;
+    const int n_cta = min(32, a.n_streams - s0);
+    const L::Slow* rows = reinterpret_cast<const L::Slow*>(a.slow);
+    const int64_t n = a.n_frames;
+    const int n_tiles = (int)((n + 31) / 32);
+    // State words (faust::Cbg::State): hL[32] 0..31, hR[32] 32..63, pos 64, hpL 65, hpR 66, env 67, base 68, holdEnv 69
+    if (warp < kFirWarps) {
+        int pos0[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {                    // frames -1 - d (d = lane) of the call = delay-line entry (pos - d) & 31
+            const int si = warp * 4 + q;
+            pos0[q] = 0;
+            if (si < n_cta) {
+                const size_t s = (size_t)(s0 + si);
+                pos0[q] = (int)a.state[64 * ns + s] & 31;
+                float* r = sm.ring + si * kRingP;
+                r[(-1 - lane) & (kRing - 1)] = __uint_as_float(a.state[(size_t)((pos0[q] - lane) & 31) * ns + s]);
+                r[kRing + ((-1 - lane) & (kRing - 1))] = __uint_as_float(a.state[(size_t)(32 + ((pos0[q] - lane) & 31)) * ns + s]);
+            }
+        }
+        __syncwarp();
+        for (int i = 0; i < n_tiles + 2; ++i) {
+            if (i >= 2) {                                // outputs of tile i - 2
+                const int t = i - 2;
+                const int64_t nn = (int64_t)t * 32 + lane;
+                if (nn < n) {
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const int si = warp * 4 + q;
+                        if (si < n_cta) {
+                            float* o = a.out + (size_t)(s0 + si) * 2 * a.row_stride + nn;
+                            o[0] = sm.out[t & 1][0][si * kTP + lane];
+                            o[a.row_stride] = sm.out[t & 1][1][si * kTP + lane];
+                        }
+                    }
+                }
+            }
+            if (i < n_tiles) {
+                const int64_t f0 = (int64_t)i * 32, nn = f0 + lane;
+                const bool ok = nn < n;
+                const int rp = (int)(nn & (kRing - 1));
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int si = warp * 4 + q;
+                    if (si < n_cta) {
+                        const float* x = a.in + (size_t)(s0 + si) * 2 * a.row_stride + nn;
+                        float* r = sm.ring + si * kRingP;
+                        r[rp] = ok ? x[0] : 0.0f;
+                        r[kRing + rp] = ok ? x[a.row_stride] : 0.0f;
+                    }
+                }
+                __syncwarp();
+                // slider-rate row of this lane's frame (the last row persists)
+                const int64_t r0 = f0 % a.block_len;
+                int64_t blk = f0 / a.block_len;
+                if (r0 + 32 > a.block_len) blk = nn / a.block_len;
+                const size_t row = (size_t)(blk < a.n_rows ? blk : a.n_rows - 1) * ns;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int si = warp * 4 + q;
+                    if (si < n_cta) {
+                        const float* r = sm.ring + si * kRingP;
+                        const RingX xl{r, rp}, xr{r + kRing, rp};
+                        const int mode = rows[row + s0 + si].mode;
+                        L::Pred p;
+                        if (mode == 0) p = L::predict(xl, xr, 0);
+                        else if (mode == 1) p = L::predict(xl, xr, 1);
+                        else p = L::predict(xl, xr, 2);
+                        float (*fo)[32 * kTP] = sm.fir[i & 1];
+                        const int o = si * kTP + lane;
+                        fo[0][o] = p.xC_L; fo[1][o] = p.xC_R; fo[2][o] = p.pred_L; fo[3][o] = p.pred_R; fo[4][o] = p.e_norm;
+                    }
+                }
+            }
+            __syncthreads();
+        }
+        // the delay line as the generic kernel leaves it: pos advanced by n, entry (pos - d) & 31 = frame n - 1 - d
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int si = warp * 4 + q;
+            if (si < n_cta) {
+                const size_t s = (size_t)(s0 + si);
+                const int pos = (int)((pos0[q] + n) & 31);
+                const float* r = sm.ring + si * kRingP;
+                const int rp = (int)((n - 1 - lane) & (kRing - 1));
+                a.state[(size_t)((pos - lane) & 31) * ns + s] = __float_as_uint(r[rp]);
+                a.state[(size_t)(32 + ((pos - lane) & 31)) * ns + s] = __float_as_uint(r[kRing + rp]);
+                if (lane == 0) a.state[64 * ns + s] = (unsigned)pos;
+            }
+        }
+    } else {
+        const bool live = lane < n_cta;
+        const size_t s = (size_t)(s0 + (live ? lane : 0));
+        L::Rec m{__uint_as_float(a.state[65 * ns + s]), __uint_as_float(a.state[66 * ns + s]), __uint_as_float(a.state[67 * ns + s]),
+                 __uint_as_float(a.state[68 * ns + s]), __uint_as_float(a.state[69 * ns + s])};
+        L::Slow c = rows[s];
+        int blk = 0;
+        int64_t blk_end = a.block_len;
+        const float* r = sm.ring + (live ? lane : 0) * kRingP;
+        for (int i = 0; i < n_tiles + 2; ++i) {
+            if (live && i >= 1 && i - 1 < n_tiles) {
+                const int t = i - 1;
+                const int64_t f0 = (int64_t)t * 32;
+                const int nv = (int)min((int64_t)32, n - f0);
+                float (*fi)[32 * kTP] = sm.fir[t & 1];
+                float (*fo)[32 * kTP] = sm.out[t & 1];
+                for (int f = 0; f < nv; ++f) {
+                    const int64_t nn = f0 + f;
+                    if (nn >= blk_end) {                 // a new host block: its slider-rate row (the last row persists)
+                        ++blk; blk_end += a.block_len;
+                        c = rows[(size_t)(blk < a.n_rows ? blk : a.n_rows - 1) * ns + s];
+                    }
+                    const int rp = (int)(nn & (kRing - 1)), rq = (int)((nn - 1) & (kRing - 1));
+                    const int o = lane * kTP + f;
+                    const L::Pred p{fi[0][o], fi[1][o], fi[2][o], fi[3][o], fi[4][o]};
+                    float ov[2];
+                    L::tail(m, c, r[rp], r[kRing + rp], r[rq], r[kRing + rq], p, ov);
+                    fo[0][o] = ov[0]; fo[1][o] = ov[1];
+                }
+            }
+            __syncthreads();
+        }
+        if (live) {
+            a.state[65 * ns + s] = __float_as_uint(m.hpL); a.state[66 * ns + s] = __float_as_uint(m.hpR);
+            a.state[67 * ns + s] = __float_as_uint(m.env); a.state[68 * ns + s] = __float_as_uint(m.base);
+            a.state[69 * ns + s] = __float_as_uint(m.holdEnv);
+        }
+    }
+}
+static_assert(sizeof(faust::Cbg::State) == 70 * 4, "cbg_tiled_kernel addresses the state words of faust::Cbg::State by number");
+
+template <class L> struct TiledLaunch { static int go(const FaustArgs&, cudaStream_t) { return 0; } };        // 0 = no tiled kernel for this leaf
+template <> struct TiledLaunch<faust::Cbg> {
+    static int go(const FaustArgs& a, cudaStream_t st)
+    {
+        static DeviceOnce attr_once;
+        if (attr_once.pending()) {
+            if (!cuda_ok(cudaFuncSetAttribute(cbg_tiled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(cbg::Smem)), "ClickBeGoneSG smem attr")) return -1;
+            attr_once.mark();
+        }
+        cbg_tiled_kernel<<<(unsigned)((a.n_streams + 31) / 32), cbg::kThreads, sizeof(cbg::Smem), st>>>(a);
+        return cuda_ok(cudaGetLastError(), "cbg_tiled_kernel") ? 1 : -1;
+    }
+};
+
 template <class L>
 class FaustLeaf : public PluginImpl {
     typename L::Konst k_{};
@@ -154,8 +329,12 @@ public:
         if (n <= 0) return true;
         FaustArgs a{in, out, stride, n, I.n_streams, I.block_len, nbq, d_slow, d_state};
         const bool timed = I.time_begin();
-        faust_leaf_kernel<L><<<(unsigned)((I.n_streams + 31) / 32), 32, 0, I.stream>>>(a, k_);
-        if (!cuda_ok(cudaGetLastError(), "faust_leaf_kernel")) return false;
+        const int tiled = I.opt_scalar_f32 ? 0 : TiledLaunch<L>::go(a, I.stream);      // option scalar_f32 = 1: the generic kernel for every leaf
+        if (tiled < 0) return false;
+        if (!tiled) {
+            faust_leaf_kernel<L><<<(unsigned)((I.n_streams + 31) / 32), 32, 0, I.stream>>>(a, k_);
+            if (!cuda_ok(cudaGetLastError(), "faust_leaf_kernel")) return false;
+        }
         if (timed) I.time_end();
         ++I.launches;
         return true;
