@@ -5,6 +5,8 @@
 // without -double); compiled with -fmad=false (za_gpu/build.py) so the .dsp's operation order is not contracted.
 //   * kernel: one warp per CTA, lane = stream, state in registers / local memory for the whole call; audio moves as
 //     [channels x 32 streams] x 32-frame tiles through shared memory so HBM sees 128-byte row segments (in == out legal);
+//     the next tile arrives by cp.async while the current one is computed (with one warp per SM a plain load loop paid a
+//     full memory latency per row: 192 rows per tile for the six-channel RED);
 //   * slider-rate values (Faust's fSlow expressions) are evaluated on the HOST with the host libm once per (host block,
 //     stream) whose zone values changed, uploaded as rows;
 //   * zones: the quantised value narrowed to float (FaustJuceProcessor.cpp:467-471).
@@ -35,24 +37,47 @@ __global__ void __launch_bounds__(32) faust_leaf_kernel(const FaustArgs a, const
 {
     constexpr int kCh = L::kIn > L::kOut ? L::kIn : L::kOut;
     constexpr int kWords = (int)(sizeof(typename L::State) / 4);
-    __shared__ float tile[kCh * 32 * kP];
+    constexpr int kTile = kCh * 32 * kP;
+    extern __shared__ __align__(16) float faust_tiles[];        // two tiles: the next one arrives by cp.async while this one is computed
     const int lane = threadIdx.x, s0 = blockIdx.x * 32, s = s0 + lane;
     const bool live = s < a.n_streams;
     const size_t ns = (size_t)a.n_streams;
     typename L::State st;
     unsigned* sw = reinterpret_cast<unsigned*>(&st);
-#pragma unroll 1
+    // small states: fully unrolled word copies, so every access to `st` has a constant index and it lives in registers
+    // (a rolled loop takes its address and pins the whole struct to local memory)
+    constexpr int kUnroll = kWords <= 48 ? kWords : 1;
+#pragma unroll kUnroll
     for (int w = 0; w < kWords; ++w) sw[w] = live ? a.state[(size_t)w * ns + s] : 0u;
     const typename L::Slow* rows = reinterpret_cast<const typename L::Slow*>(a.slow);
     typename L::Slow c = rows[live ? s : 0];
     int blk = 0;
     int64_t blk_end = a.block_len;
-    for (int64_t f0 = 0; f0 < a.n_frames; f0 += 32) {
+    // row q of the CTA: stream q / kIn, channel q % kIn; lane = frame.  One 4-byte cp.async per element (the tile pitch of 33
+    // keeps lane = stream accesses conflict-free, so rows are not 16-byte aligned); frames past the call are zero-filled.
+    auto fetch = [&](int64_t f0, float* tile) {
         const int nv = (int)min((int64_t)32, a.n_frames - f0);
-        for (int q = 0; q < 32 * L::kIn; ++q) {                 // row q of the CTA: stream q / kIn, channel q % kIn; lane = frame
+        const int bytes = lane < nv ? 4 : 0;
+#pragma unroll 4
+        for (int q = 0; q < 32 * L::kIn; ++q) {
             const int si = q / L::kIn, ch = q - si * L::kIn;
-            const bool ok = s0 + si < a.n_streams && lane < nv;
-            tile[(ch * 32 + si) * kP + lane] = ok ? a.in[((size_t)(s0 + si) * L::kIn + ch) * a.row_stride + f0 + lane] : 0.0f;
+            const bool ok = s0 + si < a.n_streams;
+            const float* src = a.in + ((size_t)(s0 + (ok ? si : 0)) * L::kIn + ch) * a.row_stride + (bytes ? f0 + lane : 0);
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"((uint32_t)__cvta_generic_to_shared(tile + (ch * 32 + si) * kP + lane)),
+                         "l"(src), "r"(ok ? bytes : 0) : "memory");
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    if (a.n_frames > 0) fetch(0, faust_tiles);
+    int buf = 0;
+    for (int64_t f0 = 0; f0 < a.n_frames; f0 += 32, buf ^= 1) {
+        const int nv = (int)min((int64_t)32, a.n_frames - f0);
+        float* tile = faust_tiles + buf * kTile;
+        if (f0 + 32 < a.n_frames) {
+            fetch(f0 + 32, faust_tiles + (buf ^ 1) * kTile);     // in == out is legal: those frames are stored two iterations from now
+            asm volatile("cp.async.wait_group 1;" ::: "memory");
+        } else {
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
         }
         __syncwarp();
         if (live) {
@@ -70,6 +95,7 @@ __global__ void __launch_bounds__(32) faust_leaf_kernel(const FaustArgs a, const
             }
         }
         __syncwarp();
+#pragma unroll 4
         for (int q = 0; q < 32 * L::kOut; ++q) {
             const int si = q / L::kOut, ch = q - si * L::kOut;
             if (s0 + si < a.n_streams && lane < nv)
@@ -78,8 +104,21 @@ __global__ void __launch_bounds__(32) faust_leaf_kernel(const FaustArgs a, const
         __syncwarp();
     }
     if (live)
-#pragma unroll 1
+#pragma unroll kUnroll
         for (int w = 0; w < kWords; ++w) a.state[(size_t)w * ns + s] = sw[w];
+}
+
+template <class L> bool launch_generic(const FaustArgs& a, const typename L::Konst& k, cudaStream_t st)
+{
+    constexpr int kCh = L::kIn > L::kOut ? L::kIn : L::kOut;
+    constexpr size_t smem = (size_t)2 * kCh * 32 * kP * sizeof(float);
+    static DeviceOnce attr_once;
+    if (smem > 48 * 1024 && attr_once.pending()) {
+        if (!cuda_ok(cudaFuncSetAttribute(faust_leaf_kernel<L>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "Faust leaf smem attr")) return false;
+        attr_once.mark();
+    }
+    faust_leaf_kernel<L><<<(unsigned)((a.n_streams + 31) / 32), 32, smem, st>>>(a, k);
+    return cuda_ok(cudaGetLastError(), "faust_leaf_kernel");
 }
 
 // ---- ClickBeGoneSG, tiled ---------------------------------------------------------------------------------------------------
@@ -332,8 +371,7 @@ public:
         const int tiled = I.opt_scalar_f32 ? 0 : TiledLaunch<L>::go(a, I.stream);      // option scalar_f32 = 1: the generic kernel for every leaf
         if (tiled < 0) return false;
         if (!tiled) {
-            faust_leaf_kernel<L><<<(unsigned)((I.n_streams + 31) / 32), 32, 0, I.stream>>>(a, k_);
-            if (!cuda_ok(cudaGetLastError(), "faust_leaf_kernel")) return false;
+            if (!launch_generic<L>(a, k_, I.stream)) return false;
         }
         if (timed) I.time_end();
         ++I.launches;
