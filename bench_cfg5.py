@@ -40,6 +40,8 @@ PHASE_B = {"SOMA"}
 # 505-520 ms for the plain two-phase schedule -- ClickBeGoneSG's delay lines live off the L1 too and it slows down from
 # ~290 to 410-495 ms while SOMA runs beside it.  Default: sched=0.
 LONG_POLE = {"ClickBeGoneSG"}
+# `--option sched=2`: the stream-per-thread Faust leaves with small tiles (VAR, RED) keep SOMA company in phase B
+PHASE_B_WIDE = {"SOMA", "VAR", "RED"}
 LAUNCH_FIRST = ["ClickBeGoneSG", "RTT", "RED", "ATTACK", "VAR"]
 TOTAL_STREAMS = 65536
 FAUST = {"VAR", "ModTilt", "ClickBeGoneSG", "GTS", "RED"}
@@ -100,22 +102,23 @@ def run(args, ctx, sub=False):
     # launch order inside phase A: the long latency-bound kernels first (they hold one or two warps per SM for the whole
     # phase), the short bandwidth-heavy hand-written kernels after them
     order = sorted(jobs, key=lambda j: LAUNCH_FIRST.index(j["key"]) if j["key"] in LAUNCH_FIRST else len(LAUNCH_FIRST)) if sched else jobs
-    free = LONG_POLE if sched else set()
-    sa = [j["st"] for j in jobs if j["key"] not in PHASE_B and j["key"] not in free]
-    sb = [j["st"] for j in jobs if j["key"] in PHASE_B]
+    free = LONG_POLE if sched == 1 else set()
+    phase_b = PHASE_B_WIDE if sched == 2 else PHASE_B
+    sa = [j["st"] for j in jobs if j["key"] not in phase_b and j["key"] not in free]
+    sb = [j["st"] for j in jobs if j["key"] in phase_b]
 
     def step():
         for a_ in sa:                                # phase A starts when the previous step's phase B is done
             for b_ in sb:
                 a_.wait_stream(b_)
         for j in order:
-            if j["key"] not in PHASE_B:
+            if j["key"] not in phase_b:
                 j["bp"].process(j["x"], out=j["y"])
         for b_ in sb:                                # phase B: after phase A, except the long pole, which it overlaps
             for a_ in sa:
                 b_.wait_stream(a_)
         for j in order:
-            if j["key"] in PHASE_B:
+            if j["key"] in phase_b:
                 j["bp"].process(j["x"], out=j["y"])
 
     main_stream = torch.cuda.current_stream()
