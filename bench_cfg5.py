@@ -42,6 +42,8 @@ PHASE_B = {"SOMA"}
 LONG_POLE = {"ClickBeGoneSG"}
 # `--option sched=2`: the stream-per-thread Faust leaves with small tiles (VAR, RED) keep SOMA company in phase B
 PHASE_B_WIDE = {"SOMA", "VAR", "RED"}
+# `--option sched=3`: the compute-bound scan kernels (small shared-memory footprint) fill the shadow of SOMA instead
+PHASE_B_SCAN = {"SOMA", "ERBTilt", "SpectralStabilizer", "ModTilt"}
 LAUNCH_FIRST = ["ClickBeGoneSG", "RTT", "RED", "ATTACK", "VAR"]
 TOTAL_STREAMS = 65536
 FAUST = {"VAR", "ModTilt", "ClickBeGoneSG", "GTS", "RED"}
@@ -77,7 +79,7 @@ def run(args, ctx, sub=False):
         bp = za_gpu.BatchProcessor(key, per_leaf, SRATE, 512, p_leaf, local)
         bp.set_stream(st.cuda_stream)
         for ov in getattr(args, "option", None) or []:          # --option Leaf:name=value (experiments on one leaf of the mix)
-            if ov.startswith(key + ":"):
+            if ov.startswith(key + ":") or ov.startswith("*:"):
                 name, val = ov.split(":", 1)[1].split("=")
                 bp.set_option(name, int(val))
         first = (rank * len(leaves) + li) * per_leaf            # absolute stream numbers of this leaf's shard
@@ -103,7 +105,7 @@ def run(args, ctx, sub=False):
     # phase), the short bandwidth-heavy hand-written kernels after them
     order = sorted(jobs, key=lambda j: LAUNCH_FIRST.index(j["key"]) if j["key"] in LAUNCH_FIRST else len(LAUNCH_FIRST)) if sched else jobs
     free = LONG_POLE if sched == 1 else set()
-    phase_b = PHASE_B_WIDE if sched == 2 else PHASE_B
+    phase_b = PHASE_B_WIDE if sched == 2 else (PHASE_B_SCAN if sched == 3 else PHASE_B)
     sa = [j["st"] for j in jobs if j["key"] not in phase_b and j["key"] not in free]
     sb = [j["st"] for j in jobs if j["key"] in phase_b]
 

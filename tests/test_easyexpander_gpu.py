@@ -200,3 +200,32 @@ def test_fp32_v3_chunked_call_is_bit_identical(gpu, ref):
         parts.append(bp.process(np.ascontiguousarray(x[:, :, b0 * 512:b1 * 512]), params=np.ascontiguousarray(p[b0:b1])))
     bp.close()
     assert np.array_equal(np.concatenate(parts, axis=2), whole)
+
+
+def test_detector_filter_sliders_move_inside_a_call_on_the_device_path(gpu, ref):
+    """All five sliders automated per block, the detector HPF / LPF frequencies included (the only @slider inputs that go
+    through exp(): their coefficients come from per-grid-value tables made with the host libm).  The call must stay on the
+    device parameter path (two launches: parameter kernel + render) and match the reference like any other render:
+    fp64 <= 1e-12 of level, the hysteresis flag exact; fp32 below -100 dBFS."""
+    ns, nf = 19, 512 * 60 + 77
+    x = wl.programme_bursts(ns, nf)
+    nb = (nf + 511) // 512
+    base = np.array([s["default"] for s in ref.sliders], np.float32)
+    base[3], base[4] = 120.0, 6000.0
+    p = wl.automation(ref.sliders, nb, ns, which=[0, 1, 2, 3, 4], base=base)
+    p[5:9, :, 3] = 0.0                                   # HPF off for a few blocks (hpf_on toggles), off-grid values elsewhere
+    p[11, :, 4] = 20000.0                                # LPF off for one block
+    assert len(np.unique(p[:, 0, 3])) > 10 and len(np.unique(p[:, 0, 4])) > 10
+    y, yd, v = ref.render(p, x, want_f64=True, want_vars=True)
+    bp = gpu.BatchProcessor("EasyExpander", ns, precision="f64").prepare(p[0])
+    tap = np.zeros_like(yd)
+    l0 = bp.launch_count()
+    bp.process(x, tap64=tap, params=p)
+    assert bp.launch_count() - l0 == 2                   # not the host coefficient path (one launch), not one launch per block
+    assert rel_err(tap, yd).max() <= TOL64
+    assert np.array_equal(bp.read_state("expanding"), v["expanding"])
+    bp.close()
+    bp = gpu.BatchProcessor("EasyExpander", ns, precision="f32").prepare(p[0])
+    out = bp.process(x, params=p)
+    assert max(dbfs_rms(out[s].astype(np.float64) - yd[s]) for s in range(ns)) < -100.0
+    bp.close()

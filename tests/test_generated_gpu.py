@@ -305,3 +305,32 @@ def test_every_fft_hook_on_the_device(gpu, log2n):
         d = np.abs(tap - yd).max() / np.abs(yd).max()
         assert d <= (0.0 if mode == 5 else 5e-15), (mode, d)
         bp.close()
+
+
+@pytest.mark.parametrize("key,prec", [("RTT", "f64"), ("ATTACK", "f64"), ("SOMA", "f32")])
+def test_streams_per_warp_does_not_change_a_bit(gpu, key, prec):
+    """jsfx_process_kernel with 8 / 16 / 32 streams per warp (option lanes_per_warp): the per-stream arithmetic is the same thread code, so outputs and state are identical
+    bits for every choice, partial last warps included; the 32-lane render is the one checked against the reference."""
+    ref = zo.RefPlugin(key)
+    ns, nf = 45, 6000 + 13
+    p, x = make_case(ref, ns, nf, True)
+    _, yd, vref = ref.render(p, x, want_f64=True, want_vars=True)
+    names = list(vref)[:6]
+    outs = {}
+    for lanes in (32, 16, 8):
+        bp = gpu.BatchProcessor(key, ns, precision=prec).prepare(p[0])
+        bp.set_option("lanes_per_warp", lanes)
+        tap = np.zeros_like(yd) if prec == "f64" else None
+        out = bp.process(x, tap64=tap, params=p)
+        outs[lanes] = (out, tap, {n: bp.read_state(n) for n in names})
+        bp.close()
+    if prec == "f64":
+        assert rel_err(outs[32][1], yd).max() <= TOL64
+    else:
+        assert max(dbfs_rms(outs[32][0][s].astype(np.float64) - yd[s]) for s in range(ns)) < -100.0
+    for lanes in (16, 8):
+        assert np.array_equal(outs[lanes][0].view(np.uint32), outs[32][0].view(np.uint32)), lanes
+        if prec == "f64":
+            assert np.array_equal(outs[lanes][1].view(np.uint64), outs[32][1].view(np.uint64)), lanes
+        for n, v in outs[32][2].items():
+            assert np.array_equal(outs[lanes][2][n], v, equal_nan=True), (lanes, n)

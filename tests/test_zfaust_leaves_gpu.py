@@ -120,3 +120,25 @@ def test_clickbegonesg_tiled_kernel_is_bit_identical_to_the_generic_kernel(gpu, 
     assert np.array_equal(states[0][:64].astype(np.float32).view(np.uint32), states[1][:64].astype(np.float32).view(np.uint32))
     assert np.array_equal(states[0][65:].astype(np.float32).view(np.uint32), states[1][65:].astype(np.float32).view(np.uint32))
     assert np.abs(outs[0] - x[:, :2]).max() > 1e-3          # clicks were repaired: not a pass-through comparison
+
+
+@pytest.mark.parametrize("key", ["VAR", "RED"])
+def test_generic_kernel_streams_per_warp_does_not_change_a_bit(gpu, key):
+    """faust_leaf_kernel with 8 / 16 / 32 streams per warp (option lanes_per_warp): identical bits,
+    partial last warps and CTAs included."""
+    port = zo.PortPlugin(key)
+    ns, nf, block = 45, 6000 + 13, 512
+    x = make_input(key, port, ns, nf)
+    base = np.array([s["default"] for s in port.sliders], np.float32)
+    p = wl.automation(port.sliders, (nf + block - 1) // block, ns, which=[0, 1, 2], base=base)
+    y, _ = port.render(p, x, block=block)
+    outs = {}
+    for lanes in (32, 16, 8):
+        bp = gpu.BatchProcessor(key, ns, 48000.0, block, "f32").prepare(p[0])
+        bp.set_option("lanes_per_warp", lanes)
+        outs[lanes] = (bp.process(x, params=p), np.stack([bp.read_state(f"state[{k}]") for k in range(8)]))
+        bp.close()
+    assert dbfs_rms(outs[32][0].astype(np.float64) - y) < -100.0
+    for lanes in (16, 8):
+        assert np.array_equal(outs[lanes][0].view(np.uint32), outs[32][0].view(np.uint32)), lanes
+        assert np.array_equal(outs[lanes][1], outs[32][1], equal_nan=True), lanes

@@ -1,11 +1,6 @@
 mkdir -p gpurun_out
-for w in 1 2 4; do for nb in 1 2; do
-  echo -n "cascade8 warps=$w nbuf=$nb: "
-  timeout 120 python bench.py --workload cfg2 --seconds 30 --steps 3 --warmup 3 --no-cpu --no-e2e --no-f64 --no-parity --warps $w --option tile_buffers=$nb 2>&1 | grep -o '"kernel_ms_per_launch": [0-9.]*\|unknown\|error[^"]*' | head -2 | tr '\n' ' '; echo
-done; done
-for o in sched=0 sched=2 sched=0 sched=2; do
-python bench.py --workload cfg5 --steps 6 --warmup 3 --no-cpu --no-e2e --no-parity --option $o > gpurun_out/r02p_cfg5.json 2>gpurun_out/r02p_cfg5.err; python - <<PY
-import json; d=json.loads(open('gpurun_out/r02p_cfg5.json').read().strip().splitlines()[-1]); print('$o', round(d['ms_per_step'],1), {k:round(v,1) for k,v in d['roofline']['per_leaf_kernel_ms'].items()})
-PY
-done
-TAG=r02p tools/gpu_run.sh smoke
+TAG=r02r PYTEST_ARGS="--maxfail=5" tools/gpu_run.sh tests
+# launch list of the benched command (after it exited 0 without ncu in this same call)
+python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/r02r_plain.json 2> gpurun_out/r02r_plain.err || exit 1
+ncu --metrics gpu__time_duration.sum --clock-control none -c 2500 --csv --log-file gpurun_out/r02_bench_launches.csv python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/r02r_ncu.json 2> gpurun_out/r02r_ncu.err
+echo "ncu rc=$?"; wc -l gpurun_out/r02_bench_launches.csv

@@ -48,6 +48,7 @@ struct GenLaunch {
     const double* q; const int* decl_index0;
     void* state; void* mem; unsigned* mt; int* err; double srate;
     int64_t fft_scratch; const double* tw;
+    int lanes;
 };
 }
 #else
@@ -498,18 +499,22 @@ __device__ __forceinline__ void cp_async4(float* smem_dst, const float* gmem_src
 }
 
 template <class S, typename R, bool TAP>
-__global__ void __launch_bounds__(32 * GenWarps<S>::value, 1) jsfx_process_kernel(const GenLaunch a)
+__global__ void __launch_bounds__(128, 1) jsfx_process_kernel(const GenLaunch a)
 {
     // Audio tiles, [2 buffers][kCh][32 streams][kF frames + 1]: the tile after the one being computed is already on
     // its way from HBM (cp.async), so the only warp of the SM does not sit out a DRAM latency per tile (ncu, profiles/
     // r01_generic_rtt_ncu.md: 26 % of the samples were the tile-in stores waiting for their loads).  kF: see TileFrames.
     extern __shared__ float tiles_cta[];
-    constexpr int kF = TileFrames<S>::value, kP = kF + 1, kTile = S::kCh * 32 * kP, kRows = 32 / kF;   // rows per copy instruction
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, s0 = (blockIdx.x * GenWarps<S>::value + warp) * 32, s = s0 + lane;
+    // Streams per warp L = a.lanes (8, 16 or 32): a stream's @sample is one long dependent chain, so a warp with 8 busy
+    // lanes runs as fast as one with 32; at a few thousand streams the host spreads them over 4x as many warps (one per SM
+    // scheduler instead of one per SM).  All 32 lanes move the audio tiles either way.
+    constexpr int kF = TileFrames<S>::value, kP = kF + 1, kRows = 32 / kF;   // rows per copy instruction
+    const int L = a.lanes, kTile = S::kCh * L * kP;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, s0 = (blockIdx.x * (blockDim.x >> 5) + warp) * L, s = s0 + lane;
     if (s0 >= a.n_streams) return;                 // the warps of a CTA never synchronise with each other
     float* const tiles = tiles_cta + warp * 2 * kTile;
-    const bool live = s < a.n_streams;             // dead lanes only help move the audio tiles
-    const int ns_cta = min(32, a.n_streams - s0);
+    const bool live = lane < L && s < a.n_streams; // dead lanes only help move the audio tiles
+    const int ns_cta = min(L, a.n_streams - s0);
     const int half = lane / kF, fl = lane % kF;    // tile I/O: kF lanes per row, lane = frame
     Rt<R> c;
     R v[S::kVars];
@@ -524,7 +529,7 @@ __global__ void __launch_bounds__(32 * GenWarps<S>::value, 1) jsfx_process_kerne
         const float* src = a.in + (size_t)s0 * S::kIn * a.row_stride + frame0 + (fl < nf ? fl : 0);
         for (int q0 = 0; q0 < nq; q0 += kRows) {
             const int q = q0 + half;
-            if (q < nq) cp_async4(tile + ((q % S::kIn) * 32 + q / S::kIn) * kP + fl, src + (size_t)q * a.row_stride, fl < nf);
+            if (q < nq) cp_async4(tile + ((q % S::kIn) * L + q / S::kIn) * kP + fl, src + (size_t)q * a.row_stride, fl < nf);
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
     };
@@ -563,12 +568,12 @@ __global__ void __launch_bounds__(32 * GenWarps<S>::value, 1) jsfx_process_kerne
             if (live) {
                 for (int f = 0; f < nf; ++f) {
 #pragma unroll
-                    for (int ch = 0; ch < S::kCh; ++ch) c.spl[ch] = ch < S::kIn ? (R)tile[(ch * 32 + lane) * kP + f] : (R)0;
+                    for (int ch = 0; ch < S::kCh; ++ch) c.spl[ch] = ch < S::kIn ? (R)tile[(ch * L + lane) * kP + f] : (R)0;
                     S::template sample<R>(c, v);
 #pragma unroll
                     for (int ch = 0; ch < S::kOut; ++ch) {
                         if (TAP) a.tap[((size_t)s * S::kOut + ch) * a.row_stride + pos + f0 + f] = (double)c.spl[ch];
-                        tile[(ch * 32 + lane) * kP + f] = (float)c.spl[ch];
+                        tile[(ch * L + lane) * kP + f] = (float)c.spl[ch];
                     }
                 }
             }
@@ -579,7 +584,7 @@ __global__ void __launch_bounds__(32 * GenWarps<S>::value, 1) jsfx_process_kerne
 #pragma unroll 4
                 for (int q0 = 0; q0 < nq; q0 += kRows) {
                     const int q = q0 + half;
-                    if (q < nq && fl < nf) dst[(size_t)q * a.row_stride] = tile[((q % S::kOut) * 32 + q / S::kOut) * kP + fl];
+                    if (q < nq && fl < nf) dst[(size_t)q * a.row_stride] = tile[((q % S::kOut) * L + q / S::kOut) * kP + fl];
                 }
             }
             __syncwarp();
@@ -600,9 +605,21 @@ template <class S> bool launch_prepare(const GenLaunch& a, int precision, cudaSt
 }
 template <class S> bool launch_process(const GenLaunch& a, int precision, cudaStream_t st)
 {
-    constexpr int kGenWarps = GenWarps<S>::value;
-    const int blocks = (a.n_streams + 32 * kGenWarps - 1) / (32 * kGenWarps);
-    const size_t smem = (size_t)kGenWarps * 2 * S::kCh * 32 * (TileFrames<S>::value + 1) * sizeof(float);
+    // Streams per warp and warps per CTA.  Leaves with a mem[] heap keep single-warp CTAs (GenWarps above: their hot lines
+    // live in L1); heap-less leaves keep four warps per CTA whenever their tiles fit.  Streams per warp: 32 unless the caller
+    // asks for 16 or 8 (option "lanes_per_warp").  Measured on B200: spreading 4096 streams over 4x as many warps gains 7 %
+    // (VAR) to 17 % (RTT) when the handle has the GPU to itself -- the translated code is instruction-fetch bound as much as
+    // latency bound -- and LOSES 15 % in the concurrent cfg5 mix (a warp with 8 live lanes costs a full issue slot), so it
+    // is not the default.
+    GenLaunch b = a;
+    int L = a.lanes, W = GenWarps<S>::value;
+    auto smem_of = [&](int w, int l) { return (size_t)w * 2 * S::kCh * l * (TileFrames<S>::value + 1) * sizeof(float); };
+    if (L != 8 && L != 16) L = 32;
+    if (S::kMemSlots == 0) { W = 4; while (W > 1 && smem_of(W, L) > 160 * 1024) W >>= 1; }
+    b.lanes = L;
+    const int kGenWarps = W;
+    const int blocks = (a.n_streams + L * kGenWarps - 1) / (L * kGenWarps);
+    const size_t smem = smem_of(W, L);
     auto go = [&](auto kern) {
         if (smem > 48 * 1024 && !cuda_ok(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "jsfx_process_kernel smem attr")) return false;
         // Leaves with a heap live off the L1 (their hot mem[] lines; SpectralStabilizer ~34 KB per warp).  Left alone, the
@@ -610,7 +627,7 @@ template <class S> bool launch_process(const GenLaunch& a, int precision, cudaSt
         // 64 KB of L1: fine for 2 warps per SM, thrashing beyond (ncu at 16 384 streams: L1 hit rate 98.8 % -> 89.8 %,
         // long_scoreboard 2 % -> 31 %, 2.3x the time per frame).  Ask for a 100 KB carve-out instead: 5 CTAs per SM, 128 KB L1 (64 KB / 3 CTAs measured too: see DESIGN.md 4.5).
         if (S::kMemSlots > 0 && !cuda_ok(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 44), "jsfx_process_kernel carve-out")) return false;
-        kern<<<blocks, 32 * kGenWarps, smem, st>>>(a);
+        kern<<<blocks, 32 * kGenWarps, smem, st>>>(b);
         return cuda_ok(cudaGetLastError(), "jsfx_process_kernel launch");
     };
     if (precision) return a.tap ? go(jsfx_process_kernel<S, double, true>) : go(jsfx_process_kernel<S, double, false>);

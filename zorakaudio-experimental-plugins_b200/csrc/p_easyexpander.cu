@@ -89,6 +89,9 @@ struct EEParamArgs {
     EECoef* out;               // [nb][ns]
     int nb, ns;
     SliderQ q[5];
+    const double* tab_hpf;     // 1 - exp(-2 pi f / srate) for every grid value of the detector HPF slider (host libm), or null
+    const double* tab_lpf;     // the same for the detector LPF slider
+    int n_hpf, n_lpf;
 };
 
 // One thread per (block, stream): quantise threshold / depth / contour exactly as the host does and derive the
@@ -105,6 +108,15 @@ __global__ void ee_param_kernel(const EEParamArgs a)
     const double cont = __ddiv_rn(quantise_dev(a.q[2], p[2]), 100.0);
     const double rb = __dadd_rn(1.5, __dmul_rn(2.5, cont));
     c.ratio_base = rb < 1.0 ? 1.0 : rb;
+    if (a.tab_hpf) {
+        // the detector-filter sliders may move inside the call: a quantised value is mn + k step for an integer k, and the
+        // table holds the host libm's coefficient for exactly that double (:169-175), so this equals the host path bit for bit
+        const double fh = quantise_dev(a.q[3], p[3]), fl = quantise_dev(a.q[4], p[4]);
+        int kh = (int)llround(__ddiv_rn(__dsub_rn(fh, a.q[3].mn), a.q[3].step)), kl = (int)llround(__ddiv_rn(__dsub_rn(fl, a.q[4].mn), a.q[4].step));
+        kh = kh < 0 ? 0 : (kh >= a.n_hpf ? a.n_hpf - 1 : kh); kl = kl < 0 ? 0 : (kl >= a.n_lpf ? a.n_lpf - 1 : kl);
+        c.hpf_on = fh > 0.0; c.hpf_c = c.hpf_on ? a.tab_hpf[kh] : 0.0;
+        c.lpf_on = fl < 20000.0; c.lpf_c = c.lpf_on ? a.tab_lpf[kl] : 0.0;
+    }
     a.out[i] = c;
 }
 
@@ -116,6 +128,8 @@ class EasyExpander : public PluginImpl {
     float* d_params = nullptr;        // raw automation rows of the current call
     size_t params_cap = 0;
     EECoef* d_per_stream = nullptr;
+    double* d_tab_hpf = nullptr; double* d_tab_lpf = nullptr;   // detector-filter coefficients per slider grid value (host libm)
+    int n_tab_hpf = 0, n_tab_lpf = 0;
     cudaEvent_t ev_params = nullptr, ev_consumed = nullptr;   // upload done / previous rows consumed
     cudaStream_t up_stream = nullptr; // uploads overlap the previous call's kernel
     int n_sm = 148;
@@ -123,7 +137,7 @@ class EasyExpander : public PluginImpl {
     bool coef_valid = false;
 
 public:
-    ~EasyExpander() override { cudaFree(d_state); cudaFree(d_coef); cudaFree(d_params); cudaFree(d_per_stream); if (ev_params) cudaEventDestroy(ev_params); if (ev_consumed) cudaEventDestroy(ev_consumed); if (up_stream) cudaStreamDestroy(up_stream); }
+    ~EasyExpander() override { cudaFree(d_state); cudaFree(d_coef); cudaFree(d_params); cudaFree(d_per_stream); cudaFree(d_tab_hpf); cudaFree(d_tab_lpf); if (ev_params) cudaEventDestroy(ev_params); if (ev_consumed) cudaEventDestroy(ev_consumed); if (up_stream) cudaStreamDestroy(up_stream); }
 
     bool create(Instance& I) override
     {
@@ -131,7 +145,40 @@ public:
         cudaDeviceProp prop;
         if (!cuda_ok(cudaGetDeviceProperties(&prop, I.device), "device properties")) return false;
         n_sm = prop.multiProcessorCount;
+        if (I.decls.size() == 5 && !build_filter_tables(I)) return false;
         return cuda_ok(cudaMalloc(&d_state, (size_t)I.n_streams * kEEState * sizeof(double)), "EasyExpander state");
+    }
+
+    // 1 - exp(-2 pi f / srate) for every value the detector HPF / LPF sliders can take after quantisation (20 001 + 19 981
+    // values), from the host's libm, so the device parameter path serves calls in which those sliders move (it used to hand
+    // the whole batch to the host path as soon as one stream moved one of them)
+    bool build_filter_tables(Instance& I)
+    {
+        double* dst[2] = {nullptr, nullptr};
+        int cnt[2] = {0, 0};
+        for (int t = 0; t < 2; ++t) {
+            const SliderDecl& d = I.decls[3 + t];
+            const double mn = (double)d.min, mx = (double)d.max, step = (double)(d.step > 0.0f ? d.step : 1.0f);
+            const int64_t n = (int64_t)std::llround((mx - mn) / step) + 1;
+            if (d.is_choice || n < 1 || n > (1 << 20)) return true;          // unusual declaration: keep the per-stream host path
+            std::vector<double> tab((size_t)n);
+            for (int64_t k = 0; k < n; ++k) {
+                double v = mn + (double)k * step;                            // quantise_slider's own expression
+                v = v < mn ? mn : (v > mx ? mx : v);
+                double sl[5] = {0.0, 0.0, 0.0, t == 0 ? v : 0.0, t == 1 ? v : 20000.0};
+                EECoef c;
+                ee_slider(sl, I.srate, c);
+                tab[(size_t)k] = t == 0 ? c.hpf_c : c.lpf_c;
+            }
+            if (!cuda_ok(cudaMalloc(&dst[t], tab.size() * sizeof(double)), "EasyExpander filter table") ||
+                !cuda_ok(cudaMemcpy(dst[t], tab.data(), tab.size() * sizeof(double), cudaMemcpyHostToDevice), "EasyExpander filter table upload")) {
+                cudaFree(dst[0]); cudaFree(dst[1]);
+                return false;
+            }
+            cnt[t] = (int)n;
+        }
+        d_tab_hpf = dst[0]; d_tab_lpf = dst[1]; n_tab_hpf = cnt[0]; n_tab_lpf = cnt[1];
+        return true;
     }
 
     bool reset(Instance& I) override   // @init: all state zero except det_db_m = -120 (:139-150)
@@ -202,16 +249,16 @@ public:
         return true;
     }
 
-    // Automation on the device: upload the raw float rows, quantise + derive there.  Applicable when the detector
-    // filter sliders (the only @slider inputs that go through exp()) do not move inside the call, so their
-    // coefficients come from the host's glibc once per stream and every value stays bit-identical to the host path.
+    // Automation on the device: upload the raw float rows, quantise + derive there.  The detector filter sliders (the only
+    // @slider inputs that go through exp()) take their coefficients from per-grid-value tables made with the host's glibc
+    // (build_filter_tables), so every value stays bit-identical to the host path whether or not they move inside the call.
     int run_blocks_raw(Instance& I, const float* params, int nb, const float* in, float* out, double* tap,
                        int64_t n, int64_t stride) override
     {
         const int ns = I.n_streams, nd = (int)I.decls.size();
         if (nd != 5) return 0;
         std::vector<uint8_t> moved(ns, 0);
-        parallel_for(ns, 64, [&](int64_t sb, int64_t se) {
+        if (!d_tab_hpf) parallel_for(ns, 64, [&](int64_t sb, int64_t se) {
             for (int64_t s = sb; s < se; ++s) {
                 const float h = params[(size_t)s * nd + 3], l = params[(size_t)s * nd + 4];
                 for (int b = 1; b < nb; ++b) {
@@ -220,7 +267,8 @@ public:
                 }
             }
         });
-        for (int s = 0; s < ns; ++s) if (moved[s]) return 0;
+        if (!d_tab_hpf)
+            for (int s = 0; s < ns; ++s) if (moved[s]) return 0;
         std::vector<EECoef> ps(ns);
         for (int s = 0; s < ns; ++s) {
             double sl[5];
@@ -254,6 +302,7 @@ public:
         cudaStreamWaitEvent(I.stream, ev_params, 0);
         EEParamArgs pa{};
         pa.params = d_params; pa.per_stream = d_per_stream; pa.out = d_coef; pa.nb = nb; pa.ns = ns;
+        pa.tab_hpf = d_tab_hpf; pa.tab_lpf = d_tab_lpf; pa.n_hpf = n_tab_hpf; pa.n_lpf = n_tab_lpf;
         for (int j = 0; j < 5; ++j) {
             const SliderDecl& d = I.decls[j];
             pa.q[j] = SliderQ{(double)d.min, (double)d.max, (double)(d.step > 0.0f ? d.step : 1.0f), d.is_choice ? 1 : 0};

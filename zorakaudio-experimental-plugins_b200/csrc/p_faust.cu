@@ -28,19 +28,26 @@ struct FaustArgs {
     int n_streams, block_len, n_rows;
     const void* slow;           // [n_rows][n_streams] Leaf::Slow
     unsigned* state;            // [words][n_streams]
+    int lanes;                  // generic kernel: streams per warp (8 / 16 / 32)
 };
 
 constexpr int kP = 33;
 
 template <class L>
-__global__ void __launch_bounds__(32) faust_leaf_kernel(const FaustArgs a, const typename L::Konst k)
+__global__ void __launch_bounds__(128) faust_leaf_kernel(const FaustArgs a, const typename L::Konst k)
 {
     constexpr int kCh = L::kIn > L::kOut ? L::kIn : L::kOut;
     constexpr int kWords = (int)(sizeof(typename L::State) / 4);
-    constexpr int kTile = kCh * 32 * kP;
-    extern __shared__ __align__(16) float faust_tiles[];        // two tiles: the next one arrives by cp.async while this one is computed
-    const int lane = threadIdx.x, s0 = blockIdx.x * 32, s = s0 + lane;
-    const bool live = s < a.n_streams;
+    // Four independent warps per CTA (they never synchronise with each other), SL = a.lanes streams per warp: a stream's
+    // frame() is one long dependent chain, so a warp with 8 busy lanes runs as fast as one with 32 and a few thousand
+    // streams are spread over 4x as many warps; all 32 lanes move the audio tiles.
+    const int SL = a.lanes, kTile = kCh * SL * kP;
+    extern __shared__ __align__(16) float faust_tiles_cta[];    // per warp two tiles: the next one arrives by cp.async while this one is computed
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, s0 = (blockIdx.x * (blockDim.x >> 5) + warp) * SL, s = s0 + lane;
+    if (s0 >= a.n_streams) return;
+    float* const faust_tiles = faust_tiles_cta + warp * 2 * kTile;
+    const bool live = lane < SL && s < a.n_streams;
+    const int n_w = min(SL, a.n_streams - s0);
     const size_t ns = (size_t)a.n_streams;
     typename L::State st;
     unsigned* sw = reinterpret_cast<unsigned*>(&st);
@@ -59,12 +66,11 @@ __global__ void __launch_bounds__(32) faust_leaf_kernel(const FaustArgs a, const
         const int nv = (int)min((int64_t)32, a.n_frames - f0);
         const int bytes = lane < nv ? 4 : 0;
 #pragma unroll 4
-        for (int q = 0; q < 32 * L::kIn; ++q) {
+        for (int q = 0; q < n_w * L::kIn; ++q) {
             const int si = q / L::kIn, ch = q - si * L::kIn;
-            const bool ok = s0 + si < a.n_streams;
-            const float* src = a.in + ((size_t)(s0 + (ok ? si : 0)) * L::kIn + ch) * a.row_stride + (bytes ? f0 + lane : 0);
-            asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"((uint32_t)__cvta_generic_to_shared(tile + (ch * 32 + si) * kP + lane)),
-                         "l"(src), "r"(ok ? bytes : 0) : "memory");
+            const float* src = a.in + ((size_t)(s0 + si) * L::kIn + ch) * a.row_stride + (bytes ? f0 + lane : 0);
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"((uint32_t)__cvta_generic_to_shared(tile + (ch * SL + si) * kP + lane)),
+                         "l"(src), "r"(bytes) : "memory");
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
     };
@@ -88,18 +94,18 @@ __global__ void __launch_bounds__(32) faust_leaf_kernel(const FaustArgs a, const
                 }
                 float iv[L::kIn], ov[L::kOut];
 #pragma unroll
-                for (int ch = 0; ch < L::kIn; ++ch) iv[ch] = tile[(ch * 32 + lane) * kP + f];
+                for (int ch = 0; ch < L::kIn; ++ch) iv[ch] = tile[(ch * SL + lane) * kP + f];
                 L::frame(st, c, k, iv, ov);
 #pragma unroll
-                for (int ch = 0; ch < L::kOut; ++ch) tile[(ch * 32 + lane) * kP + f] = ov[ch];
+                for (int ch = 0; ch < L::kOut; ++ch) tile[(ch * SL + lane) * kP + f] = ov[ch];
             }
         }
         __syncwarp();
 #pragma unroll 4
-        for (int q = 0; q < 32 * L::kOut; ++q) {
+        for (int q = 0; q < n_w * L::kOut; ++q) {
             const int si = q / L::kOut, ch = q - si * L::kOut;
-            if (s0 + si < a.n_streams && lane < nv)
-                a.out[((size_t)(s0 + si) * L::kOut + ch) * a.row_stride + f0 + lane] = tile[(ch * 32 + si) * kP + lane];
+            if (lane < nv)
+                a.out[((size_t)(s0 + si) * L::kOut + ch) * a.row_stride + f0 + lane] = tile[(ch * SL + si) * kP + lane];
         }
         __syncwarp();
     }
@@ -108,16 +114,16 @@ __global__ void __launch_bounds__(32) faust_leaf_kernel(const FaustArgs a, const
         for (int w = 0; w < kWords; ++w) a.state[(size_t)w * ns + s] = sw[w];
 }
 
-template <class L> bool launch_generic(const FaustArgs& a, const typename L::Konst& k, cudaStream_t st)
+template <class L> bool launch_generic(FaustArgs a, const typename L::Konst& k, cudaStream_t st)
 {
     constexpr int kCh = L::kIn > L::kOut ? L::kIn : L::kOut;
-    constexpr size_t smem = (size_t)2 * kCh * 32 * kP * sizeof(float);
-    static DeviceOnce attr_once;
-    if (smem > 48 * 1024 && attr_once.pending()) {
-        if (!cuda_ok(cudaFuncSetAttribute(faust_leaf_kernel<L>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "Faust leaf smem attr")) return false;
-        attr_once.mark();
-    }
-    faust_leaf_kernel<L><<<(unsigned)((a.n_streams + 31) / 32), 32, smem, st>>>(a, k);
+    int SL = a.lanes;
+    if (SL != 8 && SL != 16) SL = 32;                // option "lanes_per_warp"; narrower warps measured +7 % solo, -15 % in the cfg5 mix (jsfx_rt.cuh)
+    a.lanes = SL;
+    const int W = 4;
+    const size_t smem = (size_t)W * 2 * kCh * SL * kP * sizeof(float);
+    if (smem > 48 * 1024 && !cuda_ok(cudaFuncSetAttribute(faust_leaf_kernel<L>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "Faust leaf smem attr")) return false;
+    faust_leaf_kernel<L><<<(unsigned)((a.n_streams + SL * W - 1) / (SL * W)), 32 * W, smem, st>>>(a, k);
     return cuda_ok(cudaGetLastError(), "faust_leaf_kernel");
 }
 
@@ -366,7 +372,7 @@ public:
             if (slow_valid) h_slow_dev = h_slow;
         }
         if (n <= 0) return true;
-        FaustArgs a{in, out, stride, n, I.n_streams, I.block_len, nbq, d_slow, d_state};
+        FaustArgs a{in, out, stride, n, I.n_streams, I.block_len, nbq, d_slow, d_state, I.opt_lanes};
         const bool timed = I.time_begin();
         const int tiled = I.opt_scalar_f32 ? 0 : TiledLaunch<L>::go(a, I.stream);      // option scalar_f32 = 1: the generic kernel for every leaf
         if (tiled < 0) return false;
