@@ -9,7 +9,7 @@ THE DEVICE from the counter-based generator (za_gpu_synth, seed = absolute strea
 outside the timed region, outputs are reduced to per-stream checksums + energy by a device kernel, and a random
 subset of streams of every leaf is re-rendered by the CPU oracle (oracle/_ref, or the float restatement for Faust
 leaves) for the first chunk: `parity_spot_check`.  Every leaf has its own handle and CUDA stream, so the kernels of a
-step overlap on the device inside the two phases described at PHASE_B below; the step is timed with CUDA events
+step overlap on the device as described at PHASE_B below; the step is timed with CUDA events
 bracketing all of them.
 """
 from __future__ import annotations
@@ -28,23 +28,28 @@ SEED = 7000
 # The cfg5 leaf set of SURVEY.md section 8(d), in its order.
 CFG5_LEAVES = ["EasyExpander", "RTT", "SOMA", "ATTACK", "ERBTilt", "SpectralStabilizer", "cascade8", "stft_mask2048",
                "VAR", "ModTilt", "ClickBeGoneSG", "GTS", "RED"]
-# Schedule of one step, two phases, every leaf on its own CUDA stream inside a phase:
-#   A: the hand-written leaves and the heap-less translated leaves -- short kernels with big shared-memory tiles;
-#   B: the translated leaf that keeps its state in a mem[] heap (SOMA; SpectralStabilizer and ERBTilt were in this phase
-#      until they got their own scan kernels) -- a long kernel that lives off the L1.  Shared memory is carved out of the same 228 KB as
-#      the L1, so while phase-A kernels are resident on an SM the heap leaves' lines are evicted (measured in round 1:
-#      SpectralStabilizer / ERBTilt 3x slower inside a free-for-all mix).
+# Schedule of one step (`--option sched=N`; every leaf renders on its own CUDA stream):
+#   5 (default)  no phases: all 13 leaves at once, the long latency-bound stream-per-thread kernels launched first, SOMA / RTT /
+#                VAR on high-priority CUDA streams.  Measured on B200 after ERBTilt / SpectralStabilizer / ClickBeGoneSG got
+#                their own kernels: 165 ms per step against 257 ms for the two-phase schedule on the same box (SOMA takes
+#                105 ms alone and ~150 ms inside the mix, and it is what the step now waits for).
+#   4            as 5 without stream priorities (187-190 ms); `--option order=K` picks another launch order (179-213 ms).
+#   0            the round-1 two-phase schedule: A = everything but PHASE_B, then B = the translated leaf that keeps its
+#                state in a mem[] heap (SOMA) alone -- shared memory is carved out of the same 228 KB as the L1, and while the
+#                heap leaves SpectralStabilizer / ERBTilt were still translated they ran 3x slower inside a free-for-all mix.
+#   1            0 with ClickBeGoneSG outside the phase barrier (596-626 ms against 505-520 ms when it was still the generic
+#                kernel with its delay lines in local memory).
+#   2 / 3        0 with VAR + RED, or with the scan kernels, moved into phase B (within 2 % of 0).
 PHASE_B = {"SOMA"}
-# Experiment kept behind `--option sched=1`: the longest kernel of a step (ClickBeGoneSG: stream per thread, one warp per SM)
-# outside the phase barrier, launched first, phase B overlapping its tail.  Measured on B200: 596-626 ms per step against
-# 505-520 ms for the plain two-phase schedule -- ClickBeGoneSG's delay lines live off the L1 too and it slows down from
-# ~290 to 410-495 ms while SOMA runs beside it.  Default: sched=0.
 LONG_POLE = {"ClickBeGoneSG"}
-# `--option sched=2`: the stream-per-thread Faust leaves with small tiles (VAR, RED) keep SOMA company in phase B
 PHASE_B_WIDE = {"SOMA", "VAR", "RED"}
-# `--option sched=3`: the compute-bound scan kernels (small shared-memory footprint) fill the shadow of SOMA instead
 PHASE_B_SCAN = {"SOMA", "ERBTilt", "SpectralStabilizer", "ModTilt"}
 LAUNCH_FIRST = ["ClickBeGoneSG", "RTT", "RED", "ATTACK", "VAR"]
+LAUNCH_ORDERS = [LAUNCH_FIRST,
+                 ["SOMA", "RTT", "VAR", "RED", "ATTACK", "ClickBeGoneSG", "GTS"],
+                 ["EasyExpander", "cascade8", "stft_mask2048", "ModTilt", "ERBTilt", "SpectralStabilizer", "GTS", "ClickBeGoneSG"],   # bandwidth kernels first
+                 ["RTT", "SOMA", "ATTACK", "RED", "VAR"],
+                 ["SOMA", "ClickBeGoneSG", "RTT", "RED", "ATTACK", "VAR"]]
 TOTAL_STREAMS = 65536
 FAUST = {"VAR", "ModTilt", "ClickBeGoneSG", "GTS", "RED"}
 
@@ -71,10 +76,11 @@ def run(args, ctx, sub=False):
     nf = int(sec * SRATE)
     prec = "f32" if sub else args.precision
     steps = max(3, args.steps // 4) if sub else args.steps
+    hi_prio = not any(ov.startswith("sched=") and ov != "sched=5" for ov in (getattr(args, "option", None) or []))
     jobs, alg_bytes, frames = [], 0, 0
     for li, key in enumerate(leaves):
         info = za_gpu.plugin_info(key)
-        st = torch.cuda.Stream()
+        st = torch.cuda.Stream(priority=-1) if (hi_prio and key in ("SOMA", "RTT", "VAR")) else torch.cuda.Stream()
         p_leaf = "f32" if info.kind == 1 else prec
         bp = za_gpu.BatchProcessor(key, per_leaf, SRATE, 512, p_leaf, local)
         bp.set_stream(st.cuda_stream)
@@ -97,15 +103,19 @@ def run(args, ctx, sub=False):
         for j in jobs:
             za_gpu.synth_into(j["x"], j["kind"], SEED, j["first"], t0=chunk * nf, cuda_stream=j["st"].cuda_stream)
 
-    sched = 0
+    sched = 5
     for ov in getattr(args, "option", None) or []:
         if ov.startswith("sched="):
             sched = int(ov.split("=")[1])
     # launch order inside phase A: the long latency-bound kernels first (they hold one or two warps per SM for the whole
     # phase), the short bandwidth-heavy hand-written kernels after them
-    order = sorted(jobs, key=lambda j: LAUNCH_FIRST.index(j["key"]) if j["key"] in LAUNCH_FIRST else len(LAUNCH_FIRST)) if sched else jobs
+    first = LAUNCH_FIRST
+    for ov in getattr(args, "option", None) or []:          # --option order=K: launch-order experiments
+        if ov.startswith("order="):
+            first = LAUNCH_ORDERS[int(ov.split("=")[1])]
+    order = sorted(jobs, key=lambda j: first.index(j["key"]) if j["key"] in first else len(first)) if sched else jobs
     free = LONG_POLE if sched == 1 else set()
-    phase_b = PHASE_B_WIDE if sched == 2 else (PHASE_B_SCAN if sched == 3 else PHASE_B)
+    phase_b = PHASE_B_WIDE if sched == 2 else (PHASE_B_SCAN if sched == 3 else (set() if sched >= 4 else PHASE_B))   # 4, 5: no phases
     sa = [j["st"] for j in jobs if j["key"] not in phase_b and j["key"] not in free]
     sb = [j["st"] for j in jobs if j["key"] in phase_b]
 
@@ -234,7 +244,7 @@ def run(args, ctx, sub=False):
                    "leaves_not_built": not_built, "streams_per_gpu": per_leaf * len(leaves), "streams_per_leaf_per_gpu": per_leaf,
                    "frames_per_stream_per_step": nf, "block_len": 512, "l2": "inputs (%.1f GB per step per GPU) larger than L2" % (alg_bytes / 2e9),
                    "input": "generated on the device per time chunk by za_gpu_synth (counter-based, seed = absolute stream number), outside the timed events",
-                   "parallelism": f"streams sharded x{world}; per step two phases (hand-written + heap-less leaves, then the mem[]-heap leaves), one CUDA stream per leaf inside a phase"},
+                   "parallelism": f"streams sharded x{world}; one CUDA stream per leaf, schedule {sched} (bench_cfg5.py: 5 = all leaves at once, long latency-bound kernels launched first and on high-priority streams; 0 = two phases)"},
         "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
         "roofline": {"bound": "hbm", "achieved": ach, "peak": ctx.peak, "unit": "GB/s", "frac": ach / ctx.peak, "peak_source": ctx.peak_kind,
                      "traffic": None, "kernel": "all leaves' kernels of one step, overlapped", "kernel_ms_per_launch": ms,

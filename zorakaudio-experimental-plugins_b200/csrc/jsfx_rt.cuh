@@ -605,17 +605,18 @@ template <class S> bool launch_prepare(const GenLaunch& a, int precision, cudaSt
 }
 template <class S> bool launch_process(const GenLaunch& a, int precision, cudaStream_t st)
 {
-    // Streams per warp and warps per CTA.  Leaves with a mem[] heap keep single-warp CTAs (GenWarps above: their hot lines
-    // live in L1); heap-less leaves keep four warps per CTA whenever their tiles fit.  Streams per warp: 32 unless the caller
-    // asks for 16 or 8 (option "lanes_per_warp").  Measured on B200: spreading 4096 streams over 4x as many warps gains 7 %
-    // (VAR) to 17 % (RTT) when the handle has the GPU to itself -- the translated code is instruction-fetch bound as much as
-    // latency bound -- and LOSES 15 % in the concurrent cfg5 mix (a warp with 8 live lanes costs a full issue slot), so it
-    // is not the default.
+    // Streams per warp: 32 unless the caller asks for 16 or 8 (option "lanes_per_warp", a measurement switch).  A stream's
+    // time axis is sequential, so at a few thousand streams the launch takes frames x (latency of one frame's dependent
+    // chain) however the streams are spread over warps and SMs: measured on B200, RTT 4096 streams x 10 s takes 629 ms as
+    // 128 one-warp CTAs and as 64 two-warp CTAs, 520 ms with 8 streams per warp (less divergence per warp), and the
+    // concurrent cfg5 mix loses 15 % with narrow warps (a warp with 8 live lanes costs a full issue slot).  Only a shorter
+    // chain per frame or time-parallel kernels (the scan kernels) make these leaves faster.
     GenLaunch b = a;
     int L = a.lanes, W = GenWarps<S>::value;
     auto smem_of = [&](int w, int l) { return (size_t)w * 2 * S::kCh * l * (TileFrames<S>::value + 1) * sizeof(float); };
     if (L != 8 && L != 16) L = 32;
-    if (S::kMemSlots == 0) { W = 4; while (W > 1 && smem_of(W, L) > 160 * 1024) W >>= 1; }
+    // 32 streams per warp: the round-1 shapes (GenWarps).  Narrower warps: four per CTA when the tiles fit.
+    if (L != 32 && S::kMemSlots == 0) { W = 4; while (W > 1 && smem_of(W, L) > 160 * 1024) W >>= 1; }
     b.lanes = L;
     const int kGenWarps = W;
     const int blocks = (a.n_streams + L * kGenWarps - 1) / (L * kGenWarps);

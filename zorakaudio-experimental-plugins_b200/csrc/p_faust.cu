@@ -120,7 +120,7 @@ template <class L> bool launch_generic(FaustArgs a, const typename L::Konst& k, 
     int SL = a.lanes;
     if (SL != 8 && SL != 16) SL = 32;                // option "lanes_per_warp"; narrower warps measured +7 % solo, -15 % in the cfg5 mix (jsfx_rt.cuh)
     a.lanes = SL;
-    const int W = 4;
+    const int W = 1;                                 // one warp per CTA (the round-1 shape; see the measurement note in jsfx_rt.cuh)
     const size_t smem = (size_t)W * 2 * kCh * SL * kP * sizeof(float);
     if (smem > 48 * 1024 && !cuda_ok(cudaFuncSetAttribute(faust_leaf_kernel<L>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "Faust leaf smem attr")) return false;
     faust_leaf_kernel<L><<<(unsigned)((a.n_streams + SL * W - 1) / (SL * W)), 32 * W, smem, st>>>(a, k);
