@@ -229,3 +229,32 @@ def test_detector_filter_sliders_move_inside_a_call_on_the_device_path(gpu, ref)
     out = bp.process(x, params=p)
     assert max(dbfs_rms(out[s].astype(np.float64) - yd[s]) for s in range(ns)) < -100.0
     bp.close()
+
+
+def test_long_automated_call_is_rendered_in_pipelined_segments(gpu, ref):
+    """Calls of 512 host blocks or more are cut into time segments (parameter rows of segment k + 1 upload while segment k
+    renders; state carries through the state rows): 600 blocks -> 2 segments = 4 launches, the result equal to the
+    reference like any render (fp64 <= 1e-12 of level, flag exact) and, in float, bit-identical to the same frames fed
+    in two calls at the segment boundary."""
+    ns, nb = 6, 600
+    nf = 512 * nb - 100                                  # ragged last block
+    p, x = make_case(ref, ns, nf, True, detector_filters=True)
+    y, yd, v = ref.render(p, x, want_f64=True, want_vars=True)
+    bp = gpu.BatchProcessor("EasyExpander", ns, precision="f64").prepare(p[0])
+    tap = np.zeros_like(yd)
+    l0 = bp.launch_count()
+    bp.process(x, tap64=tap, params=p)
+    assert bp.launch_count() - l0 == 4
+    assert rel_err(tap, yd).max() <= TOL64
+    assert np.array_equal(bp.read_state("expanding"), v["expanding"])
+    bp.close()
+    bp = gpu.BatchProcessor("EasyExpander", ns, precision="f32").prepare(p[0])
+    whole = bp.process(x, params=p)
+    bp.close()
+    bp = gpu.BatchProcessor("EasyExpander", ns, precision="f32").prepare(p[0])
+    cut = 300 * 512
+    parts = [bp.process(np.ascontiguousarray(x[:, :, :cut]), params=np.ascontiguousarray(p[:300])),
+             bp.process(np.ascontiguousarray(x[:, :, cut:]), params=np.ascontiguousarray(p[300:]))]
+    bp.close()
+    assert np.array_equal(np.concatenate(parts, axis=2), whole)
+    assert max(dbfs_rms(whole[s].astype(np.float64) - yd[s]) for s in range(ns)) < -100.0

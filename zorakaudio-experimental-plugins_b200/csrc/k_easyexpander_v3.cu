@@ -30,8 +30,6 @@ namespace {
 
 constexpr int kF = 32;             // frames per batch
 constexpr int kMaxS = 32;          // streams per CTA
-constexpr int kWarps = 24;
-constexpr int kThreads = kWarps * 32;
 constexpr int kRowP = 36;          // floats per [stream] row of a 32-frame tile
 constexpr int kIoP = 64;           // I/O ring: [stream][ch][32 frames], 16-byte chunk c of a row stored at c ^ (stream & 7)
 constexpr int kBpP = kF * 4 + 4;   // [stream][frame][4 band pairs] + 4: pair sums w_j env_j + w_j+1 env_j+1 of lane jj
@@ -41,10 +39,15 @@ constexpr int kIoSlots = 16;       // I/O ring: a batch's slot is filled by cp.a
 constexpr int kLead = 6;           // iterations between the cp.async issue of a super-batch and its first batch
 constexpr int kDbSlots = 3;        // det_db / target rows live from P2 (i) to G2 (i + 2)
 
-constexpr int kQ = 2;              // streams per helper warp
+#ifndef ZA_EE_KQ
+#define ZA_EE_KQ 2
+#endif
+constexpr int kQ = ZA_EE_KQ;       // streams per helper warp (2: 16 helper warps, 24 warps per CTA; 4: 8 helper warps, 16 warps per CTA)
 enum { R_FILTER = 4, R_G1 = 5, R_G2 = 6, R_NONE = 7, R_HELP = 8 };
 // Warp w runs on scheduler w & 3.  Every scheduler gets one band warp; the sequential warps (G2, G1, filter) take one
-// scheduler each and the helpers fill up: with the 28 streams of a cfg3 CTA helpers 0..13 are active (14 and 15 idle).
+// scheduler each and the helpers fill up: with the 28 streams of a cfg3 CTA helpers 0..13 (kQ = 2) or 0..6 (kQ = 4) are active.
+#if ZA_EE_KQ == 2
+constexpr int kWarps = 24;
 //                                  scheduler: 0            1            2            3
 __constant__ int kRoleV3[kWarps] = {0,           1,           2,           3,
                                     R_G2,        R_G1,        R_FILTER,    R_HELP + 0,
@@ -53,6 +56,15 @@ __constant__ int kRoleV3[kWarps] = {0,           1,           2,           3,
                                     R_HELP + 14, R_HELP + 9,  R_HELP + 10, R_HELP + 11,
                                     R_NONE,      R_HELP + 15, R_HELP + 12, R_HELP + 13};
 constexpr int kLiveWarps = 23;
+#else
+constexpr int kWarps = 16;
+__constant__ int kRoleV3[kWarps] = {0,           1,           2,           3,
+                                    R_G2,        R_G1,        R_FILTER,    R_HELP + 3,
+                                    R_HELP + 0,  R_HELP + 1,  R_HELP + 2,  R_HELP + 6,
+                                    R_NONE,      R_HELP + 4,  R_HELP + 5,  R_HELP + 7};
+constexpr int kLiveWarps = 15;
+#endif
+constexpr int kThreads = kWarps * 32;
 
 struct SmemV3 {
     alignas(16) float io[kIoSlots][kMaxS * kIoP];
@@ -423,50 +435,47 @@ easyexpander_v3_kernel(const EEArgs a, const int spc)
             nthr[q] = crow[q][0].thresh_db; ndep[q] = crow[q][0].depth_db; nrat[q] = crow[q][0].ratio_base;
         }
         fetch(0); fetch(1);
-        for (int i = 0; i < n_iter; ++i) {
-            // ---- S0: super-batch i / 4 has to be in the ring when this iteration's barrier publishes batch i; the one
-            // ---- that starts kLead iterations from now is requested
+        // P2 of one batch: band sum in the script's order, level, memoryless half of the gain computer
+        auto p2_math = [&](const float4 pr, const int q, float& det_lin, float& det_db, float& target_gr) {
+            const float sum = fmaxf(((pr.x + pr.y) + pr.z) + pr.w, eps);
+            det_lin = sum * rsqrt_fast(sum);
+            det_db = db_per_lg2_pow * lg2_fast(sum);
+            float d = thr[q] - det_db;
+            d = d < 0.f ? 0.f : d;
+            const float xk = d * (1.0f / 6.0f);                              // knee_db = 6 (:34)
+            const float smo = (xk * xk) * fmaf(-2.0f, xk, 3.0f);
+            const float re1 = d < 6.0f ? rm1[q] * smo : rm1[q];               // ratio_eff - 1
+            target_gr = d * re1;
+            target_gr = target_gr > dep[q] ? dep[q] : target_gr;
+        };
+        auto next_block_rows = [&]() {                                        // entering a host block: its row was fetched a block ago
+            const int nr = bw.row + 1 < bw.n_rows ? bw.row + 1 : bw.n_rows - 1;
+#pragma unroll
+            for (int q = 0; q < kQ; ++q) {
+                thr[q] = (float)nthr[q]; dep[q] = (float)ndep[q]; rm1[q] = (float)(nrat[q] - 1.0);
+                const EECoef& c = crow[q][(size_t)nr * ns];
+                nthr[q] = c.thresh_db; ndep[q] = c.depth_db; nrat[q] = c.ratio_base;
+            }
+        };
+        // one iteration, any position in the render (pipeline fill and drain, ragged last batch, partial helpers)
+        auto body_any = [&](const int i) {
             if ((i & (kSB - 1)) == 0) asm volatile("cp.async.wait_group 1;" ::: "memory");
             if (((i + kLead) & (kSB - 1)) == 0) fetch((i + kLead) / kSB);
             if (act) {
-                // ---- P2: batch i - 3: band sum in the script's order, level, memoryless half of the gain computer ------
                 if (i >= 3 && i - 3 < n_batches && !(a.role_off & 16)) {
                     const int b = i - 3;
-                    if (bw.enter((int64_t)b * kF)) {
-                        const int nr = bw.row + 1 < bw.n_rows ? bw.row + 1 : bw.n_rows - 1;
-#pragma unroll
-                        for (int q = 0; q < kQ; ++q) {
-                            thr[q] = (float)nthr[q]; dep[q] = (float)ndep[q]; rm1[q] = (float)(nrat[q] - 1.0);
-                            const EECoef& c = crow[q][(size_t)nr * ns];
-                            nthr[q] = c.thresh_db; ndep[q] = c.depth_db; nrat[q] = c.ratio_base;
-                        }
-                    }
+                    if (bw.enter((int64_t)b * kF)) next_block_rows();
                     const float* bp = sm.bp[b & 1] + (kQ * h) * kBpP;
                     float* lin = sm.lin[b & 1] + (kQ * h) * kRowP + lane;
                     float* db = sm.db[b % kDbSlots] + (kQ * h) * kRowP + lane;
                     float* tg = sm.tg[b % kDbSlots] + (kQ * h) * kRowP + lane;
-                    float sum[kQ];
 #pragma unroll
                     for (int q = 0; q < kQ; ++q) {
-                        const int qq = has[q] ? q : 0;
-                        const float4 pr = *reinterpret_cast<const float4*>(bp + qq * kBpP + bpA);
-                        sum[q] = fmaxf(((pr.x + pr.y) + pr.z) + pr.w, eps);
-                    }
-#pragma unroll
-                    for (int q = 0; q < kQ; ++q) {
-                        const float det_lin = sum[q] * rsqrt_fast(sum[q]);
-                        const float det_db = db_per_lg2_pow * lg2_fast(sum[q]);
-                        float d = thr[q] - det_db;
-                        d = d < 0.f ? 0.f : d;
-                        const float xk = d * (1.0f / 6.0f);                              // knee_db = 6 (:34)
-                        const float smo = (xk * xk) * fmaf(-2.0f, xk, 3.0f);
-                        const float re1 = d < 6.0f ? rm1[q] * smo : rm1[q];               // ratio_eff - 1
-                        float target_gr = d * re1;
-                        target_gr = target_gr > dep[q] ? dep[q] : target_gr;
+                        float det_lin, det_db, target_gr;
+                        p2_math(*reinterpret_cast<const float4*>(bp + (has[q] ? q : 0) * kBpP + bpA), q, det_lin, det_db, target_gr);
                         if (has[q]) { lin[q * kRowP] = det_lin; db[q * kRowP] = det_db; tg[q * kRowP] = target_gr; }
                     }
                 }
-                // ---- S4: batch i - 6: exp and the output multiplies; 128-byte row stores --------------------------------
                 if (i >= 6 && i - 6 < n_batches && !(a.role_off & 32)) {
                     const int b = i - 6;
                     const float* io = sm.io[b & (kIoSlots - 1)];
@@ -481,7 +490,58 @@ easyexpander_v3_kernel(const EEArgs a, const int spc)
                 }
             }
             v3_sync();
+        };
+        // Steady state (6 <= i < n_batches + 3, a helper with all its streams, no measurement switches): every stage is due,
+        // every S4 batch is whole, so the iteration carries no validity checks; host blocks are counted in batches.
+        bool all = act && a.role_off == 0;
+#pragma unroll
+        for (int q = 0; q < kQ; ++q) all = all && has[q];
+        int i = 0;
+        const int i_steady = all ? 6 : n_iter, i_drain = all ? n_batches + 3 : n_iter;
+        for (; i < i_steady && i < n_iter; ++i) body_any(i);
+        if (i < i_drain) {
+            const int bpb = a.block_len / kF;                                 // batches per host block
+            // batch i - 3 of P2: batches left in its host block (bw is positioned by the last body_any call)
+            int left = (int)((bw.next - (int64_t)(i - 3) * kF) / kF);
+            const float* bpq = sm.bp[0] + (kQ * h) * kBpP + bpA;
+            float* linq = sm.lin[0] + (kQ * h) * kRowP + lane;
+            float* dbq = sm.db[0] + (kQ * h) * kRowP + lane;
+            float* tgq = sm.tg[0] + (kQ * h) * kRowP + lane;
+            const float* gq = sm.gain[0] + (kQ * h) * kRowP + lane;
+            int slot3 = (i - 3) % kDbSlots;
+            float* op[kQ];
+#pragma unroll
+            for (int q = 0; q < kQ; ++q) op[q] = orow[q] + (int64_t)(i - 6) * kF + lane;
+            for (; i < i_drain; ++i) {
+                if ((i & (kSB - 1)) == 0) asm volatile("cp.async.wait_group 1;" ::: "memory");
+                if (((i + kLead) & (kSB - 1)) == 0) fetch((i + kLead) / kSB);
+                if (left == 0) { bw.row += 1; bw.next += a.block_len; next_block_rows(); left = bpb; }
+                --left;
+                const int par3 = (i - 3) & 1, par6 = i & 1;                      // (i - 6) & 1 == i & 1
+                const float* io = sm.io[(i - 6) & (kIoSlots - 1)];
+#pragma unroll
+                for (int q = 0; q < kQ; ++q) {
+                    float det_lin, det_db, target_gr;
+                    p2_math(*reinterpret_cast<const float4*>(bpq + par3 * (kMaxS * kBpP) + q * kBpP), q, det_lin, det_db, target_gr);
+                    linq[par3 * (kMaxS * kRowP) + q * kRowP] = det_lin;
+                    dbq[slot3 * (kMaxS * kRowP) + q * kRowP] = det_db;
+                    tgq[slot3 * (kMaxS * kRowP) + q * kRowP] = target_gr;
+                }
+#pragma unroll
+                for (int q = 0; q < kQ; ++q) {
+                    const float gain_lin = ex2_fast(gq[par6 * (kMaxS * kRowP) + q * kRowP] * lg2_per_db);
+                    op[q][0] = io[fo[q]] * gain_lin;
+                    op[q][rs] = io[fo[q] + 32] * gain_lin;
+                    op[q] += kF;
+                }
+                slot3 = slot3 == kDbSlots - 1 ? 0 : slot3 + 1;
+                v3_sync();
+            }
+            // hand the block position back to the general body
+            // (bw.row / bw.next were advanced block by block above; batches of the current block already consumed do not matter
+            //  to BlockWalk::enter, which only compares a batch's first frame with bw.next)
         }
+        for (; i < n_iter; ++i) body_any(i);
     }
 }
 

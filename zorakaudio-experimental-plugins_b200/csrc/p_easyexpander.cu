@@ -295,29 +295,48 @@ public:
         } else {
             cudaStreamWaitEvent(up_stream, ev_consumed, 0);      // the previous call's parameter kernel has read the buffers
         }
-        if (!cuda_ok(cudaMemcpyAsync(d_per_stream, ps.data(), ps.size() * sizeof(EECoef), cudaMemcpyHostToDevice, up_stream), "per-stream coef upload") ||
-            !cuda_ok(cudaMemcpyAsync(d_params, params, rows * nd * sizeof(float), cudaMemcpyHostToDevice, up_stream), "params upload"))
+        if (!cuda_ok(cudaMemcpyAsync(d_per_stream, ps.data(), ps.size() * sizeof(EECoef), cudaMemcpyHostToDevice, up_stream), "per-stream coef upload"))
             return -1;
-        cudaEventRecord(ev_params, up_stream);
-        cudaStreamWaitEvent(I.stream, ev_params, 0);
+        // Long calls are cut into time segments of whole host blocks: the rows of segment k + 1 upload (and, from pageable
+        // memory, are staged by the host) while segment k's kernel runs, so only the first segment's upload is exposed
+        // (cfg3: 460 MB of rows per 60 s call, ~9 ms at PCIe rate, was all in front of the one launch).  State carries from
+        // launch to launch in the state rows like between calls.
+        const int64_t total_blocks = (n + I.block_len - 1) / I.block_len;
+        int nseg = 1;
+        if (nb >= 512 && nb >= total_blocks) nseg = (int)std::min<int64_t>(8, nb / 256);
+        const int seg_blocks = (nb + nseg - 1) / nseg;
         EEParamArgs pa{};
-        pa.params = d_params; pa.per_stream = d_per_stream; pa.out = d_coef; pa.nb = nb; pa.ns = ns;
+        pa.per_stream = d_per_stream; pa.ns = ns;
         pa.tab_hpf = d_tab_hpf; pa.tab_lpf = d_tab_lpf; pa.n_hpf = n_tab_hpf; pa.n_lpf = n_tab_lpf;
         for (int j = 0; j < 5; ++j) {
             const SliderDecl& d = I.decls[j];
             pa.q[j] = SliderQ{(double)d.min, (double)d.max, (double)(d.step > 0.0f ? d.step : 1.0f), d.is_choice ? 1 : 0};
         }
-        ee_param_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, I.stream>>>(pa);
-        if (!cuda_ok(cudaGetLastError(), "ee_param_kernel launch")) return -1;
-        cudaEventRecord(ev_consumed, I.stream);
-        ++I.launches;
-        EEArgs a{};
-        a.in = in; a.out = out; a.tap = tap; a.row_stride = stride; a.n_frames = n;
-        a.n_streams = ns; a.block_len = I.block_len; a.n_coef_blocks = nb; a.coef = d_coef; a.state = d_state; a.k = k_; a.role_off = I.opt_role_off;
-        const bool timed = I.time_begin();
-        if (!easyexpander_launch(a, I.precision, n_sm, I.stream, I.opt_scalar_f32)) return -1;
-        if (timed) I.time_end();
-        ++I.launches;
+        for (int k = 0; k < nseg; ++k) {
+            const int b0 = k * seg_blocks, b1 = std::min(nb, b0 + seg_blocks);
+            if (b0 >= b1) break;
+            const size_t r0 = (size_t)b0 * ns, nr = (size_t)(b1 - b0) * ns;
+            if (!cuda_ok(cudaMemcpyAsync(d_params + r0 * nd, params + r0 * nd, nr * nd * sizeof(float), cudaMemcpyHostToDevice, up_stream), "params upload"))
+                return -1;
+            cudaEventRecord(ev_params, up_stream);
+            cudaStreamWaitEvent(I.stream, ev_params, 0);
+            pa.params = d_params + r0 * nd; pa.out = d_coef + r0; pa.nb = b1 - b0;
+            ee_param_kernel<<<(unsigned)((nr + 255) / 256), 256, 0, I.stream>>>(pa);
+            if (!cuda_ok(cudaGetLastError(), "ee_param_kernel launch")) return -1;
+            if (k == nseg - 1 || b1 == nb) cudaEventRecord(ev_consumed, I.stream);
+            ++I.launches;
+            const int64_t f0 = (int64_t)b0 * I.block_len;
+            const int64_t f1 = (k == nseg - 1 || b1 == nb) ? n : std::min<int64_t>(n, (int64_t)b1 * I.block_len);
+            if (f1 <= f0) continue;
+            EEArgs a{};
+            a.in = in + f0; a.out = out + f0; a.tap = tap ? tap + f0 : nullptr; a.row_stride = stride; a.n_frames = f1 - f0;
+            a.n_streams = ns; a.block_len = I.block_len; a.n_coef_blocks = b1 - b0; a.coef = d_coef + r0; a.state = d_state; a.k = k_;
+            a.role_off = I.opt_role_off;
+            const bool timed = I.time_begin();
+            if (!easyexpander_launch(a, I.precision, n_sm, I.stream, I.opt_scalar_f32)) return -1;
+            if (timed) I.time_end();
+            ++I.launches;
+        }
         return 1;
     }
 

@@ -20,6 +20,8 @@ COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-fvisibility=hi
 
 # Faust leaves restate the .dsp's separate float multiplies and adds: no FMA contraction in those translation units
 PER_FILE = {"p_faust.cu": ["-fmad=false"], "k_gts.cu": ["-fmad=false"]}
+if os.environ.get("ZA_EE_KQ"):          # measurement builds of the EasyExpander v3 kernel: streams per helper warp (2 or 4)
+    PER_FILE["k_easyexpander_v3.cu"] = ["-DZA_EE_KQ=" + os.environ["ZA_EE_KQ"]]
 
 
 def sources():
