@@ -93,7 +93,9 @@ __device__ __forceinline__ void band_group(const R* xd, R* bpw, int f0, int nv, 
                 ic1 = fma_((R)2.0, v1, -ic1);
                 ic2 = fma_(c.g2, v1, ic2);
             } else {
-                v1 = div_<R>(add(mul(c.g, sub(xv[k], ic2)), ic1), c.den);
+                // x / den as x * (1 / den): one rounding more than the script's division (<= 1 ulp per frame in a stable
+                // recursion -- measured 1e-15 of level against the reference, criterion 1e-12) for a third of the FP64 work
+                v1 = mul(add(mul(c.g, sub(xv[k], ic2)), ic1), c.a1);
                 const R v2 = add(ic2, mul(c.g, v1));
                 ic1 = sub(mul((R)2.0, v1), ic1);
                 ic2 = sub(mul((R)2.0, v2), ic2);
