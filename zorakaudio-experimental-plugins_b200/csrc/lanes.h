@@ -19,9 +19,11 @@ using LF = float;
 using LD = double;
 using LB = bool;
 #define ZA_LN __device__ __forceinline__
-ZA_LN float mul(float a, float b) { return __fmul_rn(a, b); }
-ZA_LN float add(float a, float b) { return __fadd_rn(a, b); }
-ZA_LN float sub(float a, float b) { return __fsub_rn(a, b); }
+// float: plain operators, so nvcc contracts a * b + c into one FFMA (the float mode only has to null below -100 dBFS; FADD +
+// FMUL pairs were a quarter of the scan kernels' issue slots).  double: the _rn intrinsics, never contracted (1e-12 parity).
+ZA_LN float mul(float a, float b) { return a * b; }
+ZA_LN float add(float a, float b) { return a + b; }
+ZA_LN float sub(float a, float b) { return a - b; }
 ZA_LN float fma_rn(float a, float b, float c) { return __fmaf_rn(a, b, c); }
 ZA_LN float div_(float a, float b) { return __fdiv_rn(a, b); }
 ZA_LN float div_fast_(float a, float b) { return __fdividef(a, b); }
