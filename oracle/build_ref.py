@@ -107,6 +107,78 @@ def build_shadow(force: bool = False) -> Path | None:
     return so
 
 
+def _cxx_block(text: str, start: int) -> str:
+    """The declaration that begins at `start`, up to and including its closing brace (plus a `;` after a struct).  A small
+    C++ scanner: braces inside string / raw-string / char literals and comments do not count."""
+    i, depth, n = start, 0, len(text)
+    while i < n:
+        c = text[i]
+        if text.startswith("//", i):
+            i = text.index("\n", i)
+        elif text.startswith("/*", i):
+            i = text.index("*/", i) + 2
+        elif text.startswith('R"(', i):
+            i = text.index(')"', i) + 2
+        elif c == '"':
+            i += 1
+            while text[i] != '"':
+                i += 2 if text[i] == "\\" else 1
+            i += 1
+        elif c == "'":
+            i += 1
+            while text[i] != "'":
+                i += 2 if text[i] == "\\" else 1
+            i += 1
+        else:
+            if c == "{":
+                depth += 1
+            elif c == "}":
+                depth -= 1
+                if depth == 0:
+                    i += 1
+                    while i < n and text[i] in " \t":
+                        i += 1
+                    return text[start:i + 1] if i < n and text[i] == ";" else text[start:i]
+            i += 1
+    raise RuntimeError("unbalanced braces in the reference source")
+
+
+PARSER_DECLS = ["struct JsfxSliderDecl", "static inline std::string trimAscii (std::string s)",
+                "static std::vector<std::string> splitTopLevelCommas (const std::string& s)",
+                "static bool parseFloat (const std::string& s, float& out)",
+                "static juce::String parseJsfxStringDefaultToken (std::string tok)",
+                "static std::vector<JsfxSliderDecl> parseJsfxSliderDecls (const char* jsfxText, juce::String* outHelpText = nullptr)"]
+
+
+def build_parser(force: bool = False) -> Path | None:
+    """The reference's own slider-declaration parser (src/JSFXJuceProcessor.cpp: JsfxSliderDecl :526, trimAscii :567,
+    splitTopLevelCommas / parseFloat / parseJsfxStringDefaultToken :633-704, parseJsfxSliderDecls :710-939) behind a C entry
+    point: the declarations are cut out of the source where it lies into a temporary oracle/_ref/ref_parser_extract.inc, compiled
+    inside oracle/ref_parser_shim.cpp (which supplies the three JUCE names they use), and the extract is deleted again."""
+    src = REF / "src" / "JSFXJuceProcessor.cpp"
+    lib = OUT / "libref_parser.so"
+    if not src.exists():
+        return lib if lib.exists() else None
+    shim = HERE / "ref_parser_shim.cpp"
+    if lib.exists() and not force and not _newer(lib, src, shim, Path(__file__)):
+        return lib
+    OUT.mkdir(exist_ok=True)
+    text = src.read_text(errors="replace")
+    parts = []
+    for d in PARSER_DECLS:
+        at = text.find(d)
+        if at < 0:
+            raise RuntimeError(f"reference parser: `{d}` not found in {src}")
+        parts.append(f"// ---- {src.name}, line {text.count(chr(10), 0, at) + 1} ----\n" + _cxx_block(text, at) + "\n")
+    (OUT / "ref_parser_extract.inc").write_text("// generated by oracle/build_ref.py::build_parser from the reference source; not tracked\n" + "\n".join(parts))
+    r = subprocess.run([os.environ.get("CXX", "g++"), "-O1", "-std=c++17", "-shared", "-fPIC", "-fvisibility=hidden", "-static-libstdc++", "-static-libgcc", "-Wl,-Bsymbolic", "-Wl,--exclude-libs,ALL", "-I", str(HERE),
+                        str(shim), "-o", str(lib)], capture_output=True, text=True)
+    (OUT / "ref_parser_extract.inc").unlink()           # only the compiled library stays (and travels to the GPU box)
+    if r.returncode != 0:
+        raise RuntimeError("reference parser build failed:\n" + r.stdout + r.stderr)
+    return lib
+
+
 def build_all(keys=None, force: bool = False) -> dict:
     res = {}
     if keys is None:
@@ -115,6 +187,11 @@ def build_all(keys=None, force: bool = False) -> dict:
         except subprocess.CalledProcessError as e:
             print(f"[build_ref] shadow_eel: FAILED ({e})", file=sys.stderr)
             res["shadow_eel"] = None
+        try:
+            res["ref_parser"] = build_parser(force)
+        except (RuntimeError, ValueError) as e:
+            print(f"[build_ref] ref_parser: FAILED ({e})", file=sys.stderr)
+            res["ref_parser"] = None
     for k in (keys or PLUGINS):
         try:
             res[k] = build_one(k, force)

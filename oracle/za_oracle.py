@@ -147,6 +147,28 @@ def _llround(x):
 # ------------------------------------------------------------------------------------------------
 # plugin sources (the catalog stays where it is; authored workloads live in the package)
 # ------------------------------------------------------------------------------------------------
+class _RefSliderDecl(C.Structure):
+    _fields_ = [("index0", C.c_int32), ("is_choice", C.c_int32), ("n_choices", C.c_int32), ("is_string", C.c_int32), ("hidden", C.c_int32),
+                ("shape", C.c_int32), ("default", C.c_float), ("min", C.c_float), ("max", C.c_float), ("step", C.c_float),
+                ("shape_mod", C.c_float), ("var", C.c_char * 64), ("name", C.c_char * 128)]
+
+
+def have_ref_parser() -> bool:
+    return (HERE / "_ref" / "libref_parser.so").exists()
+
+
+def ref_parse_sliders(text: str):
+    """The REFERENCE'S OWN parseJsfxSliderDecls (src/JSFXJuceProcessor.cpp:710-939), compiled from where it lies by
+    build_ref.build_parser() behind oracle/ref_parser_shim.cpp: list of dicts like parse_sliders() below."""
+    lib = C.CDLL(str(HERE / "_ref" / "libref_parser.so"))
+    lib.ref_parse_sliders.argtypes = [C.c_char_p, C.POINTER(_RefSliderDecl), C.c_int]
+    arr = (_RefSliderDecl * 64)()
+    n = lib.ref_parse_sliders(text.encode("utf-8", "replace"), arr, 64)
+    return [dict(index0=d.index0, default=d.default, min=d.min, max=d.max, step=d.step, is_choice=bool(d.is_choice), n_choices=d.n_choices,
+                 is_string=bool(d.is_string), hidden=bool(d.hidden), shape=d.shape, shape_mod=d.shape_mod, var=d.var.decode(),
+                 name=d.name.decode("utf-8", "replace")) for d in arr[:n]]
+
+
 def plugin_source_text(key: str) -> str:
     """Slider layout text.  Authored workloads: read the .jsfx.  Catalog leaves: the layout is
     committed in the package's plugin table (the reference tree does not exist on the GPU box)."""

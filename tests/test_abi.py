@@ -65,6 +65,58 @@ def test_parser_grammar_cases(built_lib):
     assert by[7].is_choice and by[2].step == 1.0 and by[4].min == 0.0 and by[4].max == 10.0
 
 
+GRAMMAR_CASES = "\n".join([
+    "slider1:thresh_db=-40<-80,0,0.1>Threshold (dB)",
+    "slider3:350<50,1200,1:sqr>Release",
+    "slider8:style=1<0,4,1{Clean,Punch,Dense,Body,Wild}>--Style",
+    "slider4:det_hpf_hz=0<0,20000,1:log=1000>Det HPF",
+    "slider9:/some/path:none:File",
+    "slider10:#name=\"x\"<string>Text",
+    "slider11:label_only",
+    "  slider 12 : a = 3 < 1 , 2 >  clamped default",
+    "slider13:0.5<0,1>no step",
+    "slider14:2<0,4,{A,B,C}>choices without a step",
+    "slider15:1<0,3,1{ , ,}>empty choice labels",
+    "slider16:5<0,10,0>zero step",
+    "slider17:5<0,10,-1>negative step",
+    "slider18:x=abc<0,1,0.1>unparsable default",
+    "slider19:1<0,1,1:log>log without a midpoint",
+    "slider70:1<0,1,1>ignored",
+    "slider0:1<0,1,1>ignored too",
+    "slider5:7<10,0>swapped range, default step",
+    "slider3:1<0,1,1>duplicate index keeps the first",
+    "// #TOOLTIP: a tooltip",
+    "slider20:0<-1,1,0.01>-hidden",
+    "slider21:g=-3<-80,0,0.1>G ; trailing",
+])
+
+
+def test_parser_equals_the_references_own_parser(built_lib):
+    """za_gpu_parse_sliders against parseJsfxSliderDecls ITSELF (src/JSFXJuceProcessor.cpp:710-939, compiled from where it lies by
+    oracle/build_ref.py::build_parser behind oracle/ref_parser_shim.cpp), on every .jsfx of the reference catalog (where the
+    reference tree is present), on the authored workloads and on grammar corner cases.  The library lists the FLOAT
+    parameters, i.e. the reference's declarations minus the string-input sliders its parameter layout skips (:2766-2772).
+    The Python restatement in oracle/za_oracle.py is held to the same."""
+    import glob
+    import za_gpu
+    if not zo.have_ref_parser():
+        pytest.skip("oracle/_ref/libref_parser.so not built")
+    texts = {"grammar cases": GRAMMAR_CASES}
+    for f in sorted(glob.glob("/root/reference/plugins/**/*.jsfx", recursive=True) + glob.glob(str(Path(__file__).resolve().parent.parent / "zorakaudio-experimental-plugins_b200" / "plugins" / "**" / "*.jsfx"), recursive=True)):
+        texts[f] = open(f, encoding="utf-8", errors="replace").read()
+    n = 0
+    for name, text in texts.items():
+        ref = [d for d in zo.ref_parse_sliders(text) if not d["is_string"]]
+        key = lambda d: (d["index0"], d["is_choice"], d["var"], np.float32(d["default"]), np.float32(d["min"]), np.float32(d["max"]), np.float32(d["step"]))
+        ours = [(a.index0, bool(a.is_choice), a.alias.decode(), a.def_, a.min, a.max, a.step) for a in za_gpu.parse_sliders(text)]
+        assert ours == [key(d) for d in ref], name
+        assert [key(d) for d in zo.parse_sliders(text)] == [key(d) for d in ref], name
+        n += len(ref)
+    assert n >= 20
+    by = {d["index0"]: d for d in zo.ref_parse_sliders(GRAMMAR_CASES)}
+    assert by[9]["is_string"] and by[19]["hidden"] and by[7]["n_choices"] == 5 and 69 not in by       # the corner cases were exercised
+
+
 def test_quantiser_matches_oracle(built_lib):
     import za_gpu
     text = zo.plugin_source_text("cascade8") + "\nslider20:mode=1<0,4,1{A,B,C,D,E}>Mode\nslider21:g=-3<-80,0,0.1>G\n"
