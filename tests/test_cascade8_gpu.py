@@ -182,3 +182,82 @@ def test_large_batch_spot_checked_against_oracle(gpu):
     bp.sync()
     assert torch.equal(y2, y * 2.0)
     bp.close()
+
+
+def _auto_case(ns, nf, block, rows=None, which=None):
+    ref = zo.best_oracle("cascade8")
+    x = wl.noise_two_sines(ns, nf)
+    nb = (nf + block - 1) // block if rows is None else rows
+    base = wl.cascade8_params(ns)
+    p = wl.automation(ref.sliders, nb, ns, which=list(range(15)) if which is None else which, base=base[0])
+    p[:, :, :] = np.where(np.isfinite(p), p, base[None])
+    return ref, p, x
+
+
+@pytest.mark.parametrize("ns,nf,block,rows", [(37, 512 * 40 + 77, 512, None), (9, 100 * 61 + 3, 100, None), (5, 512 * 12, 512, 5), (3, 31 * 7 + 5, 31, None)])
+def test_automated_render_in_one_launch_per_segment(gpu, ns, nf, block, rows):
+    """Per-block automation of all 15 sliders through cascade8_auto_kernel (scan tables rebuilt on the device per host block):
+    fp64 within 1e-12 of level of the reference render and the filter state equal to rounding, for block lengths that do and
+    do not divide the tiles, a ragged end, fewer parameter rows than host blocks (the last row persists); not one launch per
+    block; and the same bits as the old launch-per-block path (option force_generic_io) to the criterion."""
+    ref, p, x = _auto_case(ns, nf, block, rows)
+    y, yd, v = ref.render(p, x, want_f64=True, want_vars=True, block=block)
+    bp = gpu.BatchProcessor("cascade8", ns, 48000.0, block, "f64").prepare(p[0])
+    tap = np.zeros_like(yd)
+    l0 = bp.launch_count()
+    out = bp.process(x, tap64=tap, params=p)
+    nbq = min(len(p), (nf + block - 1) // block)
+    assert bp.launch_count() - l0 <= 2 * ((nbq + 255) // 256) + 4, bp.launch_count() - l0
+    assert rel_err(tap, yd).max() <= TOL64
+    assert np.mean(out == y) > 0.9999
+    for name in ("z11", "z32", "z62", "lp7", "lp8"):
+        assert np.allclose(bp.read_state(name), v[name], rtol=1e-9, atol=1e-14), name
+    bp.close()
+    bp = gpu.BatchProcessor("cascade8", ns, 48000.0, block, "f64").prepare(p[0])
+    bp.set_option("force_generic_io", 1)                 # the block-by-block path of the static kernels
+    tap2 = np.zeros_like(yd)
+    bp.process(x, tap64=tap2, params=p)
+    assert rel_err(tap2, yd).max() <= TOL64 and rel_err(tap, tap2).max() <= TOL64
+    bp.close()
+
+
+def test_automated_render_fp32_and_what_follows_it(gpu):
+    """Float mode of the automation kernel (< -100 dBFS per stream); a static call after an automated one continues from its
+    state with the LAST row's coefficients (the static kernels' tables follow); an automated render fed in two calls gives
+    the bits of one call."""
+    ns, block = 21, 512
+    nf = block * 30
+    ref, p, x = _auto_case(ns, nf, block)
+    xs = wl.noise_two_sines(ns, 4096 + 11, first_stream=100)
+    pall = np.concatenate([p, np.repeat(p[-1:], (xs.shape[-1] + block - 1) // block, axis=0)], axis=0)
+    _, yd = ref.render(pall, np.concatenate([x, xs], axis=2), want_f64=True, block=block)
+    for prec in ("f32", "f64"):
+        bp = gpu.BatchProcessor("cascade8", ns, 48000.0, block, prec).prepare(p[0])
+        a = bp.process(x, params=p)
+        b = bp.process(xs)                                # static: no parameter rows
+        got = np.concatenate([a, b], axis=2).astype(np.float64)
+        worst = max(dbfs_rms(got[s] - yd[s]) for s in range(ns))
+        print(f"cascade8 automated then static, {prec}: worst stream {worst:.1f} dBFS")
+        assert worst < (-100.0 if prec == "f32" else -120.0), worst   # f64: what is left is the float store of a hot (resonant, Q up to 8) signal
+        bp.close()
+        bp = gpu.BatchProcessor("cascade8", ns, 48000.0, block, prec).prepare(p[0])
+        cut = block * 11
+        parts = [bp.process(np.ascontiguousarray(x[:, :, :cut]), params=np.ascontiguousarray(p[:11])),
+                 bp.process(np.ascontiguousarray(x[:, :, cut:]), params=np.ascontiguousarray(p[11:]))]
+        assert np.array_equal(np.concatenate(parts, axis=2), a), prec
+        bp.close()
+
+
+def test_automated_render_longer_than_a_segment(gpu):
+    """More host blocks than one 256-block segment of coefficient rows, with sliders that move only in some blocks (the
+    unchanged rows are copies and the kernel keeps its tables across them)."""
+    ns, block = 4, 64
+    nf = block * 700 + 9
+    ref, p, x = _auto_case(ns, nf, block, which=[0, 4, 14])
+    p[100:400] = p[100]                                    # a long stretch without movement, across the segment boundary
+    _, yd = ref.render(p, x, want_f64=True, block=block)
+    bp = gpu.BatchProcessor("cascade8", ns, 48000.0, block, "f64").prepare(p[0])
+    tap = np.zeros_like(yd)
+    bp.process(x, tap64=tap, params=p)
+    assert rel_err(tap, yd).max() <= TOL64
+    bp.close()

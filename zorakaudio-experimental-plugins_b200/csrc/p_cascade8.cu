@@ -65,7 +65,7 @@ class Cascade8 : public PluginImpl {
     double* d_state = nullptr;
 
 public:
-    ~Cascade8() override { cudaFree(d_coef); cudaFree(d_tables); cudaFree(d_tables_x2); cudaFree(d_state); }
+    ~Cascade8() override { cudaFree(d_coef); cudaFree(d_tables); cudaFree(d_tables_x2); cudaFree(d_state); cudaFree(d_rows[0]); cudaFree(d_rows[1]); }
 
     bool create(Instance& I) override
     {
@@ -101,6 +101,84 @@ public:
         }
         return cascade8_build_tables(d_coef + (size_t)s0 * kC8Coefs,
                                      (char*)d_tables + (size_t)s0 * cascade8_tables_bytes(I.precision), ns, I.precision, I.stream);
+    }
+
+    // Per-block automation: the whole trajectory in one launch per 256-block segment (k_cascade8_auto.cu) instead of one
+    // launch, one upload and two table kernels per host block in which a slider moved.  @slider runs on the host with the host
+    // libm for every (block, stream) whose quantised sliders differ from the previous block's (other rows are copies, which is
+    // what tells the kernel to keep its tables).  Returns 0 (not taken) when no slider moves inside the call: the static
+    // kernels are faster then.
+    double* d_rows[2] = {nullptr, nullptr};
+    size_t rows_cap = 0;
+    std::vector<double> h_rows, h_q;
+
+    int run_blocks_raw(Instance& I, const float* params, int nb, const float* in, float* out, double* tap, int64_t n, int64_t stride) override
+    {
+        const int ns = I.n_streams, nd = (int)I.decls.size();
+        if (nd != 15 || I.opt_force_generic || nb < 2) return 0;
+        // does anything move?  (raw host values: equal floats quantise equally)
+        bool moves = false;
+        for (int b = 1; b < nb && !moves; ++b)
+            moves = std::memcmp(params + (size_t)b * ns * nd, params, (size_t)ns * nd * sizeof(float)) != 0;
+        if (!moves) return 0;
+        constexpr int kSeg = 256;
+        const size_t seg_rows = (size_t)std::min(nb, kSeg) * ns;
+        if (seg_rows * kC8Coefs > rows_cap) {
+            cudaFree(d_rows[0]); cudaFree(d_rows[1]); d_rows[0] = d_rows[1] = nullptr; rows_cap = 0;
+            if (!cuda_ok(cudaMalloc(&d_rows[0], seg_rows * kC8Coefs * sizeof(double)), "cascade8 coefficient rows") ||
+                !cuda_ok(cudaMalloc(&d_rows[1], seg_rows * kC8Coefs * sizeof(double)), "cascade8 coefficient rows")) return -1;
+            rows_cap = seg_rows * kC8Coefs;
+        }
+        h_rows.resize(seg_rows * kC8Coefs);
+        h_q.assign((size_t)ns * nd, 0.0);                 // quantised sliders of the previous block, per stream
+        std::vector<uint8_t> have((size_t)ns, 0);
+        const int64_t total_blocks = (n + I.block_len - 1) / I.block_len;
+        int seg = 0;
+        for (int b0 = 0; b0 < nb; b0 += kSeg, ++seg) {
+            const int b1 = std::min(nb, b0 + kSeg);
+            parallel_for(ns, 16, [&](int64_t sa, int64_t sb) {
+                for (int64_t s = sa; s < sb; ++s) {
+                    double* prev = &h_q[(size_t)s * nd];
+                    for (int b = b0; b < b1; ++b) {
+                        const float* p = params + ((size_t)b * ns + s) * nd;
+                        double q[15];
+                        bool ch = !have[s];
+                        for (int j = 0; j < nd; ++j) { q[j] = quantise_slider(I.decls[j], p[j]); ch = ch || q[j] != prev[j]; }
+                        double* row = &h_rows[((size_t)(b - b0) * ns + s) * kC8Coefs];
+                        if (ch) {
+                            c8_slider(q, I.srate, row);
+                            std::memcpy(prev, q, sizeof(double) * nd);
+                            have[s] = 1;
+                        } else if (b > b0) {
+                            std::memcpy(row, row - (size_t)ns * kC8Coefs, sizeof(double) * kC8Coefs);
+                        } else {
+                            std::memcpy(row, &h_coef[(size_t)s * kC8Coefs], sizeof(double) * kC8Coefs);    // first block of a later segment: the last row of the one before
+                        }
+                        if (b == b1 - 1) std::memcpy(&h_coef[(size_t)s * kC8Coefs], row, sizeof(double) * kC8Coefs);
+                    }
+                }
+            });
+            // h_rows is pageable: the copy is staged before cudaMemcpyAsync returns, so the buffer can be refilled; the device
+            // buffers alternate, and the stream order keeps segment k's kernel ahead of the upload that reuses its buffer
+            double* dr = d_rows[seg & 1];
+            if (!cuda_ok(cudaMemcpyAsync(dr, h_rows.data(), (size_t)(b1 - b0) * ns * kC8Coefs * sizeof(double), cudaMemcpyHostToDevice, I.stream), "cascade8 rows upload"))
+                return -1;
+            ++I.launches;
+            const int64_t f0 = (int64_t)b0 * I.block_len;
+            const int64_t f1 = (b1 == nb) ? n : std::min<int64_t>(n, (int64_t)b1 * I.block_len);
+            if (f1 <= f0) break;
+            const bool timed = I.time_begin();
+            if (!cascade8_auto_launch(in + f0, out + f0, tap ? tap + f0 : nullptr, stride, f1 - f0, ns, I.block_len, b1 - b0, dr, d_state, I.precision, I.stream))
+                return -1;
+            if (timed) I.time_end();
+            ++I.launches;
+            if (b1 >= total_blocks) break;
+        }
+        // the static kernels' coefficients and tables follow the last row, for whatever call comes next
+        if (!cuda_ok(cudaMemcpyAsync(d_coef, h_coef.data(), h_coef.size() * sizeof(double), cudaMemcpyHostToDevice, I.stream), "cascade8 coef upload")) return -1;
+        if (d_tables_x2 && !cascade8_x2_build_tables(d_coef, d_tables_x2, ns, I.stream)) return -1;
+        if (!cascade8_build_tables(d_coef, d_tables, ns, I.precision, I.stream)) return -1;
+        return 1;
     }
 
     bool run(Instance& I, int s0, int ns, const float* in, float* out, double* tap, int64_t n, int64_t stride) override

@@ -195,6 +195,20 @@ static bool process_range_engine(Instance& I, const float* params, int n_param_b
         }
         return I.impl->run_blocks(I, s0, ns, q.data(), nbq, in, out, tap, n_frames, stride);
     }
+    // plugins without per-block coefficient rows in their throughput kernels may still render an automated call in one go
+    if (params && n_param_blocks > 1 && n_blocks > 1 && s0 == 0 && ns == I.n_streams) {
+        const int nbq = (int)std::min<int64_t>(n_param_blocks, n_blocks);
+        const int r = I.impl->run_blocks_raw(I, params, nbq, in, out, tap, n_frames, stride);
+        if (r < 0) return false;
+        if (r > 0) {   // st.sliders after the call = the last row, quantised
+            for (int s = 0; s < ns; ++s) {
+                for (int j = 0; j < nd; ++j)
+                    I.sliders[(size_t)s * nd + j] = quantise_slider(I.decls[j], params[((size_t)(nbq - 1) * ns + s) * nd + j]);
+                I.sliders_valid[s] = 1;
+            }
+            return true;
+        }
+    }
     std::vector<int> changed;
     int64_t run_start = 0;     // first frame of the pending run
     for (int64_t b = 0; b < n_blocks; ++b) {

@@ -28,6 +28,9 @@ bool make_chunk_tensor_map(CUtensorMap* map, const float* base, int64_t n_chunks
 // ---- cascade8 (LTI cascade: 6 TDF-II biquads + 2 one-poles) -----------------------------------
 constexpr int kC8Coefs = 36;     // per stream: 6 x (b0,b1,b2,a1,a2), a7, 1-a7, c8, mix, pad
 constexpr int kC8State = 16;     // per stream: z[6][2], lp7, lp8, pad (double, persists across calls)
+// k_cascade8_auto.cu: renders with per-block coefficient rows [n_rows][n_streams][kC8Coefs] in one launch (tables rebuilt on the device)
+bool cascade8_auto_launch(const float* in, float* out, double* tap, int64_t row_stride, int64_t n_frames, int n_streams, int block_len,
+                          int n_rows, const double* coef, double* state, int precision, cudaStream_t stream);
 
 struct C8Launch {
     const float* in;         // row 0, first frame of this launch
