@@ -46,7 +46,28 @@ constexpr int kQ = ZA_EE_KQ;       // streams per helper warp (2: 16 helper warp
 enum { R_FILTER = 4, R_G1 = 5, R_G2 = 6, R_NONE = 7, R_HELP = 8 };
 // Warp w runs on scheduler w & 3.  Every scheduler gets one band warp; the sequential warps (G2, G1, filter) take one
 // scheduler each and the helpers fill up: with the 28 streams of a cfg3 CTA helpers 0..13 (kQ = 2) or 0..6 (kQ = 4) are active.
-#if ZA_EE_KQ == 2
+#ifndef ZA_EE_PPL
+#define ZA_EE_PPL 1
+#endif
+constexpr int kPPL = ZA_EE_PPL;    // band pairs per lane of a band warp: 1 (default) = four band warps of 8 streams, one dependent
+                                   // chain per lane; 2 = two band warps of 16 streams with two independent chains per lane.
+                                   // Measured on B200 (build switch ZA_EE_PPL=2): 3x SLOWER (31.4 against 10.6 ms per segment) --
+                                   // the chain interleaves as hoped, but the band work (2300 issue slots per batch) then sits on
+                                   // two schedulers instead of four and, under the 80-register cap of 768 threads, the compiler
+                                   // rebuilds the store address every frame; kept as a negative result.
+constexpr int kBandWarpsN = 4 / kPPL, kLPS = 4 / kPPL;      // band warps; lanes per stream
+#if ZA_EE_KQ == 2 && ZA_EE_PPL == 2
+constexpr int kWarps = 24;
+// two band warps, each with a scheduler it shares with two helpers only; the sequential warps and the other helpers on the other two
+//                                  scheduler: 0            1            2            3
+__constant__ int kRoleV3[kWarps] = {0,           1,           R_G2,        R_G1,
+                                    R_HELP + 0,  R_HELP + 2,  R_FILTER,    R_HELP + 8,
+                                    R_HELP + 1,  R_HELP + 3,  R_HELP + 4,  R_HELP + 9,
+                                    R_HELP + 14, R_HELP + 13, R_HELP + 5,  R_HELP + 10,
+                                    R_NONE,      R_HELP + 15, R_HELP + 6,  R_HELP + 11,
+                                    R_NONE,      R_NONE,      R_HELP + 7,  R_HELP + 12};
+constexpr int kLiveWarps = 21;
+#elif ZA_EE_KQ == 2
 constexpr int kWarps = 24;
 //                                  scheduler: 0            1            2            3
 __constant__ int kRoleV3[kWarps] = {0,           1,           2,           3,
@@ -57,6 +78,7 @@ __constant__ int kRoleV3[kWarps] = {0,           1,           2,           3,
                                     R_NONE,      R_HELP + 15, R_HELP + 12, R_HELP + 13};
 constexpr int kLiveWarps = 23;
 #else
+static_assert(ZA_EE_PPL == 1, "four streams per helper: only with four band warps");
 constexpr int kWarps = 16;
 __constant__ int kRoleV3[kWarps] = {0,           1,           2,           3,
                                     R_G2,        R_G1,        R_FILTER,    R_HELP + 3,
@@ -109,7 +131,7 @@ struct BandS3 { p2 i1, i2, e; };
 // eight frames of one band pair: u = 2 a2 i2 + x,  s = 2 a1 i1 + u (= 2 v1 / k),  i1' = (2 a1 - 1) i1 + u,  i2' = i2 + g s,
 // E' = (1 - c) E + (w c k^2 / 4) s^2, with k = 2 g / den the input gain the states are divided by (svf_bp, :74-93; :200-219)
 template <bool FULL>
-__device__ __forceinline__ void band_group3(const float* xd, float* pa, float* pb, int f0, int nv, bool wr, const BandK3& c, BandS3& s)
+__device__ __forceinline__ void band_group3(const float* xd, float* pa, int f0, int nv, bool wr, const BandK3 (&c)[kPPL], BandS3 (&s)[kPPL])
 {
     float xv[8];
     if (FULL) {
@@ -122,14 +144,22 @@ __device__ __forceinline__ void band_group3(const float* xd, float* pa, float* p
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
         if (FULL || f0 + k < nv) {
-            const p2 u = fma2(c.a22, s.i2, pk(xv[k], xv[k]));
-            const p2 sv = fma2(c.a12, s.i1, u);
-            s.i1 = fma2(c.c1, s.i1, u);
-            s.i2 = fma2(c.g, sv, s.i2);
-            s.e = fma2(c.kq, mul2(sv, sv), mul2(c.omc, s.e));
-            float e0, e1;
-            unpk(s.e, e0, e1);
-            if (wr) pa[(f0 + k) * 4] = e0 + e1;
+            float ps[kPPL];
+#pragma unroll
+            for (int p = 0; p < kPPL; ++p) {                               // kPPL independent chains
+                const p2 u = fma2(c[p].a22, s[p].i2, pk(xv[k], xv[k]));
+                const p2 sv = fma2(c[p].a12, s[p].i1, u);
+                s[p].i1 = fma2(c[p].c1, s[p].i1, u);
+                s[p].i2 = fma2(c[p].g, sv, s[p].i2);
+                s[p].e = fma2(c[p].kq, mul2(sv, sv), mul2(c[p].omc, s[p].e));
+                float e0, e1;
+                unpk(s[p].e, e0, e1);
+                ps[p] = e0 + e1;
+            }
+            if (wr) {
+                if (kPPL == 2) *reinterpret_cast<float2*>(pa + (f0 + k) * 4) = make_float2(ps[0], ps[kPPL - 1]);
+                else pa[(f0 + k) * 4] = ps[0];
+            }
         }
     }
 }
@@ -220,47 +250,57 @@ easyexpander_v3_kernel(const EEArgs a, const int spc)
     const int n_batches = (int)((n + kF - 1) / kF);
     const int n_iter = n_batches + 7;
 
-    if (role < 4) {
-        // ============================ band warps: SVF + power follower, two bands per lane, eight streams per warp ========
-        const int sl = lane >> 2, jj = lane & 3;
-        const int ls = 8 * role + sl;
-        const bool act = 8 * role < ns_cta, live = ls < ns_cta;
+    if (role < kBandWarpsN) {
+        // ============================ band warps: SVF + power follower; kPPL band pairs per lane, 8 kPPL streams per warp ====
+        const int sl = lane / kLPS, jj = lane % kLPS;
+        const int ls = 8 * kPPL * role + sl;
+        const bool act = 8 * kPPL * role < ns_cta, live = ls < ns_cta;
         const int sg = s_base + (live ? ls : (ns_cta - 1));
-        const int jA = 2 * jj, jB = jA + 1;
-        const double gA = a.k.g[jA], gB = a.k.g[jB], dA = a.k.den[jA], dB = a.k.den[jB], bc = a.k.band_c;
-        const float kA = (float)(2.0 * gA / dA), kB = (float)(2.0 * gB / dB);      // input gain of the unscaled recurrence
-        const float wA = (float)a.k.w[jA], wB = (float)a.k.w[jB];
-        const BandK3 bk{pk((float)(-2.0 * gA / dA), (float)(-2.0 * gB / dB)), pk((float)(2.0 / dA), (float)(2.0 / dB)),
-                        pk((float)(2.0 / dA - 1.0), (float)(2.0 / dB - 1.0)), pk((float)gA, (float)gB),
-                        pk((float)(1.0 - bc), (float)(1.0 - bc)),
-                        pk((float)((double)wA * bc * 0.25 * (double)kA * (double)kA), (float)((double)wB * bc * 0.25 * (double)kB * (double)kB))};
+        const double bc = a.k.band_c;
         double* st = a.state + sg;
-        BandS3 bs{pk((float)(st[(0 + jA) * ns] / (double)kA), (float)(st[(0 + jB) * ns] / (double)kB)),
-                  pk((float)(st[(8 + jA) * ns] / (double)kA), (float)(st[(8 + jB) * ns] / (double)kB)),
-                  pk((float)(st[(16 + jA) * ns] * (double)wA), (float)(st[(16 + jB) * ns] * (double)wB))};
+        BandK3 bk[kPPL];
+        BandS3 bs[kPPL];
+        float kA[kPPL], kB[kPPL], wA[kPPL], wB[kPPL];
+#pragma unroll
+        for (int p = 0; p < kPPL; ++p) {
+            const int jA = 2 * (jj * kPPL + p), jB = jA + 1;
+            const double gA = a.k.g[jA], gB = a.k.g[jB], dA = a.k.den[jA], dB = a.k.den[jB];
+            kA[p] = (float)(2.0 * gA / dA); kB[p] = (float)(2.0 * gB / dB);      // input gain of the unscaled recurrence
+            wA[p] = (float)a.k.w[jA]; wB[p] = (float)a.k.w[jB];
+            bk[p] = BandK3{pk((float)(-2.0 * gA / dA), (float)(-2.0 * gB / dB)), pk((float)(2.0 / dA), (float)(2.0 / dB)),
+                           pk((float)(2.0 / dA - 1.0), (float)(2.0 / dB - 1.0)), pk((float)gA, (float)gB),
+                           pk((float)(1.0 - bc), (float)(1.0 - bc)),
+                           pk((float)((double)wA[p] * bc * 0.25 * (double)kA[p] * (double)kA[p]), (float)((double)wB[p] * bc * 0.25 * (double)kB[p] * (double)kB[p]))};
+            bs[p] = BandS3{pk((float)(st[(0 + jA) * ns] / (double)kA[p]), (float)(st[(0 + jB) * ns] / (double)kB[p])),
+                           pk((float)(st[(8 + jA) * ns] / (double)kA[p]), (float)(st[(8 + jB) * ns] / (double)kB[p])),
+                           pk((float)(st[(16 + jA) * ns] * (double)wA[p]), (float)(st[(16 + jB) * ns] * (double)wB[p]))};
+        }
         for (int i = 0; i < n_iter; ++i) {
             if (act && i >= 2 && i - 2 < n_batches && !(a.role_off & 1)) {
                 const int b = i - 2;
                 const int lr = live ? ls : 0;                        // rows exist for kMaxS streams only; the others never store
                 const float* xd = sm.xd[b & 1] + lr * kRowP;
                 const int nv = (int)min((int64_t)kF, n - (int64_t)b * kF);
-                float* pa = sm.bp[b & 1] + lr * kBpP + jj;
-                float* pb = nullptr;
+                float* pa = sm.bp[b & 1] + lr * kBpP + jj * kPPL;
                 if (nv == kF) {
 #pragma unroll 1
-                    for (int f0 = 0; f0 < kF; f0 += 8) band_group3<true>(xd, pa, pb, f0, nv, live, bk, bs);
+                    for (int f0 = 0; f0 < kF; f0 += 8) band_group3<true>(xd, pa, f0, nv, live, bk, bs);
                 } else {
 #pragma unroll 1
-                    for (int f0 = 0; f0 < kF; f0 += 8) band_group3<false>(xd, pa, pb, f0, nv, live, bk, bs);
+                    for (int f0 = 0; f0 < kF; f0 += 8) band_group3<false>(xd, pa, f0, nv, live, bk, bs);
                 }
             }
             v3_sync();
         }
         if (live) {
-            float lo_, hi_;
-            unpk(bs.i1, lo_, hi_); st[(0 + jA) * ns] = (double)lo_ * (double)kA; st[(0 + jB) * ns] = (double)hi_ * (double)kB;
-            unpk(bs.i2, lo_, hi_); st[(8 + jA) * ns] = (double)lo_ * (double)kA; st[(8 + jB) * ns] = (double)hi_ * (double)kB;
-            unpk(bs.e, lo_, hi_); st[(16 + jA) * ns] = (double)lo_ / (double)wA; st[(16 + jB) * ns] = (double)hi_ / (double)wB;
+#pragma unroll
+            for (int p = 0; p < kPPL; ++p) {
+                const int jA = 2 * (jj * kPPL + p), jB = jA + 1;
+                float lo_, hi_;
+                unpk(bs[p].i1, lo_, hi_); st[(0 + jA) * ns] = (double)lo_ * (double)kA[p]; st[(0 + jB) * ns] = (double)hi_ * (double)kB[p];
+                unpk(bs[p].i2, lo_, hi_); st[(8 + jA) * ns] = (double)lo_ * (double)kA[p]; st[(8 + jB) * ns] = (double)hi_ * (double)kB[p];
+                unpk(bs[p].e, lo_, hi_); st[(16 + jA) * ns] = (double)lo_ / (double)wA[p]; st[(16 + jB) * ns] = (double)hi_ / (double)wB[p];
+            }
         }
     } else if (role == R_FILTER) {
         // ============================ filter warp: lane = stream (batch i - 1) ========================================

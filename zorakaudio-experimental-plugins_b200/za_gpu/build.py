@@ -22,6 +22,8 @@ COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-fvisibility=hi
 PER_FILE = {"p_faust.cu": ["-fmad=false"], "k_gts.cu": ["-fmad=false"]}
 if os.environ.get("ZA_EE_KQ"):          # measurement builds of the EasyExpander v3 kernel: streams per helper warp (2 or 4)
     PER_FILE["k_easyexpander_v3.cu"] = ["-DZA_EE_KQ=" + os.environ["ZA_EE_KQ"]]
+if os.environ.get("ZA_EE_PPL"):         # ... and band pairs per band-warp lane (1 or 2)
+    PER_FILE.setdefault("k_easyexpander_v3.cu", []).append("-DZA_EE_PPL=" + os.environ["ZA_EE_PPL"])
 
 
 def sources():
