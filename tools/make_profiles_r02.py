@@ -19,6 +19,8 @@ CAPS = [
      "python bench.py --workload cfg3 --seconds 2 --steps 1 --warmup 3 --no-cpu --no-e2e --no-parity --no-f64 --subs ''", 4096 * 96000, "cfg3"),
     ("r02_cascade8", "cascade8_x2", "cascade8 fp32 (`cascade8_x2_kernel`)",
      "python bench.py --workload cfg2 --seconds 10 --steps 1 --warmup 3 --no-cpu --no-e2e --no-parity --no-f64", 1024 * 480000, "cfg2"),
+    ("r02_cbg_tiled", "cbg_tiled", "Faust leaf ClickBeGoneSG fp32, tiled kernel (`cbg_tiled_kernel`: 8 FIR warps with lane = frame + 1 recurrence warp with lane = stream per 32-stream CTA, inputs by cp.async one tile ahead)",
+     "python tools/prof_run.py --plugin ClickBeGoneSG --streams 4096 --seconds 2 --reps 2", 4096 * 96000, None),
     ("r02_gts", "gts", "Faust leaf GTS fp32 (`gts_kernel`: time-parallel 257-tap Gaussian FIR rebuilt per frame)",
      "python bench.py --workload gts --seconds 2 --steps 1 --warmup 3 --no-cpu --no-e2e --no-parity", 4096 * 96000, "gts"),
 ]
