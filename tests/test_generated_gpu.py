@@ -320,6 +320,7 @@ def test_streams_per_warp_does_not_change_a_bit(gpu, key, prec):
     for lanes in (32, 16, 8):
         bp = gpu.BatchProcessor(key, ns, precision=prec).prepare(p[0])
         bp.set_option("lanes_per_warp", lanes)
+        bp.set_option("unstaged", 1)                      # the option belongs to the one-thread-per-stream kernel
         tap = np.zeros_like(yd) if prec == "f64" else None
         out = bp.process(x, tap64=tap, params=p)
         outs[lanes] = (out, tap, {n: bp.read_state(n) for n in names})
@@ -334,3 +335,41 @@ def test_streams_per_warp_does_not_change_a_bit(gpu, key, prec):
             assert np.array_equal(outs[lanes][1].view(np.uint64), outs[32][1].view(np.uint64)), lanes
         for n, v in outs[32][2].items():
             assert np.array_equal(outs[lanes][2][n], v, equal_nan=True), (lanes, n)
+
+
+STAGED = ["SOMA"]                                         # leaves the translator cuts into a stage pipeline (jsfxc.py::STAGE_CUTS)
+
+
+@pytest.mark.parametrize("key", STAGED)
+@pytest.mark.parametrize("block", [512, 100, 7])
+def test_stage_pipeline_equals_the_one_thread_kernel(gpu, key, block):
+    """jsfx_staged_kernel (one warp per group of @sample statements, values crossing a cut through shared-memory rings) runs
+    the same statements in the same order on the same values as jsfx_process_kernel: in float64 the outputs and every state
+    variable are the same bits, over two calls (state, heap and PRNG carried), host blocks that cut the 32-frame tiles and
+    the batches, per-block automation and a partial last CTA; the float64 render is the one checked against the reference."""
+    ref = zo.RefPlugin(key)
+    ns, nf = 45, 3000 + 13
+    x = wl.programme_bursts(ns, nf, n_ch=ref.n_in)
+    base = np.array([s["default"] for s in ref.sliders], np.float32)
+    p = wl.automation(ref.sliders, (nf + block - 1) // block, ns, which=list(range(min(3, len(base)))), base=base)
+    _, yd = ref.render(p, x, want_f64=True, block=block)
+    cut = (1500 // block) * block                          # second call starts on a host-block boundary, as a host would
+    res = {}
+    for unstaged in (1, 0):
+        for prec in ("f64", "f32"):
+            bp = gpu.BatchProcessor(key, ns, block_len=block, precision=prec).prepare(p[0])
+            bp.set_option("unstaged", unstaged)
+            t1, t2 = (np.zeros((ns, ref.n_out, cut)), np.zeros((ns, ref.n_out, nf - cut))) if prec == "f64" else (None, None)
+            o1 = bp.process(np.ascontiguousarray(x[:, :, :cut]), tap64=t1, params=p[:cut // block])
+            o2 = bp.process(np.ascontiguousarray(x[:, :, cut:]), tap64=t2, params=p[cut // block:])
+            tap = np.concatenate([t1, t2], axis=2) if prec == "f64" else None
+            res[(unstaged, prec)] = (np.concatenate([o1, o2], axis=2), tap, bp.save_state())      # variables, sliders, heap, PRNG
+            bp.close()
+    a, b = res[(1, "f64")], res[(0, "f64")]
+    assert np.array_equal(a[1].view(np.uint64), b[1].view(np.uint64))
+    assert np.array_equal(a[0].view(np.uint32), b[0].view(np.uint32))
+    assert np.array_equal(a[2], b[2])
+    assert rel_err(b[1], yd).max() <= TOL64
+    # float32: the same statements too, but nvcc contracts a * b + c only where both halves sit in one stage
+    worst = max(dbfs_rms(res[(0, "f32")][0][s].astype(np.float64) - b[1][s]) for s in range(ns))
+    assert worst < -100.0, worst

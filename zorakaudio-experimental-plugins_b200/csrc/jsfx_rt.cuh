@@ -48,7 +48,7 @@ struct GenLaunch {
     const double* q; const int* decl_index0;
     void* state; void* mem; unsigned* mt; int* err; double srate;
     int64_t fft_scratch; const double* tw;
-    int lanes;
+    int lanes, unstaged;
 };
 }
 #else
@@ -596,6 +596,166 @@ __global__ void __launch_bounds__(128, 1) jsfx_process_kernel(const GenLaunch a)
     if (live) ctx_close<S, R>(c, v, a, s, valid ? (R)1 : (R)0);
 }
 
+// ---- stage pipeline (leaves the translator could cut, jsfxc.py::plan_stages) --------------------------------------------
+// One CTA = 32 streams x K warps: warp k runs statements [cut k, cut k+1) of @sample (S::Staged::run<R, F, k>) for frame batch
+// i - k while warp k + 1 runs the next group on batch i - k - 1 -- the EasyExpander role pipeline, generated.  A stream's
+// time axis stays sequential, but the dependent chain of one frame is spread over K warps that work at the same time.
+// Every warp keeps its OWN copy of the variables and replays the host-block protocol (slider push, @slider, @block) when
+// its own frame counter enters a block; the planner has checked that those sections do not read what @sample writes.  What
+// crosses a cut inside a frame travels through per-value rings in shared memory (mb[slot][F][32], ring depth = distance to
+// the furthest consumer + 1), one __syncthreads per batch of F frames.  Same statements in the same order on the same
+// values: in float64 the outputs and states are bit-identical to jsfx_process_kernel.
+struct NoStages { static constexpr int kStages = 1, kMailSlots = 1; };
+
+template <class S, typename R> __host__ __device__ constexpr int staged_frames()     // frames per batch: rings of at most 72 KB (two CTAs per SM)
+{
+    int f = 32;
+    while (f > 2 && (size_t)S::Staged::kMailSlots * f * 32 * sizeof(R) > 72 * 1024) f >>= 1;
+    return f;
+}
+template <class S, typename R> __host__ __device__ constexpr size_t staged_smem()
+{
+    return (size_t)S::Staged::kMailSlots * staged_frames<S, R>() * 32 * sizeof(R) + (size_t)(2 * S::kIn + S::kOut) * 32 * 33 * sizeof(float);
+}
+
+template <class S, typename R, bool TAP, int K>
+__device__ __forceinline__ void staged_role(const GenLaunch& a, R* mb, float* tiles, int lane, int s0)
+{
+    using P = typename S::Staged;
+    constexpr int KS = P::kStages, F = staged_frames<S, R>(), kF = 32, kP = 33, kTile = S::kIn * 32 * kP;
+    constexpr bool first = K == 0, last = K == KS - 1;
+    const int s = s0 + lane;
+    const bool live = s < a.n_streams;
+    const int ns_cta = min(32, a.n_streams - s0);
+    float* const out_tile = tiles + 2 * kTile;
+    Rt<R> c;
+    R v[S::kVars];
+    bool valid = false;
+    if (live) {
+        ctx_open<S, R>(c, v, a, s);
+        valid = reinterpret_cast<const R*>(a.state)[(long long)(S::kVars + 64) * a.n_streams + s] != (R)0;
+    }
+    auto fetch = [&](float* tile, int64_t frame0, int nf) {
+        const int nq = ns_cta * S::kIn;
+        const float* src = a.in + (size_t)s0 * S::kIn * a.row_stride + frame0 + (lane < nf ? lane : 0);
+        for (int q = 0; q < nq; ++q) cp_async4(tile + ((q % S::kIn) * 32 + q / S::kIn) * kP + lane, src + (size_t)q * a.row_stride, lane < nf);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    for (int j = 0; j < K; ++j) __syncthreads();                 // pipeline fill: batch 0 reaches this stage at iteration K
+    int64_t pos = 0;
+    int nb = (int)min((int64_t)a.block_len, a.n_frames - pos);
+    int buf = 0, bt = 0;
+    if (first && a.n_frames > 0) fetch(tiles, 0, min(kF, nb));
+    for (int blk = 0; pos < a.n_frames; ++blk) {
+        if (live) {
+            if (a.n_rows > 0) {
+                const bool changed = push_sliders<S, R>(c, v, a, blk < a.n_rows ? blk : a.n_rows - 1, s, valid);
+                valid = true;
+                if (changed) S::template slider<R>(c, v);
+            }
+            c.samplesblock = (R)nb;
+            c.pending = 0;
+            S::template block<R>(c, v);
+            if (c.pending) S::template slider<R>(c, v);
+        }
+        const int nb_next = (int)min((int64_t)a.block_len, a.n_frames - (pos + nb));
+        for (int f0 = 0; f0 < nb; f0 += kF) {
+            const int nf = min(kF, nb - f0);
+            const float* tile = tiles + buf * kTile;
+            if (first) {
+                const bool more_here = f0 + kF < nb;
+                const int64_t nx0 = more_here ? pos + f0 + kF : pos + nb;
+                const int nxf = more_here ? min(kF, nb - f0 - kF) : min(kF, nb_next);
+                if (nxf > 0) {
+                    fetch(tiles + (buf ^ 1) * kTile, nx0, nxf);
+                    asm volatile("cp.async.wait_group 1;" ::: "memory");
+                } else {
+                    asm volatile("cp.async.wait_group 0;" ::: "memory");
+                }
+                __syncwarp();
+            }
+            for (int b0 = 0; b0 < nf; b0 += F) {
+                const int nbf = min(F, nf - b0);
+                if (live) {
+                    for (int f = 0; f < nbf; ++f) {
+                        if (first) {
+#pragma unroll
+                            for (int ch = 0; ch < S::kCh; ++ch) c.spl[ch] = ch < S::kIn ? (R)tile[(ch * 32 + lane) * kP + b0 + f] : (R)0;
+                        }
+                        P::template run<R, F, K>(c, v, mb, bt, f * 32 + lane);
+                        if (last) {
+#pragma unroll
+                            for (int ch = 0; ch < S::kOut; ++ch) {
+                                if (TAP) a.tap[((size_t)s * S::kOut + ch) * a.row_stride + pos + f0 + b0 + f] = (double)c.spl[ch];
+                                out_tile[(ch * 32 + lane) * kP + b0 + f] = (float)c.spl[ch];
+                            }
+                        }
+                    }
+                }
+                ++bt;
+                __syncthreads();
+            }
+            if (last) {
+                __syncwarp();
+                const int nq = ns_cta * S::kOut;
+                float* dst = a.out + (size_t)s0 * S::kOut * a.row_stride + pos + f0 + lane;
+                if (lane < nf) {
+#pragma unroll 4
+                    for (int q = 0; q < nq; ++q) dst[(size_t)q * a.row_stride] = out_tile[((q % S::kOut) * 32 + q / S::kOut) * kP + lane];
+                }
+                __syncwarp();
+            }
+            if (first) { __syncwarp(); buf ^= 1; }
+        }
+        pos += nb;
+        nb = nb_next;
+    }
+    for (int j = K; j < KS - 1; ++j) __syncthreads();            // drain
+    if (live) {                                                  // every variable from the stage that owns it; the rest from stage 0
+        R* st = reinterpret_cast<R*>(a.state) + s;
+        const long long ns = a.n_streams;
+#pragma unroll
+        for (int k = 0; k < S::kVars; ++k)
+            if (P::owner(k) == K) st[(long long)k * ns] = v[k];
+        if (first) {
+#pragma unroll
+            for (int k = 0; k < 64; ++k) st[(long long)(S::kVars + k) * ns] = c.sliders[k];
+            st[(long long)(S::kVars + 64) * ns] = valid ? (R)1 : (R)0;
+        }
+        if (c.amax >= c.cap || c.amax32 >= (int)c.cap) *c.err = 1;
+    }
+}
+
+template <class S, typename R, bool TAP, int K>
+__device__ __forceinline__ void staged_pick(const GenLaunch& a, R* mb, float* tiles, int warp, int lane, int s0)
+{
+    if constexpr (K < S::Staged::kStages) {
+        if (warp == K) staged_role<S, R, TAP, K>(a, mb, tiles, lane, s0);
+        else staged_pick<S, R, TAP, K + 1>(a, mb, tiles, warp, lane, s0);
+    }
+}
+
+template <class S, typename R, bool TAP>
+__global__ void __launch_bounds__(32 * S::Staged::kStages, 1) jsfx_staged_kernel(const GenLaunch a)
+{
+    extern __shared__ __align__(16) unsigned char staged_smem_raw[];
+    R* mb = reinterpret_cast<R*>(staged_smem_raw);
+    float* tiles = reinterpret_cast<float*>(staged_smem_raw + (size_t)S::Staged::kMailSlots * staged_frames<S, R>() * 32 * sizeof(R));
+    staged_pick<S, R, TAP, 0>(a, mb, tiles, threadIdx.x >> 5, threadIdx.x & 31, blockIdx.x * 32);
+}
+
+template <class S> bool launch_staged(const GenLaunch& a, int precision, cudaStream_t st)
+{
+    const int blocks = (a.n_streams + 31) / 32;
+    auto go = [&](auto kern, size_t smem) {
+        if (smem > 48 * 1024 && !cuda_ok(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "jsfx_staged_kernel smem attr")) return false;
+        kern<<<blocks, 32 * S::Staged::kStages, smem, st>>>(a);
+        return cuda_ok(cudaGetLastError(), "jsfx_staged_kernel launch");
+    };
+    if (precision) return a.tap ? go(jsfx_staged_kernel<S, double, true>, staged_smem<S, double>()) : go(jsfx_staged_kernel<S, double, false>, staged_smem<S, double>());
+    return go(jsfx_staged_kernel<S, float, false>, staged_smem<S, float>());
+}
+
 template <class S> bool launch_prepare(const GenLaunch& a, int precision, cudaStream_t st)
 {
     const int blocks = (a.n_streams + 31) / 32;
@@ -611,6 +771,9 @@ template <class S> bool launch_process(const GenLaunch& a, int precision, cudaSt
     // 128 one-warp CTAs and as 64 two-warp CTAs, 520 ms with 8 streams per warp (less divergence per warp), and the
     // concurrent cfg5 mix loses 15 % with narrow warps (a warp with 8 live lanes costs a full issue slot).  Only a shorter
     // chain per frame or time-parallel kernels (the scan kernels) make these leaves faster.
+    if constexpr (S::Staged::kStages > 1) {
+        if (!a.unstaged) return launch_staged<S>(a, precision, st);
+    }
     GenLaunch b = a;
     int L = a.lanes, W = GenWarps<S>::value;
     auto smem_of = [&](int w, int l) { return (size_t)w * 2 * S::kCh * l * (TileFrames<S>::value + 1) * sizeof(float); };
@@ -685,7 +848,10 @@ template <class S, typename R> void emu_process(const GenLaunch& a)
 }  // namespace jsfx
 }  // namespace za
 
-// Emitted at the end of every generated translation unit.
+// Emitted at the end of every generated translation unit.  (A unit with a stage pipeline defines ZA_JSFX_STAGED_IMPL first.)
+#ifndef ZA_JSFX_STAGED_IMPL
+#define ZA_JSFX_STAGED_IMPL ::za::jsfx::NoStages
+#endif
 #ifdef ZA_JSFX_HOST_EMU
 #define ZA_JSFX_DEFINE_PLUGIN(IDENT, KEY, MEM_SLOTS, HAS_BLOCK, HAS_SLIDER)                                            \
     struct Script {                                                                                                     \
@@ -714,6 +880,7 @@ template <class S, typename R> void emu_process(const GenLaunch& a)
         static constexpr int kVars = g_##IDENT::kVars, kIn = g_##IDENT::kIn, kOut = g_##IDENT::kOut, kCh = g_##IDENT::kCh, kDecl = g_##IDENT::kDecl; \
         static constexpr long long kMemSlots = (MEM_SLOTS);                                                             \
         static constexpr long long kFftScratch = g_##IDENT::kFftScratch;                                                \
+        using Staged = ZA_JSFX_STAGED_IMPL;                                                                             \
         static __host__ __device__ constexpr int alias(int i0) { return g_##IDENT::alias_slot(i0); }                    \
         static __host__ __device__ constexpr int decl(int j) { return g_##IDENT::decl_slot(j); }                        \
         template <typename R> static __device__ __forceinline__ void init(Rt<R>& c, R* v) { sec_init<R>(c, v); }       \

@@ -34,7 +34,7 @@ class GenericPlugin : public PluginImpl {
         a.mem_slots = I.opt_heap_slots > 0 ? std::min<int64_t>(I.opt_heap_slots, d_->mem_slots) : d_->mem_slots;   // (tests shrink the heap to provoke the overflow path)
         a.n_streams = I.n_streams; a.block_len = I.block_len; a.n_decl = (int)I.decls.size();
         a.decl_index0 = d_index0; a.state = d_state; a.mem = d_mem; a.mt = d_mt; a.err = d_err; a.srate = I.srate;
-        a.fft_scratch = d_->fft_scratch; a.tw = d_tw; a.lanes = I.opt_lanes;
+        a.fft_scratch = d_->fft_scratch; a.tw = d_tw; a.lanes = I.opt_lanes; a.unstaged = I.opt_unstaged;
         return a;
     }
     std::vector<double> q_last;     // rows already on the device: static parameters are not uploaded again (a pageable

@@ -699,6 +699,7 @@ ZA_API int za_gpu_set_option(za_gpu_handle h, const char* name, int value)
     else if (!std::strcmp(name, "scalar_f32")) I.opt_scalar_f32 = value;
     else if (!std::strcmp(name, "heap_slots")) I.opt_heap_slots = value;
     else if (!std::strcmp(name, "copy_only")) I.opt_copy_only = value;
+    else if (!std::strcmp(name, "unstaged")) I.opt_unstaged = value;        // translated leaves with a stage pipeline: 1 = the one-thread-per-stream kernel (cross-check)
     else if (!std::strcmp(name, "lanes_per_warp")) I.opt_lanes = value;     // stream-per-thread kernels: 8 / 16 streams per warp instead of 32 (measurement)
     else if (!std::strcmp(name, "role_off")) I.opt_role_off = value;      // measurement only: warp roles of a pipeline kernel that skip their work
     else { set_error(std::string("unknown option ") + name); return ZA_ERR_ARG; }

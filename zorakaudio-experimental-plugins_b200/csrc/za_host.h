@@ -115,7 +115,7 @@ struct Instance {
     std::unique_ptr<PluginImpl> impl;
     int64_t launches = 0;
     // options
-    int opt_force_generic = 0, opt_warps = 0, opt_host_chunk = 0, opt_nbuf = 0, opt_scalar_f32 = 0, opt_heap_slots = 0, opt_copy_only = 0, opt_role_off = 0, opt_lanes = 0;
+    int opt_force_generic = 0, opt_warps = 0, opt_host_chunk = 0, opt_nbuf = 0, opt_scalar_f32 = 0, opt_heap_slots = 0, opt_copy_only = 0, opt_role_off = 0, opt_lanes = 0, opt_unstaged = 0;
     int create_status = ZA_ERR_CUDA;         // what za_gpu_create returns when impl->create() fails (a refusal sets ZA_ERR_UNSUPPORTED)
     // timing of the dominant kernel
     std::vector<cudaEvent_t> ev;             // pairs

@@ -436,7 +436,12 @@ class Unit:
         self.spec = {}            # (section, fn) -> C name
         self.spec_code = []       # emitted function definitions, callee first
         self.in_progress = set()
-        self.body = {s: Emitter(self, s, {}, set()).run(self.progs[s]) for s in SECTIONS}
+        self.fn_trace = {}        # specialised function -> access trace of its body (stage planner)
+        self.body, self.trace, self.stmt_lines = {}, {}, {}
+        for s in SECTIONS:
+            em = Emitter(self, s, {}, set())
+            self.body[s] = em.run(self.progs[s])
+            self.trace[s], self.stmt_lines[s] = em.trace, em.stmt_lines
         self.n_in, self.n_out = pin_counts(header, self.spl_reads, self.spl_writes)
         self.alias = {}           # slider index0 -> var name
         for l in self.slider_lines:
@@ -488,6 +493,7 @@ class Unit:
         args = "".join(f", R p_{re.sub(r'[^A-Za-z0-9_]', '_', p)}" for p in params)
         code = [f"template <typename R> __device__ ZA_JSFX_FN R {cn}(Rt<R>& c, R* v{args})", "{"] + em.lines + [f"    return {val};", "}", ""]
         self.spec_code += code
+        self.fn_trace[cn] = em.trace
         self.in_progress.discard(key)
         self.spec[key] = cn
         return cn
@@ -507,11 +513,19 @@ class Emitter:
         self.u, self.section, self.local_map, self.params = unit, section, local_map, params
         self.instance_map, self.namespace = instance_map or {}, namespace
         self.lines, self.n, self.ind = [], 0, 1
+        # what the stage planner reads (plan_stages): ("acc", key, read, write) per variable / heap / PRNG access in evaluation
+        # order, ("if",) ("else",) ("endif",) ("loop",) ("endloop",) around conditional code, ("call", fn) for user functions
+        self.trace, self.stmt_lines = [], []
 
     def run(self, prog):
-        for n in prog:
+        for i, n in enumerate(prog):
+            self.stmt_lines.append(len(self.lines))
+            self.trace.append(("stmt", i))
             self.ex(n)
         return self.lines
+
+    def acc(self, key, read, write):
+        self.trace.append(("acc", key, read, write))
 
     def w(self, s):
         self.lines.append("    " * self.ind + s)
@@ -524,6 +538,12 @@ class Emitter:
 
     # ---- variables --------------------------------------------------------------------------------------
     def ref(self, name: str, write: bool = False, read: bool = True) -> str:
+        r = self._ref(name, write, read)
+        if not r.startswith("p_"):
+            self.acc(r.split(" /*")[0], read, write)
+        return r
+
+    def _ref(self, name: str, write: bool = False, read: bool = True) -> str:
         if name in self.params:
             return "p_" + re.sub(r"[^A-Za-z0-9_]", "_", name)
         if name in self.local_map:
@@ -578,6 +598,7 @@ class Emitter:
             return self.tmp(self.ref(name))
         if k == "index":
             b = self.ex(n[1]); i = self.ex(n[2])
+            self.acc("__mem", True, False)
             return self.tmp(f"c.ldi(c.addr1({i}))" if b == "R(0)" else f"c.ld({b}, {i})")
         if k == "un":
             a = self.ex(n[2])
@@ -590,11 +611,14 @@ class Emitter:
             c = self.ex(n[1])
             t = self.tmp()
             self.w(f"if (truthy_({c})) {{"); self.ind += 1
+            self.trace.append(("if",))
             a = self.ex(n[2]); self.w(f"{t} = {a};"); self.ind -= 1
             self.w("} else {"); self.ind += 1
+            self.trace.append(("else",))
             b = self.ex(n[3]) if n[3] is not None else "R(0)"
             self.w(f"{t} = {b};"); self.ind -= 1
             self.w("}")
+            self.trace.append(("endif",))
             return t
         if k == "seq":
             v = "R(0)"
@@ -607,14 +631,18 @@ class Emitter:
             self.n += 1
             i = f"i{self.n}"
             self.w(f"for (long long {i} = 0, n{i} = to_count({cnt}); {i} < n{i}; ++{i}) {{"); self.ind += 1
+            self.trace.append(("loop",))
             v = self.ex(n[2]); self.w(f"{t} = {v};"); self.ind -= 1
             self.w("}")
+            self.trace.append(("endloop",))
             return t
         if k == "while":
             self.w("for (;;) {"); self.ind += 1
+            self.trace.append(("loop",))
             c = self.ex(n[1]); self.w(f"if (!truthy_({c})) break;")
             self.ex(n[2]); self.ind -= 1
             self.w("}")
+            self.trace.append(("endloop",))
             return "R(0)"
         if k == "bin":
             op = n[1]
@@ -622,8 +650,10 @@ class Emitter:
                 l = self.ex(n[2])
                 t = self.tmp("R(1)" if op == "||" else "R(0)")
                 self.w(f"if ({'!' if op == '||' else ''}truthy_({l})) {{"); self.ind += 1
+                self.trace.append(("if",))
                 r = self.ex(n[3]); self.w(f"{t} = truthy_({r}) ? R(1) : R(0);"); self.ind -= 1
                 self.w("}")
+                self.trace += [("else",), ("endif",)]
                 return t
             l = self.ex(n[2]); r = self.ex(n[3])
             return self.tmp(self.binop(op, l, r))
@@ -642,6 +672,7 @@ class Emitter:
                 b = self.ex(tgt[1]); i = self.ex(tgt[2])
                 self.n += 1
                 a = f"a{self.n}"
+                self.acc("__mem", True, True)
                 self.w(f"const auto {a} = c.addr1({i});" if b == "R(0)" else f"const auto {a} = c.addr({b}, {i});")
                 if op == "=":
                     self.w(f"c.st({a}, {rhs});")
@@ -651,6 +682,7 @@ class Emitter:
                 self.w(f"c.st({a}, {out});")
                 return out
             # slider(i) / spl(i)
+            self.acc("__dyn", True, True)
             idx = self.ex(tgt[2][0])
             arr = "sliders" if tgt[1] == "slider" else "spl"
             base = "to_i32(%s) - 1" % idx if tgt[1] == "slider" else "to_i32(%s)" % idx
@@ -706,6 +738,7 @@ class Emitter:
             want = len(self.u.fundefs[base][2])
             av = (av + ["R(0)"] * want)[:want]
             cn = self.u.specialise(self.section, base, call_ns)
+            self.trace.append(("call", cn))
             return self.tmp(f"{cn}<R>(c, v{''.join(', ' + a for a in av)})")
         if fn in ("sliderchange", "slider_automate") and 1 <= len(args) <= 2:
             # a direct sliderN argument is its bit (_emit_slider_mask_arg, :4133-4144); both builtins OR the mask into the pending
@@ -714,14 +747,17 @@ class Emitter:
             mask = lit(float(1 << (int(m.group(1)) - 1))) if m and 1 <= int(m.group(1)) <= 64 else self.ex(args[0])
             if len(args) == 2:
                 self.ex(args[1])
+            self.acc("__pending", True, True)
             return self.tmp(f"c.sliderchange({mask})")
         if fn in FFT_CALLS and len(args) == 2:             # runtime hooks (:5498-5564) -> per-stream device FFT on the heap (jsfx_rt.cuh)
             av = [self.ex(a) for a in args]
             self.u.uses_fft = True
+            self.acc("__mem", True, True)
             return self.tmp(FFT_CALLS[fn].format(*av))
         if fn == "convolve_c" and len(args) == 3:
             av = [self.ex(a) for a in args]
             self.u.uses_fft = True
+            self.acc("__mem", True, True)
             return self.tmp(f"c.convolve_c({av[0]}, {av[1]}, {av[2]})")
         if fn.startswith("gfx_") or fn in NOOP_CALLS or fn in ("slider_show", "freembuf"):
             for a in args:
@@ -743,7 +779,12 @@ class Emitter:
         if fn == "invsqrt" and len(av) == 1:
             return self.tmp(f"m_invsqrt({av[0]})")
         if fn == "rand" and len(av) <= 1:
+            self.acc("__mt", True, True)
             return self.tmp(f"c.rand({av[0] if av else 'R(1)'}, {1 if av else 0})")
+        if fn in ("memset", "memcpy") and len(av) == 3:
+            self.acc("__mem", True, True)
+        if fn in ("spl", "slider") and len(av) == 1:
+            self.acc("__dyn", True, True)
         if fn == "memset" and len(av) == 3:
             self.w(f"c.memset({av[0]}, {av[1]}, {av[2]});")
             return av[0]
@@ -755,6 +796,173 @@ class Emitter:
         if fn == "slider" and len(av) == 1:
             return self.tmp(f"c.slider_dyn({av[0]})")
         raise NotImplementedError(f"{self.u.key}: call {fn}/{len(av)}")
+
+
+# ------------------------------------------------------------------------------------------------------
+# stage planner: @sample cut into K consecutive groups of top-level statements, one warp per group (jsfx_rt.cuh,
+# jsfx_staged_kernel).  Stage k works on frame batch i - k while stage k + 1 works on batch i - k - 1, so a value may only
+# flow FORWARD within a frame; whatever a frame carries over to the next one must stay inside one stage.
+# ------------------------------------------------------------------------------------------------------
+STAGE_CUTS = {
+    # leaf -> ([variables whose first top-level assignment opens a new stage], {special keys allowed in several stages})
+    # SOMA: detector + look-ahead ring | gain computer | add-back filters, saturator, motion noise | ceiling guards, meters,
+    # history.  The heap is touched by the first stage (look-ahead rings) and the last (history arrays): disjoint regions.
+    "SOMA": (["depth_now", "add_lp120L", "safety_gain"], ("__mem",)),
+}
+
+
+class StagePlan:
+    pass
+
+
+def plan_stages(u: "Unit", cut_vars, n_ch: int, n_out: int, allow=()):
+    prog = u.progs["sample"]
+    cuts = []
+    for name in cut_vars:
+        hit = [i for i, n in enumerate(prog) if n[0] == "assign" and n[2] == ("var", name)]
+        if not hit:
+            raise ValueError(f"{u.key}: no top-level assignment to {name}")
+        cuts.append(hit[0])
+    if cuts != sorted(set(cuts)) or (cuts and cuts[0] == 0):
+        raise ValueError(f"{u.key}: stage cuts out of order: {cuts}")
+    K = len(cuts) + 1
+    special = ("__mem", "__mt", "__pending")
+    lw, writers, D = {}, {}, set()
+    exposed, imports, special_stages = set(), {}, {k: set() for k in special}
+    for ch in range(n_ch):                                 # the frame prologue of stage 0 sets every channel
+        lw[f"c.spl[{ch}]"] = 0; D.add(f"c.spl[{ch}]")
+    state = {"stage": 0, "cond": 0, "D": D}
+    stack = []
+
+    def access(key, r, w):
+        st = state["stage"]
+        if key == "__dyn":
+            raise ValueError(f"{u.key}: spl(i) / slider(i) with a computed index cannot be staged")
+        if key in special:
+            special_stages[key].add(st)
+            return
+        if r or (w and state["cond"] > 0):
+            if key in lw:
+                if lw[key] != st:
+                    imports[(key, st)] = lw[key]
+            elif key not in state["D"]:
+                exposed.add((st, key))
+        if w:
+            lw[key] = st
+            writers.setdefault(key, set()).add(st)
+            if state["cond"] == 0:
+                state["D"].add(key)
+
+    def walk(trace, top):
+        for ev in trace:
+            k = ev[0]
+            if k == "stmt":
+                if top:
+                    state["stage"] = sum(1 for c in cuts if ev[1] >= c)
+            elif k == "acc":
+                access(ev[1], ev[2], ev[3])
+            elif k == "if":
+                stack.append(["if", set(state["D"]), None]); state["cond"] += 1
+            elif k == "else":
+                stack[-1][2] = state["D"]; state["D"] = set(stack[-1][1])
+            elif k == "endif":
+                fr = stack.pop(); state["D"] = fr[2] & state["D"]; state["cond"] -= 1
+            elif k == "loop":
+                stack.append(["loop", set(state["D"])]); state["cond"] += 1
+            elif k == "endloop":
+                fr = stack.pop(); state["D"] = fr[1]; state["cond"] -= 1
+            elif k == "call":
+                walk(u.fn_trace[ev[1]], False)
+
+    walk(u.trace["sample"], True)
+    state["stage"] = K - 1
+    for ch in range(n_out):                                # the frame epilogue of the last stage stores the outputs
+        access(f"c.spl[{ch}]", True, False)
+    own = {k: max(v) for k, v in writers.items()}
+    bad = sorted(f"{k} (read at the frame start in stage {st}, written last in stage {own[k]})" for st, k in exposed if k in own and own[k] != st)
+    if bad:
+        raise ValueError(f"{u.key}: cut carries a value backwards: " + "; ".join(bad))
+    for k, st in special_stages.items():
+        if len(st) > 1 and k not in allow:
+            raise ValueError(f"{u.key}: {k} is used by stages {sorted(st)}")
+    for k in own:
+        if k.startswith("c.sliders["):
+            raise ValueError(f"{u.key}: @sample writes {k}")
+
+    # @slider / @block run in every stage warp on that warp's copy of the variables: they may not read what @sample computes,
+    # and must be repeatable (no heap stores, no rand)
+    def flat(trace, out):
+        for ev in trace:
+            if ev[0] == "acc":
+                out.append(ev)
+            elif ev[0] == "call":
+                flat(u.fn_trace[ev[1]], out)
+        return out
+    plan_block_writes = set()
+    for sec in ("slider", "block"):
+        for _, key, r, w in flat(u.trace[sec], []):
+            if w:
+                plan_block_writes.add(key)
+            if key in own and r and key not in allow:
+                raise ValueError(f"{u.key}: @{sec} reads {key}, which @sample writes")
+            if ((key == "__mem" and w) or key in ("__mt", "__dyn")) and f"{sec}:{key}" not in allow:
+                raise ValueError(f"{u.key}: @{sec} uses {key}")
+
+    plan = StagePlan()
+    plan.K, plan.cuts, plan.own = K, cuts, own
+    plan.block_writes = plan_block_writes
+    mails = {}                                             # (key, from) -> furthest consumer
+    for (key, to), frm in imports.items():
+        mails[(key, frm)] = max(mails.get((key, frm), 0), to)
+    plan.mail, off = {}, 0                                 # (key, from) -> (offset in slots, ring depth)
+    for (key, frm), to in sorted(mails.items(), key=lambda kv: (kv[0][1], kv[0][0])):
+        depth = 1
+        while depth < to - frm + 1:
+            depth *= 2
+        plan.mail[(key, frm)] = (off, depth); off += depth
+    plan.slots = off
+    plan.imports = [[(key, *plan.mail[(key, frm)]) for (key, to), frm in sorted(imports.items()) if to == k] for k in range(K)]
+    plan.exports = [[(key, *od) for (key, frm), od in sorted(plan.mail.items()) if frm == k] for k in range(K)]
+    plan.special = {k: sorted(v) for k, v in special_stages.items()}
+    return plan
+
+
+def emit_stages(u: "Unit", plan: StagePlan):
+    out = []
+    body, sl = u.body["sample"], u.stmt_lines["sample"] + [len(u.body["sample"])]
+    bounds = [0] + plan.cuts + [len(u.progs["sample"])]
+    out.append(f"// @sample as {plan.K} pipeline stages (one warp each, jsfx_staged_kernel): stage k runs statements {bounds} [k] .. [k+1] of")
+    out.append("// @sample; values that cross a cut travel through per-value rings in shared memory (mb: [slot][F frames][32 streams]).")
+    cell = lambda off, depth: f"mb[({off} + (bt & {depth - 1})) * (F * 32) + fl]"
+    for k in range(plan.K):
+        out.append(f"template <typename R, int F> __device__ __forceinline__ void stage{k}(Rt<R>& c, R* v, R* mb, int bt, int fl)")
+        out.append("{")
+        for key, off, depth in plan.imports[k]:
+            out.append(f"    {key} = {cell(off, depth)};")
+        out += body[sl[bounds[k]]:sl[bounds[k + 1]]]
+        for key, off, depth in plan.exports[k]:
+            out.append(f"    {cell(off, depth)} = {key};")
+        out.append("}")
+        out.append("")
+    out.append("struct StagedImpl {")
+    out.append(f"    static constexpr int kStages = {plan.K}, kMailSlots = {max(plan.slots, 1)};")
+    own = {key: 0 for key in plan.block_writes if key.startswith("v[")}
+    own.update({key: st for key, st in plan.own.items() if key.startswith("v[")})
+    for i0, nm in u.alias.items():                          # slider aliases are pushed per block
+        own.setdefault(f"v[{u.vars[nm]}]", 0)
+    sel = "".join(f"k == {int(key[2:-1])} ? {st} : " for key, st in sorted(own.items(), key=lambda kv: int(kv[0][2:-1])))
+    out.append("    // the stage whose copy of v[k] is the state at the end of a call (-1: nothing on the process path writes v[k])")
+    out.append(f"    static __host__ __device__ constexpr int owner(int k) {{ return {sel}-1; }}")
+    out.append("    template <typename R, int F, int K> static __device__ __forceinline__ void run(Rt<R>& c, R* v, R* mb, int bt, int fl)")
+    out.append("    {")
+    for k in range(plan.K):
+        out.append(f"        if constexpr (K == {k}) stage{k}<R, F>(c, v, mb, bt, fl);")
+    out.append("    }")
+    out.append("};")
+    out.append("#undef ZA_JSFX_STAGED_IMPL")
+    out.append("#define ZA_JSFX_STAGED_IMPL StagedImpl")
+    out.append("")
+    return out
 
 
 # ------------------------------------------------------------------------------------------------------
@@ -808,6 +1016,9 @@ def generate(key: str, jsfx_path: str, mem_slots: int, source_label: str, fft_ma
         out.append('    ""')
     out.append("    ;")
     out.append("")
+    if key in STAGE_CUTS:
+        cut_vars, allow = STAGE_CUTS[key]
+        out += emit_stages(u, plan_stages(u, cut_vars, nch, u.n_out, allow))
     out.append(f"ZA_JSFX_DEFINE_PLUGIN({ident}, \"{key}\", {mem_slots}, {1 if u.body['block'] else 0}, {1 if u.body['slider'] else 0})")
     out.append("")
     out.append("}}}  // namespace")
