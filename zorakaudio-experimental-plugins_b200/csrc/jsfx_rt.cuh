@@ -374,25 +374,46 @@ template <typename R> struct Rt {
     // MT19937, seed 0x4141F00D, lazily initialised while the index is 0 (:3880-4060); rand([max]) = genrand_int32 *
     // (1 / 0xFFFFFFFF) * max(1, floor(arg)) (:5294-5323)
     // (static: the context object itself never has its address taken, so its arrays can live in registers)
-    static __device__ __noinline__ unsigned genrand(unsigned* mt, long long stride)
+    // Slow path, out of line: lazy seeding (stored index 0) and the block regeneration (stored index 624).  The regeneration
+    // runs in groups of 8 words with all 17 loads of a group issued before its stores (word k needs the OLD words k, k + 1 and
+    // word k + 397, which is either old or was stored at least 227 words earlier): one memory latency per group instead of
+    // three per word -- with the one-word-at-a-time loop the state column in L2 made rand() 40 % of SOMA's frame time.
+    static __device__ __noinline__ void mt_refill(unsigned* mt, long long stride, unsigned idx)
     {
         const int N = 624, M = 397;
-        unsigned idx = mt[624 * stride];
         if (idx == 0) {
             unsigned prev = 0x4141F00Du;
             mt[0] = prev;
             for (int k = 1; k < N; ++k) { prev = 1812433253u * (prev ^ (prev >> 30)) + (unsigned)k; mt[k * stride] = prev; }
-            idx = N;
         }
-        if (idx >= (unsigned)N) {
-            for (int k = 0; k < N; ++k) {
-                const unsigned y = (mt[k * stride] & 0x80000000u) | (mt[((k + 1) % N) * stride] & 0x7fffffffu);
-                mt[k * stride] = mt[((k + M) % N) * stride] ^ (y >> 1) ^ ((y & 1u) ? 0x9908B0DFu : 0u);
+        for (int k0 = 0; k0 < N; k0 += 8) {                // 624 = 78 x 8
+            unsigned a[9], m[8];
+#pragma unroll
+            for (int j = 0; j < 9; ++j) a[j] = mt[((k0 + j) % N) * stride];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) m[j] = mt[((k0 + j + M) % N) * stride];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const unsigned y = (a[j] & 0x80000000u) | (a[j + 1] & 0x7fffffffu);
+                mt[(k0 + j) * stride] = m[j] ^ (y >> 1) ^ ((y & 1u) ? 0x9908B0DFu : 0u);
             }
-            idx = 0;
         }
-        unsigned y = mt[idx * stride];
-        mt[624 * stride] = idx + 1;
+    }
+    // Fast path: the index lives in a register for the length of a launch (the stored copy at word 624 is kept up to date), and
+    // the next two state words are fetched two draws ahead (mt_p0 = word idx, mt_p1 = word idx + 1), so a draw waits for no load.
+    unsigned mt_idx, mt_p0, mt_p1;
+    __device__ __forceinline__ unsigned genrand()
+    {
+        const unsigned N = 624;
+        bool reload = false;
+        if (mt_idx == 0xFFFFFFFFu) { mt_idx = mt[624 * stride]; reload = true; }      // first draw of this launch
+        if (mt_idx == 0 || mt_idx >= N) { mt_refill(mt, stride, mt_idx); mt_idx = 0; reload = true; }
+        if (reload) { mt_p0 = mt[mt_idx * stride]; mt_p1 = mt_idx + 1 < N ? mt[(mt_idx + 1) * stride] : 0u; }
+        unsigned y = mt_p0;
+        mt_p0 = mt_p1;
+        if (mt_idx + 2 < N) mt_p1 = mt[(mt_idx + 2) * stride];
+        mt_idx += 1;
+        mt[624 * stride] = mt_idx;
         y ^= y >> 11; y ^= (y << 7) & 0x9D2C5680u; y ^= (y << 15) & 0xEFC60000u; y ^= y >> 18;
         return y;
     }
@@ -400,7 +421,7 @@ template <typename R> struct Rt {
     {
         R mx = has_arg ? m_floor(arg) : (R)1;
         if (mx < (R)1) mx = (R)1;
-        const double r = __dmul_rn((double)genrand(mt, stride), 1.0 / 4294967295.0);
+        const double r = __dmul_rn((double)genrand(), 1.0 / 4294967295.0);
         return (R)__dmul_rn(r, (double)mx);
     }
 };
@@ -413,7 +434,7 @@ __device__ __forceinline__ void ctx_open(Rt<R>& c, R* v, const GenLaunch& a, int
 {
     const long long ns = a.n_streams;
     c.mem = reinterpret_cast<R*>(a.mem) + sc; c.stride = ns; c.cap = a.mem_slots;
-    c.mt = a.mt + sc; c.err = a.err; c.amax = -1; c.amax32 = -1;
+    c.mt = a.mt + sc; c.mt_idx = 0xFFFFFFFFu; c.mt_p0 = c.mt_p1 = 0u; c.err = a.err; c.amax = -1; c.amax32 = -1;
     c.cap32 = (int)a.mem_slots; c.stride_bytes = (unsigned)a.n_streams * (unsigned)sizeof(R);
     c.srate = (R)a.srate; c.samplesblock = (R)0; c.pending = 0;
     c.scr = a.mem_slots + 1; c.scr_n = a.fft_scratch; c.tw = a.tw;       // scratch sits behind the spare slot out-of-range accesses land in
