@@ -327,6 +327,7 @@ template <typename R> struct Rt {
     {
         return reinterpret_cast<R*>(reinterpret_cast<char*>(mem) + (unsigned long long)a * stride_bytes);
     }
+    int pf;                 // 1 in the stage pipelines (jsfx_staged_kernel): rand() reads its state through the shared-memory window
     __device__ __forceinline__ R ldi(long long a)
     {
         amax = a > amax ? a : amax;
@@ -375,7 +376,7 @@ template <typename R> struct Rt {
     // (1 / 0xFFFFFFFF) * max(1, floor(arg)) (:5294-5323)
     // (static: the context object itself never has its address taken, so its arrays can live in registers)
     // Slow path, out of line: lazy seeding (stored index 0) and the block regeneration (stored index 624).  The regeneration
-    // runs in groups of 8 words with all 17 loads of a group issued before its stores (word k needs the OLD words k, k + 1 and
+    // runs in groups of 24 words with all 49 loads of a group issued before its stores (word k needs the OLD words k, k + 1 and
     // word k + 397, which is either old or was stored at least 227 words earlier): one memory latency per group instead of
     // three per word -- with the one-word-at-a-time loop the state column in L2 made rand() 40 % of SOMA's frame time.
     static __device__ __noinline__ void mt_refill(unsigned* mt, long long stride, unsigned idx)
@@ -386,32 +387,53 @@ template <typename R> struct Rt {
             mt[0] = prev;
             for (int k = 1; k < N; ++k) { prev = 1812433253u * (prev ^ (prev >> 30)) + (unsigned)k; mt[k * stride] = prev; }
         }
-        for (int k0 = 0; k0 < N; k0 += 8) {                // 624 = 78 x 8
-            unsigned a[9], m[8];
+        constexpr int G = 24;                              // 624 = 26 x 24
+        for (int k0 = 0; k0 < N; k0 += G) {
+            unsigned a[G + 1], m[G];
 #pragma unroll
-            for (int j = 0; j < 9; ++j) a[j] = mt[((k0 + j) % N) * stride];
+            for (int j = 0; j < G + 1; ++j) a[j] = mt[((k0 + j) % N) * stride];
 #pragma unroll
-            for (int j = 0; j < 8; ++j) m[j] = mt[((k0 + j + M) % N) * stride];
+            for (int j = 0; j < G; ++j) m[j] = mt[((k0 + j + M) % N) * stride];
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
+            for (int j = 0; j < G; ++j) {
                 const unsigned y = (a[j] & 0x80000000u) | (a[j + 1] & 0x7fffffffu);
                 mt[(k0 + j) * stride] = m[j] ^ (y >> 1) ^ ((y & 1u) ? 0x9908B0DFu : 0u);
             }
         }
     }
-    // Fast path: the index lives in a register for the length of a launch (the stored copy at word 624 is kept up to date), and
-    // the next two state words are fetched two draws ahead (mt_p0 = word idx, mt_p1 = word idx + 1), so a draw waits for no load.
-    unsigned mt_idx, mt_p0, mt_p1;
+    // Fast path: the index lives in a register for the length of a launch (the stored copy at word 624 is kept up to date).
+    // Stage pipelines (mtw != nullptr, flag pf) also keep a 16-word window of the column in shared memory, filled by 4-byte
+    // cp.async eight draws ahead: one commit group per draw (empty past word 623), so `wait_group 8` is exactly "the word of this
+    // draw has landed" and a draw never waits for L2.  (Measured alternatives: words held in registers make the draw wait on
+    // the loads in flight as soon as they are shifted or selected; prefetch.global.L1 eight draws ahead changed nothing.)
+    unsigned mt_idx;
+    unsigned* mtw;                                         // this lane's column of the window: word k at mtw[(k & 15) * 32]
+    __device__ __forceinline__ void mt_fetch(unsigned k)
+    {
+        if (k < 624u) {
+            const unsigned d = (unsigned)__cvta_generic_to_shared(mtw + (k & 15u) * 32u);
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(mt + (long long)k * stride) : "memory");
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
     __device__ __forceinline__ unsigned genrand()
     {
-        const unsigned N = 624;
-        bool reload = false;
-        if (mt_idx == 0xFFFFFFFFu) { mt_idx = mt[624 * stride]; reload = true; }      // first draw of this launch
-        if (mt_idx == 0 || mt_idx >= N) { mt_refill(mt, stride, mt_idx); mt_idx = 0; reload = true; }
-        if (reload) { mt_p0 = mt[mt_idx * stride]; mt_p1 = mt_idx + 1 < N ? mt[(mt_idx + 1) * stride] : 0u; }
-        unsigned y = mt_p0;
-        mt_p0 = mt_p1;
-        if (mt_idx + 2 < N) mt_p1 = mt[(mt_idx + 2) * stride];
+        const unsigned N = 624, kAhead = 8;
+        bool fill = false;
+        if (mt_idx == 0xFFFFFFFFu) { mt_idx = mt[624 * stride]; fill = true; }        // first draw of this launch
+        if (mt_idx == 0 || mt_idx >= N) { mt_refill(mt, stride, mt_idx); mt_idx = 0; fill = true; }
+        unsigned y;
+        if (pf) {
+            if (fill) {
+                __threadfence_block();
+                for (unsigned d = 0; d < kAhead; ++d) mt_fetch(mt_idx + d);
+            }
+            mt_fetch(mt_idx + kAhead);
+            asm volatile("cp.async.wait_group 8;" ::: "memory");
+            y = mtw[(mt_idx & 15u) * 32u];
+        } else {
+            y = mt[mt_idx * stride];
+        }
         mt_idx += 1;
         mt[624 * stride] = mt_idx;
         y ^= y >> 11; y ^= (y << 7) & 0x9D2C5680u; y ^= (y << 15) & 0xEFC60000u; y ^= y >> 18;
@@ -434,7 +456,7 @@ __device__ __forceinline__ void ctx_open(Rt<R>& c, R* v, const GenLaunch& a, int
 {
     const long long ns = a.n_streams;
     c.mem = reinterpret_cast<R*>(a.mem) + sc; c.stride = ns; c.cap = a.mem_slots;
-    c.mt = a.mt + sc; c.mt_idx = 0xFFFFFFFFu; c.mt_p0 = c.mt_p1 = 0u; c.err = a.err; c.amax = -1; c.amax32 = -1;
+    c.mt = a.mt + sc; c.mt_idx = 0xFFFFFFFFu; c.mtw = nullptr; c.pf = 0; c.err = a.err; c.amax = -1; c.amax32 = -1;
     c.cap32 = (int)a.mem_slots; c.stride_bytes = (unsigned)a.n_streams * (unsigned)sizeof(R);
     c.srate = (R)a.srate; c.samplesblock = (R)0; c.pending = 0;
     c.scr = a.mem_slots + 1; c.scr_n = a.fft_scratch; c.tw = a.tw;       // scratch sits behind the spare slot out-of-range accesses land in
@@ -628,15 +650,20 @@ __global__ void __launch_bounds__(128, 1) jsfx_process_kernel(const GenLaunch a)
 // values: in float64 the outputs and states are bit-identical to jsfx_process_kernel.
 struct NoStages { static constexpr int kStages = 1, kMailSlots = 1; };
 
-template <class S, typename R> __host__ __device__ constexpr int staged_frames()     // frames per batch: rings of at most 72 KB (two CTAs per SM)
+// shared memory of a CTA: [rings][audio tiles: 2 x kIn in, kOut out][MT19937 window]
+template <class S> __host__ __device__ constexpr size_t staged_fixed_smem()
+{
+    return (size_t)(2 * S::kIn + S::kOut) * 32 * 33 * sizeof(float) + 16 * 32 * sizeof(unsigned);
+}
+template <class S, typename R> __host__ __device__ constexpr int staged_frames()     // frames per batch: two CTAs per SM (110 KB each)
 {
     int f = 32;
-    while (f > 2 && (size_t)S::Staged::kMailSlots * f * 32 * sizeof(R) > 72 * 1024) f >>= 1;
+    while (f > 2 && (size_t)S::Staged::kMailSlots * f * 32 * sizeof(R) + staged_fixed_smem<S>() > 110 * 1024) f >>= 1;
     return f;
 }
 template <class S, typename R> __host__ __device__ constexpr size_t staged_smem()
 {
-    return (size_t)S::Staged::kMailSlots * staged_frames<S, R>() * 32 * sizeof(R) + (size_t)(2 * S::kIn + S::kOut) * 32 * 33 * sizeof(float);
+    return (size_t)S::Staged::kMailSlots * staged_frames<S, R>() * 32 * sizeof(R) + staged_fixed_smem<S>();
 }
 
 template <class S, typename R, bool TAP, int K>
@@ -654,6 +681,8 @@ __device__ __forceinline__ void staged_role(const GenLaunch& a, R* mb, float* ti
     bool valid = false;
     if (live) {
         ctx_open<S, R>(c, v, a, s);
+        c.pf = 1;
+        c.mtw = reinterpret_cast<unsigned*>(tiles + (2 * S::kIn + S::kOut) * 32 * kP) + lane;
         valid = reinterpret_cast<const R*>(a.state)[(long long)(S::kVars + 64) * a.n_streams + s] != (R)0;
     }
     auto fetch = [&](float* tile, int64_t frame0, int nf) {
@@ -757,7 +786,7 @@ __device__ __forceinline__ void staged_pick(const GenLaunch& a, R* mb, float* ti
 }
 
 template <class S, typename R, bool TAP>
-__global__ void __launch_bounds__(32 * S::Staged::kStages, 1) jsfx_staged_kernel(const GenLaunch a)
+__global__ void __launch_bounds__(32 * S::Staged::kStages, S::Staged::kStages > 4 ? 2 : 1) jsfx_staged_kernel(const GenLaunch a)
 {
     extern __shared__ __align__(16) unsigned char staged_smem_raw[];
     R* mb = reinterpret_cast<R*>(staged_smem_raw);

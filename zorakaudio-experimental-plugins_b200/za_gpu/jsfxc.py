@@ -805,9 +805,16 @@ class Emitter:
 # ------------------------------------------------------------------------------------------------------
 STAGE_CUTS = {
     # leaf -> ([variables whose first top-level assignment opens a new stage], {special keys allowed in several stages})
-    # SOMA: detector + look-ahead ring | gain computer | add-back filters, saturator, motion noise | ceiling guards, meters,
-    # history.  The heap is touched by the first stage (look-ahead rings) and the last (history arrays): disjoint regions.
-    "SOMA": (["depth_now", "add_lp120L", "safety_gain"], ("__mem",)),
+    # SOMA: drive + look-ahead ring | detector | gain computer | add-back filters + presence | body saturator, motion noise,
+    # sum | ceiling guards, meters, history.  The heap is touched by the first stage (look-ahead rings) and the last (history
+    # arrays): disjoint regions.
+    "SOMA": (["absL", "depth_now", "add_lp120L", "bodyDrive", "safety_gain"], ("__mem",)),
+    # RTT: band powers | envelope followers | voice / other excess | permissions | guard + references | tail seed and age |
+    # threshold + target | gain smoothing + output.  `prev_ref_off = ref_off` (last statement) moves up behind its only reader.
+    "RTT": (["Ey", "v_exc", "Eo_db", "guard_tgt", "tail_seed_ratio_db", "age_w", "tgt_db_sm"], (), ("prev_ref_off",)),
+    # ATTACK reuses its temporaries (s, v, oldvS) in every band block, so its cuts are statement numbers: band split | slopes of
+    # the low and mid band | slopes of the high band + magnitudes | reference followers | ratios | envelopes | gains + output
+    "ATTACK": ([20, 52, 80, 92, 104, 105], ()),
 }
 
 
@@ -815,11 +822,47 @@ class StagePlan:
     pass
 
 
-def plan_stages(u: "Unit", cut_vars, n_ch: int, n_out: int, allow=()):
+def plan_stages(u: "Unit", cut_vars, n_ch: int, n_out: int, allow=(), moves=()):
     prog = u.progs["sample"]
+    # per-statement pieces of the access trace
+    segs, cur = [], None
+    for ev in u.trace["sample"]:
+        if ev[0] == "stmt":
+            cur = []; segs.append(cur)
+        else:
+            cur.append(ev)
+
+    def flat(trace, out):
+        for ev in trace:
+            if ev[0] == "acc":
+                out.append(ev)
+            elif ev[0] == "call":
+                flat(u.fn_trace[ev[1]], out)
+        return out
+    # moves: the LAST top-level `x = ...` is hoisted to just behind the last earlier statement that touches x (a trailing
+    # `prev = cur` would otherwise tie the first reader of prev and the end of @sample into one stage).  Legal when nothing
+    # in between writes what the moved statement reads.
+    order = list(range(len(prog)))
+    for name in moves:
+        src = [i for i, n in enumerate(prog) if n[0] == "assign" and n[1] == "=" and n[2] == ("var", name)][-1]
+        key = f"v[{u.vars[name]}]"
+        mine = flat(segs[src], [])
+        if any(k.startswith("__") for _, k, _, _ in mine):
+            raise ValueError(f"{u.key}: cannot move the assignment to {name}")
+        reads = {k for _, k, r, _ in mine if r}
+        pos = order.index(src)
+        dst = pos
+        while dst > 0 and not any(k == key for _, k, _, _ in flat(segs[order[dst - 1]], [])):
+            if any(w and k in reads for _, k, _, w in flat(segs[order[dst - 1]], [])):
+                raise ValueError(f"{u.key}: moving the assignment to {name} would cross a write of what it reads")
+            dst -= 1
+        order.insert(dst, order.pop(pos))
     cuts = []
     for name in cut_vars:
-        hit = [i for i, n in enumerate(prog) if n[0] == "assign" and n[2] == ("var", name)]
+        if isinstance(name, int) or name.isdigit():        # a statement number (scripts that reuse their temporaries)
+            cuts.append(order.index(int(name)))
+            continue
+        hit = [j for j, i in enumerate(order) if prog[i][0] == "assign" and prog[i][2] == ("var", name)]
         if not hit:
             raise ValueError(f"{u.key}: no top-level assignment to {name}")
         cuts.append(hit[0])
@@ -856,10 +899,7 @@ def plan_stages(u: "Unit", cut_vars, n_ch: int, n_out: int, allow=()):
     def walk(trace, top):
         for ev in trace:
             k = ev[0]
-            if k == "stmt":
-                if top:
-                    state["stage"] = sum(1 for c in cuts if ev[1] >= c)
-            elif k == "acc":
+            if k == "acc":
                 access(ev[1], ev[2], ev[3])
             elif k == "if":
                 stack.append(["if", set(state["D"]), None]); state["cond"] += 1
@@ -874,7 +914,9 @@ def plan_stages(u: "Unit", cut_vars, n_ch: int, n_out: int, allow=()):
             elif k == "call":
                 walk(u.fn_trace[ev[1]], False)
 
-    walk(u.trace["sample"], True)
+    for j, i in enumerate(order):
+        state["stage"] = sum(1 for c in cuts if j >= c)
+        walk(segs[i], True)
     state["stage"] = K - 1
     for ch in range(n_out):                                # the frame epilogue of the last stage stores the outputs
         access(f"c.spl[{ch}]", True, False)
@@ -891,13 +933,6 @@ def plan_stages(u: "Unit", cut_vars, n_ch: int, n_out: int, allow=()):
 
     # @slider / @block run in every stage warp on that warp's copy of the variables: they may not read what @sample computes,
     # and must be repeatable (no heap stores, no rand)
-    def flat(trace, out):
-        for ev in trace:
-            if ev[0] == "acc":
-                out.append(ev)
-            elif ev[0] == "call":
-                flat(u.fn_trace[ev[1]], out)
-        return out
     plan_block_writes = set()
     for sec in ("slider", "block"):
         for _, key, r, w in flat(u.trace[sec], []):
@@ -909,7 +944,7 @@ def plan_stages(u: "Unit", cut_vars, n_ch: int, n_out: int, allow=()):
                 raise ValueError(f"{u.key}: @{sec} uses {key}")
 
     plan = StagePlan()
-    plan.K, plan.cuts, plan.own = K, cuts, own
+    plan.K, plan.cuts, plan.own, plan.order = K, cuts, own, order
     plan.block_writes = plan_block_writes
     mails = {}                                             # (key, from) -> furthest consumer
     for (key, to), frm in imports.items():
@@ -931,15 +966,18 @@ def emit_stages(u: "Unit", plan: StagePlan):
     out = []
     body, sl = u.body["sample"], u.stmt_lines["sample"] + [len(u.body["sample"])]
     bounds = [0] + plan.cuts + [len(u.progs["sample"])]
+    moved = [i for j, i in enumerate(plan.order) if i != j and (j == 0 or plan.order[j - 1] != i - 1) and i > j]
     out.append(f"// @sample as {plan.K} pipeline stages (one warp each, jsfx_staged_kernel): stage k runs statements {bounds} [k] .. [k+1] of")
-    out.append("// @sample; values that cross a cut travel through per-value rings in shared memory (mb: [slot][F frames][32 streams]).")
+    out.append("// @sample; values that cross a cut travel through per-value rings in shared memory (mb: [slot][F frames][32 streams])."
+               + (f"  Statements hoisted: {moved}." if moved else ""))
     cell = lambda off, depth: f"mb[({off} + (bt & {depth - 1})) * (F * 32) + fl]"
     for k in range(plan.K):
         out.append(f"template <typename R, int F> __device__ __forceinline__ void stage{k}(Rt<R>& c, R* v, R* mb, int bt, int fl)")
         out.append("{")
         for key, off, depth in plan.imports[k]:
             out.append(f"    {key} = {cell(off, depth)};")
-        out += body[sl[bounds[k]]:sl[bounds[k + 1]]]
+        for i in plan.order[bounds[k]:bounds[k + 1]]:
+            out += body[sl[i]:sl[i + 1]]
         for key, off, depth in plan.exports[k]:
             out.append(f"    {cell(off, depth)} = {key};")
         out.append("}")
@@ -1017,8 +1055,8 @@ def generate(key: str, jsfx_path: str, mem_slots: int, source_label: str, fft_ma
     out.append("    ;")
     out.append("")
     if key in STAGE_CUTS:
-        cut_vars, allow = STAGE_CUTS[key]
-        out += emit_stages(u, plan_stages(u, cut_vars, nch, u.n_out, allow))
+        cut_vars, allow, *moves = STAGE_CUTS[key]
+        out += emit_stages(u, plan_stages(u, cut_vars, nch, u.n_out, allow, moves[0] if moves else ()))
     out.append(f"ZA_JSFX_DEFINE_PLUGIN({ident}, \"{key}\", {mem_slots}, {1 if u.body['block'] else 0}, {1 if u.body['slider'] else 0})")
     out.append("")
     out.append("}}}  // namespace")
