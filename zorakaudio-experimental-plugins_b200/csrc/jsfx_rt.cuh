@@ -649,16 +649,28 @@ __global__ void __launch_bounds__(128, 1) jsfx_process_kernel(const GenLaunch a)
 // the furthest consumer + 1), one __syncthreads per batch of F frames.  Same statements in the same order on the same
 // values: in float64 the outputs and states are bit-identical to jsfx_process_kernel.
 struct NoStages { static constexpr int kStages = 1, kMailSlots = 1; };
+// batch number of a stage modulo every ring depth a plan can ask for (2 .. 9), kept incrementally
+struct BatchMod {
+    int r2 = 0, r3 = 0, r4 = 0, r5 = 0, r6 = 0, r7 = 0, r8 = 0, r9 = 0;
+    __device__ __forceinline__ void next()
+    {
+        r2 = r2 + 1 == 2 ? 0 : r2 + 1; r3 = r3 + 1 == 3 ? 0 : r3 + 1; r4 = r4 + 1 == 4 ? 0 : r4 + 1; r5 = r5 + 1 == 5 ? 0 : r5 + 1;
+        r6 = r6 + 1 == 6 ? 0 : r6 + 1; r7 = r7 + 1 == 7 ? 0 : r7 + 1; r8 = r8 + 1 == 8 ? 0 : r8 + 1; r9 = r9 + 1 == 9 ? 0 : r9 + 1;
+    }
+};
 
 // shared memory of a CTA: [rings][audio tiles: 2 x kIn in, kOut out][MT19937 window]
+// frames per audio tile.  (16 for the 8-input RTT, which leaves its rings room for 5-frame instead of 2-frame batches, was
+// measured: 45.7 ms against 27.2 ms per 5041 x 1 s -- the first stage's warp pays for twice the copy instructions.)
+template <class S> __host__ __device__ constexpr int staged_tile_frames() { return 32; }
 template <class S> __host__ __device__ constexpr size_t staged_fixed_smem()
 {
-    return (size_t)(2 * S::kIn + S::kOut) * 32 * 33 * sizeof(float) + 16 * 32 * sizeof(unsigned);
+    return (size_t)(2 * S::kIn + S::kOut) * 32 * (staged_tile_frames<S>() + 1) * sizeof(float) + 16 * 32 * sizeof(unsigned);
 }
 template <class S, typename R> __host__ __device__ constexpr int staged_frames()     // frames per batch: two CTAs per SM (110 KB each)
 {
     int f = 32;
-    while (f > 2 && (size_t)S::Staged::kMailSlots * f * 32 * sizeof(R) + staged_fixed_smem<S>() > 110 * 1024) f >>= 1;
+    while (f > 2 && (size_t)S::Staged::kMailSlots * f * 32 * sizeof(R) + staged_fixed_smem<S>() > 110 * 1024) --f;
     return f;
 }
 template <class S, typename R> __host__ __device__ constexpr size_t staged_smem()
@@ -670,7 +682,8 @@ template <class S, typename R, bool TAP, int K>
 __device__ __forceinline__ void staged_role(const GenLaunch& a, R* mb, float* tiles, int lane, int s0)
 {
     using P = typename S::Staged;
-    constexpr int KS = P::kStages, F = staged_frames<S, R>(), kF = 32, kP = 33, kTile = S::kIn * 32 * kP;
+    constexpr int KS = P::kStages, F = staged_frames<S, R>(), kF = staged_tile_frames<S>(), kP = kF + 1, kTile = S::kIn * 32 * kP, kRows = 32 / kF;
+    const int half = lane / kF, fl = lane % kF;                  // tile I/O: kF lanes per row, lane = frame
     constexpr bool first = K == 0, last = K == KS - 1;
     const int s = s0 + lane;
     const bool live = s < a.n_streams;
@@ -687,14 +700,18 @@ __device__ __forceinline__ void staged_role(const GenLaunch& a, R* mb, float* ti
     }
     auto fetch = [&](float* tile, int64_t frame0, int nf) {
         const int nq = ns_cta * S::kIn;
-        const float* src = a.in + (size_t)s0 * S::kIn * a.row_stride + frame0 + (lane < nf ? lane : 0);
-        for (int q = 0; q < nq; ++q) cp_async4(tile + ((q % S::kIn) * 32 + q / S::kIn) * kP + lane, src + (size_t)q * a.row_stride, lane < nf);
+        const float* src = a.in + (size_t)s0 * S::kIn * a.row_stride + frame0 + (fl < nf ? fl : 0);
+        for (int q0 = 0; q0 < nq; q0 += kRows) {
+            const int q = q0 + half;
+            if (q < nq) cp_async4(tile + ((q % S::kIn) * 32 + q / S::kIn) * kP + fl, src + (size_t)q * a.row_stride, fl < nf);
+        }
         asm volatile("cp.async.commit_group;" ::: "memory");
     };
     for (int j = 0; j < K; ++j) __syncthreads();                 // pipeline fill: batch 0 reaches this stage at iteration K
     int64_t pos = 0;
     int nb = (int)min((int64_t)a.block_len, a.n_frames - pos);
-    int buf = 0, bt = 0;
+    int buf = 0;
+    BatchMod bt;
     if (first && a.n_frames > 0) fetch(tiles, 0, min(kF, nb));
     for (int blk = 0; pos < a.n_frames; ++blk) {
         if (live) {
@@ -742,16 +759,19 @@ __device__ __forceinline__ void staged_role(const GenLaunch& a, R* mb, float* ti
                         }
                     }
                 }
-                ++bt;
+                bt.next();
                 __syncthreads();
             }
             if (last) {
                 __syncwarp();
                 const int nq = ns_cta * S::kOut;
-                float* dst = a.out + (size_t)s0 * S::kOut * a.row_stride + pos + f0 + lane;
-                if (lane < nf) {
+                float* dst = a.out + (size_t)s0 * S::kOut * a.row_stride + pos + f0 + fl;
+                if (fl < nf) {
 #pragma unroll 4
-                    for (int q = 0; q < nq; ++q) dst[(size_t)q * a.row_stride] = out_tile[((q % S::kOut) * 32 + q / S::kOut) * kP + lane];
+                    for (int q0 = 0; q0 < nq; q0 += kRows) {
+                        const int q = q0 + half;
+                        if (q < nq) dst[(size_t)q * a.row_stride] = out_tile[((q % S::kOut) * 32 + q / S::kOut) * kP + fl];
+                    }
                 }
                 __syncwarp();
             }

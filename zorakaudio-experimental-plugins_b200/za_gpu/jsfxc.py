@@ -951,9 +951,7 @@ def plan_stages(u: "Unit", cut_vars, n_ch: int, n_out: int, allow=(), moves=()):
         mails[(key, frm)] = max(mails.get((key, frm), 0), to)
     plan.mail, off = {}, 0                                 # (key, from) -> (offset in slots, ring depth)
     for (key, frm), to in sorted(mails.items(), key=lambda kv: (kv[0][1], kv[0][0])):
-        depth = 1
-        while depth < to - frm + 1:
-            depth *= 2
+        depth = to - frm + 1
         plan.mail[(key, frm)] = (off, depth); off += depth
     plan.slots = off
     plan.imports = [[(key, *plan.mail[(key, frm)]) for (key, to), frm in sorted(imports.items()) if to == k] for k in range(K)]
@@ -968,11 +966,11 @@ def emit_stages(u: "Unit", plan: StagePlan):
     bounds = [0] + plan.cuts + [len(u.progs["sample"])]
     moved = [i for j, i in enumerate(plan.order) if i != j and (j == 0 or plan.order[j - 1] != i - 1) and i > j]
     out.append(f"// @sample as {plan.K} pipeline stages (one warp each, jsfx_staged_kernel): stage k runs statements {bounds} [k] .. [k+1] of")
-    out.append("// @sample; values that cross a cut travel through per-value rings in shared memory (mb: [slot][F frames][32 streams])."
+    out.append("// @sample; values that cross a cut travel through per-value rings in shared memory (mb: [slot][F frames][32 streams]; ring depth = stages crossed + 1)."
                + (f"  Statements hoisted: {moved}." if moved else ""))
-    cell = lambda off, depth: f"mb[({off} + (bt & {depth - 1})) * (F * 32) + fl]"
+    cell = lambda off, depth: f"mb[({off} + bt.r{depth}) * (F * 32) + fl]"       # bt.rD = batch number mod D
     for k in range(plan.K):
-        out.append(f"template <typename R, int F> __device__ __forceinline__ void stage{k}(Rt<R>& c, R* v, R* mb, int bt, int fl)")
+        out.append(f"template <typename R, int F> __device__ __forceinline__ void stage{k}(Rt<R>& c, R* v, R* mb, const BatchMod& bt, int fl)")
         out.append("{")
         for key, off, depth in plan.imports[k]:
             out.append(f"    {key} = {cell(off, depth)};")
@@ -991,7 +989,7 @@ def emit_stages(u: "Unit", plan: StagePlan):
     sel = "".join(f"k == {int(key[2:-1])} ? {st} : " for key, st in sorted(own.items(), key=lambda kv: int(kv[0][2:-1])))
     out.append("    // the stage whose copy of v[k] is the state at the end of a call (-1: nothing on the process path writes v[k])")
     out.append(f"    static __host__ __device__ constexpr int owner(int k) {{ return {sel}-1; }}")
-    out.append("    template <typename R, int F, int K> static __device__ __forceinline__ void run(Rt<R>& c, R* v, R* mb, int bt, int fl)")
+    out.append("    template <typename R, int F, int K> static __device__ __forceinline__ void run(Rt<R>& c, R* v, R* mb, const BatchMod& bt, int fl)")
     out.append("    {")
     for k in range(plan.K):
         out.append(f"        if constexpr (K == {k}) stage{k}<R, F>(c, v, mb, bt, fl);")
