@@ -122,6 +122,43 @@ def test_clickbegonesg_tiled_kernel_is_bit_identical_to_the_generic_kernel(gpu, 
     assert np.abs(outs[0] - x[:, :2]).max() > 1e-3          # clicks were repaired: not a pass-through comparison
 
 
+@pytest.mark.parametrize("ns,block,cuts", [(37, 512, (0, 31, 31 + 45, 31 + 45 + 4096 + 13, 12000)), (70, 100, (0, 6000, 6001, 9000)),
+                                           (3, 7, (0, 64, 2000))])
+def test_red_tiled_kernel_is_bit_identical_to_the_generic_kernel(gpu, ns, block, cuts):
+    """red_tiled_kernel (p_faust.cu: powers, detector and gain lane = frame, the two + six followers lane = stream, five tiles
+    in flight) is made of the same Red::powers / envelopes / detect / reduction_db / gain as Red::frame in the generic
+    stream-per-thread kernel (option scalar_f32 = 1): six output channels AND the eight state words must be the same bits,
+    over several calls of ragged lengths, host blocks that cut the 32-frame tiles, partial CTAs, all three sliders moving per
+    block; the render is also checked against the restatement."""
+    key = "RED"
+    port = zo.PortPlugin(key)
+    nf = cuts[-1]
+    x = make_input(key, port, ns, nf)
+    base = np.array([s["default"] for s in port.sliders], np.float32)
+    p = wl.automation(port.sliders, (nf + block - 1) // block, ns, which=[0, 1, 2], base=base)
+    outs, states = [], []
+    for generic in (0, 1):
+        bp = gpu.BatchProcessor(key, ns, 48000.0, block, "f32").prepare(p[0])
+        bp.set_option("scalar_f32", generic)
+        parts = []
+        for c0, c1 in zip(cuts[:-1], cuts[1:]):
+            if c0 % block:
+                b0 = c0 // block
+                parts.append(bp.process(np.ascontiguousarray(x[:, :, c0:c1]), params=np.ascontiguousarray(p[b0:b0 + 1])))
+            else:
+                parts.append(bp.process(np.ascontiguousarray(x[:, :, c0:c1]), params=np.ascontiguousarray(p[c0 // block:(c1 + block - 1) // block])))
+        outs.append(np.concatenate(parts, axis=2))
+        states.append(np.stack([bp.read_state(f"state[{k}]") for k in range(8)]))
+        bp.close()
+    assert np.array_equal(outs[0].view(np.uint32), outs[1].view(np.uint32))
+    assert np.array_equal(states[0].astype(np.float32).view(np.uint32), states[1].astype(np.float32).view(np.uint32))
+    assert np.abs(outs[0][:, :2] - x[:, :2]).max() > 1e-3    # the wet pair was ducked: not a pass-through comparison
+    assert np.array_equal(outs[0][:, 2:], x[:, 2:])          # the other four channels pass through
+    if all(c % block == 0 for c in cuts[1:-1]):              # one continuous automation: the restatement renders the same call
+        y, _ = port.render(p, x, block=block)
+        assert dbfs_rms(outs[0].astype(np.float64) - y) < -100.0
+
+
 @pytest.mark.parametrize("key", ["VAR", "RED"])
 def test_generic_kernel_streams_per_warp_does_not_change_a_bit(gpu, key):
     """faust_leaf_kernel with 8 / 16 / 32 streams per warp (option lanes_per_warp): identical bits,
@@ -136,6 +173,7 @@ def test_generic_kernel_streams_per_warp_does_not_change_a_bit(gpu, key):
     for lanes in (32, 16, 8):
         bp = gpu.BatchProcessor(key, ns, 48000.0, block, "f32").prepare(p[0])
         bp.set_option("lanes_per_warp", lanes)
+        bp.set_option("scalar_f32", 1)                   # the generic kernel (RED has a tiled one by default)
         outs[lanes] = (bp.process(x, params=p), np.stack([bp.read_state(f"state[{k}]") for k in range(8)]))
         bp.close()
     assert dbfs_rms(outs[32][0].astype(np.float64) - y) < -100.0

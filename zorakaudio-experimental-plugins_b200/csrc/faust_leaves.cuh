@@ -62,29 +62,51 @@ struct Red {
         c.pad0 = c.pad1 = 0.0f;
     }
     ZA_FL static float smoothstep01(float x) { const float x1 = clampf_(x, 0.0f, 1.0f); return (x1 * x1) * (3.0f - (2.0f * x1)); }
-    ZA_FL static void frame(State& m, const Slow& c, const Konst& k, const float* in, float* out)
+    // frame() in five pieces, so that the tiled kernel (p_faust.cu, red_tiled_kernel) can run the memoryless ones lane = frame
+    // and only the recurrences lane = stream: the same operations on the same values in the same order either way.
+    ZA_FL static void powers(float wetL, float wetR, float refL, float refR, float& wet_p, float& ref_p)       // :68-69
+    {
+        wet_p = 0.5f * ((wetL * wetL) + (wetR * wetR)); ref_p = 0.5f * ((refL * refL) + (refR * refR));
+    }
+    ZA_FL static void envelopes(State& m, const Konst& k, float wet_p, float ref_p)                            // :72-73 (carried)
+    {
+        smooth_(m.wet_env2, k.pole_rms, wet_p); smooth_(m.ref_env2, k.pole_rms, ref_p);
+    }
+    struct Det { float dryA, offA, tgt0; };
+    ZA_FL static Det detect(const Slow& c, const Konst& k, float wet_env2, float ref_env2)                     // memoryless
     {
         const float eps = 1e-12f;
-        const float wetL = in[0], wetR = in[1], refL = in[4], refR = in[5];
-        const float wet_p = 0.5f * ((wetL * wetL) + (wetR * wetR)), ref_p = 0.5f * ((refL * refL) + (refR * refR));   // :68-69
-        smooth_(m.wet_env2, k.pole_rms, wet_p); smooth_(m.ref_env2, k.pole_rms, ref_p);                           // :72-73
-        const float Ey = fmaxf(sqrtf(fmaxf(m.wet_env2, 0.0f)), k.floor_lin), Ex = fmaxf(sqrtf(fmaxf(m.ref_env2, 0.0f)), k.floor_lin);
-        const float dryA = Ex > k.dry_on_lin ? 1.0f : 0.0f, offA = Ex <= k.ref_off_lin ? 1.0f : 0.0f;               // :78-79
-        smooth_(m.offA_s, c.pole_grace, offA);                                                                     // :83
-        const float tail_w = (1.0f - offA) + (offA * smoothstep01(m.offA_s));                                      // :84
+        const float Ey = fmaxf(sqrtf(fmaxf(wet_env2, 0.0f)), k.floor_lin), Ex = fmaxf(sqrtf(fmaxf(ref_env2, 0.0f)), k.floor_lin);
+        Det d;
+        d.dryA = Ex > k.dry_on_lin ? 1.0f : 0.0f; d.offA = Ex <= k.ref_off_lin ? 1.0f : 0.0f;                     // :78-79
         const float rdB = 20.0f * log10f(fmaxf((Ey + eps) / (Ex + eps), 1e-30f));                                  // :87
         const float over = rdB - c.thr_db;
         const float over_eff = over <= 0.0f ? 0.0f : over * smoothstep01(clampf_(over / fmaxf(c.knee_db, 0.001f), 0.0f, 1.0f));   // :91-94
-        const float tgt0 = over_eff > 0.0f ? fminf(c.maxduck, over_eff * c.ratio) : 0.0f;                          // :97
-        smooth_(m.tgt_db, k.pole_tgt, tgt0 * tail_w);                                                              // :98,101
-        smooth_(m.dryA_s, k.pole_dry, dryA);                                                                       // :107
+        d.tgt0 = over_eff > 0.0f ? fminf(c.maxduck, over_eff * c.ratio) : 0.0f;                                    // :97
+        return d;
+    }
+    ZA_FL static float reduction_db(State& m, const Slow& c, const Konst& k, const Det& d)                     // carried: six followers
+    {
+        smooth_(m.offA_s, c.pole_grace, d.offA);                                                                   // :83
+        const float tail_w = (1.0f - d.offA) + (d.offA * smoothstep01(m.offA_s));                                  // :84
+        smooth_(m.tgt_db, k.pole_tgt, d.tgt0 * tail_w);                                                            // :98,101
+        smooth_(m.dryA_s, k.pole_dry, d.dryA);                                                                     // :107
         smooth_(m.tgt_hold_s, k.pole_hold, m.tgt_db);
-        const float tgt_pin = ((1.0f - dryA) * fmaxf(m.tgt_db, m.tgt_hold_s)) + (dryA * m.tgt_db);                 // :112-113
+        const float tgt_pin = ((1.0f - d.dryA) * fmaxf(m.tgt_db, m.tgt_hold_s)) + (d.dryA * m.tgt_db);             // :112-113
         const float x = fabsf(tgt_pin);
         { const float cc = x > m.gr_norm ? k.c_atk : c.c_rel; m.gr_norm = ((1.0f - cc) * x) + (cc * m.gr_norm); }     // :120
         { const float cc = x > m.gr_fast ? k.c_atk : k.c_rel_in; m.gr_fast = ((1.0f - cc) * x) + (cc * m.gr_fast); }  // :121
-        const float gr_db = ((1.0f - m.dryA_s) * m.gr_norm) + (m.dryA_s * m.gr_fast);                              // :124
-        const float g = db2lin_(-gr_db);                                                                           // :127
+        return ((1.0f - m.dryA_s) * m.gr_norm) + (m.dryA_s * m.gr_fast);                                           // :124
+    }
+    ZA_FL static float gain(float gr_db) { return db2lin_(-gr_db); }                                             // :127
+    ZA_FL static void frame(State& m, const Slow& c, const Konst& k, const float* in, float* out)
+    {
+        const float wetL = in[0], wetR = in[1], refL = in[4], refR = in[5];
+        float wet_p, ref_p;
+        powers(wetL, wetR, refL, refR, wet_p, ref_p);
+        envelopes(m, k, wet_p, ref_p);
+        const Det d = detect(c, k, m.wet_env2, m.ref_env2);
+        const float g = gain(reduction_db(m, c, k, d));
         out[0] = wetL * g; out[1] = wetR * g; out[2] = in[2]; out[3] = in[3]; out[4] = refL; out[5] = refR;       // :43
     }
 };

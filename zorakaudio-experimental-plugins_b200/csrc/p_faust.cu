@@ -200,6 +200,7 @@ __global__ void __launch_bounds__(cbg::kThreads) cbg_tiled_kernel(const FaustArg
         };
         fetch(0);
         int mode_q[4] = {0, 0, 0, 0};
+        bool was_ragged = false;
         for (int i = 0; i < n_tiles + 2; ++i) {
             asm volatile("cp.async.wait_group 0;" ::: "memory");       // tile i is in the ring
             __syncwarp();
@@ -227,7 +228,9 @@ __global__ void __launch_bounds__(cbg::kThreads) cbg_tiled_kernel(const FaustArg
                 int64_t blk = f0 / a.block_len;
                 if (r0 + 32 > a.block_len) blk = nn / a.block_len;
                 const size_t row = (size_t)(blk < a.n_rows ? blk : a.n_rows - 1) * ns;
-                const bool reread = i == 0 || r0 == 0 || r0 + 32 > a.block_len;     // the row can only change where a host block starts
+                const bool ragged = r0 + 32 > a.block_len;                          // the tile spans host blocks: row per lane
+                const bool reread = i == 0 || r0 == 0 || ragged || was_ragged;      // else the row can only change where a host block starts
+                was_ragged = ragged;
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     const int si = warp * 4 + q;
@@ -323,9 +326,175 @@ __global__ void __launch_bounds__(cbg::kThreads) cbg_tiled_kernel(const FaustArg
 }
 static_assert(sizeof(faust::Cbg::State) == 70 * 4, "cbg_tiled_kernel addresses the state words of faust::Cbg::State by number");
 
-template <class L> struct TiledLaunch { static int go(const FaustArgs&, cudaStream_t) { return 0; } };        // 0 = no tiled kernel for this leaf
+// ---- RED, tiled ---------------------------------------------------------------------------------------------------------------
+// RED's frame is a chain of two envelope followers, a memoryless level detector (two sqrt, a division, log10, a knee), six more
+// followers and a memoryless dB -> gain (powf): the generic kernel above walks that chain of ~300 dependent instructions once per
+// frame with one warp per SM (48.8 ms per 5041 streams x 1 s).  Here one CTA = 32 streams = 8 map warps (lane = frame, four
+// streams each) + 2 recurrence warps (lane = stream), software-pipelined over 32-frame tiles with one __syncthreads per tile;
+// at iteration i:
+//   map warps    powers of tile i (inputs fetched one iteration ahead, in registers)        -> P
+//   warp R1      the two envelope followers over tile i - 1, frame after frame              P -> E
+//   map warps    detector of tile i - 2 (Red::detect, slider-rate row of the frame)         E -> D
+//   warp R2      the six followers over tile i - 3 (Red::reduction_db)                      D -> G
+//   map warps    gain of tile i - 4 (Red::gain), inputs of that tile re-read (L2), six output rows stored.
+// All five are the functions Red::frame is made of, so outputs and state rows are bit-identical to the generic kernel's.
+namespace red {
+constexpr int kMapWarps = 8, kThreads = (kMapWarps + 2) * 32, kTP = 33, kPlane = 32 * kTP, kLag = 4;
+struct Smem { float P[2][2][kPlane], E[2][2][kPlane], D[2][3][kPlane], G[2][kPlane]; };
+}  // namespace red
+
+__global__ void __launch_bounds__(red::kThreads) red_tiled_kernel(const FaustArgs a, const faust::Red::Konst k)
+{
+    using L = faust::Red;
+    using namespace red;
+    extern __shared__ __align__(16) unsigned char red_smem_raw[];
+    Smem& sm = *reinterpret_cast<Smem*>(red_smem_raw);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, s0 = blockIdx.x * 32;
+    const size_t ns = (size_t)a.n_streams;
+    const int n_cta = min(32, a.n_streams - s0);
+    const L::Slow* rows = reinterpret_cast<const L::Slow*>(a.slow);
+    const int64_t n = a.n_frames;
+    const int n_tiles = (int)((n + 31) / 32);
+    // State words (faust::Red::State): wet_env2 0, ref_env2 1 (warp R1); offA_s 2, tgt_db 3, dryA_s 4, tgt_hold_s 5, gr_norm 6, gr_fast 7 (R2)
+    if (warp < kMapWarps) {
+        float nx[4][4];                                   // wetL, wetR, refL, refR of the next tile, per stream of this warp
+        auto fetch = [&](int t) {
+            const int64_t nn = (int64_t)t * 32 + lane;
+            const bool ok = t < n_tiles && nn < n;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int si = warp * 4 + q;
+                const float* x = a.in + (size_t)(s0 + si) * 6 * a.row_stride + nn;
+                const bool go = ok && si < n_cta;
+                nx[q][0] = go ? x[0] : 0.0f; nx[q][1] = go ? x[a.row_stride] : 0.0f;
+                nx[q][2] = go ? x[4 * a.row_stride] : 0.0f; nx[q][3] = go ? x[5 * a.row_stride] : 0.0f;
+            }
+        };
+        fetch(0);
+        L::Slow cq[4];
+        bool was_ragged = false;
+        for (int i = 0; i < n_tiles + kLag; ++i) {
+            if (i < n_tiles) {                           // powers of tile i
+                const int o = lane;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int si = warp * 4 + q;
+                    float wp, rp;
+                    L::powers(nx[q][0], nx[q][1], nx[q][2], nx[q][3], wp, rp);
+                    sm.P[i & 1][0][si * kTP + o] = wp; sm.P[i & 1][1][si * kTP + o] = rp;
+                }
+            }
+            fetch(i + 1);                                // in == out is legal: tile i + 1 is stored five iterations from now
+            if (i >= 2 && i - 2 < n_tiles) {             // detector of tile i - 2
+                const int t = i - 2;
+                const int64_t f0 = (int64_t)t * 32, nn = f0 + lane;
+                const int64_t r0 = f0 % a.block_len;
+                int64_t blk = f0 / a.block_len;
+                if (r0 + 32 > a.block_len) blk = nn / a.block_len;
+                const size_t row = (size_t)(blk < a.n_rows ? blk : a.n_rows - 1) * ns;
+                const bool ragged = r0 + 32 > a.block_len;                            // the tile spans host blocks: row per lane
+                const bool reread = t == 0 || r0 == 0 || ragged || was_ragged;        // else the row can only change where a host block starts
+                was_ragged = ragged;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int si = warp * 4 + q;
+                    if (si < n_cta) {
+                        if (reread) cq[q] = rows[row + s0 + si];
+                        const L::Det d = L::detect(cq[q], k, sm.E[t & 1][0][si * kTP + lane], sm.E[t & 1][1][si * kTP + lane]);
+                        sm.D[t & 1][0][si * kTP + lane] = d.dryA; sm.D[t & 1][1][si * kTP + lane] = d.offA; sm.D[t & 1][2][si * kTP + lane] = d.tgt0;
+                    }
+                }
+            }
+            if (i >= kLag) {                             // gain and outputs of tile i - 4
+                const int t = i - kLag;
+                const int64_t nn = (int64_t)t * 32 + lane;
+                if (nn < n) {
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const int si = warp * 4 + q;
+                        if (si < n_cta) {
+                            const float* x = a.in + (size_t)(s0 + si) * 6 * a.row_stride + nn;
+                            float* y = a.out + (size_t)(s0 + si) * 6 * a.row_stride + nn;
+                            float v[6];
+#pragma unroll
+                            for (int ch = 0; ch < 6; ++ch) v[ch] = x[ch * a.row_stride];
+                            const float g = L::gain(sm.G[t & 1][si * kTP + lane]);
+                            y[0] = v[0] * g; y[a.row_stride] = v[1] * g;
+#pragma unroll
+                            for (int ch = 2; ch < 6; ++ch) y[ch * a.row_stride] = v[ch];
+                        }
+                    }
+                }
+            }
+            __syncthreads();
+        }
+    } else {
+        const bool r1 = warp == kMapWarps;               // R1: envelopes, one tile behind the powers; R2: followers, three behind
+        const int lag = r1 ? 1 : 3;
+        const bool live = lane < n_cta;
+        const size_t s = (size_t)(s0 + (live ? lane : 0));
+        L::State m{};
+        if (r1) { m.wet_env2 = __uint_as_float(a.state[0 * ns + s]); m.ref_env2 = __uint_as_float(a.state[1 * ns + s]); }
+        else {
+            m.offA_s = __uint_as_float(a.state[2 * ns + s]); m.tgt_db = __uint_as_float(a.state[3 * ns + s]); m.dryA_s = __uint_as_float(a.state[4 * ns + s]);
+            m.tgt_hold_s = __uint_as_float(a.state[5 * ns + s]); m.gr_norm = __uint_as_float(a.state[6 * ns + s]); m.gr_fast = __uint_as_float(a.state[7 * ns + s]);
+        }
+        L::Slow c = rows[s];
+        int blk = 0;
+        int64_t blk_end = a.block_len;
+        for (int i = 0; i < n_tiles + kLag; ++i) {
+            const int t = i - lag;
+            if (live && t >= 0 && t < n_tiles) {
+                const int64_t f0 = (int64_t)t * 32;
+                const int nv = (int)min((int64_t)32, n - f0);
+                const int o = lane * kTP;
+                if (r1) {
+#pragma unroll 8
+                    for (int f = 0; f < nv; ++f) {
+                        L::envelopes(m, k, sm.P[t & 1][0][o + f], sm.P[t & 1][1][o + f]);
+                        sm.E[t & 1][0][o + f] = m.wet_env2; sm.E[t & 1][1][o + f] = m.ref_env2;
+                    }
+                } else {
+#pragma unroll 4
+                    for (int f = 0; f < nv; ++f) {
+                        if (f0 + f >= blk_end) {         // a new host block: its slider-rate row (the last row persists)
+                            const int64_t b = (f0 + f) / a.block_len;
+                            blk = (int)b; blk_end = (b + 1) * a.block_len;
+                            c = rows[(size_t)(blk < a.n_rows ? blk : a.n_rows - 1) * ns + s];
+                        }
+                        const L::Det d{sm.D[t & 1][0][o + f], sm.D[t & 1][1][o + f], sm.D[t & 1][2][o + f]};
+                        sm.G[t & 1][o + f] = L::reduction_db(m, c, k, d);
+                    }
+                }
+            }
+            __syncthreads();
+        }
+        if (live) {
+            if (r1) { a.state[0 * ns + s] = __float_as_uint(m.wet_env2); a.state[1 * ns + s] = __float_as_uint(m.ref_env2); }
+            else {
+                a.state[2 * ns + s] = __float_as_uint(m.offA_s); a.state[3 * ns + s] = __float_as_uint(m.tgt_db); a.state[4 * ns + s] = __float_as_uint(m.dryA_s);
+                a.state[5 * ns + s] = __float_as_uint(m.tgt_hold_s); a.state[6 * ns + s] = __float_as_uint(m.gr_norm); a.state[7 * ns + s] = __float_as_uint(m.gr_fast);
+            }
+        }
+    }
+}
+static_assert(sizeof(faust::Red::State) == 8 * 4, "red_tiled_kernel addresses the state words of faust::Red::State by number");
+
+template <class L> struct TiledLaunch { static int go(const FaustArgs&, const typename L::Konst&, cudaStream_t) { return 0; } };        // 0 = no tiled kernel for this leaf
+template <> struct TiledLaunch<faust::Red> {
+    static int go(const FaustArgs& a, const faust::Red::Konst& k, cudaStream_t st)
+    {
+        static DeviceOnce attr_once;
+        if (attr_once.pending()) {
+            if (!cuda_ok(cudaFuncSetAttribute(red_tiled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(red::Smem)), "RED smem attr")) return -1;
+            attr_once.mark();
+        }
+        red_tiled_kernel<<<(unsigned)((a.n_streams + 31) / 32), red::kThreads, sizeof(red::Smem), st>>>(a, k);
+        return cuda_ok(cudaGetLastError(), "red_tiled_kernel") ? 1 : -1;
+    }
+};
 template <> struct TiledLaunch<faust::Cbg> {
-    static int go(const FaustArgs& a, cudaStream_t st)
+    static int go(const FaustArgs& a, const faust::Cbg::Konst&, cudaStream_t st)
     {
         static DeviceOnce attr_once;
         if (attr_once.pending()) {
@@ -409,7 +578,7 @@ public:
         if (n <= 0) return true;
         FaustArgs a{in, out, stride, n, I.n_streams, I.block_len, nbq, d_slow, d_state, I.opt_lanes};
         const bool timed = I.time_begin();
-        const int tiled = I.opt_scalar_f32 ? 0 : TiledLaunch<L>::go(a, I.stream);      // option scalar_f32 = 1: the generic kernel for every leaf
+        const int tiled = I.opt_scalar_f32 ? 0 : TiledLaunch<L>::go(a, k_, I.stream);      // option scalar_f32 = 1: the generic kernel for every leaf
         if (tiled < 0) return false;
         if (!tiled) {
             if (!launch_generic<L>(a, k_, I.stream)) return false;
