@@ -21,6 +21,10 @@ CAPS = [
      "python bench.py --workload cfg2 --seconds 10 --steps 1 --warmup 3 --no-cpu --no-e2e --no-parity --no-f64", 1024 * 480000, "cfg2"),
     ("r02_cbg_tiled", "cbg_tiled", "Faust leaf ClickBeGoneSG fp32, tiled kernel (`cbg_tiled_kernel`: 8 FIR warps with lane = frame + 1 recurrence warp with lane = stream per 32-stream CTA, inputs by cp.async one tile ahead)",
      "python tools/prof_run.py --plugin ClickBeGoneSG --streams 4096 --seconds 2 --reps 2", 4096 * 96000, None),
+    ("r02_soma_staged", "soma_staged", "translated leaf SOMA fp32 as a 6-stage pipeline (`jsfx_staged_kernel`: one warp per group of @sample statements, shared-memory rings between them, rand() state through a cp.async window)",
+     "python tools/prof_run.py --plugin SOMA --streams 5041 --seconds 1 --reps 2", 5041 * 48000, None),
+    ("r02_rtt_staged", "rtt_staged", "translated leaf RTT fp32 (8 inputs, 2 outputs) as an 8-stage pipeline (`jsfx_staged_kernel`, 2-frame batches)",
+     "python tools/prof_run.py --plugin RTT --streams 5041 --seconds 1 --reps 2", 5041 * 48000, None),
     ("r02_gts", "gts", "Faust leaf GTS fp32 (`gts_kernel`: time-parallel 257-tap Gaussian FIR rebuilt per frame)",
      "python bench.py --workload gts --seconds 2 --steps 1 --warmup 3 --no-cpu --no-e2e --no-parity", 4096 * 96000, "gts"),
 ]

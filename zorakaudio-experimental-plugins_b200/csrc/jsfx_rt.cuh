@@ -410,11 +410,15 @@ template <typename R> struct Rt {
     unsigned* mtw;                                         // this lane's column of the window: word k at mtw[(k & 15) * 32]
     __device__ __forceinline__ void mt_fetch(unsigned k)
     {
+#ifndef ZA_JSFX_HOST_EMU
         if (k < 624u) {
             const unsigned d = (unsigned)__cvta_generic_to_shared(mtw + (k & 15u) * 32u);
             asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(mt + (long long)k * stride) : "memory");
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
+#else
+        (void)k;
+#endif
     }
     __device__ __forceinline__ unsigned genrand()
     {
@@ -423,6 +427,7 @@ template <typename R> struct Rt {
         if (mt_idx == 0xFFFFFFFFu) { mt_idx = mt[624 * stride]; fill = true; }        // first draw of this launch
         if (mt_idx == 0 || mt_idx >= N) { mt_refill(mt, stride, mt_idx); mt_idx = 0; fill = true; }
         unsigned y;
+#ifndef ZA_JSFX_HOST_EMU
         if (pf) {
             if (fill) {
                 __threadfence_block();
@@ -431,7 +436,10 @@ template <typename R> struct Rt {
             mt_fetch(mt_idx + kAhead);
             asm volatile("cp.async.wait_group 8;" ::: "memory");
             y = mtw[(mt_idx & 15u) * 32u];
-        } else {
+        } else
+#endif
+        {
+            (void)fill; (void)kAhead;
             y = mt[mt_idx * stride];
         }
         mt_idx += 1;
@@ -445,6 +453,18 @@ template <typename R> struct Rt {
         if (mx < (R)1) mx = (R)1;
         const double r = __dmul_rn((double)genrand(), 1.0 / 4294967295.0);
         return (R)__dmul_rn(r, (double)mx);
+    }
+};
+
+// stage pipelines (jsfx_staged_kernel below): the plan a generated unit carries, and the batch counter its stages index rings with
+struct NoStages { static constexpr int kStages = 1, kMailSlots = 1; };
+// batch number of a stage modulo every ring depth a plan can ask for (2 .. 9), kept incrementally
+struct BatchMod {
+    int r2 = 0, r3 = 0, r4 = 0, r5 = 0, r6 = 0, r7 = 0, r8 = 0, r9 = 0;
+    __device__ __forceinline__ void next()
+    {
+        r2 = r2 + 1 == 2 ? 0 : r2 + 1; r3 = r3 + 1 == 3 ? 0 : r3 + 1; r4 = r4 + 1 == 4 ? 0 : r4 + 1; r5 = r5 + 1 == 5 ? 0 : r5 + 1;
+        r6 = r6 + 1 == 6 ? 0 : r6 + 1; r7 = r7 + 1 == 7 ? 0 : r7 + 1; r8 = r8 + 1 == 8 ? 0 : r8 + 1; r9 = r9 + 1 == 9 ? 0 : r9 + 1;
     }
 };
 
@@ -648,17 +668,6 @@ __global__ void __launch_bounds__(128, 1) jsfx_process_kernel(const GenLaunch a)
 // crosses a cut inside a frame travels through per-value rings in shared memory (mb[slot][F][32], ring depth = distance to
 // the furthest consumer + 1), one __syncthreads per batch of F frames.  Same statements in the same order on the same
 // values: in float64 the outputs and states are bit-identical to jsfx_process_kernel.
-struct NoStages { static constexpr int kStages = 1, kMailSlots = 1; };
-// batch number of a stage modulo every ring depth a plan can ask for (2 .. 9), kept incrementally
-struct BatchMod {
-    int r2 = 0, r3 = 0, r4 = 0, r5 = 0, r6 = 0, r7 = 0, r8 = 0, r9 = 0;
-    __device__ __forceinline__ void next()
-    {
-        r2 = r2 + 1 == 2 ? 0 : r2 + 1; r3 = r3 + 1 == 3 ? 0 : r3 + 1; r4 = r4 + 1 == 4 ? 0 : r4 + 1; r5 = r5 + 1 == 5 ? 0 : r5 + 1;
-        r6 = r6 + 1 == 6 ? 0 : r6 + 1; r7 = r7 + 1 == 7 ? 0 : r7 + 1; r8 = r8 + 1 == 8 ? 0 : r8 + 1; r9 = r9 + 1 == 9 ? 0 : r9 + 1;
-    }
-};
-
 // shared memory of a CTA: [rings][audio tiles: 2 x kIn in, kOut out][MT19937 window]
 // frames per audio tile.  (16 for the 8-input RTT, which leaves its rings room for 5-frame instead of 2-frame batches, was
 // measured: 45.7 ms against 27.2 ms per 5041 x 1 s -- the first stage's warp pays for twice the copy instructions.)
