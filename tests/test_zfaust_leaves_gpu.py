@@ -124,19 +124,20 @@ def test_clickbegonesg_tiled_kernel_is_bit_identical_to_the_generic_kernel(gpu, 
 
 @pytest.mark.parametrize("ns,block,cuts", [(37, 512, (0, 31, 31 + 45, 31 + 45 + 4096 + 13, 12000)), (70, 100, (0, 6000, 6001, 9000)),
                                            (3, 7, (0, 64, 2000))])
-def test_red_tiled_kernel_is_bit_identical_to_the_generic_kernel(gpu, ns, block, cuts):
+@pytest.mark.parametrize("key,n_state", [("RED", 8), ("VAR", 27)])
+def test_red_tiled_kernel_is_bit_identical_to_the_generic_kernel(gpu, key, n_state, ns, block, cuts):
     """red_tiled_kernel (p_faust.cu: powers, detector and gain lane = frame, the two + six followers lane = stream, five tiles
     in flight) is made of the same Red::powers / envelopes / detect / reduction_db / gain as Red::frame in the generic
     stream-per-thread kernel (option scalar_f32 = 1): six output channels AND the eight state words must be the same bits,
     over several calls of ragged lengths, host blocks that cut the 32-frame tiles, partial CTAs, all three sliders moving per
-    block; the render is also checked against the restatement."""
-    key = "RED"
+    block; the render is also checked against the restatement.  The same for var_tiled_kernel (Var::detector / control /
+    envelope / bands / mix, three recurrence warps, 16 streams per CTA) and VAR's 27 state words (noise generator included)."""
     port = zo.PortPlugin(key)
     nf = cuts[-1]
     x = make_input(key, port, ns, nf)
     base = np.array([s["default"] for s in port.sliders], np.float32)
     p = wl.automation(port.sliders, (nf + block - 1) // block, ns, which=[0, 1, 2], base=base)
-    outs, states = [], []
+    outs, states, blobs = [], [], []
     for generic in (0, 1):
         bp = gpu.BatchProcessor(key, ns, 48000.0, block, "f32").prepare(p[0])
         bp.set_option("scalar_f32", generic)
@@ -148,12 +149,15 @@ def test_red_tiled_kernel_is_bit_identical_to_the_generic_kernel(gpu, ns, block,
             else:
                 parts.append(bp.process(np.ascontiguousarray(x[:, :, c0:c1]), params=np.ascontiguousarray(p[c0 // block:(c1 + block - 1) // block])))
         outs.append(np.concatenate(parts, axis=2))
-        states.append(np.stack([bp.read_state(f"state[{k}]") for k in range(8)]))
+        states.append(np.stack([bp.read_state(f"state[{k}]") for k in range(n_state)]))
+        blobs.append(bp.save_state())
         bp.close()
     assert np.array_equal(outs[0].view(np.uint32), outs[1].view(np.uint32))
-    assert np.array_equal(states[0].astype(np.float32).view(np.uint32), states[1].astype(np.float32).view(np.uint32))
-    assert np.abs(outs[0][:, :2] - x[:, :2]).max() > 1e-3    # the wet pair was ducked: not a pass-through comparison
-    assert np.array_equal(outs[0][:, 2:], x[:, 2:])          # the other four channels pass through
+    assert np.array_equal(states[0], states[1], equal_nan=True)
+    assert np.array_equal(blobs[0], blobs[1])                # the checkpoint blob: every state word as stored, integer ones included
+    assert np.abs(outs[0][:, :2] - x[:, :2]).max() > 1e-4    # the effect did something: not a pass-through comparison
+    if key == "RED":
+        assert np.array_equal(outs[0][:, 2:], x[:, 2:])      # the other four channels pass through
     if all(c % block == 0 for c in cuts[1:-1]):              # one continuous automation: the restatement renders the same call
         y, _ = port.render(p, x, block=block)
         assert dbfs_rms(outs[0].astype(np.float64) - y) < -100.0

@@ -257,33 +257,71 @@ struct Var {
     }
     static void slow(const float* z, float, Slow& c) { c.amount_t = z[0] / 100.0f; c.sens_t = z[1] / 100.0f; c.floorLin = host_db2lin(z[2]); c.pad = 0.0f; }
     ZA_FL static float onepole_exp(float& st, float a, float x) { st = (x * (1.0f - a)) + (st * a); return st; }   // :78
-    ZA_FL static void frame(State& m, const Slow& c, const Konst& k, const float* in, float* out)
+    // frame() in five pieces (as for RED), so that the tiled kernel (p_faust.cu, var_tiled_kernel) runs the memoryless ones lane =
+    // frame and the three recurrences lane = stream on a warp each: the same operations on the same values either way.
+    struct DetOut { float amount, sens, hfLvl, lapL, denomL, lapR, denomR; };
+    ZA_FL static DetOut detector(State& m, const Slow& c, const Konst& k, float inL, float inR)                   // carried
     {
-        const float eps = 1e-12f, inL = in[0], inR = in[1];
+        const float eps = 1e-12f;
         smooth_(m.amount, k.smoo_p, c.amount_t); smooth_(m.sens, k.smoo_p, c.sens_t);                             // :88-89
-        const float maxExp_lin = db2lin_(5.0f * m.amount), airMix = 0.25f * m.amount, thrN = 0.18f - (0.13f * m.sens);   // :95-100
         const float detL = tf22t_(k.det, m.detL, inL), detR = tf22t_(k.det, m.detR, inR);                        // :117-118
         onepole_exp(m.hfLvl, k.hfLvl_a, 0.5f * (fabsf(detL) + fabsf(detR)));                                     // :121-124
-        const float gu = fminf(1.0f, fmaxf(0.0f, ((m.hfLvl / (c.floorLin + eps)) - 1.0f) / (2.0f - 1.0f)));
-        const float gate = (gu * gu) * (3.0f - (2.0f * gu));                                                      // :126
         onepole_exp(m.sm1L, k.detSmooth_a, detL); onepole_exp(m.sm2L, k.detSmooth_a, m.sm1L);                    // :130
         onepole_exp(m.sm1R, k.detSmooth_a, detR); onepole_exp(m.sm2R, k.detSmooth_a, m.sm1R);
         const float s0L = m.sm2L, s1L = m.s1L, s2L = m.s2L, s0R = m.sm2R, s1R = m.s1R, s2R = m.s2R;               // :134-142
-        const float lapL = (s0L - (2.0f * s1L)) + s2L, lapR = (s0R - (2.0f * s1R)) + s2R;
-        const float denomL = ((fabsf(s0L) + (2.0f * fabsf(s1L))) + fabsf(s2L)) + eps, denomR = ((fabsf(s0R) + (2.0f * fabsf(s1R))) + fabsf(s2R)) + eps;
+        DetOut d;
+        d.amount = m.amount; d.sens = m.sens; d.hfLvl = m.hfLvl;
+        d.lapL = (s0L - (2.0f * s1L)) + s2L; d.lapR = (s0R - (2.0f * s1R)) + s2R;
+        d.denomL = ((fabsf(s0L) + (2.0f * fabsf(s1L))) + fabsf(s2L)) + eps; d.denomR = ((fabsf(s0R) + (2.0f * fabsf(s1R))) + fabsf(s2R)) + eps;
         m.s2L = s1L; m.s1L = s0L; m.s2R = s1R; m.s1R = s0R;
-        const float curvN = 0.5f * ((fabsf(lapL) / denomL) + (fabsf(lapR) / denomR));                              // :147-149
-        { const float cc = curvN > m.env ? k.c_atk : k.c_rel; m.env = ((1.0f - cc) * curvN) + (cc * m.env); }     // :152
-        const float u = fmaxf(0.0f, (m.env / thrN) - 1.0f);
-        const float t = (u / (1.0f + u)) * gate;                                                                  // :155-156
-        const float t2 = powf(fmaxf(eps, t), 1.8f);                                                               // :157
-        const float g = 1.0f + (t * (maxExp_lin - 1.0f));                                                         // :160
-        const float hfL = tf22t_(k.hf, m.hf2L, tf22t_(k.hf, m.hf1L, inL)), hfR = tf22t_(k.hf, m.hf2R, tf22t_(k.hf, m.hf1R, inR));   // :163-164
+        return d;
+    }
+    struct Ctl { float curvN, thrN, gate, mE1, airMix; };
+    ZA_FL static Ctl control(const Slow& c, const DetOut& d)                                                      // memoryless
+    {
+        const float eps = 1e-12f;
+        Ctl q;
+        const float maxExp_lin = db2lin_(5.0f * d.amount);                                                        // :95-100
+        q.airMix = 0.25f * d.amount; q.thrN = 0.18f - (0.13f * d.sens);
+        const float gu = fminf(1.0f, fmaxf(0.0f, ((d.hfLvl / (c.floorLin + eps)) - 1.0f) / (2.0f - 1.0f)));
+        q.gate = (gu * gu) * (3.0f - (2.0f * gu));                                                                // :126
+        q.curvN = 0.5f * ((fabsf(d.lapL) / d.denomL) + (fabsf(d.lapR) / d.denomR));                               // :147-149
+        q.mE1 = maxExp_lin - 1.0f;
+        return q;
+    }
+    ZA_FL static float envelope(State& m, const Konst& k, float curvN)                                            // carried, :152
+    {
+        const float cc = curvN > m.env ? k.c_atk : k.c_rel;
+        m.env = ((1.0f - cc) * curvN) + (cc * m.env);
+        return m.env;
+    }
+    struct Hf { float hfL, hfR, air; };
+    ZA_FL static Hf bands(State& m, const Konst& k, float inL, float inR)                                         // carried
+    {
+        Hf h;
+        h.hfL = tf22t_(k.hf, m.hf2L, tf22t_(k.hf, m.hf1L, inL)); h.hfR = tf22t_(k.hf, m.hf2R, tf22t_(k.hf, m.hf1R, inR));   // :163-164
         m.noise = (int)((unsigned)m.noise * 1103515245u + 12345u);
-        const float air = tf22t_(k.air, m.airZ, (float)m.noise / 2147483647.0f);                                  // :170-174 (nL == nR)
-        const float airGain = (t2 * k.airBase) * airMix;                                                          // :176
-        out[0] = (inL + (hfL * (g - 1.0f))) + (air * airGain);                                                    // :180 (outGain = 1)
-        out[1] = (inR + (hfR * (g - 1.0f))) + (air * airGain);
+        h.air = tf22t_(k.air, m.airZ, (float)m.noise / 2147483647.0f);                                            // :170-174 (nL == nR)
+        return h;
+    }
+    ZA_FL static void mix(const Konst& k, const Ctl& q, float env, const Hf& h, float inL, float inR, float* out)   // memoryless
+    {
+        const float eps = 1e-12f;
+        const float u = fmaxf(0.0f, (env / q.thrN) - 1.0f);
+        const float t = (u / (1.0f + u)) * q.gate;                                                                // :155-156
+        const float t2 = powf(fmaxf(eps, t), 1.8f);                                                               // :157
+        const float g = 1.0f + (t * q.mE1);                                                                       // :160
+        const float airGain = (t2 * k.airBase) * q.airMix;                                                        // :176
+        out[0] = (inL + (h.hfL * (g - 1.0f))) + (h.air * airGain);                                                // :180 (outGain = 1)
+        out[1] = (inR + (h.hfR * (g - 1.0f))) + (h.air * airGain);
+    }
+    ZA_FL static void frame(State& m, const Slow& c, const Konst& k, const float* in, float* out)
+    {
+        const DetOut d = detector(m, c, k, in[0], in[1]);
+        const Ctl q = control(c, d);
+        const float env = envelope(m, k, q.curvN);
+        const Hf h = bands(m, k, in[0], in[1]);
+        mix(k, q, env, h, in[0], in[1], out);
     }
 };
 

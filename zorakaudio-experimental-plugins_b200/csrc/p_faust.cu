@@ -13,6 +13,7 @@
 // These leaves are sequential by nature (switching followers, max-hold envelopes, hysteresis): the kernel is
 // latency-bound at 4096 streams like every stream-per-thread kernel here; parity target = the float restatement
 // (the test-side C port of the .dsp; PARITY UNPINNED).
+#include <cstddef>
 #include <cstring>
 
 #include "za_host.h"
@@ -480,7 +481,188 @@ __global__ void __launch_bounds__(red::kThreads) red_tiled_kernel(const FaustArg
 }
 static_assert(sizeof(faust::Red::State) == 8 * 4, "red_tiled_kernel addresses the state words of faust::Red::State by number");
 
+// ---- VAR, tiled ---------------------------------------------------------------------------------------------------------------
+// VAR's frame: a detector chain (two biquads, five one-poles, a 3-tap Laplacian), memoryless control values (powf, three
+// divisions), a switching envelope, a high-pass biquad pair per channel plus a noise band, and a memoryless mix (powf, two
+// divisions).  One CTA = 16 streams (so that two CTAs share an SM) = 4 map warps (lane = frame, four streams each) + 3
+// recurrence warps (lane = stream), 32-frame tiles, one __syncthreads per tile; at iteration i:
+//   map   inputs of tile i (fetched one iteration ahead, in registers) -> IN               R1  Var::detector over tile i - 1   IN -> A
+//   map   Var::control of tile i - 2 (slider-rate row of the frame)     A -> Bc, Bq         R2  Var::envelope over tile i - 3   Bc -> C
+//   map   Var::mix of tile i - 4, inputs re-read (L2), outputs stored   Bq, C, D -> out     R3  Var::bands over tile i - 3      IN -> D
+// The five functions are what Var::frame is made of: outputs and the 27 state words are bit-identical to the generic kernel's.
+namespace var {
+constexpr int kStreams = 16, kMapWarps = 4, kThreads = (kMapWarps + 3) * 32, kTP = 33, kPlane = kStreams * kTP, kLag = 4;
+struct Smem { float IN[4][2][kPlane], A[2][7][kPlane], Bc[2][kPlane], Bq[3][4][kPlane], C[2][kPlane], D[2][3][kPlane]; };
+}  // namespace var
+
+__global__ void __launch_bounds__(var::kThreads, 2) var_tiled_kernel(const FaustArgs a, const faust::Var::Konst k)
+{
+    using L = faust::Var;
+    using namespace var;
+    extern __shared__ __align__(16) unsigned char var_smem_raw[];
+    Smem& sm = *reinterpret_cast<Smem*>(var_smem_raw);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, s0 = blockIdx.x * kStreams;
+    const size_t ns = (size_t)a.n_streams;
+    const int n_cta = min(kStreams, a.n_streams - s0);
+    const L::Slow* rows = reinterpret_cast<const L::Slow*>(a.slow);
+    const int64_t n = a.n_frames;
+    const int n_tiles = (int)((n + 31) / 32);
+    auto ldw = [&](int w, size_t s) { return __uint_as_float(a.state[(size_t)w * ns + s]); };
+    auto stw = [&](int w, size_t s, float v) { a.state[(size_t)w * ns + s] = __float_as_uint(v); };
+    if (warp < kMapWarps) {
+        float nx[4][2];
+        auto fetch = [&](int t) {
+            const int64_t nn = (int64_t)t * 32 + lane;
+            const bool ok = t < n_tiles && nn < n;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int si = warp * 4 + q;
+                const float* x = a.in + (size_t)(s0 + si) * 2 * a.row_stride + nn;
+                const bool go = ok && si < n_cta;
+                nx[q][0] = go ? x[0] : 0.0f; nx[q][1] = go ? x[a.row_stride] : 0.0f;
+            }
+        };
+        fetch(0);
+        L::Slow cq[4];
+        bool was_ragged = false;
+        for (int i = 0; i < n_tiles + kLag; ++i) {
+            if (i < n_tiles) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int o = (warp * 4 + q) * kTP + lane;
+                    sm.IN[i & 3][0][o] = nx[q][0]; sm.IN[i & 3][1][o] = nx[q][1];
+                }
+            }
+            fetch(i + 1);                                // in == out is legal: tile i + 1 is stored five iterations from now
+            if (i >= 2 && i - 2 < n_tiles) {             // control values of tile i - 2
+                const int t = i - 2;
+                const int64_t f0 = (int64_t)t * 32, nn = f0 + lane;
+                const int64_t r0 = f0 % a.block_len;
+                int64_t blk = f0 / a.block_len;
+                const bool ragged = r0 + 32 > a.block_len;                            // the tile spans host blocks: row per lane
+                if (ragged) blk = nn / a.block_len;
+                const size_t row = (size_t)(blk < a.n_rows ? blk : a.n_rows - 1) * ns;
+                const bool reread = t == 0 || r0 == 0 || ragged || was_ragged;
+                was_ragged = ragged;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int si = warp * 4 + q, o = si * kTP + lane;
+                    if (si < n_cta) {
+                        if (reread) cq[q] = rows[row + s0 + si];
+                        const float (*A)[kPlane] = sm.A[t & 1];
+                        const L::DetOut d{A[0][o], A[1][o], A[2][o], A[3][o], A[4][o], A[5][o], A[6][o]};
+                        const L::Ctl c = L::control(cq[q], d);
+                        sm.Bc[t & 1][o] = c.curvN;
+                        float (*B)[kPlane] = sm.Bq[t % 3];
+                        B[0][o] = c.thrN; B[1][o] = c.gate; B[2][o] = c.mE1; B[3][o] = c.airMix;
+                    }
+                }
+            }
+            if (i >= kLag) {                             // mix and outputs of tile i - 4
+                const int t = i - kLag;
+                const int64_t nn = (int64_t)t * 32 + lane;
+                if (nn < n) {
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const int si = warp * 4 + q, o = si * kTP + lane;
+                        if (si < n_cta) {
+                            const float* x = a.in + (size_t)(s0 + si) * 2 * a.row_stride + nn;
+                            float* y = a.out + (size_t)(s0 + si) * 2 * a.row_stride + nn;
+                            const float inL = x[0], inR = x[a.row_stride];
+                            const float (*B)[kPlane] = sm.Bq[t % 3];
+                            const L::Ctl c{0.0f, B[0][o], B[1][o], B[2][o], B[3][o]};
+                            const L::Hf h{sm.D[t & 1][0][o], sm.D[t & 1][1][o], sm.D[t & 1][2][o]};
+                            float ov[2];
+                            L::mix(k, c, sm.C[t & 1][o], h, inL, inR, ov);
+                            y[0] = ov[0]; y[a.row_stride] = ov[1];
+                        }
+                    }
+                }
+            }
+            __syncthreads();
+        }
+    } else {
+        const int role = warp - kMapWarps;               // 0: detector (R1), 1: envelope (R2), 2: bands (R3)
+        const int lag = role == 0 ? 1 : 3;
+        const bool live = lane < n_cta;
+        const size_t s = (size_t)(s0 + (live ? lane : 0));
+        // State words (faust::Var::State): amount 0, sens 1, detL 2-3, detR 4-5, hf1L 6-7, hf2L 8-9, hf1R 10-11, hf2R 12-13, airZ 14-15,
+        // hfLvl 16, sm1L 17, sm2L 18, sm1R 19, sm2R 20, s1L 21, s2L 22, s1R 23, s2R 24, env 25, noise 26
+        L::State m{};
+        if (role == 0) {
+            m.amount = ldw(0, s); m.sens = ldw(1, s); m.detL = {ldw(2, s), ldw(3, s)}; m.detR = {ldw(4, s), ldw(5, s)};
+            m.hfLvl = ldw(16, s); m.sm1L = ldw(17, s); m.sm2L = ldw(18, s); m.sm1R = ldw(19, s); m.sm2R = ldw(20, s);
+            m.s1L = ldw(21, s); m.s2L = ldw(22, s); m.s1R = ldw(23, s); m.s2R = ldw(24, s);
+        } else if (role == 1) {
+            m.env = ldw(25, s);
+        } else {
+            m.hf1L = {ldw(6, s), ldw(7, s)}; m.hf2L = {ldw(8, s), ldw(9, s)}; m.hf1R = {ldw(10, s), ldw(11, s)}; m.hf2R = {ldw(12, s), ldw(13, s)};
+            m.airZ = {ldw(14, s), ldw(15, s)}; m.noise = (int)a.state[26 * ns + s];
+        }
+        L::Slow c = rows[s];
+        int64_t blk_end = a.block_len;
+        for (int i = 0; i < n_tiles + kLag; ++i) {
+            const int t = i - lag;
+            if (live && t >= 0 && t < n_tiles) {
+                const int64_t f0 = (int64_t)t * 32;
+                const int nv = (int)min((int64_t)32, n - f0);
+                const int o = lane * kTP;
+                if (role == 0) {
+#pragma unroll 4
+                    for (int f = 0; f < nv; ++f) {
+                        if (f0 + f >= blk_end) {         // a new host block: its slider-rate row (the last row persists)
+                            const int64_t b = (f0 + f) / a.block_len;
+                            blk_end = (b + 1) * a.block_len;
+                            c = rows[(size_t)(b < a.n_rows ? b : a.n_rows - 1) * ns + s];
+                        }
+                        const L::DetOut d = L::detector(m, c, k, sm.IN[t & 3][0][o + f], sm.IN[t & 3][1][o + f]);
+                        float (*A)[kPlane] = sm.A[t & 1];
+                        A[0][o + f] = d.amount; A[1][o + f] = d.sens; A[2][o + f] = d.hfLvl; A[3][o + f] = d.lapL; A[4][o + f] = d.denomL;
+                        A[5][o + f] = d.lapR; A[6][o + f] = d.denomR;
+                    }
+                } else if (role == 1) {
+#pragma unroll 8
+                    for (int f = 0; f < nv; ++f) sm.C[t & 1][o + f] = L::envelope(m, k, sm.Bc[t & 1][o + f]);
+                } else {
+#pragma unroll 4
+                    for (int f = 0; f < nv; ++f) {
+                        const L::Hf h = L::bands(m, k, sm.IN[t & 3][0][o + f], sm.IN[t & 3][1][o + f]);
+                        sm.D[t & 1][0][o + f] = h.hfL; sm.D[t & 1][1][o + f] = h.hfR; sm.D[t & 1][2][o + f] = h.air;
+                    }
+                }
+            }
+            __syncthreads();
+        }
+        if (live) {
+            if (role == 0) {
+                stw(0, s, m.amount); stw(1, s, m.sens); stw(2, s, m.detL.s1); stw(3, s, m.detL.s2); stw(4, s, m.detR.s1); stw(5, s, m.detR.s2);
+                stw(16, s, m.hfLvl); stw(17, s, m.sm1L); stw(18, s, m.sm2L); stw(19, s, m.sm1R); stw(20, s, m.sm2R);
+                stw(21, s, m.s1L); stw(22, s, m.s2L); stw(23, s, m.s1R); stw(24, s, m.s2R);
+            } else if (role == 1) {
+                stw(25, s, m.env);
+            } else {
+                stw(6, s, m.hf1L.s1); stw(7, s, m.hf1L.s2); stw(8, s, m.hf2L.s1); stw(9, s, m.hf2L.s2); stw(10, s, m.hf1R.s1); stw(11, s, m.hf1R.s2);
+                stw(12, s, m.hf2R.s1); stw(13, s, m.hf2R.s2); stw(14, s, m.airZ.s1); stw(15, s, m.airZ.s2); a.state[26 * ns + s] = (unsigned)m.noise;
+            }
+        }
+    }
+}
+static_assert(sizeof(faust::Var::State) == 27 * 4 && offsetof(faust::Var::State, hfLvl) == 16 * 4 && offsetof(faust::Var::State, env) == 25 * 4,
+              "var_tiled_kernel addresses the state words of faust::Var::State by number");
+
 template <class L> struct TiledLaunch { static int go(const FaustArgs&, const typename L::Konst&, cudaStream_t) { return 0; } };        // 0 = no tiled kernel for this leaf
+template <> struct TiledLaunch<faust::Var> {
+    static int go(const FaustArgs& a, const faust::Var::Konst& k, cudaStream_t st)
+    {
+        static DeviceOnce attr_once;
+        if (attr_once.pending()) {
+            if (!cuda_ok(cudaFuncSetAttribute(var_tiled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(var::Smem)), "VAR smem attr")) return -1;
+            attr_once.mark();
+        }
+        var_tiled_kernel<<<(unsigned)((a.n_streams + var::kStreams - 1) / var::kStreams), var::kThreads, sizeof(var::Smem), st>>>(a, k);
+        return cuda_ok(cudaGetLastError(), "var_tiled_kernel") ? 1 : -1;
+    }
+};
 template <> struct TiledLaunch<faust::Red> {
     static int go(const FaustArgs& a, const faust::Red::Konst& k, cudaStream_t st)
     {
