@@ -69,6 +69,9 @@ def run(args, ctx, sub=False):
     rank, world, local = ctx.rank, ctx.world, ctx.local
     have = set(za_gpu.plugin_keys())
     leaves = [k for k in CFG5_LEAVES if k in have]
+    for ov in getattr(args, "option", None) or []:          # --option only=A+B+C: a subset of the leaves (experiments; not cfg5)
+        if ov.startswith("only="):
+            leaves = [k for k in leaves if k in ov[5:].split("+")]
     not_built = [k for k in CFG5_LEAVES if k not in have]
     total = (args.streams if not sub and args.streams else TOTAL_STREAMS)
     per_leaf = total // world // len(leaves)
@@ -180,13 +183,16 @@ def run(args, ctx, sub=False):
         clk.start()
     l0 = sum(j["bp"].launch_count() for j in jobs)
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    host_issue_ms = 0.0
     for i in range(steps):
         gen(warm + i)                               # the next time chunk of every stream (outside the step's events)
         fence()
         ev[i][0].record(main_stream)
         for j in jobs:
             j["st"].wait_event(ev[i][0])
+        t_h = time.perf_counter()
         step()
+        host_issue_ms += (time.perf_counter() - t_h) * 1e3 / steps      # host time to issue the step (the GPU is not waited for)
         fence()
         ev[i][1].record(main_stream)
     torch.cuda.synchronize()
@@ -248,7 +254,7 @@ def run(args, ctx, sub=False):
         "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
         "roofline": {"bound": "hbm", "achieved": ach, "peak": ctx.peak, "unit": "GB/s", "frac": ach / ctx.peak, "peak_source": ctx.peak_kind,
                      "traffic": None, "kernel": "all leaves' kernels of one step, overlapped", "kernel_ms_per_launch": ms,
-                     "algorithmic_bytes_per_launch": alg_bytes, "per_leaf_kernel_ms": per_leaf_ms},
+                     "algorithmic_bytes_per_launch": alg_bytes, "per_leaf_kernel_ms": per_leaf_ms, "host_issue_ms_per_step": host_issue_ms},
         "cpu_baseline": cpu, "parity_spot_check": parity, "output_checksums_chunk0": sums,
     }
 

@@ -25,6 +25,10 @@ CAPS = [
      "python tools/prof_run.py --plugin SOMA --streams 5041 --seconds 1 --reps 2", 5041 * 48000, None),
     ("r02_rtt_staged", "rtt_staged", "translated leaf RTT fp32 (8 inputs, 2 outputs) as an 8-stage pipeline (`jsfx_staged_kernel`, 2-frame batches)",
      "python tools/prof_run.py --plugin RTT --streams 5041 --seconds 1 --reps 2", 5041 * 48000, None),
+    ("r02_red_tiled", "red_tiled", "Faust leaf RED fp32 (6 in / 6 out), tiled kernel (`red_tiled_kernel`: 8 map warps lane = frame + 2 recurrence warps lane = stream per 32-stream CTA)",
+     "python tools/prof_run.py --plugin RED --streams 5041 --seconds 1 --reps 2", 5041 * 48000, None),
+    ("r02_var_tiled", "var_tiled", "Faust leaf VAR fp32, tiled kernel (`var_tiled_kernel`: 4 map warps lane = frame + 3 recurrence warps lane = stream per 16-stream CTA)",
+     "python tools/prof_run.py --plugin VAR --streams 5041 --seconds 1 --reps 2", 5041 * 48000, None),
     ("r02_gts", "gts", "Faust leaf GTS fp32 (`gts_kernel`: time-parallel 257-tap Gaussian FIR rebuilt per frame)",
      "python bench.py --workload gts --seconds 2 --steps 1 --warmup 3 --no-cpu --no-e2e --no-parity", 4096 * 96000, "gts"),
 ]
