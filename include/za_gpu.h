@@ -145,7 +145,11 @@ ZA_API int za_gpu_last_kernel_ms(za_gpu_handle h, double* ms, int* launches);
 /* Tuning knobs for experiments: name = "force_generic_io" | "warps_per_stream" | "host_chunk_frames" |
  * "tile_buffers" (1|2, packed fp32 kernel) | "scalar_f32" (1 = fp32 on the scalar-FFMA kernel) |
  * "heap_slots" (translated leaves: use a smaller mem[] heap than the plugin was sized for; an access beyond it fails the
- * call -- ZA_ERR_STATE, "mem[] index beyond the heap" -- on that call (host memory) or on the next call / za_gpu_sync). */
+ * call -- ZA_ERR_STATE, "mem[] index beyond the heap" -- on that call (host memory) or on the next call / za_gpu_sync) |
+ * "scalar_f32" also: 1 = the generic stream-per-thread kernel for the Faust leaves that have a tiled one (RED, VAR, ClickBeGoneSG),
+ * 1 / 2 = the older EasyExpander fp32 kernels | "unstaged" (1 = translated leaves with a stage pipeline -- RTT, SOMA, ATTACK --
+ * on the one-thread-per-stream kernel; same bits in float64) | "lanes_per_warp" (8 | 16: streams per warp of the stream-per-thread
+ * kernels) | "role_off" (EasyExpander v3 role ablation; measurement only: outputs are not valid). */
 ZA_API int za_gpu_set_option(za_gpu_handle h, const char* name, int value);
 
 /* ---- one-shot form sketched in BASELINE.json north_star ------------------------------------ */
