@@ -672,14 +672,23 @@ __global__ void __launch_bounds__(128, 1) jsfx_process_kernel(const GenLaunch a)
 // frames per audio tile.  (16 for the 8-input RTT, which leaves its rings room for 5-frame instead of 2-frame batches, was
 // measured: 45.7 ms against 27.2 ms per 5041 x 1 s -- the first stage's warp pays for twice the copy instructions.)
 template <class S> __host__ __device__ constexpr int staged_tile_frames() { return 32; }
+// input tiles: two (the next one on its way while this one is computed), or ONE where many input channels (RTT: 8) would leave
+// the rings room for 2-frame batches only -- the first stage then waits out one copy latency per 32 frames, which it has time for
+template <class S> __host__ __device__ constexpr int staged_in_tiles() { return S::kIn > 4 ? 1 : 2; }
 template <class S> __host__ __device__ constexpr size_t staged_fixed_smem()
 {
-    return (size_t)(2 * S::kIn + S::kOut) * 32 * (staged_tile_frames<S>() + 1) * sizeof(float) + 16 * 32 * sizeof(unsigned);
+    return (size_t)(staged_in_tiles<S>() * S::kIn + S::kOut) * 32 * (staged_tile_frames<S>() + 1) * sizeof(float) + 16 * 32 * sizeof(unsigned);
 }
+// Shared-memory budget of a stage-pipeline CTA (two CTAs per SM at 110 KB).  72 KB was measured too (more room for other
+// kernels' CTAs in the cfg5 mix): the mixed step stays at 149-150 ms, SOMA alone goes 27.8 -> 30.4 ms with its shorter batches.
+#ifndef ZA_STAGED_SMEM_KB
+#define ZA_STAGED_SMEM_KB 110
+#endif
+constexpr size_t kStagedSmemBudget = (size_t)ZA_STAGED_SMEM_KB * 1024;
 template <class S, typename R> __host__ __device__ constexpr int staged_frames()     // frames per batch: two CTAs per SM (110 KB each)
 {
     int f = 32;
-    while (f > 2 && (size_t)S::Staged::kMailSlots * f * 32 * sizeof(R) + staged_fixed_smem<S>() > 110 * 1024) --f;
+    while (f > 2 && (size_t)S::Staged::kMailSlots * f * 32 * sizeof(R) + staged_fixed_smem<S>() > kStagedSmemBudget) --f;
     return f;
 }
 template <class S, typename R> __host__ __device__ constexpr size_t staged_smem()
@@ -697,14 +706,15 @@ __device__ __forceinline__ void staged_role(const GenLaunch& a, R* mb, float* ti
     const int s = s0 + lane;
     const bool live = s < a.n_streams;
     const int ns_cta = min(32, a.n_streams - s0);
-    float* const out_tile = tiles + 2 * kTile;
+    constexpr int kInTiles = staged_in_tiles<S>();
+    float* const out_tile = tiles + kInTiles * kTile;
     Rt<R> c;
     R v[S::kVars];
     bool valid = false;
     if (live) {
         ctx_open<S, R>(c, v, a, s);
         c.pf = 1;
-        c.mtw = reinterpret_cast<unsigned*>(tiles + (2 * S::kIn + S::kOut) * 32 * kP) + lane;
+        c.mtw = reinterpret_cast<unsigned*>(tiles + (kInTiles * S::kIn + S::kOut) * 32 * kP) + lane;
         valid = reinterpret_cast<const R*>(a.state)[(long long)(S::kVars + 64) * a.n_streams + s] != (R)0;
     }
     auto fetch = [&](float* tile, int64_t frame0, int nf) {
@@ -721,7 +731,7 @@ __device__ __forceinline__ void staged_role(const GenLaunch& a, R* mb, float* ti
     int nb = (int)min((int64_t)a.block_len, a.n_frames - pos);
     int buf = 0;
     BatchMod bt;
-    if (first && a.n_frames > 0) fetch(tiles, 0, min(kF, nb));
+    if (first && kInTiles == 2 && a.n_frames > 0) fetch(tiles, 0, min(kF, nb));
     for (int blk = 0; pos < a.n_frames; ++blk) {
         if (live) {
             if (a.n_rows > 0) {
@@ -738,7 +748,11 @@ __device__ __forceinline__ void staged_role(const GenLaunch& a, R* mb, float* ti
         for (int f0 = 0; f0 < nb; f0 += kF) {
             const int nf = min(kF, nb - f0);
             const float* tile = tiles + buf * kTile;
-            if (first) {
+            if (first && kInTiles == 1) {
+                fetch(tiles, pos + f0, nf);
+                asm volatile("cp.async.wait_group 0;" ::: "memory");
+                __syncwarp();
+            } else if (first) {
                 const bool more_here = f0 + kF < nb;
                 const int64_t nx0 = more_here ? pos + f0 + kF : pos + nb;
                 const int nxf = more_here ? min(kF, nb - f0 - kF) : min(kF, nb_next);
@@ -784,7 +798,7 @@ __device__ __forceinline__ void staged_role(const GenLaunch& a, R* mb, float* ti
                 }
                 __syncwarp();
             }
-            if (first) { __syncwarp(); buf ^= 1; }
+            if (first) { __syncwarp(); if (kInTiles == 2) buf ^= 1; }
         }
         pos += nb;
         nb = nb_next;
