@@ -679,6 +679,11 @@ template <class S> __host__ __device__ constexpr size_t staged_fixed_smem()
 {
     return (size_t)(staged_in_tiles<S>() * S::kIn + S::kOut) * 32 * (staged_tile_frames<S>() + 1) * sizeof(float) + 16 * 32 * sizeof(unsigned);
 }
+// CTAs per SM the stage pipelines are compiled for (register cap): two for five and more stages.  (Three -- 85-113 registers
+// per thread, with a 72 KB shared-memory budget -- is a measurement build: -DZA_STAGED_MIN_CTAS\(K\)=3.)
+#ifndef ZA_STAGED_MIN_CTAS
+#define ZA_STAGED_MIN_CTAS(K) ((K) > 4 ? 2 : 1)
+#endif
 // Shared-memory budget of a stage-pipeline CTA (two CTAs per SM at 110 KB).  72 KB was measured too (more room for other
 // kernels' CTAs in the cfg5 mix): the mixed step stays at 149-150 ms, SOMA alone goes 27.8 -> 30.4 ms with its shorter batches.
 #ifndef ZA_STAGED_SMEM_KB
@@ -829,7 +834,7 @@ __device__ __forceinline__ void staged_pick(const GenLaunch& a, R* mb, float* ti
 }
 
 template <class S, typename R, bool TAP>
-__global__ void __launch_bounds__(32 * S::Staged::kStages, S::Staged::kStages > 4 ? 2 : 1) jsfx_staged_kernel(const GenLaunch a)
+__global__ void __launch_bounds__(32 * S::Staged::kStages, ZA_STAGED_MIN_CTAS(S::Staged::kStages)) jsfx_staged_kernel(const GenLaunch a)
 {
     extern __shared__ __align__(16) unsigned char staged_smem_raw[];
     R* mb = reinterpret_cast<R*>(staged_smem_raw);

@@ -24,6 +24,9 @@ if os.environ.get("ZA_EE_KQ"):          # measurement builds of the EasyExpander
     PER_FILE["k_easyexpander_v3.cu"] = ["-DZA_EE_KQ=" + os.environ["ZA_EE_KQ"]]
 if os.environ.get("ZA_EE_PPL"):         # ... and band pairs per band-warp lane (1 or 2)
     PER_FILE.setdefault("k_easyexpander_v3.cu", []).append("-DZA_EE_PPL=" + os.environ["ZA_EE_PPL"])
+if os.environ.get("ZA_STAGED_CTAS"):    # measurement builds of the stage pipelines: CTAs per SM they are compiled for, shared-memory budget in KB
+    for _f in ("g_RTT.cu", "g_SOMA.cu", "g_ATTACK.cu"):
+        PER_FILE[_f] = ["-DZA_STAGED_MIN_CTAS(K)=" + os.environ["ZA_STAGED_CTAS"], "-DZA_STAGED_SMEM_KB=" + os.environ.get("ZA_STAGED_SMEM_KB", "110")]
 
 
 def sources():
