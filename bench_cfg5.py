@@ -32,8 +32,11 @@ CFG5_LEAVES = ["EasyExpander", "RTT", "SOMA", "ATTACK", "ERBTilt", "SpectralStab
 #   5 (default)  no phases: all 13 leaves at once, the long latency-bound stream-per-thread kernels launched first, SOMA / RTT /
 #                VAR on high-priority CUDA streams.  Measured on B200 after ERBTilt / SpectralStabilizer / ClickBeGoneSG got
 #                their own kernels: 165 ms per step against 257 ms for the two-phase schedule on the same box (SOMA takes
-#                105 ms alone and ~150 ms inside the mix, and it is what the step now waits for).
-#   4            as 5 without stream priorities (187-190 ms); `--option order=K` picks another launch order (179-213 ms).
+#                105 ms alone and ~150 ms inside the mix, and it is what the step now waits for).  With the stage pipelines
+#                (SOMA / RTT / ATTACK), the tiled RED / VAR kernels and the next chunk's generators kept out of the timed
+#                region: 118 ms, and the schedule hardly matters any more.
+#   4            as 5 without stream priorities (187-190 ms then, 119 now); `--option order=K` picks another launch order
+#                (179-213 ms then, 118-126 now).
 #   0            the round-1 two-phase schedule: A = everything but PHASE_B, then B = the translated leaf that keeps its
 #                state in a mem[] heap (SOMA) alone -- shared memory is carved out of the same 228 KB as the L1, and while the
 #                heap leaves SpectralStabilizer / ERBTilt were still translated they ran 3x slower inside a free-for-all mix.
