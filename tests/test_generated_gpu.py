@@ -337,7 +337,7 @@ def test_streams_per_warp_does_not_change_a_bit(gpu, key, prec):
             assert np.array_equal(outs[lanes][2][n], v, equal_nan=True), (lanes, n)
 
 
-STAGED = ["SOMA", "RTT", "ATTACK"]                                         # leaves the translator cuts into a stage pipeline (jsfxc.py::STAGE_CUTS)
+STAGED = ["SOMA", "RTT", "ATTACK", "SaliencePush", "ADS"]                                         # leaves the translator cuts into a stage pipeline (jsfxc.py::STAGE_CUTS)
 
 
 @pytest.mark.parametrize("key", STAGED)

@@ -19,6 +19,34 @@ if not cuts:
         what = n[2][1] if n[0] == "assign" and n[2][0] == "var" else n[0]
         print(f"{i:4d} {sl[i + 1] - sl[i]:5d} lines  {what}")
     sys.exit(0)
+if cuts and cuts[0] == "--auto":             # --auto K [+key ...]: K stages with the smallest largest stage (emitted lines) over the legal cut points
+    import functools
+    K, allow = int(cuts[1]), tuple(c[1:] for c in cuts[2:] if c.startswith("+"))
+    nch = max(u.n_in, u.n_out, (max(u.used_spl) + 1) if u.used_spl else 0, 1)
+    legal = []
+    for i in range(1, len(prog)):
+        try:
+            jsfxc.plan_stages(u, [i], nch, u.n_out, allow); legal.append(i)
+        except ValueError:
+            pass
+    pts = [0] + legal + [len(prog)]
+
+    @functools.lru_cache(None)
+    def best(ai, k):
+        if k == 1:
+            return (sl[pts[-1]] - sl[pts[ai]], ())
+        res = (10 ** 9, ())
+        for bi in range(ai + 1, len(pts) - 1):
+            c = sl[pts[bi]] - sl[pts[ai]]
+            if c >= res[0]:
+                break
+            r = best(bi, k - 1)
+            if max(c, r[0]) < res[0]:
+                res = (max(c, r[0]), (pts[bi],) + r[1])
+        return res
+    m, found = best(0, K)
+    print(f"{len(legal)} legal cut points of {len(prog) - 1}; best {K} stages: cuts {list(found)}, largest stage {m} lines")
+    cuts = [str(c) for c in found] + ["+" + a_ for a_ in allow]
 allow = tuple(c[1:] for c in cuts if c.startswith("+"))
 moves = tuple(c[1:] for c in cuts if c.startswith("^"))          # ^name: hoist the last assignment to name
 cuts = [c for c in cuts if c[0] not in "+^"]

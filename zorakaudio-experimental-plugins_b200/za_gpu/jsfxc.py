@@ -815,6 +815,10 @@ STAGE_CUTS = {
     # ATTACK reuses its temporaries (s, v, oldvS) in every band block, so its cuts are statement numbers: band split | slopes of
     # the low and mid band | slopes of the high band + magnitudes | reference followers | ratios | envelopes | gains + output
     "ATTACK": ([20, 52, 80, 92, 104, 105], ()),
+    # SaliencePush and ADS (no heap, no rand): cuts chosen by `tools/stage_plan.py <key> <file> --auto K`, which balances the
+    # emitted lines per stage over the legal cut points
+    "SaliencePush": ([20, 35, 45, 58, 69], ()),
+    "ADS": ([21, 38, 56, 71, 94, 112, 130], ()),
 }
 
 
