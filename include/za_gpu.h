@@ -147,8 +147,8 @@ ZA_API int za_gpu_last_kernel_ms(za_gpu_handle h, double* ms, int* launches);
  * "heap_slots" (translated leaves: use a smaller mem[] heap than the plugin was sized for; an access beyond it fails the
  * call -- ZA_ERR_STATE, "mem[] index beyond the heap" -- on that call (host memory) or on the next call / za_gpu_sync) |
  * "scalar_f32" also: 1 = the generic stream-per-thread kernel for the Faust leaves that have a tiled one (RED, VAR, ClickBeGoneSG),
- * 1 / 2 = the older EasyExpander fp32 kernels | "unstaged" (1 = translated leaves with a stage pipeline -- RTT, SOMA, ATTACK, ADS, SaliencePush --
- * on the one-thread-per-stream kernel; same bits in float64) | "lanes_per_warp" (8 | 16: streams per warp of the stream-per-thread
+ * 1 / 2 = the older EasyExpander fp32 kernels | "unstaged" (translated leaves with a stage pipeline -- RTT, SOMA, ATTACK, ADS, SaliencePush: 1 = the
+ * one-thread-per-stream kernel, 2 = the pipeline whatever the batch size, 0 = picked by batch size; same bits in float64) | "lanes_per_warp" (8 | 16: streams per warp of the stream-per-thread
  * kernels) | "role_off" (EasyExpander v3 role ablation; measurement only: outputs are not valid). */
 ZA_API int za_gpu_set_option(za_gpu_handle h, const char* name, int value);
 

@@ -870,7 +870,18 @@ template <class S> bool launch_process(const GenLaunch& a, int precision, cudaSt
     // concurrent cfg5 mix loses 15 % with narrow warps (a warp with 8 live lanes costs a full issue slot).  Only a shorter
     // chain per frame or time-parallel kernels (the scan kernels) make these leaves faster.
     if constexpr (S::Staged::kStages > 1) {
-        if (!a.unstaged) return launch_staged<S>(a, precision, st);
+        // The pipeline holds 32 streams per CTA and two CTAs per SM.  Leaves whose one-thread kernel runs four warps per CTA
+        // (no heap, at most four channels) catch up once the batch is more than that: measured on B200 (0.5 s, pipeline /
+        // one-thread): SaliencePush 9472 streams 10.4 / 14.5 ms, 18 944: 20.8 / 14.5, 37 888: 41.6 / 29.0; ATTACK 8.8 / 17.7,
+        // 17.6 / 17.7, 35.1 / 35.3.  RTT (8 inputs) and SOMA (heap) stay 1.5-2.8x ahead up to 37 888 streams (13.8 / 27.8 ...
+        // 55.2 / 81.5; 13.4 / 37.4 ... 55.0 / 86.1).  Option "unstaged": 0 = this rule, 1 = one-thread kernel, 2 = pipeline.
+        bool staged = a.unstaged != 1;
+        if (a.unstaged == 0 && GenWarps<S>::value == 4) {
+            int dev = 0, n_sm = 148;
+            if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
+            staged = a.n_streams <= 2 * 32 * n_sm;
+        }
+        if (staged) return launch_staged<S>(a, precision, st);
     }
     GenLaunch b = a;
     int L = a.lanes, W = GenWarps<S>::value;

@@ -155,7 +155,7 @@ struct GenLaunch {
     int64_t fft_scratch;                           // slots of FFT scratch per stream behind the heap (0: the script calls no FFT hook)
     const double* tw;                              // device: e^{-2 pi i k / 32768}, k < 16384, (cos, -sin) pairs
     int lanes;                                     // streams per warp of jsfx_process_kernel: 8 / 16 / 32, 0 = picked at launch
-    int unstaged;                                  // 1 = one thread per stream even where the leaf has a stage pipeline (option "unstaged")
+    int unstaged;                                  // leaves with a stage pipeline: 0 = picked by batch size, 1 = one thread per stream, 2 = pipeline (option "unstaged")
 };
 struct GenDesc {
     const char* key; const char* slider_text;
