@@ -146,7 +146,8 @@ ZA_API int za_gpu_last_kernel_ms(za_gpu_handle h, double* ms, int* launches);
  * "tile_buffers" (1|2, packed fp32 kernel) | "scalar_f32" (1 = fp32 on the scalar-FFMA kernel) |
  * "heap_slots" (translated leaves: use a smaller mem[] heap than the plugin was sized for; an access beyond it fails the
  * call -- ZA_ERR_STATE, "mem[] index beyond the heap" -- on that call (host memory) or on the next call / za_gpu_sync) |
- * "scalar_f32" also: 1 = the generic stream-per-thread kernel for the Faust leaves that have a tiled one (RED, VAR, ClickBeGoneSG),
+ * "scalar_f32" also: 1 = the generic stream-per-thread kernel for the Faust leaves that have a tiled one (RED, VAR, ClickBeGoneSG;
+ * 2 = the tiled one whatever the batch size, 0 = VAR switches to the generic kernel above ~160 streams per SM),
  * 1 / 2 = the older EasyExpander fp32 kernels | "unstaged" (translated leaves with a stage pipeline -- RTT, SOMA, ATTACK, ADS, SaliencePush: 1 = the
  * one-thread-per-stream kernel, 2 = the pipeline whatever the batch size, 0 = picked by batch size; same bits in float64) | "lanes_per_warp" (8 | 16: streams per warp of the stream-per-thread
  * kernels) | "role_off" (EasyExpander v3 role ablation; measurement only: outputs are not valid). */

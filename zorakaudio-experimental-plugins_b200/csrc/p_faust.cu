@@ -30,6 +30,7 @@ struct FaustArgs {
     const void* slow;           // [n_rows][n_streams] Leaf::Slow
     unsigned* state;            // [words][n_streams]
     int lanes;                  // generic kernel: streams per warp (8 / 16 / 32)
+    int force_tiled;            // option scalar_f32 = 2: the tiled kernel whatever the batch size
 };
 
 constexpr int kP = 33;
@@ -654,6 +655,15 @@ template <class L> struct TiledLaunch { static int go(const FaustArgs&, const ty
 template <> struct TiledLaunch<faust::Var> {
     static int go(const FaustArgs& a, const faust::Var::Konst& k, cudaStream_t st)
     {
+        // 16 streams per CTA, two CTAs per SM: the time grows with every 4736 streams, while the generic kernel (eight one-warp
+        // CTAs per SM) stays flat up to 37 888.  Measured per 0.5 s, tiled / generic: 9472 streams 6.0 / 15.5 ms, 18 944: 12.0 /
+        // 15.5, 37 888: 24.0 / 17.3 -- the generic kernel takes over at ~160 streams per SM.  (RED and ClickBeGoneSG tiled stay
+        // 1.8-5x ahead up to 37 888 streams.)
+        if (!a.force_tiled) {
+            int dev = 0, n_sm = 148;
+            if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
+            if (a.n_streams > 160 * n_sm) return 0;
+        }
         static DeviceOnce attr_once;
         if (attr_once.pending()) {
             if (!cuda_ok(cudaFuncSetAttribute(var_tiled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(var::Smem)), "VAR smem attr")) return -1;
@@ -758,9 +768,9 @@ public:
             if (slow_valid) h_slow_dev = h_slow;
         }
         if (n <= 0) return true;
-        FaustArgs a{in, out, stride, n, I.n_streams, I.block_len, nbq, d_slow, d_state, I.opt_lanes};
+        FaustArgs a{in, out, stride, n, I.n_streams, I.block_len, nbq, d_slow, d_state, I.opt_lanes, I.opt_scalar_f32 == 2};
         const bool timed = I.time_begin();
-        const int tiled = I.opt_scalar_f32 ? 0 : TiledLaunch<L>::go(a, k_, I.stream);      // option scalar_f32 = 1: the generic kernel for every leaf
+        const int tiled = I.opt_scalar_f32 == 1 ? 0 : TiledLaunch<L>::go(a, k_, I.stream);      // option scalar_f32 = 1: the generic kernel for every leaf, 2: the tiled one
         if (tiled < 0) return false;
         if (!tiled) {
             if (!launch_generic<L>(a, k_, I.stream)) return false;
