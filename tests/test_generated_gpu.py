@@ -375,3 +375,28 @@ def test_stage_pipeline_equals_the_one_thread_kernel(gpu, key, block):
     e_staged = dbfs_rms(res[(2, "f32")][0].astype(np.float64) - b[1])
     e_one = dbfs_rms(res[(1, "f32")][0].astype(np.float64) - b[1])
     assert e_staged < max(-100.0, e_one + 3.0), (e_staged, e_one)      # ATTACK's float32 slope detectors sit near -87 dBFS on these bursts either way
+
+
+@pytest.mark.parametrize("key", ["SOMA", "RTT"])
+def test_stage_pipeline_on_calls_shorter_than_its_depth(gpu, key):
+    """Calls of 1, 2, 3, 7, 33 and 64 frames in a row (fewer batches than the pipeline has stages: fill and drain overlap), then
+    one of 1500 (SOMA's look-ahead keeps the first ~100 output frames at zero): the float64 outputs and the checkpoint blob
+    after the last call equal the one-thread kernel's, bit for bit."""
+    ref = zo.RefPlugin(key)
+    ns, lens = 35, (1, 2, 3, 7, 33, 64, 1500)
+    x = wl.programme_bursts(ns, sum(lens), n_ch=ref.n_in)
+    base = np.tile(np.array([s["default"] for s in ref.sliders], np.float32), (ns, 1))
+    res = {}
+    for unstaged in (1, 2):
+        bp = gpu.BatchProcessor(key, ns, block_len=512, precision="f64").prepare(base)
+        bp.set_option("unstaged", unstaged)
+        taps, f0 = [], 0
+        for n in lens:
+            t = np.zeros((ns, ref.n_out, n))
+            bp.process(np.ascontiguousarray(x[:, :, f0:f0 + n]), tap64=t, params=base)
+            taps.append(t); f0 += n
+        res[unstaged] = (np.concatenate(taps, axis=2), bp.save_state())
+        bp.close()
+    assert np.array_equal(res[1][0].view(np.uint64), res[2][0].view(np.uint64))
+    assert np.array_equal(res[1][1], res[2][1])
+    assert np.abs(res[2][0]).max() > 0.0
